@@ -1,0 +1,708 @@
+// extract_kernels.cu — sm_100a kernels of the ORB extractor hot path.
+// Every kernel is batched over frames (blockIdx.y = frame) so that one launch covers a whole
+// batch of same-sized frames.  Integer arithmetic reproduces OpenCV 4.13's fixed-point paths bit
+// for bit; float arithmetic is written with explicit round-to-nearest intrinsics so nvcc cannot
+// contract it into FMAs the reference's build (-ffp-contract=off oracle) does not execute.
+#include "ygz_common.cuh"
+#include "orb_pattern.inc"
+
+namespace ygz {
+
+// =================================================================================================
+// K1 — pyramid level by cv::resize(INTER_LINEAR), 8UC1 (src/ORBextractor.cc:1139).
+// OpenCV's HResizeLinear/VResizeLinear fixed point: 11-bit coefficients, horizontal pass in int32,
+// vertical pass ((b0*(r0>>4))>>16 + (b1*(r1>>4))>>16 + 2) >> 2.  The coefficient tables are built on
+// the host (extractor.cu, makeResizeTables) with the double/float recipe of resize.cpp, so the
+// kernel is integer-only.  One thread produces 4 horizontally adjacent pixels (one 32-bit store).
+// Table entry X[dx] = {x0 | x1<<16, a0 | a1<<16}; Y[dy] = {y0 | y1<<16, b0 | b1<<16}.
+__global__ void __launch_bounds__(256) k_resize(const __grid_constant__ FrameGeom G, const DevBuffers B, int level) {
+    const LevelGeom &D = G.lv[level];
+    const LevelGeom &S = G.lv[level - 1];
+    const int f = blockIdx.z;
+    const int dx0 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int dy = blockIdx.y * 8 + threadIdx.y;
+    if (dx0 >= D.pitch || dy >= D.h) return;
+    const uint8_t *src = levelPtr(G, B, f, level - 1);
+    uint8_t *dst = B.pyr + (long long)f * G.slabBytes + D.off + (long long)dy * D.pitch + dx0;
+    const int sp = S.pitch;
+    uint32_t out = 0;
+    if (D.area2x) {  // ResizeAreaFast 2x2 mean
+        const uint8_t *s0 = src + (long long)(2 * dy) * sp, *s1 = s0 + sp;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int dx = min(dx0 + i, D.w - 1);
+            const int v = (s0[2 * dx] + s0[2 * dx + 1] + s1[2 * dx] + s1[2 * dx + 1] + 2) >> 2;
+            out |= (uint32_t)v << (8 * i);
+        }
+    } else {
+        const int2 ty = __ldg(B.tabs + D.tabY + dy);
+        const uint8_t *s0 = src + (long long)(ty.x & 0xffff) * sp;
+        const uint8_t *s1 = src + (long long)((uint32_t)ty.x >> 16) * sp;
+        const int b0 = (short)(ty.y & 0xffff), b1 = (short)((uint32_t)ty.y >> 16);
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int2 tx = __ldg(B.tabs + D.tabX + dx0 + i);  // table is padded to the pitch
+            const int x0 = tx.x & 0xffff, x1 = (uint32_t)tx.x >> 16;
+            const int a0 = (short)(tx.y & 0xffff), a1 = (short)((uint32_t)tx.y >> 16);
+            const int r0 = s0[x0] * a0 + s0[x1] * a1;
+            const int r1 = s1[x0] * a0 + s1[x1] * a1;
+            int v = (((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2;
+            v = min(max(v, 0), 255);
+            out |= (uint32_t)v << (8 * i);
+        }
+    }
+    *reinterpret_cast<uint32_t *>(dst) = out;  // pitch is a multiple of 64: padding bytes are scratch
+}
+
+int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nFrames, cudaStream_t s) {
+    const LevelGeom &D = G.lv[level];
+    dim3 block(32, 8), grid((D.pitch / 4 + 31) / 32, (D.h + 7) / 8, nFrames);
+    k_resize<<<grid, block, 0, s>>>(G, B, level);
+    return 1;
+}
+
+// =================================================================================================
+// K2 — per-cell FAST-9/16 + 3x3 NMS + threshold fallback (src/ORBextractor.cc:747-781 calling
+// cv::FAST twice per cell).  One CTA per cell.  The corner measure m (max over the 16 arcs of 9
+// contiguous circle pixels of min(v-p) resp. min(p-v)) does not depend on the threshold: a pixel
+// is a corner at threshold t iff m > t and its OpenCV score is m-1.  So the CTA computes m once for
+// the cell's detection area (the cell minus a 3-px frame), runs the in-cell NMS at iniThFAST, and
+// only if nothing survives runs it again at minThFAST — exactly the reference's "if empty, retry".
+// NMS neighbours outside the detection area count as 0, as in cv::FAST on the cell sub-image.
+// Survivors are appended (unordered) to the level's candidate array with an order key
+// (cell, y-in-cell, x-in-cell) that encodes the reference's vToDistributeKeys order, which is all
+// the quadtree needs from the order (its only order dependence is "first wins" on response ties).
+constexpr int kFastThreads = 128;
+constexpr int kCellMax = 64;                 // wCell, hCell < 60 always (width/floor(width/30))
+constexpr int kTilePitch = kCellMax + 8;     // image tile pitch (cell + 6, padded)
+constexpr int kScorePitch = kCellMax + 2;
+
+__device__ __forceinline__ int min3i(int a, int b, int c) { return min(min(a, b), c); }
+__device__ __forceinline__ int max3i(int a, int b, int c) { return max(max(a, b), c); }
+
+// m of the pixel at tile position p (pointer into the shared image tile).
+__device__ __forceinline__ int fastMeasure(const uint8_t *p) {
+    constexpr int P = kTilePitch;
+    const int v = p[0];
+    int d[16];
+    d[0] = v - p[3 * P];       d[1] = v - p[3 * P + 1];   d[2] = v - p[2 * P + 2];   d[3] = v - p[P + 3];
+    d[4] = v - p[3];           d[5] = v - p[-P + 3];      d[6] = v - p[-2 * P + 2];  d[7] = v - p[-3 * P + 1];
+    d[8] = v - p[-3 * P];      d[9] = v - p[-3 * P - 1];  d[10] = v - p[-2 * P - 2]; d[11] = v - p[-P - 3];
+    d[12] = v - p[-3];         d[13] = v - p[P - 3];      d[14] = v - p[2 * P - 2];  d[15] = v - p[3 * P - 1];
+    int lo3[16], hi3[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        lo3[k] = min3i(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+        hi3[k] = max3i(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+    }
+    int best = -256, worst = 256;  // max over arcs of min(d), min over arcs of max(d)
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        best = max(best, min3i(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]));
+        worst = min(worst, max3i(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]));
+    }
+    return max(best, -worst);
+}
+
+__device__ __forceinline__ int fastStored(int m, int t) { return m > t ? m - 1 : 0; }  // cv::FAST's score buffer
+
+__device__ __forceinline__ bool fastKeep(const uint8_t *sc, int t) {
+    constexpr int P = kScorePitch;
+    const int m = sc[0];
+    if (m <= t) return false;
+    const int s = m - 1;
+    return s > fastStored(sc[-1], t) && s > fastStored(sc[1], t) && s > fastStored(sc[-P - 1], t) &&
+           s > fastStored(sc[-P], t) && s > fastStored(sc[-P + 1], t) && s > fastStored(sc[P - 1], t) &&
+           s > fastStored(sc[P], t) && s > fastStored(sc[P + 1], t);
+}
+
+__global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+    __shared__ __align__(16) uint8_t tile[(kCellMax + 6) * kTilePitch];
+    __shared__ uint8_t score[(kCellMax + 2) * kScorePitch];
+    const int f = blockIdx.y;
+    int level = 0;
+    while (level + 1 < G.nlevels && (int)blockIdx.x >= G.lv[level + 1].cellStart) level++;
+    const LevelGeom &L = G.lv[level];
+    const int cell = blockIdx.x - L.cellStart;
+    const int ci = cell / L.nCols, cj = cell - ci * L.nCols;
+    // cell window (src/ORBextractor.cc:749-762); detection area = window minus 3 px
+    const int maxBX = L.w - kMinBorder, maxBY = L.h - kMinBorder;
+    const int iniY = kMinBorder + ci * L.hCell, iniX = kMinBorder + cj * L.wCell;
+    if (iniY >= maxBY - 3 || iniX >= maxBX - 6) return;
+    const int maxY = min(iniY + L.hCell + 6, maxBY), maxX = min(iniX + L.wCell + 6, maxBX);
+    const int tw = maxX - iniX, th = maxY - iniY;   // window size
+    const int dw = tw - 6, dh = th - 6;              // detection area size
+    if (dw <= 0 || dh <= 0) return;
+    const uint8_t *img = levelPtr(G, B, f, level);
+    for (int i = threadIdx.x; i < tw * th; i += kFastThreads) {
+        const int y = i / tw, x = i - y * tw;
+        tile[y * kTilePitch + x] = img[(long long)(iniY + y) * L.pitch + iniX + x];
+    }
+    for (int i = threadIdx.x; i < (dh + 2) * kScorePitch; i += kFastThreads) score[i] = 0;
+    __syncthreads();
+    const int minTh = G.minTh, iniTh = G.iniTh;
+    for (int i = threadIdx.x; i < dw * dh; i += kFastThreads) {
+        const int y = i / dw, x = i - y * dw;
+        const int m = fastMeasure(&tile[(y + 3) * kTilePitch + x + 3]);
+        score[(y + 1) * kScorePitch + x + 1] = (uint8_t)(m > minTh ? m : 0);
+    }
+    __syncthreads();
+    int any = 0;
+    for (int i = threadIdx.x; i < dw * dh; i += kFastThreads) {
+        const int y = i / dw, x = i - y * dw;
+        any |= fastKeep(&score[(y + 1) * kScorePitch + x + 1], iniTh);
+    }
+    const int t = __syncthreads_or(any) ? iniTh : minTh;
+    uint2 *cand = B.cand + (long long)f * G.candPerFrame + L.candOff;
+    int *counter = B.candCount + f * kMaxLevels + level;
+    const int lane = threadIdx.x & 31;
+    for (int i0 = 0; i0 < dw * dh; i0 += kFastThreads) {
+        const int i = i0 + threadIdx.x;
+        bool keep = false;
+        int y = 0, x = 0;
+        if (i < dw * dh) {
+            y = i / dw; x = i - y * dw;
+            keep = fastKeep(&score[(y + 1) * kScorePitch + x + 1], t);
+        }
+        const unsigned mask = __ballot_sync(0xffffffffu, keep);
+        if (mask == 0) continue;
+        int base = 0;
+        if (lane == __ffs(mask) - 1) base = atomicAdd(counter, __popc(mask));
+        base = __shfl_sync(0xffffffffu, base, __ffs(mask) - 1);
+        if (keep) {
+            const int slot = base + __popc(mask & ((1u << lane) - 1));
+            if (slot < L.candCap) {
+                const int m = score[(y + 1) * kScorePitch + x + 1];
+                const uint32_t ax = iniX + 3 + x, ay = iniY + 3 + y;  // absolute level coordinates
+                cand[slot] = make_uint2(ax | (ay << 12) | ((uint32_t)(m - 1) << 24),
+                                        ((uint32_t)cell << 12) | ((uint32_t)y << 6) | (uint32_t)x);
+            } else {
+                atomicOr(B.status, 1);
+            }
+        }
+    }
+}
+
+int launchFast(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s) {
+    if (G.totalCells == 0) return 0;
+    k_fast<<<dim3(G.totalCells, nFrames), kFastThreads, 0, s>>>(G, B);
+    return 1;
+}
+
+// =================================================================================================
+// K3 — DistributeOctTree (src/ORBextractor.cc:533-723) + DivideNode (:479-531), one CTA per
+// (frame, level), reproducing the reference's node list ORDER and split order exactly.
+//
+// The reference is a serial std::list algorithm; what it computes can be stated without the list:
+//  * a pass splits a set of parent nodes in a processing order r = 0..P-1; every non-empty child is
+//    push_front'ed in n1..n4 order, so after the pass the list reads: children of the LAST processed
+//    parent (n4..n1), ..., children of the first, then the untouched nodes in their old order;
+//  * phase 1 (:591-643) processes every multi-point node in list order; phase 2 (:649-699) takes the
+//    multi-point children of the previous pass, sorts them by (size, pointer) and splits from the
+//    largest down, stopping as soon as the list holds N nodes.  Pointer order is canonicalised to
+//    creation order (SURVEY.md §7 hard part 1), i.e. the push order of the previous pass (`seq`);
+//  * the final pick per node (:703-720) is the max response, first in key order on ties; key order
+//    inside a node is the original vToDistributeKeys order, carried here by the candidates' order key.
+// So points never move: each point carries the index of its node, and a pass is two sweeps over the
+// points (count children, relabel) plus block-wide scans over the node list.
+constexpr int kQtThreads = 512;
+
+struct QtSmem {
+    short4 *bA, *bB;      // node bounds x0,x1,y0,y1 (x = UL.x, y = UR.x, z = UL.y, w = BL.y)
+    int *cA, *cB;         // points per node
+    int *gA, *gB;         // seq (creation order in the latest pass) if multi-point child of it, else -1
+    int *procOrder;       // per list node: processing rank r or -1
+    int *byOrder;         // rank -> list node
+    int *childCnt;        // [4*r + q]
+    int *childIdx;        // [4*r + q] -> new list index
+    int *oldToNew;        // untouched node -> new list index
+    int *scanR, *scanU;   // scan scratch
+    int *misc;            // [0..31] warp sums, [32] nToExpand
+};
+
+__device__ __forceinline__ int qtQuadrant(uint32_t xyr, const short4 b) {
+    // DivideNode (:481-482, 512-523): halfX = ceil((UR.x-UL.x)/2), child by pt.x < UL.x+halfX etc.
+    const int x = (int)(xyr & 0xfff) - kMinBorder, y = (int)((xyr >> 12) & 0xfff) - kMinBorder;
+    const int mx = b.x + ((b.y - b.x + 1) >> 1), my = b.z + ((b.w - b.z + 1) >> 1);
+    return (x < mx ? 0 : 1) + (y < my ? 0 : 2);
+}
+
+// In-place exclusive scan of a[0..n) by the whole CTA; returns the total.  `ws` = 33 ints scratch.
+__device__ int qtScan(int *a, int n, int *ws) {
+    const int T = kQtThreads, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int chunk = (n + T - 1) / T;
+    const int b = min(tid * chunk, n), e = min(b + chunk, n);
+    int sum = 0;
+    for (int i = b; i < e; i++) sum += a[i];
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+    }
+    if (lane == 31) ws[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        int w = lane < T / 32 ? ws[lane] : 0;
+        int winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += v;
+        }
+        if (lane < T / 32) ws[lane] = winc - w;
+        if (lane == 31) ws[32] = winc;
+    }
+    __syncthreads();
+    int run = ws[wid] + inc - sum;
+    for (int i = b; i < e; i++) { const int v = a[i]; a[i] = run; run += v; }
+    const int total = ws[32];
+    __syncthreads();
+    return total;
+}
+
+// Sweep 1 of a pass: per processed parent (rank r), count the points falling in each quadrant.
+__device__ void qtCountChildren(const QtSmem &S, const short4 *bnd, int P, const uint2 *cand, const uint16_t *nodeOf, int np) {
+    for (int i = threadIdx.x; i < 4 * P; i += kQtThreads) S.childCnt[i] = 0;
+    __syncthreads();
+    for (int p = threadIdx.x; p < np; p += kQtThreads) {
+        const int nd = nodeOf[p];
+        const int r = S.procOrder[nd];
+        if (r >= 0) atomicAdd(&S.childCnt[4 * r + qtQuadrant(cand[p].x, bnd[nd])], 1);
+    }
+    __syncthreads();
+}
+
+// Rest of a pass: builds the new list (into b2/c2/g2) from the old one (b1/c1) given procOrder /
+// byOrder / childCnt for P processed parents, relabels the points.  Returns the new list size and
+// the number of multi-point children through *nToExpand.
+__device__ int qtCommit(const QtSmem &S, const short4 *b1, const int *c1, short4 *b2, int *c2, int *g2, int n, int P,
+                        const uint2 *cand, uint16_t *nodeOf, int np, int *nToExpand) {
+    const int tid = threadIdx.x;
+    for (int r = tid; r < P; r += kQtThreads) {
+        const int *c = &S.childCnt[4 * r];
+        S.scanR[r] = (c[0] > 0) + (c[1] > 0) + (c[2] > 0) + (c[3] > 0);
+    }
+    for (int i = tid; i < n; i += kQtThreads) S.scanU[i] = S.procOrder[i] < 0;
+    if (tid == 0) S.misc[33] = 0;
+    __syncthreads();
+    const int totalChildren = qtScan(S.scanR, P, S.misc);
+    const int untouched = qtScan(S.scanU, n, S.misc);
+    for (int r = tid; r < P; r += kQtThreads) {
+        const short4 pb = b1[S.byOrder[r]];
+        const int mx = pb.x + ((pb.y - pb.x + 1) >> 1), my = pb.z + ((pb.w - pb.z + 1) >> 1);
+        int seq = S.scanR[r], multi = 0;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const int cnt = S.childCnt[4 * r + q];
+            if (cnt > 0) {
+                const int pos = totalChildren - 1 - seq;
+                short4 cb;
+                cb.x = (q & 1) ? mx : pb.x; cb.y = (q & 1) ? pb.y : mx;
+                cb.z = (q & 2) ? my : pb.z; cb.w = (q & 2) ? pb.w : my;
+                b2[pos] = cb; c2[pos] = cnt; g2[pos] = cnt > 1 ? seq : -1;
+                S.childIdx[4 * r + q] = pos;
+                multi += cnt > 1;
+                seq++;
+            }
+        }
+        if (multi) atomicAdd(&S.misc[33], multi);
+    }
+    for (int i = tid; i < n; i += kQtThreads) {
+        if (S.procOrder[i] < 0) {
+            const int pos = totalChildren + S.scanU[i];
+            b2[pos] = b1[i]; c2[pos] = c1[i]; g2[pos] = -1;
+            S.oldToNew[i] = pos;
+        }
+    }
+    __syncthreads();
+    for (int p = tid; p < np; p += kQtThreads) {
+        const int nd = nodeOf[p];
+        const int r = S.procOrder[nd];
+        nodeOf[p] = (uint16_t)(r >= 0 ? S.childIdx[4 * r + qtQuadrant(cand[p].x, b1[nd])] : S.oldToNew[nd]);
+    }
+    *nToExpand = S.misc[33];
+    __syncthreads();
+    return totalChildren + untouched;
+}
+
+__global__ void __launch_bounds__(kQtThreads) k_quadtree(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+    extern __shared__ __align__(16) unsigned char qtRaw[];
+    const int level = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
+    const LevelGeom &L = G.lv[level];
+    int *keptCount = B.keptCount + f * kMaxLevels + level;
+    const int np = L.nCols == 0 ? 0 : min(B.candCount[f * kMaxLevels + level], L.candCap);
+    if (np == 0) { if (tid == 0) *keptCount = 0; return; }
+    const int C = G.maxListCap;
+    QtSmem S;
+    {
+        unsigned char *p = qtRaw;
+        S.bA = (short4 *)p; p += sizeof(short4) * C;
+        S.bB = (short4 *)p; p += sizeof(short4) * C;
+        S.cA = (int *)p; p += 4 * C;   S.cB = (int *)p; p += 4 * C;
+        S.gA = (int *)p; p += 4 * C;   S.gB = (int *)p; p += 4 * C;
+        S.procOrder = (int *)p; p += 4 * C;   S.byOrder = (int *)p; p += 4 * C;
+        S.childCnt = (int *)p; p += 16 * C;   S.childIdx = (int *)p; p += 16 * C;
+        S.oldToNew = (int *)p; p += 4 * C;
+        S.scanR = (int *)p; p += 4 * C;   S.scanU = (int *)p; p += 4 * C;
+        S.misc = (int *)p;
+    }
+    const uint2 *cand = B.cand + (long long)f * G.candPerFrame + L.candOff;
+    uint16_t *nodeOf = B.nodeOf + (long long)f * G.candPerFrame + L.candOff;
+    const int N = L.nTarget;
+    short4 *b1 = S.bA, *b2 = S.bB;
+    int *c1 = S.cA, *c2 = S.cB, *g1 = S.gA, *g2 = S.gB;
+
+    // ---- roots (:537-574): nIni roots of width hX over [0, maxX-minX) x [0, maxY-minY]; empty ones dropped
+    const int nIni = L.nIni;
+    const float hX = L.hX;
+    for (int i = tid; i < nIni; i += kQtThreads) S.childCnt[i] = 0;
+    __syncthreads();
+    for (int p = tid; p < np; p += kQtThreads) {
+        const int x = (int)(cand[p].x & 0xfff) - kMinBorder;
+        const int root = (int)__fdiv_rn((float)x, hX);
+        nodeOf[p] = (uint16_t)root;
+        atomicAdd(&S.childCnt[root], 1);
+    }
+    __syncthreads();
+    for (int i = tid; i < nIni; i += kQtThreads) S.scanU[i] = S.childCnt[i] > 0;
+    __syncthreads();
+    int n = qtScan(S.scanU, nIni, S.misc);
+    for (int i = tid; i < nIni; i += kQtThreads) {
+        const int cnt = S.childCnt[i];
+        if (cnt > 0) {
+            const int pos = S.scanU[i];
+            b1[pos] = make_short4((short)(int)__fmul_rn(hX, (float)i), (short)(int)__fmul_rn(hX, (float)(i + 1)), 0,
+                                  (short)(L.h - 2 * kMinBorder));
+            c1[pos] = cnt; g1[pos] = -1;
+        }
+    }
+    __syncthreads();
+    for (int p = tid; p < np; p += kQtThreads) nodeOf[p] = (uint16_t)S.scanU[nodeOf[p]];
+    __syncthreads();
+
+    // ---- main loop (:576-700)
+    bool finish = false;
+    while (!finish) {
+        const int prevSize = n;
+        // phase-1 pass: every multi-point node, in list order
+        for (int i = tid; i < n; i += kQtThreads) S.scanR[i] = c1[i] > 1;
+        __syncthreads();
+        int P = qtScan(S.scanR, n, S.misc);
+        for (int i = tid; i < n; i += kQtThreads) {
+            const bool e = c1[i] > 1;
+            S.procOrder[i] = e ? S.scanR[i] : -1;
+            if (e) S.byOrder[S.scanR[i]] = i;
+        }
+        __syncthreads();
+        int nToExpand = 0;
+        if (P > 0) {
+            qtCountChildren(S, b1, P, cand, nodeOf, np);
+            n = qtCommit(S, b1, c1, b2, c2, g2, n, P, cand, nodeOf, np, &nToExpand);
+            { short4 *t = b1; b1 = b2; b2 = t; } { int *t = c1; c1 = c2; c2 = t; } { int *t = g1; g1 = g2; g2 = t; }
+        }
+        if (n >= N || n == prevSize) {
+            finish = true;
+        } else if (n + nToExpand * 3 > N) {
+            // phase 2 (:649-699): latest multi-point children, largest first (later-created first among equals)
+            while (!finish) {
+                const int prevSize2 = n;
+                // compact the generation: gen entry e -> list node, keyed by (size, seq)
+                for (int i = tid; i < n; i += kQtThreads) S.scanR[i] = g1[i] >= 0;
+                __syncthreads();
+                const int F = qtScan(S.scanR, n, S.misc);
+                for (int i = tid; i < n; i += kQtThreads) if (g1[i] >= 0) S.oldToNew[S.scanR[i]] = i;
+                __syncthreads();
+                // rank r = number of generation nodes that sort after this one (processed earlier)
+                for (int i = tid; i < n; i += kQtThreads) S.procOrder[i] = -1;
+                __syncthreads();
+                for (int e = tid; e < F; e += kQtThreads) {
+                    const int i = S.oldToNew[e];
+                    const int sz = c1[i], sq = g1[i];
+                    int r = 0;
+                    for (int e2 = 0; e2 < F; e2++) {
+                        const int j = S.oldToNew[e2];
+                        const int sz2 = c1[j];
+                        r += (sz2 > sz) || (sz2 == sz && g1[j] > sq);
+                    }
+                    S.procOrder[i] = r;
+                    S.byOrder[r] = i;
+                }
+                __syncthreads();
+                qtCountChildren(S, b1, F, cand, nodeOf, np);
+                // the split loop breaks once the list holds N nodes: rank r is processed iff the list
+                // size after ranks < r is still below N
+                for (int r = tid; r < F; r += kQtThreads) {
+                    const int *c = &S.childCnt[4 * r];
+                    S.scanU[r] = (c[0] > 0) + (c[1] > 0) + (c[2] > 0) + (c[3] > 0) - 1;
+                }
+                __syncthreads();
+                qtScan(S.scanU, F, S.misc);   // exclusive: gain of ranks < r
+                if (tid == 0) S.misc[34] = 0;
+                __syncthreads();
+                int cntProc = 0;
+                for (int r = tid; r < F; r += kQtThreads) cntProc += (n + S.scanU[r] < N);
+                if (cntProc) atomicAdd(&S.misc[34], cntProc);
+                __syncthreads();
+                P = S.misc[34];   // processed ranks are a prefix 0..P-1 (gains are >= 0)
+                for (int r = tid; r < F; r += kQtThreads) if (r >= P) S.procOrder[S.byOrder[r]] = -1;
+                __syncthreads();
+                n = qtCommit(S, b1, c1, b2, c2, g2, n, P, cand, nodeOf, np, &nToExpand);
+                { short4 *t = b1; b1 = b2; b2 = t; } { int *t = c1; c1 = c2; c2 = t; } { int *t = g1; g1 = g2; g2 = t; }
+                if (n >= N || n == prevSize2) finish = true;
+            }
+        }
+    }
+
+    // ---- best response per node, first in key order on ties (:703-720); output in list order
+    unsigned long long *best = (unsigned long long *)S.childCnt;
+    for (int i = tid; i < n; i += kQtThreads) best[i] = 0ull;
+    __syncthreads();
+    for (int p = tid; p < np; p += kQtThreads) {
+        const uint2 c = cand[p];
+        const unsigned long long key = ((unsigned long long)(c.x >> 24) << 32) | (unsigned long long)(0xffffffffu - c.y);
+        atomicMax(&best[nodeOf[p]], key);
+    }
+    __syncthreads();
+    uint32_t *kept = B.kept + (long long)f * G.keptCap + L.keptOff;
+    for (int p = tid; p < np; p += kQtThreads) {
+        const uint2 c = cand[p];
+        const unsigned long long key = ((unsigned long long)(c.x >> 24) << 32) | (unsigned long long)(0xffffffffu - c.y);
+        const int nd = nodeOf[p];
+        if (best[nd] == key && nd < L.listCap) kept[nd] = c.x;
+    }
+    if (tid == 0) {
+        *keptCount = min(n, L.listCap);
+        if (n > L.listCap) atomicOr(B.status, 2);
+    }
+}
+
+size_t quadtreeSmemBytes(int listCap) {
+    const size_t C = (size_t)listCap;
+    return sizeof(short4) * 2 * C + 4 * C * 4 + 4 * C * 2 + 16 * C * 2 + 4 * C * 3 + 40 * 4;
+}
+
+int launchQuadtree(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s) {
+    k_quadtree<<<dim3(G.nlevels, nFrames), kQtThreads, quadtreeSmemBytes(G.maxListCap), s>>>(G, B);
+    return 1;
+}
+
+// =================================================================================================
+// K5 — cv::GaussianBlur(7x7, sigma 2, BORDER_REFLECT_101) on every level (src/ORBextractor.cc:1009-1010),
+// OpenCV >= 3.4 fixed-point path: taps {18,34,48,56,48,34,18}/256, horizontal sum in 16 bits,
+// vertical sum in 32 bits, one rounding (v + 32768) >> 16.  Shared-memory tile with a 3-px halo;
+// one launch covers all levels of all frames (tiles enumerated level-major).
+constexpr int kBlurTW = 128, kBlurTH = 16, kBlurThreads = 256;
+constexpr int kBlurRawPitch = kBlurTW + 8;
+
+__device__ __forceinline__ int reflect101(int p, int len) {
+    if (len == 1) return 0;
+    while ((unsigned)p >= (unsigned)len) p = p < 0 ? -p : 2 * len - 2 - p;
+    return p;
+}
+
+__global__ void __launch_bounds__(kBlurThreads) k_blur(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+    __shared__ uint8_t raw[(kBlurTH + 6) * kBlurRawPitch];
+    __shared__ uint16_t hs[(kBlurTH + 6) * kBlurTW];
+    const int f = blockIdx.y, tid = threadIdx.x;
+    int level = 0;
+    while (level + 1 < G.nlevels && (int)blockIdx.x >= G.lv[level + 1].tileStart) level++;
+    const LevelGeom &L = G.lv[level];
+    const int t = blockIdx.x - L.tileStart;
+    const int ty = t / L.tilesX, tx = t - ty * L.tilesX;
+    const int x0 = tx * kBlurTW, y0 = ty * kBlurTH;
+    const int tw = min(kBlurTW, L.w - x0), th = min(kBlurTH, L.h - y0);
+    const uint8_t *img = levelPtr(G, B, f, level);
+    for (int i = tid; i < (th + 6) * (tw + 6); i += kBlurThreads) {
+        const int y = i / (tw + 6), x = i - y * (tw + 6);
+        const int sy = reflect101(y0 + y - 3, L.h), sx = reflect101(x0 + x - 3, L.w);
+        raw[y * kBlurRawPitch + x] = img[(long long)sy * L.pitch + sx];
+    }
+    __syncthreads();
+    for (int i = tid; i < (th + 6) * tw; i += kBlurThreads) {
+        const int y = i / tw, x = i - y * tw;
+        const uint8_t *r = &raw[y * kBlurRawPitch + x];
+        const int acc = 18 * (r[0] + r[6]) + 34 * (r[1] + r[5]) + 48 * (r[2] + r[4]) + 56 * r[3];
+        hs[y * kBlurTW + x] = (uint16_t)acc;
+    }
+    __syncthreads();
+    uint8_t *dst = B.blur + (long long)f * B.blurSlab + B.blurOff[level];
+    const int dp = B.blurPitch[level];
+    for (int i = tid; i < th * tw; i += kBlurThreads) {
+        const int y = i / tw, x = i - y * tw;
+        const uint16_t *c = &hs[y * kBlurTW + x];
+        const uint32_t acc = 18u * (c[0] + c[6 * kBlurTW]) + 34u * (c[kBlurTW] + c[5 * kBlurTW]) +
+                             48u * (c[2 * kBlurTW] + c[4 * kBlurTW]) + 56u * c[3 * kBlurTW];
+        dst[(long long)(y0 + y) * dp + x0 + x] = (uint8_t)((acc + 32768u) >> 16);
+    }
+}
+
+int launchBlur(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s) {
+    if (G.totalTiles == 0) return 0;
+    k_blur<<<dim3(G.totalTiles, nFrames), kBlurThreads, 0, s>>>(G, B);
+    return 1;
+}
+
+// =================================================================================================
+// K4 + K6 — IC_Angle (src/ORBextractor.cc:77-101) on the unblurred level, then computeOrbDescriptor
+// (:105-149) on the blurred level, one warp per kept keypoint; also the final assembly (:1019-1026):
+// level-major concatenation, pt *= mvScaleFactor[level] for level > 0.
+//
+// cosf/sinf: the reference calls cos(float)/sin(float) under `using namespace std` (:67,108-109),
+// i.e. glibc's float routines.  devCosf/devSinf restate glibc 2.39's s_cosf.c/s_sinf.c (double
+// polynomial with fused multiply-adds, x86-64 FMA variant) op for op — IEEE double fma on the GPU
+// gives the same bits.  cv::fastAtan2 (OpenCV mathfuncs_core atan_f32) is restated in float with
+// explicit round-to-nearest mul/add so no contraction happens.
+__device__ __forceinline__ float sincosPolyDev(double x, double x2, int n, bool neg) {
+    const double C0 = 1.0, C1 = -0x1.ffffffd0c621cp-2, C2 = 0x1.55553e1068f19p-5, C3 = -0x1.6c087e89a359dp-10,
+                 C4 = 0x1.99343027bf8c3p-16;
+    const double S1 = -0x1.555545995a603p-3, S2 = 0x1.1107605230bc4p-7, S3 = -0x1.994eb3774cf24p-13;
+    if ((n & 1) == 0) {
+        const double x3 = __dmul_rn(x, x2);
+        const double s1 = __fma_rn(x2, S3, S2);
+        const double x7 = __dmul_rn(x3, x2);
+        const double s = __fma_rn(x3, S1, x);
+        return (float)__fma_rn(x7, s1, s);
+    }
+    const double sg = neg ? -1.0 : 1.0;
+    const double x4 = __dmul_rn(x2, x2);
+    const double c2 = __fma_rn(x2, sg * C4, sg * C3);
+    const double c1 = __fma_rn(x2, sg * C1, sg * C0);
+    const double x6 = __dmul_rn(x4, x2);
+    const double c = __fma_rn(x4, sg * C2, c1);
+    return (float)__fma_rn(x6, c2, c);
+}
+__device__ __forceinline__ void devSinCosf(float y, float *sn, float *cs) {
+    const uint32_t top = (__float_as_uint(y) >> 20) & 0x7ff;
+    double x = (double)y;
+    if (top < 0x3f4) {  // |y| < pi/4
+        const double x2 = __dmul_rn(x, x);
+        if (top < 0x398) { *sn = y; *cs = 1.0f; return; }
+        *sn = sincosPolyDev(x, x2, 0, false);
+        *cs = sincosPolyDev(x, x2, 1, false);
+        return;
+    }
+    const double r = __dmul_rn(x, 0x1.45f306dc9c883p+23);
+    const int n = (__double2int_rz(r) + 0x800000) >> 24;
+    x = __fma_rn(-(double)n, 0x1.921fb54442d18p+0, x);
+    const double sgn = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;
+    const double xs = __dmul_rn(x, sgn), x2 = __dmul_rn(x, x);
+    *sn = sincosPolyDev(xs, x2, n, (n & 2) != 0);
+    *cs = sincosPolyDev(xs, x2, n ^ 1, (n & 2) != 0);
+}
+
+__device__ __forceinline__ float devFastAtan2(float y, float x) {
+    const float k = (float)(180.0 / 3.14159265358979323846);
+    const float p1 = 0.9997878412794807f * k, p3 = -0.3258083974640975f * k, p5 = 0.1555786518463281f * k,
+                p7 = -0.04432655554792128f * k;
+    const float eps = 2.2204460492503131e-16f;
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a, c, c2;
+    if (ax >= ay) {
+        c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+        c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+        c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+__device__ __align__(16) signed char gPattern[1024];  // filled from kOrbPattern by configureKernels()
+
+constexpr int kDescWarps = 8;
+
+__global__ void __launch_bounds__(kDescWarps * 32) k_describe(const __grid_constant__ FrameGeom G, const DevBuffers B, int cap,
+                                                              int32_t *counts, ygzorb_keypoint *kps, uint8_t *desc) {
+    const int f = blockIdx.y, lane = threadIdx.x & 31;
+    const int j = blockIdx.x * kDescWarps + (threadIdx.x >> 5);
+    // level-major offsets from the per-level kept counts
+    const int *kc = B.keptCount + f * kMaxLevels;
+    int level = -1, k = 0, total = 0;
+    for (int l = 0; l < G.nlevels; l++) {
+        const int c = kc[l];
+        if (level < 0 && j < total + c) { level = l; k = j - total; }
+        total += c;
+    }
+    if (j == 0 && lane == 0) counts[f] = min(total, cap);
+    if (level < 0 || j >= cap) return;
+    const LevelGeom &L = G.lv[level];
+    const uint32_t xyr = B.kept[(long long)f * G.keptCap + L.keptOff + k];
+    const int x = xyr & 0xfff, y = (xyr >> 12) & 0xfff;
+    // ---- IC_Angle: lane <-> column u = lane-15, rows v = -15..15 limited by umax[|v|]
+    const uint8_t *c0 = levelPtr(G, B, f, level) + (long long)y * L.pitch + x;
+    int m10 = 0, m01 = 0;
+    const int u = lane - kHalfPatch;
+    if (lane < 31) {
+        const int au = abs(u);
+#pragma unroll 1
+        for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
+            if (au <= G.umax[abs(v)]) {
+                const int I = c0[(long long)v * L.pitch + u];
+                m10 += u * I;
+                m01 += v * I;
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    }
+    const float angle = devFastAtan2((float)m01, (float)m10);
+    // ---- descriptor: lane <-> byte, 8 tests each
+    const float factorPI = (float)(3.14159265358979323846 / 180.f);
+    float a, b;
+    devSinCosf(__fmul_rn(angle, factorPI), &b, &a);
+    const uint8_t *cb = B.blur + (long long)f * B.blurSlab + B.blurOff[level] + (long long)y * B.blurPitch[level] + x;
+    const int bp = B.blurPitch[level];
+    const char4 *pat = reinterpret_cast<const char4 *>(gPattern) + lane * 8;  // 8 tests (x0,y0,x1,y1) per byte
+    int val = 0;
+#pragma unroll
+    for (int t = 0; t < 8; t++) {
+        const char4 p = pat[t];
+        // GET_VALUE(idx) = center[cvRound(x*b + y*a)*step + cvRound(x*a - y*b)]  (:114-116)
+        const float x0 = p.x, y0 = p.y, x1 = p.z, y1 = p.w;
+        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
+        const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
+        const int q1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+        const int t0 = cb[r0 * bp + q0], t1 = cb[r1 * bp + q1];
+        val |= (t0 < t1) << t;
+    }
+    const long long o = (long long)f * cap + j;
+    desc[o * 32 + lane] = (uint8_t)val;
+    if (lane == 0) {
+        ygzorb_keypoint kp;
+        kp.x = (float)x; kp.y = (float)y;
+        if (level != 0) { kp.x = __fmul_rn(kp.x, L.scale); kp.y = __fmul_rn(kp.y, L.scale); }
+        kp.size = L.kpSize; kp.angle = angle; kp.response = (float)(xyr >> 24);
+        kp.octave = level; kp.class_id = -1;
+        kps[o] = kp;
+    }
+}
+
+int launchDescribe(const FrameGeom &G, const DevBuffers &B, int nFrames, int cap, int32_t *counts,
+                   ygzorb_keypoint *kps, uint8_t *desc, cudaStream_t s) {
+    const int blocks = (min(cap, G.keptCap) + kDescWarps - 1) / kDescWarps;
+    k_describe<<<dim3(max(blocks, 1), nFrames), kDescWarps * 32, 0, s>>>(G, B, cap, counts, kps, desc);
+    return 1;
+}
+
+static bool gConfigured[64];
+
+int configureKernels() {
+    int dev = 0;
+    YGZ_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && gConfigured[dev]) return 0;
+    YGZ_CUDA(cudaMemcpyToSymbol(gPattern, kOrbPattern, sizeof(kOrbPattern)));
+    YGZ_CUDA(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    if (dev >= 0 && dev < 64) gConfigured[dev] = true;
+    return 0;
+}
+
+}  // namespace ygz

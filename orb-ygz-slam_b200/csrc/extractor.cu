@@ -1,0 +1,672 @@
+// extractor.cu — host side of the extractor: the constructor's tables (src/ORBextractor.cc:412-470),
+// per-image geometry, workspace, stage orchestration on the handle's stream, and the C ABI of
+// include/ygzorb.h.  No CPU compute path: everything below either sizes buffers / fills lookup
+// tables or enqueues kernels.
+#include <algorithm>
+#include <cfloat>
+#include <climits>
+#include <cmath>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "ygz_common.cuh"
+
+namespace ygz {
+
+static thread_local std::string gLastError;
+void setError(const std::string &msg) { gLastError = msg; }
+int cudaFail(cudaError_t e, const char *what, const char *file, int line) {
+    char buf[512];
+    snprintf(buf, sizeof buf, "CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+    gLastError = buf;
+    return YGZORB_E_CUDA;
+}
+static int argFail(const char *msg) { gLastError = msg; return YGZORB_E_ARG; }
+
+// OpenCV's cvRound / cvFloor / cvCeil on the host (round-half-to-even under the default FP mode).
+static inline int cvRoundF(float v) { return (int)lrintf(v); }
+static inline int cvRoundD(double v) { return (int)lrint(v); }
+static inline int cvFloorF(float v) { return (int)floorf(v); }
+static inline int alignUp(int v, int a) { return (v + a - 1) / a * a; }
+static inline long long alignUpLL(long long v, long long a) { return (v + a - 1) / a * a; }
+
+struct Tables {
+    std::vector<float> scale, invScale, sigma2, invSigma2;
+    std::vector<int> nPerLevel;
+    int umax[16];
+};
+
+// src/ORBextractor.cc:412-470.  `scaleFactor` is a double member initialised from the float
+// argument (include/ORBextractor.h:157), so the products are taken in double and rounded to float.
+static Tables makeTables(const ygzorb_params &p) {
+    Tables t;
+    const int L = p.nlevels;
+    const double sf = (double)p.scaleFactor;
+    t.scale.assign(L, 1.f); t.sigma2.assign(L, 1.f); t.invScale.resize(L); t.invSigma2.resize(L);
+    for (int i = 1; i < L; i++) {
+        t.scale[i] = (float)((double)t.scale[i - 1] * sf);
+        t.sigma2[i] = t.scale[i] * t.scale[i];
+    }
+    for (int i = 0; i < L; i++) { t.invScale[i] = 1.0f / t.scale[i]; t.invSigma2[i] = 1.0f / t.sigma2[i]; }
+    t.nPerLevel.assign(L, 0);
+    const float factor = (float)(1.0f / sf);
+    float nDesired = (float)(p.nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)L)));
+    int sum = 0;
+    for (int l = 0; l < L - 1; l++) {
+        t.nPerLevel[l] = cvRoundF(nDesired);
+        sum += t.nPerLevel[l];
+        nDesired *= factor;
+    }
+    t.nPerLevel[L - 1] = std::max(p.nfeatures - sum, 0);
+    const int vmax = cvFloorF(kHalfPatch * std::sqrt(2.f) / 2 + 1);
+    const int vmin = (int)std::ceil(kHalfPatch * std::sqrt(2.f) / 2);
+    const double hp2 = kHalfPatch * kHalfPatch;
+    for (int v = 0; v <= vmax; ++v) t.umax[v] = cvRoundD(std::sqrt(hp2 - v * v));
+    for (int v = kHalfPatch, v0 = 0; v >= vmin; --v) {
+        while (t.umax[v0] == t.umax[v0 + 1]) ++v0;
+        t.umax[v] = v0;
+        ++v0;
+    }
+    return t;
+}
+
+// Coefficient tables of cv::resize INTER_LINEAR 8U (OpenCV imgproc/resize.cpp, resizeGeneric_ +
+// HResizeLinear<uchar,int,short,2048>): fx = (float)((dx+0.5)*scale-0.5), sx = floor(fx), fx -= sx,
+// columns clamped with the weight forced to 0/1, rows clamped with the weight kept; weights are
+// saturate_cast<short>(w*2048).  Entries packed for k_resize.
+static inline short satShort(float v) {
+    const int i = cvRoundF(v);
+    return (short)std::min(std::max(i, (int)SHRT_MIN), (int)SHRT_MAX);
+}
+static inline int packS(short lo, short hi) { return (int)((uint32_t)(uint16_t)lo | ((uint32_t)(uint16_t)hi << 16)); }
+
+static bool makeResizeTables(int sw, int sh, int dw, int dh, int padW, std::vector<int2> &X, std::vector<int2> &Y) {
+    const double isx = (double)dw / sw, isy = (double)dh / sh;
+    const double scx = 1. / isx, scy = 1. / isy;
+    const int ix = (int)std::nearbyint(scx), iy = (int)std::nearbyint(scy);
+    const bool area2x = std::abs(scx - ix) < DBL_EPSILON && std::abs(scy - iy) < DBL_EPSILON && ix == 2 && iy == 2;
+    X.resize(padW); Y.resize(dh);
+    for (int dx = 0; dx < padW; dx++) {
+        const int d = std::min(dx, dw - 1);
+        float fx = (float)((d + 0.5) * scx - 0.5);
+        int sx = cvFloorF(fx);
+        fx -= sx;
+        if (sx < 0) { fx = 0; sx = 0; }
+        if (sx >= sw - 1) { fx = 0; sx = sw - 1; }
+        X[dx].x = (int)((uint32_t)sx | ((uint32_t)std::min(sx + 1, sw - 1) << 16));
+        X[dx].y = packS(satShort((1.f - fx) * 2048.f), satShort(fx * 2048.f));
+    }
+    for (int dy = 0; dy < dh; dy++) {
+        float fy = (float)((dy + 0.5) * scy - 0.5);
+        const int sy = cvFloorF(fy);
+        fy -= sy;
+        const int y0 = std::min(std::max(sy, 0), sh - 1), y1 = std::min(std::max(sy + 1, 0), sh - 1);
+        Y[dy].x = (int)((uint32_t)y0 | ((uint32_t)y1 << 16));
+        Y[dy].y = packS(satShort((1.f - fy) * 2048.f), satShort(fy * 2048.f));
+    }
+    return area2x;
+}
+
+// Everything that depends on the image size.  Returns 0 or an error code.
+static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, int stride, FrameGeom &G,
+                        std::vector<int2> &tabs, long long blurOff[kMaxLevels], int blurPitch[kMaxLevels],
+                        long long *blurSlab) {
+    memset(&G, 0, sizeof G);
+    G.nlevels = P.nlevels; G.w = w; G.h = h; G.iniTh = P.iniThFAST; G.minTh = P.minThFAST;
+    for (int v = 0; v < 16; v++) G.umax[v] = T.umax[v];
+    tabs.clear();
+    long long off = 0, candOff = 0, bOff = 0;
+    int cells = 0, tiles = 0, keptOff = 0;
+    for (int l = 0; l < P.nlevels; l++) {
+        LevelGeom &L = G.lv[l];
+        L.w = cvRoundF((float)w * T.invScale[l]);   // :1131-1133, from LEVEL-0 dims
+        L.h = cvRoundF((float)h * T.invScale[l]);
+        if (L.w < 1 || L.h < 1) return argFail("pyramid level collapses to zero size (cv::resize would throw)");
+        if (L.w > 4095 || L.h > 4095) return argFail("image larger than 4095 px is not supported");
+        L.pitch = l == 0 ? stride : alignUp(L.w, 64);
+        L.scale = T.scale[l];
+        L.kpSize = (float)(int)(31 * T.scale[l]);  // :787 PATCH_SIZE*mvScaleFactor[level], truncated to int
+        L.nTarget = T.nPerLevel[l];
+        if (l > 0) {
+            L.off = off;
+            off += alignUpLL((long long)L.pitch * L.h, 256);
+            std::vector<int2> X, Y;
+            L.area2x = makeResizeTables(G.lv[l - 1].w, G.lv[l - 1].h, L.w, L.h, L.pitch, X, Y) ? 1 : 0;
+            L.tabX = (int)tabs.size(); tabs.insert(tabs.end(), X.begin(), X.end());
+            L.tabY = (int)tabs.size(); tabs.insert(tabs.end(), Y.begin(), Y.end());
+        }
+        blurPitch[l] = alignUp(L.w, 64);
+        blurOff[l] = bOff;
+        bOff += alignUpLL((long long)blurPitch[l] * L.h, 256);
+        // cells (:728-745)
+        const int maxBX = L.w - kMinBorder, maxBY = L.h - kMinBorder;
+        const float width = (float)(maxBX - kMinBorder), height = (float)(maxBY - kMinBorder);
+        const int nCols = (int)(width / 30.f), nRows = (int)(height / 30.f);
+        L.cellStart = cells;
+        L.candOff = candOff;
+        L.keptOff = keptOff;
+        if (nCols > 0 && nRows > 0) {
+            L.nCols = nCols; L.nRows = nRows;
+            L.wCell = (int)std::ceil(width / nCols);
+            L.hCell = (int)std::ceil(height / nRows);
+            if (L.wCell > 64 || L.hCell > 64) return argFail("internal: FAST cell larger than 64 px");
+            cells += nCols * nRows;
+            // NMS leaves at most one survivor per 2x2 block of a cell's detection area
+            long long cap = 0;
+            for (int i = 0; i < nRows; i++) {
+                const int iniY = kMinBorder + i * L.hCell;
+                if (iniY >= maxBY - 3) continue;
+                const int dh = std::min(iniY + L.hCell + 6, maxBY) - iniY - 6;
+                if (dh <= 0) continue;
+                for (int j = 0; j < nCols; j++) {
+                    const int iniX = kMinBorder + j * L.wCell;
+                    if (iniX >= maxBX - 6) continue;
+                    const int dw = std::min(iniX + L.wCell + 6, maxBX) - iniX - 6;
+                    if (dw > 0) cap += (long long)((dw + 1) / 2) * ((dh + 1) / 2);
+                }
+            }
+            L.candCap = (int)cap;
+            // quadtree roots (:537-543)
+            L.nIni = (int)std::round((float)(maxBX - kMinBorder) / (maxBY - kMinBorder));
+            if (L.nIni < 1) return argFail("level narrower than half its height: the reference's quadtree has no root (nIni == 0)");
+            L.hX = (float)(maxBX - kMinBorder) / L.nIni;
+            L.listCap = std::max(L.nTarget + 3, 4 * L.nIni) + 1;
+            if (L.listCap > 16000) return argFail("nfeatures per level too large (quadtree list bound > 16000)");
+        } else {
+            L.listCap = 0;  // canonicalised: nRows == 0 -> ceil(x/0) in the reference, no cells run
+        }
+        candOff += alignUpLL(L.candCap, 32);
+        keptOff += L.listCap;
+        G.maxListCap = std::max(G.maxListCap, L.listCap);
+        L.tilesX = (L.w + 127) / 128; L.tilesY = (L.h + 15) / 16;
+        L.tileStart = tiles;
+        tiles += L.tilesX * L.tilesY;
+    }
+    G.totalCells = cells; G.totalTiles = tiles;
+    G.slabBytes = std::max(off, 256LL);
+    G.candPerFrame = std::max(candOff, 32LL);
+    G.keptCap = std::max(keptOff, 1);
+    G.maxListCap = std::max(G.maxListCap, 8);
+    *blurSlab = bOff;
+    if (quadtreeSmemBytes(G.maxListCap) > 200 * 1024) return argFail("nfeatures per level too large for the quadtree kernel's shared memory");
+    return 0;
+}
+
+
+// -------------------------------------------------------------------------------------------------
+struct Extractor {
+    ygzorb_params params;
+    Tables tables;
+    int device = 0, maxBatch = 1;
+    cudaStream_t stream = nullptr;
+    // geometry of the current image size
+    int gw = -1, gh = -1, gstride = -1;
+    FrameGeom G;
+    DevBuffers B;
+    long long blurOff[kMaxLevels]; int blurPitch[kMaxLevels]; long long blurSlab = 0;
+    // device workspace (grown on demand)
+    uint8_t *dIn = nullptr; size_t inBytes = 0;
+    uint8_t *dPyr = nullptr; size_t pyrBytes = 0;
+    uint8_t *dBlur = nullptr; size_t blurBytes = 0;
+    int2 *dTabs = nullptr; size_t tabBytes = 0;
+    uint2 *dCand = nullptr; size_t candBytes = 0;
+    uint16_t *dNodeOf = nullptr; size_t nodeBytes = 0;
+    uint32_t *dKept = nullptr; size_t keptBytes = 0;
+    int *dCounts = nullptr;   // [maxBatch][kMaxLevels] x2 (cand, kept) + status
+    int32_t *dOutCounts = nullptr; ygzorb_keypoint *dOutKps = nullptr; uint8_t *dOutDesc = nullptr;
+    size_t outCap = 0;  // records per frame the dOut* buffers hold
+    int lastFrames = 0; bool lastInDevice = false; bool stagesValid = false;
+    const uint8_t *lastIn = nullptr; long long lastInFrameStride = 0;
+    long long launches = 0;
+    bool profiling = false;
+    cudaEvent_t ev[8] = {};
+    float stageMs[8] = {};
+};
+
+template <class T> static int growBuf(T *&p, size_t &have, size_t need) {
+    if (need <= have && p) return 0;
+    if (p) YGZ_CUDA(cudaFree(p));
+    p = nullptr; have = 0;
+    YGZ_CUDA(cudaMalloc((void **)&p, std::max<size_t>(need, 256)));
+    have = need;
+    return 0;
+}
+
+static int ensureGeometry(Extractor *ex, int w, int h, int stride, int nFrames, bool inDevice) {
+    if (w != ex->gw || h != ex->gh || stride != ex->gstride) {
+        std::vector<int2> tabs;
+        FrameGeom G;
+        long long bo[kMaxLevels]; int bp[kMaxLevels]; long long bs = 0;
+        // host frames are packed into the staging buffer with stride == w
+        const int rc = makeGeometry(ex->params, ex->tables, w, h, stride, G, tabs, bo, bp, &bs);
+        if (rc) return rc;
+        ex->G = G; memcpy(ex->blurOff, bo, sizeof bo); memcpy(ex->blurPitch, bp, sizeof bp); ex->blurSlab = bs;
+        ex->gw = w; ex->gh = h; ex->gstride = stride;
+        ex->stagesValid = false;
+        YGZ_CUDA(cudaStreamSynchronize(ex->stream));
+        if (int rc2 = growBuf(ex->dTabs, ex->tabBytes, std::max<size_t>(tabs.size(), 1) * sizeof(int2))) return rc2;
+        if (!tabs.empty()) YGZ_CUDA(cudaMemcpy(ex->dTabs, tabs.data(), tabs.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    }
+    const size_t nb = (size_t)ex->maxBatch;
+    (void)nFrames;
+    int rc;
+    if (!inDevice && (rc = growBuf(ex->dIn, ex->inBytes, nb * (size_t)w * h + 64))) return rc;
+    if ((rc = growBuf(ex->dPyr, ex->pyrBytes, nb * (size_t)ex->G.slabBytes))) return rc;
+    if ((rc = growBuf(ex->dBlur, ex->blurBytes, nb * (size_t)ex->blurSlab))) return rc;
+    if ((rc = growBuf(ex->dCand, ex->candBytes, nb * (size_t)ex->G.candPerFrame * sizeof(uint2)))) return rc;
+    if ((rc = growBuf(ex->dNodeOf, ex->nodeBytes, nb * (size_t)ex->G.candPerFrame * sizeof(uint16_t)))) return rc;
+    if ((rc = growBuf(ex->dKept, ex->keptBytes, nb * (size_t)ex->G.keptCap * sizeof(uint32_t)))) return rc;
+    DevBuffers &B = ex->B;
+    B.pyr = ex->dPyr; B.blur = ex->dBlur; B.blurSlab = ex->blurSlab;
+    for (int l = 0; l < kMaxLevels; l++) { B.blurOff[l] = ex->blurOff[l]; B.blurPitch[l] = ex->blurPitch[l]; }
+    B.tabs = ex->dTabs; B.cand = ex->dCand; B.nodeOf = ex->dNodeOf; B.kept = ex->dKept;
+    B.candCount = ex->dCounts; B.keptCount = ex->dCounts + nb * kMaxLevels; B.status = ex->dCounts + 2 * nb * kMaxLevels;
+    return 0;
+}
+
+static int ensureOut(Extractor *ex, int cap) {
+    if ((size_t)cap <= ex->outCap && ex->dOutKps) return 0;
+    YGZ_CUDA(cudaStreamSynchronize(ex->stream));
+    if (ex->dOutKps) YGZ_CUDA(cudaFree(ex->dOutKps));
+    if (ex->dOutDesc) YGZ_CUDA(cudaFree(ex->dOutDesc));
+    ex->dOutKps = nullptr; ex->dOutDesc = nullptr; ex->outCap = 0;
+    YGZ_CUDA(cudaMalloc((void **)&ex->dOutKps, (size_t)ex->maxBatch * cap * sizeof(ygzorb_keypoint)));
+    YGZ_CUDA(cudaMalloc((void **)&ex->dOutDesc, (size_t)ex->maxBatch * cap * 32));
+    ex->outCap = cap;
+    return 0;
+}
+
+// Upload (host input) or alias (device input) level 0 of a chunk of frames.
+static int bindInput(Extractor *ex, const uint8_t *frames, int n, int w, int h, int stride, size_t frameStride, bool inDevice) {
+    if (inDevice) {
+        ex->B.in = frames; ex->B.inFrameStride = (long long)frameStride;
+        return 0;
+    }
+    // staging buffer is continuous: pitch == w (the geometry was built with stride == w for host input)
+    if (stride == w && frameStride == (size_t)w * h) {
+        YGZ_CUDA(cudaMemcpyAsync(ex->dIn, frames, (size_t)n * w * h, cudaMemcpyHostToDevice, ex->stream));
+    } else if (frameStride == (size_t)stride * h) {
+        YGZ_CUDA(cudaMemcpy2DAsync(ex->dIn, w, frames, stride, w, (size_t)h * n, cudaMemcpyHostToDevice, ex->stream));
+    } else {
+        for (int f = 0; f < n; f++)
+            YGZ_CUDA(cudaMemcpy2DAsync(ex->dIn + (size_t)f * w * h, w, frames + f * frameStride, stride, w, h,
+                                       cudaMemcpyHostToDevice, ex->stream));
+    }
+    ex->B.in = ex->dIn; ex->B.inFrameStride = (long long)w * h;
+    return 0;
+}
+
+static int runPyramid(Extractor *ex, int n) {
+    for (int l = 1; l < ex->G.nlevels; l++) ex->launches += launchResizeLevel(ex->G, ex->B, l, n, ex->stream);
+    return 0;
+}
+
+#define YGZ_MARK(i) do { if (ex->profiling) YGZ_CUDA(cudaEventRecord(ex->ev[i], ex->stream)); } while (0)
+
+static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int h, int stride, size_t frameStride,
+                        unsigned flags, int cap, int32_t *counts, ygzorb_keypoint *kps, uint8_t *desc) {
+    const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
+    const int gstride = inDev ? stride : w;
+    int rc = ensureGeometry(ex, w, h, gstride, n, inDev);
+    if (rc) return rc;
+    if (cap < ex->G.keptCap) { setError("cap is smaller than ygzorb_extractor_max_keypoints()"); return YGZORB_E_CAPACITY; }
+    if (!outDev && (rc = ensureOut(ex, cap))) return rc;
+    YGZ_MARK(0);
+    if ((rc = bindInput(ex, frames, n, w, h, stride, frameStride, inDev))) return rc;
+    YGZ_CUDA(cudaMemsetAsync(ex->dCounts, 0, (2 * (size_t)ex->maxBatch * kMaxLevels + 1) * sizeof(int), ex->stream));
+    YGZ_MARK(1);
+    runPyramid(ex, n);
+    YGZ_MARK(2);
+    ex->launches += launchFast(ex->G, ex->B, n, ex->stream);
+    YGZ_MARK(3);
+    ex->launches += launchQuadtree(ex->G, ex->B, n, ex->stream);
+    YGZ_MARK(4);
+    ex->launches += launchBlur(ex->G, ex->B, n, ex->stream);
+    YGZ_MARK(5);
+    int32_t *oc = outDev ? counts : ex->dOutCounts;
+    ygzorb_keypoint *ok = outDev ? kps : ex->dOutKps;
+    uint8_t *od = outDev ? desc : ex->dOutDesc;
+    ex->launches += launchDescribe(ex->G, ex->B, n, cap, oc, ok, od, ex->stream);
+    YGZ_MARK(6);
+    if (!outDev) {
+        YGZ_CUDA(cudaMemcpyAsync(counts, oc, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, ex->stream));
+        YGZ_CUDA(cudaMemcpyAsync(kps, ok, (size_t)n * cap * sizeof(ygzorb_keypoint), cudaMemcpyDeviceToHost, ex->stream));
+        YGZ_CUDA(cudaMemcpyAsync(desc, od, (size_t)n * cap * 32, cudaMemcpyDeviceToHost, ex->stream));
+    }
+    YGZ_MARK(7);
+    YGZ_CUDA(cudaGetLastError());
+    ex->lastFrames = n; ex->stagesValid = true;
+    return 0;
+}
+
+static int finishProfile(Extractor *ex) {
+    if (!ex->profiling) return 0;
+    for (int i = 0; i < 7; i++) YGZ_CUDA(cudaEventElapsedTime(&ex->stageMs[i], ex->ev[i], ex->ev[i + 1]));
+    return 0;
+}
+
+static int checkStatus(Extractor *ex) {
+    int st = 0;
+    YGZ_CUDA(cudaMemcpy(&st, ex->B.status, sizeof st, cudaMemcpyDeviceToHost));
+    if (st) { setError("internal capacity overflow in the FAST/quadtree stage (status " + std::to_string(st) + ")"); return YGZORB_E_CAPACITY; }
+    return 0;
+}
+
+}  // namespace ygz
+
+// =================================================================================================
+// C ABI
+using namespace ygz;
+
+extern "C" {
+
+const char *ygzorb_last_error(void) { return gLastError.c_str(); }
+const char *ygzorb_version(void) { return "ygzorb-b200 0.1 (sm_100a)"; }
+
+int ygzorb_device_count(void) {
+    int n = 0;
+    YGZ_CUDA(cudaGetDeviceCount(&n));
+    return n;
+}
+
+int ygzorb_extractor_create(const ygzorb_params *params, int max_w, int max_h, int max_batch, int device,
+                            ygzorb_extractor **out) {
+    if (!params || !out) return argFail("null argument");
+    if (params->nlevels < 1 || params->nlevels > kMaxLevels) return argFail("nlevels must be in [1, 16]");
+    if (params->nfeatures < 1 || !(params->scaleFactor > 1.0f)) return argFail("nfeatures must be >= 1 and scaleFactor > 1");
+    if (params->iniThFAST < 1 || params->iniThFAST > 255 || params->minThFAST < 1 || params->minThFAST > params->iniThFAST)
+        return argFail("FAST thresholds must satisfy 1 <= minThFAST <= iniThFAST <= 255");
+    if (max_batch < 1 || max_batch > 65535) return argFail("max_batch must be in [1, 65535]");
+    (void)max_w; (void)max_h;  // workspace is sized on first use and grown on demand
+    YGZ_CUDA(cudaSetDevice(device));
+    Extractor *ex = new Extractor();
+    ex->params = *params; ex->tables = makeTables(*params); ex->device = device; ex->maxBatch = max_batch;
+    memset(&ex->B, 0, sizeof ex->B);
+    int rc = configureKernels();
+    if (rc) { delete ex; return rc; }
+    cudaError_t e = cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&ex->dCounts, (2 * (size_t)max_batch * kMaxLevels + 1) * sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc((void **)&ex->dOutCounts, (size_t)max_batch * sizeof(int32_t));
+    for (int i = 0; i < 8 && e == cudaSuccess; i++) e = cudaEventCreate(&ex->ev[i]);
+    if (e != cudaSuccess) { ygzorb_extractor_destroy((ygzorb_extractor *)ex); return cudaFail(e, "extractor_create", __FILE__, __LINE__); }
+    *out = (ygzorb_extractor *)ex;
+    return 0;
+}
+
+void ygzorb_extractor_destroy(ygzorb_extractor *h) {
+    Extractor *ex = (Extractor *)h;
+    if (!ex) return;
+    cudaSetDevice(ex->device);
+    if (ex->stream) cudaStreamSynchronize(ex->stream);
+    void *bufs[] = {ex->dIn, ex->dPyr, ex->dBlur, ex->dTabs, ex->dCand, ex->dNodeOf, ex->dKept, ex->dCounts,
+                    ex->dOutCounts, ex->dOutKps, ex->dOutDesc};
+    for (void *p : bufs) if (p) cudaFree(p);
+    for (int i = 0; i < 8; i++) if (ex->ev[i]) cudaEventDestroy(ex->ev[i]);
+    if (ex->stream) cudaStreamDestroy(ex->stream);
+    delete ex;
+}
+
+int ygzorb_extractor_tables(const ygzorb_extractor *h, float *scale, float *inv_scale, float *sigma2,
+                            float *inv_sigma2, int *n_per_level, int *umax16) {
+    const Extractor *ex = (const Extractor *)h;
+    if (!ex) return argFail("null extractor");
+    for (int l = 0; l < ex->params.nlevels; l++) {
+        if (scale) scale[l] = ex->tables.scale[l];
+        if (inv_scale) inv_scale[l] = ex->tables.invScale[l];
+        if (sigma2) sigma2[l] = ex->tables.sigma2[l];
+        if (inv_sigma2) inv_sigma2[l] = ex->tables.invSigma2[l];
+        if (n_per_level) n_per_level[l] = ex->tables.nPerLevel[l];
+    }
+    if (umax16) for (int v = 0; v < 16; v++) umax16[v] = ex->tables.umax[v];
+    return 0;
+}
+
+static int geometryOnly(const Extractor *ex, int w, int h, FrameGeom &G) {
+    std::vector<int2> tabs;
+    long long bo[kMaxLevels]; int bp[kMaxLevels]; long long bs;
+    return makeGeometry(ex->params, ex->tables, w, h, w, G, tabs, bo, bp, &bs);
+}
+
+int ygzorb_extractor_level_sizes(const ygzorb_extractor *h, int w, int hgt, int *lw, int *lh) {
+    const Extractor *ex = (const Extractor *)h;
+    if (!ex || !lw || !lh) return argFail("null argument");
+    for (int l = 0; l < ex->params.nlevels; l++) {
+        lw[l] = cvRoundF((float)w * ex->tables.invScale[l]);
+        lh[l] = cvRoundF((float)hgt * ex->tables.invScale[l]);
+    }
+    return 0;
+}
+
+int ygzorb_extractor_max_keypoints(const ygzorb_extractor *h, int w, int hgt) {
+    const Extractor *ex = (const Extractor *)h;
+    if (!ex) return argFail("null extractor");
+    if (w <= 0 || hgt <= 0) return 1;
+    FrameGeom G;
+    const int rc = geometryOnly(ex, w, hgt, G);
+    return rc ? rc : G.keptCap;
+}
+
+static int checkFrames(Extractor *ex, const uint8_t *frames, int n, int w, int h, int stride) {
+    if (!ex) return argFail("null extractor");
+    if (n < 0) return argFail("n_frames < 0");
+    if (n > 0 && w > 0 && h > 0 && !frames) return argFail("null frames pointer");
+    if (w > 0 && stride < w) return argFail("stride < w");
+    return 0;
+}
+
+int ygzorb_extract_batch(ygzorb_extractor *h, const uint8_t *frames, int n_frames, int w, int hgt, int stride,
+                         size_t frame_stride, unsigned flags, int cap, int32_t *counts, ygzorb_keypoint *keypoints,
+                         uint8_t *desc) {
+    Extractor *ex = (Extractor *)h;
+    int rc = checkFrames(ex, frames, n_frames, w, hgt, stride);
+    if (rc) return rc;
+    if (!counts || (n_frames > 0 && cap > 0 && (!keypoints || !desc))) return argFail("null output pointer");
+    YGZ_CUDA(cudaSetDevice(ex->device));
+    const bool outDev = flags & YGZORB_OUT_DEVICE;
+    if (w <= 0 || hgt <= 0 || n_frames == 0) {  // empty image: silent return, nothing extracted (:972-973)
+        if (outDev) { if (n_frames) YGZ_CUDA(cudaMemsetAsync(counts, 0, (size_t)n_frames * 4, ex->stream)); }
+        else for (int f = 0; f < n_frames; f++) counts[f] = 0;
+        return 0;
+    }
+    if (frame_stride == 0) frame_stride = (size_t)stride * hgt;
+    for (int f0 = 0; f0 < n_frames; f0 += ex->maxBatch) {
+        const int n = std::min(ex->maxBatch, n_frames - f0);
+        // chunks reuse the workspace: a host-output chunk must be drained before the next one starts
+        rc = extractChunk(ex, frames + (size_t)f0 * frame_stride, n, w, hgt, stride, frame_stride, flags, cap,
+                          counts + f0, keypoints + (size_t)f0 * cap, desc + (size_t)f0 * cap * 32);
+        if (rc) return rc;
+        if (!outDev && f0 + n < n_frames) YGZ_CUDA(cudaStreamSynchronize(ex->stream));
+    }
+    if (!(flags & YGZORB_NO_SYNC)) return ygzorb_extractor_sync(h);
+    return 0;
+}
+
+int ygzorb_compute_pyramid_batch(ygzorb_extractor *h, const uint8_t *frames, int n_frames, int w, int hgt,
+                                 int stride, size_t frame_stride, unsigned flags) {
+    Extractor *ex = (Extractor *)h;
+    int rc = checkFrames(ex, frames, n_frames, w, hgt, stride);
+    if (rc) return rc;
+    if (w <= 0 || hgt <= 0 || n_frames == 0) return 0;
+    if (n_frames > ex->maxBatch) return argFail("n_frames exceeds max_batch (the pyramid of every frame must stay resident)");
+    YGZ_CUDA(cudaSetDevice(ex->device));
+    if (frame_stride == 0) frame_stride = (size_t)stride * hgt;
+    const bool inDev = flags & YGZORB_IN_DEVICE;
+    if ((rc = ensureGeometry(ex, w, hgt, inDev ? stride : w, n_frames, inDev))) return rc;
+    if ((rc = bindInput(ex, frames, n_frames, w, hgt, stride, frame_stride, inDev))) return rc;
+    runPyramid(ex, n_frames);
+    YGZ_CUDA(cudaGetLastError());
+    ex->lastFrames = n_frames; ex->stagesValid = false;
+    if (!(flags & YGZORB_NO_SYNC)) YGZ_CUDA(cudaStreamSynchronize(ex->stream));
+    return 0;
+}
+
+static int copyLevelOut(Extractor *ex, const uint8_t *src, int pitch, int w, int hh, uint8_t *dst) {
+    YGZ_CUDA(cudaMemcpy2DAsync(dst, w, src, pitch, w, hh, cudaMemcpyDeviceToHost, ex->stream));
+    return 0;
+}
+
+int ygzorb_get_pyramid_level(ygzorb_extractor *h, int frame, int level, uint8_t *dst) {
+    Extractor *ex = (Extractor *)h;
+    if (!ex || !dst) return argFail("null argument");
+    if (ex->lastFrames <= 0) { setError("no pyramid computed yet"); return YGZORB_E_STATE; }
+    if (frame < 0 || frame >= ex->lastFrames || level < 0 || level >= ex->G.nlevels) return argFail("frame/level out of range");
+    YGZ_CUDA(cudaSetDevice(ex->device));
+    const LevelGeom &L = ex->G.lv[level];
+    const uint8_t *src = level == 0 ? ex->B.in + (long long)frame * ex->B.inFrameStride
+                                    : ex->B.pyr + (long long)frame * ex->G.slabBytes + L.off;
+    int rc = copyLevelOut(ex, src, L.pitch, L.w, L.h, dst);
+    if (rc) return rc;
+    YGZ_CUDA(cudaStreamSynchronize(ex->stream));
+    return 0;
+}
+
+int ygzorb_get_pyramid(ygzorb_extractor *h, int frame, uint8_t *dst) {
+    Extractor *ex = (Extractor *)h;
+    if (!ex || !dst) return argFail("null argument");
+    if (ex->lastFrames <= 0) { setError("no pyramid computed yet"); return YGZORB_E_STATE; }
+    if (frame < 0 || frame >= ex->lastFrames) return argFail("frame out of range");
+    YGZ_CUDA(cudaSetDevice(ex->device));
+    size_t off = 0;
+    for (int l = 0; l < ex->G.nlevels; l++) {
+        const LevelGeom &L = ex->G.lv[l];
+        const uint8_t *src = l == 0 ? ex->B.in + (long long)frame * ex->B.inFrameStride
+                                    : ex->B.pyr + (long long)frame * ex->G.slabBytes + L.off;
+        int rc = copyLevelOut(ex, src, L.pitch, L.w, L.h, dst + off);
+        if (rc) return rc;
+        off += (size_t)L.w * L.h;
+    }
+    YGZ_CUDA(cudaStreamSynchronize(ex->stream));
+    return 0;
+}
+
+int ygzorb_get_blurred_level(ygzorb_extractor *h, int frame, int level, uint8_t *dst) {
+    Extractor *ex = (Extractor *)h;
+    if (!ex || !dst) return argFail("null argument");
+    if (!ex->stagesValid) { setError("no extraction ran yet"); return YGZORB_E_STATE; }
+    if (frame < 0 || frame >= ex->lastFrames || level < 0 || level >= ex->G.nlevels) return argFail("frame/level out of range");
+    YGZ_CUDA(cudaSetDevice(ex->device));
+    const LevelGeom &L = ex->G.lv[level];
+    int rc = copyLevelOut(ex, ex->B.blur + (long long)frame * ex->blurSlab + ex->blurOff[level], ex->blurPitch[level], L.w, L.h, dst);
+    if (rc) return rc;
+    YGZ_CUDA(cudaStreamSynchronize(ex->stream));
+    return 0;
+}
+
+int ygzorb_get_candidates(ygzorb_extractor *h, int frame, int level, int cap, int16_t *x, int16_t *y,
+                          uint8_t *response, uint32_t *order_key) {
+    Extractor *ex = (Extractor *)h;
+    if (!ex) return argFail("null extractor");
+    if (!ex->stagesValid) { setError("no extraction ran yet"); return YGZORB_E_STATE; }
+    if (frame < 0 || frame >= ex->lastFrames || level < 0 || level >= ex->G.nlevels) return argFail("frame/level out of range");
+    YGZ_CUDA(cudaSetDevice(ex->device));
+    YGZ_CUDA(cudaStreamSynchronize(ex->stream));
+    int n = 0;
+    YGZ_CUDA(cudaMemcpy(&n, ex->B.candCount + frame * kMaxLevels + level, sizeof n, cudaMemcpyDeviceToHost));
+    n = std::min(n, ex->G.lv[level].candCap);
+    std::vector<uint2> tmp((size_t)std::max(n, 1));
+    if (n > 0)
+        YGZ_CUDA(cudaMemcpy(tmp.data(), ex->B.cand + (long long)frame * ex->G.candPerFrame + ex->G.lv[level].candOff,
+                            (size_t)n * sizeof(uint2), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n && i < cap; i++) {
+        if (x) x[i] = (int16_t)((int)(tmp[i].x & 0xfff) - kMinBorder);
+        if (y) y[i] = (int16_t)((int)((tmp[i].x >> 12) & 0xfff) - kMinBorder);
+        if (response) response[i] = (uint8_t)(tmp[i].x >> 24);
+        if (order_key) order_key[i] = tmp[i].y;
+    }
+    return n;
+}
+
+int ygzorb_extractor_sync(ygzorb_extractor *h) {
+    Extractor *ex = (Extractor *)h;
+    if (!ex) return argFail("null extractor");
+    YGZ_CUDA(cudaSetDevice(ex->device));
+    YGZ_CUDA(cudaStreamSynchronize(ex->stream));
+    int rc = finishProfile(ex);
+    if (rc) return rc;
+    return ex->B.status ? checkStatus(ex) : 0;
+}
+
+void *ygzorb_extractor_stream(ygzorb_extractor *h) { return h ? (void *)((Extractor *)h)->stream : nullptr; }
+long long ygzorb_extractor_launch_count(const ygzorb_extractor *h) { return h ? ((const Extractor *)h)->launches : 0; }
+
+int ygzorb_extractor_set_profiling(ygzorb_extractor *h, int on) {
+    if (!h) return argFail("null extractor");
+    ((Extractor *)h)->profiling = on != 0;
+    return 0;
+}
+int ygzorb_extractor_stage_ms(ygzorb_extractor *h, float *ms, int n) {
+    Extractor *ex = (Extractor *)h;
+    if (!ex || !ms) return argFail("null argument");
+    for (int i = 0; i < n && i < 8; i++) ms[i] = ex->stageMs[i];
+    return 0;
+}
+
+}  // extern "C"
+
+// ---- stand-alone stages (single host image; allocate, run one kernel, free) --------------------
+namespace {
+struct TmpDev {
+    std::vector<void *> ptrs;
+    ~TmpDev() { for (void *p : ptrs) cudaFree(p); }
+    template <class T> cudaError_t alloc(T **p, size_t bytes) {
+        cudaError_t e = cudaMalloc((void **)p, std::max<size_t>(bytes, 256));
+        if (e == cudaSuccess) ptrs.push_back(*p);
+        return e;
+    }
+};
+}  // namespace
+
+extern "C" int ygzorb_resize_linear_u8(const uint8_t *src, int sw, int sh, uint8_t *dst, int dw, int dh, int device) {
+    if (!src || !dst) return argFail("null argument");
+    if (sw < 1 || sh < 1 || dw < 1 || dh < 1 || sw > 65535 || sh > 65535) return argFail("bad size");
+    YGZ_CUDA(cudaSetDevice(device));
+    FrameGeom G; memset(&G, 0, sizeof G);
+    DevBuffers B; memset(&B, 0, sizeof B);
+    G.nlevels = 2; G.w = sw; G.h = sh;
+    G.lv[0].w = sw; G.lv[0].h = sh; G.lv[0].pitch = sw;
+    LevelGeom &D = G.lv[1];
+    D.w = dw; D.h = dh; D.pitch = alignUp(dw, 64); D.off = 0;
+    std::vector<int2> X, Y;
+    D.area2x = makeResizeTables(sw, sh, dw, dh, D.pitch, X, Y) ? 1 : 0;
+    D.tabX = 0; D.tabY = (int)X.size();
+    X.insert(X.end(), Y.begin(), Y.end());
+    G.slabBytes = (long long)D.pitch * dh;
+    TmpDev tmp;
+    uint8_t *dS = nullptr, *dD = nullptr; int2 *dT = nullptr;
+    YGZ_CUDA(tmp.alloc(&dS, (size_t)sw * sh));
+    YGZ_CUDA(tmp.alloc(&dD, (size_t)G.slabBytes));
+    YGZ_CUDA(tmp.alloc(&dT, X.size() * sizeof(int2)));
+    YGZ_CUDA(cudaMemcpy(dS, src, (size_t)sw * sh, cudaMemcpyHostToDevice));
+    YGZ_CUDA(cudaMemcpy(dT, X.data(), X.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    B.in = dS; B.inFrameStride = (long long)sw * sh; B.pyr = dD; B.tabs = dT;
+    launchResizeLevel(G, B, 1, 1, 0);
+    YGZ_CUDA(cudaGetLastError());
+    YGZ_CUDA(cudaMemcpy2D(dst, dw, dD, D.pitch, dw, dh, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+extern "C" int ygzorb_gaussian_blur7_u8(const uint8_t *src, int w, int h, uint8_t *dst, int device) {
+    if (!src || !dst) return argFail("null argument");
+    if (w < 1 || h < 1) return argFail("bad size");
+    YGZ_CUDA(cudaSetDevice(device));
+    FrameGeom G; memset(&G, 0, sizeof G);
+    DevBuffers B; memset(&B, 0, sizeof B);
+    G.nlevels = 1; G.w = w; G.h = h;
+    LevelGeom &L = G.lv[0];
+    L.w = w; L.h = h; L.pitch = w;
+    L.tilesX = (w + 127) / 128; L.tilesY = (h + 15) / 16; L.tileStart = 0;
+    G.totalTiles = L.tilesX * L.tilesY;
+    TmpDev tmp;
+    uint8_t *dS = nullptr, *dD = nullptr;
+    const int dp = alignUp(w, 64);
+    YGZ_CUDA(tmp.alloc(&dS, (size_t)w * h));
+    YGZ_CUDA(tmp.alloc(&dD, (size_t)dp * h));
+    YGZ_CUDA(cudaMemcpy(dS, src, (size_t)w * h, cudaMemcpyHostToDevice));
+    B.in = dS; B.inFrameStride = (long long)w * h; B.blur = dD; B.blurSlab = (long long)dp * h; B.blurPitch[0] = dp;
+    // blur tiles are enumerated through blockIdx.x: keep the grid inside the x-dimension limit
+    launchBlur(G, B, 1, 0);
+    YGZ_CUDA(cudaGetLastError());
+    YGZ_CUDA(cudaMemcpy2D(dst, w, dD, dp, w, h, cudaMemcpyDeviceToHost));
+    return 0;
+}
