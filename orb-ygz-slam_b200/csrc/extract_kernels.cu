@@ -74,52 +74,69 @@ int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nF
 // the quadtree needs from the order (its only order dependence is "first wins" on response ties).
 constexpr int kFastThreads = 128;
 constexpr int kCellMax = 64;                 // wCell, hCell < 60 always (width/floor(width/30))
-constexpr int kTilePitch = kCellMax + 8;     // image tile pitch (cell + 6, padded)
-constexpr int kScorePitch = kCellMax + 2;
+constexpr int kTilePitch = 76;               // image tile pitch: cell + 6 + up to 3 alignment bytes, multiple of 4
+constexpr int kScorePitch = 68;              // score tile pitch: detection width + 2, multiple of 4
 
-__device__ __forceinline__ int min3i(int a, int b, int c) { return min(min(a, b), c); }
-__device__ __forceinline__ int max3i(int a, int b, int c) { return max(max(a, b), c); }
+// The 16 ring differences are kept as packed 16-bit pairs E = (d + 256) | (256 - d) << 16 with
+// d = v - p, both halves positive, so ONE VIMNMX3.U16x2 handles the "darker" arcs (low half) and
+// the "brighter" arcs (high half) at once.  E = base + p * 0xFFFF with base = packed (v + 256, 256 - v):
+// no borrow crosses the halves because v + 256 - p >= 1.
+__device__ __forceinline__ unsigned fastBase(int v) { return (unsigned)(v + 256) * 0xFFFF0001u + (512u << 16); }
+__device__ __forceinline__ unsigned fastE(int p, unsigned base) { return (unsigned)p * 0xFFFFu + base; }
 
-// m of the pixel at tile position p (pointer into the shared image tile).
-__device__ __forceinline__ int fastMeasure(const uint8_t *p) {
+// Corner measure m (max over the 16 arcs of 9 contiguous ring pixels of min(v-p) resp. min(p-v)),
+// OpenCV fast_score.cpp cornerScore<16> without the threshold clamp.  `pre` = minThFAST + 256: the
+// function returns -1 early when no two adjacent compass pixels are both darker / both brighter
+// than the threshold (an arc of 9 always holds two adjacent compass pixels), i.e. m <= minThFAST.
+__device__ __forceinline__ int fastMeasure(const uint8_t *p, unsigned pre) {
     constexpr int P = kTilePitch;
-    const int v = p[0];
-    int d[16];
-    d[0] = v - p[3 * P];       d[1] = v - p[3 * P + 1];   d[2] = v - p[2 * P + 2];   d[3] = v - p[P + 3];
-    d[4] = v - p[3];           d[5] = v - p[-P + 3];      d[6] = v - p[-2 * P + 2];  d[7] = v - p[-3 * P + 1];
-    d[8] = v - p[-3 * P];      d[9] = v - p[-3 * P - 1];  d[10] = v - p[-2 * P - 2]; d[11] = v - p[-P - 3];
-    d[12] = v - p[-3];         d[13] = v - p[P - 3];      d[14] = v - p[2 * P - 2];  d[15] = v - p[3 * P - 1];
-    int lo3[16], hi3[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        lo3[k] = min3i(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-        hi3[k] = max3i(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+    const unsigned base = fastBase(p[0]);
+    unsigned e[16];
+    e[0] = fastE(p[3 * P], base); e[4] = fastE(p[3], base); e[8] = fastE(p[-3 * P], base); e[12] = fastE(p[-3], base);
+    {
+        const unsigned pm = __vimax3_u16x2(__vminu2(e[0], e[4]), __vminu2(e[4], e[8]),
+                                           __vmaxu2(__vminu2(e[8], e[12]), __vminu2(e[12], e[0])));
+        if ((pm & 0xffffu) <= pre && (pm >> 16) <= pre) return -1;
     }
-    int best = -256, worst = 256;  // max over arcs of min(d), min over arcs of max(d)
+    e[1] = fastE(p[3 * P + 1], base);   e[2] = fastE(p[2 * P + 2], base);   e[3] = fastE(p[P + 3], base);
+    e[5] = fastE(p[-P + 3], base);      e[6] = fastE(p[-2 * P + 2], base);  e[7] = fastE(p[-3 * P + 1], base);
+    e[9] = fastE(p[-3 * P - 1], base);  e[10] = fastE(p[-2 * P - 2], base); e[11] = fastE(p[-P - 3], base);
+    e[13] = fastE(p[P - 3], base);      e[14] = fastE(p[2 * P - 2], base);  e[15] = fastE(p[3 * P - 1], base);
+    unsigned lo3[16];
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        best = max(best, min3i(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]));
-        worst = min(worst, max3i(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]));
-    }
-    return max(best, -worst);
+    for (int k = 0; k < 16; k++) lo3[k] = __vimin3_u16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
+    unsigned lo9[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) lo9[k] = __vimin3_u16x2(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]);
+    unsigned r = __vimax3_u16x2(lo9[0], lo9[1], lo9[2]);
+#pragma unroll
+    for (int k = 3; k < 15; k += 2) r = __vimax3_u16x2(r, lo9[k], lo9[k + 1]);
+    r = __vmaxu2(r, lo9[15]);
+    return (int)max(r & 0xffffu, r >> 16) - 256;
 }
 
-__device__ __forceinline__ int fastStored(int m, int t) { return m > t ? m - 1 : 0; }  // cv::FAST's score buffer
-
-__device__ __forceinline__ bool fastKeep(const uint8_t *sc, int t) {
-    constexpr int P = kScorePitch;
-    const int m = sc[0];
-    if (m <= t) return false;
-    const int s = m - 1;
-    return s > fastStored(sc[-1], t) && s > fastStored(sc[1], t) && s > fastStored(sc[-P - 1], t) &&
-           s > fastStored(sc[-P], t) && s > fastStored(sc[-P + 1], t) && s > fastStored(sc[P - 1], t) &&
-           s > fastStored(sc[P], t) && s > fastStored(sc[P + 1], t);
+// Appends `value` for every lane with `pred` to a shared list (order irrelevant); one shared atomic per warp.
+__device__ __forceinline__ void fastAppend(bool pred, uint16_t value, uint16_t *list, int *counter) {
+    const unsigned mask = __ballot_sync(0xffffffffu, pred);
+    if (mask == 0) return;
+    const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (pred) list[base + __popc(mask & ((1u << lane) - 1))] = value;
 }
 
+// NMS of cv::FAST is threshold-independent on m: a corner at threshold t (m > t) survives iff its
+// stored score m-1 exceeds the stored scores of its 8 neighbours, and a neighbour's stored score is
+// n-1 if n > t and 0 otherwise; since m > t >= 1 this is exactly "every neighbour has n < m".  The
+// score tile holds m for m > minThFAST and 0 elsewhere (and outside the detection area).
 __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
     __shared__ __align__(16) uint8_t tile[(kCellMax + 6) * kTilePitch];
-    __shared__ uint8_t score[(kCellMax + 2) * kScorePitch];
-    const int f = blockIdx.y;
+    __shared__ __align__(16) uint8_t score[(kCellMax + 2) * kScorePitch];
+    __shared__ uint16_t corners[kCellMax * kCellMax];   // y<<6 | x of pixels with m > minThFAST
+    __shared__ uint16_t maxima[kCellMax * kCellMax / 4 + 64];  // local maxima among them
+    __shared__ int nList[2];
+    const int f = blockIdx.y, tid = threadIdx.x;
     int level = 0;
     while (level + 1 < G.nlevels && (int)blockIdx.x >= G.lv[level + 1].cellStart) level++;
     const LevelGeom &L = G.lv[level];
@@ -133,36 +150,79 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
     const int tw = maxX - iniX, th = maxY - iniY;   // window size
     const int dw = tw - 6, dh = th - 6;              // detection area size
     if (dw <= 0 || dh <= 0) return;
-    const uint8_t *img = levelPtr(G, B, f, level);
-    for (int i = threadIdx.x; i < tw * th; i += kFastThreads) {
-        const int y = i / tw, x = i - y * tw;
-        tile[y * kTilePitch + x] = img[(long long)(iniY + y) * L.pitch + iniX + x];
+    const int npx = dw * dh;
+    const uint8_t *img = levelPtr(G, B, f, level) + (long long)iniY * L.pitch;
+    // ---- tile load: aligned 32-bit words when the level allows it; tile column c <-> image x = xa + c
+    const bool aligned = ((L.pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(img) & 3) == 0);
+    const int xa = aligned ? (iniX & ~3) : iniX, ox = iniX - xa;
+    if (aligned) {
+        const int nw = (ox + tw + 3) >> 2;           // words per row (<= 19)
+        const unsigned wmagic = (1u << 16) / (unsigned)nw + 1;
+        for (int i = tid; i < nw * th; i += kFastThreads) {
+            const int y = (int)(((unsigned)i * wmagic) >> 16), wq = i - y * nw;
+            *reinterpret_cast<uint32_t *>(&tile[y * kTilePitch + 4 * wq]) =
+                __ldg(reinterpret_cast<const uint32_t *>(img + (long long)y * L.pitch + xa) + wq);
+        }
+    } else {
+        const int lane = tid & 31, wid = tid >> 5;
+        for (int y = wid; y < th; y += kFastThreads / 32) {
+            const uint8_t *row = img + (long long)y * L.pitch + xa;
+            for (int x = lane; x < tw; x += 32) tile[y * kTilePitch + x] = row[x];
+        }
     }
-    for (int i = threadIdx.x; i < (dh + 2) * kScorePitch; i += kFastThreads) score[i] = 0;
+    for (int i = tid; i < (dh + 2) * (kScorePitch / 4); i += kFastThreads) reinterpret_cast<uint32_t *>(score)[i] = 0;
+    if (tid < 2) nList[tid] = 0;
     __syncthreads();
     const int minTh = G.minTh, iniTh = G.iniTh;
-    for (int i = threadIdx.x; i < dw * dh; i += kFastThreads) {
-        const int y = i / dw, x = i - y * dw;
-        const int m = fastMeasure(&tile[(y + 3) * kTilePitch + x + 3]);
-        score[(y + 1) * kScorePitch + x + 1] = (uint8_t)(m > minTh ? m : 0);
+    const unsigned magic = (1u << 18) / (unsigned)dw + 1;   // i / dw for i < 4096, dw <= 64
+    // ---- phase 1: measure of every detection pixel; corners at minThFAST -> score tile + list
+    for (int i0 = 0; i0 < npx; i0 += kFastThreads) {
+        const int i = i0 + tid;
+        bool corner = false;
+        int y = 0, x = 0;
+        if (i < npx) {
+            y = (int)(((unsigned)i * magic) >> 18); x = i - y * dw;
+            const int m = fastMeasure(&tile[(y + 3) * kTilePitch + ox + x + 3], (unsigned)minTh + 256u);
+            corner = m > minTh;
+            if (corner) score[(y + 1) * kScorePitch + x + 1] = (uint8_t)m;
+        }
+        fastAppend(corner, (uint16_t)((y << 6) | x), corners, &nList[0]);
     }
     __syncthreads();
+    // ---- phase 2: strict local maxima of m among the corners
+    const int n1 = nList[0];
     int any = 0;
-    for (int i = threadIdx.x; i < dw * dh; i += kFastThreads) {
-        const int y = i / dw, x = i - y * dw;
-        any |= fastKeep(&score[(y + 1) * kScorePitch + x + 1], iniTh);
+    for (int i0 = 0; i0 < n1; i0 += kFastThreads) {
+        const int i = i0 + tid;
+        bool ismax = false;
+        uint16_t yx = 0;
+        if (i < n1) {
+            yx = corners[i];
+            const uint8_t *sc = &score[((yx >> 6) + 1) * kScorePitch + (yx & 63) + 1];
+            const int m = sc[0];
+            const int nb = max(max(max(sc[-1], sc[1]), max(sc[-kScorePitch - 1], sc[-kScorePitch])),
+                               max(max(sc[-kScorePitch + 1], sc[kScorePitch - 1]), max(sc[kScorePitch], sc[kScorePitch + 1])));
+            ismax = nb < m;
+            any |= ismax && m > iniTh;
+        }
+        fastAppend(ismax, yx, maxima, &nList[1]);
     }
+    // ---- threshold fallback: iniThFAST unless nothing survives in the cell (src/ORBextractor.cc:764-770)
     const int t = __syncthreads_or(any) ? iniTh : minTh;
+    const int n2 = nList[1];
     uint2 *cand = B.cand + (long long)f * G.candPerFrame + L.candOff;
     int *counter = B.candCount + f * kMaxLevels + level;
-    const int lane = threadIdx.x & 31;
-    for (int i0 = 0; i0 < dw * dh; i0 += kFastThreads) {
-        const int i = i0 + threadIdx.x;
+    const int lane = tid & 31;
+    for (int i0 = 0; i0 < n2; i0 += kFastThreads) {
+        if (i0 + (tid & ~31) >= n2) break;   // whole warp beyond the list
+        const int i = i0 + tid;
         bool keep = false;
-        int y = 0, x = 0;
-        if (i < dw * dh) {
-            y = i / dw; x = i - y * dw;
-            keep = fastKeep(&score[(y + 1) * kScorePitch + x + 1], t);
+        int y = 0, x = 0, m = 0;
+        if (i < n2) {
+            const int yx = maxima[i];
+            y = yx >> 6; x = yx & 63;
+            m = score[(y + 1) * kScorePitch + x + 1];
+            keep = m > t;
         }
         const unsigned mask = __ballot_sync(0xffffffffu, keep);
         if (mask == 0) continue;
@@ -172,7 +232,6 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
         if (keep) {
             const int slot = base + __popc(mask & ((1u << lane) - 1));
             if (slot < L.candCap) {
-                const int m = score[(y + 1) * kScorePitch + x + 1];
                 const uint32_t ax = iniX + 3 + x, ay = iniY + 3 + y;  // absolute level coordinates
                 cand[slot] = make_uint2(ax | (ay << 12) | ((uint32_t)(m - 1) << 24),
                                         ((uint32_t)cell << 12) | ((uint32_t)y << 6) | (uint32_t)x);
@@ -492,8 +551,10 @@ int launchQuadtree(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStr
 // OpenCV >= 3.4 fixed-point path: taps {18,34,48,56,48,34,18}/256, horizontal sum in 16 bits,
 // vertical sum in 32 bits, one rounding (v + 32768) >> 16.  Shared-memory tile with a 3-px halo;
 // one launch covers all levels of all frames (tiles enumerated level-major).
-constexpr int kBlurTW = 128, kBlurTH = 16, kBlurThreads = 256;
-constexpr int kBlurRawPitch = kBlurTW + 8;
+// Tile = kBlurTW x kBlurTH outputs per CTA (ygz_common.cuh); 256 threads = 64 column groups of 4 px x 4 row groups.
+constexpr int kBlurThreads = 256;
+constexpr int kBlurRawPitch = kBlurTW + 8;      // bytes; raw column c <-> image x = x0 - 4 + c (word aligned)
+constexpr int kBlurRawRows = kBlurTH + 6;
 
 __device__ __forceinline__ int reflect101(int p, int len) {
     if (len == 1) return 0;
@@ -502,38 +563,78 @@ __device__ __forceinline__ int reflect101(int p, int len) {
 }
 
 __global__ void __launch_bounds__(kBlurThreads) k_blur(const __grid_constant__ FrameGeom G, const DevBuffers B) {
-    __shared__ uint8_t raw[(kBlurTH + 6) * kBlurRawPitch];
-    __shared__ uint16_t hs[(kBlurTH + 6) * kBlurTW];
+    __shared__ __align__(16) uint8_t raw[kBlurRawRows * kBlurRawPitch];
+    __shared__ __align__(16) uint2 hs[kBlurRawRows * (kBlurTW / 4)];   // 4 x u16 horizontal sums
     const int f = blockIdx.y, tid = threadIdx.x;
     int level = 0;
     while (level + 1 < G.nlevels && (int)blockIdx.x >= G.lv[level + 1].tileStart) level++;
     const LevelGeom &L = G.lv[level];
     const int t = blockIdx.x - L.tileStart;
-    const int ty = t / L.tilesX, tx = t - ty * L.tilesX;
-    const int x0 = tx * kBlurTW, y0 = ty * kBlurTH;
-    const int tw = min(kBlurTW, L.w - x0), th = min(kBlurTH, L.h - y0);
+    const int tyI = t / L.tilesX, txI = t - tyI * L.tilesX;
+    const int x0 = txI * kBlurTW, y0 = tyI * kBlurTH;
     const uint8_t *img = levelPtr(G, B, f, level);
-    for (int i = tid; i < (th + 6) * (tw + 6); i += kBlurThreads) {
-        const int y = i / (tw + 6), x = i - y * (tw + 6);
-        const int sy = reflect101(y0 + y - 3, L.h), sx = reflect101(x0 + x - 3, L.w);
-        raw[y * kBlurRawPitch + x] = img[(long long)sy * L.pitch + sx];
+    const bool aligned = ((L.pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(img) & 3) == 0);
+    // ---- stage the raw tile (+3 halo, REFLECT_101 about the true image edge), 32-bit words where possible
+    constexpr int kWords = kBlurRawPitch / 4;
+    for (int i = tid; i < kBlurRawRows * kWords; i += kBlurThreads) {
+        const int r = i / kWords, wq = i - r * kWords;
+        const int sy = reflect101(y0 + r - 3, L.h);
+        const int x = x0 - 4 + 4 * wq;
+        const uint8_t *row = img + (long long)sy * L.pitch;
+        uint32_t v;
+        if (aligned && x >= 0 && x + 3 < L.w) {
+            v = *reinterpret_cast<const uint32_t *>(row + x);
+        } else if (x + 3 < -3 || x > L.w + 2 + 3) {
+            v = 0;   // never read: beyond the halo of the last partial tile
+        } else {
+            v = (uint32_t)row[reflect101(x, L.w)] | ((uint32_t)row[reflect101(x + 1, L.w)] << 8) |
+                ((uint32_t)row[reflect101(x + 2, L.w)] << 16) | ((uint32_t)row[reflect101(x + 3, L.w)] << 24);
+        }
+        *reinterpret_cast<uint32_t *>(&raw[r * kBlurRawPitch + 4 * wq]) = v;
     }
     __syncthreads();
-    for (int i = tid; i < (th + 6) * tw; i += kBlurThreads) {
-        const int y = i / tw, x = i - y * tw;
-        const uint8_t *r = &raw[y * kBlurRawPitch + x];
-        const int acc = 18 * (r[0] + r[6]) + 34 * (r[1] + r[5]) + 48 * (r[2] + r[4]) + 56 * r[3];
-        hs[y * kBlurTW + x] = (uint16_t)acc;
+    // ---- horizontal pass: 4 outputs per thread from raw columns 4tx+1 .. 4tx+10
+    const int tx = tid & 63, tg = tid >> 6;
+    for (int r = tg; r < kBlurRawRows; r += 4) {
+        const uint32_t *w = reinterpret_cast<const uint32_t *>(&raw[r * kBlurRawPitch + 4 * tx]);
+        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
+        int p[10];   // columns 4tx+1 .. 4tx+10
+        p[0] = (w0 >> 8) & 255; p[1] = (w0 >> 16) & 255; p[2] = w0 >> 24;
+        p[3] = w1 & 255; p[4] = (w1 >> 8) & 255; p[5] = (w1 >> 16) & 255; p[6] = w1 >> 24;
+        p[7] = w2 & 255; p[8] = (w2 >> 8) & 255; p[9] = (w2 >> 16) & 255;
+        uint32_t o[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            o[k] = 18 * (p[k] + p[k + 6]) + 34 * (p[k + 1] + p[k + 5]) + 48 * (p[k + 2] + p[k + 4]) + 56 * p[k + 3];
+        hs[r * (kBlurTW / 4) + tx] = make_uint2(o[0] | (o[1] << 16), o[2] | (o[3] << 16));
     }
     __syncthreads();
+    // ---- vertical pass: each thread 4 columns x 8 rows, sliding over 14 rows of horizontal sums
+    const int x = x0 + 4 * tx;
+    if (x >= L.w) return;
     uint8_t *dst = B.blur + (long long)f * B.blurSlab + B.blurOff[level];
     const int dp = B.blurPitch[level];
-    for (int i = tid; i < th * tw; i += kBlurThreads) {
-        const int y = i / tw, x = i - y * tw;
-        const uint16_t *c = &hs[y * kBlurTW + x];
-        const uint32_t acc = 18u * (c[0] + c[6 * kBlurTW]) + 34u * (c[kBlurTW] + c[5 * kBlurTW]) +
-                             48u * (c[2 * kBlurTW] + c[4 * kBlurTW]) + 56u * c[3 * kBlurTW];
-        dst[(long long)(y0 + y) * dp + x0 + x] = (uint8_t)((acc + 32768u) >> 16);
+    constexpr int kRowsPer = kBlurTH / 4;
+    const int rBase = tg * kRowsPer;
+    uint2 win[kRowsPer + 6];
+#pragma unroll
+    for (int k = 0; k < kRowsPer + 6; k++) win[k] = hs[(rBase + k) * (kBlurTW / 4) + tx];
+#pragma unroll
+    for (int k = 0; k < kRowsPer; k++) {
+        const int y = y0 + rBase + k;
+        if (y < L.h) {
+            uint32_t out = 0;
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                auto get = [&](int j) -> uint32_t {
+                    const uint32_t word = (c < 2) ? win[k + j].x : win[k + j].y;
+                    return (c & 1) ? (word >> 16) : (word & 0xffffu);
+                };
+                const uint32_t acc = 18u * (get(0) + get(6)) + 34u * (get(1) + get(5)) + 48u * (get(2) + get(4)) + 56u * get(3);
+                out |= ((acc + 32768u) >> 16) << (8 * c);
+            }
+            *reinterpret_cast<uint32_t *>(dst + (long long)y * dp + x) = out;
+        }
     }
 }
 

@@ -179,7 +179,7 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
         candOff += alignUpLL(L.candCap, 32);
         keptOff += L.listCap;
         G.maxListCap = std::max(G.maxListCap, L.listCap);
-        L.tilesX = (L.w + 127) / 128; L.tilesY = (L.h + 15) / 16;
+        L.tilesX = (L.w + kBlurTW - 1) / kBlurTW; L.tilesY = (L.h + kBlurTH - 1) / kBlurTH;
         L.tileStart = tiles;
         tiles += L.tilesX * L.tilesY;
     }
@@ -655,7 +655,7 @@ extern "C" int ygzorb_gaussian_blur7_u8(const uint8_t *src, int w, int h, uint8_
     G.nlevels = 1; G.w = w; G.h = h;
     LevelGeom &L = G.lv[0];
     L.w = w; L.h = h; L.pitch = w;
-    L.tilesX = (w + 127) / 128; L.tilesY = (h + 15) / 16; L.tileStart = 0;
+    L.tilesX = (w + kBlurTW - 1) / kBlurTW; L.tilesY = (h + kBlurTH - 1) / kBlurTH; L.tileStart = 0;
     G.totalTiles = L.tilesX * L.tilesY;
     TmpDev tmp;
     uint8_t *dS = nullptr, *dD = nullptr;

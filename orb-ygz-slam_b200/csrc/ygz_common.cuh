@@ -14,6 +14,7 @@ constexpr int kMaxLevels = 16;
 constexpr int kEdge = 19;        // EDGE_THRESHOLD, src/ORBextractor.cc:72
 constexpr int kMinBorder = 16;   // EDGE_THRESHOLD - 3, :733
 constexpr int kHalfPatch = 15;   // HALF_PATCH_SIZE, :71
+constexpr int kBlurTW = 256, kBlurTH = 32;  // blur tile (k_blur)
 
 // Per-level geometry, computed once per (w, h) on the host with the reference's float arithmetic
 // (src/ORBextractor.cc:728-745 cells, :537-556 quadtree roots, :1131-1133 sizes).
