@@ -1,0 +1,359 @@
+// match_oracle.cpp — TEST INFRASTRUCTURE ONLY.  CPU restatement of the reference's Hamming matching
+// paths on flat arrays (part 2 of the oracle; part 1 is orb_oracle.cpp).  Linked into
+// oracle/libygz_oracle.so; used by tests/, smoke() and bench.py's CPU legs — never by the product.
+//
+// PARITY UNPINNED: src/ORBmatcher.cc and src/Frame.cc cannot be compiled in this image (they need
+// Eigen, sophus, DBoW2::Vocabulary, OpenCV C++, glog) and the reference ships no test vectors for
+// them, so these functions are line-by-line restatements checked only against brute-force
+// re-derivations in tests/test_match_oracle.py.  Citations are file:line in /root/reference.
+#include <algorithm>
+#include <atomic>
+#include <climits>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <thread>
+#include <utility>
+#include <vector>
+
+#define YGZO_API extern "C" __attribute__((visibility("default")))
+
+namespace {
+
+const int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;   // src/ORBmatcher.cc:36-38
+const int GRID_COLS = 64, GRID_ROWS = 48;                  // include/Frame.h:27-28
+
+struct KeyPoint { float x, y, size, angle, response; int octave, class_id; };  // cv::KeyPoint, 28 B
+static_assert(sizeof(KeyPoint) == 28, "cv::KeyPoint layout");
+
+template <class F> void parallelFor(long n, int threads, long chunk, F body) {
+    if (threads <= 1 || n <= chunk) { body(0, n); return; }
+    std::atomic<long> next{0};
+    std::vector<std::thread> th;
+    for (int t = 0; t < threads; t++)
+        th.emplace_back([&]() { for (;;) { const long b = next.fetch_add(chunk); if (b >= n) break; body(b, std::min(n, b + chunk)); } });
+    for (auto &t : th) t.join();
+}
+
+// ORBmatcher::DescriptorDistance — src/ORBmatcher.cc:1507-1523 (the __SSE2__ branch: popcount per 32-bit word).
+inline int descriptorDistance(const uint8_t *a, const uint8_t *b) {
+    int dist = 0;
+    for (int i = 0; i < 8; i++) {
+        uint32_t x, y;
+        std::memcpy(&x, a + 4 * i, 4); std::memcpy(&y, b + 4 * i, 4);
+        dist += __builtin_popcount(x ^ y);
+    }
+    return dist;
+}
+
+// Frame::PosInGrid + AssignFeaturesToGrid — src/Frame.cc:314-330, 483-493.  round() = half away from zero.
+struct Grid {
+    std::vector<int> cell[GRID_COLS][GRID_ROWS];
+    float minX, minY, invW, invH;
+};
+void assignGrid(Grid &g, const KeyPoint *kps, int n, float minX, float minY, float invW, float invH) {
+    g.minX = minX; g.minY = minY; g.invW = invW; g.invH = invH;
+    for (int i = 0; i < n; i++) {
+        const int px = (int)std::round((kps[i].x - minX) * invW);
+        const int py = (int)std::round((kps[i].y - minY) * invH);
+        if (px < 0 || px >= GRID_COLS || py < 0 || py >= GRID_ROWS) continue;
+        g.cell[px][py].push_back(i);
+    }
+}
+
+// Frame::GetFeaturesInArea — src/Frame.cc:424-481.
+void featuresInArea(const Grid &g, const KeyPoint *kps, float x, float y, float r, int minLevel, int maxLevel,
+                    std::vector<int> &out) {
+    out.clear();
+    const int nMinCellX = std::max(0, (int)std::floor((x - g.minX - r) * g.invW));
+    if (nMinCellX >= GRID_COLS) return;
+    const int nMaxCellX = std::min(GRID_COLS - 1, (int)std::ceil((x - g.minX + r) * g.invW));
+    if (nMaxCellX < 0) return;
+    const int nMinCellY = std::max(0, (int)std::floor((y - g.minY - r) * g.invH));
+    if (nMinCellY >= GRID_ROWS) return;
+    const int nMaxCellY = std::min(GRID_ROWS - 1, (int)std::ceil((y - g.minY + r) * g.invH));
+    if (nMaxCellY < 0) return;
+    const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+    for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+        for (int iy = nMinCellY; iy <= nMaxCellY; iy++)
+            for (int idx : g.cell[ix][iy]) {
+                const KeyPoint &kp = kps[idx];
+                if (bCheckLevels) {
+                    if (kp.octave < minLevel) continue;
+                    if (maxLevel >= 0 && kp.octave > maxLevel) continue;
+                }
+                const float dx = kp.x - x, dy = kp.y - y;
+                if (std::fabs(dx) < r && std::fabs(dy) < r) out.push_back(idx);
+            }
+}
+
+// ORBmatcher::ComputeThreeMaxima — src/ORBmatcher.cc:1471-1502, on bin sizes.
+void threeMaxima(const int *sizes, int L, int &ind1, int &ind2, int &ind3) {
+    int max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < L; i++) {
+        const int s = sizes[i];
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+
+inline int rotationBin(float a1, float a2) {   // src/ORBmatcher.cc:697-702 (same at :221-226, 1318-1323)
+    float rot = a1 - a2;
+    if (rot < 0.0) rot += 360.0f;
+    int bin = (int)std::round(rot * (1.0f / HISTO_LENGTH));
+    if (bin == HISTO_LENGTH) bin = 0;
+    return bin;
+}
+
+}  // namespace
+
+// ================================================================================================
+YGZO_API int ygzo_descriptor_distance(const uint8_t *a, const uint8_t *b) { return descriptorDistance(a, b); }
+
+// Brute-force kNN (k = 2) + ratio test, BASELINE.json config 5: the best / second-best rule of
+// ORBmatcher::SearchByBoW (src/ORBmatcher.cc:193-217) over ALL train rows in index order.
+// match[q] = best index if bestDist1 <= th and (float)bestDist1 < ratio * (float)bestDist2, else -1.
+YGZO_API void ygzo_hamming_knn2(const uint8_t *query, int nq, const uint8_t *train, int nt, float ratio, int th,
+                                int threads, int32_t *bestIdx, int32_t *d1, int32_t *d2, int32_t *match) {
+    parallelFor(nq, threads, 64, [&](long b, long e) {
+        for (long q = b; q < e; q++) {
+            int bestDist1 = 256, bestDist2 = 256, best = -1;
+            const uint8_t *dq = query + q * 32;
+            for (int j = 0; j < nt; j++) {
+                const int dist = descriptorDistance(dq, train + (size_t)j * 32);
+                if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; best = j; }
+                else if (dist < bestDist2) bestDist2 = dist;
+            }
+            bestIdx[q] = best; d1[q] = bestDist1; d2[q] = bestDist2;
+            match[q] = (bestDist1 <= th && (float)bestDist1 < ratio * (float)bestDist2) ? best : -1;
+        }
+    });
+}
+
+// ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th, checkLevel) — src/ORBmatcher.cc:44-126
+// with RadiusByViewingCos (:128-133).  MapPoint state is flattened: inView = mbTrackInView && !isBad(),
+// hasObs = Observations() > 0 (decides whether a claimed keypoint blocks later MapPoints, :89-91).
+// claimed[idx] = the frame already holds a MapPoint with observations at idx on entry.
+// kpToMp[idx] = index of the MapPoint written to F.mvpMapPoints[idx] by this call (last writer), else -1.
+YGZO_API int ygzo_search_by_projection(const void *kpsV, const uint8_t *desc, const float *uRight, const uint8_t *claimed,
+                                       int n, float minX, float minY, float invW, float invH, const float *scaleFactors,
+                                       const float *projX, const float *projY, const float *projXR, const float *viewCos,
+                                       const int32_t *level, const uint8_t *inView, const uint8_t *hasObs,
+                                       const uint8_t *mpDesc, int m, float th, int checkLevel, float nnratio,
+                                       int32_t *kpToMp, int32_t *mpBestIdx) {
+    const KeyPoint *kps = (const KeyPoint *)kpsV;
+    Grid g;
+    assignGrid(g, kps, n, minX, minY, invW, invH);
+    std::vector<int> owner(n, -1);               // MapPoint index written this call
+    std::vector<uint8_t> blocked(n, 0);
+    for (int i = 0; i < n; i++) { kpToMp[i] = -1; blocked[i] = claimed ? claimed[i] : 0; }
+    int nmatches = 0;
+    const bool bFactor = th != 1.0;
+    std::vector<int> vIndices;
+    for (int iMP = 0; iMP < m; iMP++) {
+        if (mpBestIdx) mpBestIdx[iMP] = -1;
+        if (!inView[iMP]) continue;
+        const int nPredictedLevel = level[iMP];
+        float r = viewCos[iMP] > 0.998 ? 2.5f : 4.0f;
+        if (bFactor) r *= th;
+        const float rad = r * scaleFactors[nPredictedLevel];
+        if (checkLevel) featuresInArea(g, kps, projX[iMP], projY[iMP], rad, nPredictedLevel - 1, nPredictedLevel, vIndices);
+        else featuresInArea(g, kps, projX[iMP], projY[iMP], rad, -1, -1, vIndices);
+        if (vIndices.empty()) continue;
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int idx : vIndices) {
+            if (blocked[idx]) continue;
+            if (uRight && uRight[idx] > 0) {
+                const float er = std::fabs(projXR[iMP] - uRight[idx]);
+                if (er > rad) continue;
+            }
+            const int dist = descriptorDistance(mpDesc + (size_t)iMP * 32, desc + (size_t)idx * 32);
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = kps[idx].octave; bestIdx = idx; }
+            else if (dist < bestDist2) { bestLevel2 = kps[idx].octave; bestDist2 = dist; }
+        }
+        if (bestDist <= TH_HIGH) {
+            if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+            kpToMp[bestIdx] = iMP;
+            blocked[bestIdx] = hasObs[iMP] ? 1 : 0;
+            if (mpBestIdx) mpBestIdx[iMP] = bestIdx;
+            nmatches++;
+        }
+    }
+    return nmatches;
+}
+
+// ORBmatcher::SearchForTriangulation — src/ORBmatcher.cc:597-746 with CheckDistEpipolarLine (:136-153).
+// The two DBoW2::FeatureVectors (std::map<NodeId, vector<unsigned>>, ascending NodeId) are flattened
+// to CSR: nodeIds[k] ascending, features of node k = feats[start[k] .. start[k+1]).  hasMP = the
+// keyframe already holds a MapPoint at that keypoint (GetMapPoint != NULL).  (ex, ey) = epipole of
+// KF1's centre in KF2 (:604-610, computed by the caller).  F12 row-major: F12[3*r + c] = F12(r, c).
+// matches12[idx1] = idx2 or -1 (vMatches12); returns nmatches.  vbMatched2 is never set by the
+// reference (:616, 660), so keypoints of KF2 can be matched more than once — reproduced.
+YGZO_API int ygzo_search_for_triangulation(
+    const void *kps1V, const uint8_t *desc1, const float *uRight1, const uint8_t *hasMP1, int n1,
+    const uint32_t *nodeIds1, const int32_t *start1, const uint32_t *feats1, int nNodes1,
+    const void *kps2V, const uint8_t *desc2, const float *uRight2, const uint8_t *hasMP2, int n2,
+    const uint32_t *nodeIds2, const int32_t *start2, const uint32_t *feats2, int nNodes2,
+    const float *scaleFactors2, const float *levelSigma2_2, const float *F12, float ex, float ey,
+    int bOnlyStereo, int checkOrientation, int32_t *matches12) {
+    const KeyPoint *kps1 = (const KeyPoint *)kps1V, *kps2 = (const KeyPoint *)kps2V;
+    (void)n2;
+    int nmatches = 0;
+    for (int i = 0; i < n1; i++) matches12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    int a = 0, b = 0;
+    while (a < nNodes1 && b < nNodes2) {
+        if (nodeIds1[a] == nodeIds2[b]) {
+            for (int i1 = start1[a]; i1 < start1[a + 1]; i1++) {
+                const int idx1 = (int)feats1[i1];
+                if (hasMP1[idx1]) continue;
+                const bool bStereo1 = uRight1[idx1] >= 0;
+                if (bOnlyStereo && !bStereo1) continue;
+                const KeyPoint &kp1 = kps1[idx1];
+                int bestDist = TH_LOW, bestIdx2 = -1;
+                for (int i2 = start2[b]; i2 < start2[b + 1]; i2++) {
+                    const int idx2 = (int)feats2[i2];
+                    if (hasMP2[idx2]) continue;
+                    const bool bStereo2 = uRight2[idx2] >= 0;
+                    if (bOnlyStereo && !bStereo2) continue;
+                    const int dist = descriptorDistance(desc1 + (size_t)idx1 * 32, desc2 + (size_t)idx2 * 32);
+                    if (dist > TH_LOW || dist > bestDist) continue;
+                    const KeyPoint &kp2 = kps2[idx2];
+                    if (!bStereo1 && !bStereo2) {
+                        const float distex = ex - kp2.x, distey = ey - kp2.y;
+                        if (distex * distex + distey * distey < 100 * scaleFactors2[kp2.octave]) continue;
+                    }
+                    // CheckDistEpipolarLine
+                    const float la = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
+                    const float lb = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
+                    const float lc = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];
+                    const float num = la * kp2.x + lb * kp2.y + lc;
+                    const float den = la * la + lb * lb;
+                    if (den == 0) continue;
+                    const float dsqr = num * num / den;
+                    if (dsqr < 3.84 * levelSigma2_2[kp2.octave]) { bestIdx2 = idx2; bestDist = dist; }
+                }
+                if (bestIdx2 >= 0) {
+                    matches12[idx1] = bestIdx2;
+                    nmatches++;
+                    if (checkOrientation) rotHist[rotationBin(kp1.angle, kps2[bestIdx2].angle)].push_back(idx1);
+                }
+            }
+            a++; b++;
+        } else if (nodeIds1[a] < nodeIds2[b]) {
+            a = (int)(std::lower_bound(nodeIds1, nodeIds1 + nNodes1, nodeIds2[b]) - nodeIds1);
+        } else {
+            b = (int)(std::lower_bound(nodeIds2, nodeIds2 + nNodes2, nodeIds1[a]) - nodeIds2);
+        }
+    }
+    if (checkOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1, sizes[HISTO_LENGTH];
+        for (int i = 0; i < HISTO_LENGTH; i++) sizes[i] = (int)rotHist[i].size();
+        threeMaxima(sizes, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx1 : rotHist[i]) { matches12[idx1] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
+// Frame::ComputeStereoMatches — src/Frame.cc:509-682.  Pyramids: level l of the left / right
+// extractor at pyrL + offL[l], continuous (step == cols == lw[l]).  Outputs mvuRight / mvDepth
+// (-1 = no match) and, for tests, the integer SAD kept per accepted keypoint (bestDistOut, -1 if none).
+// UB in the reference when no keypoint matches at all (:671 indexes an empty vector) -> no cut here.
+YGZO_API void ygzo_stereo_match(const void *kpsLV, const uint8_t *descL, int nL, const void *kpsRV, const uint8_t *descR,
+                                int nR, const uint8_t *pyrL, const uint8_t *pyrR, const int64_t *off, const int32_t *lw,
+                                const int32_t *lh, const float *scaleFactors, const float *invScaleFactors,
+                                float mbf, float mb, float *uRightOut, float *depthOut, int32_t *bestDistOut) {
+    const KeyPoint *kpsL = (const KeyPoint *)kpsLV, *kpsR = (const KeyPoint *)kpsRV;
+    for (int i = 0; i < nL; i++) { uRightOut[i] = -1.0f; depthOut[i] = -1.0f; if (bestDistOut) bestDistOut[i] = -1; }
+    const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
+    const int nRows = lh[0];
+    std::vector<std::vector<int>> vRowIndices(nRows);
+    for (int iR = 0; iR < nR; iR++) {
+        const float kpY = kpsR[iR].y;
+        const float r = 2.0f * scaleFactors[kpsR[iR].octave];
+        const int maxr = (int)std::ceil(kpY + r), minr = (int)std::floor(kpY - r);
+        for (int yi = minr; yi <= maxr; yi++)
+            if (yi >= 0 && yi < nRows) vRowIndices[yi].push_back(iR);   // out of range = UB in the reference
+    }
+    const float minZ = mb, minD = 0, maxD = mbf / minZ;
+    std::vector<std::pair<int, int>> vDistIdx;
+    for (int iL = 0; iL < nL; iL++) {
+        const KeyPoint &kpL = kpsL[iL];
+        const int levelL = kpL.octave;
+        const float vL = kpL.y, uL = kpL.x;
+        const int row = (int)vL;
+        if (row < 0 || row >= nRows) continue;
+        const std::vector<int> &vCandidates = vRowIndices[row];
+        if (vCandidates.empty()) continue;
+        const float minU = uL - maxD, maxU = uL - minD;
+        if (maxU < 0) continue;
+        int bestDist = TH_HIGH, bestIdxR = 0;
+        for (int iR : vCandidates) {
+            const KeyPoint &kpR = kpsR[iR];
+            if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
+            const float uR = kpR.x;
+            if (uR >= minU && uR <= maxU) {
+                const int dist = descriptorDistance(descL + (size_t)iL * 32, descR + (size_t)iR * 32);
+                if (dist < bestDist) { bestDist = dist; bestIdxR = iR; }
+            }
+        }
+        if (bestDist < thOrbDist) {
+            const float uR0 = kpsR[bestIdxR].x;
+            const float scaleFactor = invScaleFactors[kpL.octave];
+            const float scaleduL = std::round(kpL.x * scaleFactor);
+            const float scaledvL = std::round(kpL.y * scaleFactor);
+            const float scaleduR0 = std::round(uR0 * scaleFactor);
+            const int w = 5, L = 5;
+            const int lvW = lw[kpL.octave];
+            const uint8_t *imL = pyrL + off[kpL.octave], *imR = pyrR + off[kpL.octave];
+            const int y0 = (int)(scaledvL - w), xL0 = (int)(scaleduL - w);
+            const float iniu = scaleduR0 + L - w, endu = scaleduR0 + L + w + 1;
+            if (iniu < 0 || endu >= lvW) continue;
+            const int cL = imL[(size_t)(y0 + w) * lvW + xL0 + w];
+            int bestSad = INT_MAX, bestincR = 0;
+            float vDists[2 * 5 + 1];
+            for (int incR = -L; incR <= L; incR++) {
+                const int xR0 = (int)(scaleduR0 + incR - w);
+                const int cR = imR[(size_t)(y0 + w) * lvW + xR0 + w];
+                double acc = 0;   // cv::norm(NORM_L1) of two CV_32F patches accumulates |a - b| in double
+                for (int yy = 0; yy < 2 * w + 1; yy++)
+                    for (int xx = 0; xx < 2 * w + 1; xx++) {
+                        const float a = (float)imL[(size_t)(y0 + yy) * lvW + xL0 + xx] - (float)cL;
+                        const float b = (float)imR[(size_t)(y0 + yy) * lvW + xR0 + xx] - (float)cR;
+                        acc += std::fabs(a - b);
+                    }
+                const float dist = (float)acc;
+                if (dist < bestSad) { bestSad = (int)dist; bestincR = incR; }
+                vDists[L + incR] = dist;
+            }
+            if (bestincR == -L || bestincR == L) continue;
+            const float dist1 = vDists[L + bestincR - 1], dist2 = vDists[L + bestincR], dist3 = vDists[L + bestincR + 1];
+            const float deltaR = (dist1 - dist3) / (2.0f * (dist1 + dist3 - 2.0f * dist2));
+            if (deltaR < -1 || deltaR > 1) continue;
+            float bestuR = scaleFactors[kpL.octave] * ((float)scaleduR0 + (float)bestincR + deltaR);
+            float disparity = (uL - bestuR);
+            if (disparity >= minD && disparity < maxD) {
+                if (disparity <= 0) { disparity = 0.01; bestuR = uL - 0.01; }
+                depthOut[iL] = mbf / disparity;
+                uRightOut[iL] = bestuR;
+                if (bestDistOut) bestDistOut[iL] = bestSad;
+                vDistIdx.push_back(std::make_pair(bestSad, iL));
+            }
+        }
+    }
+    if (vDistIdx.empty()) return;
+    std::sort(vDistIdx.begin(), vDistIdx.end());
+    const float median = vDistIdx[vDistIdx.size() / 2].first;
+    const float thDist = 1.5f * 1.4f * median;
+    for (int i = (int)vDistIdx.size() - 1; i >= 0; i--) {
+        if (vDistIdx[i].first < thDist) break;
+        uRightOut[vDistIdx[i].second] = -1;
+        depthOut[vDistIdx[i].second] = -1;
+    }
+}

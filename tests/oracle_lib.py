@@ -34,7 +34,7 @@ def lib():
 
 
 def _p(a):
-    return a.ctypes.data_as(C.c_void_p)
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
 
 
 def _img(a):
@@ -174,3 +174,88 @@ def extract_batch(p, frames, threads=1, cap=None, want_output=True):
     lib().ygzo_extract_batch(C.byref(p), _p(frames), n, w, h, cap, threads, _p(counts),
                              _p(kps) if want_output else None, _p(desc) if want_output else None)
     return counts, kps, desc
+
+
+# ---- part 2: matchers (oracle/match_oracle.cpp) ------------------------------------------------
+def descriptor_distance(a, b):
+    a = np.ascontiguousarray(a, np.uint8)
+    b = np.ascontiguousarray(b, np.uint8)
+    return lib().ygzo_descriptor_distance(_p(a), _p(b))
+
+
+def hamming_knn2(query, train, ratio, th, threads=1):
+    query = np.ascontiguousarray(query, np.uint8)
+    train = np.ascontiguousarray(train, np.uint8)
+    nq, nt = len(query), len(train)
+    idx, d1, d2, match = (np.zeros(nq, np.int32) for _ in range(4))
+    lib().ygzo_hamming_knn2(_p(query), nq, _p(train), nt, C.c_float(ratio), th, threads, _p(idx), _p(d1), _p(d2), _p(match))
+    return idx, d1, d2, match
+
+
+def grid_inv(min_x, min_y, max_x, max_y):
+    """mfGridElementWidthInv / HeightInv (src/Frame.cc:296-297), float arithmetic."""
+    inv_w = np.float32(64) / (np.float32(max_x) - np.float32(min_x))
+    inv_h = np.float32(48) / (np.float32(max_y) - np.float32(min_y))
+    return np.float32(inv_w), np.float32(inv_h)
+
+
+def search_by_projection(kps, desc, u_right, claimed, bounds, scale_factors, mp, th, check_level, nnratio):
+    """mp: dict with proj_x, proj_y, proj_xr, view_cos (f4), level (i4), in_view, has_obs (u1), desc (m,32)."""
+    n, m = len(kps), len(mp["proj_x"])
+    kps = np.ascontiguousarray(kps)
+    desc = np.ascontiguousarray(desc, np.uint8)
+    min_x, min_y, max_x, max_y = bounds
+    inv_w, inv_h = grid_inv(*bounds)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    kp_to_mp = np.zeros(max(n, 1), np.int32)
+    mp_best = np.zeros(max(m, 1), np.int32)
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    u8 = lambda a: np.ascontiguousarray(a, np.uint8)
+    px, py, pxr, vc = f32(mp["proj_x"]), f32(mp["proj_y"]), f32(mp["proj_xr"]), f32(mp["view_cos"])
+    lv, iv, ho, md = np.ascontiguousarray(mp["level"], np.int32), u8(mp["in_view"]), u8(mp["has_obs"]), u8(mp["desc"])
+    ur = f32(u_right) if u_right is not None else None
+    cl = u8(claimed) if claimed is not None else None
+    nm = lib().ygzo_search_by_projection(_p(kps), _p(desc), _p(ur), _p(cl), n, C.c_float(min_x), C.c_float(min_y),
+                                         C.c_float(inv_w), C.c_float(inv_h), _p(sf), _p(px), _p(py), _p(pxr), _p(vc),
+                                         _p(lv), _p(iv), _p(ho), _p(md), m, C.c_float(th), int(check_level),
+                                         C.c_float(nnratio), _p(kp_to_mp), _p(mp_best))
+    return nm, kp_to_mp[:n].copy(), mp_best[:m].copy()
+
+
+def search_for_triangulation(kf1, kf2, F12, ex, ey, only_stereo, check_orientation):
+    """kf: dict with kps, desc, u_right, has_mp, node_ids, node_start, node_feats, scale_factors, level_sigma2."""
+    def pk(kf):
+        return (np.ascontiguousarray(kf["kps"]), np.ascontiguousarray(kf["desc"], np.uint8),
+                np.ascontiguousarray(kf["u_right"], np.float32), np.ascontiguousarray(kf["has_mp"], np.uint8),
+                np.ascontiguousarray(kf["node_ids"], np.uint32), np.ascontiguousarray(kf["node_start"], np.int32),
+                np.ascontiguousarray(kf["node_feats"], np.uint32))
+    a, b = pk(kf1), pk(kf2)
+    sf2 = np.ascontiguousarray(kf2["scale_factors"], np.float32)
+    s2 = np.ascontiguousarray(kf2["level_sigma2"], np.float32)
+    F = np.ascontiguousarray(F12, np.float32).reshape(9)
+    m12 = np.zeros(max(len(a[0]), 1), np.int32)
+    nm = lib().ygzo_search_for_triangulation(
+        _p(a[0]), _p(a[1]), _p(a[2]), _p(a[3]), len(a[0]), _p(a[4]), _p(a[5]), _p(a[6]), len(a[4]),
+        _p(b[0]), _p(b[1]), _p(b[2]), _p(b[3]), len(b[0]), _p(b[4]), _p(b[5]), _p(b[6]), len(b[4]),
+        _p(sf2), _p(s2), _p(F), C.c_float(ex), C.c_float(ey), int(only_stereo), int(check_orientation), _p(m12))
+    return nm, m12[:len(a[0])].copy()
+
+
+def stereo_match(kps_l, desc_l, kps_r, desc_r, pyr_l, pyr_r, scale_factors, inv_scale_factors, bf, b):
+    """pyr_*: list of level images (uint8 2-D).  Returns (u_right, depth, best_sad)."""
+    kps_l, kps_r = np.ascontiguousarray(kps_l), np.ascontiguousarray(kps_r)
+    desc_l, desc_r = np.ascontiguousarray(desc_l, np.uint8), np.ascontiguousarray(desc_r, np.uint8)
+    lw = np.array([l.shape[1] for l in pyr_l], np.int32)
+    lh = np.array([l.shape[0] for l in pyr_l], np.int32)
+    off = np.zeros(len(pyr_l), np.int64)
+    off[1:] = np.cumsum(lw[:-1].astype(np.int64) * lh[:-1])
+    pl = np.concatenate([np.ascontiguousarray(l, np.uint8).ravel() for l in pyr_l])
+    pr = np.concatenate([np.ascontiguousarray(l, np.uint8).ravel() for l in pyr_r])
+    n = len(kps_l)
+    ur, dp = np.zeros(max(n, 1), np.float32), np.zeros(max(n, 1), np.float32)
+    bd = np.zeros(max(n, 1), np.int32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    isf = np.ascontiguousarray(inv_scale_factors, np.float32)
+    lib().ygzo_stereo_match(_p(kps_l), _p(desc_l), n, _p(kps_r), _p(desc_r), len(kps_r), _p(pl), _p(pr), _p(off), _p(lw),
+                            _p(lh), _p(sf), _p(isf), C.c_float(bf), C.c_float(b), _p(ur), _p(dp), _p(bd))
+    return ur[:n].copy(), dp[:n].copy(), bd[:n].copy()

@@ -73,3 +73,108 @@ def flip_bits(desc, nflips, rng):
         for b in bits:
             out[i, b >> 3] ^= np.uint8(1 << (b & 7))
     return out
+
+
+# ---- matcher inputs -------------------------------------------
+def scale_tables(scale=1.2, levels=8):
+    """mvScaleFactor / mvInvScaleFactor / mvLevelSigma2 as the extractor builds them (float chain)."""
+    sf = np.ones(levels, np.float32)
+    for i in range(1, levels):
+        sf[i] = np.float32(np.float64(sf[i - 1]) * np.float64(np.float32(scale)))
+    return sf, (np.float32(1.0) / sf).astype(np.float32), (sf * sf).astype(np.float32)
+
+
+def projection_case(kps, desc, n_mp, seed, jitter=3.0, p_not_in_view=0.05, p_no_obs=0.03, stereo=False):
+    """n_mp synthetic MapPoints drawn from a frame's own keypoints: projected position = keypoint
+    +-jitter px, level = source octave, descriptor = source descriptor with 0..40 random bit flips."""
+    rng = np.random.default_rng(seed)
+    n = len(kps)
+    src = rng.integers(0, n, size=n_mp)
+    mp = {
+        "proj_x": (kps["x"][src] + rng.uniform(-jitter, jitter, n_mp)).astype(np.float32),
+        "proj_y": (kps["y"][src] + rng.uniform(-jitter, jitter, n_mp)).astype(np.float32),
+        "view_cos": rng.uniform(0.9, 1.0, n_mp).astype(np.float32),
+        "level": kps["octave"][src].astype(np.int32),
+        "in_view": (rng.uniform(size=n_mp) >= p_not_in_view).astype(np.uint8),
+        "has_obs": (rng.uniform(size=n_mp) >= p_no_obs).astype(np.uint8),
+        "desc": flip_bits(desc[src], rng.integers(0, 41, size=n_mp), rng),
+        "src": src,
+    }
+    mp["proj_xr"] = (mp["proj_x"] - rng.uniform(2, 60, n_mp)).astype(np.float32)
+    u_right = None
+    if stereo:
+        u_right = np.where(rng.uniform(size=n) < 0.6, kps["x"] - rng.uniform(2, 60, n), -1.0).astype(np.float32)
+    claimed = (rng.uniform(size=n) < 0.05).astype(np.uint8)
+    return mp, u_right, claimed
+
+
+def feature_vector(n, n_nodes, seed, base=None, p_keep=0.8):
+    """Synthetic DBoW2::FeatureVector as CSR: ascending node ids, features in insertion (index) order.
+    With `base` (node of each feature of another keyframe mapped through `src`) matched features
+    share nodes with probability p_keep."""
+    rng = np.random.default_rng(seed)
+    node = rng.integers(0, n_nodes, size=n) * 7 + 3
+    if base is not None:
+        keep = rng.uniform(size=n) < p_keep
+        node = np.where(keep, base, node)
+    ids = np.unique(node)
+    start = np.zeros(len(ids) + 1, np.int32)
+    feats = []
+    for k, nid in enumerate(ids):
+        f = np.nonzero(node == nid)[0]
+        feats.append(f)
+        start[k + 1] = start[k] + len(f)
+    feats = np.concatenate(feats).astype(np.uint32) if feats else np.zeros(0, np.uint32)
+    return node, ids.astype(np.uint32), start, feats
+
+
+def triangulation_case(kps, desc, seed, levels=8, scale=1.2, n_nodes=120):
+    """KF1 = the given features; KF2 = a shuffled subset moved along x (pure x translation, so the
+    epipolar line of (x1, y1) is y2 ~= y1) with descriptor noise, plus unrelated features."""
+    rng = np.random.default_rng(seed)
+    n1 = len(kps)
+    sf, isf, s2 = scale_tables(scale, levels)
+    perm = rng.permutation(n1)
+    n2 = n1
+    kps2 = kps[perm].copy()
+    moved = rng.uniform(size=n2) < 0.7
+    kps2["x"] = np.where(moved, kps2["x"] - rng.uniform(1, 40, n2), rng.uniform(20, 700, n2)).astype(np.float32)
+    kps2["y"] = np.where(moved, kps2["y"] + rng.normal(0, 1.0, n2) * sf[kps2["octave"]], rng.uniform(20, 450, n2)).astype(np.float32)
+    kps2["angle"] = np.mod(kps2["angle"] + rng.normal(0, 8, n2), 360).astype(np.float32)
+    desc2 = flip_bits(desc[perm], np.where(moved, rng.integers(0, 60, n2), 128), rng)
+    node1, ids1, st1, f1 = feature_vector(n1, n_nodes, seed + 1)
+    node2, ids2, st2, f2 = feature_vector(n2, n_nodes, seed + 2, base=node1[perm])
+    kf1 = {"kps": kps, "desc": desc, "u_right": np.where(rng.uniform(size=n1) < 0.3, kps["x"] - 5, -1).astype(np.float32),
+           "has_mp": (rng.uniform(size=n1) < 0.3).astype(np.uint8), "node_ids": ids1, "node_start": st1, "node_feats": f1,
+           "scale_factors": sf, "level_sigma2": s2}
+    kf2 = {"kps": kps2, "desc": desc2, "u_right": np.where(rng.uniform(size=n2) < 0.3, kps2["x"] - 5, -1).astype(np.float32),
+           "has_mp": (rng.uniform(size=n2) < 0.3).astype(np.uint8), "node_ids": ids2, "node_start": st2, "node_feats": f2,
+           "scale_factors": sf, "level_sigma2": s2}
+    F12 = np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32) + rng.normal(0, 1e-5, (3, 3)).astype(np.float32)
+    return kf1, kf2, F12, np.float32(400.0), np.float32(240.0)
+
+
+def stereo_pair(w, h, seed, max_disp=40):
+    """Left = textured frame; right = left resampled with a smooth disparity field (2..max_disp px) + noise."""
+    rng = np.random.default_rng(seed)
+    wide = textured_frame(w + max_disp + 8, h, seed).astype(np.float64)
+    left = wide[:, :w]
+    disp = 2 + (max_disp - 2) * (0.5 + 0.5 * np.sin(np.linspace(0, 3.0, h)))[:, None] * np.ones((1, w))
+    xs = np.arange(w)[None, :] + disp       # right(x) = left(x + d): a point at uL appears at uR = uL - d
+    x0 = np.floor(xs).astype(int)
+    fr = xs - x0
+    rows = np.arange(h)[:, None]
+    right = wide[rows, x0] * (1 - fr) + wide[rows, x0 + 1] * fr + rng.normal(0, 2.0, (h, w))
+    return np.clip(np.rint(left), 0, 255).astype(np.uint8), np.clip(np.rint(right), 0, 255).astype(np.uint8)
+
+
+def knn_case(nq, nt, seed):
+    """Config 5: train uniform random; half of the queries are train rows with Binomial(256, 0.1) bit flips."""
+    rng = np.random.default_rng(seed)
+    train = rng.integers(0, 256, size=(nt, 32), dtype=np.uint8)
+    query = rng.integers(0, 256, size=(nq, 32), dtype=np.uint8)
+    half = nq // 2
+    src = rng.integers(0, nt, size=half)
+    noise = np.packbits((rng.uniform(size=(half, 256)) < 0.1).astype(np.uint8), axis=1, bitorder="little")
+    query[:half] = train[src] ^ noise
+    return query, train

@@ -1,0 +1,242 @@
+"""CPU checks of the matcher oracle (oracle/match_oracle.cpp): 'parity unpinned' by the reference,
+so each function is compared with an independent brute-force re-derivation in numpy / pure Python
+written from the reference's rules, on small seeded cases."""
+import math
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+import synth
+
+
+def _hamming_matrix(a, b):
+    x = np.bitwise_xor(a[:, None, :], b[None, :, :])
+    return np.unpackbits(x, axis=2).sum(axis=2).astype(np.int32)
+
+
+def _features(w=320, h=240, seed=3, nf=400):
+    img = synth.textured_frame(w, h, seed)
+    return img, O.extract(O.params(nf), img)
+
+
+def test_descriptor_distance():
+    rng = np.random.default_rng(0)
+    a = rng.integers(0, 256, size=(50, 32), dtype=np.uint8)
+    b = rng.integers(0, 256, size=(50, 32), dtype=np.uint8)
+    d = _hamming_matrix(a, b)
+    for i in range(50):
+        assert O.descriptor_distance(a[i], b[i]) == d[i, i]
+    assert O.descriptor_distance(a[0], a[0]) == 0
+    assert O.descriptor_distance(np.zeros(32, np.uint8), np.full(32, 255, np.uint8)) == 256
+
+
+@pytest.mark.parametrize("nq,nt,ratio,th", [(200, 300, 0.6, 50), (64, 1, 0.9, 100), (100, 257, 0.75, 256), (5, 0, 0.6, 50)])
+def test_knn2_vs_numpy(nq, nt, ratio, th):
+    q, t = synth.knn_case(nq, max(nt, 1), 5)
+    t = t[:nt]
+    idx, d1, d2, match = O.hamming_knn2(q, t, ratio, th, threads=2)
+    if nt == 0:
+        assert (idx == -1).all() and (d1 == 256).all() and (match == -1).all()
+        return
+    D = _hamming_matrix(q, t)
+    bi = D.argmin(axis=1)                       # first index of the minimum
+    assert np.array_equal(idx, bi) and np.array_equal(d1, D[np.arange(nq), bi])
+    D2 = D.copy(); D2[np.arange(nq), bi] = 257
+    exp2 = np.minimum(D2.min(axis=1), 256) if nt > 1 else np.full(nq, 256)
+    assert np.array_equal(d2, exp2)
+    ok = (d1 <= th) & (d1.astype(np.float32) < np.float32(ratio) * d2.astype(np.float32))
+    assert np.array_equal(match, np.where(ok, bi, -1))
+
+
+def _py_search_by_projection(kps, desc, u_right, claimed, bounds, sf, mp, th, check_level, ratio):
+    """Independent pure-Python restatement of src/ORBmatcher.cc:44-126 + src/Frame.cc:424-493."""
+    f = np.float32
+    min_x, min_y, max_x, max_y = [f(v) for v in bounds]
+    inv_w, inv_h = f(64) / (max_x - min_x), f(48) / (max_y - min_y)
+    rnd = lambda v: int(math.floor(abs(v) + 0.5)) * (1 if v >= 0 else -1)
+    grid = {}
+    for i in range(len(kps)):
+        px, py = rnd(float((kps["x"][i] - min_x) * inv_w)), rnd(float((kps["y"][i] - min_y) * inv_h))
+        if 0 <= px < 64 and 0 <= py < 48:
+            grid.setdefault((px, py), []).append(i)
+    D = _hamming_matrix(mp["desc"], desc)
+    blocked = claimed.astype(bool).copy() if claimed is not None else np.zeros(len(kps), bool)
+    kp_to_mp = np.full(len(kps), -1, np.int32)
+    best_of = np.full(len(mp["proj_x"]), -1, np.int32)
+    n = 0
+    for i in range(len(mp["proj_x"])):
+        if not mp["in_view"][i]:
+            continue
+        lvl = int(mp["level"][i])
+        r = f(2.5) if float(mp["view_cos"][i]) > 0.998 else f(4.0)
+        if th != 1.0:
+            r = f(r * f(th))
+        rad = f(r * sf[lvl])
+        x, y = f(mp["proj_x"][i]), f(mp["proj_y"][i])
+        cx0 = max(0, math.floor(float(f(f(x - min_x - rad) * inv_w)))); cx1 = min(63, math.ceil(float(f(f(x - min_x + rad) * inv_w))))
+        cy0 = max(0, math.floor(float(f(f(y - min_y - rad) * inv_h)))); cy1 = min(47, math.ceil(float(f(f(y - min_y + rad) * inv_h))))
+        if cx0 >= 64 or cx1 < 0 or cy0 >= 48 or cy1 < 0:
+            continue
+        b1, b2, l1, l2, bi = 256, 256, -1, -1, -1
+        found = False
+        for ix in range(cx0, cx1 + 1):
+            for iy in range(cy0, cy1 + 1):
+                for idx in grid.get((ix, iy), []):
+                    o = int(kps["octave"][idx])
+                    if check_level and (o < lvl - 1 or o > lvl):
+                        continue
+                    if not (abs(f(kps["x"][idx] - x)) < rad and abs(f(kps["y"][idx] - y)) < rad):
+                        continue
+                    found = True
+                    if blocked[idx]:
+                        continue
+                    if u_right is not None and u_right[idx] > 0 and abs(f(mp["proj_xr"][i] - u_right[idx])) > rad:
+                        continue
+                    d = int(D[i, idx])
+                    if d < b1:
+                        b2, b1, l2, l1, bi = b1, d, l1, o, idx
+                    elif d < b2:
+                        l2, b2 = o, d
+        if not found:
+            continue
+        if b1 <= 100:
+            if l1 == l2 and f(b1) > f(ratio) * f(b2):
+                continue
+            kp_to_mp[bi] = i; blocked[bi] = bool(mp["has_obs"][i]); best_of[i] = bi; n += 1
+    return n, kp_to_mp, best_of
+
+
+@pytest.mark.parametrize("th,check_level,stereo,seed", [(1.0, False, False, 1), (5.0, False, True, 2), (3.0, True, False, 3),
+                                                         (15.0, False, False, 4)])
+def test_search_by_projection_vs_python(th, check_level, stereo, seed):
+    img, (kps, desc) = _features(seed=seed)
+    sf, _, _ = synth.scale_tables()
+    mp, u_right, claimed = synth.projection_case(kps, desc, 600, seed, stereo=stereo)
+    bounds = (0.0, 0.0, float(img.shape[1]), float(img.shape[0]))
+    a = O.search_by_projection(kps, desc, u_right, claimed, bounds, sf, mp, th, check_level, 0.8)
+    b = _py_search_by_projection(kps, desc, u_right, claimed, bounds, sf, mp, th, check_level, 0.8)
+    assert a[0] == b[0] and a[0] > 50
+    assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+
+
+def test_search_by_projection_order_dependence():
+    """Two MapPoints with the same descriptor on the same keypoint: the first claims it, the second must skip it."""
+    img, (kps, desc) = _features(seed=9)
+    sf, _, _ = synth.scale_tables()
+    k = 10
+    mp = {"proj_x": np.array([kps["x"][k]] * 2, np.float32), "proj_y": np.array([kps["y"][k]] * 2, np.float32),
+          "proj_xr": np.zeros(2, np.float32), "view_cos": np.array([0.95, 0.95], np.float32),
+          "level": np.array([kps["octave"][k]] * 2, np.int32), "in_view": np.ones(2, np.uint8),
+          "has_obs": np.array([1, 1], np.uint8), "desc": np.stack([desc[k], desc[k]])}
+    nm, kp_to_mp, best = O.search_by_projection(kps, desc, None, None, (0, 0, img.shape[1], img.shape[0]), sf, mp, 1.0, False, 0.8)
+    assert best[0] == k and kp_to_mp[k] == 0 and best[1] != k
+    mp["has_obs"] = np.array([0, 1], np.uint8)          # first has no observations: the second overwrites it
+    nm, kp_to_mp, best = O.search_by_projection(kps, desc, None, None, (0, 0, img.shape[1], img.shape[0]), sf, mp, 1.0, False, 0.8)
+    assert best[0] == k and best[1] == k and kp_to_mp[k] == 1 and nm == 2
+
+
+def _py_triangulation(kf1, kf2, F12, ex, ey, only_stereo, check_ori):
+    f = np.float32
+    D = _hamming_matrix(kf1["desc"], kf2["desc"])
+    n1 = len(kf1["kps"])
+    m12 = np.full(n1, -1, np.int32)
+    nodes2 = {int(nid): k for k, nid in enumerate(kf2["node_ids"])}
+    F = F12.astype(np.float32)
+    bins = {}
+    for a, nid in enumerate(kf1["node_ids"]):
+        if int(nid) not in nodes2:
+            continue
+        b = nodes2[int(nid)]
+        for idx1 in kf1["node_feats"][kf1["node_start"][a]:kf1["node_start"][a + 1]]:
+            idx1 = int(idx1)
+            if kf1["has_mp"][idx1]:
+                continue
+            s1 = kf1["u_right"][idx1] >= 0
+            if only_stereo and not s1:
+                continue
+            x1, y1 = f(kf1["kps"]["x"][idx1]), f(kf1["kps"]["y"][idx1])
+            best, bi = 50, -1
+            for idx2 in kf2["node_feats"][kf2["node_start"][b]:kf2["node_start"][b + 1]]:
+                idx2 = int(idx2)
+                if kf2["has_mp"][idx2]:
+                    continue
+                s2 = kf2["u_right"][idx2] >= 0
+                if only_stereo and not s2:
+                    continue
+                d = int(D[idx1, idx2])
+                if d > 50 or d > best:
+                    continue
+                x2, y2, o2 = f(kf2["kps"]["x"][idx2]), f(kf2["kps"]["y"][idx2]), int(kf2["kps"]["octave"][idx2])
+                if not s1 and not s2:
+                    dx, dy = f(f(ex) - x2), f(f(ey) - y2)
+                    if f(f(dx * dx) + f(dy * dy)) < f(f(100) * kf2["scale_factors"][o2]):
+                        continue
+                la = f(f(f(x1 * F[0, 0]) + f(y1 * F[1, 0])) + F[2, 0])
+                lb = f(f(f(x1 * F[0, 1]) + f(y1 * F[1, 1])) + F[2, 1])
+                lc = f(f(f(x1 * F[0, 2]) + f(y1 * F[1, 2])) + F[2, 2])
+                num = f(f(f(la * x2) + f(lb * y2)) + lc)
+                den = f(f(la * la) + f(lb * lb))
+                if den == 0:
+                    continue
+                dsqr = f(f(num * num) / den)
+                if float(dsqr) < 3.84 * float(kf2["level_sigma2"][o2]):
+                    best, bi = d, idx2
+            if bi >= 0:
+                m12[idx1] = bi
+                rot = f(kf1["kps"]["angle"][idx1] - kf2["kps"]["angle"][bi])
+                if rot < 0:
+                    rot = f(rot + f(360))
+                v = float(f(rot * f(f(1.0) / f(30))))
+                bn = int(math.floor(abs(v) + 0.5))
+                bins.setdefault(0 if bn == 30 else bn, []).append(idx1)
+    if check_ori:
+        sizes = [len(bins.get(i, [])) for i in range(30)]
+        m1 = m2 = m3 = 0; i1 = i2 = i3 = -1
+        for i, s in enumerate(sizes):
+            if s > m1:
+                m3, m2, m1, i3, i2, i1 = m2, m1, s, i2, i1, i
+            elif s > m2:
+                m3, m2, i3, i2 = m2, s, i2, i
+            elif s > m3:
+                m3, i3 = s, i
+        if m2 < f(0.1) * f(m1):
+            i2 = i3 = -1
+        elif m3 < f(0.1) * f(m1):
+            i3 = -1
+        for i in range(30):
+            if i not in (i1, i2, i3):
+                for idx1 in bins.get(i, []):
+                    m12[idx1] = -1
+    return int((m12 >= 0).sum()), m12
+
+
+@pytest.mark.parametrize("only_stereo,check_ori,seed", [(False, False, 1), (False, True, 2), (True, True, 3)])
+def test_triangulation_vs_python(only_stereo, check_ori, seed):
+    _, (kps, desc) = _features(seed=seed + 10)
+    kf1, kf2, F12, ex, ey = synth.triangulation_case(kps, desc, seed)
+    a = O.search_for_triangulation(kf1, kf2, F12, ex, ey, only_stereo, check_ori)
+    b = _py_triangulation(kf1, kf2, F12, ex, ey, only_stereo, check_ori)
+    assert a[0] == b[0] and np.array_equal(a[1], b[1])
+    assert a[0] > (5 if only_stereo else 30)
+
+
+def test_stereo_match_recovers_disparity():
+    w, h = 480, 200
+    left, right = synth.stereo_pair(w, h, 5)
+    p = O.params(600)
+    kl, dl = O.extract(p, left)
+    kr, dr = O.extract(p, right)
+    sf, isf, _ = synth.scale_tables()
+    ur, depth, sad = O.stereo_match(kl, dl, kr, dr, O.pyramid(p, left), O.pyramid(p, right), sf, isf, bf=40.0, b=0.5)
+    ok = ur >= 0
+    assert ok.sum() > 100
+    disp_true = 2 + 38 * (0.5 + 0.5 * np.sin(np.linspace(0, 3.0, h)))[np.clip(kl["y"][ok].astype(int), 0, h - 1)]
+    err = np.abs((kl["x"][ok] - ur[ok]) - disp_true)
+    assert np.median(err) < 1.0                         # sub-pixel refinement lands on the synthetic disparity
+    assert np.allclose(depth[ok], np.float32(40.0) / (kl["x"][ok] - ur[ok]), rtol=1e-6)
+    assert ((ur < 0) == (depth < 0)).all()
+    # outlier cut: every surviving SAD is below 1.5*1.4*median of the accepted ones (src/Frame.cc:670-681)
+    acc = sad[sad >= 0]
+    med = np.sort(acc)[len(acc) // 2]
+    assert (sad[ok] < np.float32(1.5) * np.float32(1.4) * np.float32(med)).all()
