@@ -120,6 +120,110 @@ int ygzorb_extractor_stage_ms(ygzorb_extractor *ex, float *ms, int n);
 int ygzorb_resize_linear_u8(const uint8_t *src, int sw, int sh, uint8_t *dst, int dw, int dh, int device);
 int ygzorb_gaussian_blur7_u8(const uint8_t *src, int w, int h, uint8_t *dst, int device);
 
+/* ---- ORBmatcher Hamming paths and Frame::ComputeStereoMatches ------------------------------- */
+
+#define YGZORB_TH_HIGH 100   /* ORBmatcher::TH_HIGH, src/ORBmatcher.cc:36 */
+#define YGZORB_TH_LOW 50     /* ORBmatcher::TH_LOW,  src/ORBmatcher.cc:37 */
+
+/* One matcher = one CUDA stream + scratch on `device`.  ORBmatcher objects are stack-local per call
+ * site and used concurrently from the Tracking / LocalMapping / LoopClosing threads (SURVEY.md
+ * §8(b)): create one handle per calling thread; calls on different handles run concurrently.
+ * Pointer placement per call: YGZORB_IN_DEVICE = every input array pointer is device memory,
+ * YGZORB_OUT_DEVICE = every output array pointer is device memory; default host. */
+typedef struct ygzorb_matcher ygzorb_matcher;
+int ygzorb_matcher_create(int device, ygzorb_matcher **out);
+void ygzorb_matcher_destroy(ygzorb_matcher *m);
+int ygzorb_matcher_sync(ygzorb_matcher *m);
+void *ygzorb_matcher_stream(ygzorb_matcher *m);
+long long ygzorb_matcher_launch_count(const ygzorb_matcher *m);
+
+/* ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1507-1523) on n row pairs a[i], b[i] (32 B rows). */
+int ygzorb_descriptor_distance(ygzorb_matcher *m, const uint8_t *a, const uint8_t *b, int n, unsigned flags,
+                               int32_t *dist);
+
+/* Brute-force Hamming kNN (k = 2) + ratio test (BASELINE.json config 5): for every query row the
+ * best / second-best rule of ORBmatcher::SearchByBoW (src/ORBmatcher.cc:193-217) over all nt train
+ * rows in index order.  best_idx/d1/d2 = bestIdxF/bestDist1/bestDist2 (-1/256/256 if nt == 0);
+ * match[q] = best_idx if d1 <= th and (float)d1 < ratio*(float)d2 (:207-209), else -1.  Any output
+ * pointer may be NULL. */
+int ygzorb_hamming_knn2(ygzorb_matcher *m, const uint8_t *query, int nq, const uint8_t *train, int nt, float ratio,
+                        int th, unsigned flags, int32_t *best_idx, int32_t *d1, int32_t *d2, int32_t *match);
+/* Selects the POPC/LOP3 balance of the kNN kernel (0: 8 POPC per pair ... 3: 4 POPC + carry-save adders);
+ * all variants return identical results.  Default 2. */
+int ygzorb_matcher_set_knn_variant(ygzorb_matcher *m, int variant);
+/* Measured integer-pipe peak of the device in 32-bit POPC per second (register-only popc/xor/add
+ * microkernel) — the denominator of the Hamming roofline. */
+int ygzorb_measure_popc_peak(ygzorb_matcher *m, double *popc_per_s);
+
+/* The Frame arrays the searches read (include/Frame.h:248-332) for n_frames frames at fixed strides
+ * (frame f: n_kp[f] records starting at f*kp_stride). */
+typedef struct ygzorb_frame_features {
+    int n_frames, kp_stride;
+    const int32_t *n_kp;          /* Frame::N */
+    const ygzorb_keypoint *kps;   /* mvKeys / mvKeysUn */
+    const uint8_t *desc;          /* mDescriptors, 32 B rows */
+    const float *u_right;         /* mvuRight, or NULL (monocular: all -1) */
+    const uint8_t *claimed;       /* 1 where mvpMapPoints[i] is set with Observations() > 0 on entry, or NULL */
+    float min_x, min_y, max_x, max_y; /* mnMinX, mnMinY, mnMaxX, mnMaxY (src/Frame.cc:502-507) */
+    int nlevels;
+    const float *scale_factors;   /* mvScaleFactors[nlevels], HOST pointer always */
+} ygzorb_frame_features;
+
+/* MapPoints after Frame::isInFrustum (src/Frame.cc:363-422; MapPoint.h:95-102), frame f: n_mp[f]
+ * entries starting at f*mp_stride, in vpMapPoints order. */
+typedef struct ygzorb_mappoint_proj {
+    int mp_stride;
+    const int32_t *n_mp;
+    const float *proj_x, *proj_y, *proj_xr, *view_cos;   /* mTrackProjX/Y/XR, mTrackViewCos */
+    const int32_t *level;                                /* mnTrackScaleLevel */
+    const uint8_t *in_view;                              /* mbTrackInView && !isBad() */
+    const uint8_t *has_obs;                              /* Observations() > 0 */
+    const uint8_t *desc;                                 /* GetDescriptor(), 32 B rows */
+} ygzorb_mappoint_proj;
+
+/* ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th, checkLevel)
+ * (src/ORBmatcher.cc:44-126), batched over frames, reproducing the serial claim order.
+ * kp_to_mp[f*kp_stride + i] = index of the MapPoint left in F.mvpMapPoints[i] by the call, or -1;
+ * mp_best_idx[f*mp_stride + j] = keypoint MapPoint j was assigned to, or -1 (may be NULL);
+ * n_matches[f] = the function's return value. */
+int ygzorb_search_by_projection(ygzorb_matcher *m, const ygzorb_frame_features *frames, const ygzorb_mappoint_proj *mps,
+                                float th, int check_level, float nnratio, unsigned flags, int32_t *kp_to_mp,
+                                int32_t *mp_best_idx, int32_t *n_matches);
+
+/* KeyFrame arrays read by SearchForTriangulation (include/KeyFrame.h:236-271); the DBoW2::FeatureVector
+ * (Thirdparty/DBoW2/DBoW2/FeatureVector.h:23-24, std::map<NodeId, vector<unsigned>>) flattened to CSR:
+ * node_ids ascending, features of node k = node_feats[node_start[k] .. node_start[k+1]). */
+typedef struct ygzorb_keyframe_features {
+    int n, n_nodes, nlevels;
+    const ygzorb_keypoint *kps;    /* mvKeysUn */
+    const uint8_t *desc;
+    const float *u_right;          /* mvuRight (< 0: monocular keypoint) */
+    const uint8_t *has_mappoint;   /* GetMapPoint(i) != NULL */
+    const uint32_t *node_ids;
+    const int32_t *node_start;
+    const uint32_t *node_feats;
+    const float *scale_factors;    /* HOST pointers always */
+    const float *level_sigma2;
+} ygzorb_keyframe_features;
+
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo)
+ * (src/ORBmatcher.cc:597-746).  f12 row-major (f12[3*r+c] = F12(r,c)); (ex, ey) = the epipole of :604-610.
+ * matches12[i] = matched keypoint of KF2 or -1 (vMatches12; the pair list is its non-negative entries
+ * in index order); *n_matches = return value. */
+int ygzorb_search_for_triangulation(ygzorb_matcher *m, const ygzorb_keyframe_features *kf1,
+                                    const ygzorb_keyframe_features *kf2, const float *f12, float ex, float ey,
+                                    int only_stereo, int check_orientation, unsigned flags, int32_t *matches12,
+                                    int32_t *n_matches);
+
+/* Frame::ComputeStereoMatches() (src/Frame.cc:509-682).  The patch search reads the pyramids of the
+ * Left and Right extractors (mpORBextractorLeft/Right->mvImagePyramid, :604-623): frame `frame` of the
+ * last batch of `left` / `right`.  kps/desc: mvKeys / mDescriptors and mvKeysRight / mDescriptorsRight.
+ * Outputs mvuRight[n_left], mvDepth[n_left] (-1 = no match).  mbf, mb as in Frame (bf, bf/fx). */
+int ygzorb_stereo_match(ygzorb_matcher *m, ygzorb_extractor *left, ygzorb_extractor *right, int frame,
+                        const ygzorb_keypoint *kps_left, const uint8_t *desc_left, int n_left,
+                        const ygzorb_keypoint *kps_right, const uint8_t *desc_right, int n_right, float mbf, float mb,
+                        unsigned flags, float *u_right, float *depth);
+
 #ifdef __cplusplus
 }
 #endif

@@ -355,6 +355,28 @@ static int checkStatus(Extractor *ex) {
 
 }  // namespace ygz
 
+namespace ygz {
+
+int extractorLevelView(ygzorb_extractor *h, int frame, int level, LevelView *out) {
+    Extractor *ex = (Extractor *)h;
+    if (!ex || !out) { setError("null argument"); return YGZORB_E_ARG; }
+    if (ex->lastFrames <= 0) { setError("extractor holds no pyramid yet"); return YGZORB_E_STATE; }
+    if (frame < 0 || frame >= ex->lastFrames || level < 0 || level >= ex->G.nlevels) { setError("frame/level out of range"); return YGZORB_E_ARG; }
+    YGZ_CUDA(cudaStreamSynchronize(ex->stream));
+    const LevelGeom &L = ex->G.lv[level];
+    out->ptr = level == 0 ? ex->B.in + (long long)frame * ex->B.inFrameStride : ex->B.pyr + (long long)frame * ex->G.slabBytes + L.off;
+    out->pitch = L.pitch; out->w = L.w; out->h = L.h;
+    return 0;
+}
+int extractorTables(ygzorb_extractor *h, int *nlevels, const float **scale, const float **invScale) {
+    Extractor *ex = (Extractor *)h;
+    if (!ex) { setError("null extractor"); return YGZORB_E_ARG; }
+    *nlevels = ex->params.nlevels; *scale = ex->tables.scale.data(); *invScale = ex->tables.invScale.data();
+    return 0;
+}
+
+}  // namespace ygz
+
 // =================================================================================================
 // C ABI
 using namespace ygz;

@@ -1,0 +1,346 @@
+// matcher.cu — host side of the Hamming matching paths: handle (stream + scratch pool), argument
+// marshalling between host/device buffers, and the C ABI of include/ygzorb.h.  No CPU compute path.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "ygz_match.cuh"
+
+namespace ygz {
+
+static int argFailM(const char *msg) { setError(msg); return YGZORB_E_ARG; }
+
+struct Scratch { void *p = nullptr; size_t bytes = 0; };
+
+struct Matcher {
+    int device = 0, smCount = 148;
+    cudaStream_t stream = nullptr;
+    std::vector<Scratch> pool;
+    long long launches = 0;
+    int knnVariant = 2;
+    int32_t *dStatus = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+// Device scratch slot `slot`, grown on demand (the stream is drained before a buffer is replaced).
+static int scratch(Matcher *m, int slot, size_t bytes, void **out) {
+    if ((int)m->pool.size() <= slot) m->pool.resize(slot + 1);
+    Scratch &s = m->pool[slot];
+    if (s.bytes < bytes || !s.p) {
+        YGZ_CUDA(cudaStreamSynchronize(m->stream));
+        if (s.p) YGZ_CUDA(cudaFree(s.p));
+        s.p = nullptr; s.bytes = 0;
+        const size_t want = std::max<size_t>(bytes + bytes / 4, 256);
+        YGZ_CUDA(cudaMalloc(&s.p, want));
+        s.bytes = want;
+    }
+    *out = s.p;
+    return 0;
+}
+
+// Input array: device pointers are used in place, host arrays are staged into scratch slot `slot`.
+template <class T> static int stageIn(Matcher *m, int slot, const T *src, size_t count, bool inDev, const T **out) {
+    if (!src) { *out = nullptr; return 0; }
+    if (inDev) { *out = src; return 0; }
+    void *p = nullptr;
+    int rc = scratch(m, slot, count * sizeof(T), &p);
+    if (rc) return rc;
+    if (count) YGZ_CUDA(cudaMemcpyAsync(p, src, count * sizeof(T), cudaMemcpyHostToDevice, m->stream));
+    *out = (const T *)p;
+    return 0;
+}
+// Output array: device pointers are written in place, host arrays get a scratch slot + a D2H copy later.
+template <class T> static int stageOut(Matcher *m, int slot, T *dst, size_t count, bool outDev, T **out) {
+    if (dst && outDev) { *out = dst; return 0; }
+    void *p = nullptr;
+    int rc = scratch(m, slot, std::max<size_t>(count, 1) * sizeof(T), &p);
+    if (rc) return rc;
+    *out = (T *)p;
+    return 0;
+}
+template <class T> static int copyOut(Matcher *m, T *dst, const T *dev, size_t count, bool outDev) {
+    if (!dst || outDev || count == 0) return 0;
+    YGZ_CUDA(cudaMemcpyAsync(dst, dev, count * sizeof(T), cudaMemcpyDeviceToHost, m->stream));
+    return 0;
+}
+static int finish(Matcher *m, unsigned flags) {
+    YGZ_CUDA(cudaGetLastError());
+    if (!(flags & YGZORB_NO_SYNC)) YGZ_CUDA(cudaStreamSynchronize(m->stream));
+    return 0;
+}
+
+}  // namespace ygz
+
+using namespace ygz;
+
+extern "C" {
+
+int ygzorb_matcher_create(int device, ygzorb_matcher **out) {
+    if (!out) return argFailM("null argument");
+    YGZ_CUDA(cudaSetDevice(device));
+    Matcher *m = new Matcher();
+    m->device = device;
+    cudaDeviceProp prop;
+    cudaError_t e = cudaGetDeviceProperties(&prop, device);
+    if (e == cudaSuccess) m->smCount = prop.multiProcessorCount;
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&m->dStatus, 64);
+    if (e == cudaSuccess) e = cudaMemset(m->dStatus, 0, 64);
+    if (e == cudaSuccess) e = cudaEventCreate(&m->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&m->ev1);
+    if (e != cudaSuccess) { ygzorb_matcher_destroy((ygzorb_matcher *)m); return cudaFail(e, "matcher_create", __FILE__, __LINE__); }
+    *out = (ygzorb_matcher *)m;
+    return 0;
+}
+
+void ygzorb_matcher_destroy(ygzorb_matcher *h) {
+    Matcher *m = (Matcher *)h;
+    if (!m) return;
+    cudaSetDevice(m->device);
+    if (m->stream) cudaStreamSynchronize(m->stream);
+    for (Scratch &s : m->pool) if (s.p) cudaFree(s.p);
+    if (m->dStatus) cudaFree(m->dStatus);
+    if (m->ev0) cudaEventDestroy(m->ev0);
+    if (m->ev1) cudaEventDestroy(m->ev1);
+    if (m->stream) cudaStreamDestroy(m->stream);
+    delete m;
+}
+
+int ygzorb_matcher_sync(ygzorb_matcher *h) {
+    Matcher *m = (Matcher *)h;
+    if (!m) return argFailM("null matcher");
+    YGZ_CUDA(cudaSetDevice(m->device));
+    YGZ_CUDA(cudaStreamSynchronize(m->stream));
+    return 0;
+}
+void *ygzorb_matcher_stream(ygzorb_matcher *h) { return h ? (void *)((Matcher *)h)->stream : nullptr; }
+long long ygzorb_matcher_launch_count(const ygzorb_matcher *h) { return h ? ((const Matcher *)h)->launches : 0; }
+
+int ygzorb_matcher_set_knn_variant(ygzorb_matcher *h, int variant) {
+    if (!h || variant < 0 || variant > 3) return argFailM("variant must be 0..3");
+    ((Matcher *)h)->knnVariant = variant;
+    return 0;
+}
+
+int ygzorb_measure_popc_peak(ygzorb_matcher *h, double *popcPerS) {
+    Matcher *m = (Matcher *)h;
+    if (!m || !popcPerS) return argFailM("null argument");
+    YGZ_CUDA(cudaSetDevice(m->device));
+    const int blocks = m->smCount * 8, threads = 256, iters = 4096;
+    void *out = nullptr;
+    int rc = scratch(m, 0, (size_t)blocks * threads * 4, &out);
+    if (rc) return rc;
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; rep++) {
+        YGZ_CUDA(cudaEventRecord(m->ev0, m->stream));
+        m->launches += launchPopcPeak((unsigned *)out, blocks, threads, iters, m->stream);
+        YGZ_CUDA(cudaEventRecord(m->ev1, m->stream));
+        YGZ_CUDA(cudaStreamSynchronize(m->stream));
+        float ms = 0;
+        YGZ_CUDA(cudaEventElapsedTime(&ms, m->ev0, m->ev1));
+        if (rep > 0) best = std::min(best, ms);
+    }
+    *popcPerS = (double)blocks * threads * iters * 32.0 / (best * 1e-3);
+    return 0;
+}
+
+int ygzorb_descriptor_distance(ygzorb_matcher *h, const uint8_t *a, const uint8_t *b, int n, unsigned flags, int32_t *dist) {
+    Matcher *m = (Matcher *)h;
+    if (!m || n < 0 || (n > 0 && (!a || !b || !dist))) return argFailM("bad argument");
+    if (n == 0) return 0;
+    YGZ_CUDA(cudaSetDevice(m->device));
+    const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
+    const uint8_t *da, *db; int32_t *dd;
+    int rc;
+    if ((rc = stageIn(m, 0, a, (size_t)n * 32, inDev, &da))) return rc;
+    if ((rc = stageIn(m, 1, b, (size_t)n * 32, inDev, &db))) return rc;
+    if ((rc = stageOut(m, 2, dist, (size_t)n, outDev, &dd))) return rc;
+    m->launches += launchDescriptorDistance(da, db, n, dd, m->stream);
+    if ((rc = copyOut(m, dist, dd, (size_t)n, outDev))) return rc;
+    return finish(m, flags);
+}
+
+int ygzorb_hamming_knn2(ygzorb_matcher *h, const uint8_t *query, int nq, const uint8_t *train, int nt, float ratio,
+                        int th, unsigned flags, int32_t *bestIdx, int32_t *d1, int32_t *d2, int32_t *match) {
+    Matcher *m = (Matcher *)h;
+    if (!m || nq < 0 || nt < 0 || (nq > 0 && !query) || (nt > 0 && !train)) return argFailM("bad argument");
+    if (nq == 0) return 0;
+    YGZ_CUDA(cudaSetDevice(m->device));
+    const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
+    const uint8_t *dq, *dt;
+    int rc;
+    if ((rc = stageIn(m, 0, query, (size_t)nq * 32, inDev, &dq))) return rc;
+    if (nt > 0) { if ((rc = stageIn(m, 1, train, (size_t)nt * 32, inDev, &dt))) return rc; }
+    else { void *p; if ((rc = scratch(m, 1, 256, &p))) return rc; dt = (const uint8_t *)p; }
+    const int splits = knnSplits(nq, nt, m->smCount);
+    void *partial = nullptr;
+    if ((rc = scratch(m, 2, knnPartialBytes(nq, splits), &partial))) return rc;
+    int32_t *oi = nullptr, *o1 = nullptr, *o2 = nullptr, *om = nullptr;
+    if (bestIdx && (rc = stageOut(m, 3, bestIdx, (size_t)nq, outDev, &oi))) return rc;
+    if (d1 && (rc = stageOut(m, 4, d1, (size_t)nq, outDev, &o1))) return rc;
+    if (d2 && (rc = stageOut(m, 5, d2, (size_t)nq, outDev, &o2))) return rc;
+    if (match && (rc = stageOut(m, 6, match, (size_t)nq, outDev, &om))) return rc;
+    m->launches += launchKnn2(dq, nq, dt, nt, ratio, th, splits, partial, m->knnVariant, oi, o1, o2, om, m->stream);
+    if ((rc = copyOut(m, bestIdx, oi, (size_t)nq, outDev))) return rc;
+    if ((rc = copyOut(m, d1, o1, (size_t)nq, outDev))) return rc;
+    if ((rc = copyOut(m, d2, o2, (size_t)nq, outDev))) return rc;
+    if ((rc = copyOut(m, match, om, (size_t)nq, outDev))) return rc;
+    return finish(m, flags);
+}
+
+int ygzorb_search_by_projection(ygzorb_matcher *h, const ygzorb_frame_features *F, const ygzorb_mappoint_proj *P, float th,
+                                int checkLevel, float nnratio, unsigned flags, int32_t *kpToMp, int32_t *mpBestIdx,
+                                int32_t *nMatches) {
+    Matcher *m = (Matcher *)h;
+    if (!m || !F || !P || !kpToMp || !nMatches) return argFailM("null argument");
+    if (F->n_frames < 0 || F->kp_stride < 1 || P->mp_stride < 1) return argFailM("bad sizes");
+    if (F->nlevels < 1 || F->nlevels > kMaxLevels || !F->scale_factors) return argFailM("nlevels must be 1..16 with scale_factors");
+    if (!F->n_kp || !F->kps || !F->desc || !P->n_mp || !P->proj_x || !P->proj_y || !P->view_cos || !P->level || !P->in_view ||
+        !P->has_obs || !P->desc) return argFailM("null array in frame/mappoint view");
+    if (F->u_right && !P->proj_xr) return argFailM("proj_xr is required when u_right is given");
+    if (F->n_frames == 0) return 0;
+    YGZ_CUDA(cudaSetDevice(m->device));
+    const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
+    const size_t nf = F->n_frames, nk = nf * F->kp_stride, nm = nf * P->mp_stride;
+    ProjArgs A;
+    memset(&A, 0, sizeof A);
+    A.nFrames = F->n_frames; A.kpStride = F->kp_stride; A.mpStride = P->mp_stride;
+    int rc;
+    if ((rc = stageIn(m, 0, F->n_kp, nf, inDev, &A.nKp))) return rc;
+    if ((rc = stageIn(m, 1, P->n_mp, nf, inDev, &A.nMp))) return rc;
+    if ((rc = stageIn(m, 2, F->kps, nk, inDev, &A.kps))) return rc;
+    if ((rc = stageIn(m, 3, F->desc, nk * 32, inDev, &A.desc))) return rc;
+    if ((rc = stageIn(m, 4, F->u_right, F->u_right ? nk : 0, inDev, &A.uRight))) return rc;
+    if ((rc = stageIn(m, 5, F->claimed, F->claimed ? nk : 0, inDev, &A.claimed))) return rc;
+    if ((rc = stageIn(m, 6, P->proj_x, nm, inDev, &A.projX))) return rc;
+    if ((rc = stageIn(m, 7, P->proj_y, nm, inDev, &A.projY))) return rc;
+    if ((rc = stageIn(m, 8, P->proj_xr, P->proj_xr ? nm : 0, inDev, &A.projXR))) return rc;
+    if ((rc = stageIn(m, 9, P->view_cos, nm, inDev, &A.viewCos))) return rc;
+    if ((rc = stageIn(m, 10, P->level, nm, inDev, &A.level))) return rc;
+    if ((rc = stageIn(m, 11, P->in_view, nm, inDev, &A.inView))) return rc;
+    if ((rc = stageIn(m, 12, P->has_obs, nm, inDev, &A.hasObs))) return rc;
+    if ((rc = stageIn(m, 13, P->desc, nm * 32, inDev, &A.mpDesc))) return rc;
+    A.minX = F->min_x; A.minY = F->min_y;
+    A.invW = (float)kGridCols / (F->max_x - F->min_x);   // mfGridElementWidthInv, src/Frame.cc:296-297
+    A.invH = (float)kGridRows / (F->max_y - F->min_y);
+    for (int l = 0; l < F->nlevels; l++) A.scale[l] = F->scale_factors[l];
+    A.th = th; A.nnratio = nnratio; A.checkLevel = checkLevel;
+    if ((rc = stageOut(m, 14, kpToMp, nk, outDev, &A.kpToMp))) return rc;
+    if ((rc = stageOut(m, 15, mpBestIdx, nm, outDev, &A.mpBestIdx))) return rc;
+    if ((rc = stageOut(m, 16, nMatches, nf, outDev, &A.nMatches))) return rc;
+    void *p;
+    if ((rc = scratch(m, 17, nk * 4, &p))) return rc;
+    A.claimTime = (int32_t *)p;
+    if ((rc = scratch(m, 18, nk * 4, &p))) return rc;
+    A.gridList = (int32_t *)p;
+    m->launches += launchSearchByProjection(A, F->kp_stride, m->stream);
+    if ((rc = copyOut(m, kpToMp, A.kpToMp, nk, outDev))) return rc;
+    if ((rc = copyOut(m, mpBestIdx, A.mpBestIdx, nm, outDev))) return rc;
+    if ((rc = copyOut(m, nMatches, A.nMatches, nf, outDev))) return rc;
+    return finish(m, flags);
+}
+
+
+static int stageKf(Matcher *m, int slot0, const ygzorb_keyframe_features *K, bool inDev, KfView *V) {
+    int rc;
+    V->n = K->n; V->nNodes = K->n_nodes;
+    if ((rc = stageIn(m, slot0 + 0, K->kps, (size_t)K->n, inDev, &V->kps))) return rc;
+    if ((rc = stageIn(m, slot0 + 1, K->desc, (size_t)K->n * 32, inDev, &V->desc))) return rc;
+    if ((rc = stageIn(m, slot0 + 2, K->u_right, (size_t)K->n, inDev, &V->uRight))) return rc;
+    if ((rc = stageIn(m, slot0 + 3, K->has_mappoint, (size_t)K->n, inDev, &V->hasMP))) return rc;
+    if ((rc = stageIn(m, slot0 + 4, K->node_ids, (size_t)K->n_nodes, inDev, &V->nodeIds))) return rc;
+    if ((rc = stageIn(m, slot0 + 5, K->node_start, (size_t)K->n_nodes + 1, inDev, &V->nodeStart))) return rc;
+    // every keypoint sits in at most one node: node_feats has at most n entries (its exact length is node_start[n_nodes])
+    size_t nFeats = (size_t)K->n;
+    if (!inDev && K->n_nodes > 0) nFeats = (size_t)K->node_start[K->n_nodes];
+    if ((rc = stageIn(m, slot0 + 6, K->node_feats, nFeats, inDev, &V->nodeFeats))) return rc;
+    return 0;
+}
+
+int ygzorb_search_for_triangulation(ygzorb_matcher *h, const ygzorb_keyframe_features *K1, const ygzorb_keyframe_features *K2,
+                                    const float *f12, float ex, float ey, int onlyStereo, int checkOrientation,
+                                    unsigned flags, int32_t *matches12, int32_t *nMatches) {
+    Matcher *m = (Matcher *)h;
+    if (!m || !K1 || !K2 || !f12 || !matches12 || !nMatches) return argFailM("null argument");
+    if (K1->n < 0 || K2->n < 0 || K1->n_nodes < 0 || K2->n_nodes < 0) return argFailM("bad sizes");
+    if (K2->nlevels < 1 || K2->nlevels > kMaxLevels || !K2->scale_factors || !K2->level_sigma2) return argFailM("kf2 scale tables missing");
+    for (const ygzorb_keyframe_features *K : {K1, K2})
+        if (K->n > 0 && (!K->kps || !K->desc || !K->u_right || !K->has_mappoint)) return argFailM("null keyframe array");
+    YGZ_CUDA(cudaSetDevice(m->device));
+    const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
+    if (K1->n == 0) { if (outDev) YGZ_CUDA(cudaMemsetAsync(nMatches, 0, 4, m->stream)); else *nMatches = 0; return finish(m, flags); }
+    TriArgs A;
+    memset(&A, 0, sizeof A);
+    int rc;
+    if ((rc = stageKf(m, 0, K1, inDev, &A.kf1))) return rc;
+    if ((rc = stageKf(m, 7, K2, inDev, &A.kf2))) return rc;
+    for (int l = 0; l < K2->nlevels; l++) { A.scale2[l] = K2->scale_factors[l]; A.sigma2_2[l] = K2->level_sigma2[l]; }
+    for (int i = 0; i < 9; i++) A.F12[i] = f12[i];
+    A.ex = ex; A.ey = ey; A.onlyStereo = onlyStereo; A.checkOrientation = checkOrientation;
+    if ((rc = stageOut(m, 14, matches12, (size_t)K1->n, outDev, &A.matches12))) return rc;
+    if ((rc = stageOut(m, 15, nMatches, 1, outDev, &A.nMatches))) return rc;
+    void *p;
+    if ((rc = scratch(m, 16, (size_t)K1->n * 4, &p))) return rc;
+    A.nodeOf1 = (int32_t *)p;
+    m->launches += launchTriangulation(A, m->stream);
+    if ((rc = copyOut(m, matches12, A.matches12, (size_t)K1->n, outDev))) return rc;
+    if ((rc = copyOut(m, nMatches, A.nMatches, 1, outDev))) return rc;
+    return finish(m, flags);
+}
+
+int ygzorb_stereo_match(ygzorb_matcher *h, ygzorb_extractor *left, ygzorb_extractor *right, int frame,
+                        const ygzorb_keypoint *kpsL, const uint8_t *descL, int nL, const ygzorb_keypoint *kpsR,
+                        const uint8_t *descR, int nR, float mbf, float mb, unsigned flags, float *uRight, float *depth) {
+    Matcher *m = (Matcher *)h;
+    if (!m || !left || !right || nL < 0 || nR < 0 || (nL > 0 && (!kpsL || !descL || !uRight || !depth)) ||
+        (nR > 0 && (!kpsR || !descR))) return argFailM("bad argument");
+    if (nL == 0) return 0;
+    YGZ_CUDA(cudaSetDevice(m->device));
+    const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
+    StereoArgs A;
+    memset(&A, 0, sizeof A);
+    int nlevels = 0, nlevelsR = 0;
+    const float *sc = nullptr, *isc = nullptr, *scR = nullptr, *iscR = nullptr;
+    int rc;
+    if ((rc = extractorTables(left, &nlevels, &sc, &isc))) return rc;
+    if ((rc = extractorTables(right, &nlevelsR, &scR, &iscR))) return rc;
+    if (nlevels != nlevelsR) return argFailM("left and right extractors differ in nlevels");
+    A.nlevels = nlevels;
+    float maxScale = 1.f;
+    for (int l = 0; l < nlevels; l++) {
+        LevelView vl, vr;
+        if ((rc = extractorLevelView(left, frame, l, &vl))) return rc;    // drains the extractor's stream
+        if ((rc = extractorLevelView(right, frame, l, &vr))) return rc;
+        if (vl.w != vr.w || vl.h != vr.h) return argFailM("left and right pyramids differ in size");
+        A.lvL[l] = vl.ptr; A.lvR[l] = vr.ptr; A.pitchL[l] = vl.pitch; A.pitchR[l] = vr.pitch; A.lw[l] = vl.w; A.lh[l] = vl.h;
+        A.scale[l] = sc[l]; A.invScale[l] = isc[l];
+        maxScale = std::max(maxScale, sc[l]);
+    }
+    A.nL = nL; A.nR = nR; A.mbf = mbf; A.mb = mb;
+    if ((rc = stageIn(m, 0, kpsL, (size_t)nL, inDev, &A.kpsL))) return rc;
+    if ((rc = stageIn(m, 1, descL, (size_t)nL * 32, inDev, &A.descL))) return rc;
+    if (nR > 0) {
+        if ((rc = stageIn(m, 2, kpsR, (size_t)nR, inDev, &A.kpsR))) return rc;
+        if ((rc = stageIn(m, 3, descR, (size_t)nR * 32, inDev, &A.descR))) return rc;
+    }
+    if ((rc = stageOut(m, 4, uRight, (size_t)nL, outDev, &A.uRight))) return rc;
+    if ((rc = stageOut(m, 5, depth, (size_t)nL, outDev, &A.depth))) return rc;
+    void *p;
+    if ((rc = scratch(m, 6, (size_t)nL * 4, &p))) return rc;
+    A.bestDist = (int32_t *)p;
+    if ((rc = scratch(m, 7, ((size_t)A.lh[0] + 2) * 4, &p))) return rc;
+    A.rowStart = (int32_t *)p;
+    A.rowListCap = std::max(nR, 1) * ((int)std::ceil(4.f * maxScale) + 4);   // rows floor(y-2s)..ceil(y+2s) per right keypoint
+    if ((rc = scratch(m, 8, (size_t)A.rowListCap * 4, &p))) return rc;
+    A.rowList = (int32_t *)p;
+    if ((rc = scratch(m, 9, (size_t)nL * 4, &p))) return rc;
+    A.sortBuf = (int32_t *)p;
+    A.status = m->dStatus;
+    m->launches += launchStereo(A, m->stream);
+    if ((rc = copyOut(m, uRight, A.uRight, (size_t)nL, outDev))) return rc;
+    if ((rc = copyOut(m, depth, A.depth, (size_t)nL, outDev))) return rc;
+    return finish(m, flags);
+}
+
+}  // extern "C"

@@ -90,4 +90,10 @@ int launchDescribe(const FrameGeom &G, const DevBuffers &B, int nFrames, int cap
 size_t quadtreeSmemBytes(int listCap);
 int configureKernels();  // one-time cudaFuncSetAttribute calls
 
+// Views into an extractor's device-resident pyramid for the matcher (extractor.cu).  Both drain the
+// extractor's stream first, so the pointers are safe to read from another stream.
+struct LevelView { const uint8_t *ptr; int pitch, w, h; };
+int extractorLevelView(ygzorb_extractor *ex, int frame, int level, LevelView *out);
+int extractorTables(ygzorb_extractor *ex, int *nlevels, const float **scale, const float **invScale);
+
 }  // namespace ygz

@@ -1,0 +1,80 @@
+// ygz_match.cuh — declarations shared by match_kernels.cu / matcher.cu.
+#pragma once
+#include "ygz_common.cuh"
+
+namespace ygz {
+
+constexpr int kGridCols = 64, kGridRows = 48;          // FRAME_GRID_COLS/ROWS, include/Frame.h:27-28
+constexpr int kThHigh = 100, kThLow = 50, kHistoLength = 30;  // src/ORBmatcher.cc:36-38
+
+// Device-side view of the arguments of SearchByProjection for a batch of frames (all device pointers).
+struct ProjArgs {
+    int nFrames, kpStride, mpStride;
+    const int32_t *nKp, *nMp;
+    const ygzorb_keypoint *kps;
+    const uint8_t *desc;
+    const float *uRight;       // may be null
+    const uint8_t *claimed;    // may be null
+    float minX, minY, invW, invH;
+    float scale[kMaxLevels];
+    const float *projX, *projY, *projXR, *viewCos;
+    const int32_t *level;
+    const uint8_t *inView, *hasObs, *mpDesc;
+    float th, nnratio;
+    int checkLevel;
+    int32_t *kpToMp, *mpBestIdx, *nMatches;   // outputs (mpBestIdx is also the iteration state)
+    int32_t *claimTime;                       // scratch [nFrames * kpStride]
+    int32_t *gridList;                        // scratch [nFrames * kpStride]
+};
+
+struct KfView {          // one KeyFrame's arrays for SearchForTriangulation (device pointers)
+    int n, nNodes;
+    const ygzorb_keypoint *kps;
+    const uint8_t *desc;
+    const float *uRight;
+    const uint8_t *hasMP;
+    const uint32_t *nodeIds;
+    const int32_t *nodeStart;
+    const uint32_t *nodeFeats;
+};
+struct TriArgs {
+    KfView kf1, kf2;
+    float scale2[kMaxLevels], sigma2_2[kMaxLevels];
+    float F12[9];
+    float ex, ey;
+    int onlyStereo, checkOrientation;
+    int32_t *matches12;     // [kf1.n]
+    int32_t *nodeOf1;       // scratch [kf1.n]: index into kf2's node list, or -1
+    int32_t *nMatches;      // [1]
+    int32_t *hist;          // scratch [kHistoLength]
+};
+
+struct StereoArgs {
+    const ygzorb_keypoint *kpsL, *kpsR;
+    const uint8_t *descL, *descR;
+    int nL, nR, nlevels;
+    const uint8_t *lvL[kMaxLevels], *lvR[kMaxLevels];   // level base pointers (left / right pyramids)
+    int pitchL[kMaxLevels], pitchR[kMaxLevels], lw[kMaxLevels], lh[kMaxLevels];
+    float scale[kMaxLevels], invScale[kMaxLevels];
+    float mbf, mb;
+    float *uRight, *depth;      // outputs [nL]
+    int32_t *bestDist;          // scratch/output [nL]: integer SAD of accepted keypoints, -1 otherwise
+    int32_t *rowStart;          // scratch [rows + 1]
+    int32_t *rowList;           // scratch [rowListCap]
+    int rowListCap;
+    int32_t *sortBuf;           // scratch [nL]
+    int32_t *status;
+};
+
+int launchPopcPeak(unsigned *out, int blocks, int threads, int iters, cudaStream_t s);
+int launchDescriptorDistance(const uint8_t *a, const uint8_t *b, int n, int32_t *dist, cudaStream_t s);
+int knnSplits(int nq, int nt, int smCount);
+size_t knnPartialBytes(int nq, int splits);
+int launchKnn2(const uint8_t *query, int nq, const uint8_t *train, int nt, float ratio, int th, int splits, void *partial,
+               int variant, int32_t *bestIdx, int32_t *d1, int32_t *d2, int32_t *match, cudaStream_t s);
+int launchSearchByProjection(const ProjArgs &A, int maxKp, cudaStream_t s);
+int launchTriangulation(const TriArgs &A, cudaStream_t s);
+int launchStereo(const StereoArgs &A, cudaStream_t s);
+int configureMatchKernels();
+
+}  // namespace ygz

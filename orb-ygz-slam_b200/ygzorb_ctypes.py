@@ -196,3 +196,173 @@ def gaussian_blur7(src, device=0):
     dst = np.zeros_like(src)
     check(lib().ygzorb_gaussian_blur7_u8(_p(src), src.shape[1], src.shape[0], _p(dst), device))
     return dst
+
+
+# ---- matcher --------------------------------------------------------------------------------------
+class FrameFeatures(C.Structure):
+    _fields_ = [("n_frames", C.c_int), ("kp_stride", C.c_int), ("n_kp", C.c_void_p), ("kps", C.c_void_p),
+                ("desc", C.c_void_p), ("u_right", C.c_void_p), ("claimed", C.c_void_p),
+                ("min_x", C.c_float), ("min_y", C.c_float), ("max_x", C.c_float), ("max_y", C.c_float),
+                ("nlevels", C.c_int), ("scale_factors", C.c_void_p)]
+
+
+class MapPointProj(C.Structure):
+    _fields_ = [("mp_stride", C.c_int), ("n_mp", C.c_void_p), ("proj_x", C.c_void_p), ("proj_y", C.c_void_p),
+                ("proj_xr", C.c_void_p), ("view_cos", C.c_void_p), ("level", C.c_void_p), ("in_view", C.c_void_p),
+                ("has_obs", C.c_void_p), ("desc", C.c_void_p)]
+
+
+class KeyFrameFeatures(C.Structure):
+    _fields_ = [("n", C.c_int), ("n_nodes", C.c_int), ("nlevels", C.c_int), ("kps", C.c_void_p), ("desc", C.c_void_p),
+                ("u_right", C.c_void_p), ("has_mappoint", C.c_void_p), ("node_ids", C.c_void_p),
+                ("node_start", C.c_void_p), ("node_feats", C.c_void_p), ("scale_factors", C.c_void_p),
+                ("level_sigma2", C.c_void_p)]
+
+
+def _ptr(a):
+    return a.ctypes.data if a is not None else None
+
+
+class Matcher:
+    """Handle behind ygz::ORBmatcher's Hamming searches and Frame::ComputeStereoMatches."""
+
+    def __init__(self, device=0):
+        h = C.c_void_p()
+        L = lib()
+        L.ygzorb_matcher_destroy.restype = None
+        L.ygzorb_matcher_destroy.argtypes = [C.c_void_p]
+        L.ygzorb_matcher_stream.restype = C.c_void_p
+        L.ygzorb_matcher_stream.argtypes = [C.c_void_p]
+        L.ygzorb_matcher_launch_count.restype = C.c_longlong
+        L.ygzorb_matcher_launch_count.argtypes = [C.c_void_p]
+        L.ygzorb_hamming_knn2.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_int,
+                                          C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ygzorb_descriptor_distance.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_void_p]
+        L.ygzorb_search_by_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_float,
+                                                  C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ygzorb_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float,
+                                                      C.c_float, C.c_int, C.c_int, C.c_uint, C.c_void_p, C.c_void_p]
+        L.ygzorb_stereo_match.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                          C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_uint, C.c_void_p,
+                                          C.c_void_p]
+        L.ygzorb_measure_popc_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        check(L.ygzorb_matcher_create(device, C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().ygzorb_matcher_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def sync(self):
+        check(lib().ygzorb_matcher_sync(self.h))
+
+    def stream(self):
+        return lib().ygzorb_matcher_stream(self.h)
+
+    def launch_count(self):
+        return int(lib().ygzorb_matcher_launch_count(self.h))
+
+    def set_knn_variant(self, v):
+        check(lib().ygzorb_matcher_set_knn_variant(self.h, v))
+
+    def popc_peak(self):
+        v = C.c_double()
+        check(lib().ygzorb_measure_popc_peak(self.h, C.byref(v)))
+        return v.value
+
+    def descriptor_distance(self, a, b):
+        a = np.ascontiguousarray(a, np.uint8).reshape(-1, 32)
+        b = np.ascontiguousarray(b, np.uint8).reshape(-1, 32)
+        out = np.zeros(len(a), np.int32)
+        check(lib().ygzorb_descriptor_distance(self.h, _ptr(a), _ptr(b), len(a), 0, _ptr(out)))
+        return out
+
+    def hamming_knn2(self, query, train, ratio, th):
+        query = np.ascontiguousarray(query, np.uint8).reshape(-1, 32)
+        train = np.ascontiguousarray(train, np.uint8).reshape(-1, 32)
+        nq = len(query)
+        idx, d1, d2, match = (np.zeros(max(nq, 1), np.int32) for _ in range(4))
+        check(lib().ygzorb_hamming_knn2(self.h, _ptr(query), nq, _ptr(train) if len(train) else None, len(train), ratio, th,
+                                        0, _ptr(idx), _ptr(d1), _ptr(d2), _ptr(match)))
+        return idx[:nq], d1[:nq], d2[:nq], match[:nq]
+
+    def hamming_knn2_raw(self, q_ptr, nq, t_ptr, nt, ratio, th, flags, idx_ptr, d1_ptr, d2_ptr, match_ptr):
+        check(lib().ygzorb_hamming_knn2(self.h, q_ptr, nq, t_ptr, nt, ratio, th, flags, idx_ptr, d1_ptr, d2_ptr, match_ptr))
+
+    def search_by_projection(self, frames, mps, bounds, scale_factors, th, check_level, nnratio):
+        """frames: list of (kps, desc, u_right|None, claimed|None); mps: list of dicts (see tests/synth.projection_case).
+        Returns per frame (n_matches, kp_to_mp, mp_best_idx)."""
+        nf = len(frames)
+        ks = max(max(len(f[0]) for f in frames), 1)
+        ms = max(max(len(m["proj_x"]) for m in mps), 1)
+        n_kp = np.array([len(f[0]) for f in frames], np.int32)
+        n_mp = np.array([len(m["proj_x"]) for m in mps], np.int32)
+        kps = np.zeros((nf, ks), KP_DTYPE); desc = np.zeros((nf, ks, 32), np.uint8)
+        has_ur = any(f[2] is not None for f in frames); has_cl = any(f[3] is not None for f in frames)
+        ur = np.full((nf, ks), -1, np.float32) if has_ur else None
+        cl = np.zeros((nf, ks), np.uint8) if has_cl else None
+        for i, f in enumerate(frames):
+            kps[i, :len(f[0])] = f[0]; desc[i, :len(f[0])] = f[1]
+            if f[2] is not None:
+                ur[i, :len(f[0])] = f[2]
+            if f[3] is not None:
+                cl[i, :len(f[0])] = f[3]
+        pa = {k: np.zeros((nf, ms), np.float32) for k in ("proj_x", "proj_y", "proj_xr", "view_cos")}
+        lv = np.zeros((nf, ms), np.int32); iv = np.zeros((nf, ms), np.uint8); ho = np.zeros((nf, ms), np.uint8)
+        md = np.zeros((nf, ms, 32), np.uint8)
+        for i, m in enumerate(mps):
+            k = len(m["proj_x"])
+            for key in pa:
+                pa[key][i, :k] = m[key]
+            lv[i, :k] = m["level"]; iv[i, :k] = m["in_view"]; ho[i, :k] = m["has_obs"]; md[i, :k] = m["desc"]
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        F = FrameFeatures(nf, ks, _ptr(n_kp), _ptr(kps), _ptr(desc), _ptr(ur), _ptr(cl), bounds[0], bounds[1], bounds[2],
+                          bounds[3], len(sf), _ptr(sf))
+        P = MapPointProj(ms, _ptr(n_mp), _ptr(pa["proj_x"]), _ptr(pa["proj_y"]), _ptr(pa["proj_xr"]), _ptr(pa["view_cos"]),
+                         _ptr(lv), _ptr(iv), _ptr(ho), _ptr(md))
+        kp_to_mp = np.zeros((nf, ks), np.int32); best = np.zeros((nf, ms), np.int32); nm = np.zeros(nf, np.int32)
+        check(lib().ygzorb_search_by_projection(self.h, C.byref(F), C.byref(P), th, int(check_level), nnratio, 0,
+                                                _ptr(kp_to_mp), _ptr(best), _ptr(nm)))
+        return [(int(nm[i]), kp_to_mp[i, :n_kp[i]].copy(), best[i, :n_mp[i]].copy()) for i in range(nf)]
+
+    def search_by_projection_raw(self, F, P, th, check_level, nnratio, flags, kp_to_mp_ptr, best_ptr, nm_ptr):
+        check(lib().ygzorb_search_by_projection(self.h, C.byref(F), C.byref(P), th, int(check_level), nnratio, flags,
+                                                kp_to_mp_ptr, best_ptr, nm_ptr))
+
+    def search_for_triangulation(self, kf1, kf2, F12, ex, ey, only_stereo, check_orientation):
+        keep = []
+
+        def view(kf):
+            a = [np.ascontiguousarray(kf["kps"]), np.ascontiguousarray(kf["desc"], np.uint8),
+                 np.ascontiguousarray(kf["u_right"], np.float32), np.ascontiguousarray(kf["has_mp"], np.uint8),
+                 np.ascontiguousarray(kf["node_ids"], np.uint32), np.ascontiguousarray(kf["node_start"], np.int32),
+                 np.ascontiguousarray(kf["node_feats"], np.uint32), np.ascontiguousarray(kf["scale_factors"], np.float32),
+                 np.ascontiguousarray(kf["level_sigma2"], np.float32)]
+            keep.append(a)
+            return KeyFrameFeatures(len(a[0]), len(a[4]), len(a[7]), *[_ptr(x) for x in a])
+        v1, v2 = view(kf1), view(kf2)
+        F = np.ascontiguousarray(F12, np.float32).reshape(9)
+        m12 = np.zeros(max(v1.n, 1), np.int32); nm = np.zeros(1, np.int32)
+        check(lib().ygzorb_search_for_triangulation(self.h, C.byref(v1), C.byref(v2), _ptr(F), float(ex), float(ey),
+                                                    int(only_stereo), int(check_orientation), 0, _ptr(m12), _ptr(nm)))
+        return int(nm[0]), m12[:v1.n].copy()
+
+    def stereo_match(self, ex_left, ex_right, frame, kps_l, desc_l, kps_r, desc_r, bf, b):
+        kps_l, kps_r = np.ascontiguousarray(kps_l), np.ascontiguousarray(kps_r)
+        desc_l, desc_r = np.ascontiguousarray(desc_l, np.uint8), np.ascontiguousarray(desc_r, np.uint8)
+        n = len(kps_l)
+        ur = np.zeros(max(n, 1), np.float32); dp = np.zeros(max(n, 1), np.float32)
+        check(lib().ygzorb_stereo_match(self.h, ex_left.h, ex_right.h, frame, _ptr(kps_l), _ptr(desc_l), n, _ptr(kps_r),
+                                        _ptr(desc_r), len(kps_r), bf, b, 0, _ptr(ur), _ptr(dp)))
+        return ur[:n].copy(), dp[:n].copy()
+
+
+def hamming_knn2(query, train, ratio, th, device=0):
+    m = Matcher(device)
+    try:
+        return m.hamming_knn2(query, train, ratio, th)
+    finally:
+        m.close()

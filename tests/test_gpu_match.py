@@ -1,0 +1,111 @@
+"""GPU parity of the Hamming matching paths (libygzorb_cuda.so through the C ABI) against the CPU
+oracle (oracle/match_oracle.cpp): indices and integer distances bit-exact; stereo uRight / depth
+floats compared bit-exact (same float op order, no contraction)."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+import synth
+from ygz import Y
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def matcher():
+    m = Y.Matcher()
+    yield m
+    m.close()
+
+
+@pytest.fixture(scope="module")
+def feats():
+    img = synth.textured_frame(752, 480, 0)
+    ex = Y.Extractor(1000)
+    kps, desc = ex.extract(img)
+    ex.close()
+    return img, kps, desc
+
+
+def test_descriptor_distance(matcher):
+    rng = np.random.default_rng(0)
+    a = rng.integers(0, 256, size=(1000, 32), dtype=np.uint8)
+    b = rng.integers(0, 256, size=(1000, 32), dtype=np.uint8)
+    b[:10] = a[:10]; b[10] = ~a[10]
+    d = matcher.descriptor_distance(a, b)
+    exp = np.unpackbits(a ^ b, axis=1).sum(axis=1)
+    assert np.array_equal(d, exp) and d[0] == 0 and d[10] == 256
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2, 3])
+@pytest.mark.parametrize("nq,nt,ratio,th", [(1000, 1500, 0.6, 50), (3, 1, 0.9, 100), (513, 512, 0.75, 256), (700, 70001, 0.9, 100),
+                                            (5, 0, 0.6, 50), (2049, 513, 0.6, 50)])
+def test_knn2_vs_oracle(matcher, variant, nq, nt, ratio, th):
+    q, t = synth.knn_case(nq, max(nt, 1), nq + nt)
+    t = t[:nt]
+    if nt > 10:
+        t[7] = t[3]; q[0] = t[3]          # exact duplicate rows: the first index must win, d2 == d1 == 0
+    matcher.set_knn_variant(variant)
+    a = matcher.hamming_knn2(q, t, ratio, th)
+    b = O.hamming_knn2(q, t, ratio, th, threads=8)
+    for x, y, name in zip(a, b, ("idx", "d1", "d2", "match")):
+        assert np.array_equal(x, y), name
+    matcher.set_knn_variant(2)
+
+
+@pytest.mark.parametrize("th,check_level,stereo,seed", [(1.0, False, False, 1), (5.0, False, True, 2), (3.0, True, False, 3),
+                                                         (15.0, False, False, 4)])
+def test_search_by_projection_vs_oracle(matcher, feats, th, check_level, stereo, seed):
+    img, kps, desc = feats
+    sf, _, _ = synth.scale_tables()
+    bounds = (0.0, 0.0, float(img.shape[1]), float(img.shape[0]))
+    frames, mps, exp = [], [], []
+    for k in range(3):                                     # a small batch, ragged MapPoint counts
+        mp, u_right, claimed = synth.projection_case(kps, desc, 3000 - 500 * k, seed * 10 + k, stereo=stereo)
+        frames.append((kps, desc, u_right, claimed)); mps.append(mp)
+        exp.append(O.search_by_projection(kps, desc, u_right, claimed, bounds, sf, mp, th, check_level, 0.8))
+    got = matcher.search_by_projection(frames, mps, bounds, sf, th, check_level, 0.8)
+    for g, e in zip(got, exp):
+        assert g[0] == e[0] and e[0] > 100
+        assert np.array_equal(g[1], e[1]) and np.array_equal(g[2], e[2])
+
+
+def test_search_by_projection_claim_chain(matcher, feats):
+    """Many MapPoints aimed at the same keypoints: long claim chains must resolve like the serial loop."""
+    img, kps, desc = feats
+    sf, _, _ = synth.scale_tables()
+    rng = np.random.default_rng(5)
+    src = np.repeat(rng.integers(0, len(kps), size=40), 25)
+    mp = {"proj_x": kps["x"][src].copy(), "proj_y": kps["y"][src].copy(), "proj_xr": np.zeros(len(src), np.float32),
+          "view_cos": np.full(len(src), 0.95, np.float32), "level": kps["octave"][src].astype(np.int32),
+          "in_view": np.ones(len(src), np.uint8), "has_obs": (rng.uniform(size=len(src)) < 0.8).astype(np.uint8),
+          "desc": synth.flip_bits(desc[src], rng.integers(0, 10, size=len(src)), rng)}
+    bounds = (0.0, 0.0, float(img.shape[1]), float(img.shape[0]))
+    e = O.search_by_projection(kps, desc, None, None, bounds, sf, mp, 8.0, False, 0.9)
+    g = matcher.search_by_projection([(kps, desc, None, None)], [mp], bounds, sf, 8.0, False, 0.9)[0]
+    assert g[0] == e[0] and np.array_equal(g[1], e[1]) and np.array_equal(g[2], e[2])
+
+
+@pytest.mark.parametrize("only_stereo,check_ori,seed", [(False, False, 1), (False, True, 2), (True, True, 3)])
+def test_triangulation_vs_oracle(matcher, feats, only_stereo, check_ori, seed):
+    _, kps, desc = feats
+    kf1, kf2, F12, ex, ey = synth.triangulation_case(kps, desc, seed)
+    e = O.search_for_triangulation(kf1, kf2, F12, ex, ey, only_stereo, check_ori)
+    g = matcher.search_for_triangulation(kf1, kf2, F12, ex, ey, only_stereo, check_ori)
+    assert g[0] == e[0] and np.array_equal(g[1], e[1]) and e[0] > (5 if only_stereo else 20)
+
+
+@pytest.mark.parametrize("w,h,nf,seed", [(640, 240, 800, 5), (1241, 376, 2000, 6)])
+def test_stereo_vs_oracle(matcher, w, h, nf, seed):
+    left, right = synth.stereo_pair(w, h, seed)
+    exl, exr = Y.Extractor(nf), Y.Extractor(nf)
+    kl, dl = exl.extract(left)
+    kr, dr = exr.extract(right)
+    p = O.params(nf)
+    sf, isf = exl.tables()["scale"], exl.tables()["inv_scale"]
+    bf, b = 386.1448, 386.1448 / 718.856                    # Examples/Stereo/KITTI00-02.yaml
+    ur, depth, _ = O.stereo_match(kl, dl, kr, dr, O.pyramid(p, left), O.pyramid(p, right), sf, isf, bf, b)
+    gur, gdepth = matcher.stereo_match(exl, exr, 0, kl, dl, kr, dr, bf, b)
+    assert (ur >= 0).sum() > 100
+    assert gur.tobytes() == ur.tobytes() and gdepth.tobytes() == depth.tobytes()
+    exl.close(); exr.close()
