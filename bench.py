@@ -118,6 +118,51 @@ def run_port_cpu(frames, threads, repeat):
     return {"frames": len(frames) * repeat, "seconds": sec, "frames_per_s": len(frames) * repeat / sec, "threads": threads}
 
 
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+SBP_TH, SBP_RATIO = 1.0, 0.8     # Tracking::SearchLocalPoints: ORBmatcher matcher(0.8); th = 1 (src/Tracking.cc:1662-1674)
+
+
+def make_mappoints(counts, kps, desc, seed):
+    """per frame N_MAPPOINTS synthetic MapPoints = random keypoints of the frame's
+    extraction, projected with +-3 px jitter, viewCos ~ U(0.9, 1), level = source octave, descriptor =
+    source descriptor with 0..40 random bit flips.  Arrays at fixed stride (F, N_MAPPOINTS)."""
+    F, M = len(counts), N_MAPPOINTS
+    rng = np.random.default_rng(seed)
+    mp = {"proj_x": np.zeros((F, M), np.float32), "proj_y": np.zeros((F, M), np.float32),
+          "proj_xr": np.zeros((F, M), np.float32), "view_cos": rng.uniform(0.9, 1.0, (F, M)).astype(np.float32),
+          "level": np.zeros((F, M), np.int32), "in_view": np.ones((F, M), np.uint8), "has_obs": np.ones((F, M), np.uint8),
+          "desc": np.zeros((F, M, 32), np.uint8)}
+    for f in range(F):
+        n = int(counts[f])
+        if n == 0:
+            mp["in_view"][f] = 0
+            continue
+        src = rng.integers(0, n, size=M)
+        mp["proj_x"][f] = kps["x"][f, src] + rng.uniform(-3, 3, M).astype(np.float32)
+        mp["proj_y"][f] = kps["y"][f, src] + rng.uniform(-3, 3, M).astype(np.float32)
+        mp["level"][f] = kps["octave"][f, src]
+        pflip = rng.integers(0, 41, size=M).astype(np.float32) / 256.0
+        bits = rng.random((M, 256), dtype=np.float32) < pflip[:, None]
+        mp["desc"][f] = desc[f, src] ^ np.packbits(bits, axis=1, bitorder="little")
+    mp["n_mp"] = np.full(F, M, np.int32)
+    return mp
+
+
+def cpu_search_by_projection(counts, kps, desc, mp, threads, repeat):
+    """Times the oracle port of ORBmatcher::SearchByProjection (threads over frames) on host cores."""
+    import oracle_lib as O
+    import synth
+    sf, _, _ = synth.scale_tables(SCALE, LEVELS)
+    t0 = time.perf_counter()
+    for _ in range(repeat):
+        _, nm = O.search_by_projection_batch(counts, mp["n_mp"], kps, desc, (0.0, 0.0, float(W), float(H)), sf, mp,
+                                             SBP_TH, False, SBP_RATIO, threads=threads)
+    sec = time.perf_counter() - t0
+    return {"frames": len(counts) * repeat, "seconds": sec, "frames_per_s": len(counts) * repeat / sec,
+            "matches_per_frame": float(nm.mean())}
+
+
 def cpu_extract(frames, threads, repeat):
     if os.path.exists(ref_binary()):
         return "reference", run_reference_cpu(frames, threads, repeat)
@@ -125,40 +170,51 @@ def cpu_extract(frames, threads, repeat):
 
 
 def run_reference_arm(args, rank, world):
-    """--impl reference: the reference's CPU implementation on the box's host cores, rank 0 only."""
+    """--impl reference: the reference's CPU implementation of the step on the box's host cores, rank 0 only:
+    ORBextractor.cc itself (oracle/_ref, compiled from the reference's own source) + the oracle port of
+    SearchByProjection (ORBmatcher.cc cannot be compiled in this image)."""
     if rank != 0:
         return
+    import oracle_lib as O
     threads = os.cpu_count() or 1
     sample = max(2 * threads, 16)
     frames = make_frames(sample, 0)
+    p = O.params(NFEAT, SCALE, LEVELS, INI_TH, MIN_TH)
+    cap = NFEAT + 64
+    counts, kps, desc = O.extract_batch(p, frames, threads=threads, cap=cap)    # untimed set-up: inputs of the search
+    mp = make_mappoints(counts, kps, desc, 1)
     kind, _ = cpu_extract(frames[: max(threads, 4)], threads, 1)   # warm-up of page cache / binary
     for _ in range(max(args.warmup - 1, 0)):
         cpu_extract(frames, threads, 1)
     t0 = time.perf_counter()
-    inner = 0.0
+    t_ext = t_sbp = 0.0
     for _ in range(args.steps):
         _, st = cpu_extract(frames, threads, 1)
-        inner += st["seconds"]
+        t_ext += st["seconds"]
+        sb = cpu_search_by_projection(counts, kps, desc, mp, threads, 1)
+        t_sbp += sb["seconds"]
     wall = time.perf_counter() - t0
-    fps = sample * args.steps / inner
+    fps = sample * args.steps / (t_ext + t_sbp)
     line = {
         "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * inner / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": 1e3 * (t_ext + t_sbp) / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "EuRoC-shape 752x480 mono frame stream, 1000 features (configs[1]); bounded sample of "
-                               "%d frames per step" % sample, "nfeatures": NFEAT, "scale": SCALE, "levels": LEVELS,
-                   "fast": [INI_TH, MIN_TH]},
+        "config": {"workload": "EuRoC-shape 752x480 mono frame stream, 1000 features + SearchByProjection against %d "
+                               "projected MapPoints (configs[1]); bounded sample of %d frames per step" % (N_MAPPOINTS, sample),
+                   "nfeatures": NFEAT, "scale": SCALE, "levels": LEVELS, "fast": [INI_TH, MIN_TH], "mappoints": N_MAPPOINTS},
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind,
-                         "sample": "%d frames x %d steps, %d threads over frames; timed inside the binary "
-                                   "(file I/O excluded), wall %.1f s" % (sample, args.steps, threads, wall)},
+                         "sample": "%d frames x %d steps, %d threads over frames; extraction = reference ORBextractor.cc "
+                                   "(timed inside the binary), SearchByProjection = oracle port; wall %.1f s"
+                                   % (sample, args.steps, threads, wall)},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "hamming": {"mappoints_per_s": sample * args.steps * N_MAPPOINTS / t_sbp, "extract_frames_per_s": sample * args.steps / t_ext},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
 
-
 def run_ours(args, rank, local_rank, world):
     import torch
+    import synth
     import ygzorb_ctypes as Y
     if not torch.cuda.is_available() or Y.device_count() < 1:
         raise RuntimeError("bench.py needs a CUDA device: the product has no CPU path")
@@ -168,28 +224,61 @@ def run_ours(args, rank, local_rank, world):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
-    B = args.batch
+    B, M = args.batch, N_MAPPOINTS
     frames_np = make_frames(B, seed0=100 * rank)
     host_in = torch.empty((B, H, W), dtype=torch.uint8).pin_memory()
     host_in.numpy()[:] = frames_np
     dev_in = host_in.to(dev)
     ex = Y.Extractor(NFEAT, SCALE, LEVELS, INI_TH, MIN_TH, max_batch=B, device=local_rank)
+    mt = Y.Matcher(local_rank)
+    mt.set_stream(ex.stream())          # the search consumes the extraction's device-resident outputs in stream order
     cap = ex.max_keypoints(W, H)
     d_counts = torch.zeros(B, dtype=torch.int32, device=dev)
     d_kps = torch.zeros((B, cap, 7), dtype=torch.float32, device=dev)
     d_desc = torch.zeros((B, cap, 32), dtype=torch.uint8, device=dev)
-    h_counts = torch.zeros(B, dtype=torch.int32).pin_memory()
-    h_kps = torch.zeros((B, cap, 7), dtype=torch.float32).pin_memory()
-    h_desc = torch.zeros((B, cap, 32), dtype=torch.uint8).pin_memory()
+    d_kp2mp = torch.zeros((B, cap), dtype=torch.int32, device=dev)
+    d_best = torch.zeros((B, M), dtype=torch.int32, device=dev)
+    d_nm = torch.zeros(B, dtype=torch.int32, device=dev)
     stream = torch.cuda.ExternalStream(ex.stream(), device=dev)
+    # ---- set-up (untimed): one extraction to derive the synthetic MapPoints of every frame
+    ex.extract_raw(dev_in.data_ptr(), B, W, H, W, W * H, Y.IN_DEVICE | Y.OUT_DEVICE, cap,
+                   d_counts.data_ptr(), d_kps.data_ptr(), d_desc.data_ptr())
+    counts0 = d_counts.cpu().numpy()
+    kps0 = d_kps.cpu().numpy().view(KP_DTYPE).reshape(B, cap)
+    desc0 = d_desc.cpu().numpy()
+    mp = make_mappoints(counts0, kps0, desc0, 1 + rank)
+    mp_keys = ["n_mp", "proj_x", "proj_y", "proj_xr", "view_cos", "level", "in_view", "has_obs", "desc"]
+    h_mp = {k: torch.from_numpy(mp[k]).pin_memory() for k in mp_keys}
+    d_mp = {k: h_mp[k].to(dev) for k in mp_keys}
+    sf, _, _ = synth.scale_tables(SCALE, LEVELS)
+    assert sf.tobytes() == ex.tables()["scale"].tobytes()
+    F = Y.FrameFeatures(B, cap, d_counts.data_ptr(), d_kps.data_ptr(), d_desc.data_ptr(), None, None,
+                        0.0, 0.0, float(W), float(H), LEVELS, sf.ctypes.data)
+    P = Y.MapPointProj(M, *[d_mp[k].data_ptr() for k in mp_keys])
+    # pinned host mirrors of the results for the end-to-end leg
+    h_out = {"counts": torch.zeros(B, dtype=torch.int32).pin_memory(), "kps": torch.zeros((B, cap, 7)).pin_memory(),
+             "desc": torch.zeros((B, cap, 32), dtype=torch.uint8).pin_memory(),
+             "kp2mp": torch.zeros((B, cap), dtype=torch.int32).pin_memory(), "nm": torch.zeros(B, dtype=torch.int32).pin_memory()}
+    d_out = {"counts": d_counts, "kps": d_kps, "desc": d_desc, "kp2mp": d_kp2mp, "nm": d_nm}
+    dflags = Y.IN_DEVICE | Y.OUT_DEVICE | Y.NO_SYNC
+
+    def search():
+        mt.search_by_projection_raw(F, P, SBP_TH, False, SBP_RATIO, dflags, d_kp2mp.data_ptr(), d_best.data_ptr(), d_nm.data_ptr())
 
     def step_device():
-        ex.extract_raw(dev_in.data_ptr(), B, W, H, W, W * H, Y.IN_DEVICE | Y.OUT_DEVICE | Y.NO_SYNC, cap,
-                       d_counts.data_ptr(), d_kps.data_ptr(), d_desc.data_ptr())
+        ex.extract_raw(dev_in.data_ptr(), B, W, H, W, W * H, dflags, cap, d_counts.data_ptr(), d_kps.data_ptr(), d_desc.data_ptr())
+        search()
 
-    def step_host():
-        ex.extract_raw(host_in.data_ptr(), B, W, H, W, W * H, Y.NO_SYNC, cap,
-                       h_counts.data_ptr(), h_kps.data_ptr(), h_desc.data_ptr())
+    def step_host():   # frames and MapPoints come from pinned host memory, every result goes back to the host
+        ex.extract_raw(host_in.data_ptr(), B, W, H, W, W * H, Y.OUT_DEVICE | Y.NO_SYNC, cap,
+                       d_counts.data_ptr(), d_kps.data_ptr(), d_desc.data_ptr())
+        with torch.cuda.stream(stream):
+            for k in mp_keys:
+                d_mp[k].copy_(h_mp[k], non_blocking=True)
+        search()
+        with torch.cuda.stream(stream):
+            for k in h_out:
+                h_out[k].copy_(d_out[k], non_blocking=True)
 
     def barrier():
         if dist is not None:
@@ -200,7 +289,7 @@ def run_ours(args, rank, local_rank, world):
     def timed(step, steps):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        l0 = ex.launch_count()
+        l0 = ex.launch_count() + mt.launch_count()
         e0.record(stream)
         for _ in range(steps):
             step()
@@ -212,7 +301,7 @@ def run_ours(args, rank, local_rank, world):
             t = torch.tensor([ms], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
-        return ms, ex.launch_count() - l0
+        return ms, ex.launch_count() + mt.launch_count() - l0
 
     for _ in range(args.warmup):
         step_device()
@@ -222,70 +311,131 @@ def run_ours(args, rank, local_rank, world):
     ms, launches = timed(step_device, args.steps)
     clocks = sampler.stop()
     n_kp = int(d_counts.sum().item())
-    # end to end through the C ABI with host buffers (H2D of the frames + D2H of the results every step)
+    n_match = int(d_nm.sum().item())
     for _ in range(max(args.warmup // 2, 1)):
         step_host()
     ex.sync()
     ms_e2e, _ = timed(step_host, args.steps)
-    assert int(h_counts.sum().item()) == n_kp, "host and device paths disagree"
-    # per-stage device times (CUDA events between the stages, on the extractor's stream)
+    assert int(h_out["counts"].sum().item()) == n_kp and int(h_out["nm"].sum().item()) == n_match, "host and device paths disagree"
+    # per-stage device times: CUDA events between the extractor's stages + around the search, on the shared stream
     ex.set_profiling(True)
     acc = np.zeros(8)
     reps = 3
     for _ in range(reps):
-        step_device()
+        ex.extract_raw(dev_in.data_ptr(), B, W, H, W, W * H, dflags, cap, d_counts.data_ptr(), d_kps.data_ptr(), d_desc.data_ptr())
         ex.sync()
         acc += ex.stage_ms()
     ex.set_profiling(False)
     stage_ms = {STAGE_NAMES[i]: float(acc[i] / reps) for i in range(7)}
+    ms_sbp, _ = timed(search, args.steps)
+    stage_ms["search_by_projection"] = ms_sbp / args.steps
+    def shutdown():
+        mt.set_stream(None)
+        mt.close()
+        ex.close()
+        if dist is not None:
+            dist.destroy_process_group()
+
     if rank != 0:
+        shutdown()
         return
+    line = build_line(args, world, B, cap, ms, ms_e2e, launches, clocks, stage_ms, n_kp, n_match, h_mp, mp_keys)
+    if world == 1 and not args.no_cpu:
+        line["hamming"].update(knn_probe(Y, mt, torch))
+        line["cpu_baseline"] = cpu_baseline_leg(frames_np, counts0, kps0, desc0, mp)
+    print(json.dumps(line), flush=True)
+    shutdown()
+
+
+def build_line(args, world, B, cap, ms, ms_e2e, launches, clocks, stage_ms, n_kp, n_match, h_mp, mp_keys):
     hbm_peak, peak_src = peaks()
+    M = N_MAPPOINTS
     fps = world * B * args.steps / (ms * 1e-3)
     fps_e2e = world * B * args.steps / (ms_e2e * 1e-3)
-    # dominant kernel = the slowest stage; its algorithmic bytes per launch from SURVEY.md §8(d)
+    # dominant kernel = the slowest extraction stage; algorithmic bytes per launch from SURVEY.md §8(d)
     kern_stages = {"pyramid": "pyramid", "fast": "fast", "blur": "blur", "quadtree": "quadtree_orient_desc",
                    "orient_desc": "quadtree_orient_desc"}
     dom = max(kern_stages, key=lambda k: stage_ms[k])
     launches_per_stage = {"pyramid": LEVELS - 1}.get(dom, 1)
     dom_bytes = STAGE_BYTES[kern_stages[dom]] * B
     achieved = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+    staged = STAGED_TOTAL * B * args.steps / (ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_" + dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
-                "launches_in_stage": launches_per_stage,
-                "algorithmic_bytes_per_launch": dom_bytes / launches_per_stage,
-                "pipeline_staged_GBps": STAGED_TOTAL * B * args.steps / (ms * 1e-3) / 1e9,
-                "pipeline_frac": STAGED_TOTAL * B * args.steps / (ms * 1e-3) / 1e9 / hbm_peak}
-    line = {
+                "launches_in_stage": launches_per_stage, "algorithmic_bytes_per_launch": dom_bytes / launches_per_stage,
+                "pipeline_staged_GBps": staged, "pipeline_frac": staged / hbm_peak}
+    mp_bytes = sum(int(h_mp[k].numel() * h_mp[k].element_size()) for k in mp_keys)
+    return {
         "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "EuRoC-shape 752x480 mono frame stream, 1000 features (configs[1]); %d frames per step "
-                               "per GPU" % B, "nfeatures": NFEAT, "scale": SCALE, "levels": LEVELS, "fast": [INI_TH, MIN_TH],
-                   "batch": B, "l2": "inputs larger than L2 (%.0f MB of frames + %.0f MB of pyramid/blur workspace per step)"
-                                    % (B * W * H / 1e6, B * 2.0)},
+        "config": {"workload": "EuRoC-shape 752x480 mono frame stream, 1000 features + SearchByProjection against %d projected "
+                               "MapPoints per frame (configs[1]); %d frames per step per GPU" % (M, B),
+                   "nfeatures": NFEAT, "scale": SCALE, "levels": LEVELS, "fast": [INI_TH, MIN_TH], "mappoints": M, "batch": B,
+                   "sbp": {"th": SBP_TH, "nnratio": SBP_RATIO},
+                   "l2": "inputs larger than L2 (%.0f MB of frames + %.0f MB of pyramid/blur workspace per step)"
+                         % (B * W * H / 1e6, B * 2.0)},
         "clocks": clocks,
-        "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": B * W * H,
-                "d2h_bytes_per_step": B * (4 + cap * 60), "ms_per_step": ms_e2e / args.steps},
+        "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": B * W * H + mp_bytes,
+                "d2h_bytes_per_step": B * (4 + cap * 60 + cap * 4 + 4), "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches,
         "roofline": roofline,
         "stage_ms_per_step": stage_ms,
         "keypoints_per_frame": n_kp / B,
+        "hamming": {"mappoints_per_s": world * B * M / (stage_ms["search_by_projection"] * 1e-3),
+                    "mappoint_matches_per_frame": n_match / B, "sbp_ms_per_step": stage_ms["search_by_projection"]},
     }
-    if world == 1 and not args.no_cpu:
-        threads = os.cpu_count() or 1
-        sample = frames_np[: max(2 * threads, 16)]
-        kind, st1 = cpu_extract(sample, threads, 1)
-        repeat = int(max(1, min(50, 12.0 / max(st1["seconds"], 1e-3))))
-        kind, st = cpu_extract(sample, threads, repeat)
-        line["cpu_baseline"] = {"value": st["frames_per_s"], "unit": "frames/s", "cores": threads, "kind": kind,
-                                "sample": "%d frames x %d repeats of the same workload, threads over frames (%.1f s)"
-                                          % (len(sample), repeat, st["seconds"])}
-        kind1, s1 = cpu_extract(sample[:8], 1, 1)
-        line["cpu_baseline"]["single_thread_frames_per_s"] = s1["frames_per_s"]
-    print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
+
+
+def knn_probe(Y, mt, torch):
+    """Bounded sample of BASELINE.json config 5 (brute-force kNN-2 + ratio): 32768 queries x 1M train rows on one GPU,
+    against the measured POPC peak (8 POPC32 per 256-bit pair)."""
+    import synth
+    nq, nt = 32768, 1 << 20
+    q, t = synth.knn_case(nq, nt, 1)
+    dq, dt = torch.from_numpy(q).cuda(), torch.from_numpy(t).cuda()
+    out = [torch.zeros(nq, dtype=torch.int32, device="cuda") for _ in range(4)]
+    mt.sync()
+    peak = mt.popc_peak()
+    stream = torch.cuda.ExternalStream(mt.stream())
+    flags = Y.IN_DEVICE | Y.OUT_DEVICE | Y.NO_SYNC
+    for _ in range(2):
+        mt.hamming_knn2_raw(dq.data_ptr(), nq, dt.data_ptr(), nt, 0.6, 50, flags, *[o.data_ptr() for o in out])
+    mt.sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    reps = 3
+    for _ in range(reps):
+        mt.hamming_knn2_raw(dq.data_ptr(), nq, dt.data_ptr(), nt, 0.6, 50, flags, *[o.data_ptr() for o in out])
+    e1.record(stream)
+    mt.sync()
+    ms = e0.elapsed_time(e1) / reps
+    pairs = nq * nt / (ms * 1e-3)
+    return {"knn2": {"workload": "%d x %d 256-bit rows, k=2 + ratio 0.6 (bounded sample of configs[4])" % (nq, nt),
+                     "pairs_per_s": pairs, "ms": ms, "popc_peak_per_s": peak, "bound": "int-pipe (POPC)",
+                     "frac_of_popc_peak": pairs * 8 / peak, "matches": int((out[3] >= 0).sum().item())}}
+
+
+def cpu_baseline_leg(frames_np, counts, kps, desc, mp):
+    """The reference's CPU path on the box's host cores, bounded sample of the same workload."""
+    threads = os.cpu_count() or 1
+    n = max(2 * threads, 16)
+    sample = frames_np[:n]
+    kind, st1 = cpu_extract(sample, threads, 1)
+    repeat = int(max(1, min(200, 12.0 / max(st1["seconds"], 1e-3))))
+    kind, st = cpu_extract(sample, threads, repeat)
+    sub = {k: np.ascontiguousarray(v[:n]) for k, v in mp.items()}
+    sb1 = cpu_search_by_projection(counts[:n].copy(), np.ascontiguousarray(kps[:n]), np.ascontiguousarray(desc[:n]), sub, threads, 1)
+    rep2 = int(max(1, min(200, 3.0 / max(sb1["seconds"], 1e-4))))
+    sb = cpu_search_by_projection(counts[:n].copy(), np.ascontiguousarray(kps[:n]), np.ascontiguousarray(desc[:n]), sub, threads, rep2)
+    fps = 1.0 / (1.0 / st["frames_per_s"] + 1.0 / sb["frames_per_s"])
+    _, s1 = cpu_extract(sample[:8], 1, 1)
+    return {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind,
+            "sample": "%d frames: extraction x %d repeats = reference ORBextractor.cc (%.1f s, %.1f frames/s), SearchByProjection "
+                      "x %d repeats = oracle port (%.1f s, %.0f frames/s); threads over frames"
+                      % (n, repeat, st["seconds"], st["frames_per_s"], rep2, sb["seconds"], sb["frames_per_s"]),
+            "extract_frames_per_s": st["frames_per_s"], "sbp_mappoints_per_s": sb["frames_per_s"] * N_MAPPOINTS,
+            "single_thread_extract_frames_per_s": s1["frames_per_s"]}
 
 
 def main():
@@ -295,7 +445,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=512)
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline and kNN legs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

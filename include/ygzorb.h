@@ -135,6 +135,9 @@ int ygzorb_matcher_create(int device, ygzorb_matcher **out);
 void ygzorb_matcher_destroy(ygzorb_matcher *m);
 int ygzorb_matcher_sync(ygzorb_matcher *m);
 void *ygzorb_matcher_stream(ygzorb_matcher *m);
+/* Run this matcher's work on another cudaStream_t of the same device (e.g. ygzorb_extractor_stream(), so
+ * that a search consumes an extraction's device-resident outputs in stream order); NULL = its own stream. */
+int ygzorb_matcher_set_stream(ygzorb_matcher *m, void *stream);
 long long ygzorb_matcher_launch_count(const ygzorb_matcher *m);
 
 /* ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1507-1523) on n row pairs a[i], b[i] (32 B rows). */

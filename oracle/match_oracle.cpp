@@ -357,3 +357,22 @@ YGZO_API void ygzo_stereo_match(const void *kpsLV, const uint8_t *descL, int nL,
         depthOut[vDistIdx[i].second] = -1;
     }
 }
+
+// Batch of frames at fixed strides (same layout as ygzorb_search_by_projection), threads over frames:
+// the timed CPU port of bench.py's SearchByProjection leg.
+YGZO_API void ygzo_search_by_projection_batch(int nFrames, int kpStride, int mpStride, const int32_t *nKp, const int32_t *nMp,
+                                              const void *kps, const uint8_t *desc, float minX, float minY, float invW,
+                                              float invH, const float *scaleFactors, const float *projX, const float *projY,
+                                              const float *projXR, const float *viewCos, const int32_t *level,
+                                              const uint8_t *inView, const uint8_t *hasObs, const uint8_t *mpDesc, float th,
+                                              int checkLevel, float nnratio, int threads, int32_t *kpToMp, int32_t *nMatches) {
+    parallelFor(nFrames, threads, 1, [&](long b, long e) {
+        for (long f = b; f < e; f++) {
+            const size_t ko = (size_t)f * kpStride, mo = (size_t)f * mpStride;
+            nMatches[f] = ygzo_search_by_projection((const char *)kps + ko * 28, desc + ko * 32, nullptr, nullptr, nKp[f], minX, minY,
+                                                    invW, invH, scaleFactors, projX + mo, projY + mo, projXR + mo, viewCos + mo,
+                                                    level + mo, inView + mo, hasObs + mo, mpDesc + mo * 32, nMp[f], th, checkLevel,
+                                                    nnratio, kpToMp + ko, nullptr);
+        }
+    });
+}

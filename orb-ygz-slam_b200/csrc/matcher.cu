@@ -15,7 +15,7 @@ struct Scratch { void *p = nullptr; size_t bytes = 0; };
 
 struct Matcher {
     int device = 0, smCount = 148;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, ownStream = nullptr;
     std::vector<Scratch> pool;
     long long launches = 0;
     int knnVariant = 2;
@@ -84,7 +84,8 @@ int ygzorb_matcher_create(int device, ygzorb_matcher **out) {
     cudaDeviceProp prop;
     cudaError_t e = cudaGetDeviceProperties(&prop, device);
     if (e == cudaSuccess) m->smCount = prop.multiProcessorCount;
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m->ownStream, cudaStreamNonBlocking);
+    m->stream = m->ownStream;
     if (e == cudaSuccess) e = cudaMalloc((void **)&m->dStatus, 64);
     if (e == cudaSuccess) e = cudaMemset(m->dStatus, 0, 64);
     if (e == cudaSuccess) e = cudaEventCreate(&m->ev0);
@@ -98,12 +99,14 @@ void ygzorb_matcher_destroy(ygzorb_matcher *h) {
     Matcher *m = (Matcher *)h;
     if (!m) return;
     cudaSetDevice(m->device);
-    if (m->stream) cudaStreamSynchronize(m->stream);
+    // a borrowed stream (ygzorb_matcher_set_stream) may already be gone: drain the device instead of the stream
+    if (m->stream == m->ownStream) { if (m->ownStream) cudaStreamSynchronize(m->ownStream); }
+    else cudaDeviceSynchronize();
     for (Scratch &s : m->pool) if (s.p) cudaFree(s.p);
     if (m->dStatus) cudaFree(m->dStatus);
     if (m->ev0) cudaEventDestroy(m->ev0);
     if (m->ev1) cudaEventDestroy(m->ev1);
-    if (m->stream) cudaStreamDestroy(m->stream);
+    if (m->ownStream) cudaStreamDestroy(m->ownStream);
     delete m;
 }
 
@@ -116,6 +119,15 @@ int ygzorb_matcher_sync(ygzorb_matcher *h) {
 }
 void *ygzorb_matcher_stream(ygzorb_matcher *h) { return h ? (void *)((Matcher *)h)->stream : nullptr; }
 long long ygzorb_matcher_launch_count(const ygzorb_matcher *h) { return h ? ((const Matcher *)h)->launches : 0; }
+
+int ygzorb_matcher_set_stream(ygzorb_matcher *h, void *stream) {
+    Matcher *m = (Matcher *)h;
+    if (!m) return argFailM("null matcher");
+    YGZ_CUDA(cudaSetDevice(m->device));
+    YGZ_CUDA(cudaStreamSynchronize(m->stream));
+    m->stream = stream ? (cudaStream_t)stream : m->ownStream;
+    return 0;
+}
 
 int ygzorb_matcher_set_knn_variant(ygzorb_matcher *h, int variant) {
     if (!h || variant < 0 || variant > 3) return argFailM("variant must be 0..3");

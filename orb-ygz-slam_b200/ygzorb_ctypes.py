@@ -265,6 +265,11 @@ class Matcher:
     def launch_count(self):
         return int(lib().ygzorb_matcher_launch_count(self.h))
 
+    def set_stream(self, stream):
+        L = lib()
+        L.ygzorb_matcher_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        check(L.ygzorb_matcher_set_stream(self.h, stream))
+
     def set_knn_variant(self, v):
         check(lib().ygzorb_matcher_set_knn_variant(self.h, v))
 

@@ -259,3 +259,19 @@ def stereo_match(kps_l, desc_l, kps_r, desc_r, pyr_l, pyr_r, scale_factors, inv_
     lib().ygzo_stereo_match(_p(kps_l), _p(desc_l), n, _p(kps_r), _p(desc_r), len(kps_r), _p(pl), _p(pr), _p(off), _p(lw),
                             _p(lh), _p(sf), _p(isf), C.c_float(bf), C.c_float(b), _p(ur), _p(dp), _p(bd))
     return ur[:n].copy(), dp[:n].copy(), bd[:n].copy()
+
+
+def search_by_projection_batch(n_kp, n_mp, kps, desc, bounds, scale_factors, mp, th, check_level, nnratio, threads=1):
+    """Arrays at fixed strides: kps (F, ks) KP_DTYPE, desc (F, ks, 32), mp[...] (F, ms[,32]).  Returns (kp_to_mp, n_matches)."""
+    F, ks = kps.shape
+    ms = mp["proj_x"].shape[1]
+    inv_w, inv_h = grid_inv(*bounds)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    kp_to_mp = np.zeros((F, ks), np.int32)
+    nm = np.zeros(F, np.int32)
+    lib().ygzo_search_by_projection_batch(
+        F, ks, ms, _p(n_kp), _p(n_mp), _p(kps), _p(desc), C.c_float(bounds[0]), C.c_float(bounds[1]), C.c_float(inv_w),
+        C.c_float(inv_h), _p(sf), _p(mp["proj_x"]), _p(mp["proj_y"]), _p(mp["proj_xr"]), _p(mp["view_cos"]), _p(mp["level"]),
+        _p(mp["in_view"]), _p(mp["has_obs"]), _p(mp["desc"]), C.c_float(th), int(check_level), C.c_float(nnratio), threads,
+        _p(kp_to_mp), _p(nm))
+    return kp_to_mp, nm
