@@ -1,0 +1,37 @@
+// FrameLite.h — test double of the members of ygz::Frame (include/Frame.h:248-332) that the drop-in
+// classes read or write.  In an integration the reference's own Frame.h is used instead (the member
+// names below are the reference's).
+#ifndef YGZ_HOST_FRAMELITE_H_
+#define YGZ_HOST_FRAMELITE_H_
+#include <vector>
+
+#include "cvcompat.h"
+
+namespace ygz {
+class ORBextractor;
+struct MapPointLite {                       // include/MapPoint.h:95-102 + the calls SearchByProjection makes
+    float mTrackProjX = 0, mTrackProjY = 0, mTrackProjXR = 0, mTrackViewCos = 1;
+    int mnTrackScaleLevel = 0;
+    bool mbTrackInView = true, mbBad = false;
+    int nObs = 1;
+    cv::Mat mDescriptor;
+    bool isBad() const { return mbBad; }
+    int Observations() const { return nObs; }
+    cv::Mat GetDescriptor() const { return mDescriptor.clone(); }
+};
+class Frame {
+public:
+    std::vector<cv::Mat> mvImagePyramid;
+    cv::Mat mImRight;
+    int N = 0;
+    std::vector<cv::KeyPoint> mvKeys, mvKeysRight;
+    cv::Mat mDescriptors, mDescriptorsRight;
+    std::vector<float> mvuRight, mvDepth;
+    std::vector<MapPointLite *> mvpMapPoints;
+    std::vector<float> mvScaleFactors, mvInvScaleFactors;
+    float mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0;
+    float mbf = 0, mb = 0;
+    ORBextractor *mpORBextractorLeft = nullptr, *mpORBextractorRight = nullptr;
+};
+}  // namespace ygz
+#endif

@@ -1,0 +1,58 @@
+"""The drop-in C++ classes (orb-ygz-slam_b200/host: ygz::ORBextractor, ygz::ORBmatcher) driven the way
+the reference's callers drive them (host_demo.cc), compared with the oracle."""
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+import synth
+from ygz import Y, PKG
+
+pytestmark = pytest.mark.gpu
+DEMO = os.path.join(PKG, "host", "host_demo")
+
+
+def test_host_classes_end_to_end():
+    if not os.path.exists(DEMO):
+        subprocess.run(["make", "-C", os.path.join(PKG, "host")], check=True)
+    w, h, nf, n_mp = 752, 480, 1000, 3000
+    left, right = synth.stereo_pair(w, h, 11)
+    p = O.params(nf)
+    kl, dl = O.extract(p, left)
+    kr, dr = O.extract(p, right)
+    mp, _, _ = synth.projection_case(kl, dl, n_mp, 3)
+    mp["in_view"][:] = 1; mp["has_obs"][:] = 1
+    with tempfile.TemporaryDirectory() as td:
+        fin, fout = os.path.join(td, "in.bin"), os.path.join(td, "out.bin")
+        with open(fin, "wb") as f:
+            np.array([w, h, nf, n_mp], np.int32).tofile(f)
+            left.tofile(f); right.tofile(f)
+            rec = np.zeros(n_mp, np.dtype([("v", "<f4", 3), ("lvl", "<i4"), ("d", "u1", 32)]))
+            rec["v"][:, 0] = mp["proj_x"]; rec["v"][:, 1] = mp["proj_y"]; rec["v"][:, 2] = mp["view_cos"]
+            rec["lvl"] = mp["level"]; rec["d"] = mp["desc"]
+            rec.tofile(f)
+        res = subprocess.run([DEMO, fin, fout], capture_output=True, text=True)
+        assert res.returncode == 0, res.stdout + res.stderr
+        buf = open(fout, "rb").read()
+    off = 0
+
+    def take(dtype, n):
+        nonlocal off
+        a = np.frombuffer(buf, dtype, n, off)
+        off += a.nbytes
+        return a
+    nL = int(take("<i4", 1)[0]); gkl = take(Y.KP_DTYPE, nL); gdl = take(np.uint8, nL * 32).reshape(nL, 32)
+    nR = int(take("<i4", 1)[0]); gkr = take(Y.KP_DTYPE, nR); gdr = take(np.uint8, nR * 32).reshape(nR, 32)
+    gur = take("<f4", nL); gdepth = take("<f4", nL)
+    gnm = int(take("<i4", 1)[0]); gassign = take("<i4", nL)
+    assert gkl.tobytes() == kl.tobytes() and np.array_equal(gdl, dl)
+    assert gkr.tobytes() == kr.tobytes() and np.array_equal(gdr, dr)
+    sf, isf, _ = synth.scale_tables()
+    bf = np.float32(386.1448)
+    ur, depth, _ = O.stereo_match(kl, dl, kr, dr, O.pyramid(p, left), O.pyramid(p, right), sf, isf, float(bf), float(bf / np.float32(718.856)))
+    assert gur.tobytes() == ur.tobytes() and gdepth.tobytes() == depth.tobytes() and (ur >= 0).sum() > 100
+    nm, kp_to_mp, _ = O.search_by_projection(kl, dl, None, None, (0.0, 0.0, float(w), float(h)), sf, mp, 1.0, False, 0.8)
+    assert gnm == nm and np.array_equal(gassign, kp_to_mp) and nm > 300
