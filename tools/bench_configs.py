@@ -1,0 +1,176 @@
+"""Secondary benchmarks for the other BASELINE.json configs (bench.py covers configs[1]):
+  --config 0 : one 640x480 frame, 1000 features — single-frame latency through the C ABI (host in/out)
+  --config 2 : KITTI-shape 1241x376 stereo pair, 2000 features/image + ComputeStereoMatches (host in/out)
+  --config 3 : batched extraction of N_FRAMES 1280x720 frames, 2000 features, frame-sharded over the ranks
+  --config 4 : brute-force kNN-2 + ratio, NQ x NT 256-bit rows, query-sharded over the ranks
+Run under torchrun for > 1 GPU.  One JSON line per run on rank 0; times are CUDA-event device times, max over ranks
+(configs 0/2: host wall clock around synchronous calls, since the host round trip is the point)."""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "orb-ygz-slam_b200"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+import sharding  # noqa: E402
+import synth  # noqa: E402
+import ygzorb_ctypes as Y  # noqa: E402
+
+
+def setup():
+    rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    return rank, local, world, dev
+
+
+def single_frame(args, rank, local, world, dev):
+    img = synth.textured_frame(640, 480, 7)
+    ex = Y.Extractor(1000, device=local)
+    pinned = torch.from_numpy(img).pin_memory()
+    cap = ex.max_keypoints(640, 480)
+    counts = torch.zeros(1, dtype=torch.int32).pin_memory(); kps = torch.zeros((cap, 7)).pin_memory()
+    desc = torch.zeros((cap, 32), dtype=torch.uint8).pin_memory()
+    def once():
+        ex.extract_raw(pinned.data_ptr(), 1, 640, 480, 640, 640 * 480, 0, cap, counts.data_ptr(), kps.data_ptr(), desc.data_ptr())
+    for _ in range(20):
+        once()
+    t0 = time.perf_counter()
+    for _ in range(args.reps):
+        once()
+    dt = (time.perf_counter() - t0) / args.reps
+    return {"config": "one 640x480 frame, 1000 features, host in/out, synchronous call", "latency_ms": dt * 1e3,
+            "frames_per_s": 1 / dt, "keypoints": int(counts[0]), "launches_per_frame": 11}
+
+
+def stereo(args, rank, local, world, dev):
+    w, h, nf = 1241, 376, 2000
+    left, right = synth.stereo_pair(w, h, 6)
+    exl, exr, mt = Y.Extractor(nf, device=local), Y.Extractor(nf, device=local), Y.Matcher(local)
+    bf, b = 386.1448, 386.1448 / 718.856
+    def once():
+        kl, dl = exl.extract(left); kr, dr = exr.extract(right)
+        return mt.stereo_match(exl, exr, 0, kl, dl, kr, dr, bf, b), len(kl), len(kr)
+    for _ in range(5):
+        once()
+    t0 = time.perf_counter()
+    for _ in range(args.reps):
+        (ur, dp), nl, nr = once()
+    dt = (time.perf_counter() - t0) / args.reps
+    return {"config": "1241x376 stereo pair, 2000 features/image + ComputeStereoMatches, host in/out (numpy binding)",
+            "latency_ms": dt * 1e3, "pairs_per_s": 1 / dt, "left_kp": nl, "right_kp": nr, "stereo_matches": int((ur >= 0).sum())}
+
+
+def batched(args, rank, local, world, dev):
+    w, h, nf, n_total, chunk = 1280, 720, 2000, args.frames, args.chunk
+    b, e = sharding.shard_range(n_total, rank, world)
+    n = e - b
+    base = synth.frame_batch(w, h, min(chunk, max(n, 1)), seed0=200 + rank, distinct=8)
+    d_in = torch.from_numpy(base).to(dev)                     # the shard is streamed chunk by chunk from HBM
+    ex = Y.Extractor(nf, max_batch=chunk, device=local)
+    cap = ex.max_keypoints(w, h)
+    counts = torch.zeros(max(n, 1), dtype=torch.int32, device=dev)
+    kps = torch.zeros((max(n, 1), cap, 7), device=dev); desc = torch.zeros((max(n, 1), cap, 32), dtype=torch.uint8, device=dev)
+    stream = torch.cuda.ExternalStream(ex.stream(), device=dev)
+    flags = Y.IN_DEVICE | Y.OUT_DEVICE | Y.NO_SYNC
+    def run():
+        for f0 in range(0, n, chunk):
+            m = min(chunk, n - f0)
+            ex.extract_raw(d_in.data_ptr(), m, w, h, w, w * h, flags, cap, counts[f0:].data_ptr(), kps[f0:].data_ptr(), desc[f0:].data_ptr())
+    run(); ex.sync()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream); run(); e1.record(stream); ex.sync()
+    ms = e0.elapsed_time(e1)
+    t_g = time.perf_counter()
+    if world > 1:   # the only communication: gather of (count, keypoints, descriptors) per frame to rank 0
+        sharding.gather_rows(counts[:n].unsqueeze(1), n_total); sharding.gather_rows(kps[:n], n_total); sharding.gather_rows(desc[:n], n_total)
+        torch.cuda.synchronize()
+        ms = sharding.max_over_ranks(ms, dev)
+    gather_ms = (time.perf_counter() - t_g) * 1e3
+    staged = 13392083
+    return {"config": "%d frames 1280x720, 2000 features, frame-sharded over %d GPU(s), chunk %d (the chunk's frames are reused from HBM)"
+                      % (n_total, world, chunk), "ms": ms, "frames_per_s": n_total / (ms * 1e-3), "gather_ms_wall": gather_ms,
+            "keypoints_per_frame": float(counts[:n].float().mean().item()) if n else 0,
+            "staged_GBps": staged * n_total / (ms * 1e-3) / 1e9, "scaling": "strong"}
+
+
+def knn(args, rank, local, world, dev):
+    nq, nt = args.nq, args.nt
+    b, e = sharding.shard_range(nq, rank, world)
+    rng = np.random.default_rng(5)
+    train = torch.from_numpy(rng.integers(0, 256, size=(nt, 32), dtype=np.uint8)).to(dev) if rank == 0 else torch.zeros((nt, 32), dtype=torch.uint8, device=dev)
+    if world > 1:
+        dist.broadcast(train, src=0)                          # train rows replicated once (32 MB for 1M)
+    g = torch.Generator(device=dev); g.manual_seed(100 + rank)
+    n = e - b
+    query = torch.randint(0, 256, (max(n, 1), 32), dtype=torch.uint8, device=dev, generator=g)
+    half = n // 2
+    if half:
+        src = torch.randint(0, nt, (half,), device=dev, generator=g)
+        noise = (torch.rand((half, 32, 8), device=dev, generator=g) < 0.1).to(torch.uint8)
+        bits = (noise << torch.arange(8, device=dev, dtype=torch.uint8)).sum(dim=2).to(torch.uint8)
+        query[:half] = train[src] ^ bits
+    mt = Y.Matcher(local)
+    out = torch.zeros((max(n, 1), 4), dtype=torch.int32, device=dev)
+    cols = [torch.zeros(max(n, 1), dtype=torch.int32, device=dev) for _ in range(4)]
+    stream = torch.cuda.ExternalStream(mt.stream(), device=dev)
+    flags = Y.IN_DEVICE | Y.OUT_DEVICE | Y.NO_SYNC
+    def run():
+        mt.hamming_knn2_raw(query.data_ptr(), n, train.data_ptr(), nt, args.ratio, 50, flags, *[c.data_ptr() for c in cols])
+    mt.hamming_knn2_raw(query.data_ptr(), min(n, 4096), train.data_ptr(), nt, args.ratio, 50, flags, *[c.data_ptr() for c in cols]); mt.sync()
+    peak = mt.popc_peak()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream); run(); e1.record(stream); mt.sync()
+    ms = e0.elapsed_time(e1)
+    out = torch.stack(cols, dim=1)
+    t_g = time.perf_counter()
+    if world > 1:
+        full = sharding.gather_rows(out[:n], nq)
+        torch.cuda.synchronize()
+        ms = sharding.max_over_ranks(ms, dev)
+        matches = int((full[:, 3] >= 0).sum().item()) if rank == 0 else 0
+    else:
+        matches = int((out[:n, 3] >= 0).sum().item())
+    gather_ms = (time.perf_counter() - t_g) * 1e3
+    pairs = nq * nt / (ms * 1e-3)
+    return {"config": "brute-force Hamming kNN k=2 + ratio %.2f, %d x %d rows, query-sharded over %d GPU(s)" % (args.ratio, nq, nt, world),
+            "ms": ms, "pairs_per_s": pairs, "queries_per_s": nq / (ms * 1e-3), "gather_ms_wall": gather_ms, "matches": matches,
+            "popc_peak_per_s_per_gpu": peak, "frac_of_popc_peak": pairs * 8 / (peak * world), "scaling": "strong"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--config", type=int, required=True)
+    ap.add_argument("--reps", type=int, default=200)
+    ap.add_argument("--frames", type=int, default=4096)
+    ap.add_argument("--chunk", type=int, default=256)
+    ap.add_argument("--nq", type=int, default=1 << 20)
+    ap.add_argument("--nt", type=int, default=1 << 20)
+    ap.add_argument("--ratio", type=float, default=0.6)
+    args = ap.parse_args()
+    rank, local, world, dev = setup()
+    fn = {0: single_frame, 2: stereo, 3: batched, 4: knn}[args.config]
+    res = fn(args, rank, local, world, dev)
+    res["n_gpus"] = world
+    if rank == 0:
+        print(json.dumps(res), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
