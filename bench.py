@@ -330,11 +330,14 @@ def run_ours(args, rank, local_rank, world):
     ms_sbp, _ = timed(search, args.steps)
     stage_ms["search_by_projection"] = ms_sbp / args.steps
     def shutdown():
-        mt.set_stream(None)
-        mt.close()
-        ex.close()
+        # torch's pinned-memory allocator records events on the extractor's stream when its buffers are freed at
+        # interpreter exit, i.e. after the handles (and their streams) are gone: leave without running destructors.
+        torch.cuda.synchronize()
         if dist is not None:
             dist.destroy_process_group()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
     if rank != 0:
         shutdown()
