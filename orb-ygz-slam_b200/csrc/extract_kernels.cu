@@ -15,48 +15,85 @@ namespace ygz {
 // the host (extractor.cu, makeResizeTables) with the double/float recipe of resize.cpp, so the
 // kernel is integer-only.  One thread produces 4 horizontally adjacent pixels (one 32-bit store).
 // Table entry X[dx] = {x0 | x1<<16, a0 | a1<<16}; Y[dy] = {y0 | y1<<16, b0 | b1<<16}.
+constexpr int kResizeRows = 4;   // destination rows per thread
+
 __global__ void __launch_bounds__(256) k_resize(const __grid_constant__ FrameGeom G, const DevBuffers B, int level) {
     const LevelGeom &D = G.lv[level];
     const LevelGeom &S = G.lv[level - 1];
     const int f = blockIdx.z;
     const int dx0 = (blockIdx.x * 32 + threadIdx.x) * 4;
-    const int dy = blockIdx.y * 8 + threadIdx.y;
-    if (dx0 >= D.pitch || dy >= D.h) return;
+    const int dyBase = (blockIdx.y * 8 + threadIdx.y) * kResizeRows;
+    if (dx0 >= D.pitch || dyBase >= D.h) return;
     const uint8_t *src = levelPtr(G, B, f, level - 1);
-    uint8_t *dst = B.pyr + (long long)f * G.slabBytes + D.off + (long long)dy * D.pitch + dx0;
+    uint8_t *dst = B.pyr + (long long)f * G.slabBytes + D.off + dx0;
     const int sp = S.pitch;
-    uint32_t out = 0;
     if (D.area2x) {  // ResizeAreaFast 2x2 mean
-        const uint8_t *s0 = src + (long long)(2 * dy) * sp, *s1 = s0 + sp;
+        for (int k = 0; k < kResizeRows; k++) {
+            const int dy = dyBase + k;
+            if (dy >= D.h) break;
+            const uint8_t *s0 = src + (long long)(2 * dy) * sp, *s1 = s0 + sp;
+            uint32_t out = 0;
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const int dx = min(dx0 + i, D.w - 1);
-            const int v = (s0[2 * dx] + s0[2 * dx + 1] + s1[2 * dx] + s1[2 * dx + 1] + 2) >> 2;
-            out |= (uint32_t)v << (8 * i);
+            for (int i = 0; i < 4; i++) {
+                const int dx = min(dx0 + i, D.w - 1);
+                const int v = (s0[2 * dx] + s0[2 * dx + 1] + s1[2 * dx] + s1[2 * dx + 1] + 2) >> 2;
+                out |= (uint32_t)v << (8 * i);
+            }
+            *reinterpret_cast<uint32_t *>(dst + (long long)dy * D.pitch) = out;
         }
-    } else {
-        const int2 ty = __ldg(B.tabs + D.tabY + dy);
-        const uint8_t *s0 = src + (long long)(ty.x & 0xffff) * sp;
-        const uint8_t *s1 = src + (long long)((uint32_t)ty.x >> 16) * sp;
-        const int b0 = (short)(ty.y & 0xffff), b1 = (short)((uint32_t)ty.y >> 16);
+        return;
+    }
+    // column taps of the 4 pixels, once per thread (the table is padded to the pitch)
+    int x0[4], x1[4], a0[4], a1[4];
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const int2 tx = __ldg(B.tabs + D.tabX + dx0 + i);  // table is padded to the pitch
-            const int x0 = tx.x & 0xffff, x1 = (uint32_t)tx.x >> 16;
-            const int a0 = (short)(tx.y & 0xffff), a1 = (short)((uint32_t)tx.y >> 16);
-            const int r0 = s0[x0] * a0 + s0[x1] * a1;
-            const int r1 = s1[x0] * a0 + s1[x1] * a1;
-            int v = (((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2;
-            v = min(max(v, 0), 255);
-            out |= (uint32_t)v << (8 * i);
+    for (int i = 0; i < 4; i++) {
+        const int2 tx = __ldg(B.tabs + D.tabX + dx0 + i);
+        x0[i] = tx.x & 0xffff; x1[i] = (uint32_t)tx.x >> 16;
+        a0[i] = (short)(tx.y & 0xffff); a1[i] = (short)((uint32_t)tx.y >> 16);
+    }
+    // rows: the horizontal pass of source row y1(dy) is reused when it is y0(dy + 1) (always, away from the edges)
+    int prevY = -1, hPrev[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int k = 0; k < kResizeRows; k++) {
+        const int dy = dyBase + k;
+        if (dy < D.h) {
+            const int2 ty = __ldg(B.tabs + D.tabY + dy);
+            const int y0 = ty.x & 0xffff, y1 = (uint32_t)ty.x >> 16;
+            const int b0 = (short)(ty.y & 0xffff), b1 = (short)((uint32_t)ty.y >> 16);
+            int h0[4], h1[4];
+            if (y0 == prevY) {
+#pragma unroll
+                for (int i = 0; i < 4; i++) h0[i] = hPrev[i];
+            } else {
+                const uint8_t *s0 = src + (long long)y0 * sp;
+#pragma unroll
+                for (int i = 0; i < 4; i++) h0[i] = s0[x0[i]] * a0[i] + s0[x1[i]] * a1[i];
+            }
+            if (y1 == y0) {
+#pragma unroll
+                for (int i = 0; i < 4; i++) h1[i] = h0[i];
+            } else {
+                const uint8_t *s1 = src + (long long)y1 * sp;
+#pragma unroll
+                for (int i = 0; i < 4; i++) h1[i] = s1[x0[i]] * a0[i] + s1[x1[i]] * a1[i];
+            }
+            uint32_t out = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                int v = (((b0 * (h0[i] >> 4)) >> 16) + ((b1 * (h1[i] >> 4)) >> 16) + 2) >> 2;
+                v = min(max(v, 0), 255);
+                out |= (uint32_t)v << (8 * i);
+                hPrev[i] = h1[i];
+            }
+            prevY = y1;
+            *reinterpret_cast<uint32_t *>(dst + (long long)dy * D.pitch) = out;  // pitch is a multiple of 64: padding is scratch
         }
     }
-    *reinterpret_cast<uint32_t *>(dst) = out;  // pitch is a multiple of 64: padding bytes are scratch
 }
 
 int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nFrames, cudaStream_t s) {
     const LevelGeom &D = G.lv[level];
-    dim3 block(32, 8), grid((D.pitch / 4 + 31) / 32, (D.h + 7) / 8, nFrames);
+    dim3 block(32, 8), grid((D.pitch / 4 + 31) / 32, (D.h + 8 * kResizeRows - 1) / (8 * kResizeRows), nFrames);
     k_resize<<<grid, block, 0, s>>>(G, B, level);
     return 1;
 }
@@ -576,49 +613,70 @@ __global__ void __launch_bounds__(kBlurThreads) k_blur(const __grid_constant__ F
     const bool aligned = ((L.pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(img) & 3) == 0);
     // ---- stage the raw tile (+3 halo, REFLECT_101 about the true image edge), 32-bit words where possible
     constexpr int kWords = kBlurRawPitch / 4;
-    for (int i = tid; i < kBlurRawRows * kWords; i += kBlurThreads) {
-        const int r = i / kWords, wq = i - r * kWords;
-        const int sy = reflect101(y0 + r - 3, L.h);
-        const int x = x0 - 4 + 4 * wq;
-        const uint8_t *row = img + (long long)sy * L.pitch;
-        uint32_t v;
-        if (aligned && x >= 0 && x + 3 < L.w) {
-            v = *reinterpret_cast<const uint32_t *>(row + x);
-        } else if (x + 3 < -3 || x > L.w + 2 + 3) {
-            v = 0;   // never read: beyond the halo of the last partial tile
-        } else {
-            v = (uint32_t)row[reflect101(x, L.w)] | ((uint32_t)row[reflect101(x + 1, L.w)] << 8) |
-                ((uint32_t)row[reflect101(x + 2, L.w)] << 16) | ((uint32_t)row[reflect101(x + 3, L.w)] << 24);
+    const bool interior = aligned && x0 >= 4 && x0 + kBlurTW + 4 <= L.w && y0 >= 3 && y0 + kBlurTH + 3 <= L.h;
+    if (interior) {
+        const uint8_t *base = img + (long long)(y0 - 3) * L.pitch + x0 - 4;
+        for (int i = tid; i < kBlurRawRows * kWords; i += kBlurThreads) {
+            const int r = i / kWords, wq = i - r * kWords;
+            *reinterpret_cast<uint32_t *>(&raw[r * kBlurRawPitch + 4 * wq]) =
+                __ldg(reinterpret_cast<const uint32_t *>(base + (long long)r * L.pitch) + wq);
         }
-        *reinterpret_cast<uint32_t *>(&raw[r * kBlurRawPitch + 4 * wq]) = v;
+    } else {
+        for (int i = tid; i < kBlurRawRows * kWords; i += kBlurThreads) {
+            const int r = i / kWords, wq = i - r * kWords;
+            const int sy = reflect101(y0 + r - 3, L.h);
+            const int x = x0 - 4 + 4 * wq;
+            const uint8_t *row = img + (long long)sy * L.pitch;
+            uint32_t v;
+            if (aligned && x >= 0 && x + 3 < L.w) {
+                v = *reinterpret_cast<const uint32_t *>(row + x);
+            } else if (x + 3 < -3 || x > L.w + 2 + 3) {
+                v = 0;   // never read: beyond the halo of the last partial tile
+            } else {
+                v = (uint32_t)row[reflect101(x, L.w)] | ((uint32_t)row[reflect101(x + 1, L.w)] << 8) |
+                    ((uint32_t)row[reflect101(x + 2, L.w)] << 16) | ((uint32_t)row[reflect101(x + 3, L.w)] << 24);
+            }
+            *reinterpret_cast<uint32_t *>(&raw[r * kBlurRawPitch + 4 * wq]) = v;
+        }
     }
     __syncthreads();
-    // ---- horizontal pass: 4 outputs per thread from raw columns 4tx+1 .. 4tx+10
+    // ---- horizontal pass: 4 outputs per thread from raw columns 4tx+1 .. 4tx+10.  Output k is the dot product of
+    // bytes (1+k .. 7+k) with {18,34,48,56,48,34,18}: two byte-aligned windows (funnel shifts) and two DP4A.
     const int tx = tid & 63, tg = tid >> 6;
+    constexpr uint32_t kW0 = 18u | (34u << 8) | (48u << 16) | (56u << 24), kW1 = 48u | (34u << 8) | (18u << 16);
     for (int r = tg; r < kBlurRawRows; r += 4) {
         const uint32_t *w = reinterpret_cast<const uint32_t *>(&raw[r * kBlurRawPitch + 4 * tx]);
         const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
-        int p[10];   // columns 4tx+1 .. 4tx+10
-        p[0] = (w0 >> 8) & 255; p[1] = (w0 >> 16) & 255; p[2] = w0 >> 24;
-        p[3] = w1 & 255; p[4] = (w1 >> 8) & 255; p[5] = (w1 >> 16) & 255; p[6] = w1 >> 24;
-        p[7] = w2 & 255; p[8] = (w2 >> 8) & 255; p[9] = (w2 >> 16) & 255;
         uint32_t o[4];
 #pragma unroll
-        for (int k = 0; k < 4; k++)
-            o[k] = 18 * (p[k] + p[k + 6]) + 34 * (p[k + 1] + p[k + 5]) + 48 * (p[k + 2] + p[k + 4]) + 56 * p[k + 3];
+        for (int k = 0; k < 3; k++) {
+            const uint32_t a = __funnelshift_r(w0, w1, 8 * (k + 1)), b = __funnelshift_r(w1, w2, 8 * (k + 1));
+            o[k] = __dp4a(b, kW1, __dp4a(a, kW0, 0u));
+        }
+        o[3] = __dp4a(w2, kW1, __dp4a(w1, kW0, 0u));
         hs[r * (kBlurTW / 4) + tx] = make_uint2(o[0] | (o[1] << 16), o[2] | (o[3] << 16));
     }
     __syncthreads();
-    // ---- vertical pass: each thread 4 columns x 8 rows, sliding over 14 rows of horizontal sums
+    // ---- vertical pass: each thread 4 columns x 8 rows over a 14-row register window.  Rows are paired per column
+    // (PRMT) so that one DP2A applies two taps: acc = (18,34).P[k] + (48,56).P[k+2] + (48,34).P[k+4] + (0,18).P[k+5].
     const int x = x0 + 4 * tx;
     if (x >= L.w) return;
     uint8_t *dst = B.blur + (long long)f * B.blurSlab + B.blurOff[level];
     const int dp = B.blurPitch[level];
     constexpr int kRowsPer = kBlurTH / 4;
     const int rBase = tg * kRowsPer;
-    uint2 win[kRowsPer + 6];
+    uint32_t pr[4][kRowsPer + 5];   // pr[c][j] = h[row j][col c] | h[row j+1][col c] << 16
+    {
+        uint2 prev = hs[rBase * (kBlurTW / 4) + tx];
 #pragma unroll
-    for (int k = 0; k < kRowsPer + 6; k++) win[k] = hs[(rBase + k) * (kBlurTW / 4) + tx];
+        for (int j = 0; j < kRowsPer + 5; j++) {
+            const uint2 cur = hs[(rBase + j + 1) * (kBlurTW / 4) + tx];
+            pr[0][j] = __byte_perm(prev.x, cur.x, 0x5410); pr[1][j] = __byte_perm(prev.x, cur.x, 0x7632);
+            pr[2][j] = __byte_perm(prev.y, cur.y, 0x5410); pr[3][j] = __byte_perm(prev.y, cur.y, 0x7632);
+            prev = cur;
+        }
+    }
+    constexpr uint32_t kV01 = 18u | (34u << 8), kV23 = 48u | (56u << 8), kV45 = 48u | (34u << 8), kV6 = 18u << 8;
 #pragma unroll
     for (int k = 0; k < kRowsPer; k++) {
         const int y = y0 + rBase + k;
@@ -626,12 +684,11 @@ __global__ void __launch_bounds__(kBlurThreads) k_blur(const __grid_constant__ F
             uint32_t out = 0;
 #pragma unroll
             for (int c = 0; c < 4; c++) {
-                auto get = [&](int j) -> uint32_t {
-                    const uint32_t word = (c < 2) ? win[k + j].x : win[k + j].y;
-                    return (c & 1) ? (word >> 16) : (word & 0xffffu);
-                };
-                const uint32_t acc = 18u * (get(0) + get(6)) + 34u * (get(1) + get(5)) + 48u * (get(2) + get(4)) + 56u * get(3);
-                out |= ((acc + 32768u) >> 16) << (8 * c);
+                uint32_t acc = __dp2a_lo(pr[c][k], kV01, 32768u);
+                acc = __dp2a_lo(pr[c][k + 2], kV23, acc);
+                acc = __dp2a_lo(pr[c][k + 4], kV45, acc);
+                acc = __dp2a_lo(pr[c][k + 5], kV6, acc);
+                out |= (acc >> 16) << (8 * c);
             }
             *reinterpret_cast<uint32_t *>(dst + (long long)y * dp + x) = out;
         }

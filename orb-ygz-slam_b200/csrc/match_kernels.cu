@@ -255,9 +255,41 @@ __device__ __forceinline__ bool posInGrid(const ProjArgs &A, float x, float y, i
 }
 
 // One MapPoint against the frame, given the claim table.  Returns the accepted keypoint or -1.
+// Candidate cache: the candidates of a MapPoint (keypoints inside its window that pass the level and
+// uRight filters) and their distances do not depend on the claims, so round 0 records them —
+// idx | dist << 16 | octave << 25, in visit order, entry k of MapPoint j at cache[(f*kProjCache + k)*mpStride + j]
+// (coalesced over j) — and later rounds only re-apply the claim table to the cached list.  MapPoints
+// with more than kProjCache candidates (large th) are re-walked in every round instead.
+constexpr int kProjCache = 12;
+constexpr int kProjOverflow = 255;
+
+__device__ __forceinline__ int projAccept(const ProjArgs &A, int bestDist, int bestDist2, int bestLevel, int bestLevel2, int bestIdx) {
+    if (bestDist <= kThHigh) {
+        if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(A.nnratio, (float)bestDist2)) return -1;
+        return bestIdx;
+    }
+    return -1;
+}
+
+__device__ int projMatchCached(const ProjArgs &A, int f, int j, int cnt, const int32_t *claimTime) {
+    int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+    const uint32_t *c = A.candCache + (size_t)f * kProjCache * A.mpStride + j;
+    for (int k = 0; k < cnt; k++) {
+        const uint32_t e = c[(size_t)k * A.mpStride];
+        const int idx = e & 0xffffu;
+        if (claimTime[idx] < j) continue;
+        const int dist = (e >> 16) & 0x1ff, oct = (int)(e >> 25);
+        if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = oct; bestIdx = idx; }
+        else if (dist < bestDist2) { bestLevel2 = oct; bestDist2 = dist; }
+    }
+    return projAccept(A, bestDist, bestDist2, bestLevel, bestLevel2, bestIdx);
+}
+
+template <bool RECORD>
 __device__ int projMatchOne(const ProjArgs &A, int f, int j, int n, const int *cellStart, const int32_t *gridList,
-                            const int32_t *claimTime) {
+                            const int32_t *claimTime, int *recorded) {
     const size_t mo = (size_t)f * A.mpStride + j;
+    if (RECORD) *recorded = 0;
     if (!A.inView[mo]) return -1;
     const int lvl = A.level[mo];
     float r = ((double)A.viewCos[mo] > 0.998) ? 2.5f : 4.0f;      // RadiusByViewingCos (:128-133)
@@ -282,6 +314,8 @@ __device__ int projMatchOne(const ProjArgs &A, int f, int j, int n, const int *c
     const float projXR = A.projXR ? A.projXR[mo] : 0.f;
     int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
     (void)n;
+    int nrec = 0;
+    uint32_t *cache = RECORD ? A.candCache + (size_t)f * kProjCache * A.mpStride + j : nullptr;
     for (int ix = cx0; ix <= cx1; ix++) {
         const int cb = ix * kGridRows;
         for (int k = cellStart[cb + cy0], ke = cellStart[cb + cy1 + 1]; k < ke; k++) {   // cells (ix, cy0..cy1) are contiguous
@@ -293,21 +327,24 @@ __device__ int projMatchOne(const ProjArgs &A, int f, int j, int n, const int *c
                 if (maxLevel >= 0 && oct > maxLevel) continue;
             }
             if (!(fabsf(__fsub_rn(kp.x, x)) < rad && fabsf(__fsub_rn(kp.y, y)) < rad)) continue;
-            if (claimTime[idx] < j) continue;                          // mvpMapPoints[idx]->Observations() > 0 (:89-91)
+            const bool skip = claimTime[idx] < j;                      // mvpMapPoints[idx]->Observations() > 0 (:89-91)
+            if (!RECORD && skip) continue;
             if (uRight) {
                 const float ur = uRight[idx];
                 if (ur > 0 && fabsf(__fsub_rn(projXR, ur)) > rad) continue;   // :93-97
             }
             const int dist = hamming256(m0, m1, desc[2 * idx], desc[2 * idx + 1]);
+            if (RECORD) {
+                if (nrec < kProjCache) cache[(size_t)nrec * A.mpStride] = (uint32_t)idx | ((uint32_t)dist << 16) | ((uint32_t)oct << 25);
+                nrec++;
+                if (skip) continue;
+            }
             if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = oct; bestIdx = idx; }
             else if (dist < bestDist2) { bestLevel2 = oct; bestDist2 = dist; }
         }
     }
-    if (bestDist <= kThHigh) {
-        if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(A.nnratio, (float)bestDist2)) return -1;
-        return bestIdx;
-    }
-    return -1;
+    if (RECORD) *recorded = nrec;
+    return projAccept(A, bestDist, bestDist2, bestLevel, bestLevel2, bestIdx);
 }
 
 __global__ void __launch_bounds__(kProjThreads) k_search_by_projection(const __grid_constant__ ProjArgs A) {
@@ -348,21 +385,31 @@ __global__ void __launch_bounds__(kProjThreads) k_search_by_projection(const __g
             gridList[k + 1] = v;
         }
     }
-    for (int j = tid; j < m; j += kProjThreads) best[j] = -2;   // "not evaluated yet"
+    uint8_t *candCnt = A.candCnt + (size_t)f * A.mpStride;
+    __syncthreads();
+    // ---- round 0: full window walk against the entry claims, recording the candidate cache
+    for (int i = tid; i < n; i += kProjThreads) claimTime[i] = (claimed && claimed[i]) ? -1 : INT_MAX;
+    __syncthreads();
+    for (int j = tid; j < m; j += kProjThreads) {
+        int nrec;
+        best[j] = projMatchOne<true>(A, f, j, n, cellStart, gridList, claimTime, &nrec);
+        candCnt[j] = (uint8_t)(nrec > kProjCache ? kProjOverflow : nrec);
+    }
     __syncthreads();
     // ---- fixed-point iteration over the claim table
-    for (int round = 0; round <= m; round++) {
+    for (int round = 1; round <= m + 1; round++) {
         for (int i = tid; i < n; i += kProjThreads) claimTime[i] = (claimed && claimed[i]) ? -1 : INT_MAX;
         __syncthreads();
-        if (round > 0)
-            for (int j = tid; j < m; j += kProjThreads) {
-                const int b = best[j];
-                if (b >= 0 && A.hasObs[(size_t)f * A.mpStride + j]) atomicMin(&claimTime[b], j);
-            }
+        for (int j = tid; j < m; j += kProjThreads) {
+            const int b = best[j];
+            if (b >= 0 && A.hasObs[(size_t)f * A.mpStride + j]) atomicMin(&claimTime[b], j);
+        }
         __syncthreads();
         int changed = 0;
         for (int j = tid; j < m; j += kProjThreads) {
-            const int b = projMatchOne(A, f, j, n, cellStart, gridList, claimTime);
+            const int cnt = candCnt[j];
+            const int b = cnt == kProjOverflow ? projMatchOne<false>(A, f, j, n, cellStart, gridList, claimTime, nullptr)
+                                               : projMatchCached(A, f, j, cnt, claimTime);
             if (b != best[j]) { best[j] = b; changed = 1; }
         }
         if (!__syncthreads_or(changed)) break;

@@ -246,6 +246,11 @@ int ygzorb_search_by_projection(ygzorb_matcher *h, const ygzorb_frame_features *
     A.claimTime = (int32_t *)p;
     if ((rc = scratch(m, 18, nk * 4, &p))) return rc;
     A.gridList = (int32_t *)p;
+    if (F->kp_stride > 65535) return argFailM("kp_stride must be <= 65535");
+    if ((rc = scratch(m, 19, nm * 12 * 4, &p))) return rc;
+    A.candCache = (uint32_t *)p;
+    if ((rc = scratch(m, 20, nm, &p))) return rc;
+    A.candCnt = (uint8_t *)p;
     m->launches += launchSearchByProjection(A, F->kp_stride, m->stream);
     if ((rc = copyOut(m, kpToMp, A.kpToMp, nk, outDev))) return rc;
     if ((rc = copyOut(m, mpBestIdx, A.mpBestIdx, nm, outDev))) return rc;

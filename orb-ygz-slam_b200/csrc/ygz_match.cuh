@@ -25,6 +25,8 @@ struct ProjArgs {
     int32_t *kpToMp, *mpBestIdx, *nMatches;   // outputs (mpBestIdx is also the iteration state)
     int32_t *claimTime;                       // scratch [nFrames * kpStride]
     int32_t *gridList;                        // scratch [nFrames * kpStride]
+    uint32_t *candCache;                      // scratch [nFrames * 12 * mpStride]
+    uint8_t *candCnt;                         // scratch [nFrames * mpStride]
 };
 
 struct KfView {          // one KeyFrame's arrays for SearchForTriangulation (device pointers)
