@@ -113,6 +113,7 @@ constexpr int kFastThreads = 128;
 constexpr int kCellMax = 64;                 // wCell, hCell < 60 always (width/floor(width/30))
 constexpr int kTilePitch = 76;               // image tile pitch: cell + 6 + up to 3 alignment bytes, multiple of 4
 constexpr int kScorePitch = 68;              // score tile pitch: detection width + 2, multiple of 4
+constexpr int kFastWarpCap = (kCellMax * kCellMax / kFastThreads + 1) * 32;   // pixels one warp visits (multiple of 32)
 
 // The 16 ring differences are kept as packed 16-bit pairs E = (d + 256) | (256 - d) << 16 with
 // d = v - p, both halves positive, so ONE VIMNMX3.U16x2 handles the "darker" arcs (low half) and
@@ -152,17 +153,6 @@ __device__ __forceinline__ int fastMeasure(const uint8_t *p, unsigned pre) {
     return (int)max(r & 0xffffu, r >> 16) - 256;
 }
 
-// Appends `value` for every lane with `pred` to a shared list (order irrelevant); one shared atomic per warp.
-__device__ __forceinline__ void fastAppend(bool pred, uint16_t value, uint16_t *list, int *counter) {
-    const unsigned mask = __ballot_sync(0xffffffffu, pred);
-    if (mask == 0) return;
-    const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
-    int base = 0;
-    if (lane == leader) base = atomicAdd(counter, __popc(mask));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (pred) list[base + __popc(mask & ((1u << lane) - 1))] = value;
-}
-
 // NMS of cv::FAST is threshold-independent on m: a corner at threshold t (m > t) survives iff its
 // stored score m-1 exceeds the stored scores of its 8 neighbours, and a neighbour's stored score is
 // n-1 if n > t and 0 otherwise; since m > t >= 1 this is exactly "every neighbour has n < m".  The
@@ -170,9 +160,8 @@ __device__ __forceinline__ void fastAppend(bool pred, uint16_t value, uint16_t *
 __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
     __shared__ __align__(16) uint8_t tile[(kCellMax + 6) * kTilePitch];
     __shared__ __align__(16) uint8_t score[(kCellMax + 2) * kScorePitch];
-    __shared__ uint16_t corners[kCellMax * kCellMax];   // y<<6 | x of pixels with m > minThFAST
-    __shared__ uint16_t maxima[kCellMax * kCellMax / 4 + 64];  // local maxima among them
-    __shared__ int nList[2];
+    __shared__ uint16_t corners[(kFastThreads / 32) * kFastWarpCap];      // per warp: y<<6 | x of pixels with m > minThFAST
+    __shared__ uint16_t maxima[(kFastThreads / 32) * (kFastWarpCap / 2)];  // per warp: strict local maxima among them
     const int f = blockIdx.y, tid = threadIdx.x;
     int level = 0;
     while (level + 1 < G.nlevels && (int)blockIdx.x >= G.lv[level + 1].cellStart) level++;
@@ -208,11 +197,15 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
         }
     }
     for (int i = tid; i < (dh + 2) * (kScorePitch / 4); i += kFastThreads) reinterpret_cast<uint32_t *>(score)[i] = 0;
-    if (tid < 2) nList[tid] = 0;
     __syncthreads();
     const int minTh = G.minTh, iniTh = G.iniTh;
     const unsigned magic = (1u << 18) / (unsigned)dw + 1;   // i / dw for i < 4096, dw <= 64
-    // ---- phase 1: measure of every detection pixel; corners at minThFAST -> score tile + list
+    // ---- phase 1: measure of every detection pixel; corners at minThFAST -> score tile + the warp's own list
+    // (lists are per warp with the fill count in a register: no shared atomics, no shuffles)
+    const int lane = tid & 31, wid = tid >> 5;
+    const unsigned ltMask = (1u << lane) - 1u;
+    uint16_t *myCorners = corners + wid * kFastWarpCap;
+    int n1 = 0;
     for (int i0 = 0; i0 < npx; i0 += kFastThreads) {
         const int i = i0 + tid;
         bool corner = false;
@@ -223,18 +216,20 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
             corner = m > minTh;
             if (corner) score[(y + 1) * kScorePitch + x + 1] = (uint8_t)m;
         }
-        fastAppend(corner, (uint16_t)((y << 6) | x), corners, &nList[0]);
+        const unsigned mask = __ballot_sync(0xffffffffu, corner);
+        if (corner) myCorners[n1 + __popc(mask & ltMask)] = (uint16_t)((y << 6) | x);
+        n1 += __popc(mask);
     }
     __syncthreads();
-    // ---- phase 2: strict local maxima of m among the corners
-    const int n1 = nList[0];
-    int any = 0;
-    for (int i0 = 0; i0 < n1; i0 += kFastThreads) {
-        const int i = i0 + tid;
+    // ---- phase 2: strict local maxima of m among the warp's corners
+    uint16_t *myMaxima = maxima + wid * (kFastWarpCap / 2);
+    int n2 = 0, any = 0;
+    for (int k0 = 0; k0 < n1; k0 += 32) {
+        const int k = k0 + lane;
         bool ismax = false;
         uint16_t yx = 0;
-        if (i < n1) {
-            yx = corners[i];
+        if (k < n1) {
+            yx = myCorners[k];
             const uint8_t *sc = &score[((yx >> 6) + 1) * kScorePitch + (yx & 63) + 1];
             const int m = sc[0];
             const int nb = max(max(max(sc[-1], sc[1]), max(sc[-kScorePitch - 1], sc[-kScorePitch])),
@@ -242,21 +237,20 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
             ismax = nb < m;
             any |= ismax && m > iniTh;
         }
-        fastAppend(ismax, yx, maxima, &nList[1]);
+        const unsigned mask = __ballot_sync(0xffffffffu, ismax);
+        if (ismax) myMaxima[n2 + __popc(mask & ltMask)] = yx;
+        n2 += __popc(mask);
     }
     // ---- threshold fallback: iniThFAST unless nothing survives in the cell (src/ORBextractor.cc:764-770)
     const int t = __syncthreads_or(any) ? iniTh : minTh;
-    const int n2 = nList[1];
     uint2 *cand = B.cand + (long long)f * G.candPerFrame + L.candOff;
     int *counter = B.candCount + f * kMaxLevels + level;
-    const int lane = tid & 31;
-    for (int i0 = 0; i0 < n2; i0 += kFastThreads) {
-        if (i0 + (tid & ~31) >= n2) break;   // whole warp beyond the list
-        const int i = i0 + tid;
+    for (int k0 = 0; k0 < n2; k0 += 32) {
+        const int k = k0 + lane;
         bool keep = false;
         int y = 0, x = 0, m = 0;
-        if (i < n2) {
-            const int yx = maxima[i];
+        if (k < n2) {
+            const int yx = myMaxima[k];
             y = yx >> 6; x = yx & 63;
             m = score[(y + 1) * kScorePitch + x + 1];
             keep = m > t;
@@ -267,7 +261,7 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
         if (lane == __ffs(mask) - 1) base = atomicAdd(counter, __popc(mask));
         base = __shfl_sync(0xffffffffu, base, __ffs(mask) - 1);
         if (keep) {
-            const int slot = base + __popc(mask & ((1u << lane) - 1));
+            const int slot = base + __popc(mask & ltMask);
             if (slot < L.candCap) {
                 const uint32_t ax = iniX + 3 + x, ay = iniY + 3 + y;  // absolute level coordinates
                 cand[slot] = make_uint2(ax | (ay << 12) | ((uint32_t)(m - 1) << 24),
@@ -611,15 +605,41 @@ __global__ void __launch_bounds__(kBlurThreads) k_blur(const __grid_constant__ F
     const int x0 = txI * kBlurTW, y0 = tyI * kBlurTH;
     const uint8_t *img = levelPtr(G, B, f, level);
     const bool aligned = ((L.pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(img) & 3) == 0);
-    // ---- stage the raw tile (+3 halo, REFLECT_101 about the true image edge), 32-bit words where possible
+    // ---- stage the raw tile (+3 halo, REFLECT_101 about the true image edge).  Words that lie fully inside the
+    // image are aligned 32-bit loads (warp = row, lanes = words: no divisions, no divergence); the <= 3 words per
+    // row that straddle the image edge are assembled byte-wise by a separate, equally uniform loop.  One
+    // reflection is enough because the halo (<= 7 px) is shorter than the image; tiny or unaligned images take
+    // the generic path.
     constexpr int kWords = kBlurRawPitch / 4;
-    const bool interior = aligned && x0 >= 4 && x0 + kBlurTW + 4 <= L.w && y0 >= 3 && y0 + kBlurTH + 3 <= L.h;
-    if (interior) {
-        const uint8_t *base = img + (long long)(y0 - 3) * L.pitch + x0 - 4;
-        for (int i = tid; i < kBlurRawRows * kWords; i += kBlurThreads) {
-            const int r = i / kWords, wq = i - r * kWords;
-            *reinterpret_cast<uint32_t *>(&raw[r * kBlurRawPitch + 4 * wq]) =
-                __ldg(reinterpret_cast<const uint32_t *>(base + (long long)r * L.pitch) + wq);
+    const int lane = tid & 31, wid = tid >> 5;
+    if (aligned && L.w >= 8 && L.h >= 8) {
+        const int wqLo = x0 == 0 ? 1 : 0;
+        const int wqHi = max(wqLo, min(kWords, (L.w - x0 + 4) >> 2));   // words with x + 3 < w
+        for (int r = wid; r < kBlurRawRows; r += kBlurThreads / 32) {
+            int sy = abs(y0 + r - 3);
+            sy = max(min(sy, 2 * (L.h - 1) - sy), 0);
+            const uint32_t *row = reinterpret_cast<const uint32_t *>(img + (long long)sy * L.pitch + x0 - 4);
+            for (int wq = wqLo + lane; wq < wqHi; wq += 32)
+                *reinterpret_cast<uint32_t *>(&raw[r * kBlurRawPitch + 4 * wq]) = __ldg(row + wq);
+        }
+        const int nRight = min(2, kWords - wqHi), nB = wqLo + nRight;
+        for (int i = tid; i < kBlurRawRows * 4; i += kBlurThreads) {
+            const int r = i >> 2, k = i & 3;
+            if (k < nB) {
+                const int wq = k < wqLo ? 0 : wqHi + (k - wqLo);
+                int sy = abs(y0 + r - 3);
+                sy = max(min(sy, 2 * (L.h - 1) - sy), 0);
+                const uint8_t *row = img + (long long)sy * L.pitch;
+                const int x = x0 - 4 + 4 * wq;
+                uint32_t v = 0;
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    int sx = abs(x + q);
+                    sx = max(min(sx, 2 * (L.w - 1) - sx), 0);
+                    v |= (uint32_t)row[sx] << (8 * q);
+                }
+                *reinterpret_cast<uint32_t *>(&raw[r * kBlurRawPitch + 4 * wq]) = v;
+            }
         }
     } else {
         for (int i = tid; i < kBlurRawRows * kWords; i += kBlurThreads) {
@@ -627,15 +647,10 @@ __global__ void __launch_bounds__(kBlurThreads) k_blur(const __grid_constant__ F
             const int sy = reflect101(y0 + r - 3, L.h);
             const int x = x0 - 4 + 4 * wq;
             const uint8_t *row = img + (long long)sy * L.pitch;
-            uint32_t v;
-            if (aligned && x >= 0 && x + 3 < L.w) {
-                v = *reinterpret_cast<const uint32_t *>(row + x);
-            } else if (x + 3 < -3 || x > L.w + 2 + 3) {
-                v = 0;   // never read: beyond the halo of the last partial tile
-            } else {
+            uint32_t v = 0;
+            if (!(x + 3 < -3 || x > L.w + 2 + 3))   // else: never read (beyond the halo of the last partial tile)
                 v = (uint32_t)row[reflect101(x, L.w)] | ((uint32_t)row[reflect101(x + 1, L.w)] << 8) |
                     ((uint32_t)row[reflect101(x + 2, L.w)] << 16) | ((uint32_t)row[reflect101(x + 3, L.w)] << 24);
-            }
             *reinterpret_cast<uint32_t *>(&raw[r * kBlurRawPitch + 4 * wq]) = v;
         }
     }
