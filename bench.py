@@ -255,30 +255,60 @@ def run_ours(args, rank, local_rank, world):
     F = Y.FrameFeatures(B, cap, d_counts.data_ptr(), d_kps.data_ptr(), d_desc.data_ptr(), None, None,
                         0.0, 0.0, float(W), float(H), LEVELS, sf.ctypes.data)
     P = Y.MapPointProj(M, *[d_mp[k].data_ptr() for k in mp_keys])
-    # pinned host mirrors of the results for the end-to-end leg
-    h_out = {"counts": torch.zeros(B, dtype=torch.int32).pin_memory(), "kps": torch.zeros((B, cap, 7)).pin_memory(),
-             "desc": torch.zeros((B, cap, 32), dtype=torch.uint8).pin_memory(),
-             "kp2mp": torch.zeros((B, cap), dtype=torch.int32).pin_memory(), "nm": torch.zeros(B, dtype=torch.int32).pin_memory()}
-    d_out = {"counts": d_counts, "kps": d_kps, "desc": d_desc, "kp2mp": d_kp2mp, "nm": d_nm}
     dflags = Y.IN_DEVICE | Y.OUT_DEVICE | Y.NO_SYNC
+    d_out = {"counts": d_counts, "kps": d_kps, "desc": d_desc, "kp2mp": d_kp2mp, "nm": d_nm}
 
-    def search():
-        mt.search_by_projection_raw(F, P, SBP_TH, False, SBP_RATIO, dflags, d_kp2mp.data_ptr(), d_best.data_ptr(), d_nm.data_ptr())
+    def search(F=F, P=P, out=d_out, best=d_best):
+        mt.search_by_projection_raw(F, P, SBP_TH, False, SBP_RATIO, dflags, out["kp2mp"].data_ptr(), best.data_ptr(),
+                                    out["nm"].data_ptr())
 
     def step_device():
         ex.extract_raw(dev_in.data_ptr(), B, W, H, W, W * H, dflags, cap, d_counts.data_ptr(), d_kps.data_ptr(), d_desc.data_ptr())
         search()
 
-    def step_host():   # frames and MapPoints come from pinned host memory, every result goes back to the host
-        ex.extract_raw(host_in.data_ptr(), B, W, H, W, W * H, Y.OUT_DEVICE | Y.NO_SYNC, cap,
-                       d_counts.data_ptr(), d_kps.data_ptr(), d_desc.data_ptr())
-        with torch.cuda.stream(stream):
+    # ---- end-to-end leg: frames and MapPoints come from pinned host memory, every result goes back to pinned
+    # host memory, each step.  Two slots of device buffers so that consecutive steps pipeline: the library
+    # uploads the frames in chunks on its own stream beside the kernels (ygzorb_extractor_set_pipeline); the
+    # MapPoint upload and the result download run on two side streams here, ordered by events.
+    copy_in, copy_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    slots = []
+    for sl in range(2):
+        o = d_out if sl == 0 else {k: torch.zeros_like(v) for k, v in d_out.items()}
+        m = d_mp if sl == 0 else {k: torch.zeros_like(v) for k, v in d_mp.items()}
+        slots.append({
+            "out": o, "mp": m, "best": d_best if sl == 0 else torch.zeros_like(d_best),
+            "F": Y.FrameFeatures(B, cap, o["counts"].data_ptr(), o["kps"].data_ptr(), o["desc"].data_ptr(), None, None,
+                                 0.0, 0.0, float(W), float(H), LEVELS, sf.ctypes.data),
+            "P": Y.MapPointProj(M, *[m[k].data_ptr() for k in mp_keys]),
+            "h_out": {k: torch.zeros(v.shape, dtype=v.dtype).pin_memory() for k, v in d_out.items()},
+            "mp_ready": torch.cuda.Event(), "search_done": torch.cuda.Event(), "out_done": torch.cuda.Event()})
+    h_out = slots[0]["h_out"]
+    host_step = [0]
+
+    def step_host():
+        S = slots[host_step[0] & 1]
+        host_step[0] += 1
+        copy_in.wait_event(S["search_done"])            # the previous search on this slot has read its MapPoints
+        with torch.cuda.stream(copy_in):
             for k in mp_keys:
-                d_mp[k].copy_(h_mp[k], non_blocking=True)
-        search()
-        with torch.cuda.stream(stream):
-            for k in h_out:
-                h_out[k].copy_(d_out[k], non_blocking=True)
+                S["mp"][k].copy_(h_mp[k], non_blocking=True)
+            S["mp_ready"].record(copy_in)
+        stream.wait_event(S["out_done"])                # the previous results of this slot are on the host
+        o = S["out"]
+        ex.extract_raw(host_in.data_ptr(), B, W, H, W, W * H, Y.OUT_DEVICE | Y.NO_SYNC, cap,
+                       o["counts"].data_ptr(), o["kps"].data_ptr(), o["desc"].data_ptr())
+        stream.wait_event(S["mp_ready"])
+        search(S["F"], S["P"], o, S["best"])
+        S["search_done"].record(stream)
+        copy_out.wait_event(S["search_done"])
+        with torch.cuda.stream(copy_out):
+            for k in o:
+                S["h_out"][k].copy_(o[k], non_blocking=True)
+            S["out_done"].record(copy_out)
+
+    def drain_host():                                    # the timed region ends when the last download has landed
+        for S in slots:
+            stream.wait_event(S["out_done"])
 
     def barrier():
         if dist is not None:
@@ -286,15 +316,18 @@ def run_ours(args, rank, local_rank, world):
         torch.cuda.synchronize()
         ex.sync()
 
-    def timed(step, steps):
+    def timed(step, steps, drain=None):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         l0 = ex.launch_count() + mt.launch_count()
         e0.record(stream)
         for _ in range(steps):
             step()
+        if drain is not None:
+            drain()
         e1.record(stream)
         ex.sync()
+        torch.cuda.synchronize()
         barrier()
         ms = e0.elapsed_time(e1)
         if dist is not None:
@@ -312,11 +345,14 @@ def run_ours(args, rank, local_rank, world):
     clocks = sampler.stop()
     n_kp = int(d_counts.sum().item())
     n_match = int(d_nm.sum().item())
-    for _ in range(max(args.warmup // 2, 1)):
+    for _ in range(max(args.warmup, 2)):
         step_host()
     ex.sync()
-    ms_e2e, _ = timed(step_host, args.steps)
-    assert int(h_out["counts"].sum().item()) == n_kp and int(h_out["nm"].sum().item()) == n_match, "host and device paths disagree"
+    torch.cuda.synchronize()
+    ms_e2e, _ = timed(step_host, args.steps, drain_host)
+    for S in slots:
+        assert int(S["h_out"]["counts"].sum().item()) == n_kp and int(S["h_out"]["nm"].sum().item()) == n_match, \
+            "host and device paths disagree"
     # per-stage device times: CUDA events between the extractor's stages + around the search, on the shared stream
     ex.set_profiling(True)
     acc = np.zeros(8)
@@ -457,7 +493,14 @@ def main():
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
         return
-    run_ours(args, rank, local_rank, world)
+    try:
+        run_ours(args, rank, local_rank, world)
+    except BaseException:
+        # leave without running destructors: a failed run must report its traceback, not a teardown crash
+        import traceback
+        traceback.print_exc()
+        sys.stdout.flush(); sys.stderr.flush()
+        os._exit(1)
 
 
 if __name__ == "__main__":

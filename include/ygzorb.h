@@ -28,7 +28,8 @@ extern "C" {
 /* Buffer-placement flags of the batch entry points. */
 #define YGZORB_IN_DEVICE 1u    /* input frames pointer is device memory (default: host) */
 #define YGZORB_OUT_DEVICE 2u   /* counts / keypoints / descriptors pointers are device memory */
-#define YGZORB_KEEP_STAGES 4u  /* keep blurred levels + FAST candidates readable (parity tests) */
+#define YGZORB_KEEP_STAGES 4u  /* one chunk per max_batch frames (no upload pipelining), so that the stage taps
+                                  (pyramid, blurred levels, FAST candidates) cover every frame of the call */
 #define YGZORB_NO_SYNC 8u      /* return after enqueueing; caller calls ygzorb_extractor_sync() */
 
 const char *ygzorb_last_error(void);
@@ -104,7 +105,13 @@ int ygzorb_get_blurred_level(ygzorb_extractor *ex, int frame, int level, uint8_t
 int ygzorb_get_candidates(ygzorb_extractor *ex, int frame, int level, int cap, int16_t *x, int16_t *y,
                           uint8_t *response, uint32_t *order_key);
 
+/* Wait for everything the extractor enqueued (kernels and the host-output downloads). */
 int ygzorb_extractor_sync(ygzorb_extractor *ex);
+/* Host-input calls are pipelined in chunks of `frames_per_chunk` frames (default 128): the upload of
+ * chunk k+1 and the download of chunk k-1 run on their own streams beside the kernels of chunk k, and
+ * with YGZORB_NO_SYNC also beside the tail of the previous call.  0 = one chunk per max_batch.  The stage
+ * taps then hold the LAST chunk only (pass YGZORB_KEEP_STAGES for parity tests). */
+int ygzorb_extractor_set_pipeline(ygzorb_extractor *ex, int frames_per_chunk);
 /* The extractor's cudaStream_t (as void*), for callers that time with CUDA events. */
 void *ygzorb_extractor_stream(ygzorb_extractor *ex);
 /* Kernel launches enqueued by this extractor since creation (bench.py's gpu_launches). */

@@ -112,34 +112,55 @@ int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nF
 constexpr int kFastThreads = 128;
 constexpr int kCellMax = 64;                 // wCell, hCell < 60 always (width/floor(width/30))
 constexpr int kTilePitch = 76;               // image tile pitch: cell + 6 + up to 3 alignment bytes, multiple of 4
-constexpr int kScorePitch = 68;              // score tile pitch: detection width + 2, multiple of 4
 constexpr int kFastWarpCap = (kCellMax * kCellMax / kFastThreads + 1) * 32;   // pixels one warp visits (multiple of 32)
 
 // The 16 ring differences are kept as packed 16-bit pairs E = (d + 256) | (256 - d) << 16 with
 // d = v - p, both halves positive, so ONE VIMNMX3.U16x2 handles the "darker" arcs (low half) and
 // the "brighter" arcs (high half) at once.  E = base + p * 0xFFFF with base = packed (v + 256, 256 - v):
 // no borrow crosses the halves because v + 256 - p >= 1.
+// Shared-memory accessors on 32-bit shared-window addresses.  With generic pointers the compiler
+// re-derives the CTA's shared window base (S2UR CgaCtaId + ULEA) at every use inside the pixel loop;
+// taking the address once with __cvta_generic_to_shared keeps the loop to the loads themselves.
+__device__ __forceinline__ unsigned smemAddr(const void *p) {
+    unsigned a = (unsigned)__cvta_generic_to_shared(p);
+    asm volatile("mov.u32 %0, %0;" : "+r"(a));   // opaque: stops the rematerialisation of the window base at every use
+    return a;
+}
+template <int IMM> __device__ __forceinline__ unsigned ldsU8(unsigned a) {
+    unsigned v;
+    asm volatile("ld.shared.u8 %0, [%1+%2];" : "=r"(v) : "r"(a), "n"(IMM));
+    return v;
+}
+__device__ __forceinline__ unsigned ldsU16(unsigned a) {
+    unsigned v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void stsU8(unsigned a, unsigned v) { asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v)); }
+__device__ __forceinline__ void stsU16(unsigned a, unsigned v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "r"(v)); }
+
 __device__ __forceinline__ unsigned fastBase(int v) { return (unsigned)(v + 256) * 0xFFFF0001u + (512u << 16); }
 __device__ __forceinline__ unsigned fastE(int p, unsigned base) { return (unsigned)p * 0xFFFFu + base; }
 
 // Corner measure m (max over the 16 arcs of 9 contiguous ring pixels of min(v-p) resp. min(p-v)),
-// OpenCV fast_score.cpp cornerScore<16> without the threshold clamp.  `pre` = minThFAST + 256: the
+// OpenCV fast_score.cpp cornerScore<16> without the threshold clamp.  `pre2` = minThFAST + 256 in both halves: the
 // function returns -1 early when no two adjacent compass pixels are both darker / both brighter
 // than the threshold (an arc of 9 always holds two adjacent compass pixels), i.e. m <= minThFAST.
-__device__ __forceinline__ int fastMeasure(const uint8_t *p, unsigned pre) {
+__device__ __forceinline__ int fastMeasure(unsigned p, unsigned pre2) {
     constexpr int P = kTilePitch;
-    const unsigned base = fastBase(p[0]);
+    const unsigned base = fastBase((int)ldsU8<0>(p));
     unsigned e[16];
-    e[0] = fastE(p[3 * P], base); e[4] = fastE(p[3], base); e[8] = fastE(p[-3 * P], base); e[12] = fastE(p[-3], base);
+    e[0] = fastE(ldsU8<3 * P>(p), base); e[4] = fastE(ldsU8<3>(p), base);
+    e[8] = fastE(ldsU8<-3 * P>(p), base); e[12] = fastE(ldsU8<-3>(p), base);
     {
         const unsigned pm = __vimax3_u16x2(__vminu2(e[0], e[4]), __vminu2(e[4], e[8]),
                                            __vmaxu2(__vminu2(e[8], e[12]), __vminu2(e[12], e[0])));
-        if ((pm & 0xffffu) <= pre && (pm >> 16) <= pre) return -1;
+        if (__vmaxu2(pm, pre2) == pre2) return -1;
     }
-    e[1] = fastE(p[3 * P + 1], base);   e[2] = fastE(p[2 * P + 2], base);   e[3] = fastE(p[P + 3], base);
-    e[5] = fastE(p[-P + 3], base);      e[6] = fastE(p[-2 * P + 2], base);  e[7] = fastE(p[-3 * P + 1], base);
-    e[9] = fastE(p[-3 * P - 1], base);  e[10] = fastE(p[-2 * P - 2], base); e[11] = fastE(p[-P - 3], base);
-    e[13] = fastE(p[P - 3], base);      e[14] = fastE(p[2 * P - 2], base);  e[15] = fastE(p[3 * P - 1], base);
+    e[1] = fastE(ldsU8<3 * P + 1>(p), base);   e[2] = fastE(ldsU8<2 * P + 2>(p), base);   e[3] = fastE(ldsU8<P + 3>(p), base);
+    e[5] = fastE(ldsU8<-P + 3>(p), base);      e[6] = fastE(ldsU8<-2 * P + 2>(p), base);  e[7] = fastE(ldsU8<-3 * P + 1>(p), base);
+    e[9] = fastE(ldsU8<-3 * P - 1>(p), base);  e[10] = fastE(ldsU8<-2 * P - 2>(p), base); e[11] = fastE(ldsU8<-P - 3>(p), base);
+    e[13] = fastE(ldsU8<P - 3>(p), base);      e[14] = fastE(ldsU8<2 * P - 2>(p), base);  e[15] = fastE(ldsU8<3 * P - 1>(p), base);
     unsigned lo3[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) lo3[k] = __vimin3_u16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
@@ -159,7 +180,7 @@ __device__ __forceinline__ int fastMeasure(const uint8_t *p, unsigned pre) {
 // score tile holds m for m > minThFAST and 0 elsewhere (and outside the detection area).
 __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
     __shared__ __align__(16) uint8_t tile[(kCellMax + 6) * kTilePitch];
-    __shared__ __align__(16) uint8_t score[(kCellMax + 2) * kScorePitch];
+    __shared__ __align__(16) uint8_t score[(kCellMax + 2) * kTilePitch];
     __shared__ uint16_t corners[(kFastThreads / 32) * kFastWarpCap];      // per warp: y<<6 | x of pixels with m > minThFAST
     __shared__ uint16_t maxima[(kFastThreads / 32) * (kFastWarpCap / 2)];  // per warp: strict local maxima among them
     const int f = blockIdx.y, tid = threadIdx.x;
@@ -196,29 +217,49 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
             for (int x = lane; x < tw; x += 32) tile[y * kTilePitch + x] = row[x];
         }
     }
-    for (int i = tid; i < (dh + 2) * (kScorePitch / 4); i += kFastThreads) reinterpret_cast<uint32_t *>(score)[i] = 0;
+    // score tile border (the detection area itself is fully written by phase 1)
+    for (int i = tid; i < 2 * (dw + 2); i += kFastThreads) {
+        const int r = i >= dw + 2;
+        score[(r ? (dh + 1) * kTilePitch : 0) + i - r * (dw + 2)] = 0;
+    }
+    for (int i = tid; i < 2 * dh; i += kFastThreads) {
+        const int r = i >= dh;
+        score[(i - r * dh + 1) * kTilePitch + (r ? dw + 1 : 0)] = 0;
+    }
     __syncthreads();
     const int minTh = G.minTh, iniTh = G.iniTh;
-    const unsigned magic = (1u << 18) / (unsigned)dw + 1;   // i / dw for i < 4096, dw <= 64
-    // ---- phase 1: measure of every detection pixel; corners at minThFAST -> score tile + the warp's own list
-    // (lists are per warp with the fill count in a register: no shared atomics, no shuffles)
+    // ---- phase 1: measure of every detection pixel -> score tile (same pitch as the image tile, so one
+    // offset `off` = y * pitch + x addresses both); corners at minThFAST go to the warp's own list
+    // (fill count in a register: no shared atomics, no shuffles).  Pixel i = y * dw + x advances by
+    // kFastThreads per iteration; (x, off) are updated incrementally.
     const int lane = tid & 31, wid = tid >> 5;
     const unsigned ltMask = (1u << lane) - 1u;
     uint16_t *myCorners = corners + wid * kFastWarpCap;
+    const float rdw = __fdividef(1.0f, (float)dw);
+    const int stepY = (int)((kFastThreads + 0.5f) * rdw), stepX = kFastThreads - stepY * dw;
+    const int stepOff = stepY * kTilePitch + stepX, wrapOff = kTilePitch - dw;
+    int x, off;
+    {
+        const int y = (int)(((float)tid + 0.5f) * rdw);
+        x = tid - y * dw; off = y * kTilePitch + x;
+    }
+    const unsigned centre = smemAddr(tile + 3 * kTilePitch + 3 + ox);
+    const unsigned sc0a = smemAddr(score + kTilePitch + 1);
+    uint8_t *sc0 = score + kTilePitch + 1;
+    const unsigned pre2 = ((unsigned)minTh + 256u) * 0x10001u;
+    const unsigned cornersAt = smemAddr(myCorners);
     int n1 = 0;
-    for (int i0 = 0; i0 < npx; i0 += kFastThreads) {
-        const int i = i0 + tid;
-        bool corner = false;
-        int y = 0, x = 0;
+    for (int i = tid; i - lane < npx; i += kFastThreads) {
+        int m = -1;
         if (i < npx) {
-            y = (int)(((unsigned)i * magic) >> 18); x = i - y * dw;
-            const int m = fastMeasure(&tile[(y + 3) * kTilePitch + ox + x + 3], (unsigned)minTh + 256u);
-            corner = m > minTh;
-            if (corner) score[(y + 1) * kScorePitch + x + 1] = (uint8_t)m;
+            m = fastMeasure(centre + off, pre2);
+            stsU8(sc0a + off, (unsigned)max(m, 0));
         }
-        const unsigned mask = __ballot_sync(0xffffffffu, corner);
-        if (corner) myCorners[n1 + __popc(mask & ltMask)] = (uint16_t)((y << 6) | x);
+        const unsigned mask = __ballot_sync(0xffffffffu, m > minTh);
+        if (m > minTh) stsU16(cornersAt + 2 * (n1 + __popc(mask & ltMask)), (unsigned)off);
         n1 += __popc(mask);
+        x += stepX; off += stepOff;
+        if (x >= dw) { x -= dw; off += wrapOff; }
     }
     __syncthreads();
     // ---- phase 2: strict local maxima of m among the warp's corners
@@ -227,18 +268,18 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
     for (int k0 = 0; k0 < n1; k0 += 32) {
         const int k = k0 + lane;
         bool ismax = false;
-        uint16_t yx = 0;
+        uint16_t o = 0;
         if (k < n1) {
-            yx = myCorners[k];
-            const uint8_t *sc = &score[((yx >> 6) + 1) * kScorePitch + (yx & 63) + 1];
+            o = myCorners[k];
+            const uint8_t *sc = sc0 + o;
             const int m = sc[0];
-            const int nb = max(max(max(sc[-1], sc[1]), max(sc[-kScorePitch - 1], sc[-kScorePitch])),
-                               max(max(sc[-kScorePitch + 1], sc[kScorePitch - 1]), max(sc[kScorePitch], sc[kScorePitch + 1])));
+            const int nb = max(max(max(sc[-1], sc[1]), max(sc[-kTilePitch - 1], sc[-kTilePitch])),
+                               max(max(sc[-kTilePitch + 1], sc[kTilePitch - 1]), max(sc[kTilePitch], sc[kTilePitch + 1])));
             ismax = nb < m;
             any |= ismax && m > iniTh;
         }
         const unsigned mask = __ballot_sync(0xffffffffu, ismax);
-        if (ismax) myMaxima[n2 + __popc(mask & ltMask)] = yx;
+        if (ismax) myMaxima[n2 + __popc(mask & ltMask)] = o;
         n2 += __popc(mask);
     }
     // ---- threshold fallback: iniThFAST unless nothing survives in the cell (src/ORBextractor.cc:764-770)
@@ -248,11 +289,11 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
     for (int k0 = 0; k0 < n2; k0 += 32) {
         const int k = k0 + lane;
         bool keep = false;
-        int y = 0, x = 0, m = 0;
+        int y = 0, x = 0, m = 0;   // (x shadows the phase-1 counter on purpose: it is dead here)
         if (k < n2) {
-            const int yx = myMaxima[k];
-            y = yx >> 6; x = yx & 63;
-            m = score[(y + 1) * kScorePitch + x + 1];
+            const int o = myMaxima[k];
+            y = (o * ((1 << 20) / kTilePitch + 1)) >> 20; x = o - y * kTilePitch;   // exact for o < 2^13
+            m = sc0[o];
             keep = m > t;
         }
         const unsigned mask = __ballot_sync(0xffffffffu, keep);

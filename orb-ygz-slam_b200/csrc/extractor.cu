@@ -206,7 +206,12 @@ struct Extractor {
     DevBuffers B;
     long long blurOff[kMaxLevels]; int blurPitch[kMaxLevels]; long long blurSlab = 0;
     // device workspace (grown on demand)
-    uint8_t *dIn = nullptr; size_t inBytes = 0;
+    // host-input staging: two slots filled by the upload stream while the compute stream works on the other
+    uint8_t *dIn[2] = {}; size_t inBytes[2] = {};
+    cudaStream_t h2d = nullptr, d2h = nullptr;
+    cudaEvent_t inReady[2] = {}, inFree[2] = {}, outReady[2] = {}, outFree[2] = {};
+    unsigned inSeq = 0, outSeq = 0;
+    int pipeFrames = 128;      // frames per pipelined chunk of a host-input call (0: one chunk per max_batch)
     uint8_t *dPyr = nullptr; size_t pyrBytes = 0;
     uint8_t *dBlur = nullptr; size_t blurBytes = 0;
     int2 *dTabs = nullptr; size_t tabBytes = 0;
@@ -214,7 +219,8 @@ struct Extractor {
     uint16_t *dNodeOf = nullptr; size_t nodeBytes = 0;
     uint32_t *dKept = nullptr; size_t keptBytes = 0;
     int *dCounts = nullptr;   // [maxBatch][kMaxLevels] x2 (cand, kept) + status
-    int32_t *dOutCounts = nullptr; ygzorb_keypoint *dOutKps = nullptr; uint8_t *dOutDesc = nullptr;
+    // host-output staging, two slots drained by the download stream
+    int32_t *dOutCounts[2] = {}; ygzorb_keypoint *dOutKps[2] = {}; uint8_t *dOutDesc[2] = {};
     size_t outCap = 0;  // records per frame the dOut* buffers hold
     int lastFrames = 0; bool lastInDevice = false; bool stagesValid = false;
     const uint8_t *lastIn = nullptr; long long lastInFrameStride = 0;
@@ -251,7 +257,9 @@ static int ensureGeometry(Extractor *ex, int w, int h, int stride, int nFrames, 
     const size_t nb = (size_t)ex->maxBatch;
     (void)nFrames;
     int rc;
-    if (!inDevice && (rc = growBuf(ex->dIn, ex->inBytes, nb * (size_t)w * h + 64))) return rc;
+    if (!inDevice)
+        for (int sl = 0; sl < 2; sl++)
+            if ((rc = growBuf(ex->dIn[sl], ex->inBytes[sl], nb * (size_t)w * h + 64))) return rc;
     if ((rc = growBuf(ex->dPyr, ex->pyrBytes, nb * (size_t)ex->G.slabBytes))) return rc;
     if ((rc = growBuf(ex->dBlur, ex->blurBytes, nb * (size_t)ex->blurSlab))) return rc;
     if ((rc = growBuf(ex->dCand, ex->candBytes, nb * (size_t)ex->G.candPerFrame * sizeof(uint2)))) return rc;
@@ -266,34 +274,52 @@ static int ensureGeometry(Extractor *ex, int w, int h, int stride, int nFrames, 
 }
 
 static int ensureOut(Extractor *ex, int cap) {
-    if ((size_t)cap <= ex->outCap && ex->dOutKps) return 0;
+    if ((size_t)cap <= ex->outCap && ex->dOutKps[0]) return 0;
     YGZ_CUDA(cudaStreamSynchronize(ex->stream));
-    if (ex->dOutKps) YGZ_CUDA(cudaFree(ex->dOutKps));
-    if (ex->dOutDesc) YGZ_CUDA(cudaFree(ex->dOutDesc));
-    ex->dOutKps = nullptr; ex->dOutDesc = nullptr; ex->outCap = 0;
-    YGZ_CUDA(cudaMalloc((void **)&ex->dOutKps, (size_t)ex->maxBatch * cap * sizeof(ygzorb_keypoint)));
-    YGZ_CUDA(cudaMalloc((void **)&ex->dOutDesc, (size_t)ex->maxBatch * cap * 32));
+    YGZ_CUDA(cudaStreamSynchronize(ex->d2h));
+    for (int sl = 0; sl < 2; sl++) {
+        if (ex->dOutKps[sl]) YGZ_CUDA(cudaFree(ex->dOutKps[sl]));
+        if (ex->dOutDesc[sl]) YGZ_CUDA(cudaFree(ex->dOutDesc[sl]));
+        ex->dOutKps[sl] = nullptr; ex->dOutDesc[sl] = nullptr;
+    }
+    ex->outCap = 0;
+    for (int sl = 0; sl < 2; sl++) {
+        YGZ_CUDA(cudaMalloc((void **)&ex->dOutKps[sl], (size_t)ex->maxBatch * cap * sizeof(ygzorb_keypoint)));
+        YGZ_CUDA(cudaMalloc((void **)&ex->dOutDesc[sl], (size_t)ex->maxBatch * cap * 32));
+    }
     ex->outCap = cap;
     return 0;
 }
 
-// Upload (host input) or alias (device input) level 0 of a chunk of frames.
-static int bindInput(Extractor *ex, const uint8_t *frames, int n, int w, int h, int stride, size_t frameStride, bool inDevice) {
+// Host input: enqueue the upload of a chunk of frames into the next staging slot on the upload stream
+// (which first waits until the kernels that last read that slot are done).  Returns the slot.
+static int uploadInput(Extractor *ex, const uint8_t *frames, int n, int w, int h, int stride, size_t frameStride, int *slotOut) {
+    const int sl = (int)(ex->inSeq++ & 1u);
+    uint8_t *dst = ex->dIn[sl];
+    YGZ_CUDA(cudaStreamWaitEvent(ex->h2d, ex->inFree[sl], 0));
+    // staging buffer is continuous: pitch == w (the geometry was built with stride == w for host input)
+    if (stride == w && frameStride == (size_t)w * h) {
+        YGZ_CUDA(cudaMemcpyAsync(dst, frames, (size_t)n * w * h, cudaMemcpyHostToDevice, ex->h2d));
+    } else if (frameStride == (size_t)stride * h) {
+        YGZ_CUDA(cudaMemcpy2DAsync(dst, w, frames, stride, w, (size_t)h * n, cudaMemcpyHostToDevice, ex->h2d));
+    } else {
+        for (int f = 0; f < n; f++)
+            YGZ_CUDA(cudaMemcpy2DAsync(dst + (size_t)f * w * h, w, frames + f * frameStride, stride, w, h,
+                                       cudaMemcpyHostToDevice, ex->h2d));
+    }
+    YGZ_CUDA(cudaEventRecord(ex->inReady[sl], ex->h2d));
+    *slotOut = sl;
+    return 0;
+}
+
+// Make level 0 of the chunk visible to the kernels: alias device input, or wait for the slot's upload.
+static int bindInput(Extractor *ex, const uint8_t *frames, int w, int h, size_t frameStride, bool inDevice, int slot) {
     if (inDevice) {
         ex->B.in = frames; ex->B.inFrameStride = (long long)frameStride;
         return 0;
     }
-    // staging buffer is continuous: pitch == w (the geometry was built with stride == w for host input)
-    if (stride == w && frameStride == (size_t)w * h) {
-        YGZ_CUDA(cudaMemcpyAsync(ex->dIn, frames, (size_t)n * w * h, cudaMemcpyHostToDevice, ex->stream));
-    } else if (frameStride == (size_t)stride * h) {
-        YGZ_CUDA(cudaMemcpy2DAsync(ex->dIn, w, frames, stride, w, (size_t)h * n, cudaMemcpyHostToDevice, ex->stream));
-    } else {
-        for (int f = 0; f < n; f++)
-            YGZ_CUDA(cudaMemcpy2DAsync(ex->dIn + (size_t)f * w * h, w, frames + f * frameStride, stride, w, h,
-                                       cudaMemcpyHostToDevice, ex->stream));
-    }
-    ex->B.in = ex->dIn; ex->B.inFrameStride = (long long)w * h;
+    YGZ_CUDA(cudaStreamWaitEvent(ex->stream, ex->inReady[slot], 0));
+    ex->B.in = ex->dIn[slot]; ex->B.inFrameStride = (long long)w * h;
     return 0;
 }
 
@@ -304,16 +330,13 @@ static int runPyramid(Extractor *ex, int n) {
 
 #define YGZ_MARK(i) do { if (ex->profiling) YGZ_CUDA(cudaEventRecord(ex->ev[i], ex->stream)); } while (0)
 
-static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int h, int stride, size_t frameStride,
-                        unsigned flags, int cap, int32_t *counts, ygzorb_keypoint *kps, uint8_t *desc) {
+// Kernels of one chunk (its input already uploaded into `slot` when it comes from the host).
+static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int h, size_t frameStride,
+                        unsigned flags, int cap, int slot, int32_t *counts, ygzorb_keypoint *kps, uint8_t *desc) {
     const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
-    const int gstride = inDev ? stride : w;
-    int rc = ensureGeometry(ex, w, h, gstride, n, inDev);
-    if (rc) return rc;
-    if (cap < ex->G.keptCap) { setError("cap is smaller than ygzorb_extractor_max_keypoints()"); return YGZORB_E_CAPACITY; }
-    if (!outDev && (rc = ensureOut(ex, cap))) return rc;
+    int rc;
     YGZ_MARK(0);
-    if ((rc = bindInput(ex, frames, n, w, h, stride, frameStride, inDev))) return rc;
+    if ((rc = bindInput(ex, frames, w, h, frameStride, inDev, slot))) return rc;
     YGZ_CUDA(cudaMemsetAsync(ex->dCounts, 0, (2 * (size_t)ex->maxBatch * kMaxLevels + 1) * sizeof(int), ex->stream));
     YGZ_MARK(1);
     runPyramid(ex, n);
@@ -324,15 +347,21 @@ static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int 
     YGZ_MARK(4);
     ex->launches += launchBlur(ex->G, ex->B, n, ex->stream);
     YGZ_MARK(5);
-    int32_t *oc = outDev ? counts : ex->dOutCounts;
-    ygzorb_keypoint *ok = outDev ? kps : ex->dOutKps;
-    uint8_t *od = outDev ? desc : ex->dOutDesc;
+    const int os = outDev ? 0 : (int)(ex->outSeq++ & 1u);
+    int32_t *oc = outDev ? counts : ex->dOutCounts[os];
+    ygzorb_keypoint *ok = outDev ? kps : ex->dOutKps[os];
+    uint8_t *od = outDev ? desc : ex->dOutDesc[os];
+    if (!outDev) YGZ_CUDA(cudaStreamWaitEvent(ex->stream, ex->outFree[os], 0));
     ex->launches += launchDescribe(ex->G, ex->B, n, cap, oc, ok, od, ex->stream);
     YGZ_MARK(6);
-    if (!outDev) {
-        YGZ_CUDA(cudaMemcpyAsync(counts, oc, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, ex->stream));
-        YGZ_CUDA(cudaMemcpyAsync(kps, ok, (size_t)n * cap * sizeof(ygzorb_keypoint), cudaMemcpyDeviceToHost, ex->stream));
-        YGZ_CUDA(cudaMemcpyAsync(desc, od, (size_t)n * cap * 32, cudaMemcpyDeviceToHost, ex->stream));
+    if (!inDev) YGZ_CUDA(cudaEventRecord(ex->inFree[slot], ex->stream));   // IC_Angle was the last reader of level 0
+    if (!outDev) {   // drain on the download stream so that the next chunk's kernels overlap it
+        YGZ_CUDA(cudaEventRecord(ex->outReady[os], ex->stream));
+        YGZ_CUDA(cudaStreamWaitEvent(ex->d2h, ex->outReady[os], 0));
+        YGZ_CUDA(cudaMemcpyAsync(counts, oc, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, ex->d2h));
+        YGZ_CUDA(cudaMemcpyAsync(kps, ok, (size_t)n * cap * sizeof(ygzorb_keypoint), cudaMemcpyDeviceToHost, ex->d2h));
+        YGZ_CUDA(cudaMemcpyAsync(desc, od, (size_t)n * cap * 32, cudaMemcpyDeviceToHost, ex->d2h));
+        YGZ_CUDA(cudaEventRecord(ex->outFree[os], ex->d2h));
     }
     YGZ_MARK(7);
     YGZ_CUDA(cudaGetLastError());
@@ -409,7 +438,13 @@ int ygzorb_extractor_create(const ygzorb_params *params, int max_w, int max_h, i
     if (rc) { delete ex; return rc; }
     cudaError_t e = cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaMalloc((void **)&ex->dCounts, (2 * (size_t)max_batch * kMaxLevels + 1) * sizeof(int));
-    if (e == cudaSuccess) e = cudaMalloc((void **)&ex->dOutCounts, (size_t)max_batch * sizeof(int32_t));
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ex->h2d, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ex->d2h, cudaStreamNonBlocking);
+    for (int sl = 0; sl < 2 && e == cudaSuccess; sl++) {
+        e = cudaMalloc((void **)&ex->dOutCounts[sl], (size_t)max_batch * sizeof(int32_t));
+        cudaEvent_t *evs[] = {&ex->inReady[sl], &ex->inFree[sl], &ex->outReady[sl], &ex->outFree[sl]};
+        for (cudaEvent_t *pe : evs) if (e == cudaSuccess) e = cudaEventCreateWithFlags(pe, cudaEventDisableTiming);
+    }
     for (int i = 0; i < 8 && e == cudaSuccess; i++) e = cudaEventCreate(&ex->ev[i]);
     if (e != cudaSuccess) { ygzorb_extractor_destroy((ygzorb_extractor *)ex); return cudaFail(e, "extractor_create", __FILE__, __LINE__); }
     *out = (ygzorb_extractor *)ex;
@@ -420,12 +455,17 @@ void ygzorb_extractor_destroy(ygzorb_extractor *h) {
     Extractor *ex = (Extractor *)h;
     if (!ex) return;
     cudaSetDevice(ex->device);
-    if (ex->stream) cudaStreamSynchronize(ex->stream);
-    void *bufs[] = {ex->dIn, ex->dPyr, ex->dBlur, ex->dTabs, ex->dCand, ex->dNodeOf, ex->dKept, ex->dCounts,
-                    ex->dOutCounts, ex->dOutKps, ex->dOutDesc};
+    cudaStream_t streams[] = {ex->h2d, ex->stream, ex->d2h};
+    for (cudaStream_t st : streams) if (st) cudaStreamSynchronize(st);
+    void *bufs[] = {ex->dIn[0], ex->dIn[1], ex->dPyr, ex->dBlur, ex->dTabs, ex->dCand, ex->dNodeOf, ex->dKept, ex->dCounts,
+                    ex->dOutCounts[0], ex->dOutCounts[1], ex->dOutKps[0], ex->dOutKps[1], ex->dOutDesc[0], ex->dOutDesc[1]};
     for (void *p : bufs) if (p) cudaFree(p);
     for (int i = 0; i < 8; i++) if (ex->ev[i]) cudaEventDestroy(ex->ev[i]);
-    if (ex->stream) cudaStreamDestroy(ex->stream);
+    for (int sl = 0; sl < 2; sl++) {
+        cudaEvent_t evs[] = {ex->inReady[sl], ex->inFree[sl], ex->outReady[sl], ex->outFree[sl]};
+        for (cudaEvent_t e : evs) if (e) cudaEventDestroy(e);
+    }
+    for (cudaStream_t st : streams) if (st) cudaStreamDestroy(st);
     delete ex;
 }
 
@@ -492,13 +532,28 @@ int ygzorb_extract_batch(ygzorb_extractor *h, const uint8_t *frames, int n_frame
         return 0;
     }
     if (frame_stride == 0) frame_stride = (size_t)stride * hgt;
-    for (int f0 = 0; f0 < n_frames; f0 += ex->maxBatch) {
-        const int n = std::min(ex->maxBatch, n_frames - f0);
-        // chunks reuse the workspace: a host-output chunk must be drained before the next one starts
-        rc = extractChunk(ex, frames + (size_t)f0 * frame_stride, n, w, hgt, stride, frame_stride, flags, cap,
+    const bool inDev = flags & YGZORB_IN_DEVICE;
+    // Chunking.  Device input: chunks of max_batch (the workspace size).  Host input: chunks of the pipeline
+    // size, the upload of chunk k+1 (upload stream, other staging slot) overlapping the kernels of chunk k and
+    // the download of chunk k-1 (download stream); YGZORB_KEEP_STAGES asks for one chunk so that the stage
+    // taps cover every frame of the call.
+    int chunk = ex->maxBatch;
+    if (!inDev && !(flags & YGZORB_KEEP_STAGES) && !ex->profiling && ex->pipeFrames > 0) chunk = std::min(chunk, ex->pipeFrames);
+    if ((rc = ensureGeometry(ex, w, hgt, inDev ? stride : w, std::min(chunk, n_frames), inDev))) return rc;
+    if (cap < ex->G.keptCap) { setError("cap is smaller than ygzorb_extractor_max_keypoints()"); return YGZORB_E_CAPACITY; }
+    if (!outDev && (rc = ensureOut(ex, cap))) return rc;
+    int slot = 0, nextSlot = 0;
+    if (!inDev && (rc = uploadInput(ex, frames, std::min(chunk, n_frames), w, hgt, stride, frame_stride, &nextSlot))) return rc;
+    for (int f0 = 0; f0 < n_frames; f0 += chunk) {
+        const int n = std::min(chunk, n_frames - f0);
+        slot = nextSlot;
+        if (!inDev && f0 + n < n_frames) {   // enqueue the next upload before this chunk's kernels
+            const int n2 = std::min(chunk, n_frames - f0 - n);
+            if ((rc = uploadInput(ex, frames + (size_t)(f0 + n) * frame_stride, n2, w, hgt, stride, frame_stride, &nextSlot))) return rc;
+        }
+        rc = extractChunk(ex, frames + (size_t)f0 * frame_stride, n, w, hgt, frame_stride, flags, cap, slot,
                           counts + f0, keypoints + (size_t)f0 * cap, desc + (size_t)f0 * cap * 32);
         if (rc) return rc;
-        if (!outDev && f0 + n < n_frames) YGZ_CUDA(cudaStreamSynchronize(ex->stream));
     }
     if (!(flags & YGZORB_NO_SYNC)) return ygzorb_extractor_sync(h);
     return 0;
@@ -515,8 +570,11 @@ int ygzorb_compute_pyramid_batch(ygzorb_extractor *h, const uint8_t *frames, int
     if (frame_stride == 0) frame_stride = (size_t)stride * hgt;
     const bool inDev = flags & YGZORB_IN_DEVICE;
     if ((rc = ensureGeometry(ex, w, hgt, inDev ? stride : w, n_frames, inDev))) return rc;
-    if ((rc = bindInput(ex, frames, n_frames, w, hgt, stride, frame_stride, inDev))) return rc;
+    int slot = 0;
+    if (!inDev && (rc = uploadInput(ex, frames, n_frames, w, hgt, stride, frame_stride, &slot))) return rc;
+    if ((rc = bindInput(ex, frames, w, hgt, frame_stride, inDev, slot))) return rc;
     runPyramid(ex, n_frames);
+    if (!inDev) YGZ_CUDA(cudaEventRecord(ex->inFree[slot], ex->stream));
     YGZ_CUDA(cudaGetLastError());
     ex->lastFrames = n_frames; ex->stagesValid = false;
     if (!(flags & YGZORB_NO_SYNC)) YGZ_CUDA(cudaStreamSynchronize(ex->stream));
@@ -604,9 +662,18 @@ int ygzorb_extractor_sync(ygzorb_extractor *h) {
     if (!ex) return argFail("null extractor");
     YGZ_CUDA(cudaSetDevice(ex->device));
     YGZ_CUDA(cudaStreamSynchronize(ex->stream));
+    YGZ_CUDA(cudaStreamSynchronize(ex->d2h));      // host outputs of the last call(s) are complete after this
     int rc = finishProfile(ex);
     if (rc) return rc;
     return ex->B.status ? checkStatus(ex) : 0;
+}
+
+int ygzorb_extractor_set_pipeline(ygzorb_extractor *h, int frames_per_chunk) {
+    Extractor *ex = (Extractor *)h;
+    if (!ex) return argFail("null extractor");
+    if (frames_per_chunk < 0) return argFail("frames_per_chunk < 0");
+    ex->pipeFrames = frames_per_chunk;
+    return 0;
 }
 
 void *ygzorb_extractor_stream(ygzorb_extractor *h) { return h ? (void *)((Extractor *)h)->stream : nullptr; }

@@ -175,6 +175,9 @@ class Extractor:
     def launch_count(self):
         return int(lib().ygzorb_extractor_launch_count(self.h))
 
+    def set_pipeline(self, frames_per_chunk):
+        check(lib().ygzorb_extractor_set_pipeline(self.h, int(frames_per_chunk)))
+
     def set_profiling(self, on):
         check(lib().ygzorb_extractor_set_profiling(self.h, int(on)))
 

@@ -130,3 +130,46 @@ def test_strided_input_and_repeatability():
     b = ex.extract(view)
     assert a[0].tobytes() == b[0].tobytes() and np.array_equal(a[1], b[1])
     ex.close()
+
+
+@pytest.mark.parametrize("pipe,max_batch", [(2, 16), (3, 4), (0, 16), (128, 16)])
+def test_pipelined_host_chunks(pipe, max_batch):
+    """Host-input calls split into pipelined chunks (upload / kernels / download on three streams, two staging
+    slots each way) must give exactly the per-frame results, also over back-to-back NO_SYNC calls that reuse
+    the slots while earlier work is still in flight."""
+    w, h = 320, 240
+    frames = np.stack([synth.textured_frame(w, h, 150 + i) if i % 3 else synth.mixed_frame(w, h, 150 + i) for i in range(11)])
+    p = O.params(500, 1.2, 8, 20, 7)
+    want = [O.extract(p, f) for f in frames]
+    ex = Y.Extractor(500, 1.2, 8, 20, 7, max_batch=max_batch)
+    ex.set_pipeline(pipe)
+    outs = ex.extract_batch(frames)
+    for f in range(len(frames)):
+        assert outs[f][0].tobytes() == want[f][0].tobytes(), "frame %d" % f
+        assert np.array_equal(outs[f][1], want[f][1])
+    # three un-synchronised calls into separate host buffers, then one sync
+    cap = ex.max_keypoints(w, h)
+    bufs = []
+    for r in range(3):
+        sel = np.ascontiguousarray(frames[r:r + 7])
+        counts = np.zeros(7, np.int32); kps = np.zeros((7, cap), Y.KP_DTYPE); desc = np.zeros((7, cap, 32), np.uint8)
+        ex.extract_raw(sel.ctypes.data, 7, w, h, w, w * h, Y.NO_SYNC, cap, counts.ctypes.data, kps.ctypes.data, desc.ctypes.data)
+        bufs.append((sel, counts, kps, desc))
+    ex.sync()
+    for r, (_, counts, kps, desc) in enumerate(bufs):
+        for i in range(7):
+            assert kps[i, :counts[i]].tobytes() == want[r + i][0].tobytes(), (r, i)
+            assert np.array_equal(desc[i, :counts[i]], want[r + i][1])
+    ex.close()
+
+
+def test_keep_stages_covers_whole_call():
+    """YGZORB_KEEP_STAGES turns the upload pipelining off: the stage taps then hold every frame of the call."""
+    w, h = 200, 160
+    frames = np.stack([synth.textured_frame(w, h, 170 + i) for i in range(5)])
+    ex = Y.Extractor(300, max_batch=8)
+    ex.set_pipeline(2)
+    ex.extract_batch(frames, Y.KEEP_STAGES)
+    for f in range(5):
+        assert np.array_equal(ex.pyramid(f, w, h)[0], frames[f])
+    ex.close()
