@@ -184,19 +184,12 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
     __shared__ uint16_t corners[(kFastThreads / 32) * kFastWarpCap];      // per warp: y<<6 | x of pixels with m > minThFAST
     __shared__ uint16_t maxima[(kFastThreads / 32) * (kFastWarpCap / 2)];  // per warp: strict local maxima among them
     const int f = blockIdx.y, tid = threadIdx.x;
-    int level = 0;
-    while (level + 1 < G.nlevels && (int)blockIdx.x >= G.lv[level + 1].cellStart) level++;
+    // cell window (src/ORBextractor.cc:749-762) from the host-built cell table; detection area = window minus 3 px
+    const int2 ce = __ldg(B.tabs + G.cellTab + blockIdx.x);
+    const int level = ce.x >> 24, iniX = ce.x & 0xfff, iniY = (ce.x >> 12) & 0xfff;
+    const int dw = ce.y & 127, dh = (ce.y >> 7) & 127, cell = (int)((unsigned)ce.y >> 14);
+    const int tw = dw + 6, th = dh + 6;              // window size
     const LevelGeom &L = G.lv[level];
-    const int cell = blockIdx.x - L.cellStart;
-    const int ci = cell / L.nCols, cj = cell - ci * L.nCols;
-    // cell window (src/ORBextractor.cc:749-762); detection area = window minus 3 px
-    const int maxBX = L.w - kMinBorder, maxBY = L.h - kMinBorder;
-    const int iniY = kMinBorder + ci * L.hCell, iniX = kMinBorder + cj * L.wCell;
-    if (iniY >= maxBY - 3 || iniX >= maxBX - 6) return;
-    const int maxY = min(iniY + L.hCell + 6, maxBY), maxX = min(iniX + L.wCell + 6, maxBX);
-    const int tw = maxX - iniX, th = maxY - iniY;   // window size
-    const int dw = tw - 6, dh = th - 6;              // detection area size
-    if (dw <= 0 || dh <= 0) return;
     const int npx = dw * dh;
     const uint8_t *img = levelPtr(G, B, f, level) + (long long)iniY * L.pitch;
     // ---- tile load: aligned 32-bit words when the level allows it; tile column c <-> image x = xa + c
@@ -204,9 +197,9 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
     const int xa = aligned ? (iniX & ~3) : iniX, ox = iniX - xa;
     if (aligned) {
         const int nw = (ox + tw + 3) >> 2;           // words per row (<= 19)
-        const unsigned wmagic = (1u << 16) / (unsigned)nw + 1;
+        const float rnw = __fdividef(1.0f, (float)nw);   // (i + 0.5) / nw is never within rounding error of an integer
         for (int i = tid; i < nw * th; i += kFastThreads) {
-            const int y = (int)(((unsigned)i * wmagic) >> 16), wq = i - y * nw;
+            const int y = (int)(((float)i + 0.5f) * rnw), wq = i - y * nw;
             *reinterpret_cast<uint32_t *>(&tile[y * kTilePitch + 4 * wq]) =
                 __ldg(reinterpret_cast<const uint32_t *>(img + (long long)y * L.pitch + xa) + wq);
         }
@@ -847,20 +840,23 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(const __grid_const
     const LevelGeom &L = G.lv[level];
     const uint32_t xyr = B.kept[(long long)f * G.keptCap + L.keptOff + k];
     const int x = xyr & 0xfff, y = (xyr >> 12) & 0xfff;
-    // ---- IC_Angle: lane <-> column u = lane-15, rows v = -15..15 limited by umax[|v|]
+    // ---- IC_Angle (:79-109): lane <-> column u = lane-15; the rows of the circular patch that hold column u
+    // are |v| <= vmaxOfU[|u|], taken in +-v pairs like the reference (integer sums: order-free)
     const uint8_t *c0 = levelPtr(G, B, f, level) + (long long)y * L.pitch + x;
     int m10 = 0, m01 = 0;
     const int u = lane - kHalfPatch;
     if (lane < 31) {
-        const int au = abs(u);
-#pragma unroll 1
-        for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
-            if (au <= G.umax[abs(v)]) {
-                const int I = c0[(long long)v * L.pitch + u];
-                m10 += u * I;
-                m01 += v * I;
-            }
+        const int vmax = G.vmaxOfU[abs(u)];
+        const uint8_t *up = c0 + u, *dn = up;
+        int sum = *up;
+#pragma unroll 4
+        for (int v = 1; v <= vmax; v++) {
+            up -= L.pitch; dn += L.pitch;
+            const int a = *dn, b = *up;
+            sum += a + b;
+            m01 += v * (a - b);
         }
+        m10 = u * sum;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {

@@ -115,9 +115,14 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
     memset(&G, 0, sizeof G);
     G.nlevels = P.nlevels; G.w = w; G.h = h; G.iniTh = P.iniThFAST; G.minTh = P.minThFAST;
     for (int v = 0; v < 16; v++) G.umax[v] = T.umax[v];
+    for (int a = 0; a < 16; a++) {
+        G.vmaxOfU[a] = 0;
+        for (int v = 1; v <= 15; v++) G.vmaxOfU[a] += a <= T.umax[v];
+    }
     tabs.clear();
     long long off = 0, candOff = 0, bOff = 0;
     int cells = 0, tiles = 0, keptOff = 0;
+    std::vector<int2> cellTab;
     for (int l = 0; l < P.nlevels; l++) {
         LevelGeom &L = G.lv[l];
         L.w = cvRoundF((float)w * T.invScale[l]);   // :1131-1133, from LEVEL-0 dims
@@ -151,7 +156,6 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
             L.wCell = (int)std::ceil(width / nCols);
             L.hCell = (int)std::ceil(height / nRows);
             if (L.wCell > 64 || L.hCell > 64) return argFail("internal: FAST cell larger than 64 px");
-            cells += nCols * nRows;
             // NMS leaves at most one survivor per 2x2 block of a cell's detection area
             long long cap = 0;
             for (int i = 0; i < nRows; i++) {
@@ -163,7 +167,13 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
                     const int iniX = kMinBorder + j * L.wCell;
                     if (iniX >= maxBX - 6) continue;
                     const int dw = std::min(iniX + L.wCell + 6, maxBX) - iniX - 6;
-                    if (dw > 0) cap += (long long)((dw + 1) / 2) * ((dh + 1) / 2);
+                    if (dw <= 0) continue;
+                    cap += (long long)((dw + 1) / 2) * ((dh + 1) / 2);
+                    int2 ce;
+                    ce.x = iniX | (iniY << 12) | (l << 24);
+                    ce.y = dw | (dh << 7) | ((i * nCols + j) << 14);
+                    cellTab.push_back(ce);
+                    cells++;
                 }
             }
             L.candCap = (int)cap;
@@ -184,6 +194,7 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
         tiles += L.tilesX * L.tilesY;
     }
     G.totalCells = cells; G.totalTiles = tiles;
+    G.cellTab = (int)tabs.size(); tabs.insert(tabs.end(), cellTab.begin(), cellTab.end());
     G.slabBytes = std::max(off, 256LL);
     G.candPerFrame = std::max(candOff, 32LL);
     G.keptCap = std::max(keptOff, 1);

@@ -41,12 +41,14 @@ struct FrameGeom {
     int nlevels;
     int w, h;
     int iniTh, minTh;
-    int totalCells, totalTiles;
+    int totalCells, totalTiles;   // totalCells: entries of the FAST cell table (cells with a non-empty detection area)
+    int cellTab;                  // offset of the cell table in DevBuffers::tabs (8-byte entries)
     int maxListCap;
     int keptCap;               // kept-list slots per frame (= max keypoints per frame)
     long long slabBytes;       // pyramid slab per frame (levels >= 1)
     long long candPerFrame;    // candidate slots per frame
     int umax[16];
+    int vmaxOfU[16];   // rows |v| <= vmaxOfU[|u|] of the circular patch hold column u (umax is non-increasing)
     LevelGeom lv[kMaxLevels];
 };
 
@@ -58,7 +60,7 @@ struct DevBuffers {
     long long blurSlab;
     long long blurOff[kMaxLevels];
     int blurPitch[kMaxLevels];
-    const int2 *tabs;          // resize tables
+    const int2 *tabs;          // resize tables + FAST cell table (x = iniX | iniY<<12 | level<<24, y = dw | dh<<7 | cell<<14)
     uint2 *cand;               // candidates: cand + f*candPerFrame + lv[l].candOff
     int *candCount;            // [frame][kMaxLevels]
     uint16_t *nodeOf;          // quadtree scratch, same indexing as cand
