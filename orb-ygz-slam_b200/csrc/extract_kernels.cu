@@ -17,7 +17,7 @@ namespace ygz {
 // Table entry X[dx] = {x0 | x1<<16, a0 | a1<<16}; Y[dy] = {y0 | y1<<16, b0 | b1<<16}.
 constexpr int kResizeRows = 4;   // destination rows per thread
 
-__global__ void __launch_bounds__(256) k_resize(const __grid_constant__ FrameGeom G, const DevBuffers B, int level) {
+__global__ void __launch_bounds__(256, 5) k_resize(const __grid_constant__ FrameGeom G, const DevBuffers B, int level) {
     const LevelGeom &D = G.lv[level];
     const LevelGeom &S = G.lv[level - 1];
     const int f = blockIdx.z;
@@ -618,7 +618,6 @@ int launchQuadtree(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStr
 // one launch covers all levels of all frames (tiles enumerated level-major).
 // Tile = kBlurTW x kBlurTH outputs per CTA (ygz_common.cuh); 256 threads = 64 column groups of 4 px x 4 row groups.
 constexpr int kBlurThreads = 256;
-constexpr int kBlurRawPitch = kBlurTW + 8;      // bytes; raw column c <-> image x = x0 - 4 + c (word aligned)
 constexpr int kBlurRawRows = kBlurTH + 6;
 
 __device__ __forceinline__ int reflect101(int p, int len) {
@@ -627,74 +626,73 @@ __device__ __forceinline__ int reflect101(int p, int len) {
     return p;
 }
 
+constexpr int kBlurRawPitch = kBlurTW + 32;     // bytes; raw column c <-> image x = x0 - 16 + c (16-byte aligned chunks)
+
+__device__ __forceinline__ void cpAsync16(void *smemDst, const void *gmemSrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smemDst)), "l"(gmemSrc));
+}
+
 __global__ void __launch_bounds__(kBlurThreads) k_blur(const __grid_constant__ FrameGeom G, const DevBuffers B) {
     __shared__ __align__(16) uint8_t raw[kBlurRawRows * kBlurRawPitch];
     __shared__ __align__(16) uint2 hs[kBlurRawRows * (kBlurTW / 4)];   // 4 x u16 horizontal sums
     const int f = blockIdx.y, tid = threadIdx.x;
-    int level = 0;
-    while (level + 1 < G.nlevels && (int)blockIdx.x >= G.lv[level + 1].tileStart) level++;
+    const int2 te = __ldg(B.tabs + G.tileTab + blockIdx.x);            // host-built tile table
+    const int level = te.x >> 24, x0 = te.x & 0xfff, y0 = (te.x >> 12) & 0xfff;
     const LevelGeom &L = G.lv[level];
-    const int t = blockIdx.x - L.tileStart;
-    const int tyI = t / L.tilesX, txI = t - tyI * L.tilesX;
-    const int x0 = txI * kBlurTW, y0 = tyI * kBlurTH;
     const uint8_t *img = levelPtr(G, B, f, level);
-    const bool aligned = ((L.pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(img) & 3) == 0);
-    // ---- stage the raw tile (+3 halo, REFLECT_101 about the true image edge).  Words that lie fully inside the
-    // image are aligned 32-bit loads (warp = row, lanes = words: no divisions, no divergence); the <= 3 words per
-    // row that straddle the image edge are assembled byte-wise by a separate, equally uniform loop.  One
-    // reflection is enough because the halo (<= 7 px) is shorter than the image; tiny or unaligned images take
-    // the generic path.
-    constexpr int kWords = kBlurRawPitch / 4;
-    const int lane = tid & 31, wid = tid >> 5;
+    // ---- stage the raw tile (rows y0-3 .. y0+34, columns x0-3 .. x0+258 needed; REFLECT_101 about the true image
+    // edge).  16-byte chunks that lie inside the image row go global -> shared with cp.async (no registers, all in
+    // flight at once); the columns left over at the image's left/right edge (<= 3 + 18 per row) are reflected
+    // byte-wise.  Tiny or 16-byte-unaligned levels take the generic byte path.
+    constexpr int kChunks = kBlurRawPitch / 16;   // 18
+    const bool aligned = ((L.pitch & 15) == 0) && ((reinterpret_cast<uintptr_t>(img) & 15) == 0);
     if (aligned && L.w >= 8 && L.h >= 8) {
-        const int wqLo = x0 == 0 ? 1 : 0;
-        const int wqHi = max(wqLo, min(kWords, (L.w - x0 + 4) >> 2));   // words with x + 3 < w
-        for (int r = wid; r < kBlurRawRows; r += kBlurThreads / 32) {
-            int sy = abs(y0 + r - 3);
-            sy = max(min(sy, 2 * (L.h - 1) - sy), 0);
-            const uint32_t *row = reinterpret_cast<const uint32_t *>(img + (long long)sy * L.pitch + x0 - 4);
-            for (int wq = wqLo + lane; wq < wqHi; wq += 32)
-                *reinterpret_cast<uint32_t *>(&raw[r * kBlurRawPitch + 4 * wq]) = __ldg(row + wq);
-        }
-        const int nRight = min(2, kWords - wqHi), nB = wqLo + nRight;
-        for (int i = tid; i < kBlurRawRows * 4; i += kBlurThreads) {
-            const int r = i >> 2, k = i & 3;
-            if (k < nB) {
-                const int wq = k < wqLo ? 0 : wqHi + (k - wqLo);
+        const int hm = 2 * (L.h - 1), wm = 2 * (L.w - 1);
+        for (int i = tid; i < kBlurRawRows * kChunks; i += kBlurThreads) {
+            const int r = i / kChunks, c = i - r * kChunks;
+            const int gx = x0 - 16 + 16 * c;
+            if (gx >= 0 && gx + 16 <= L.w) {
                 int sy = abs(y0 + r - 3);
-                sy = max(min(sy, 2 * (L.h - 1) - sy), 0);
-                const uint8_t *row = img + (long long)sy * L.pitch;
-                const int x = x0 - 4 + 4 * wq;
-                uint32_t v = 0;
-#pragma unroll
-                for (int q = 0; q < 4; q++) {
-                    int sx = abs(x + q);
-                    sx = max(min(sx, 2 * (L.w - 1) - sx), 0);
-                    v |= (uint32_t)row[sx] << (8 * q);
-                }
-                *reinterpret_cast<uint32_t *>(&raw[r * kBlurRawPitch + 4 * wq]) = v;
+                sy = max(min(sy, hm - sy), 0);                       // one reflection: the halo (3) is shorter than the image
+                cpAsync16(&raw[r * kBlurRawPitch + 16 * c], img + (long long)sy * L.pitch + gx);
             }
         }
+        // columns the chunks did not bring: [-3, 0) of the image, and [w & ~15, w + 3) clipped to this tile
+        const int nLeft = x0 == 0 ? 3 : 0;
+        const int rb = max(L.w & ~15, x0 - 3), re = min(L.w + 3, x0 + kBlurTW + 3);
+        const int nb = nLeft + max(re - rb, 0);
+        if (nb > 0) {
+            const float rnb = __fdividef(1.0f, (float)nb);
+            for (int i = tid; i < kBlurRawRows * nb; i += kBlurThreads) {
+                const int r = (int)(((float)i + 0.5f) * rnb), k = i - r * nb;
+                const int col = k < nLeft ? k - 3 : rb + (k - nLeft);
+                int sy = abs(y0 + r - 3);
+                sy = max(min(sy, hm - sy), 0);
+                int sx = abs(col);
+                sx = max(min(sx, wm - sx), 0);
+                raw[r * kBlurRawPitch + col - x0 + 16] = img[(long long)sy * L.pitch + sx];
+            }
+        }
+        asm volatile("cp.async.wait_all;" ::: "memory");
     } else {
-        for (int i = tid; i < kBlurRawRows * kWords; i += kBlurThreads) {
-            const int r = i / kWords, wq = i - r * kWords;
-            const int sy = reflect101(y0 + r - 3, L.h);
-            const int x = x0 - 4 + 4 * wq;
-            const uint8_t *row = img + (long long)sy * L.pitch;
-            uint32_t v = 0;
-            if (!(x + 3 < -3 || x > L.w + 2 + 3))   // else: never read (beyond the halo of the last partial tile)
-                v = (uint32_t)row[reflect101(x, L.w)] | ((uint32_t)row[reflect101(x + 1, L.w)] << 8) |
-                    ((uint32_t)row[reflect101(x + 2, L.w)] << 16) | ((uint32_t)row[reflect101(x + 3, L.w)] << 24);
-            *reinterpret_cast<uint32_t *>(&raw[r * kBlurRawPitch + 4 * wq]) = v;
+        constexpr int kCols = kBlurTW + 8;        // columns x0-4 .. x0+259
+        for (int i = tid; i < kBlurRawRows * kCols; i += kBlurThreads) {
+            const int r = i / kCols, c = i - r * kCols;
+            const int x = x0 - 4 + c;
+            uint8_t v = 0;
+            if (x >= -3 && x <= L.w + 2) v = img[(long long)reflect101(y0 + r - 3, L.h) * L.pitch + reflect101(x, L.w)];
+            raw[r * kBlurRawPitch + 12 + c] = v;
         }
     }
     __syncthreads();
-    // ---- horizontal pass: 4 outputs per thread from raw columns 4tx+1 .. 4tx+10.  Output k is the dot product of
-    // bytes (1+k .. 7+k) with {18,34,48,56,48,34,18}: two byte-aligned windows (funnel shifts) and two DP4A.
+    // ---- horizontal pass: 4 outputs per thread (columns x .. x+3) from the words w0 = [x-4, x), w1 = [x, x+4),
+    // w2 = [x+4, x+8).  Output k is the dot product of bytes (1+k .. 7+k) of that window with
+    // {18,34,48,56,48,34,18}: two byte-aligned windows (funnel shifts) and two DP4A.
     const int tx = tid & 63, tg = tid >> 6;
+    const int x = x0 + 4 * tx;
     constexpr uint32_t kW0 = 18u | (34u << 8) | (48u << 16) | (56u << 24), kW1 = 48u | (34u << 8) | (18u << 16);
     for (int r = tg; r < kBlurRawRows; r += 4) {
-        const uint32_t *w = reinterpret_cast<const uint32_t *>(&raw[r * kBlurRawPitch + 4 * tx]);
+        const uint32_t *w = reinterpret_cast<const uint32_t *>(&raw[r * kBlurRawPitch + 12 + 4 * tx]);
         const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
         uint32_t o[4];
 #pragma unroll
@@ -708,7 +706,6 @@ __global__ void __launch_bounds__(kBlurThreads) k_blur(const __grid_constant__ F
     __syncthreads();
     // ---- vertical pass: each thread 4 columns x 8 rows over a 14-row register window.  Rows are paired per column
     // (PRMT) so that one DP2A applies two taps: acc = (18,34).P[k] + (48,56).P[k+2] + (48,34).P[k+4] + (0,18).P[k+5].
-    const int x = x0 + 4 * tx;
     if (x >= L.w) return;
     uint8_t *dst = B.blur + (long long)f * B.blurSlab + B.blurOff[level];
     const int dp = B.blurPitch[level];

@@ -122,7 +122,7 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
     tabs.clear();
     long long off = 0, candOff = 0, bOff = 0;
     int cells = 0, tiles = 0, keptOff = 0;
-    std::vector<int2> cellTab;
+    std::vector<int2> cellTab, tileTab;
     for (int l = 0; l < P.nlevels; l++) {
         LevelGeom &L = G.lv[l];
         L.w = cvRoundF((float)w * T.invScale[l]);   // :1131-1133, from LEVEL-0 dims
@@ -192,9 +192,16 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
         L.tilesX = (L.w + kBlurTW - 1) / kBlurTW; L.tilesY = (L.h + kBlurTH - 1) / kBlurTH;
         L.tileStart = tiles;
         tiles += L.tilesX * L.tilesY;
+        for (int ty = 0; ty < L.tilesY; ty++)
+            for (int tx = 0; tx < L.tilesX; tx++) {
+                int2 te;
+                te.x = (tx * kBlurTW) | ((ty * kBlurTH) << 12) | (l << 24); te.y = 0;
+                tileTab.push_back(te);
+            }
     }
     G.totalCells = cells; G.totalTiles = tiles;
     G.cellTab = (int)tabs.size(); tabs.insert(tabs.end(), cellTab.begin(), cellTab.end());
+    G.tileTab = (int)tabs.size(); tabs.insert(tabs.end(), tileTab.begin(), tileTab.end());
     G.slabBytes = std::max(off, 256LL);
     G.candPerFrame = std::max(candOff, 32LL);
     G.keptCap = std::max(keptOff, 1);
@@ -763,8 +770,14 @@ extern "C" int ygzorb_gaussian_blur7_u8(const uint8_t *src, int w, int h, uint8_
     YGZ_CUDA(tmp.alloc(&dS, (size_t)w * h));
     YGZ_CUDA(tmp.alloc(&dD, (size_t)dp * h));
     YGZ_CUDA(cudaMemcpy(dS, src, (size_t)w * h, cudaMemcpyHostToDevice));
+    std::vector<int2> tileTab;
+    for (int ty = 0; ty < L.tilesY; ty++)
+        for (int tx = 0; tx < L.tilesX; tx++) tileTab.push_back(make_int2((tx * kBlurTW) | ((ty * kBlurTH) << 12), 0));
+    int2 *dT = nullptr;
+    YGZ_CUDA(tmp.alloc(&dT, tileTab.size() * sizeof(int2)));
+    YGZ_CUDA(cudaMemcpy(dT, tileTab.data(), tileTab.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    G.tileTab = 0; B.tabs = dT;
     B.in = dS; B.inFrameStride = (long long)w * h; B.blur = dD; B.blurSlab = (long long)dp * h; B.blurPitch[0] = dp;
-    // blur tiles are enumerated through blockIdx.x: keep the grid inside the x-dimension limit
     launchBlur(G, B, 1, 0);
     YGZ_CUDA(cudaGetLastError());
     YGZ_CUDA(cudaMemcpy2D(dst, w, dD, dp, w, h, cudaMemcpyDeviceToHost));

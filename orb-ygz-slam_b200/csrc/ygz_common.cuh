@@ -42,6 +42,7 @@ struct FrameGeom {
     int w, h;
     int iniTh, minTh;
     int totalCells, totalTiles;   // totalCells: entries of the FAST cell table (cells with a non-empty detection area)
+    int tileTab;                  // offset of the blur tile table in DevBuffers::tabs (x = x0 | y0<<12 | level<<24)
     int cellTab;                  // offset of the cell table in DevBuffers::tabs (8-byte entries)
     int maxListCap;
     int keptCap;               // kept-list slots per frame (= max keypoints per frame)
