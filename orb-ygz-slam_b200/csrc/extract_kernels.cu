@@ -17,7 +17,7 @@ namespace ygz {
 // Table entry X[dx] = {x0 | x1<<16, a0 | a1<<16}; Y[dy] = {y0 | y1<<16, b0 | b1<<16}.
 constexpr int kResizeRows = 4;   // destination rows per thread
 
-__global__ void __launch_bounds__(256, 5) k_resize(const __grid_constant__ FrameGeom G, const DevBuffers B, int level) {
+__global__ void __launch_bounds__(256) k_resize_generic(const __grid_constant__ FrameGeom G, const DevBuffers B, int level) {
     const LevelGeom &D = G.lv[level];
     const LevelGeom &S = G.lv[level - 1];
     const int f = blockIdx.z;
@@ -91,10 +91,90 @@ __global__ void __launch_bounds__(256, 5) k_resize(const __grid_constant__ Frame
     }
 }
 
+// Word-based variant used whenever the level qualifies (LevelGeom::fastResize, built on the host: all weights
+// >= 0, the second tap is the next column or has weight 0, the 4 pixels of a thread span <= 7 source columns;
+// plus 4-byte aligned source rows).  Per source row a thread loads the three aligned words that hold its
+// columns, funnel-shifts them to an 8-byte window that starts at its first column, and gets each pixel's
+// horizontal sum from ONE byte permutation (the two neighbouring source bytes) and ONE DP2A against the packed
+// 16-bit weights (a0 | a1 << 16) exactly as the table stores them.  The vertical pass uses the high half of
+// the 32-bit products ((b * (h >> 4)) >> 16); the saturate_cast of the reference is the identity here
+// (weights sum to 2048, so the result is <= 255).
+__global__ void __launch_bounds__(256) k_resize(const __grid_constant__ FrameGeom G, const DevBuffers B, int level) {
+    const LevelGeom &D = G.lv[level];
+    const LevelGeom &S = G.lv[level - 1];
+    const int f = blockIdx.z;
+    const int dx0 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int dyBase = (blockIdx.y * 8 + threadIdx.y) * kResizeRows;
+    if (dx0 >= D.pitch || dyBase >= D.h) return;
+    const uint8_t *src = levelPtr(G, B, f, level - 1);
+    uint8_t *dst = B.pyr + (long long)f * G.slabBytes + D.off + dx0;
+    const int sp = S.pitch;
+    // column taps, once per thread (the table is padded to the pitch)
+    uint32_t coef[4], sel[4];
+    int base;
+    {
+        const int4 *tp = reinterpret_cast<const int4 *>(B.tabs + D.tabX + dx0);   // 2 entries per 16-byte load
+        const int4 t01 = __ldg(tp), t23 = __ldg(tp + 1);
+        base = t01.x & 0xffff;
+        const int d1 = (t01.z & 0xffff) - base, d2 = (t23.x & 0xffff) - base, d3 = (t23.z & 0xffff) - base;
+        coef[0] = t01.y; coef[1] = t01.w; coef[2] = t23.y; coef[3] = t23.w;
+        sel[0] = 0x10u; sel[1] = d1 | ((d1 + 1) << 4); sel[2] = d2 | ((d2 + 1) << 4); sel[3] = d3 | ((d3 + 1) << 4);
+    }
+    const int maxWord = (sp >> 2) - 1, wb = base >> 2;
+    const int i0 = min(wb, maxWord), i1 = min(wb + 1, maxWord), i2 = min(wb + 2, maxWord);
+    const int sh0 = 8 * (base & 3);
+    auto hpass = [&](int y, uint32_t h[4]) {
+        const uint32_t *row = reinterpret_cast<const uint32_t *>(src + (long long)y * sp);
+        const uint32_t w0 = __ldg(row + i0), w1 = __ldg(row + i1), w2 = __ldg(row + i2);
+        const uint32_t v0 = __funnelshift_r(w0, w1, sh0), v1 = __funnelshift_r(w1, w2, sh0);
+#pragma unroll
+        for (int i = 0; i < 4; i++) h[i] = __dp2a_lo(coef[i], __byte_perm(v0, v1, sel[i]), 0u) >> 4;
+    };
+    // rows: the horizontal pass of source row y1(dy) is reused when it is y0(dy + 1) (warp-uniform branches)
+    int prevY = -1;
+    uint32_t hPrev[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int k = 0; k < kResizeRows; k++) {
+        const int dy = dyBase + k;
+        if (dy < D.h) {
+            const int2 ty = __ldg(B.tabs + D.tabY + dy);
+            const int y0 = ty.x & 0xffff, y1 = (uint32_t)ty.x >> 16;
+            const uint32_t b0 = (uint32_t)(ty.y & 0xffff) << 16, b1 = (uint32_t)ty.y & 0xffff0000u;
+            uint32_t h0[4], h1[4];
+            if (y0 == prevY) {
+#pragma unroll
+                for (int i = 0; i < 4; i++) h0[i] = hPrev[i];
+            } else {
+                hpass(y0, h0);
+            }
+            if (y1 == y0) {
+#pragma unroll
+                for (int i = 0; i < 4; i++) h1[i] = h0[i];
+            } else {
+                hpass(y1, h1);
+            }
+            uint32_t out = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const uint32_t v = (__umulhi(b0, h0[i]) + __umulhi(b1, h1[i]) + 2u) >> 2;
+                out |= v << (8 * i);
+                hPrev[i] = h1[i];
+            }
+            prevY = y1;
+            *reinterpret_cast<uint32_t *>(dst + (long long)dy * D.pitch) = out;  // pitch is a multiple of 64: padding is scratch
+        }
+    }
+}
+
 int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nFrames, cudaStream_t s) {
     const LevelGeom &D = G.lv[level];
+    const LevelGeom &S = G.lv[level - 1];
     dim3 block(32, 8), grid((D.pitch / 4 + 31) / 32, (D.h + 8 * kResizeRows - 1) / (8 * kResizeRows), nFrames);
-    k_resize<<<grid, block, 0, s>>>(G, B, level);
+    // level 0 is caller memory: the word path needs 4-byte aligned rows there (levels >= 1 always are)
+    const bool rowsAligned = (S.pitch & 3) == 0 &&
+                             (level > 1 || ((reinterpret_cast<uintptr_t>(B.in) & 3) == 0 && (B.inFrameStride & 3) == 0));
+    if (D.fastResize && !D.area2x && rowsAligned) k_resize<<<grid, block, 0, s>>>(G, B, level);
+    else k_resize_generic<<<grid, block, 0, s>>>(G, B, level);
     return 1;
 }
 

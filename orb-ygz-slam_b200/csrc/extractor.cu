@@ -138,6 +138,21 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
             off += alignUpLL((long long)L.pitch * L.h, 256);
             std::vector<int2> X, Y;
             L.area2x = makeResizeTables(G.lv[l - 1].w, G.lv[l - 1].h, L.w, L.h, L.pitch, X, Y) ? 1 : 0;
+            // word-based kernel: non-negative weights, second tap = next column (or weight 0), a thread's 4 pixels
+            // within 7 source columns; the X table must be 16-byte aligned for its int4 loads
+            bool fast = (L.pitch % 4) == 0;
+            for (size_t dx = 0; dx < X.size() && fast; dx++) {
+                const int x0 = X[dx].x & 0xffff, x1 = (uint32_t)X[dx].x >> 16;
+                const int a0 = (short)(X[dx].y & 0xffff), a1 = (short)((uint32_t)X[dx].y >> 16);
+                fast = a0 >= 0 && a1 >= 0 && a0 + a1 == 2048 && (x1 == x0 + 1 || a1 == 0);
+                if (fast && dx % 4 == 3) fast = x0 - (X[dx - 3].x & 0xffff) <= 6 && x0 >= (X[dx - 3].x & 0xffff);
+            }
+            for (size_t dy = 0; dy < Y.size() && fast; dy++) {
+                const int b0 = (short)(Y[dy].y & 0xffff), b1 = (short)((uint32_t)Y[dy].y >> 16);
+                fast = b0 >= 0 && b1 >= 0 && b0 + b1 == 2048;
+            }
+            L.fastResize = fast ? 1 : 0;
+            if (tabs.size() % 2) tabs.push_back(make_int2(0, 0));
             L.tabX = (int)tabs.size(); tabs.insert(tabs.end(), X.begin(), X.end());
             L.tabY = (int)tabs.size(); tabs.insert(tabs.end(), Y.begin(), Y.end());
         }

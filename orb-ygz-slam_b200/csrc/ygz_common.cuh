@@ -34,6 +34,7 @@ struct LevelGeom {
     float kpSize;             // (float)(int)(31 * scale), :787
     int tabX, tabY;           // offsets of the resize tables (in 8-byte entries)
     int area2x;               // cv::resize switches exact 2x decimation to INTER_AREA
+    int fastResize;           // the level's tables satisfy the assumptions of the word-based k_resize
     int tileStart, tilesX, tilesY;  // blur tiles
 };
 
