@@ -223,16 +223,20 @@ __device__ __forceinline__ unsigned fastBase(int v) { return (unsigned)(v + 256)
 __device__ __forceinline__ unsigned fastE(int p, unsigned base) { return (unsigned)p * 0xFFFFu + base; }
 
 // Corner measure m (max over the 16 arcs of 9 contiguous ring pixels of min(v-p) resp. min(p-v)),
-// OpenCV fast_score.cpp cornerScore<16> without the threshold clamp.  `pre2` = minThFAST + 256 in both halves: the
-// function returns -1 early when no two adjacent compass pixels are both darker / both brighter
-// than the threshold (an arc of 9 always holds two adjacent compass pixels), i.e. m <= minThFAST.
-__device__ __forceinline__ int fastMeasure(unsigned p, unsigned pre2) {
+// OpenCV fast_score.cpp cornerScore<16> without the threshold clamp.  `pre2` = minThFAST + 256 in both halves.
+// With PRETEST the function returns -1 early when no two adjacent compass pixels are both darker / both
+// brighter than the threshold (an arc of 9 always holds two adjacent compass pixels), i.e. m <= minThFAST.
+//
+// Arc network (36 packed min/max instead of 16 arcs x 8): arcs k and k+1 share the 8 ring pixels k+1..k+8, so
+//   max(arc_k, arc_k+1) = min(e_k+1 .. e_k+8, max(e_k, e_k+9))        (lattice identity)
+// and the 8-pixel cores are built from pair minima lo2_j (j odd) and their pair minima lo4_j.
+template <bool PRETEST> __device__ __forceinline__ int fastMeasure(unsigned p, unsigned pre2) {
     constexpr int P = kTilePitch;
     const unsigned base = fastBase((int)ldsU8<0>(p));
     unsigned e[16];
     e[0] = fastE(ldsU8<3 * P>(p), base); e[4] = fastE(ldsU8<3>(p), base);
     e[8] = fastE(ldsU8<-3 * P>(p), base); e[12] = fastE(ldsU8<-3>(p), base);
-    {
+    if (PRETEST) {
         const unsigned pm = __vimax3_u16x2(__vminu2(e[0], e[4]), __vminu2(e[4], e[8]),
                                            __vmaxu2(__vminu2(e[8], e[12]), __vminu2(e[12], e[0])));
         if (__vmaxu2(pm, pre2) == pre2) return -1;
@@ -241,16 +245,15 @@ __device__ __forceinline__ int fastMeasure(unsigned p, unsigned pre2) {
     e[5] = fastE(ldsU8<-P + 3>(p), base);      e[6] = fastE(ldsU8<-2 * P + 2>(p), base);  e[7] = fastE(ldsU8<-3 * P + 1>(p), base);
     e[9] = fastE(ldsU8<-3 * P - 1>(p), base);  e[10] = fastE(ldsU8<-2 * P - 2>(p), base); e[11] = fastE(ldsU8<-P - 3>(p), base);
     e[13] = fastE(ldsU8<P - 3>(p), base);      e[14] = fastE(ldsU8<2 * P - 2>(p), base);  e[15] = fastE(ldsU8<3 * P - 1>(p), base);
-    unsigned lo3[16];
+    unsigned lo2[8], lo4[8], pr[8];   // index j <-> ring position 2j+1
 #pragma unroll
-    for (int k = 0; k < 16; k++) lo3[k] = __vimin3_u16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
-    unsigned lo9[16];
+    for (int j = 0; j < 8; j++) lo2[j] = __vminu2(e[2 * j + 1], e[(2 * j + 2) & 15]);
 #pragma unroll
-    for (int k = 0; k < 16; k++) lo9[k] = __vimin3_u16x2(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]);
-    unsigned r = __vimax3_u16x2(lo9[0], lo9[1], lo9[2]);
+    for (int j = 0; j < 8; j++) lo4[j] = __vminu2(lo2[j], lo2[(j + 1) & 7]);
 #pragma unroll
-    for (int k = 3; k < 15; k += 2) r = __vimax3_u16x2(r, lo9[k], lo9[k + 1]);
-    r = __vmaxu2(r, lo9[15]);
+    for (int k = 0; k < 8; k++)      // arcs 2k and 2k+1: core = ring 2k+1 .. 2k+8 = lo4[k] and lo4[k+2]
+        pr[k] = __vimin3_u16x2(lo4[k], lo4[(k + 2) & 7], __vmaxu2(e[2 * k], e[(2 * k + 9) & 15]));
+    unsigned r = __vimax3_u16x2(__vimax3_u16x2(pr[0], pr[1], pr[2]), __vimax3_u16x2(pr[3], pr[4], pr[5]), __vmaxu2(pr[6], pr[7]));
     return (int)max(r & 0xffffu, r >> 16) - 256;
 }
 
@@ -322,13 +325,16 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
     const unsigned pre2 = ((unsigned)minTh + 256u) * 0x10001u;
     const unsigned cornersAt = smemAddr(myCorners);
     int n1 = 0;
+    bool pretest = true;   // warp-uniform: the compass pretest only pays where whole warps get rejected, so it is
+                           // switched off while the warp keeps finding corners and back on after a corner-free step
     for (int i = tid; i - lane < npx; i += kFastThreads) {
         int m = -1;
         if (i < npx) {
-            m = fastMeasure(centre + off, pre2);
+            m = pretest ? fastMeasure<true>(centre + off, pre2) : fastMeasure<false>(centre + off, pre2);
             stsU8(sc0a + off, (unsigned)max(m, 0));
         }
         const unsigned mask = __ballot_sync(0xffffffffu, m > minTh);
+        pretest = mask == 0;
         if (m > minTh) stsU16(cornersAt + 2 * (n1 + __popc(mask & ltMask)), (unsigned)off);
         n1 += __popc(mask);
         x += stepX; off += stepOff;
