@@ -307,58 +307,52 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
     // ---- phase 1: measure of every detection pixel -> score tile (same pitch as the image tile, so one
     // offset `off` = y * pitch + x addresses both); corners at minThFAST go to the warp's own list
     // (fill count in a register: no shared atomics, no shuffles).  Pixel i = y * dw + x advances by
-    // kFastThreads per iteration; (x, off) are updated incrementally.
+    // kFastThreads per iteration; y = i / dw comes from a 24-bit reciprocal (IMAD.HI on i << 8, exact for
+    // i < 4096), so the address update runs on the FMA pipe and leaves the ALU pipe to the min/max network.
     const int lane = tid & 31, wid = tid >> 5;
     const unsigned ltMask = (1u << lane) - 1u;
-    uint16_t *myCorners = corners + wid * kFastWarpCap;
-    const float rdw = __fdividef(1.0f, (float)dw);
-    const int stepY = (int)((kFastThreads + 0.5f) * rdw), stepX = kFastThreads - stepY * dw;
-    const int stepOff = stepY * kTilePitch + stepX, wrapOff = kTilePitch - dw;
-    int x, off;
-    {
-        const int y = (int)(((float)tid + 0.5f) * rdw);
-        x = tid - y * dw; off = y * kTilePitch + x;
-    }
+    // 2^24 / dw rounded up by 1..11 (the float reciprocal is good to 2^-22): the quotient is exact while
+    // i * (magic * dw - 2^24) < 2^24, i.e. up to an excess of 64 for dw <= 64
+    const unsigned magic = (unsigned)(16777216.0f * __fdividef(1.0f, (float)dw)) + 6u;
+    const int wrapOff = kTilePitch - dw;
     const unsigned centre = smemAddr(tile + 3 * kTilePitch + 3 + ox);
     const unsigned sc0a = smemAddr(score + kTilePitch + 1);
-    uint8_t *sc0 = score + kTilePitch + 1;
     const unsigned pre2 = ((unsigned)minTh + 256u) * 0x10001u;
-    const unsigned cornersAt = smemAddr(myCorners);
+    const unsigned cornersAt = smemAddr(corners + wid * kFastWarpCap);
     int n1 = 0;
-    bool pretest = true;   // warp-uniform: the compass pretest only pays where whole warps get rejected, so it is
-                           // switched off while the warp keeps finding corners and back on after a corner-free step
+    unsigned lastMask = 0;   // warp-uniform: the compass pretest only pays where whole warps get rejected, so it is
+                             // skipped while the warp keeps finding corners and used again after a corner-free step
     for (int i = tid; i - lane < npx; i += kFastThreads) {
+        const int off = (int)__umulhi((unsigned)i << 8, magic) * wrapOff + i;
         int m = -1;
         if (i < npx) {
-            m = pretest ? fastMeasure<true>(centre + off, pre2) : fastMeasure<false>(centre + off, pre2);
+            m = lastMask == 0 ? fastMeasure<true>(centre + off, pre2) : fastMeasure<false>(centre + off, pre2);
             stsU8(sc0a + off, (unsigned)max(m, 0));
         }
-        const unsigned mask = __ballot_sync(0xffffffffu, m > minTh);
-        pretest = mask == 0;
-        if (m > minTh) stsU16(cornersAt + 2 * (n1 + __popc(mask & ltMask)), (unsigned)off);
-        n1 += __popc(mask);
-        x += stepX; off += stepOff;
-        if (x >= dw) { x -= dw; off += wrapOff; }
+        lastMask = __ballot_sync(0xffffffffu, m > minTh);
+        if (m > minTh) stsU16(cornersAt + 2 * (n1 + __popc(lastMask & ltMask)), (unsigned)off);
+        n1 += __popc(lastMask);
     }
     __syncthreads();
     // ---- phase 2: strict local maxima of m among the warp's corners
-    uint16_t *myMaxima = maxima + wid * (kFastWarpCap / 2);
+    const unsigned maximaAt = smemAddr(maxima + wid * (kFastWarpCap / 2));
     int n2 = 0, any = 0;
     for (int k0 = 0; k0 < n1; k0 += 32) {
         const int k = k0 + lane;
         bool ismax = false;
-        uint16_t o = 0;
+        unsigned o = 0;
         if (k < n1) {
-            o = myCorners[k];
-            const uint8_t *sc = sc0 + o;
-            const int m = sc[0];
-            const int nb = max(max(max(sc[-1], sc[1]), max(sc[-kTilePitch - 1], sc[-kTilePitch])),
-                               max(max(sc[-kTilePitch + 1], sc[kTilePitch - 1]), max(sc[kTilePitch], sc[kTilePitch + 1])));
+            constexpr int P = kTilePitch;
+            o = ldsU16(cornersAt + 2 * k);
+            const unsigned sc = sc0a + o;
+            const unsigned m = ldsU8<0>(sc);
+            const unsigned nb = max(max(max(ldsU8<-1>(sc), ldsU8<1>(sc)), max(ldsU8<-P - 1>(sc), ldsU8<-P>(sc))),
+                                    max(max(ldsU8<-P + 1>(sc), ldsU8<P - 1>(sc)), max(ldsU8<P>(sc), ldsU8<P + 1>(sc))));
             ismax = nb < m;
-            any |= ismax && m > iniTh;
+            any |= ismax && (int)m > iniTh;
         }
         const unsigned mask = __ballot_sync(0xffffffffu, ismax);
-        if (ismax) myMaxima[n2 + __popc(mask & ltMask)] = o;
+        if (ismax) stsU16(maximaAt + 2 * (n2 + __popc(mask & ltMask)), o);
         n2 += __popc(mask);
     }
     // ---- threshold fallback: iniThFAST unless nothing survives in the cell (src/ORBextractor.cc:764-770)
@@ -368,11 +362,11 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
     for (int k0 = 0; k0 < n2; k0 += 32) {
         const int k = k0 + lane;
         bool keep = false;
-        int y = 0, x = 0, m = 0;   // (x shadows the phase-1 counter on purpose: it is dead here)
+        int y = 0, x = 0, m = 0;
         if (k < n2) {
-            const int o = myMaxima[k];
+            const int o = (int)ldsU16(maximaAt + 2 * k);
             y = (o * ((1 << 20) / kTilePitch + 1)) >> 20; x = o - y * kTilePitch;   // exact for o < 2^13
-            m = sc0[o];
+            m = (int)ldsU8<0>(sc0a + o);
             keep = m > t;
         }
         const unsigned mask = __ballot_sync(0xffffffffu, keep);
