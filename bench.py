@@ -230,6 +230,8 @@ def run_ours(args, rank, local_rank, world):
     host_in.numpy()[:] = frames_np
     dev_in = host_in.to(dev)
     ex = Y.Extractor(NFEAT, SCALE, LEVELS, INI_TH, MIN_TH, max_batch=B, device=local_rank)
+    if args.pipe >= 0:
+        ex.set_pipeline(args.pipe)
     mt = Y.Matcher(local_rank)
     mt.set_stream(ex.stream())          # the search consumes the extraction's device-resident outputs in stream order
     cap = ex.max_keypoints(W, H)
@@ -485,6 +487,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=512)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline and kNN legs")
+    ap.add_argument("--pipe", type=int, default=-1, help="frames per pipelined upload chunk of the e2e leg (-1: library default)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

@@ -107,7 +107,7 @@ int ygzorb_get_candidates(ygzorb_extractor *ex, int frame, int level, int cap, i
 
 /* Wait for everything the extractor enqueued (kernels and the host-output downloads). */
 int ygzorb_extractor_sync(ygzorb_extractor *ex);
-/* Host-input calls are pipelined in chunks of `frames_per_chunk` frames (default 128): the upload of
+/* Host-input calls are pipelined in chunks of `frames_per_chunk` frames (default 256): the upload of
  * chunk k+1 and the download of chunk k-1 run on their own streams beside the kernels of chunk k, and
  * with YGZORB_NO_SYNC also beside the tail of the previous call.  0 = one chunk per max_batch.  The stage
  * taps then hold the LAST chunk only (pass YGZORB_KEEP_STAGES for parity tests). */

@@ -244,7 +244,7 @@ struct Extractor {
     cudaStream_t h2d = nullptr, d2h = nullptr;
     cudaEvent_t inReady[2] = {}, inFree[2] = {}, outReady[2] = {}, outFree[2] = {};
     unsigned inSeq = 0, outSeq = 0;
-    int pipeFrames = 128;      // frames per pipelined chunk of a host-input call (0: one chunk per max_batch)
+    int pipeFrames = 256;      // frames per pipelined chunk of a host-input call (0: one chunk per max_batch)
     uint8_t *dPyr = nullptr; size_t pyrBytes = 0;
     uint8_t *dBlur = nullptr; size_t blurBytes = 0;
     int2 *dTabs = nullptr; size_t tabBytes = 0;
