@@ -200,6 +200,36 @@ int ygzorb_search_by_projection(ygzorb_matcher *m, const ygzorb_frame_features *
                                 float th, int check_level, float nnratio, unsigned flags, int32_t *kp_to_mp,
                                 int32_t *mp_best_idx, int32_t *n_matches);
 
+/* LastFrame side of ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono,
+ * checkLevel) (src/ORBmatcher.cc:1218-1350): frame pair f has n_pts[f] entries starting at f*pt_stride, entry i =
+ * LastFrame keypoint i. */
+typedef struct ygzorb_lastframe_points {
+    int pt_stride;
+    const int32_t *n_pts;       /* LastFrame.N */
+    const uint8_t *valid;       /* LastFrame.mvpMapPoints[i] != NULL && !LastFrame.mvbOutlier[i] (:1244-1246) */
+    const uint8_t *has_obs;     /* that MapPoint's Observations() > 0 */
+    const float *world_pos;     /* GetWorldPos(), 3 floats per entry */
+    const uint8_t *desc;        /* GetDescriptor(), 32 B rows */
+    const int32_t *octave;      /* LastFrame.mvKeys[i].octave */
+    const float *angle;         /* LastFrame.mvKeys[i].angle */
+    /* per frame pair 30 floats: Rcw (row-major 9), tcw (3) of CurrentFrame.mTcw; Rlw (9), tlw (3) of
+     * LastFrame.mTcw; CurrentFrame fx, fy, cx, cy, mbf, mb */
+    const float *pose;
+} ygzorb_lastframe_points;
+
+/* The motion-model matcher (src/ORBmatcher.cc:1218-1350 + ComputeThreeMaxima :1471-1502), batched over frame
+ * pairs and reproducing the serial claim / overwrite order and the rotation-histogram rejection.
+ * `cur` is CurrentFrame (claimed = entries of mvpMapPoints that hold a MapPoint with observations on entry;
+ * Tracking clears them first, Tracking.cc:1017).  Float evaluation order of the projection: 3-term dot products
+ * as a0 + (a1 + a2), uncontracted; invzc = (float)(1.0 / (double)z); a non-finite projection is out of view.
+ * kp_to_pt[f*kp_stride + i2] = LastFrame index whose MapPoint is left in CurrentFrame.mvpMapPoints[i2], or -1;
+ * pt_best_idx[f*pt_stride + i] = keypoint entry i matched before the rotation check, or -1 (may be NULL);
+ * n_matches[f] = the function's return value. */
+int ygzorb_search_by_projection_last(ygzorb_matcher *m, const ygzorb_frame_features *cur,
+                                     const ygzorb_lastframe_points *last, float th, int mono, int check_level,
+                                     int check_orientation, unsigned flags, int32_t *kp_to_pt, int32_t *pt_best_idx,
+                                     int32_t *n_matches);
+
 /* KeyFrame arrays read by SearchForTriangulation (include/KeyFrame.h:236-271); the DBoW2::FeatureVector
  * (Thirdparty/DBoW2/DBoW2/FeatureVector.h:23-24, std::map<NodeId, vector<unsigned>>) flattened to CSR:
  * node_ids ascending, features of node k = node_feats[node_start[k] .. node_start[k+1]). */

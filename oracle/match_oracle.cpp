@@ -185,6 +185,87 @@ YGZO_API int ygzo_search_by_projection(const void *kpsV, const uint8_t *desc, co
     return nmatches;
 }
 
+// ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono, checkLevel) —
+// src/ORBmatcher.cc:1218-1350 (the motion-model tracker's matcher) with ComputeThreeMaxima (:1471-1502).
+// LastFrame side flattened per keypoint i: valid = mvpMapPoints[i] != NULL && !mvbOutlier[i]; hasObs, worldPos
+// (GetWorldPos), ptDesc (GetDescriptor) of that MapPoint; octaveLast / angleLast = LastFrame.mvKeys[i].
+// pose[30] = Rcw (row-major 9), tcw (3), Rlw (9), tlw (3), fx, fy, cx, cy, mbf, mb.
+// Float evaluation order (the reference leaves it to Eigen + the compiler; canonical here and in the kernel):
+// a 3-term dot product is a0 + (a1 + a2) (Eigen >= 3.3 redux), products and sums uncontracted;
+// invzc = (float)(1.0 / (double)z) (:1254); a projection that is not finite counts as out of the image.
+// kpToPt[i2] = LastFrame index left in CurrentFrame.mvpMapPoints[i2] by this call, else -1.
+YGZO_API int ygzo_search_by_projection_last(const void *kpsV, const uint8_t *desc, const float *uRight,
+                                            const uint8_t *claimed, int n, float minX, float minY, float maxX, float maxY,
+                                            float invW, float invH, const float *scaleFactors, const float *pose,
+                                            const uint8_t *valid, const uint8_t *hasObs, const float *worldPos,
+                                            const uint8_t *ptDesc, const int32_t *octaveLast, const float *angleLast, int m,
+                                            float th, int bMono, int checkLevel, int checkOrientation, int32_t *kpToPt,
+                                            int32_t *ptBestIdx) {
+    const KeyPoint *kps = (const KeyPoint *)kpsV;
+    Grid g;
+    assignGrid(g, kps, n, minX, minY, invW, invH);
+    std::vector<uint8_t> blocked(n, 0);
+    for (int i = 0; i < n; i++) { kpToPt[i] = -1; blocked[i] = claimed ? claimed[i] : 0; }
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float *Rcw = pose, *tcw = pose + 9, *Rlw = pose + 12, *tlw = pose + 21;
+    const float fx = pose[24], fy = pose[25], cx = pose[26], cy = pose[27], mbf = pose[28], mb = pose[29];
+    auto dot3 = [](float a0, float a1, float a2) { const float s = a1 + a2; return a0 + s; };
+    float twc[3], tlc[3];
+    for (int r = 0; r < 3; r++) twc[r] = -dot3(Rcw[r] * tcw[0], Rcw[3 + r] * tcw[1], Rcw[6 + r] * tcw[2]);   // :1231
+    for (int r = 0; r < 3; r++) tlc[r] = dot3(Rlw[3 * r] * twc[0], Rlw[3 * r + 1] * twc[1], Rlw[3 * r + 2] * twc[2]) + tlw[r];
+    const bool bForward = tlc[2] > mb && !bMono, bBackward = -tlc[2] > mb && !bMono;   // :1238-1239
+    std::vector<int> vIndices2;
+    for (int i = 0; i < m; i++) {
+        if (ptBestIdx) ptBestIdx[i] = -1;
+        if (!valid[i]) continue;
+        const float *X = worldPos + 3 * (size_t)i;
+        float c[3];
+        for (int r = 0; r < 3; r++) c[r] = dot3(Rcw[3 * r] * X[0], Rcw[3 * r + 1] * X[1], Rcw[3 * r + 2] * X[2]) + tcw[r];
+        const float xc = c[0], yc = c[1];
+        const float invzc = (float)(1.0 / (double)c[2]);
+        if (invzc < 0) continue;
+        const float u = fx * xc * invzc + cx, v = fy * yc * invzc + cy;
+        if (!std::isfinite(u) || !std::isfinite(v)) continue;
+        if (u < minX || u > maxX) continue;
+        if (v < minY || v > maxY) continue;
+        const int nLastOctave = octaveLast[i];
+        const float radius = th * scaleFactors[nLastOctave];
+        if (!checkLevel) featuresInArea(g, kps, u, v, radius, -1, -1, vIndices2);
+        else if (bForward) featuresInArea(g, kps, u, v, radius, nLastOctave, -1, vIndices2);
+        else if (bBackward) featuresInArea(g, kps, u, v, radius, 0, nLastOctave, vIndices2);
+        else featuresInArea(g, kps, u, v, radius, nLastOctave - 1, nLastOctave + 1, vIndices2);
+        if (vIndices2.empty()) continue;
+        int bestDist = 256, bestIdx2 = -1;
+        for (int i2 : vIndices2) {
+            if (blocked[i2]) continue;
+            if (uRight && uRight[i2] > 0) {
+                const float ur = u - mbf * invzc;
+                const float er = std::fabs(ur - uRight[i2]);
+                if (er > radius) continue;
+            }
+            const int dist = descriptorDistance(ptDesc + (size_t)i * 32, desc + (size_t)i2 * 32);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= TH_HIGH) {
+            kpToPt[bestIdx2] = i;
+            blocked[bestIdx2] = hasObs[i] ? 1 : 0;
+            if (ptBestIdx) ptBestIdx[i] = bestIdx2;
+            nmatches++;
+            if (checkOrientation) rotHist[rotationBin(angleLast[i], kps[bestIdx2].angle)].push_back(bestIdx2);
+        }
+    }
+    if (checkOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1, sizes[HISTO_LENGTH];
+        for (int i = 0; i < HISTO_LENGTH; i++) sizes[i] = (int)rotHist[i].size();
+        threeMaxima(sizes, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int idx : rotHist[i]) { kpToPt[idx] = -1; nmatches--; }
+    }
+    return nmatches;
+}
+
 // ORBmatcher::SearchForTriangulation — src/ORBmatcher.cc:597-746 with CheckDistEpipolarLine (:136-153).
 // The two DBoW2::FeatureVectors (std::map<NodeId, vector<unsigned>>, ascending NodeId) are flattened
 // to CSR: nodeIds[k] ascending, features of node k = feats[start[k] .. start[k+1]).  hasMP = the

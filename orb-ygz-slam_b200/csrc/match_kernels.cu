@@ -246,6 +246,15 @@ __device__ int projScan(int *a, int n, int *ws) {   // in-place exclusive scan b
     return total;
 }
 
+// rotation-histogram bin of a match (src/ORBmatcher.cc:1318-1323, :697-702): round() = half away from zero
+__device__ __forceinline__ int rotationBinDev(float a1, float a2) {
+    float rot = __fsub_rn(a1, a2);
+    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+    int bin = (int)roundf(__fmul_rn(rot, 1.0f / kHistoLength));
+    if (bin == kHistoLength) bin = 0;
+    return bin;
+}
+
 __device__ __forceinline__ bool posInGrid(const ProjArgs &A, float x, float y, int *cell) {
     const int px = (int)roundf(__fmul_rn(__fsub_rn(x, A.minX), A.invW));   // round(): half away from zero
     const int py = (int)roundf(__fmul_rn(__fsub_rn(y, A.minY), A.invH));
@@ -271,7 +280,7 @@ __device__ __forceinline__ int projAccept(const ProjArgs &A, int bestDist, int b
     return -1;
 }
 
-__device__ int projMatchCached(const ProjArgs &A, int f, int j, int cnt, const int32_t *claimTime) {
+template <int MODE> __device__ int projMatchCached(const ProjArgs &A, int f, int j, int cnt, const int32_t *claimTime) {
     int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
     const uint32_t *c = A.candCache + (size_t)f * kProjCache * A.mpStride + j;
     for (int k = 0; k < cnt; k++) {
@@ -282,21 +291,62 @@ __device__ int projMatchCached(const ProjArgs &A, int f, int j, int cnt, const i
         if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = oct; bestIdx = idx; }
         else if (dist < bestDist2) { bestLevel2 = oct; bestDist2 = dist; }
     }
+    if (MODE == 1) return bestDist <= kThHigh ? bestIdx : -1;     // :1311 (no second-best rule in the LastFrame variant)
     return projAccept(A, bestDist, bestDist2, bestLevel, bestLevel2, bestIdx);
 }
 
-template <bool RECORD>
+// The per-point query of the window search.  MODE 0: a MapPoint after isInFrustum (:61-77).  MODE 1: keypoint j of
+// LastFrame projected with the current pose (:1242-1282); dir = 1 forward, 2 backward, 0 neither (:1238-1239).
+struct ProjQuery { float x, y, rad, xr; int minLevel, maxLevel; };
+
+__device__ __forceinline__ float projDot3(float a0, float a1, float a2) { return __fadd_rn(a0, __fadd_rn(a1, a2)); }
+
+template <int MODE> __device__ __forceinline__ bool projQuery(const ProjArgs &A, int f, int j, int dir, ProjQuery &q) {
+    const size_t mo = (size_t)f * A.mpStride + j;
+    if (!A.inView[mo]) return false;
+    if (MODE == 0) {
+        const int lvl = A.level[mo];
+        float r = ((double)A.viewCos[mo] > 0.998) ? 2.5f : 4.0f;      // RadiusByViewingCos (:128-133)
+        if (A.th != 1.0f) r = __fmul_rn(r, A.th);
+        q.rad = __fmul_rn(r, A.scale[lvl]);
+        q.x = A.projX[mo]; q.y = A.projY[mo];
+        q.xr = A.projXR ? A.projXR[mo] : 0.f;
+        q.minLevel = A.checkLevel ? lvl - 1 : -1; q.maxLevel = A.checkLevel ? lvl : -1;
+        return true;
+    }
+    const float *P = A.pose + (size_t)f * 30;
+    const float *X = A.worldPos + 3 * mo;
+    const float X0 = X[0], X1 = X[1], X2 = X[2];
+    const float xc = __fadd_rn(projDot3(__fmul_rn(P[0], X0), __fmul_rn(P[1], X1), __fmul_rn(P[2], X2)), P[9]);
+    const float yc = __fadd_rn(projDot3(__fmul_rn(P[3], X0), __fmul_rn(P[4], X1), __fmul_rn(P[5], X2)), P[10]);
+    const float zc = __fadd_rn(projDot3(__fmul_rn(P[6], X0), __fmul_rn(P[7], X1), __fmul_rn(P[8], X2)), P[11]);
+    const float invzc = __double2float_rn(__ddiv_rn(1.0, (double)zc));   // const float invzc = 1.0 / x3Dc[2] (:1254)
+    if (invzc < 0) return false;
+    const float u = __fadd_rn(__fmul_rn(__fmul_rn(P[24], xc), invzc), P[26]);
+    const float v = __fadd_rn(__fmul_rn(__fmul_rn(P[25], yc), invzc), P[27]);
+    if (!isfinite(u) || !isfinite(v)) return false;
+    if (u < A.minX || u > A.maxX) return false;
+    if (v < A.minY || v > A.maxY) return false;
+    const int oct = A.octaveLast[mo];
+    q.rad = __fmul_rn(A.th, A.scale[oct]);
+    q.x = u; q.y = v;
+    q.xr = __fsub_rn(u, __fmul_rn(P[28], invzc));
+    if (!A.checkLevel) { q.minLevel = -1; q.maxLevel = -1; }
+    else if (dir == 1) { q.minLevel = oct; q.maxLevel = -1; }
+    else if (dir == 2) { q.minLevel = 0; q.maxLevel = oct; }
+    else { q.minLevel = oct - 1; q.maxLevel = oct + 1; }
+    return true;
+}
+
+template <bool RECORD, int MODE>
 __device__ int projMatchOne(const ProjArgs &A, int f, int j, int n, const int *cellStart, const int32_t *gridList,
-                            const int32_t *claimTime, int *recorded) {
+                            const int32_t *claimTime, int *recorded, int dir) {
     const size_t mo = (size_t)f * A.mpStride + j;
     if (RECORD) *recorded = 0;
-    if (!A.inView[mo]) return -1;
-    const int lvl = A.level[mo];
-    float r = ((double)A.viewCos[mo] > 0.998) ? 2.5f : 4.0f;      // RadiusByViewingCos (:128-133)
-    if (A.th != 1.0f) r = __fmul_rn(r, A.th);
-    const float rad = __fmul_rn(r, A.scale[lvl]);
-    const float x = A.projX[mo], y = A.projY[mo];
-    const int minLevel = A.checkLevel ? lvl - 1 : -1, maxLevel = A.checkLevel ? lvl : -1;
+    ProjQuery q;
+    if (!projQuery<MODE>(A, f, j, dir, q)) return -1;
+    const float rad = q.rad, x = q.x, y = q.y;
+    const int minLevel = q.minLevel, maxLevel = q.maxLevel;
     const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, A.minX), rad), A.invW)));
     if (cx0 >= kGridCols) return -1;
     const int cx1 = min(kGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, A.minX), rad), A.invW)));
@@ -311,7 +361,7 @@ __device__ int projMatchOne(const ProjArgs &A, int f, int j, int n, const int *c
     const ygzorb_keypoint *kps = A.kps + (size_t)f * A.kpStride;
     const uint4 *desc = reinterpret_cast<const uint4 *>(A.desc + (size_t)f * A.kpStride * 32);
     const float *uRight = A.uRight ? A.uRight + (size_t)f * A.kpStride : nullptr;
-    const float projXR = A.projXR ? A.projXR[mo] : 0.f;
+    const float projXR = q.xr;
     int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
     (void)n;
     int nrec = 0;
@@ -344,11 +394,13 @@ __device__ int projMatchOne(const ProjArgs &A, int f, int j, int n, const int *c
         }
     }
     if (RECORD) *recorded = nrec;
+    if (MODE == 1) return bestDist <= kThHigh ? bestIdx : -1;
     return projAccept(A, bestDist, bestDist2, bestLevel, bestLevel2, bestIdx);
 }
 
-__global__ void __launch_bounds__(kProjThreads) k_search_by_projection(const __grid_constant__ ProjArgs A) {
+template <int MODE> __global__ void __launch_bounds__(kProjThreads) k_search_by_projection(const __grid_constant__ ProjArgs A) {
     __shared__ int cellStart[kGridCols * kGridRows + 1];
+    __shared__ int dirS, hist[kHistoLength], keep[3];
     __shared__ int cellFill[kGridCols * kGridRows];
     __shared__ int ws[40];
     const int f = blockIdx.x, tid = threadIdx.x;
@@ -386,13 +438,24 @@ __global__ void __launch_bounds__(kProjThreads) k_search_by_projection(const __g
         }
     }
     uint8_t *candCnt = A.candCnt + (size_t)f * A.mpStride;
+    if (MODE == 1 && tid == 0) {   // tlc = Rlw * (-Rcw^T tcw) + tlw; forward / backward motion along the optical axis (:1227-1239)
+        const float *P = A.pose + (size_t)f * 30;
+        float twc[3];
+#pragma unroll
+        for (int r = 0; r < 3; r++) twc[r] = -projDot3(__fmul_rn(P[r], P[9]), __fmul_rn(P[3 + r], P[10]), __fmul_rn(P[6 + r], P[11]));
+        const float tlcz = __fadd_rn(projDot3(__fmul_rn(P[18], twc[0]), __fmul_rn(P[19], twc[1]), __fmul_rn(P[20], twc[2])), P[23]);
+        const float mb = P[29];
+        dirS = A.bMono ? 0 : (tlcz > mb ? 1 : (-tlcz > mb ? 2 : 0));
+    }
+    if (MODE == 1 && tid < kHistoLength) hist[tid] = 0;
     __syncthreads();
+    const int dir = MODE == 1 ? dirS : 0;
     // ---- round 0: full window walk against the entry claims, recording the candidate cache
     for (int i = tid; i < n; i += kProjThreads) claimTime[i] = (claimed && claimed[i]) ? -1 : INT_MAX;
     __syncthreads();
     for (int j = tid; j < m; j += kProjThreads) {
         int nrec;
-        best[j] = projMatchOne<true>(A, f, j, n, cellStart, gridList, claimTime, &nrec);
+        best[j] = projMatchOne<true, MODE>(A, f, j, n, cellStart, gridList, claimTime, &nrec, dir);
         candCnt[j] = (uint8_t)(nrec > kProjCache ? kProjOverflow : nrec);
     }
     __syncthreads();
@@ -408,8 +471,8 @@ __global__ void __launch_bounds__(kProjThreads) k_search_by_projection(const __g
         int changed = 0;
         for (int j = tid; j < m; j += kProjThreads) {
             const int cnt = candCnt[j];
-            const int b = cnt == kProjOverflow ? projMatchOne<false>(A, f, j, n, cellStart, gridList, claimTime, nullptr)
-                                               : projMatchCached(A, f, j, cnt, claimTime);
+            const int b = cnt == kProjOverflow ? projMatchOne<false, MODE>(A, f, j, n, cellStart, gridList, claimTime, nullptr, dir)
+                                               : projMatchCached<MODE>(A, f, j, cnt, claimTime);
             if (b != best[j]) { best[j] = b; changed = 1; }
         }
         if (!__syncthreads_or(changed)) break;
@@ -424,6 +487,37 @@ __global__ void __launch_bounds__(kProjThreads) k_search_by_projection(const __g
         if (b >= 0) { atomicMax(&kpToMp[b], j); cnt++; }
     }
     if (cnt) atomicAdd(&ws[0], cnt);
+    if (MODE == 1 && A.checkOrientation) {
+        // ---- rotation consistency (:1316-1346): every accepted point votes; the keypoints of all entries outside the
+        // three dominant bins are cleared afterwards (also when a later point of a kept bin had overwritten them)
+        const float *angleLast = A.angleLast + (size_t)f * A.mpStride;
+        for (int j = tid; j < m; j += kProjThreads) {
+            const int b = best[j];
+            if (b >= 0) atomicAdd(&hist[rotationBinDev(angleLast[j], kps[b].angle)], 1);
+        }
+        __syncthreads();
+        if (tid == 0) {   // ComputeThreeMaxima (:1471-1502)
+            int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+            for (int i = 0; i < kHistoLength; i++) {
+                const int sz = hist[i];
+                if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
+                else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
+                else if (sz > max3) { max3 = sz; ind3 = i; }
+            }
+            if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+            else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
+            keep[0] = ind1; keep[1] = ind2; keep[2] = ind3;
+        }
+        __syncthreads();   // (also orders the kpToMp atomicMax writes above before the clears below)
+        int dropped = 0;
+        for (int j = tid; j < m; j += kProjThreads) {
+            const int b = best[j];
+            if (b < 0) continue;
+            const int bin = rotationBinDev(angleLast[j], kps[b].angle);
+            if (bin != keep[0] && bin != keep[1] && bin != keep[2]) { kpToMp[b] = -1; dropped++; }
+        }
+        if (dropped) atomicSub(&ws[0], dropped);
+    }
     __syncthreads();
     if (tid == 0) A.nMatches[f] = ws[0];
 }
@@ -431,7 +525,13 @@ __global__ void __launch_bounds__(kProjThreads) k_search_by_projection(const __g
 int launchSearchByProjection(const ProjArgs &A, int maxKp, cudaStream_t s) {
     (void)maxKp;
     if (A.nFrames <= 0) return 0;
-    k_search_by_projection<<<A.nFrames, kProjThreads, 0, s>>>(A);
+    k_search_by_projection<0><<<A.nFrames, kProjThreads, 0, s>>>(A);
+    return 1;
+}
+
+int launchSearchByProjectionLast(const ProjArgs &A, cudaStream_t s) {
+    if (A.nFrames <= 0) return 0;
+    k_search_by_projection<1><<<A.nFrames, kProjThreads, 0, s>>>(A);
     return 1;
 }
 
@@ -444,14 +544,6 @@ int launchSearchByProjection(const ProjArgs &A, int maxKp, cudaStream_t s) {
 // by the reference, so keypoints of KF1 are independent: one thread per keypoint scans its node's
 // list in KF2 in order with the reference's "dist > bestDist -> continue" rule (last one wins ties).
 constexpr int kTriThreads = 1024;
-
-__device__ __forceinline__ int rotationBinDev(float a1, float a2) {
-    float rot = __fsub_rn(a1, a2);
-    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
-    int bin = (int)roundf(__fmul_rn(rot, 1.0f / kHistoLength));
-    if (bin == kHistoLength) bin = 0;
-    return bin;
-}
 
 __global__ void __launch_bounds__(kTriThreads) k_triangulation(const __grid_constant__ TriArgs A) {
     __shared__ int hist[kHistoLength];

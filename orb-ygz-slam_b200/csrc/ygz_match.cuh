@@ -22,6 +22,12 @@ struct ProjArgs {
     const uint8_t *inView, *hasObs, *mpDesc;
     float th, nnratio;
     int checkLevel;
+    // LastFrame variant (src/ORBmatcher.cc:1218-1350): the "MapPoints" are LastFrame's keypoints; their projection
+    // is computed in the kernel from the pose (30 floats per frame pair: Rcw, tcw, Rlw, tlw, fx, fy, cx, cy, mbf, mb)
+    const float *pose, *worldPos, *angleLast;
+    const int32_t *octaveLast;
+    float maxX, maxY;
+    int bMono, checkOrientation;
     int32_t *kpToMp, *mpBestIdx, *nMatches;   // outputs (mpBestIdx is also the iteration state)
     int32_t *claimTime;                       // scratch [nFrames * kpStride]
     int32_t *gridList;                        // scratch [nFrames * kpStride]
@@ -75,6 +81,7 @@ size_t knnPartialBytes(int nq, int splits);
 int launchKnn2(const uint8_t *query, int nq, const uint8_t *train, int nt, float ratio, int th, int splits, void *partial,
                int variant, int32_t *bestIdx, int32_t *d1, int32_t *d2, int32_t *match, cudaStream_t s);
 int launchSearchByProjection(const ProjArgs &A, int maxKp, cudaStream_t s);
+int launchSearchByProjectionLast(const ProjArgs &A, cudaStream_t s);
 int launchTriangulation(const TriArgs &A, cudaStream_t s);
 int launchStereo(const StereoArgs &A, cudaStream_t s);
 int configureMatchKernels();

@@ -215,6 +215,12 @@ class MapPointProj(C.Structure):
                 ("has_obs", C.c_void_p), ("desc", C.c_void_p)]
 
 
+class LastFramePoints(C.Structure):
+    _fields_ = [("pt_stride", C.c_int), ("n_pts", C.c_void_p), ("valid", C.c_void_p), ("has_obs", C.c_void_p),
+                ("world_pos", C.c_void_p), ("desc", C.c_void_p), ("octave", C.c_void_p), ("angle", C.c_void_p),
+                ("pose", C.c_void_p)]
+
+
 class KeyFrameFeatures(C.Structure):
     _fields_ = [("n", C.c_int), ("n_nodes", C.c_int), ("nlevels", C.c_int), ("kps", C.c_void_p), ("desc", C.c_void_p),
                 ("u_right", C.c_void_p), ("has_mappoint", C.c_void_p), ("node_ids", C.c_void_p),
@@ -241,6 +247,8 @@ class Matcher:
         L.ygzorb_hamming_knn2.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_int,
                                           C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ygzorb_descriptor_distance.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_void_p]
+        L.ygzorb_search_by_projection_last.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_int,
+                                                       C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ygzorb_search_by_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_float,
                                                   C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ygzorb_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float,
@@ -335,6 +343,41 @@ class Matcher:
         check(lib().ygzorb_search_by_projection(self.h, C.byref(F), C.byref(P), th, int(check_level), nnratio, 0,
                                                 _ptr(kp_to_mp), _ptr(best), _ptr(nm)))
         return [(int(nm[i]), kp_to_mp[i, :n_kp[i]].copy(), best[i, :n_mp[i]].copy()) for i in range(nf)]
+
+    def search_by_projection_last(self, frames, lasts, bounds, scale_factors, th, mono, check_level, check_orientation):
+        """frames: list of (kps, desc, u_right|None, claimed|None) of the current frames; lasts: list of dicts with
+        valid, has_obs, world_pos (n,3), desc, octave, angle, pose (30,) (tests/synth.lastframe_case).
+        Returns per frame pair (n_matches, kp_to_pt, pt_best_idx)."""
+        nf = len(frames)
+        ks = max(max(len(f[0]) for f in frames), 1)
+        ps = max(max(len(l["valid"]) for l in lasts), 1)
+        n_kp = np.array([len(f[0]) for f in frames], np.int32)
+        n_pt = np.array([len(l["valid"]) for l in lasts], np.int32)
+        kps = np.zeros((nf, ks), KP_DTYPE); desc = np.zeros((nf, ks, 32), np.uint8)
+        has_ur = any(f[2] is not None for f in frames); has_cl = any(f[3] is not None for f in frames)
+        ur = np.full((nf, ks), -1, np.float32) if has_ur else None
+        cl = np.zeros((nf, ks), np.uint8) if has_cl else None
+        for i, f in enumerate(frames):
+            kps[i, :len(f[0])] = f[0]; desc[i, :len(f[0])] = f[1]
+            if f[2] is not None:
+                ur[i, :len(f[0])] = f[2]
+            if f[3] is not None:
+                cl[i, :len(f[0])] = f[3]
+        va = np.zeros((nf, ps), np.uint8); ho = np.zeros((nf, ps), np.uint8); wp = np.zeros((nf, ps, 3), np.float32)
+        pd = np.zeros((nf, ps, 32), np.uint8); oc = np.zeros((nf, ps), np.int32); an = np.zeros((nf, ps), np.float32)
+        pose = np.zeros((nf, 30), np.float32)
+        for i, l in enumerate(lasts):
+            k = len(l["valid"])
+            va[i, :k] = l["valid"]; ho[i, :k] = l["has_obs"]; wp[i, :k] = l["world_pos"]; pd[i, :k] = l["desc"]
+            oc[i, :k] = l["octave"]; an[i, :k] = l["angle"]; pose[i] = l["pose"]
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        F = FrameFeatures(nf, ks, _ptr(n_kp), _ptr(kps), _ptr(desc), _ptr(ur), _ptr(cl), bounds[0], bounds[1], bounds[2],
+                          bounds[3], len(sf), _ptr(sf))
+        L = LastFramePoints(ps, _ptr(n_pt), _ptr(va), _ptr(ho), _ptr(wp), _ptr(pd), _ptr(oc), _ptr(an), _ptr(pose))
+        kp_to_pt = np.zeros((nf, ks), np.int32); best = np.zeros((nf, ps), np.int32); nm = np.zeros(nf, np.int32)
+        check(lib().ygzorb_search_by_projection_last(self.h, C.byref(F), C.byref(L), th, int(mono), int(check_level),
+                                                     int(check_orientation), 0, _ptr(kp_to_pt), _ptr(best), _ptr(nm)))
+        return [(int(nm[i]), kp_to_pt[i, :n_kp[i]].copy(), best[i, :n_pt[i]].copy()) for i in range(nf)]
 
     def search_by_projection_raw(self, F, P, th, check_level, nnratio, flags, kp_to_mp_ptr, best_ptr, nm_ptr):
         check(lib().ygzorb_search_by_projection(self.h, C.byref(F), C.byref(P), th, int(check_level), nnratio, flags,

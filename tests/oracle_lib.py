@@ -222,6 +222,30 @@ def search_by_projection(kps, desc, u_right, claimed, bounds, scale_factors, mp,
     return nm, kp_to_mp[:n].copy(), mp_best[:m].copy()
 
 
+def search_by_projection_last(kps, desc, u_right, claimed, bounds, scale_factors, last, th, mono, check_level,
+                              check_orientation):
+    """last: dict with valid, has_obs (u1), world_pos (m,3) f4, desc (m,32), octave (i4), angle (f4), pose (30,) f4."""
+    n, m = len(kps), len(last["valid"])
+    kps = np.ascontiguousarray(kps)
+    desc = np.ascontiguousarray(desc, np.uint8)
+    inv_w, inv_h = grid_inv(*bounds)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    u8 = lambda a: np.ascontiguousarray(a, np.uint8)
+    ur = f32(u_right) if u_right is not None else None
+    cl = u8(claimed) if claimed is not None else None
+    va, ho, wp, pd = u8(last["valid"]), u8(last["has_obs"]), f32(last["world_pos"]), u8(last["desc"])
+    oc, an, pose = np.ascontiguousarray(last["octave"], np.int32), f32(last["angle"]), f32(last["pose"])
+    kp_to_pt = np.zeros(max(n, 1), np.int32)
+    best = np.zeros(max(m, 1), np.int32)
+    nm = lib().ygzo_search_by_projection_last(_p(kps), _p(desc), _p(ur), _p(cl), n, C.c_float(bounds[0]), C.c_float(bounds[1]),
+                                              C.c_float(bounds[2]), C.c_float(bounds[3]), C.c_float(inv_w), C.c_float(inv_h),
+                                              _p(sf), _p(pose), _p(va), _p(ho), _p(wp), _p(pd), _p(oc), _p(an), m,
+                                              C.c_float(th), int(mono), int(check_level), int(check_orientation),
+                                              _p(kp_to_pt), _p(best))
+    return nm, kp_to_pt[:n].copy(), best[:m].copy()
+
+
 def search_for_triangulation(kf1, kf2, F12, ex, ey, only_stereo, check_orientation):
     """kf: dict with kps, desc, u_right, has_mp, node_ids, node_start, node_feats, scale_factors, level_sigma2."""
     def pk(kf):

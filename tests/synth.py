@@ -108,6 +108,49 @@ def projection_case(kps, desc, n_mp, seed, jitter=3.0, p_not_in_view=0.05, p_no_
     return mp, u_right, claimed
 
 
+def lastframe_case(kps, desc, n_pts, seed, motion=(0.02, -0.01, 0.3), jitter=2.0, stereo=False, fx=458.654, fy=457.296,
+                   cx=367.215, cy=248.375, bf=47.9, p_invalid=0.1, p_no_obs=0.05, rot_outliers=0.15):
+    """A LastFrame for SearchByProjection(CurrentFrame, LastFrame, ...): n_pts of its keypoints carry MapPoints whose
+    world positions project (with the current pose) next to a keypoint of the CURRENT frame (kps/desc), so that the
+    windows are populated; some keypoint angles are rotated to feed the rotation histogram with outliers.
+    pose = identity current pose shifted by `motion` relative to the last one (tlc = motion)."""
+    rng = np.random.default_rng(seed)
+    n = len(kps)
+    src = rng.integers(0, n, size=n_pts)
+    u = kps["x"][src] + rng.uniform(-jitter, jitter, n_pts)
+    v = kps["y"][src] + rng.uniform(-jitter, jitter, n_pts)
+    z = rng.uniform(1.0, 12.0, n_pts)
+    z[rng.uniform(size=n_pts) < 0.02] *= -1.0                     # behind the camera: skipped (:1256)
+    th = rng.uniform(-0.02, 0.02, 3)                              # small rotation, exact orthonormality is irrelevant here
+    Rcw = np.array([[1, -th[2], th[1]], [th[2], 1, -th[0]], [-th[1], th[0], 1]], np.float64)
+    tcw = rng.uniform(-0.2, 0.2, 3)
+    pc = np.stack([(u - cx) / fx * z, (v - cy) / fy * z, z], 1)   # camera coordinates
+    pw = (np.linalg.inv(Rcw) @ (pc - tcw).T).T                    # world coordinates
+    # LastFrame pose: tlc = Rlw * twc + tlw = motion  (with Rlw = Rcw: tlw = motion + tcw)
+    Rlw, tlw = Rcw.copy(), np.asarray(motion, np.float64) + tcw
+    mb = bf / fx
+    pose = np.concatenate([Rcw.reshape(9), tcw, Rlw.reshape(9), tlw, [fx, fy, cx, cy, bf, mb]]).astype(np.float32)
+    ang = kps["angle"][src] + rng.normal(0, 3.0, n_pts)
+    out = rng.uniform(size=n_pts) < rot_outliers
+    ang = np.mod(np.where(out, ang + rng.uniform(40, 320, n_pts), ang), 360.0)
+    octave = np.clip(kps["octave"][src] + rng.integers(-1, 2, n_pts), 0, 7)
+    last = {
+        "valid": (rng.uniform(size=n_pts) >= p_invalid).astype(np.uint8),
+        "has_obs": (rng.uniform(size=n_pts) >= p_no_obs).astype(np.uint8),
+        "world_pos": pw.astype(np.float32),
+        "desc": flip_bits(desc[src], rng.integers(0, 50, size=n_pts), rng),
+        "octave": octave.astype(np.int32),
+        "angle": ang.astype(np.float32),
+        "pose": pose,
+        "src": src,
+    }
+    u_right = None
+    if stereo:
+        u_right = np.where(rng.uniform(size=n) < 0.6, kps["x"] - bf / rng.uniform(1.0, 12.0, n), -1.0).astype(np.float32)
+    claimed = (rng.uniform(size=n) < 0.05).astype(np.uint8)
+    return last, u_right, claimed
+
+
 def feature_vector(n, n_nodes, seed, base=None, p_keep=0.8):
     """Synthetic DBoW2::FeatureVector as CSR: ascending node ids, features in insertion (index) order.
     With `base` (node of each feature of another keyframe mapped through `src`) matched features

@@ -70,6 +70,28 @@ def test_search_by_projection_vs_oracle(matcher, feats, th, check_level, stereo,
         assert np.array_equal(g[1], e[1]) and np.array_equal(g[2], e[2])
 
 
+@pytest.mark.parametrize("th,mono,check_level,check_ori,stereo,motion,seed", [
+    (15.0, True, False, True, False, (0.02, -0.01, 0.3), 1), (7.0, False, True, True, True, (0.0, 0.0, 0.5), 2),
+    (7.0, False, True, False, True, (0.0, 0.0, -0.5), 3), (15.0, False, True, True, False, (0.05, 0.0, 0.01), 4),
+    (40.0, True, False, True, False, (0.0, 0.0, 0.0), 5)])
+def test_search_by_projection_last_vs_oracle(matcher, feats, th, mono, check_level, check_ori, stereo, motion, seed):
+    """SearchByProjection(CurrentFrame, LastFrame, ...) (src/ORBmatcher.cc:1218-1350): forward / backward / lateral
+    motion (octave windows), stereo consistency, claim order, rotation-histogram rejection; th=40 overflows the
+    candidate cache."""
+    img, kps, desc = feats
+    sf, _, _ = synth.scale_tables()
+    bounds = (0.0, 0.0, float(img.shape[1]), float(img.shape[0]))
+    frames, lasts, exp = [], [], []
+    for k in range(3):                                     # a small batch, ragged point counts
+        last, u_right, claimed = synth.lastframe_case(kps, desc, 1000 - 150 * k, seed * 10 + k, motion=motion, stereo=stereo)
+        frames.append((kps, desc, u_right, claimed)); lasts.append(last)
+        exp.append(O.search_by_projection_last(kps, desc, u_right, claimed, bounds, sf, last, th, mono, check_level, check_ori))
+    got = matcher.search_by_projection_last(frames, lasts, bounds, sf, th, mono, check_level, check_ori)
+    for g, e in zip(got, exp):
+        assert g[0] == e[0] and e[0] > 100
+        assert np.array_equal(g[1], e[1]) and np.array_equal(g[2], e[2])
+
+
 def test_search_by_projection_claim_chain(matcher, feats):
     """Many MapPoints aimed at the same keypoints: long claim chains must resolve like the serial loop."""
     img, kps, desc = feats

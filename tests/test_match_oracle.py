@@ -120,6 +120,118 @@ def test_search_by_projection_vs_python(th, check_level, stereo, seed):
     assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
 
 
+def _py_search_by_projection_last(kps, desc, u_right, claimed, bounds, sf, last, th, mono, check_level, check_ori):
+    """src/ORBmatcher.cc:1218-1350 re-derived in float32 numpy scalars (dot products as a0 + (a1 + a2))."""
+    f = np.float32
+    min_x, min_y, max_x, max_y = [f(b) for b in bounds]
+    inv_w, inv_h = f(64) / (max_x - min_x), f(48) / (max_y - min_y)
+    rnd = lambda v: int(math.floor(abs(v) + 0.5)) * (1 if v >= 0 else -1)
+    grid = {}
+    for i in range(len(kps)):
+        px, py = rnd(float((kps["x"][i] - min_x) * inv_w)), rnd(float((kps["y"][i] - min_y) * inv_h))
+        if 0 <= px < 64 and 0 <= py < 48:
+            grid.setdefault((px, py), []).append(i)
+    P = last["pose"].astype(np.float32)
+    Rcw, tcw, Rlw, tlw = P[0:9].reshape(3, 3), P[9:12], P[12:21].reshape(3, 3), P[21:24]
+    fx, fy, cx, cy, mbf, mb = P[24:30]
+    dot3 = lambda a0, a1, a2: f(a0 + f(a1 + a2))
+    twc = [f(-dot3(f(Rcw[0, r] * tcw[0]), f(Rcw[1, r] * tcw[1]), f(Rcw[2, r] * tcw[2]))) for r in range(3)]
+    tlcz = f(dot3(f(Rlw[2, 0] * twc[0]), f(Rlw[2, 1] * twc[1]), f(Rlw[2, 2] * twc[2])) + tlw[2])
+    fwd, bwd = (tlcz > mb and not mono), (-tlcz > mb and not mono)
+    D = _hamming_matrix(last["desc"], desc)
+    blocked = claimed.astype(bool).copy() if claimed is not None else np.zeros(len(kps), bool)
+    kp_to_pt = np.full(len(kps), -1, np.int32)
+    best_of = np.full(len(last["valid"]), -1, np.int32)
+    hist = [[] for _ in range(30)]
+    n = 0
+    for i in range(len(last["valid"])):
+        if not last["valid"][i]:
+            continue
+        X = last["world_pos"][i].astype(np.float32)
+        c = [f(dot3(f(Rcw[r, 0] * X[0]), f(Rcw[r, 1] * X[1]), f(Rcw[r, 2] * X[2])) + tcw[r]) for r in range(3)]
+        with np.errstate(divide="ignore"):
+            invz = f(np.float64(1.0) / np.float64(c[2]))
+        if invz < 0:
+            continue
+        u, v = f(f(f(fx * c[0]) * invz) + cx), f(f(f(fy * c[1]) * invz) + cy)
+        if not (np.isfinite(u) and np.isfinite(v)) or u < min_x or u > max_x or v < min_y or v > max_y:
+            continue
+        o = int(last["octave"][i])
+        rad = f(f(th) * sf[o])
+        if not check_level:
+            lo, hi = -1, -1
+        elif fwd:
+            lo, hi = o, -1
+        elif bwd:
+            lo, hi = 0, o
+        else:
+            lo, hi = o - 1, o + 1
+        chk = lo > 0 or hi >= 0
+        cx0 = max(0, math.floor(float(f(f(u - min_x - rad) * inv_w)))); cx1 = min(63, math.ceil(float(f(f(u - min_x + rad) * inv_w))))
+        cy0 = max(0, math.floor(float(f(f(v - min_y - rad) * inv_h)))); cy1 = min(47, math.ceil(float(f(f(v - min_y + rad) * inv_h))))
+        if cx0 >= 64 or cx1 < 0 or cy0 >= 48 or cy1 < 0:
+            continue
+        b1, bi = 256, -1
+        for ix in range(cx0, cx1 + 1):
+            for iy in range(cy0, cy1 + 1):
+                for idx in grid.get((ix, iy), []):
+                    ko = int(kps["octave"][idx])
+                    if chk and (ko < lo or (hi >= 0 and ko > hi)):
+                        continue
+                    if not (abs(f(kps["x"][idx] - u)) < rad and abs(f(kps["y"][idx] - v)) < rad):
+                        continue
+                    if blocked[idx]:
+                        continue
+                    if u_right is not None and u_right[idx] > 0 and abs(f(f(u - f(mbf * invz)) - u_right[idx])) > rad:
+                        continue
+                    d = int(D[i, idx])
+                    if d < b1:
+                        b1, bi = d, idx
+        if b1 <= 100:
+            kp_to_pt[bi] = i; blocked[bi] = bool(last["has_obs"][i]); best_of[i] = bi; n += 1
+            if check_ori:
+                rot = f(last["angle"][i] - kps["angle"][bi])
+                if rot < 0:
+                    rot = f(rot + f(360))
+                b = rnd(float(f(rot * f(f(1.0) / f(30)))))
+                hist[0 if b == 30 else b].append(bi)
+    if check_ori:
+        m1 = m2 = m3 = 0; i1 = i2 = i3 = -1
+        for i in range(30):
+            sz = len(hist[i])
+            if sz > m1:
+                m3, m2, m1, i3, i2, i1 = m2, m1, sz, i2, i1, i
+            elif sz > m2:
+                m3, m2, i3, i2 = m2, sz, i2, i
+            elif sz > m3:
+                m3, i3 = sz, i
+        if f(m2) < f(0.1) * f(m1):
+            i2 = i3 = -1
+        elif f(m3) < f(0.1) * f(m1):
+            i3 = -1
+        for i in range(30):
+            if i not in (i1, i2, i3):
+                for idx in hist[i]:
+                    kp_to_pt[idx] = -1; n -= 1
+    return n, kp_to_pt, best_of
+
+
+@pytest.mark.parametrize("th,mono,check_level,check_ori,stereo,motion,seed", [
+    (15.0, True, False, True, False, (0.02, -0.01, 0.3), 1), (7.0, False, True, True, True, (0.0, 0.0, 0.5), 2),
+    (7.0, False, True, False, True, (0.0, 0.0, -0.5), 3), (15.0, False, True, True, False, (0.05, 0.0, 0.01), 4)])
+def test_search_by_projection_last_vs_python(th, mono, check_level, check_ori, stereo, motion, seed):
+    img, (kps, desc) = _features(seed=seed)
+    sf, _, _ = synth.scale_tables()
+    last, u_right, claimed = synth.lastframe_case(kps, desc, 500, seed, motion=motion, stereo=stereo)
+    bounds = (0.0, 0.0, float(img.shape[1]), float(img.shape[0]))
+    a = O.search_by_projection_last(kps, desc, u_right, claimed, bounds, sf, last, th, mono, check_level, check_ori)
+    b = _py_search_by_projection_last(kps, desc, u_right, claimed, bounds, sf, last, th, mono, check_level, check_ori)
+    assert a[0] == b[0] and a[0] > 30
+    assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+    if check_ori:   # the rotation vote must have removed something, and never more than it added
+        assert (a[2] >= 0).sum() > a[0]
+
+
 def test_search_by_projection_order_dependence():
     """Two MapPoints with the same descriptor on the same keypoint: the first claims it, the second must skip it."""
     img, (kps, desc) = _features(seed=9)
