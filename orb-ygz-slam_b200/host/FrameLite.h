@@ -15,12 +15,23 @@ struct MapPointLite {                       // include/MapPoint.h:95-102 + the c
     bool mbTrackInView = true, mbBad = false;
     int nObs = 1;
     cv::Mat mDescriptor;
+    float mWorldPos[3] = {0, 0, 0};
+    const float *GetWorldPos() const { return mWorldPos; }       // Vector3f in the reference
     bool isBad() const { return mbBad; }
     int Observations() const { return nObs; }
     cv::Mat GetDescriptor() const { return mDescriptor.clone(); }
 };
+struct PoseLite {                           // the two accessors of Sophus::SE3f the matcher uses (mTcw)
+    float R[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, t[3] = {0, 0, 0};
+    struct Rot { const float *p; float operator()(int r, int c) const { return p[3 * r + c]; } };
+    Rot rotationMatrix() const { return Rot{R}; }
+    const float *translation() const { return t; }
+};
 class Frame {
 public:
+    PoseLite mTcw;
+    float fx = 0, fy = 0, cx = 0, cy = 0;
+    std::vector<bool> mvbOutlier;
     std::vector<cv::Mat> mvImagePyramid;
     cv::Mat mImRight;
     int N = 0;

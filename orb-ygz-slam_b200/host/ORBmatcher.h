@@ -1,6 +1,6 @@
 // ORBmatcher.h — drop-in for the Hamming paths of the reference's include/ORBmatcher.h: same class
 // name, constructor, constants and method signatures for DescriptorDistance, SearchByProjection(Frame&,
-// vector<MapPoint*>&, th, checkLevel) and the stereo matcher Frame::ComputeStereoMatches (as a free
+// vector<MapPoint*>&, th, checkLevel), SearchByProjection(Frame&, const Frame&, th, bMono, checkLevel) and the stereo matcher Frame::ComputeStereoMatches (as a free
 // function over the Frame members it uses).  The searches are templates over the reference's Frame /
 // MapPoint types so this header compiles both inside the reference tree and against host/FrameLite.h.
 // The work is done by libygzorb_cuda.so; there is no CPU implementation here except the 8-word
@@ -76,6 +76,62 @@ public:
             throw std::runtime_error(std::string("ygzorb_search_by_projection: ") + ygzorb_last_error());
         for (int i = 0; i < n; i++)
             if (kpToMp[i] >= 0) F.mvpMapPoints[i] = vpMapPoints[kpToMp[i]];      // F.mvpMapPoints[bestIdx] = pMP (:120)
+        return nmatches;
+    }
+
+    // src/ORBmatcher.cc:1218-1350 (the motion-model tracker).  FrameT needs mTcw with rotationMatrix() / translation()
+    // (Sophus SE3f in the reference) whose results index as (r, c) / [r], plus the members the reference reads.
+    template <class FrameT>
+    int SearchByProjection(FrameT &CurrentFrame, const FrameT &LastFrame, const float th, const bool bMono, bool checkLevel = true) {
+        const int n = (int)CurrentFrame.mvKeys.size(), m = LastFrame.N;
+        if (n == 0 || m <= 0) return 0;
+        float pose[30];
+        const auto Rcw = CurrentFrame.mTcw.rotationMatrix();
+        const auto tcw = CurrentFrame.mTcw.translation();
+        const auto Rlw = LastFrame.mTcw.rotationMatrix();
+        const auto tlw = LastFrame.mTcw.translation();
+        for (int r = 0; r < 3; r++) {
+            for (int c = 0; c < 3; c++) { pose[3 * r + c] = Rcw(r, c); pose[12 + 3 * r + c] = Rlw(r, c); }
+            pose[9 + r] = tcw[r]; pose[21 + r] = tlw[r];
+        }
+        pose[24] = CurrentFrame.fx; pose[25] = CurrentFrame.fy; pose[26] = CurrentFrame.cx; pose[27] = CurrentFrame.cy;
+        pose[28] = CurrentFrame.mbf; pose[29] = CurrentFrame.mb;
+        std::vector<uint8_t> valid(m), hasObs(m), pdesc((size_t)m * 32), claimed(n), desc((size_t)n * 32);
+        std::vector<float> wpos((size_t)m * 3), angle(m);
+        std::vector<int32_t> octave(m);
+        for (int i = 0; i < m; i++) {
+            auto *p = LastFrame.mvpMapPoints[i];
+            valid[i] = p && !LastFrame.mvbOutlier[i];
+            octave[i] = LastFrame.mvKeys[i].octave; angle[i] = LastFrame.mvKeys[i].angle;
+            if (!valid[i]) continue;
+            hasObs[i] = p->Observations() > 0;
+            const auto x3Dw = p->GetWorldPos();
+            for (int r = 0; r < 3; r++) wpos[(size_t)i * 3 + r] = x3Dw[r];
+            const cv::Mat d = p->GetDescriptor();
+            std::memcpy(&pdesc[(size_t)i * 32], d.ptr(0), 32);
+        }
+        bool anyRight = false;
+        for (int i = 0; i < n; i++) {
+            claimed[i] = CurrentFrame.mvpMapPoints[i] && CurrentFrame.mvpMapPoints[i]->Observations() > 0;
+            std::memcpy(&desc[(size_t)i * 32], CurrentFrame.mDescriptors.ptr(i), 32);
+            anyRight |= CurrentFrame.mvuRight[i] > 0;
+        }
+        const int32_t nKp = n, nPt = m;
+        ygzorb_frame_features fv{1, n, &nKp, (const ygzorb_keypoint *)CurrentFrame.mvKeys.data(), desc.data(),
+                                 anyRight ? CurrentFrame.mvuRight.data() : nullptr, claimed.data(), CurrentFrame.mnMinX,
+                                 CurrentFrame.mnMinY, CurrentFrame.mnMaxX, CurrentFrame.mnMaxY,
+                                 (int)CurrentFrame.mvScaleFactors.size(), CurrentFrame.mvScaleFactors.data()};
+        ygzorb_lastframe_points lv{m, &nPt, valid.data(), hasObs.data(), wpos.data(), pdesc.data(), octave.data(), angle.data(), pose};
+        std::vector<int32_t> kpToPt(n), best(m);
+        int32_t nmatches = 0;
+        if (ygzorb_search_by_projection_last(mHandle, &fv, &lv, th, bMono ? 1 : 0, checkLevel ? 1 : 0, mbCheckOrientation ? 1 : 0, 0,
+                                             kpToPt.data(), best.data(), &nmatches) != 0)
+            throw std::runtime_error(std::string("ygzorb_search_by_projection_last: ") + ygzorb_last_error());
+        // CurrentFrame.mvpMapPoints[bestIdx2] = pMP (:1312), then the rotation vote NULLs its losers (:1339-1342)
+        for (int i = 0; i < m; i++)
+            if (best[i] >= 0) CurrentFrame.mvpMapPoints[best[i]] = nullptr;
+        for (int i = 0; i < n; i++)
+            if (kpToPt[i] >= 0) CurrentFrame.mvpMapPoints[i] = LastFrame.mvpMapPoints[kpToPt[i]];
         return nmatches;
     }
 

@@ -3,9 +3,11 @@
 // Frame::ComputeStereoMatches src/Frame.cc:747) and dumps the results for tests/test_gpu_host.py.
 // usage: host_demo <in.bin> <out.bin>
 //   in.bin : int32 w, h, nfeatures, nMP | left image w*h | right image w*h |
-//            nMP x {float projX, projY, viewCos; int32 level; 32 B descriptor}
+//            nMP x {float projX, projY, viewCos; int32 level; 32 B descriptor} |
+//            int32 nLast | 30 float pose | nLast x {float wx, wy, wz, angle; int32 octave, valid, hasObs; 32 B descriptor}
 //   out.bin: int32 nL | nL x 28 B keypoints | nL x 32 B desc | int32 nR | nR keypoints | nR desc |
-//            nL x float uRight | nL x float depth | int32 nmatches | nL x int32 (MapPoint index per keypoint, -1 none)
+//            nL x float uRight | nL x float depth | int32 nmatches | nL x int32 (MapPoint index per keypoint, -1 none) |
+//            int32 nmatchesLast | nL x int32 (LastFrame index per keypoint, -1 none)
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -36,6 +38,23 @@ int main(int argc, char **argv) {
         mps[i].mDescriptor.create(1, 32, cv::CV_8U);
         rd(fi, mps[i].mDescriptor.data, 32);
     }
+    int32_t nLast = 0;
+    rd(fi, &nLast, 1);
+    float pose[30];
+    rd(fi, pose, 30);
+    std::vector<MapPointLite> lastMps(nLast);
+    Frame Last;
+    Last.N = nLast; Last.mvKeys.resize(nLast); Last.mvpMapPoints.assign(nLast, nullptr); Last.mvbOutlier.assign(nLast, false);
+    for (int i = 0; i < nLast; i++) {
+        float v[4]; int32_t q[3];
+        rd(fi, v, 4); rd(fi, q, 3);
+        for (int r = 0; r < 3; r++) lastMps[i].mWorldPos[r] = v[r];
+        Last.mvKeys[i].angle = v[3]; Last.mvKeys[i].octave = q[0];
+        lastMps[i].nObs = q[2];
+        lastMps[i].mDescriptor.create(1, 32, cv::CV_8U);
+        rd(fi, lastMps[i].mDescriptor.data, 32);
+        if (q[1]) Last.mvpMapPoints[i] = &lastMps[i];
+    }
     fclose(fi);
 
     ORBextractor exL(nfeat, 1.2f, 8, 20, 7), exR(nfeat, 1.2f, 8, 20, 7);
@@ -64,6 +83,16 @@ int main(int argc, char **argv) {
     ORBmatcher matcher(0.8f);
     const int nmatches = matcher.SearchByProjection(F, vp, 1.0f, false);
 
+    std::vector<int32_t> assign(F.N);
+    for (int i = 0; i < F.N; i++) assign[i] = F.mvpMapPoints[i] ? (int32_t)(F.mvpMapPoints[i] - mps.data()) : -1;
+    // Tracking::TrackWithMotionModel (src/Tracking.cc:1017-1026): clear, then SearchByProjection(Current, Last, th, mono)
+    for (int r = 0; r < 9; r++) { F.mTcw.R[r] = pose[r]; Last.mTcw.R[r] = pose[12 + r]; }
+    for (int r = 0; r < 3; r++) { F.mTcw.t[r] = pose[9 + r]; Last.mTcw.t[r] = pose[21 + r]; }
+    F.fx = pose[24]; F.fy = pose[25]; F.cx = pose[26]; F.cy = pose[27]; F.mbf = pose[28]; F.mb = pose[29];
+    F.mvpMapPoints.assign(F.N, nullptr);
+    ORBmatcher motionMatcher(0.9f, true);
+    const int nmatchesLast = motionMatcher.SearchByProjection(F, Last, 15.0f, true);
+
     FILE *fo = fopen(argv[2], "wb");
     int32_t nL = F.N, nR = (int32_t)F.mvKeysRight.size();
     wr(fo, &nL, 1); wr(fo, F.mvKeys.data(), nL);
@@ -73,9 +102,12 @@ int main(int argc, char **argv) {
     wr(fo, uRight.data(), nL); wr(fo, depth.data(), nL);
     int32_t nm = nmatches;
     wr(fo, &nm, 1);
-    for (int i = 0; i < nL; i++) { int32_t idx = F.mvpMapPoints[i] ? (int32_t)(F.mvpMapPoints[i] - mps.data()) : -1; wr(fo, &idx, 1); }
+    wr(fo, assign.data(), nL);
+    int32_t nml = nmatchesLast;
+    wr(fo, &nml, 1);
+    for (int i = 0; i < nL; i++) { int32_t idx = F.mvpMapPoints[i] ? (int32_t)(F.mvpMapPoints[i] - lastMps.data()) : -1; wr(fo, &idx, 1); }
     fclose(fo);
-    printf("host_demo: %d left / %d right keypoints, %d projection matches, ORBmatcher::DescriptorDistance(self)=%d\n", nL, nR, nmatches,
+    printf("host_demo: %d left / %d right keypoints, %d projection matches, %d motion-model matches, DescriptorDistance(self)=%d\n", nL, nR, nmatches, nmatchesLast,
            nL ? ORBmatcher::DescriptorDistance(F.mDescriptors.row(0), F.mDescriptors.row(0)) : 0);
     return 0;
 }

@@ -34,6 +34,15 @@ def test_host_classes_end_to_end():
             rec["v"][:, 0] = mp["proj_x"]; rec["v"][:, 1] = mp["proj_y"]; rec["v"][:, 2] = mp["view_cos"]
             rec["lvl"] = mp["level"]; rec["d"] = mp["desc"]
             rec.tofile(f)
+            n_last = 900
+            last, _, _ = synth.lastframe_case(kl, dl, n_last, 21)
+            np.array([n_last], np.int32).tofile(f)
+            last["pose"].tofile(f)
+            lrec = np.zeros(n_last, np.dtype([("v", "<f4", 4), ("q", "<i4", 3), ("d", "u1", 32)]))
+            lrec["v"][:, :3] = last["world_pos"]; lrec["v"][:, 3] = last["angle"]
+            lrec["q"][:, 0] = last["octave"]; lrec["q"][:, 1] = last["valid"]; lrec["q"][:, 2] = last["has_obs"]
+            lrec["d"] = last["desc"]
+            lrec.tofile(f)
         res = subprocess.run([DEMO, fin, fout], capture_output=True, text=True)
         assert res.returncode == 0, res.stdout + res.stderr
         buf = open(fout, "rb").read()
@@ -56,3 +65,6 @@ def test_host_classes_end_to_end():
     assert gur.tobytes() == ur.tobytes() and gdepth.tobytes() == depth.tobytes() and (ur >= 0).sum() > 100
     nm, kp_to_mp, _ = O.search_by_projection(kl, dl, None, None, (0.0, 0.0, float(w), float(h)), sf, mp, 1.0, False, 0.8)
     assert gnm == nm and np.array_equal(gassign, kp_to_mp) and nm > 300
+    gnml = int(take("<i4", 1)[0]); gassign_last = take("<i4", nL)
+    nml, kp_to_pt, _ = O.search_by_projection_last(kl, dl, None, None, (0.0, 0.0, float(w), float(h)), sf, last, 15.0, True, True, True)
+    assert gnml == nml and np.array_equal(gassign_last, kp_to_pt) and nml > 300
