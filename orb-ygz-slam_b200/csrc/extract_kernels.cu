@@ -190,9 +190,7 @@ int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nF
 // (cell, y-in-cell, x-in-cell) that encodes the reference's vToDistributeKeys order, which is all
 // the quadtree needs from the order (its only order dependence is "first wins" on response ties).
 constexpr int kFastThreads = 128;
-constexpr int kCellMax = 64;                 // wCell, hCell < 60 always (width/floor(width/30))
-constexpr int kTilePitch = 76;               // image tile pitch: cell + 6 + up to 3 alignment bytes, multiple of 4
-constexpr int kFastWarpCap = (kCellMax * kCellMax / kFastThreads + 1) * 32;   // pixels one warp visits (multiple of 32)
+constexpr int kTilePitch = kFastTilePitch;   // image / score tile pitch
 
 // The 16 ring differences are kept as packed 16-bit pairs E = (d + 256) | (256 - d) << 16 with
 // d = v - p, both halves positive, so ONE VIMNMX3.U16x2 handles the "darker" arcs (low half) and
@@ -261,11 +259,15 @@ template <bool PRETEST> __device__ __forceinline__ int fastMeasure(unsigned p, u
 // stored score m-1 exceeds the stored scores of its 8 neighbours, and a neighbour's stored score is
 // n-1 if n > t and 0 otherwise; since m > t >= 1 this is exactly "every neighbour has n < m".  The
 // score tile holds m for m > minThFAST and 0 elsewhere (and outside the detection area).
-__global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
-    __shared__ __align__(16) uint8_t tile[(kCellMax + 6) * kTilePitch];
-    __shared__ __align__(16) uint8_t score[(kCellMax + 2) * kTilePitch];
-    __shared__ uint16_t corners[(kFastThreads / 32) * kFastWarpCap];      // per warp: y<<6 | x of pixels with m > minThFAST
-    __shared__ uint16_t maxima[(kFastThreads / 32) * (kFastWarpCap / 2)];  // per warp: strict local maxima among them
+__global__ void __launch_bounds__(kFastThreads, 9) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+    // dynamic shared memory, sized by the geometry's largest cell (FrameGeom::fastRegionA/fastScoreBytes/fastWarpCap):
+    // [image tile, re-used from phase 2 on for the per-warp maxima lists][score tile][per-warp corner lists]
+    extern __shared__ __align__(16) uint8_t fastSmem[];
+    uint8_t *tile = fastSmem;
+    uint8_t *score = fastSmem + G.fastRegionA;
+    uint16_t *corners = reinterpret_cast<uint16_t *>(score + G.fastScoreBytes);   // per warp: tile offsets of pixels with m > minThFAST
+    uint16_t *maxima = reinterpret_cast<uint16_t *>(fastSmem);                    // per warp: the strict local maxima among them
+    const int kFastWarpCap = G.fastWarpCap;
     const int f = blockIdx.y, tid = threadIdx.x;
     // cell window (src/ORBextractor.cc:749-762) from the host-built cell table; detection area = window minus 3 px
     const int2 ce = __ldg(B.tabs + G.cellTab + blockIdx.x);
@@ -335,7 +337,7 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
     }
     __syncthreads();
     // ---- phase 2: strict local maxima of m among the warp's corners
-    const unsigned maximaAt = smemAddr(maxima + wid * (kFastWarpCap / 2));
+    const unsigned maximaAt = smemAddr(maxima + wid * kFastWarpCap);
     int n2 = 0, any = 0;
     for (int k0 = 0; k0 < n1; k0 += 32) {
         const int k = k0 + lane;
@@ -389,7 +391,9 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ F
 
 int launchFast(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s) {
     if (G.totalCells == 0) return 0;
-    k_fast<<<dim3(G.totalCells, nFrames), kFastThreads, 0, s>>>(G, B);
+    size_t smem = (size_t)G.fastRegionA + G.fastScoreBytes + (size_t)(kFastThreads / 32) * G.fastWarpCap * sizeof(uint16_t);
+    if (const char *pad = getenv("YGZ_FAST_SMEM_PAD")) smem += (size_t)atoi(pad);   // occupancy experiments
+    k_fast<<<dim3(G.totalCells, nFrames), kFastThreads, smem, s>>>(G, B);
     return 1;
 }
 

@@ -123,6 +123,7 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
     long long off = 0, candOff = 0, bOff = 0;
     int cells = 0, tiles = 0, keptOff = 0;
     std::vector<int2> cellTab, tileTab;
+    int maxDh = 1, maxNpx = 1;
     for (int l = 0; l < P.nlevels; l++) {
         LevelGeom &L = G.lv[l];
         L.w = cvRoundF((float)w * T.invScale[l]);   // :1131-1133, from LEVEL-0 dims
@@ -188,6 +189,7 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
                     ce.x = iniX | (iniY << 12) | (l << 24);
                     ce.y = dw | (dh << 7) | ((i * nCols + j) << 14);
                     cellTab.push_back(ce);
+                    maxDh = std::max(maxDh, dh); maxNpx = std::max(maxNpx, dw * dh);
                     cells++;
                 }
             }
@@ -215,6 +217,11 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
             }
     }
     G.totalCells = cells; G.totalTiles = tiles;
+    // k_fast shared memory: [image tile | per-warp maxima lists (alias, phase 2 on)] [score tile] [per-warp corner lists];
+    // a list holds every pixel its warp visits (strict maxima can reach 17 of 32 consecutive pixels on dot patterns)
+    G.fastWarpCap = (maxNpx + 127) / 128 * 32;
+    G.fastRegionA = alignUp(std::max((maxDh + 6) * kFastTilePitch, 8 * G.fastWarpCap), 16);
+    G.fastScoreBytes = alignUp((maxDh + 2) * kFastTilePitch, 16);
     G.cellTab = (int)tabs.size(); tabs.insert(tabs.end(), cellTab.begin(), cellTab.end());
     G.tileTab = (int)tabs.size(); tabs.insert(tabs.end(), tileTab.begin(), tileTab.end());
     G.slabBytes = std::max(off, 256LL);

@@ -14,6 +14,7 @@ constexpr int kMaxLevels = 16;
 constexpr int kEdge = 19;        // EDGE_THRESHOLD, src/ORBextractor.cc:72
 constexpr int kMinBorder = 16;   // EDGE_THRESHOLD - 3, :733
 constexpr int kHalfPatch = 15;   // HALF_PATCH_SIZE, :71
+constexpr int kFastTilePitch = 76;   // k_fast image / score tile pitch: cell + 6 + up to 3 alignment bytes, multiple of 4
 constexpr int kBlurTW = 256, kBlurTH = 32;  // blur tile (k_blur)
 
 // Per-level geometry, computed once per (w, h) on the host with the reference's float arithmetic
@@ -44,6 +45,7 @@ struct FrameGeom {
     int iniTh, minTh;
     int totalCells, totalTiles;   // totalCells: entries of the FAST cell table (cells with a non-empty detection area)
     int tileTab;                  // offset of the blur tile table in DevBuffers::tabs (x = x0 | y0<<12 | level<<24)
+    int fastRegionA, fastScoreBytes, fastWarpCap;   // k_fast dynamic shared memory layout (bytes, bytes, list entries per warp)
     int cellTab;                  // offset of the cell table in DevBuffers::tabs (8-byte entries)
     int maxListCap;
     int keptCap;               // kept-list slots per frame (= max keypoints per frame)

@@ -173,3 +173,19 @@ def test_keep_stages_covers_whole_call():
     for f in range(5):
         assert np.array_equal(ex.pyramid(f, w, h)[0], frames[f])
     ex.close()
+
+
+@pytest.mark.parametrize("px,py", [(2, 4), (2, 2), (3, 2)])
+def test_dot_grid_maxima_density(px, py):
+    """Isolated bright dots on a regular grid: every dot is a FAST corner and a strict local maximum, so up to 17
+    of 32 consecutive raster pixels survive the NMS (px=2) and a 2x2 block always holds one (px=py=2) — the densest
+    inputs for the per-warp lists of k_fast and for the per-level candidate capacity."""
+    w, h = 320, 240
+    img = np.full((h, w), 40, np.uint8)
+    img[::py, ::px] = 220
+    ex = Y.Extractor(1000, 1.2, 8, 20, 7)
+    kps, desc = ex.extract(img)
+    okps, odesc = O.extract(O.params(1000, 1.2, 8, 20, 7), img, cap=4096)
+    assert len(okps) > 200
+    assert kps.tobytes() == okps.tobytes() and np.array_equal(desc, odesc)
+    ex.close()
