@@ -401,8 +401,19 @@ def build_line(args, world, B, cap, ms, ms_e2e, launches, clocks, stage_ms, n_kp
     dom_bytes = STAGE_BYTES[kern_stages[dom]] * B
     achieved = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9
     staged = STAGED_TOTAL * B * args.steps / (ms * 1e-3) / 1e9
+    # DRAM traffic of that kernel per launch: dram__bytes_read + dram__bytes_write of one `ncu --set full` capture
+    # (tools/ncu_traffic.py -> profiles/r1_traffic.json, per frame), scaled to this launch's frames
+    traffic, traffic_src = None, None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+        tk = tj["kernels"]["k_" + dom]
+        traffic = (tk["dram_read_bytes_per_frame"] + tk["dram_write_bytes_per_frame"]) * B / launches_per_stage
+        traffic_src = "profiles/r1_traffic.json (%s, %d frames, scaled per frame)" % (tj["report"], tj["frames"])
+    except (OSError, KeyError, ValueError):
+        pass
     roofline = {"bound": "hbm", "kernel": "k_" + dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                "note": "the kernel is ALU-pipe / issue bound (ncu: 83 % issue-slot utilisation, DRAM 3 %), see DESIGN.md 5",
                 "launches_in_stage": launches_per_stage, "algorithmic_bytes_per_launch": dom_bytes / launches_per_stage,
                 "pipeline_staged_GBps": staged, "pipeline_frac": staged / hbm_peak}
     mp_bytes = sum(int(h_mp[k].numel() * h_mp[k].element_size()) for k in mp_keys)
