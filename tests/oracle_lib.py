@@ -299,3 +299,60 @@ def search_by_projection_batch(n_kp, n_mp, kps, desc, bounds, scale_factors, mp,
         _p(mp["in_view"]), _p(mp["has_obs"]), _p(mp["desc"]), C.c_float(th), int(check_level), C.c_float(nnratio), threads,
         _p(kp_to_mp), _p(nm))
     return kp_to_mp, nm
+
+
+# ---- bag of words (oracle/bow_oracle.cpp)
+class Vocabulary:
+    """Restated DBoW2 vocabulary tree (oracle side)."""
+
+    def __init__(self, handle):
+        if not handle:
+            raise RuntimeError("vocabulary could not be loaded")
+        self.h = C.c_void_p(handle)
+        info = np.zeros(5, np.int32)
+        lib().ygzo_voc_info(self.h, _p(info))
+        self.n_nodes, self.k, self.L, self.n_words, self.n_children = [int(x) for x in info]
+
+    @classmethod
+    def load_binary(cls, path):
+        lib().ygzo_voc_load_binary.restype = C.c_void_p
+        return cls(lib().ygzo_voc_load_binary(path.encode()))
+
+    @classmethod
+    def from_arrays(cls, k, L, child_start, child_list, desc, word_id, weight):
+        lib().ygzo_voc_from_arrays.restype = C.c_void_p
+        a = [np.ascontiguousarray(child_start, np.int32), np.ascontiguousarray(child_list, np.int32),
+             np.ascontiguousarray(desc, np.uint8), np.ascontiguousarray(word_id, np.int32), np.ascontiguousarray(weight, np.float64)]
+        return cls(lib().ygzo_voc_from_arrays(len(a[3]), k, L, *[_p(x) for x in a]))
+
+    def arrays(self):
+        n = self.n_nodes
+        out = {"parent": np.zeros(n, np.int32), "child_start": np.zeros(n + 1, np.int32),
+               "child_list": np.zeros(max(self.n_children, 1), np.int32), "desc": np.zeros((n, 32), np.uint8),
+               "word_id": np.zeros(n, np.int32), "weight": np.zeros(n, np.float64)}
+        lib().ygzo_voc_arrays(self.h, _p(out["parent"]), _p(out["child_start"]), _p(out["child_list"]), _p(out["desc"]),
+                              _p(out["word_id"]), _p(out["weight"]))
+        out["child_list"] = out["child_list"][:self.n_children]
+        return out
+
+    def transform(self, desc, levelsup):
+        """Returns dict: word, node (n,), weight (n,) f8; bow_word, bow_value; fv_node, fv_start, fv_feat (CSR)."""
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(desc)
+        word = np.zeros(max(n, 1), np.int32); node = np.zeros(max(n, 1), np.int32); weight = np.zeros(max(n, 1), np.float64)
+        bw = np.zeros(max(n, 1), np.int32); bv = np.zeros(max(n, 1), np.float64)
+        nn = np.zeros(1, np.int32)
+        fn = np.zeros(max(n, 1), np.int32); fs = np.zeros(n + 1, np.int32); ff = np.zeros(max(n, 1), np.int32)
+        nb = lib().ygzo_bow_transform(self.h, _p(desc), n, int(levelsup), _p(word), _p(node), _p(weight), _p(bw), _p(bv), _p(nn),
+                                      _p(fn), _p(fs), _p(ff))
+        k = int(nn[0])
+        return {"word": word[:n], "node": node[:n], "weight": weight[:n], "bow_word": bw[:nb].copy(), "bow_value": bv[:nb].copy(),
+                "fv_node": fn[:k].copy(), "fv_start": fs[:k + 1].copy(), "fv_feat": ff[:int(fs[k])].copy()}
+
+    def close(self):
+        if self.h:
+            lib().ygzo_voc_free(self.h)
+            self.h = None
+
+
+REF_BOW = os.path.join(ROOT, "oracle", "_ref", "ygz_ref_bow")
