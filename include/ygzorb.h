@@ -264,6 +264,42 @@ int ygzorb_stereo_match(ygzorb_matcher *m, ygzorb_extractor *left, ygzorb_extrac
                         const ygzorb_keypoint *kps_right, const uint8_t *desc_right, int n_right, float mbf, float mb,
                         unsigned flags, float *u_right, float *depth);
 
+/* ---- Bag of words: DBoW2::TemplatedVocabulary<cv::Mat, FORB> on the device --------------------
+ * A vocabulary is the tree of Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:98-121 (struct Node) as flat arrays: node 0 is
+ * the root; children of node i are child_list[child_start[i] .. child_start[i+1]) in the order of Node::children; a node
+ * without children is a leaf (isLeaf, :118) and carries word_id >= 0 and its weight; desc = 32 B per node. */
+typedef struct ygzorb_vocabulary ygzorb_vocabulary;
+int ygzorb_vocabulary_create(int n_nodes, int k, int L, const int32_t *child_start, const int32_t *child_list,
+                             const uint8_t *desc, const int32_t *word_id, const double *weight, int device,
+                             ygzorb_vocabulary **out);
+/* The reference's two file formats, read like TemplatedVocabulary::loadFromBinaryFile (:1478-1523; including the extra
+ * pass of its read loop, which appends the last node a second time) and ::loadFromTextFile (:1362-1448; ORBvoc.txt —
+ * blank lines are skipped, where the reference reads an uninitialised parent id from its trailing empty line).
+ * src/System.cc:183-190 picks one by file extension. */
+int ygzorb_vocabulary_load_binary(const char *path, int device, ygzorb_vocabulary **out);
+int ygzorb_vocabulary_load_text(const char *path, int device, ygzorb_vocabulary **out);
+void ygzorb_vocabulary_destroy(ygzorb_vocabulary *voc);
+/* info[0..5] = n_nodes, k, L, n_words, n_children (length of child_list), scoring*16 + weighting */
+int ygzorb_vocabulary_info(const ygzorb_vocabulary *voc, int32_t *info6);
+/* Host copies of the flat arrays (any pointer may be NULL). */
+int ygzorb_vocabulary_arrays(const ygzorb_vocabulary *voc, int32_t *child_start, int32_t *child_list, uint8_t *desc,
+                             int32_t *word_id, double *weight);
+
+/* TemplatedVocabulary::transform(features, BowVector&, FeatureVector&, levelsup) (:1149-1218, per-feature descent
+ * :1242-1282) for TF_IDF weighting and L1 scoring (the ORB vocabulary), batched over frames: frame f has n_feat[f]
+ * descriptors starting at desc + f*stride*32, as Frame::ComputeBoW passes them (src/Frame.cc:495-500).  stride <= 8192.
+ * Per feature (may be NULL): word[f*stride+i], node[f*stride+i] (the ancestor `levelsup` levels above the leaf level,
+ * 0 = root when L - levelsup <= 0), weight[f*stride+i].
+ * BowVector of frame f: bow_count[f] pairs (bow_word, bow_value)[f*stride + j] in ascending WordId — the std::map's
+ * iteration order — with the reference's doubles bit for bit (sequential += in feature order, sequential L1 norm).
+ * FeatureVector of frame f as CSR: fv_count[f] nodes, ids fv_node[f*stride + j] ascending, features of node j =
+ * fv_feat[f*stride + fv_start[f*(stride+1)+j] .. fv_start[f*(stride+1)+j+1]) in insertion order — the layout
+ * ygzorb_keyframe_features takes (node_ids, node_start, node_feats). */
+int ygzorb_bow_transform(ygzorb_matcher *m, const ygzorb_vocabulary *voc, const uint8_t *desc, const int32_t *n_feat,
+                         int n_frames, int stride, int levelsup, unsigned flags, int32_t *word, int32_t *node, double *weight,
+                         int32_t *bow_count, int32_t *bow_word, double *bow_value, int32_t *fv_count, uint32_t *fv_node,
+                         int32_t *fv_start, uint32_t *fv_feat);
+
 #ifdef __cplusplus
 }
 #endif

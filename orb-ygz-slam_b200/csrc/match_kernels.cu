@@ -9,10 +9,6 @@
 namespace ygz {
 
 // ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1507-1523): sum over 8 words of popc(a ^ b).
-__device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const uint4 b0, const uint4 b1) {
-    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
-           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
-}
 
 // Same sum with 5 POPCs: carry-save adders (LOP3 0x96 = a^b^c, 0xE8 = majority) fold six of the
 // eight XOR words into two weight-1 and two weight-2 words, then once more, so the slow POPC pipe

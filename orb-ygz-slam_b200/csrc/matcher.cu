@@ -2,7 +2,11 @@
 // marshalling between host/device buffers, and the C ABI of include/ygzorb.h.  No CPU compute path.
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstring>
+#include <fstream>
+#include <sstream>
+#include <string>
 #include <vector>
 
 #include "ygz_match.cuh"
@@ -412,6 +416,255 @@ int ygzorb_stereo_match(ygzorb_matcher *h, ygzorb_extractor *left, ygzorb_extrac
     m->launches += launchStereo(A, m->stream);
     if ((rc = copyOut(m, uRight, A.uRight, (size_t)nL, outDev))) return rc;
     if ((rc = copyOut(m, depth, A.depth, (size_t)nL, outDev))) return rc;
+    return finish(m, flags);
+}
+
+// ================================================================================================
+// Bag of words
+}  // extern "C"
+
+namespace ygz {
+
+struct Vocabulary {
+    int device = 0, k = 0, L = 0, scoring = 0, weighting = 0, nWords = 0;
+    // host copy (tree as flat arrays)
+    std::vector<int32_t> childStart, childList, wordId;
+    std::vector<double> weight;
+    std::vector<uint8_t> desc;
+    // device copy
+    int32_t *dChildStart = nullptr, *dChildList = nullptr, *dWordId = nullptr;
+    double *dWeight = nullptr;
+    uint8_t *dChildDesc = nullptr;
+};
+
+static int vocUpload(Vocabulary *v) {
+    const size_t n = v->wordId.size(), nc = v->childList.size();
+    YGZ_CUDA(cudaSetDevice(v->device));
+    std::vector<uint8_t> cdesc(std::max<size_t>(nc, 1) * 32);
+    for (size_t c = 0; c < nc; c++) memcpy(&cdesc[c * 32], &v->desc[(size_t)v->childList[c] * 32], 32);
+    YGZ_CUDA(cudaMalloc((void **)&v->dChildStart, (n + 1) * 4));
+    YGZ_CUDA(cudaMalloc((void **)&v->dChildList, std::max<size_t>(nc, 1) * 4));
+    YGZ_CUDA(cudaMalloc((void **)&v->dWordId, n * 4));
+    YGZ_CUDA(cudaMalloc((void **)&v->dWeight, n * 8));
+    YGZ_CUDA(cudaMalloc((void **)&v->dChildDesc, cdesc.size()));
+    YGZ_CUDA(cudaMemcpy(v->dChildStart, v->childStart.data(), (n + 1) * 4, cudaMemcpyHostToDevice));
+    if (nc) YGZ_CUDA(cudaMemcpy(v->dChildList, v->childList.data(), nc * 4, cudaMemcpyHostToDevice));
+    YGZ_CUDA(cudaMemcpy(v->dWordId, v->wordId.data(), n * 4, cudaMemcpyHostToDevice));
+    YGZ_CUDA(cudaMemcpy(v->dWeight, v->weight.data(), n * 8, cudaMemcpyHostToDevice));
+    YGZ_CUDA(cudaMemcpy(v->dChildDesc, cdesc.data(), cdesc.size(), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+// Validates the tree (every child id in range, reachable nodes form a tree of depth <= 32) and finishes the handle.
+static int vocFinish(Vocabulary *v, ygzorb_vocabulary **out) {
+    const int n = (int)v->wordId.size();
+    if (n < 1 || (int)v->childStart.size() != n + 1) { delete v; return argFailM("vocabulary: bad array sizes"); }
+    for (int i = 0; i < n; i++)
+        if (v->childStart[i] > v->childStart[i + 1] || v->childStart[i] < 0) { delete v; return argFailM("vocabulary: child_start is not monotone"); }
+    if (v->childStart[n] != (int)v->childList.size()) { delete v; return argFailM("vocabulary: child_start[n_nodes] != length of child_list"); }
+    for (int32_t c : v->childList)
+        if (c <= 0 || c >= n) { delete v; return argFailM("vocabulary: child id out of range"); }
+    // depth check along every root-to-leaf path (a cycle would loop the descent kernel forever)
+    std::vector<int> depth(n, -1);
+    std::vector<int> stack{0};
+    depth[0] = 0;
+    while (!stack.empty()) {
+        const int i = stack.back(); stack.pop_back();
+        for (int c = v->childStart[i]; c < v->childStart[i + 1]; c++) {
+            const int ch = v->childList[c];
+            if (depth[ch] >= 0 || depth[i] >= 32) { delete v; return argFailM("vocabulary: not a tree (shared child, cycle or depth > 32)"); }
+            depth[ch] = depth[i] + 1;
+            stack.push_back(ch);
+        }
+    }
+    v->nWords = 0;
+    for (int i = 0; i < n; i++) if (v->wordId[i] >= 0) v->nWords = std::max(v->nWords, v->wordId[i] + 1);
+    const int rc = vocUpload(v);
+    if (rc) { ygzorb_vocabulary_destroy((ygzorb_vocabulary *)v); return rc; }
+    *out = (ygzorb_vocabulary *)v;
+    return 0;
+}
+
+// children as vectors -> CSR
+static void vocFromChildren(Vocabulary *v, const std::vector<std::vector<int32_t>> &children) {
+    const size_t n = children.size();
+    v->childStart.assign(n + 1, 0);
+    v->childList.clear();
+    for (size_t i = 0; i < n; i++) {
+        v->childStart[i] = (int32_t)v->childList.size();
+        v->childList.insert(v->childList.end(), children[i].begin(), children[i].end());
+    }
+    v->childStart[n] = (int32_t)v->childList.size();
+}
+
+}  // namespace ygz
+
+extern "C" {
+
+int ygzorb_vocabulary_create(int nNodes, int k, int L, const int32_t *childStart, const int32_t *childList, const uint8_t *desc,
+                             const int32_t *wordId, const double *weight, int device, ygzorb_vocabulary **out) {
+    if (!out || !childStart || !desc || !wordId || !weight || nNodes < 1) return argFailM("null argument");
+    if (L < 0 || L > 32) return argFailM("vocabulary: L must be in [0, 32]");
+    Vocabulary *v = new Vocabulary();
+    v->device = device; v->k = k; v->L = L;
+    v->childStart.assign(childStart, childStart + nNodes + 1);
+    const int nc = childStart[nNodes];
+    if (nc < 0 || (nc > 0 && !childList)) { delete v; return argFailM("vocabulary: bad child list"); }
+    v->childList.assign(childList, childList + nc);
+    v->desc.assign(desc, desc + (size_t)nNodes * 32);
+    v->wordId.assign(wordId, wordId + nNodes);
+    v->weight.assign(weight, weight + nNodes);
+    return vocFinish(v, out);
+}
+
+int ygzorb_vocabulary_load_binary(const char *path, int device, ygzorb_vocabulary **out) {
+    if (!path || !out) return argFailM("null argument");
+    FILE *f = fopen(path, "rb");
+    if (!f) return argFailM("vocabulary: cannot open file");
+    uint32_t nbNodes = 0, sizeNode = 0;
+    int32_t hdr[4] = {0, 0, 0, 0};   // m_k, m_L, m_scoring, m_weighting (:1483-1486)
+    if (fread(&nbNodes, 4, 1, f) != 1 || fread(&sizeNode, 4, 1, f) != 1 || fread(hdr, 4, 4, f) != 4 || sizeNode < 41 ||
+        nbNodes > (1u << 28)) { fclose(f); return argFailM("vocabulary: not a binary vocabulary file"); }
+    Vocabulary *v = new Vocabulary();
+    v->device = device; v->k = hdr[0]; v->L = hdr[1]; v->scoring = hdr[2]; v->weighting = hdr[3];
+    const size_t n = (size_t)nbNodes + 1;                  // m_nodes.resize(nb_nodes + 1) (:1492)
+    std::vector<std::vector<int32_t>> children(n);
+    v->wordId.assign(n, -1); v->weight.assign(n, 0.0); v->desc.assign(n * 32, 0);
+    std::vector<char> buf(sizeNode, 0);
+    size_t nid = 1;
+    int nWords = 0;
+    bool eof = false, bad = false;
+    while (!eof && nid < n) {                              // while (!f.eof()) { f.read(buf, size_node); ... } (:1496-1515)
+        if (fread(buf.data(), 1, sizeNode, f) < sizeNode) eof = true;   // the record of the previous pass stays in buf
+        int32_t par; memcpy(&par, buf.data(), 4);
+        if (par < 0 || (size_t)par >= n || (size_t)par == nid) { bad = true; break; }
+        children[par].push_back((int32_t)nid);
+        memcpy(&v->desc[nid * 32], buf.data() + 4, 32);
+        float w; memcpy(&w, buf.data() + 36, 4);
+        v->weight[nid] = w;
+        if (buf[40]) v->wordId[nid] = nWords++;
+        nid++;
+    }
+    fclose(f);
+    if (bad) { delete v; return argFailM("vocabulary: parent id out of range"); }
+    vocFromChildren(v, children);
+    return vocFinish(v, out);
+}
+
+int ygzorb_vocabulary_load_text(const char *path, int device, ygzorb_vocabulary **out) {
+    if (!path || !out) return argFailM("null argument");
+    std::ifstream f(path);
+    if (!f.is_open()) return argFailM("vocabulary: cannot open file");
+    std::string line;
+    std::getline(f, line);
+    std::stringstream ss(line);
+    int k = -1, L = -1, n1 = -1, n2 = -1;
+    ss >> k >> L >> n1 >> n2;
+    if (k < 0 || k > 20 || L < 1 || L > 10 || n1 < 0 || n1 > 5 || n2 < 0 || n2 > 3)   // :1383-1387
+        return argFailM("vocabulary: this is not a correct text file");
+    Vocabulary *v = new Vocabulary();
+    v->device = device; v->k = k; v->L = L; v->scoring = n1; v->weighting = n2;
+    std::vector<std::vector<int32_t>> children(1);
+    v->wordId.assign(1, -1); v->weight.assign(1, 0.0); v->desc.assign(32, 0);
+    int nWords = 0;
+    bool bad = false;
+    while (std::getline(f, line)) {
+        if (line.find_first_not_of(" \t\r\n") == std::string::npos) continue;
+        std::stringstream sn(line);
+        int pid = -1, isLeaf = 0;
+        sn >> pid >> isLeaf;
+        const int nid = (int)children.size();
+        if (sn.fail() || pid < 0 || pid >= nid) { bad = true; break; }
+        children.emplace_back();
+        children[pid].push_back(nid);
+        v->desc.resize((size_t)(nid + 1) * 32, 0);
+        for (int i = 0; i < 32; i++) {                    // F::fromString (FORB.cpp:121-138)
+            int e = 0;
+            sn >> e;
+            if (!sn.fail()) v->desc[(size_t)nid * 32 + i] = (uint8_t)e;
+        }
+        double w = 0.0;
+        sn >> w;
+        v->weight.push_back(w);
+        v->wordId.push_back(isLeaf > 0 ? nWords++ : -1);
+    }
+    if (bad) { delete v; return argFailM("vocabulary: malformed node line"); }
+    vocFromChildren(v, children);
+    return vocFinish(v, out);
+}
+
+void ygzorb_vocabulary_destroy(ygzorb_vocabulary *h) {
+    Vocabulary *v = (Vocabulary *)h;
+    if (!v) return;
+    cudaSetDevice(v->device);
+    void *bufs[] = {v->dChildStart, v->dChildList, v->dWordId, v->dWeight, v->dChildDesc};
+    for (void *p : bufs) if (p) cudaFree(p);
+    delete v;
+}
+
+int ygzorb_vocabulary_info(const ygzorb_vocabulary *h, int32_t *info6) {
+    const Vocabulary *v = (const Vocabulary *)h;
+    if (!v || !info6) return argFailM("null argument");
+    info6[0] = (int32_t)v->wordId.size(); info6[1] = v->k; info6[2] = v->L; info6[3] = v->nWords;
+    info6[4] = (int32_t)v->childList.size(); info6[5] = v->scoring * 16 + v->weighting;
+    return 0;
+}
+
+int ygzorb_vocabulary_arrays(const ygzorb_vocabulary *h, int32_t *childStart, int32_t *childList, uint8_t *desc, int32_t *wordId,
+                             double *weight) {
+    const Vocabulary *v = (const Vocabulary *)h;
+    if (!v) return argFailM("null argument");
+    const size_t n = v->wordId.size();
+    if (childStart) memcpy(childStart, v->childStart.data(), (n + 1) * 4);
+    if (childList && !v->childList.empty()) memcpy(childList, v->childList.data(), v->childList.size() * 4);
+    if (desc) memcpy(desc, v->desc.data(), n * 32);
+    if (wordId) memcpy(wordId, v->wordId.data(), n * 4);
+    if (weight) memcpy(weight, v->weight.data(), n * 8);
+    return 0;
+}
+
+int ygzorb_bow_transform(ygzorb_matcher *h, const ygzorb_vocabulary *vh, const uint8_t *desc, const int32_t *nFeat, int nFrames,
+                         int stride, int levelsup, unsigned flags, int32_t *word, int32_t *node, double *weight, int32_t *bowCount,
+                         int32_t *bowWord, double *bowValue, int32_t *fvCount, uint32_t *fvNode, int32_t *fvStart, uint32_t *fvFeat) {
+    Matcher *m = (Matcher *)h;
+    const Vocabulary *v = (const Vocabulary *)vh;
+    if (!m || !v || !nFeat || (nFrames > 0 && !desc)) return argFailM("null argument");
+    if (!bowCount || !bowWord || !bowValue || !fvCount || !fvNode || !fvStart || !fvFeat) return argFailM("null output pointer");
+    if (nFrames < 0 || stride < 1 || stride > 8192) return argFailM("stride must be in [1, 8192]");
+    if (v->device != m->device) return argFailM("vocabulary and matcher live on different devices");
+    if (nFrames == 0) return 0;
+    YGZ_CUDA(cudaSetDevice(m->device));
+    const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
+    const size_t nf = nFrames, ns = nf * stride;
+    BowArgs A;
+    memset(&A, 0, sizeof A);
+    A.nFrames = nFrames; A.stride = stride; A.L = v->L; A.levelsup = levelsup;
+    A.childStart = v->dChildStart; A.childList = v->dChildList; A.childDesc = v->dChildDesc; A.wordId = v->dWordId;
+    A.nodeWeight = v->dWeight;
+    int rc;
+    if ((rc = stageIn(m, 0, nFeat, nf, inDev, &A.nFeat))) return rc;
+    if ((rc = stageIn(m, 1, desc, ns * 32, inDev, &A.desc))) return rc;
+    if ((rc = stageOut(m, 2, word, ns, outDev, &A.word))) return rc;
+    if ((rc = stageOut(m, 3, node, ns, outDev, &A.node))) return rc;
+    if ((rc = stageOut(m, 4, weight, ns, outDev, &A.weight))) return rc;
+    if ((rc = stageOut(m, 5, bowCount, nf, outDev, &A.bowCount))) return rc;
+    if ((rc = stageOut(m, 6, bowWord, ns, outDev, &A.bowWord))) return rc;
+    if ((rc = stageOut(m, 7, bowValue, ns, outDev, &A.bowValue))) return rc;
+    if ((rc = stageOut(m, 8, fvCount, nf, outDev, &A.fvCount))) return rc;
+    if ((rc = stageOut(m, 9, fvNode, ns, outDev, &A.fvNode))) return rc;
+    if ((rc = stageOut(m, 10, fvStart, nf * (stride + 1), outDev, &A.fvStart))) return rc;
+    if ((rc = stageOut(m, 11, fvFeat, ns, outDev, &A.fvFeat))) return rc;
+    m->launches += launchBowTransform(A, m->stream);
+    if ((rc = copyOut(m, word, A.word, ns, outDev))) return rc;
+    if ((rc = copyOut(m, node, A.node, ns, outDev))) return rc;
+    if ((rc = copyOut(m, weight, A.weight, ns, outDev))) return rc;
+    if ((rc = copyOut(m, bowCount, A.bowCount, nf, outDev))) return rc;
+    if ((rc = copyOut(m, bowWord, A.bowWord, ns, outDev))) return rc;
+    if ((rc = copyOut(m, bowValue, A.bowValue, ns, outDev))) return rc;
+    if ((rc = copyOut(m, fvCount, A.fvCount, nf, outDev))) return rc;
+    if ((rc = copyOut(m, fvNode, A.fvNode, ns, outDev))) return rc;
+    if ((rc = copyOut(m, fvStart, A.fvStart, nf * (stride + 1), outDev))) return rc;
+    if ((rc = copyOut(m, fvFeat, A.fvFeat, ns, outDev))) return rc;
     return finish(m, flags);
 }
 

@@ -82,6 +82,30 @@ int launchKnn2(const uint8_t *query, int nq, const uint8_t *train, int nt, float
                int variant, int32_t *bestIdx, int32_t *d1, int32_t *d2, int32_t *match, cudaStream_t s);
 int launchSearchByProjection(const ProjArgs &A, int maxKp, cudaStream_t s);
 int launchSearchByProjectionLast(const ProjArgs &A, cudaStream_t s);
+
+#ifdef __CUDACC__
+// ORBmatcher::DescriptorDistance / FORB::distance on two 256-bit rows held as 2 x uint4
+__device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const uint4 b0, const uint4 b1) {
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+#endif
+
+// Bag-of-words transform (bow_kernels.cu).  Vocabulary arrays are device pointers owned by a ygzorb_vocabulary.
+struct BowArgs {
+    int nFrames, stride, L, levelsup;
+    const int32_t *nFeat;
+    const uint8_t *desc;
+    const int32_t *childStart, *childList;    // CSR of the tree; children of node i: childList[childStart[i] .. childStart[i+1])
+    const uint8_t *childDesc;                 // 32 B per child-list entry (descriptor of childList[c])
+    const int32_t *wordId;                    // per node, -1 for inner nodes
+    const double *nodeWeight;                 // per node
+    int32_t *word, *node;                     // per feature
+    double *weight;
+    int32_t *bowCount, *bowWord; double *bowValue;
+    int32_t *fvCount; uint32_t *fvNode; int32_t *fvStart; uint32_t *fvFeat;
+};
+int launchBowTransform(const BowArgs &A, cudaStream_t s);
 int launchTriangulation(const TriArgs &A, cudaStream_t s);
 int launchStereo(const StereoArgs &A, cudaStream_t s);
 int configureMatchKernels();

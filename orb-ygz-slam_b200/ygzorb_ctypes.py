@@ -411,6 +411,73 @@ class Matcher:
         return ur[:n].copy(), dp[:n].copy()
 
 
+class Vocabulary:
+    """Device-resident DBoW2 vocabulary tree (include/ygzorb.h, bag-of-words section)."""
+
+    def __init__(self, handle):
+        self.h = handle
+        info = np.zeros(6, np.int32)
+        check(lib().ygzorb_vocabulary_info(self.h, _ptr(info)))
+        self.n_nodes, self.k, self.L, self.n_words, self.n_children = [int(x) for x in info[:5]]
+
+    @classmethod
+    def from_arrays(cls, k, L, child_start, child_list, desc, word_id, weight, device=0):
+        a = [np.ascontiguousarray(child_start, np.int32), np.ascontiguousarray(child_list, np.int32),
+             np.ascontiguousarray(desc, np.uint8), np.ascontiguousarray(word_id, np.int32), np.ascontiguousarray(weight, np.float64)]
+        h = C.c_void_p()
+        check(lib().ygzorb_vocabulary_create(len(a[3]), int(k), int(L), *[C.c_void_p(_ptr(x)) for x in a], device, C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def load_binary(cls, path, device=0):
+        h = C.c_void_p()
+        check(lib().ygzorb_vocabulary_load_binary(path.encode(), device, C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def load_text(cls, path, device=0):
+        h = C.c_void_p()
+        check(lib().ygzorb_vocabulary_load_text(path.encode(), device, C.byref(h)))
+        return cls(h)
+
+    def arrays(self):
+        n = self.n_nodes
+        out = {"child_start": np.zeros(n + 1, np.int32), "child_list": np.zeros(max(self.n_children, 1), np.int32),
+               "desc": np.zeros((n, 32), np.uint8), "word_id": np.zeros(n, np.int32), "weight": np.zeros(n, np.float64)}
+        check(lib().ygzorb_vocabulary_arrays(self.h, *[C.c_void_p(_ptr(out[k])) for k in
+                                                       ("child_start", "child_list", "desc", "word_id", "weight")]))
+        out["child_list"] = out["child_list"][:self.n_children]
+        return out
+
+    def close(self):
+        if self.h:
+            lib().ygzorb_vocabulary_destroy(self.h)
+            self.h = None
+
+
+def bow_transform(matcher, voc, frames, levelsup, stride=None):
+    """frames: list of (n_i, 32) uint8 descriptor arrays.  Returns per frame the dict tests/oracle_lib.Vocabulary.transform
+    returns (word, node, weight, bow_word, bow_value, fv_node, fv_start, fv_feat)."""
+    nf = len(frames)
+    st = stride or max(max((len(f) for f in frames), default=1), 1)
+    desc = np.zeros((nf, st, 32), np.uint8)
+    n_feat = np.array([len(f) for f in frames], np.int32)
+    for i, f in enumerate(frames):
+        desc[i, :len(f)] = f
+    word = np.zeros((nf, st), np.int32); node = np.zeros((nf, st), np.int32); weight = np.zeros((nf, st), np.float64)
+    bc = np.zeros(nf, np.int32); bw = np.zeros((nf, st), np.int32); bv = np.zeros((nf, st), np.float64)
+    fc = np.zeros(nf, np.int32); fn = np.zeros((nf, st), np.uint32); fs = np.zeros((nf, st + 1), np.int32); ff = np.zeros((nf, st), np.uint32)
+    check(lib().ygzorb_bow_transform(matcher.h, voc.h, C.c_void_p(_ptr(desc)), C.c_void_p(_ptr(n_feat)), nf, st, int(levelsup), 0,
+                                     *[C.c_void_p(_ptr(a)) for a in (word, node, weight, bc, bw, bv, fc, fn, fs, ff)]))
+    out = []
+    for i in range(nf):
+        n, nb, nn = int(n_feat[i]), int(bc[i]), int(fc[i])
+        out.append({"word": word[i, :n].copy(), "node": node[i, :n].copy(), "weight": weight[i, :n].copy(),
+                    "bow_word": bw[i, :nb].copy(), "bow_value": bv[i, :nb].copy(), "fv_node": fn[i, :nn].astype(np.int32),
+                    "fv_start": fs[i, :nn + 1].copy(), "fv_feat": ff[i, :int(fs[i, nn])].astype(np.int32)})
+    return out
+
+
 def hamming_knn2(query, train, ratio, th, device=0):
     m = Matcher(device)
     try:
