@@ -1,7 +1,9 @@
 // host_demo.cc — exercises the drop-in C++ classes the way the reference's callers do
 // (Frame::ExtractORB src/Frame.cc:332-348, Tracking::SearchLocalPoints src/Tracking.cc:1662-1674,
 // Frame::ComputeStereoMatches src/Frame.cc:747) and dumps the results for tests/test_gpu_host.py.
-// usage: host_demo <in.bin> <out.bin>
+// usage: host_demo <in.bin> <out.bin> [voc.bin bow_out.bin]
+//   with a vocabulary (binary format): Frame::ComputeBoW (src/Frame.cc:495-500) on the left descriptors ->
+//   bow_out.bin: int32 nb | nb x {int32 word, double value} | int32 nn | nn x {int32 node, int32 cnt, cnt x int32 feature}
 //   in.bin : int32 w, h, nfeatures, nMP | left image w*h | right image w*h |
 //            nMP x {float projX, projY, viewCos; int32 level; 32 B descriptor} |
 //            int32 nLast | 30 float pose | nLast x {float wx, wy, wz, angle; int32 octave, valid, hasObs; 32 B descriptor}
@@ -15,6 +17,7 @@
 #include "FrameLite.h"
 #include "ORBextractor.h"
 #include "ORBmatcher.h"
+#include "ORBVocabulary.h"
 
 using namespace ygz;
 
@@ -107,6 +110,28 @@ int main(int argc, char **argv) {
     wr(fo, &nml, 1);
     for (int i = 0; i < nL; i++) { int32_t idx = F.mvpMapPoints[i] ? (int32_t)(F.mvpMapPoints[i] - lastMps.data()) : -1; wr(fo, &idx, 1); }
     fclose(fo);
+    if (argc >= 5) {
+        ORBVocabulary voc;
+        if (!voc.loadFromBinaryFile(argv[3])) { fprintf(stderr, "cannot load vocabulary\n"); return 2; }
+        std::vector<cv::Mat> vCurrentDesc;                    // Converter::toDescriptorVector (src/Frame.cc:497)
+        for (int i = 0; i < F.mDescriptors.rows; i++) vCurrentDesc.push_back(F.mDescriptors.row(i));
+        DBoW2::BowVector bowVec;
+        DBoW2::FeatureVector featVec;
+        voc.transform(vCurrentDesc, bowVec, featVec, 4);
+        FILE *fb = fopen(argv[4], "wb");
+        int32_t nb = (int32_t)bowVec.size();
+        wr(fb, &nb, 1);
+        for (const auto &e : bowVec) { int32_t w = (int32_t)e.first; double v = e.second; wr(fb, &w, 1); wr(fb, &v, 1); }
+        int32_t nn = (int32_t)featVec.size();
+        wr(fb, &nn, 1);
+        for (const auto &e : featVec) {
+            int32_t a[2] = {(int32_t)e.first, (int32_t)e.second.size()};
+            wr(fb, a, 2);
+            for (unsigned idx : e.second) { int32_t ii = (int32_t)idx; wr(fb, &ii, 1); }
+        }
+        fclose(fb);
+        printf("host_demo: vocabulary with %u words, BowVector %d words, FeatureVector %d nodes\n", voc.size(), nb, nn);
+    }
     printf("host_demo: %d left / %d right keypoints, %d projection matches, %d motion-model matches, DescriptorDistance(self)=%d\n", nL, nR, nmatches, nmatchesLast,
            nL ? ORBmatcher::DescriptorDistance(F.mDescriptors.row(0), F.mDescriptors.row(0)) : 0);
     return 0;

@@ -43,9 +43,15 @@ def test_host_classes_end_to_end():
             lrec["q"][:, 0] = last["octave"]; lrec["q"][:, 1] = last["valid"]; lrec["q"][:, 2] = last["has_obs"]
             lrec["d"] = last["desc"]
             lrec.tofile(f)
-        res = subprocess.run([DEMO, fin, fout], capture_output=True, text=True)
+        # a vocabulary file in the reference's binary format: the golden one its own DBoW2 wrote (k=10, L=3)
+        g = np.load(os.path.join(O.ROOT, "tests", "golden", "bow_k10L3.npz"))
+        fvoc, fbow = os.path.join(td, "voc.bin"), os.path.join(td, "bow.bin")
+        open(fvoc, "wb").write(g["voc_bin"].tobytes())
+        res = subprocess.run([DEMO, fin, fout, fvoc, fbow], capture_output=True, text=True)
         assert res.returncode == 0, res.stdout + res.stderr
         buf = open(fout, "rb").read()
+        bowbuf = open(fbow, "rb").read()
+        ovoc = O.Vocabulary.load_binary(fvoc)
     off = 0
 
     def take(dtype, n):
@@ -68,3 +74,16 @@ def test_host_classes_end_to_end():
     gnml = int(take("<i4", 1)[0]); gassign_last = take("<i4", nL)
     nml, kp_to_pt, _ = O.search_by_projection_last(kl, dl, None, None, (0.0, 0.0, float(w), float(h)), sf, last, 15.0, True, True, True)
     assert gnml == nml and np.array_equal(gassign_last, kp_to_pt) and nml > 300
+    # ORBVocabulary::transform through the host class == the oracle (pinned to DBoW2) on the same descriptors
+    want = ovoc.transform(dl, 4)
+    nb = int(np.frombuffer(bowbuf, "<i4", 1, 0)[0])
+    b = np.frombuffer(bowbuf, np.dtype([("w", "<i4"), ("v", "<f8")]), nb, 4)
+    assert np.array_equal(b["w"], want["bow_word"]) and b["v"].tobytes() == want["bow_value"].tobytes() and nb > 100
+    o = 4 + nb * 12
+    nn = int(np.frombuffer(bowbuf, "<i4", 1, o)[0]); o += 4
+    assert nn == len(want["fv_node"])
+    for j in range(nn):
+        node, cnt = np.frombuffer(bowbuf, "<i4", 2, o); o += 8
+        feats = np.frombuffer(bowbuf, "<i4", int(cnt), o); o += 4 * int(cnt)
+        assert node == want["fv_node"][j] and np.array_equal(feats, want["fv_feat"][want["fv_start"][j]:want["fv_start"][j + 1]])
+    ovoc.close()
