@@ -134,3 +134,42 @@ def features_near_nodes(tree, n, seed, flips=30):
     leaves = np.nonzero(tree["word_id"] >= 0)[0]
     src = rng.choice(leaves, size=n)
     return synth.flip_bits(tree["desc"][src], rng.integers(0, flips + 1, size=n), rng)
+
+
+def full_tree(k, L, seed, p_zero=0.02):
+    """Full k-ary tree of depth L in BFS NodeId order (the shape of ORBvoc: k=10, L=6 -> 1,111,111 nodes), vectorised."""
+    rng = np.random.default_rng(seed)
+    sizes = [k ** l for l in range(L + 1)]
+    n = sum(sizes)
+    n_inner = n - sizes[-1]
+    child_start = np.zeros(n + 1, np.int64)
+    child_start[1:n_inner + 1] = np.arange(1, n_inner + 1) * k
+    child_start[n_inner + 1:] = n_inner * k
+    child_list = np.arange(1, n, dtype=np.int32)
+    desc = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    desc[0] = 0
+    word = np.full(n, -1, np.int32)
+    word[n_inner:] = np.arange(sizes[-1], dtype=np.int32)
+    weight = np.zeros(n, np.float64)
+    w = rng.uniform(0.1, 9.0, sizes[-1]).astype(np.float32).astype(np.float64)
+    w[rng.uniform(size=sizes[-1]) < p_zero] = 0.0
+    weight[n_inner:] = w
+    parent = np.zeros(n, np.int32)
+    parent[1:] = (np.arange(1, n) - 1) // k
+    return {"k": k, "L": L, "child_start": child_start.astype(np.int32), "child_list": child_list, "desc": desc, "word_id": word,
+            "weight": weight, "parent": parent}
+
+
+def write_binary_voc(path, tree):
+    """TemplatedVocabulary::saveToBinaryFile layout (TemplatedVocabulary.h:1528-1550): header nb_nodes, size_node, k, L,
+    scoring, weighting; per node 1..n-1: int32 parent, 32 B descriptor, float weight, bool isLeaf.  Needs tree['parent']."""
+    n = len(tree["word_id"])
+    rec = np.zeros(n - 1, np.dtype([("parent", "<i4"), ("desc", "u1", 32), ("weight", "<f4"), ("leaf", "u1")]))
+    rec["parent"] = tree["parent"][1:]
+    rec["desc"] = tree["desc"][1:]
+    rec["weight"] = tree["weight"][1:].astype(np.float32)
+    rec["leaf"] = (tree["child_start"][1:n] == tree["child_start"][2:n + 1]).astype(np.uint8)
+    with open(path, "wb") as f:
+        np.array([n, rec.dtype.itemsize], np.uint32).tofile(f)
+        np.array([tree["k"], tree["L"], 0, 0], np.int32).tofile(f)      # L1_NORM = 0, TF_IDF = 0 (BowVector.h:30-47)
+        rec.tofile(f)
