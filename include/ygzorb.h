@@ -255,6 +255,20 @@ int ygzorb_search_for_triangulation(ygzorb_matcher *m, const ygzorb_keyframe_fea
                                     int only_stereo, int check_orientation, unsigned flags, int32_t *matches12,
                                     int32_t *n_matches);
 
+/* ORBmatcher::SearchByBoW, both overloads, over FeatureVectors flattened like above (the output of
+ * ygzorb_bow_transform plugs in directly):
+ *   second_is_frame = 1: SearchByBoW(KeyFrame *pKF, Frame &F, vector<MapPoint*> &vpMapPointMatches)
+ *     (src/ORBmatcher.cc:155-263; Tracking::TrackReferenceKeyFrame, Relocalization).  kf1->has_mappoint = the
+ *     keyframe's MapPoint exists and !isBad(); matches[iF] (length second->n) = keyframe keypoint whose MapPoint frame
+ *     feature iF received, or -1.  Accepts bestDist1 <= TH_LOW and bestDist1 < nnratio * bestDist2.
+ *   second_is_frame = 0: SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, vector<MapPoint*> &vpMatches12) (:480-596;
+ *     LoopClosing).  has_mappoint on both sides; matches[idx1] (length kf1->n) = matched keypoint of KF2, or -1.
+ *     Accepts bestDist1 < TH_LOW (strict, as written there) and the ratio.
+ * u_right, scale_factors and level_sigma2 of the views are not read.  *n_matches = return value. */
+int ygzorb_search_by_bow(ygzorb_matcher *m, const ygzorb_keyframe_features *kf1, const ygzorb_keyframe_features *second,
+                         int second_is_frame, float nnratio, int check_orientation, unsigned flags, int32_t *matches,
+                         int32_t *n_matches);
+
 /* Frame::ComputeStereoMatches() (src/Frame.cc:509-682).  The patch search reads the pyramids of the
  * Left and Right extractors (mpORBextractorLeft/Right->mvImagePyramid, :604-623): frame `frame` of the
  * last batch of `left` / `right`.  kps/desc: mvKeys / mDescriptors and mvKeysRight / mDescriptorsRight.

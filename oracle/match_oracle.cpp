@@ -266,6 +266,67 @@ YGZO_API int ygzo_search_by_projection_last(const void *kpsV, const uint8_t *des
     return nmatches;
 }
 
+// ORBmatcher::SearchByBoW — both overloads over flattened FeatureVectors (CSR, ascending NodeId):
+//   secondIsFrame = 1: SearchByBoW(KeyFrame *pKF, Frame &F, vector<MapPoint*> &vpMapPointMatches), src/ORBmatcher.cc:155-263.
+//     hasMP1 = the keyframe's MapPoint exists and !isBad(); frame features already matched in this call are skipped;
+//     accept bestDist1 <= TH_LOW and ratio; matches[iF] (length n2) = keyframe index whose MapPoint the frame feature got.
+//   secondIsFrame = 0: SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, vector<MapPoint*> &vpMatches12), :480-596.
+//     hasMP = MapPoint exists and !isBad() on both sides; vbMatched2 blocks reuse; accept bestDist1 < TH_LOW (strict) and
+//     ratio; matches[idx1] (length n1) = matched keypoint of KF2.
+// Returns nmatches (after the rotation-histogram rejection).
+YGZO_API int ygzo_search_by_bow(const void *kps1V, const uint8_t *desc1, const uint8_t *hasMP1, int n1, const uint32_t *nodeIds1,
+                                const int32_t *start1, const uint32_t *feats1, int nNodes1, const void *kps2V,
+                                const uint8_t *desc2, const uint8_t *hasMP2, int n2, const uint32_t *nodeIds2,
+                                const int32_t *start2, const uint32_t *feats2, int nNodes2, int secondIsFrame, float nnratio,
+                                int checkOrientation, int32_t *matches) {
+    const KeyPoint *kps1 = (const KeyPoint *)kps1V, *kps2 = (const KeyPoint *)kps2V;
+    const int nOut = secondIsFrame ? n2 : n1;
+    for (int i = 0; i < nOut; i++) matches[i] = -1;
+    std::vector<uint8_t> taken2(std::max(n2, 1), 0);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    int nmatches = 0, a = 0, b = 0;
+    while (a < nNodes1 && b < nNodes2) {
+        if (nodeIds1[a] == nodeIds2[b]) {
+            for (int i1 = start1[a]; i1 < start1[a + 1]; i1++) {
+                const int idx1 = (int)feats1[i1];
+                if (!hasMP1[idx1]) continue;
+                int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+                for (int i2 = start2[b]; i2 < start2[b + 1]; i2++) {
+                    const int idx2 = (int)feats2[i2];
+                    if (taken2[idx2]) continue;
+                    if (!secondIsFrame && !hasMP2[idx2]) continue;
+                    const int dist = descriptorDistance(desc1 + (size_t)idx1 * 32, desc2 + (size_t)idx2 * 32);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = idx2; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+                const bool near = secondIsFrame ? bestDist1 <= TH_LOW : bestDist1 < TH_LOW;
+                if (near && (float)bestDist1 < nnratio * (float)bestDist2) {
+                    taken2[bestIdx2] = 1;
+                    const int slot = secondIsFrame ? bestIdx2 : idx1;
+                    matches[slot] = secondIsFrame ? idx1 : bestIdx2;
+                    if (checkOrientation) rotHist[rotationBin(kps1[idx1].angle, kps2[bestIdx2].angle)].push_back(slot);
+                    nmatches++;
+                }
+            }
+            a++; b++;
+        } else if (nodeIds1[a] < nodeIds2[b]) {
+            a = (int)(std::lower_bound(nodeIds1, nodeIds1 + nNodes1, nodeIds2[b]) - nodeIds1);
+        } else {
+            b = (int)(std::lower_bound(nodeIds2, nodeIds2 + nNodes2, nodeIds1[a]) - nodeIds2);
+        }
+    }
+    if (checkOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1, sizes[HISTO_LENGTH];
+        for (int i = 0; i < HISTO_LENGTH; i++) sizes[i] = (int)rotHist[i].size();
+        threeMaxima(sizes, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int slot : rotHist[i]) { matches[slot] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
 // ORBmatcher::SearchForTriangulation — src/ORBmatcher.cc:597-746 with CheckDistEpipolarLine (:136-153).
 // The two DBoW2::FeatureVectors (std::map<NodeId, vector<unsigned>>, ascending NodeId) are flattened
 // to CSR: nodeIds[k] ascending, features of node k = feats[start[k] .. start[k+1]).  hasMP = the

@@ -624,6 +624,88 @@ __global__ void __launch_bounds__(kTriThreads) k_triangulation(const __grid_cons
     if (tid == 0) *A.nMatches = total;
 }
 
+// K9b — ORBmatcher::SearchByBoW, both overloads (src/ORBmatcher.cc:155-263 keyframe -> frame, :480-596 keyframe ->
+// keyframe).  A feature sits in exactly one vocabulary node, so the "already matched" flags of side 2 only couple the
+// side-1 features of the SAME node: one thread per common node runs the reference's two nested loops in order, nodes
+// run in parallel.  Rotation histogram and ComputeThreeMaxima as in K9.  One CTA (the call is ~1-2k keypoints).
+__global__ void __launch_bounds__(kTriThreads) k_search_by_bow(const __grid_constant__ TriArgs A) {
+    __shared__ int hist[kHistoLength];
+    __shared__ int keep[3];
+    __shared__ int total;
+    const int tid = threadIdx.x;
+    const KfView &K1 = A.kf1, &K2 = A.kf2;
+    const bool frame2 = A.onlyStereo != 0;          // secondIsFrame rides in the onlyStereo slot
+    const int nOut = frame2 ? K2.n : K1.n;
+    for (int i = tid; i < nOut; i += kTriThreads) A.matches12[i] = -1;
+    for (int i = tid; i < K2.n; i += kTriThreads) A.nodeOf1[i] = 0;     // taken2 flags
+    if (tid < kHistoLength) hist[tid] = 0;
+    if (tid == 0) total = 0;
+    __syncthreads();
+    const uint4 *desc1 = reinterpret_cast<const uint4 *>(K1.desc), *desc2 = reinterpret_cast<const uint4 *>(K2.desc);
+    int mine = 0;
+    for (int a = tid; a < K1.nNodes; a += kTriThreads) {
+        const uint32_t id = K1.nodeIds[a];
+        int lo = 0, hi = K2.nNodes;
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (K2.nodeIds[mid] < id) lo = mid + 1; else hi = mid; }
+        if (lo >= K2.nNodes || K2.nodeIds[lo] != id) continue;
+        for (int i1 = K1.nodeStart[a]; i1 < K1.nodeStart[a + 1]; i1++) {
+            const int idx1 = K1.nodeFeats[i1];
+            if (!K1.hasMP[idx1]) continue;
+            const uint4 d0 = desc1[2 * idx1], d1 = desc1[2 * idx1 + 1];
+            int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+            for (int i2 = K2.nodeStart[lo]; i2 < K2.nodeStart[lo + 1]; i2++) {
+                const int idx2 = K2.nodeFeats[i2];
+                if (A.nodeOf1[idx2]) continue;
+                if (!frame2 && !K2.hasMP[idx2]) continue;
+                const int dist = hamming256(d0, d1, desc2[2 * idx2], desc2[2 * idx2 + 1]);
+                if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = idx2; }
+                else if (dist < bestDist2) bestDist2 = dist;
+            }
+            const bool near = frame2 ? bestDist1 <= kThLow : bestDist1 < kThLow;
+            if (near && (float)bestDist1 < __fmul_rn(A.nnratio, (float)bestDist2)) {
+                A.nodeOf1[bestIdx2] = 1;
+                const int slot = frame2 ? bestIdx2 : idx1;
+                A.matches12[slot] = frame2 ? idx1 : bestIdx2;
+                if (A.checkOrientation) atomicAdd(&hist[rotationBinDev(K1.kps[idx1].angle, K2.kps[bestIdx2].angle)], 1);
+                mine++;
+            }
+        }
+    }
+    if (mine) atomicAdd(&total, mine);
+    __syncthreads();
+    if (A.checkOrientation) {
+        if (tid == 0) {   // ComputeThreeMaxima
+            int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+            for (int i = 0; i < kHistoLength; i++) {
+                const int sz = hist[i];
+                if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
+                else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
+                else if (sz > max3) { max3 = sz; ind3 = i; }
+            }
+            if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+            else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
+            keep[0] = ind1; keep[1] = ind2; keep[2] = ind3;
+        }
+        __syncthreads();
+        int dropped = 0;
+        for (int slot = tid; slot < nOut; slot += kTriThreads) {
+            const int m = A.matches12[slot];
+            if (m < 0) continue;
+            const int idx1 = frame2 ? m : slot, idx2 = frame2 ? slot : m;
+            const int bin = rotationBinDev(K1.kps[idx1].angle, K2.kps[idx2].angle);
+            if (bin != keep[0] && bin != keep[1] && bin != keep[2]) { A.matches12[slot] = -1; dropped++; }
+        }
+        if (dropped) atomicSub(&total, dropped);
+        __syncthreads();
+    }
+    if (tid == 0) *A.nMatches = total;
+}
+
+int launchSearchByBoW(const TriArgs &A, cudaStream_t s) {
+    k_search_by_bow<<<1, kTriThreads, 0, s>>>(A);
+    return 1;
+}
+
 int launchTriangulation(const TriArgs &A, cudaStream_t s) {
     k_triangulation<<<1, kTriThreads, 0, s>>>(A);
     return 1;

@@ -419,6 +419,36 @@ int ygzorb_stereo_match(ygzorb_matcher *h, ygzorb_extractor *left, ygzorb_extrac
     return finish(m, flags);
 }
 
+int ygzorb_search_by_bow(ygzorb_matcher *h, const ygzorb_keyframe_features *K1, const ygzorb_keyframe_features *K2,
+                         int secondIsFrame, float nnratio, int checkOrientation, unsigned flags, int32_t *matches,
+                         int32_t *nMatches) {
+    Matcher *m = (Matcher *)h;
+    if (!m || !K1 || !K2 || !matches || !nMatches) return argFailM("null argument");
+    if (K1->n < 0 || K2->n < 0 || K1->n_nodes < 0 || K2->n_nodes < 0) return argFailM("bad sizes");
+    if (K1->n > 0 && (!K1->kps || !K1->desc || !K1->has_mappoint)) return argFailM("null keyframe array");
+    if (K2->n > 0 && (!K2->kps || !K2->desc || (!secondIsFrame && !K2->has_mappoint))) return argFailM("null keyframe array");
+    for (const ygzorb_keyframe_features *K : {K1, K2})
+        if (K->n_nodes > 0 && (!K->node_ids || !K->node_start || !K->node_feats)) return argFailM("null FeatureVector array");
+    YGZ_CUDA(cudaSetDevice(m->device));
+    const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
+    const size_t nOut = (size_t)(secondIsFrame ? K2->n : K1->n);
+    TriArgs A;
+    memset(&A, 0, sizeof A);
+    int rc;
+    if ((rc = stageKf(m, 0, K1, inDev, &A.kf1))) return rc;
+    if ((rc = stageKf(m, 7, K2, inDev, &A.kf2))) return rc;
+    A.onlyStereo = secondIsFrame ? 1 : 0; A.checkOrientation = checkOrientation; A.nnratio = nnratio;
+    if ((rc = stageOut(m, 14, matches, nOut, outDev, &A.matches12))) return rc;
+    if ((rc = stageOut(m, 15, nMatches, 1, outDev, &A.nMatches))) return rc;
+    void *p;
+    if ((rc = scratch(m, 16, (size_t)std::max(K2->n, 1) * 4, &p))) return rc;
+    A.nodeOf1 = (int32_t *)p;      // "already matched" flags of side 2
+    m->launches += launchSearchByBoW(A, m->stream);
+    if ((rc = copyOut(m, matches, A.matches12, nOut, outDev))) return rc;
+    if ((rc = copyOut(m, nMatches, A.nMatches, 1, outDev))) return rc;
+    return finish(m, flags);
+}
+
 // ================================================================================================
 // Bag of words
 }  // extern "C"

@@ -51,6 +51,7 @@ struct TriArgs {
     float F12[9];
     float ex, ey;
     int onlyStereo, checkOrientation;
+    float nnratio;          // SearchByBoW only
     int32_t *matches12;     // [kf1.n]
     int32_t *nodeOf1;       // scratch [kf1.n]: index into kf2's node list, or -1
     int32_t *nMatches;      // [1]
@@ -107,6 +108,7 @@ struct BowArgs {
 };
 int launchBowTransform(const BowArgs &A, cudaStream_t s);
 int launchTriangulation(const TriArgs &A, cudaStream_t s);
+int launchSearchByBoW(const TriArgs &A, cudaStream_t s);
 int launchStereo(const StereoArgs &A, cudaStream_t s);
 int configureMatchKernels();
 

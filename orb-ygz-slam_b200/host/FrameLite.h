@@ -6,6 +6,7 @@
 #include <vector>
 
 #include "cvcompat.h"
+#include "ORBVocabulary.h"
 
 namespace ygz {
 class ORBextractor;
@@ -39,10 +40,19 @@ public:
     cv::Mat mDescriptors, mDescriptorsRight;
     std::vector<float> mvuRight, mvDepth;
     std::vector<MapPointLite *> mvpMapPoints;
+    DBoW2::BowVector mBowVec;
+    DBoW2::FeatureVector mFeatVec;
     std::vector<float> mvScaleFactors, mvInvScaleFactors;
     float mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0;
     float mbf = 0, mb = 0;
     ORBextractor *mpORBextractorLeft = nullptr, *mpORBextractorRight = nullptr;
+};
+struct KeyFrameLite {                        // include/KeyFrame.h: the members SearchByBoW reads
+    std::vector<cv::KeyPoint> mvKeys;
+    cv::Mat mDescriptors;
+    DBoW2::FeatureVector mFeatVec;
+    std::vector<MapPointLite *> mvpMapPoints;
+    std::vector<MapPointLite *> GetMapPointMatches() const { return mvpMapPoints; }
 };
 }  // namespace ygz
 #endif

@@ -203,9 +203,65 @@ public:
         return nmatches;
     }
 
+    // src/ORBmatcher.cc:155-263 (Tracking::TrackReferenceKeyFrame, Relocalization).  mFeatVec of both sides is a
+    // DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>) as ORBVocabulary::transform fills it.
+    template <class KeyFrameT, class FrameT, class MapPointT>
+    int SearchByBoW(KeyFrameT *pKF, FrameT &F, std::vector<MapPointT *> &vpMapPointMatches) {
+        const std::vector<MapPointT *> vpMapPointsKF = pKF->GetMapPointMatches();
+        vpMapPointMatches.assign(F.N, nullptr);
+        BowSide a, b;
+        flattenBow(pKF->mvKeys, pKF->mDescriptors, pKF->mFeatVec, a);
+        flattenBow(F.mvKeys, F.mDescriptors, F.mFeatVec, b);
+        for (size_t i = 0; i < a.hasMP.size(); i++) a.hasMP[i] = vpMapPointsKF[i] && !vpMapPointsKF[i]->isBad();
+        std::vector<int32_t> m(std::max<size_t>(b.hasMP.size(), 1));
+        int32_t nmatches = 0;
+        if (ygzorb_search_by_bow(mHandle, &a.v, &b.v, 1, mfNNratio, mbCheckOrientation ? 1 : 0, 0, m.data(), &nmatches) != 0)
+            throw std::runtime_error(std::string("ygzorb_search_by_bow: ") + ygzorb_last_error());
+        for (int i = 0; i < F.N; i++)
+            if (m[i] >= 0) vpMapPointMatches[i] = vpMapPointsKF[m[i]];   // :209
+        return nmatches;
+    }
+
+    // src/ORBmatcher.cc:480-596 (LoopClosing::ComputeSim3)
+    template <class KeyFrameT, class MapPointT>
+    int SearchByBoW(KeyFrameT *pKF1, KeyFrameT *pKF2, std::vector<MapPointT *> &vpMatches12) {
+        const std::vector<MapPointT *> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
+        vpMatches12.assign(vpMapPoints1.size(), nullptr);
+        BowSide a, b;
+        flattenBow(pKF1->mvKeys, pKF1->mDescriptors, pKF1->mFeatVec, a);
+        flattenBow(pKF2->mvKeys, pKF2->mDescriptors, pKF2->mFeatVec, b);
+        for (size_t i = 0; i < a.hasMP.size(); i++) a.hasMP[i] = vpMapPoints1[i] && !vpMapPoints1[i]->isBad();
+        for (size_t i = 0; i < b.hasMP.size(); i++) b.hasMP[i] = vpMapPoints2[i] && !vpMapPoints2[i]->isBad();
+        std::vector<int32_t> m(std::max<size_t>(a.hasMP.size(), 1));
+        int32_t nmatches = 0;
+        if (ygzorb_search_by_bow(mHandle, &a.v, &b.v, 0, mfNNratio, mbCheckOrientation ? 1 : 0, 0, m.data(), &nmatches) != 0)
+            throw std::runtime_error(std::string("ygzorb_search_by_bow: ") + ygzorb_last_error());
+        for (size_t i = 0; i < vpMapPoints1.size(); i++)
+            if (m[i] >= 0) vpMatches12[i] = vpMapPoints2[m[i]];           // :546
+        return nmatches;
+    }
+
     ygzorb_matcher *handle() const { return mHandle; }
 
 protected:
+    struct BowSide {
+        std::vector<uint8_t> desc, hasMP; std::vector<uint32_t> ids, feats; std::vector<int32_t> start;
+        ygzorb_keyframe_features v;
+    };
+    template <class KeysT, class DescT, class FeatVecT>
+    static void flattenBow(const KeysT &keys, const DescT &descriptors, const FeatVecT &featVec, BowSide &f) {
+        const int n = (int)keys.size();
+        f.desc.resize((size_t)std::max(n, 1) * 32); f.hasMP.assign(n, 1);
+        for (int i = 0; i < n; i++) std::memcpy(&f.desc[(size_t)i * 32], descriptors.ptr(i), 32);
+        f.start.push_back(0);
+        for (const auto &node : featVec) {                   // std::map iterates in ascending NodeId
+            f.ids.push_back(node.first);
+            for (unsigned idx : node.second) f.feats.push_back(idx);
+            f.start.push_back((int32_t)f.feats.size());
+        }
+        f.v = ygzorb_keyframe_features{n, (int)f.ids.size(), 0, (const ygzorb_keypoint *)keys.data(), f.desc.data(), nullptr,
+                                       f.hasMP.data(), f.ids.data(), f.start.data(), f.feats.data(), nullptr, nullptr};
+    }
     float mfNNratio;
     bool mbCheckOrientation;
     ygzorb_matcher *mHandle;

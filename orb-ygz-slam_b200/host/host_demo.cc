@@ -129,7 +129,36 @@ int main(int argc, char **argv) {
             wr(fb, a, 2);
             for (unsigned idx : e.second) { int32_t ii = (int32_t)idx; wr(fb, &ii, 1); }
         }
+        // Tracking::TrackReferenceKeyFrame (src/Tracking.cc:955-964): a keyframe made of the right image's features, every
+        // third one without a MapPoint and every 7th one bad; then LoopClosing's keyframe-to-keyframe overload.
+        F.mFeatVec = featVec;
+        KeyFrameLite kfR, kfL;
+        std::vector<MapPointLite> mpsR(F.mvKeysRight.size()), mpsL(F.N);
+        auto fill = [&](KeyFrameLite &kf, const std::vector<cv::KeyPoint> &keys, const cv::Mat &desc, std::vector<MapPointLite> &pts) {
+            kf.mvKeys = keys; kf.mDescriptors = desc;
+            std::vector<cv::Mat> v;
+            for (int i = 0; i < desc.rows; i++) v.push_back(desc.row(i));
+            DBoW2::BowVector bv;
+            voc.transform(v, bv, kf.mFeatVec, 4);
+            kf.mvpMapPoints.assign(keys.size(), nullptr);
+            for (size_t i = 0; i < keys.size(); i++) {
+                pts[i].mbBad = i % 7 == 3;
+                if (i % 3 != 1) kf.mvpMapPoints[i] = &pts[i];
+            }
+        };
+        fill(kfR, F.mvKeysRight, F.mDescriptorsRight, mpsR);
+        fill(kfL, F.mvKeys, F.mDescriptors, mpsL);
+        ORBmatcher bowMatcher(0.7f, true);
+        std::vector<MapPointLite *> vpMatches, vpMatches12;
+        int32_t nbow = bowMatcher.SearchByBoW(&kfR, F, vpMatches);
+        wr(fb, &nbow, 1);
+        for (int i = 0; i < F.N; i++) { int32_t idx = vpMatches[i] ? (int32_t)(vpMatches[i] - mpsR.data()) : -1; wr(fb, &idx, 1); }
+        ORBmatcher loopMatcher(0.75f, true);
+        int32_t nbow12 = loopMatcher.SearchByBoW(&kfL, &kfR, vpMatches12);
+        wr(fb, &nbow12, 1);
+        for (int i = 0; i < F.N; i++) { int32_t idx = vpMatches12[i] ? (int32_t)(vpMatches12[i] - mpsR.data()) : -1; wr(fb, &idx, 1); }
         fclose(fb);
+        printf("host_demo: SearchByBoW keyframe->frame %d, keyframe->keyframe %d matches\n", nbow, nbow12);
         printf("host_demo: vocabulary with %u words, BowVector %d words, FeatureVector %d nodes\n", voc.size(), nb, nn);
     }
     printf("host_demo: %d left / %d right keypoints, %d projection matches, %d motion-model matches, DescriptorDistance(self)=%d\n", nL, nR, nmatches, nmatchesLast,

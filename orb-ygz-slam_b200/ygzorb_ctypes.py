@@ -247,6 +247,17 @@ class Matcher:
         L.ygzorb_hamming_knn2.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_int,
                                           C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ygzorb_descriptor_distance.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_void_p]
+        L.ygzorb_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_uint, C.c_void_p,
+                                           C.c_void_p]
+        L.ygzorb_bow_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_uint] + \
+            [C.c_void_p] * 10
+        L.ygzorb_vocabulary_create.argtypes = [C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_int, C.c_void_p]
+        L.ygzorb_vocabulary_load_binary.argtypes = [C.c_char_p, C.c_int, C.c_void_p]
+        L.ygzorb_vocabulary_load_text.argtypes = [C.c_char_p, C.c_int, C.c_void_p]
+        L.ygzorb_vocabulary_destroy.argtypes = [C.c_void_p]
+        L.ygzorb_vocabulary_destroy.restype = None
+        L.ygzorb_vocabulary_info.argtypes = [C.c_void_p, C.c_void_p]
+        L.ygzorb_vocabulary_arrays.argtypes = [C.c_void_p] * 6
         L.ygzorb_search_by_projection_last.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_int,
                                                        C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ygzorb_search_by_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_float,
@@ -400,6 +411,24 @@ class Matcher:
         check(lib().ygzorb_search_for_triangulation(self.h, C.byref(v1), C.byref(v2), _ptr(F), float(ex), float(ey),
                                                     int(only_stereo), int(check_orientation), 0, _ptr(m12), _ptr(nm)))
         return int(nm[0]), m12[:v1.n].copy()
+
+    def search_by_bow(self, kf1, second, second_is_frame, nnratio, check_orientation):
+        """kf dicts: kps, desc, has_mp, node_ids, node_start, node_feats.  Returns (n_matches, matches)."""
+        keep = []
+
+        def view(kf):
+            a = [np.ascontiguousarray(kf["kps"]), np.ascontiguousarray(kf["desc"], np.uint8),
+                 np.ascontiguousarray(kf["has_mp"], np.uint8), np.ascontiguousarray(kf["node_ids"], np.uint32),
+                 np.ascontiguousarray(kf["node_start"], np.int32), np.ascontiguousarray(kf["node_feats"], np.uint32)]
+            keep.append(a)
+            return KeyFrameFeatures(len(a[0]), len(a[3]), 0, _ptr(a[0]), _ptr(a[1]), None, _ptr(a[2]), _ptr(a[3]), _ptr(a[4]),
+                                    _ptr(a[5]), None, None)
+        v1, v2 = view(kf1), view(second)
+        n_out = v2.n if second_is_frame else v1.n
+        m = np.zeros(max(n_out, 1), np.int32); nm = np.zeros(1, np.int32)
+        check(lib().ygzorb_search_by_bow(self.h, C.byref(v1), C.byref(v2), int(second_is_frame), C.c_float(nnratio),
+                                         int(check_orientation), 0, _ptr(m), _ptr(nm)))
+        return int(nm[0]), m[:n_out].copy()
 
     def stereo_match(self, ex_left, ex_right, frame, kps_l, desc_l, kps_r, desc_r, bf, b):
         kps_l, kps_r = np.ascontiguousarray(kps_l), np.ascontiguousarray(kps_r)

@@ -246,6 +246,21 @@ def search_by_projection_last(kps, desc, u_right, claimed, bounds, scale_factors
     return nm, kp_to_pt[:n].copy(), best[:m].copy()
 
 
+def search_by_bow(kf1, second, second_is_frame, nnratio, check_orientation):
+    """kf dicts: kps, desc, has_mp, node_ids, node_start, node_feats.  Returns (n_matches, matches)."""
+    def pk(kf):
+        return (np.ascontiguousarray(kf["kps"]), np.ascontiguousarray(kf["desc"], np.uint8), np.ascontiguousarray(kf["has_mp"], np.uint8),
+                np.ascontiguousarray(kf["node_ids"], np.uint32), np.ascontiguousarray(kf["node_start"], np.int32),
+                np.ascontiguousarray(kf["node_feats"], np.uint32))
+    a, b = pk(kf1), pk(second)
+    n_out = len(b[0]) if second_is_frame else len(a[0])
+    m = np.zeros(max(n_out, 1), np.int32)
+    nm = lib().ygzo_search_by_bow(_p(a[0]), _p(a[1]), _p(a[2]), len(a[0]), _p(a[3]), _p(a[4]), _p(a[5]), len(a[3]),
+                                  _p(b[0]), _p(b[1]), _p(b[2]), len(b[0]), _p(b[3]), _p(b[4]), _p(b[5]), len(b[3]),
+                                  int(second_is_frame), C.c_float(nnratio), int(check_orientation), _p(m))
+    return nm, m[:n_out].copy()
+
+
 def search_for_triangulation(kf1, kf2, F12, ex, ey, only_stereo, check_orientation):
     """kf: dict with kps, desc, u_right, has_mp, node_ids, node_start, node_feats, scale_factors, level_sigma2."""
     def pk(kf):

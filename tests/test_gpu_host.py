@@ -86,4 +86,17 @@ def test_host_classes_end_to_end():
         node, cnt = np.frombuffer(bowbuf, "<i4", 2, o); o += 8
         feats = np.frombuffer(bowbuf, "<i4", int(cnt), o); o += 4 * int(cnt)
         assert node == want["fv_node"][j] and np.array_equal(feats, want["fv_feat"][want["fv_start"][j]:want["fv_start"][j + 1]])
+    # ORBmatcher::SearchByBoW, both overloads, on keyframes made of the two images (MapPoint pattern of host_demo.cc)
+    wantR = ovoc.transform(dr, 4)
+    def side(k, d, r):
+        i = np.arange(len(k))
+        return {"kps": k, "desc": d, "has_mp": ((i % 3 != 1) & (i % 7 != 3)).astype(np.uint8), "node_ids": r["fv_node"],
+                "node_start": r["fv_start"], "node_feats": r["fv_feat"]}
+    gn = int(np.frombuffer(bowbuf, "<i4", 1, o)[0]); gm = np.frombuffer(bowbuf, "<i4", nL, o + 4); o += 4 + 4 * nL
+    en, em = O.search_by_bow(side(kr, dr, wantR), side(kl, dl, want), True, 0.7, True)
+    assert gn == en and np.array_equal(gm, em) and en > 100
+    gn = int(np.frombuffer(bowbuf, "<i4", 1, o)[0]); gm = np.frombuffer(bowbuf, "<i4", nL, o + 4); o += 4 + 4 * nL
+    en, em = O.search_by_bow(side(kl, dl, want), side(kr, dr, wantR), False, 0.75, True)
+    assert gn == en and np.array_equal(gm, em) and en > 50
+    assert o == len(bowbuf)
     ovoc.close()

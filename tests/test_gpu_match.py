@@ -117,6 +117,38 @@ def test_triangulation_vs_oracle(matcher, feats, only_stereo, check_ori, seed):
     assert g[0] == e[0] and np.array_equal(g[1], e[1]) and e[0] > (5 if only_stereo else 20)
 
 
+@pytest.mark.parametrize("frame2,check_ori,ratio,n_nodes,seed", [(True, True, 0.7, 100, 1), (True, False, 0.9, 30, 2),
+                                                                (False, True, 0.75, 100, 3), (False, False, 0.6, 5, 4)])
+def test_search_by_bow_vs_oracle(matcher, feats, frame2, check_ori, ratio, n_nodes, seed):
+    """ORBmatcher::SearchByBoW, both overloads (src/ORBmatcher.cc:155-263, :480-596); few nodes = long serial chains."""
+    img, kps, desc = feats
+    kf1, kf2, _, _, _ = synth.triangulation_case(kps, desc, seed, n_nodes=n_nodes)
+    kf1["has_mp"] = 1 - kf1["has_mp"]; kf2["has_mp"] = 1 - kf2["has_mp"]
+    e = O.search_by_bow(kf1, kf2, frame2, ratio, check_ori)
+    g = matcher.search_by_bow(kf1, kf2, frame2, ratio, check_ori)
+    assert g[0] == e[0] and e[0] > 50 and np.array_equal(g[1], e[1])
+
+
+def test_bow_transform_feeds_search_by_bow(matcher, feats):
+    """The chain the tracker runs: ComputeBoW on keyframe and frame, then SearchByBoW on the two FeatureVectors."""
+    import bow_io
+    img, kps, desc = feats
+    t = bow_io.random_tree(10, 4, 3)
+    voc = Y.Vocabulary.from_arrays(t["k"], t["L"], t["child_start"], t["child_list"], t["desc"], t["word_id"], t["weight"])
+    ovoc = O.Vocabulary.from_arrays(t["k"], t["L"], t["child_start"], t["child_list"], t["desc"], t["word_id"], t["weight"])
+    rng = np.random.default_rng(8)
+    desc2 = synth.flip_bits(desc, rng.integers(0, 25, size=len(desc)), rng)
+    kps2 = kps.copy(); kps2["angle"] = np.mod(kps2["angle"] + rng.normal(0, 5, len(kps)), 360).astype(np.float32)
+    r1, r2 = Y.bow_transform(matcher, voc, [desc, desc2], 2)
+    o1, o2 = ovoc.transform(desc, 2), ovoc.transform(desc2, 2)
+    mk = lambda k, d, r: {"kps": k, "desc": d, "has_mp": np.ones(len(k), np.uint8), "node_ids": r["fv_node"],
+                          "node_start": r["fv_start"], "node_feats": r["fv_feat"]}
+    g = matcher.search_by_bow(mk(kps, desc, r1), mk(kps2, desc2, r2), True, 0.7, True)
+    e = O.search_by_bow(mk(kps, desc, o1), mk(kps2, desc2, o2), True, 0.7, True)
+    assert g[0] == e[0] and e[0] > 200 and np.array_equal(g[1], e[1])
+    voc.close(); ovoc.close()
+
+
 @pytest.mark.parametrize("w,h,nf,seed", [(640, 240, 800, 5), (1241, 376, 2000, 6)])
 def test_stereo_vs_oracle(matcher, w, h, nf, seed):
     left, right = synth.stereo_pair(w, h, seed)

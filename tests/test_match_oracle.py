@@ -333,6 +333,75 @@ def test_triangulation_vs_python(only_stereo, check_ori, seed):
     assert a[0] > (5 if only_stereo else 30)
 
 
+def _py_search_by_bow(kf1, kf2, frame2, ratio, check_ori):
+    """src/ORBmatcher.cc:155-263 / :480-596 re-derived with dict FeatureVectors."""
+    f = np.float32
+    fv1 = {int(n): kf1["node_feats"][kf1["node_start"][k]:kf1["node_start"][k + 1]] for k, n in enumerate(kf1["node_ids"])}
+    fv2 = {int(n): kf2["node_feats"][kf2["node_start"][k]:kf2["node_start"][k + 1]] for k, n in enumerate(kf2["node_ids"])}
+    D = _hamming_matrix(kf1["desc"], kf2["desc"])
+    n_out = len(kf2["kps"]) if frame2 else len(kf1["kps"])
+    matches = np.full(n_out, -1, np.int32)
+    taken = np.zeros(len(kf2["kps"]), bool)
+    hist = [[] for _ in range(30)]
+    rnd = lambda v: int(math.floor(abs(v) + 0.5)) * (1 if v >= 0 else -1)
+    n = 0
+    for node in sorted(set(fv1) & set(fv2)):
+        for i1 in fv1[node]:
+            if not kf1["has_mp"][i1]:
+                continue
+            b1, b2, bi = 256, 256, -1
+            for i2 in fv2[node]:
+                if taken[i2] or (not frame2 and not kf2["has_mp"][i2]):
+                    continue
+                d = int(D[i1, i2])
+                if d < b1:
+                    b2, b1, bi = b1, d, int(i2)
+                elif d < b2:
+                    b2 = d
+            near = b1 <= 50 if frame2 else b1 < 50
+            if near and f(b1) < f(ratio) * f(b2):
+                taken[bi] = True
+                slot = bi if frame2 else int(i1)
+                matches[slot] = int(i1) if frame2 else bi
+                n += 1
+                if check_ori:
+                    rot = f(kf1["kps"]["angle"][i1] - kf2["kps"]["angle"][bi])
+                    if rot < 0:
+                        rot = f(rot + f(360))
+                    b = rnd(float(f(rot * f(f(1.0) / f(30)))))
+                    hist[0 if b == 30 else b].append(slot)
+    if check_ori:
+        m1 = m2 = m3 = 0; i1 = i2 = i3 = -1
+        for i in range(30):
+            sz = len(hist[i])
+            if sz > m1:
+                m3, m2, m1, i3, i2, i1 = m2, m1, sz, i2, i1, i
+            elif sz > m2:
+                m3, m2, i3, i2 = m2, sz, i2, i
+            elif sz > m3:
+                m3, i3 = sz, i
+        if f(m2) < f(0.1) * f(m1):
+            i2 = i3 = -1
+        elif f(m3) < f(0.1) * f(m1):
+            i3 = -1
+        for i in range(30):
+            if i not in (i1, i2, i3):
+                for slot in hist[i]:
+                    matches[slot] = -1; n -= 1
+    return n, matches
+
+
+@pytest.mark.parametrize("frame2,check_ori,ratio,seed", [(True, True, 0.7, 1), (True, False, 0.9, 2), (False, True, 0.75, 3),
+                                                        (False, False, 0.6, 4)])
+def test_search_by_bow_vs_python(frame2, check_ori, ratio, seed):
+    img, (kps, desc) = _features(seed=seed)
+    kf1, kf2, _, _, _ = synth.triangulation_case(kps, desc, seed, n_nodes=40)
+    kf1["has_mp"] = 1 - kf1["has_mp"]; kf2["has_mp"] = 1 - kf2["has_mp"]          # most keypoints carry a MapPoint
+    a = O.search_by_bow(kf1, kf2, frame2, ratio, check_ori)
+    b = _py_search_by_bow(kf1, kf2, frame2, ratio, check_ori)
+    assert a[0] == b[0] and a[0] > 20 and np.array_equal(a[1], b[1])
+
+
 def test_stereo_match_recovers_disparity():
     w, h = 480, 200
     left, right = synth.stereo_pair(w, h, 5)
