@@ -2,7 +2,7 @@
 // Every kernel is batched over frames (blockIdx.y = frame) so that one launch covers a whole
 // batch of same-sized frames.  Integer arithmetic reproduces OpenCV 4.13's fixed-point paths bit
 // for bit; float arithmetic is written with explicit round-to-nearest intrinsics so nvcc cannot
-// contract it into FMAs the reference's build (-ffp-contract=off oracle) does not execute.
+// contract it into FMAs the reference's build (-ffp-contract=off) does not execute.
 #include "ygz_common.cuh"
 #include "orb_pattern.inc"
 

@@ -485,8 +485,8 @@ class Vocabulary:
 
 
 def bow_transform(matcher, voc, frames, levelsup, stride=None):
-    """frames: list of (n_i, 32) uint8 descriptor arrays.  Returns per frame the dict tests/oracle_lib.Vocabulary.transform
-    returns (word, node, weight, bow_word, bow_value, fv_node, fv_start, fv_feat)."""
+    """frames: list of (n_i, 32) uint8 descriptor arrays.  Returns per frame a dict with the keys word, node, weight,
+    bow_word, bow_value, fv_node, fv_start, fv_feat."""
     nf = len(frames)
     st = stride or max(max((len(f) for f in frames), default=1), 1)
     desc = np.zeros((nf, st, 32), np.uint8)
