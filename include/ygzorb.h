@@ -230,6 +230,43 @@ int ygzorb_search_by_projection_last(ygzorb_matcher *m, const ygzorb_frame_featu
                                      int check_orientation, unsigned flags, int32_t *kp_to_pt, int32_t *pt_best_idx,
                                      int32_t *n_matches);
 
+/* The MapPoints of a KeyFrame (or a candidate list) for the two projection searches that predict the scale level from
+ * the distance: entry i of frame pair f at f*pt_stride + i. */
+typedef struct ygzorb_keyframe_points {
+    int pt_stride;
+    const int32_t *n_pts;
+    const uint8_t *valid;        /* pMP != NULL && !pMP->isBad() && not in the already-found set (:1369-1372, :291-292) */
+    const float *world_pos;      /* GetWorldPos() */
+    const float *normal;         /* GetNormal() (Sim3 variant only; may be NULL otherwise) */
+    const uint8_t *desc;         /* GetDescriptor() */
+    const float *angle;          /* pKF->mvKeys[i].angle (relocalisation variant with check_orientation; else may be NULL) */
+    const float *max_distance;   /* mfMaxDistance (GetMaxDistanceInvariance() / 1.2f: the raw member, PredictScale reads it) */
+    const float *min_distance;   /* mfMinDistance */
+    /* per frame pair 30 floats: [0..8] Rcw row-major, [9..11] tcw, [12..14] Ow (Sim3 variant: -Rcw^T tcw as the caller's
+     * cv::Mat arithmetic gives it, :278; the relocalisation variant derives it itself), [24..27] fx, fy, cx, cy */
+    const float *pose;
+    float log_scale_factor;      /* mfLogScaleFactor */
+    int n_scale_levels;          /* mnScaleLevels */
+} ygzorb_keyframe_points;
+
+/* ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const set<MapPoint*> &sAlreadyFound, th, ORBdist)
+ * (src/ORBmatcher.cc:1352-1469; Tracking::Relocalization).  cur->claimed = CurrentFrame.mvpMapPoints[i] != NULL on entry;
+ * a keypoint taken by an earlier point of this call is skipped by later ones, as there.  Eigen evaluation order as in
+ * ygzorb_search_by_projection_last; PredictScale uses the correctly rounded float logarithm.  Outputs as in
+ * ygzorb_search_by_projection_last. */
+int ygzorb_search_by_projection_reloc(ygzorb_matcher *m, const ygzorb_frame_features *cur, const ygzorb_keyframe_points *pts,
+                                      float th, int orb_dist, int check_orientation, unsigned flags, int32_t *kp_to_pt,
+                                      int32_t *pt_best_idx, int32_t *n_matches);
+
+/* ORBmatcher::SearchByProjection(KeyFrame *pKF, cv::Mat Scw, const vector<MapPoint*> &vpPoints, vector<MapPoint*>
+ * &vpMatched, int th) (src/ORBmatcher.cc:265-373; LoopClosing::ComputeSim3).  kf = the KeyFrame's keypoints / descriptors
+ * with claimed = vpMatched[idx] != NULL on entry and min/max = mnMinX.. (IsInImage); the decomposition of Scw (:275-278)
+ * stays with the caller and arrives in pose.  cv::Mat arithmetic as OpenCV 4.13 evaluates it: the 3x3 by 3x1 gemm as
+ * ((a0 + a1) + a2) + c in float, cv::norm / Mat::dot in double.  kp_to_pt[idx] = index into vpPoints newly stored in
+ * vpMatched[idx], or -1. */
+int ygzorb_search_by_projection_sim3(ygzorb_matcher *m, const ygzorb_frame_features *kf, const ygzorb_keyframe_points *pts,
+                                     int th, unsigned flags, int32_t *kp_to_pt, int32_t *pt_best_idx, int32_t *n_matches);
+
 /* KeyFrame arrays read by SearchForTriangulation (include/KeyFrame.h:236-271); the DBoW2::FeatureVector
  * (Thirdparty/DBoW2/DBoW2/FeatureVector.h:23-24, std::map<NodeId, vector<unsigned>>) flattened to CSR:
  * node_ids ascending, features of node k = node_feats[node_start[k] .. node_start[k+1]). */

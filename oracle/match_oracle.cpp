@@ -266,6 +266,111 @@ YGZO_API int ygzo_search_by_projection_last(const void *kpsV, const uint8_t *des
     return nmatches;
 }
 
+// MapPoint::PredictScale (src/MapPoint.cc:343-373); log(float) resolves to the float overload under <cmath>.
+static int predictScale(float maxDistance, float currentDist, float logScaleFactor, int nScaleLevels) {
+    const float ratio = maxDistance / currentDist;
+    const float q = std::ceil(std::log(ratio) / logScaleFactor);
+    int nScale = (q >= -2147483648.0f && q < 2147483648.0f) ? (int)q : INT_MIN;   // what cvttss2si returns otherwise
+    if (nScale < 0) nScale = 0;
+    else if (nScale >= nScaleLevels) nScale = nScaleLevels - 1;
+    return nScale;
+}
+
+// The two projection searches over a KeyFrame's MapPoints that predict the level from the distance:
+//   sim3 = 0: SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, sAlreadyFound, th, ORBdist), src/ORBmatcher.cc:1352-1469.
+//     Eigen arithmetic, canonical order as in ygzo_search_by_projection_last.  pose = Rcw(9), tcw(3), -, fx, fy, cx, cy at 24..27.
+//   sim3 = 1: SearchByProjection(KeyFrame *pKF, cv::Mat Scw, vpPoints, vpMatched, th), :265-373.  pose = Rcw, tcw, Ow (12..14)
+//     as decomposed by the caller (:275-278).  cv::Mat arithmetic as OpenCV 4.13 evaluates it (tests/test_match_oracle.py
+//     checks this against cv2.gemm / cv2.norm): gemm 3x3 * 3x1 + c = ((a0 + a1) + a2) + c in float; cv::norm and Mat::dot
+//     accumulate in double in index order.
+// blocked = CurrentFrame.mvpMapPoints[i2] / vpMatched[idx] non-null on entry.  Returns nmatches.
+YGZO_API int ygzo_search_by_projection_keyframe(const void *kpsV, const uint8_t *desc, const uint8_t *claimed, int n, float minX,
+                                                float minY, float maxX, float maxY, float invW, float invH,
+                                                const float *scaleFactors, const float *pose, const uint8_t *valid,
+                                                const float *worldPos, const float *normal, const uint8_t *ptDesc,
+                                                const float *angleKF, const float *maxDistance, const float *minDistance, int m,
+                                                float logScaleFactor, int nScaleLevels, float th, int bestDistMax,
+                                                int checkOrientation, int sim3, int32_t *kpToPt, int32_t *ptBestIdx) {
+    const KeyPoint *kps = (const KeyPoint *)kpsV;
+    Grid g;
+    assignGrid(g, kps, n, minX, minY, invW, invH);
+    std::vector<uint8_t> blocked(n, 0);
+    for (int i = 0; i < n; i++) { kpToPt[i] = -1; blocked[i] = claimed ? claimed[i] : 0; }
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float *Rcw = pose, *tcw = pose + 9;
+    const float fx = pose[24], fy = pose[25], cx = pose[26], cy = pose[27];
+    auto dot3 = [](float a0, float a1, float a2) { const float s = a1 + a2; return a0 + s; };
+    float Ow[3];
+    for (int r = 0; r < 3; r++) Ow[r] = sim3 ? pose[12 + r] : -dot3(Rcw[r] * tcw[0], Rcw[3 + r] * tcw[1], Rcw[6 + r] * tcw[2]);   // :1358
+    std::vector<int> vIndices;
+    for (int i = 0; i < m; i++) {
+        if (ptBestIdx) ptBestIdx[i] = -1;
+        if (!valid[i]) continue;
+        const float *X = worldPos + 3 * (size_t)i;
+        float c[3], u, v;
+        if (!sim3) {
+            for (int r = 0; r < 3; r++) c[r] = dot3(Rcw[3 * r] * X[0], Rcw[3 * r + 1] * X[1], Rcw[3 * r + 2] * X[2]) + tcw[r];
+            const float invzc = (float)(1.0 / (double)c[2]);
+            u = fx * c[0] * invzc + cx; v = fy * c[1] * invzc + cy;
+            if (!std::isfinite(u) || !std::isfinite(v)) continue;
+            if (u < minX || u > maxX) continue;
+            if (v < minY || v > maxY) continue;
+        } else {
+            for (int r = 0; r < 3; r++) {
+                float t0 = Rcw[3 * r] * X[0]; t0 = t0 + Rcw[3 * r + 1] * X[1]; t0 = t0 + Rcw[3 * r + 2] * X[2];
+                c[r] = t0 + tcw[r];
+            }
+            if (c[2] < 0.0) continue;
+            const float invz = 1 / c[2];
+            const float x = c[0] * invz, y = c[1] * invz;
+            u = fx * x + cx; v = fy * y + cy;
+            if (!(u >= minX && u < maxX && v >= minY && v < maxY)) continue;   // KeyFrame::IsInImage
+        }
+        const float PO[3] = {X[0] - Ow[0], X[1] - Ow[1], X[2] - Ow[2]};
+        float dist3D;
+        if (!sim3) dist3D = std::sqrt(dot3(PO[0] * PO[0], PO[1] * PO[1], PO[2] * PO[2]));
+        else {
+            double s = 0;
+            for (int r = 0; r < 3; r++) s += (double)PO[r] * (double)PO[r];
+            dist3D = (float)std::sqrt(s);
+        }
+        const float maxD = 1.2f * maxDistance[i], minD = 0.8f * minDistance[i];
+        if (dist3D < minD || dist3D > maxD) continue;
+        if (sim3) {
+            double d = 0;
+            for (int r = 0; r < 3; r++) d += (double)PO[r] * (double)normal[3 * (size_t)i + r];
+            if (d < 0.5 * dist3D) continue;
+        }
+        const int nPredictedLevel = predictScale(maxDistance[i], dist3D, logScaleFactor, nScaleLevels);
+        const float radius = th * scaleFactors[nPredictedLevel];
+        featuresInArea(g, kps, u, v, radius, nPredictedLevel - 1, sim3 ? nPredictedLevel : nPredictedLevel + 1, vIndices);
+        if (vIndices.empty()) continue;
+        int bestDist = 256, bestIdx2 = -1;
+        for (int i2 : vIndices) {
+            if (blocked[i2]) continue;
+            const int dist = descriptorDistance(ptDesc + (size_t)i * 32, desc + (size_t)i2 * 32);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= bestDistMax) {
+            kpToPt[bestIdx2] = i;
+            blocked[bestIdx2] = 1;
+            if (ptBestIdx) ptBestIdx[i] = bestIdx2;
+            nmatches++;
+            if (checkOrientation) rotHist[rotationBin(angleKF[i], kps[bestIdx2].angle)].push_back(bestIdx2);
+        }
+    }
+    if (checkOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1, sizes[HISTO_LENGTH];
+        for (int i = 0; i < HISTO_LENGTH; i++) sizes[i] = (int)rotHist[i].size();
+        threeMaxima(sizes, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int idx : rotHist[i]) { kpToPt[idx] = -1; nmatches--; }
+    }
+    return nmatches;
+}
+
 // ORBmatcher::SearchByBoW — both overloads over flattened FeatureVectors (CSR, ascending NodeId):
 //   secondIsFrame = 1: SearchByBoW(KeyFrame *pKF, Frame &F, vector<MapPoint*> &vpMapPointMatches), src/ORBmatcher.cc:155-263.
 //     hasMP1 = the keyframe's MapPoint exists and !isBad(); frame features already matched in this call are skipped;

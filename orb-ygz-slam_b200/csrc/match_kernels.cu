@@ -288,6 +288,7 @@ template <int MODE> __device__ int projMatchCached(const ProjArgs &A, int f, int
         else if (dist < bestDist2) { bestLevel2 = oct; bestDist2 = dist; }
     }
     if (MODE == 1) return bestDist <= kThHigh ? bestIdx : -1;     // :1311 (no second-best rule in the LastFrame variant)
+    if (MODE >= 2) return bestDist <= A.bestDistMax ? bestIdx : -1;   // :1430 (ORBdist), :363 (TH_LOW)
     return projAccept(A, bestDist, bestDist2, bestLevel, bestLevel2, bestIdx);
 }
 
@@ -296,6 +297,66 @@ template <int MODE> __device__ int projMatchCached(const ProjArgs &A, int f, int
 struct ProjQuery { float x, y, rad, xr; int minLevel, maxLevel; };
 
 __device__ __forceinline__ float projDot3(float a0, float a1, float a2) { return __fadd_rn(a0, __fadd_rn(a1, a2)); }
+
+// MapPoint::PredictScale (src/MapPoint.cc:343-373): ceil(log(mfMaxDistance / dist) / mfLogScaleFactor), clamped.  log() of
+// a float argument resolves to logf there; here it is the double logarithm rounded to float, i.e. the correctly rounded
+// logf (the two can differ by one ulp on rare arguments, which moves the level only when the quotient sits on an integer).
+__device__ __forceinline__ int predictScale(const ProjArgs &A, float maxDistance, float dist) {
+    const float ratio = __fdiv_rn(maxDistance, dist);
+    const float q = ceilf(__fdiv_rn(__double2float_rn(log((double)ratio)), A.logScale));
+    int nScale = (q >= -2147483648.0f && q < 2147483648.0f) ? (int)q : INT_MIN;   // x86 cvttss2si on NaN / overflow
+    if (nScale < 0) nScale = 0;
+    else if (nScale >= A.nScaleLevels) nScale = A.nScaleLevels - 1;
+    return nScale;
+}
+
+// MODE 2: SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, sAlreadyFound, th, ORBdist) (:1352-1469), Eigen
+// arithmetic (3-term sums as a0 + (a1 + a2)).  MODE 3: SearchByProjection(KeyFrame *pKF, Scw, vpPoints, vpMatched, th)
+// (:265-373), cv::Mat arithmetic: gemm = ((a0 + a1) + a2) + c in float, cv::norm and Mat::dot accumulate in double.
+template <int MODE> __device__ __forceinline__ bool projQueryKeyFramePoint(const ProjArgs &A, const float *P, size_t mo, float X0,
+                                                                            float X1, float X2, ProjQuery &q) {
+    float c[3], Ow[3];
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+        const float a0 = __fmul_rn(P[3 * r], X0), a1 = __fmul_rn(P[3 * r + 1], X1), a2 = __fmul_rn(P[3 * r + 2], X2);
+        c[r] = MODE == 2 ? __fadd_rn(projDot3(a0, a1, a2), P[9 + r]) : __fadd_rn(__fadd_rn(__fadd_rn(a0, a1), a2), P[9 + r]);
+        Ow[r] = MODE == 2 ? -projDot3(__fmul_rn(P[r], P[9]), __fmul_rn(P[3 + r], P[10]), __fmul_rn(P[6 + r], P[11])) : P[12 + r];
+    }
+    float u, v;
+    if (MODE == 2) {
+        const float invzc = __double2float_rn(__ddiv_rn(1.0, (double)c[2]));
+        u = __fadd_rn(__fmul_rn(__fmul_rn(P[24], c[0]), invzc), P[26]);
+        v = __fadd_rn(__fmul_rn(__fmul_rn(P[25], c[1]), invzc), P[27]);
+        if (!isfinite(u) || !isfinite(v)) return false;
+        if (u < A.minX || u > A.maxX) return false;
+        if (v < A.minY || v > A.maxY) return false;
+    } else {
+        if ((double)c[2] < 0.0) return false;
+        const float invz = __fdiv_rn(1.0f, c[2]);
+        u = __fadd_rn(__fmul_rn(P[24], __fmul_rn(c[0], invz)), P[26]);
+        v = __fadd_rn(__fmul_rn(P[25], __fmul_rn(c[1], invz)), P[27]);
+        if (!(u >= A.minX && u < A.maxX && v >= A.minY && v < A.maxY)) return false;   // KeyFrame::IsInImage
+    }
+    const float PO0 = __fsub_rn(X0, Ow[0]), PO1 = __fsub_rn(X1, Ow[1]), PO2 = __fsub_rn(X2, Ow[2]);
+    float dist;
+    if (MODE == 2) dist = __fsqrt_rn(projDot3(__fmul_rn(PO0, PO0), __fmul_rn(PO1, PO1), __fmul_rn(PO2, PO2)));
+    else {
+        const double s = __dadd_rn(__dadd_rn(__dmul_rn(PO0, PO0), __dmul_rn(PO1, PO1)), __dmul_rn(PO2, PO2));
+        dist = __double2float_rn(__dsqrt_rn(s));
+    }
+    const float maxD = A.maxDist[mo];
+    if (dist < __fmul_rn(0.8f, A.minDist[mo]) || dist > __fmul_rn(1.2f, maxD)) return false;
+    if (MODE == 3) {   // viewing angle below 60 degrees (:322-325)
+        const float *Pn = A.normal + 3 * mo;
+        const double d = __dadd_rn(__dadd_rn(__dmul_rn(PO0, Pn[0]), __dmul_rn(PO1, Pn[1])), __dmul_rn(PO2, Pn[2]));
+        if (d < __dmul_rn(0.5, (double)dist)) return false;
+    }
+    const int lvl = predictScale(A, maxD, dist);
+    q.rad = __fmul_rn(A.th, A.scale[lvl]);
+    q.x = u; q.y = v; q.xr = 0.f;
+    q.minLevel = lvl - 1; q.maxLevel = MODE == 2 ? lvl + 1 : lvl;
+    return true;
+}
 
 template <int MODE> __device__ __forceinline__ bool projQuery(const ProjArgs &A, int f, int j, int dir, ProjQuery &q) {
     const size_t mo = (size_t)f * A.mpStride + j;
@@ -313,6 +374,7 @@ template <int MODE> __device__ __forceinline__ bool projQuery(const ProjArgs &A,
     const float *P = A.pose + (size_t)f * 30;
     const float *X = A.worldPos + 3 * mo;
     const float X0 = X[0], X1 = X[1], X2 = X[2];
+    if (MODE >= 2) return projQueryKeyFramePoint<MODE>(A, P, mo, X0, X1, X2, q);
     const float xc = __fadd_rn(projDot3(__fmul_rn(P[0], X0), __fmul_rn(P[1], X1), __fmul_rn(P[2], X2)), P[9]);
     const float yc = __fadd_rn(projDot3(__fmul_rn(P[3], X0), __fmul_rn(P[4], X1), __fmul_rn(P[5], X2)), P[10]);
     const float zc = __fadd_rn(projDot3(__fmul_rn(P[6], X0), __fmul_rn(P[7], X1), __fmul_rn(P[8], X2)), P[11]);
@@ -391,6 +453,7 @@ __device__ int projMatchOne(const ProjArgs &A, int f, int j, int n, const int *c
     }
     if (RECORD) *recorded = nrec;
     if (MODE == 1) return bestDist <= kThHigh ? bestIdx : -1;
+    if (MODE >= 2) return bestDist <= A.bestDistMax ? bestIdx : -1;
     return projAccept(A, bestDist, bestDist2, bestLevel, bestLevel2, bestIdx);
 }
 
@@ -443,7 +506,7 @@ template <int MODE> __global__ void __launch_bounds__(kProjThreads) k_search_by_
         const float mb = P[29];
         dirS = A.bMono ? 0 : (tlcz > mb ? 1 : (-tlcz > mb ? 2 : 0));
     }
-    if (MODE == 1 && tid < kHistoLength) hist[tid] = 0;
+    if (MODE >= 1 && tid < kHistoLength) hist[tid] = 0;
     __syncthreads();
     const int dir = MODE == 1 ? dirS : 0;
     // ---- round 0: full window walk against the entry claims, recording the candidate cache
@@ -461,7 +524,7 @@ template <int MODE> __global__ void __launch_bounds__(kProjThreads) k_search_by_
         __syncthreads();
         for (int j = tid; j < m; j += kProjThreads) {
             const int b = best[j];
-            if (b >= 0 && A.hasObs[(size_t)f * A.mpStride + j]) atomicMin(&claimTime[b], j);
+            if (b >= 0 && (MODE >= 2 || A.hasObs[(size_t)f * A.mpStride + j])) atomicMin(&claimTime[b], j);
         }
         __syncthreads();
         int changed = 0;
@@ -483,7 +546,7 @@ template <int MODE> __global__ void __launch_bounds__(kProjThreads) k_search_by_
         if (b >= 0) { atomicMax(&kpToMp[b], j); cnt++; }
     }
     if (cnt) atomicAdd(&ws[0], cnt);
-    if (MODE == 1 && A.checkOrientation) {
+    if (MODE >= 1 && A.checkOrientation) {
         // ---- rotation consistency (:1316-1346): every accepted point votes; the keypoints of all entries outside the
         // three dominant bins are cleared afterwards (also when a later point of a kept bin had overwritten them)
         const float *angleLast = A.angleLast + (size_t)f * A.mpStride;
@@ -522,6 +585,13 @@ int launchSearchByProjection(const ProjArgs &A, int maxKp, cudaStream_t s) {
     (void)maxKp;
     if (A.nFrames <= 0) return 0;
     k_search_by_projection<0><<<A.nFrames, kProjThreads, 0, s>>>(A);
+    return 1;
+}
+
+int launchSearchByProjectionKeyFrame(const ProjArgs &A, int sim3, cudaStream_t s) {
+    if (A.nFrames <= 0) return 0;
+    if (sim3) k_search_by_projection<3><<<A.nFrames, kProjThreads, 0, s>>>(A);
+    else k_search_by_projection<2><<<A.nFrames, kProjThreads, 0, s>>>(A);
     return 1;
 }
 

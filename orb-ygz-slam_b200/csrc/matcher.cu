@@ -318,6 +318,75 @@ int ygzorb_search_by_projection_last(ygzorb_matcher *h, const ygzorb_frame_featu
     return finish(m, flags);
 }
 
+static int searchByProjectionKeyFrame(ygzorb_matcher *h, const ygzorb_frame_features *F, const ygzorb_keyframe_points *L, float th,
+                                      int bestDistMax, int checkOrientation, int sim3, unsigned flags, int32_t *kpToPt,
+                                      int32_t *ptBestIdx, int32_t *nMatches) {
+    Matcher *m = (Matcher *)h;
+    if (!m || !F || !L || !kpToPt || !nMatches) return argFailM("null argument");
+    if (F->n_frames < 0 || F->kp_stride < 1 || L->pt_stride < 1) return argFailM("bad sizes");
+    if (F->nlevels < 1 || F->nlevels > kMaxLevels || !F->scale_factors) return argFailM("nlevels must be 1..16 with scale_factors");
+    if (L->n_scale_levels < 1 || L->n_scale_levels > F->nlevels) return argFailM("n_scale_levels must be 1..nlevels");
+    if (!F->n_kp || !F->kps || !F->desc || !L->n_pts || !L->valid || !L->world_pos || !L->desc || !L->max_distance ||
+        !L->min_distance || !L->pose || (sim3 && !L->normal) || (checkOrientation && !L->angle))
+        return argFailM("null array in frame/keyframe-point view");
+    if (F->kp_stride > 65535) return argFailM("kp_stride must be <= 65535");
+    if (F->n_frames == 0) return 0;
+    YGZ_CUDA(cudaSetDevice(m->device));
+    const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
+    const size_t nf = F->n_frames, nk = nf * F->kp_stride, nm = nf * L->pt_stride;
+    ProjArgs A;
+    memset(&A, 0, sizeof A);
+    A.nFrames = F->n_frames; A.kpStride = F->kp_stride; A.mpStride = L->pt_stride;
+    int rc;
+    if ((rc = stageIn(m, 0, F->n_kp, nf, inDev, &A.nKp))) return rc;
+    if ((rc = stageIn(m, 1, L->n_pts, nf, inDev, &A.nMp))) return rc;
+    if ((rc = stageIn(m, 2, F->kps, nk, inDev, &A.kps))) return rc;
+    if ((rc = stageIn(m, 3, F->desc, nk * 32, inDev, &A.desc))) return rc;
+    if ((rc = stageIn(m, 5, F->claimed, F->claimed ? nk : 0, inDev, &A.claimed))) return rc;
+    if ((rc = stageIn(m, 6, L->world_pos, nm * 3, inDev, &A.worldPos))) return rc;
+    if ((rc = stageIn(m, 7, L->angle, L->angle ? nm : 0, inDev, &A.angleLast))) return rc;
+    if ((rc = stageIn(m, 8, L->normal, L->normal ? nm * 3 : 0, inDev, &A.normal))) return rc;
+    if ((rc = stageIn(m, 9, L->pose, nf * 30, inDev, &A.pose))) return rc;
+    if ((rc = stageIn(m, 10, L->max_distance, nm, inDev, &A.maxDist))) return rc;
+    if ((rc = stageIn(m, 11, L->valid, nm, inDev, &A.inView))) return rc;
+    if ((rc = stageIn(m, 12, L->min_distance, nm, inDev, &A.minDist))) return rc;
+    if ((rc = stageIn(m, 13, L->desc, nm * 32, inDev, &A.mpDesc))) return rc;
+    A.minX = F->min_x; A.minY = F->min_y; A.maxX = F->max_x; A.maxY = F->max_y;
+    A.invW = (float)kGridCols / (F->max_x - F->min_x);
+    A.invH = (float)kGridRows / (F->max_y - F->min_y);
+    for (int l = 0; l < F->nlevels; l++) A.scale[l] = F->scale_factors[l];
+    A.th = th; A.checkLevel = 1; A.checkOrientation = checkOrientation;
+    A.logScale = L->log_scale_factor; A.nScaleLevels = L->n_scale_levels; A.bestDistMax = bestDistMax;
+    if ((rc = stageOut(m, 14, kpToPt, nk, outDev, &A.kpToMp))) return rc;
+    if ((rc = stageOut(m, 15, ptBestIdx, nm, outDev, &A.mpBestIdx))) return rc;
+    if ((rc = stageOut(m, 16, nMatches, nf, outDev, &A.nMatches))) return rc;
+    void *p;
+    if ((rc = scratch(m, 17, nk * 4, &p))) return rc;
+    A.claimTime = (int32_t *)p;
+    if ((rc = scratch(m, 18, nk * 4, &p))) return rc;
+    A.gridList = (int32_t *)p;
+    if ((rc = scratch(m, 19, nm * 12 * 4, &p))) return rc;
+    A.candCache = (uint32_t *)p;
+    if ((rc = scratch(m, 20, nm, &p))) return rc;
+    A.candCnt = (uint8_t *)p;
+    m->launches += launchSearchByProjectionKeyFrame(A, sim3, m->stream);
+    if ((rc = copyOut(m, kpToPt, A.kpToMp, nk, outDev))) return rc;
+    if ((rc = copyOut(m, ptBestIdx, A.mpBestIdx, nm, outDev))) return rc;
+    if ((rc = copyOut(m, nMatches, A.nMatches, nf, outDev))) return rc;
+    return finish(m, flags);
+}
+
+int ygzorb_search_by_projection_reloc(ygzorb_matcher *h, const ygzorb_frame_features *F, const ygzorb_keyframe_points *L, float th,
+                                      int orbDist, int checkOrientation, unsigned flags, int32_t *kpToPt, int32_t *ptBestIdx,
+                                      int32_t *nMatches) {
+    return searchByProjectionKeyFrame(h, F, L, th, orbDist, checkOrientation, 0, flags, kpToPt, ptBestIdx, nMatches);
+}
+
+int ygzorb_search_by_projection_sim3(ygzorb_matcher *h, const ygzorb_frame_features *F, const ygzorb_keyframe_points *L, int th,
+                                     unsigned flags, int32_t *kpToPt, int32_t *ptBestIdx, int32_t *nMatches) {
+    return searchByProjectionKeyFrame(h, F, L, (float)th, kThLow, 0, 1, flags, kpToPt, ptBestIdx, nMatches);
+}
+
 static int stageKf(Matcher *m, int slot0, const ygzorb_keyframe_features *K, bool inDev, KfView *V) {
     int rc;
     V->n = K->n; V->nNodes = K->n_nodes;

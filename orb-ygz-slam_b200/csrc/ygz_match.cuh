@@ -28,6 +28,11 @@ struct ProjArgs {
     const int32_t *octaveLast;
     float maxX, maxY;
     int bMono, checkOrientation;
+    // KeyFrame-point variants: relocalisation (:1352-1469, MODE 2; pose = Rcw, tcw, -, -, fx, fy, cx, cy) and Sim3
+    // (:265-373, MODE 3; pose = Rcw, tcw, Ow, -, fx, fy, cx, cy).  maxDist / minDist = mfMaxDistance / mfMinDistance.
+    const float *maxDist, *minDist, *normal;
+    float logScale;
+    int nScaleLevels, bestDistMax;
     int32_t *kpToMp, *mpBestIdx, *nMatches;   // outputs (mpBestIdx is also the iteration state)
     int32_t *claimTime;                       // scratch [nFrames * kpStride]
     int32_t *gridList;                        // scratch [nFrames * kpStride]
@@ -83,6 +88,7 @@ int launchKnn2(const uint8_t *query, int nq, const uint8_t *train, int nt, float
                int variant, int32_t *bestIdx, int32_t *d1, int32_t *d2, int32_t *match, cudaStream_t s);
 int launchSearchByProjection(const ProjArgs &A, int maxKp, cudaStream_t s);
 int launchSearchByProjectionLast(const ProjArgs &A, cudaStream_t s);
+int launchSearchByProjectionKeyFrame(const ProjArgs &A, int sim3, cudaStream_t s);
 
 #ifdef __CUDACC__
 // ORBmatcher::DescriptorDistance / FORB::distance on two 256-bit rows held as 2 x uint4

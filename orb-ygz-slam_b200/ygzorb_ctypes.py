@@ -221,6 +221,13 @@ class LastFramePoints(C.Structure):
                 ("pose", C.c_void_p)]
 
 
+class KeyFramePoints(C.Structure):
+    _fields_ = [("pt_stride", C.c_int), ("n_pts", C.c_void_p), ("valid", C.c_void_p), ("world_pos", C.c_void_p),
+                ("normal", C.c_void_p), ("desc", C.c_void_p), ("angle", C.c_void_p), ("max_distance", C.c_void_p),
+                ("min_distance", C.c_void_p), ("pose", C.c_void_p), ("log_scale_factor", C.c_float),
+                ("n_scale_levels", C.c_int)]
+
+
 class KeyFrameFeatures(C.Structure):
     _fields_ = [("n", C.c_int), ("n_nodes", C.c_int), ("nlevels", C.c_int), ("kps", C.c_void_p), ("desc", C.c_void_p),
                 ("u_right", C.c_void_p), ("has_mappoint", C.c_void_p), ("node_ids", C.c_void_p),
@@ -260,6 +267,10 @@ class Matcher:
         L.ygzorb_vocabulary_arrays.argtypes = [C.c_void_p] * 6
         L.ygzorb_search_by_projection_last.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_int,
                                                        C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ygzorb_search_by_projection_reloc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_uint,
+                                                        C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ygzorb_search_by_projection_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_void_p,
+                                                       C.c_void_p, C.c_void_p]
         L.ygzorb_search_by_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_float,
                                                   C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ygzorb_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float,
@@ -388,6 +399,44 @@ class Matcher:
         kp_to_pt = np.zeros((nf, ks), np.int32); best = np.zeros((nf, ps), np.int32); nm = np.zeros(nf, np.int32)
         check(lib().ygzorb_search_by_projection_last(self.h, C.byref(F), C.byref(L), th, int(mono), int(check_level),
                                                      int(check_orientation), 0, _ptr(kp_to_pt), _ptr(best), _ptr(nm)))
+        return [(int(nm[i]), kp_to_pt[i, :n_kp[i]].copy(), best[i, :n_pt[i]].copy()) for i in range(nf)]
+
+    def search_by_projection_keyframe(self, frames, pts, bounds, scale_factors, th, sim3, orb_dist=100, check_orientation=False):
+        """The relocalisation (sim3=False) and Sim3 (sim3=True) projection searches.  frames: list of (kps, desc, claimed|None);
+        pts: list of dicts with valid, world_pos, normal, desc, angle, max_distance, min_distance, pose (30,),
+        log_scale_factor, n_scale_levels (tests/synth.keyframe_points_case).  Returns per pair (n, kp_to_pt, pt_best_idx)."""
+        nf = len(frames)
+        ks = max(max(len(f[0]) for f in frames), 1)
+        ps = max(max(len(l["valid"]) for l in pts), 1)
+        n_kp = np.array([len(f[0]) for f in frames], np.int32)
+        n_pt = np.array([len(l["valid"]) for l in pts], np.int32)
+        kps = np.zeros((nf, ks), KP_DTYPE); desc = np.zeros((nf, ks, 32), np.uint8)
+        has_cl = any(f[2] is not None for f in frames)
+        cl = np.zeros((nf, ks), np.uint8) if has_cl else None
+        for i, f in enumerate(frames):
+            kps[i, :len(f[0])] = f[0]; desc[i, :len(f[0])] = f[1]
+            if f[2] is not None:
+                cl[i, :len(f[0])] = f[2]
+        va = np.zeros((nf, ps), np.uint8); wp = np.zeros((nf, ps, 3), np.float32); nr = np.zeros((nf, ps, 3), np.float32)
+        pd = np.zeros((nf, ps, 32), np.uint8); an = np.zeros((nf, ps), np.float32)
+        mx = np.ones((nf, ps), np.float32); mn = np.ones((nf, ps), np.float32)
+        pose = np.zeros((nf, 30), np.float32)
+        for i, l in enumerate(pts):
+            k = len(l["valid"])
+            va[i, :k] = l["valid"]; wp[i, :k] = l["world_pos"]; nr[i, :k] = l["normal"]; pd[i, :k] = l["desc"]
+            an[i, :k] = l["angle"]; mx[i, :k] = l["max_distance"]; mn[i, :k] = l["min_distance"]; pose[i] = l["pose"]
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        F = FrameFeatures(nf, ks, _ptr(n_kp), _ptr(kps), _ptr(desc), None, _ptr(cl), bounds[0], bounds[1], bounds[2],
+                          bounds[3], len(sf), _ptr(sf))
+        L = KeyFramePoints(ps, _ptr(n_pt), _ptr(va), _ptr(wp), _ptr(nr), _ptr(pd), _ptr(an), _ptr(mx), _ptr(mn), _ptr(pose),
+                           float(pts[0]["log_scale_factor"]), int(pts[0]["n_scale_levels"]))
+        kp_to_pt = np.zeros((nf, ks), np.int32); best = np.zeros((nf, ps), np.int32); nm = np.zeros(nf, np.int32)
+        if sim3:
+            check(lib().ygzorb_search_by_projection_sim3(self.h, C.byref(F), C.byref(L), int(th), 0, _ptr(kp_to_pt), _ptr(best),
+                                                         _ptr(nm)))
+        else:
+            check(lib().ygzorb_search_by_projection_reloc(self.h, C.byref(F), C.byref(L), th, int(orb_dist),
+                                                          int(check_orientation), 0, _ptr(kp_to_pt), _ptr(best), _ptr(nm)))
         return [(int(nm[i]), kp_to_pt[i, :n_kp[i]].copy(), best[i, :n_pt[i]].copy()) for i in range(nf)]
 
     def search_by_projection_raw(self, F, P, th, check_level, nnratio, flags, kp_to_mp_ptr, best_ptr, nm_ptr):

@@ -246,6 +246,29 @@ def search_by_projection_last(kps, desc, u_right, claimed, bounds, scale_factors
     return nm, kp_to_pt[:n].copy(), best[:m].copy()
 
 
+def search_by_projection_keyframe(kps, desc, claimed, bounds, scale_factors, pts, th, sim3, orb_dist=100,
+                                  check_orientation=False):
+    """pts: dict as tests/synth.keyframe_points_case makes it.  Returns (n_matches, kp_to_pt, pt_best_idx)."""
+    n, m = len(kps), len(pts["valid"])
+    kps = np.ascontiguousarray(kps)
+    desc = np.ascontiguousarray(desc, np.uint8)
+    inv_w, inv_h = grid_inv(*bounds)
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    u8 = lambda a: np.ascontiguousarray(a, np.uint8)
+    sf = f32(scale_factors)
+    cl = u8(claimed) if claimed is not None else None
+    va, wp, nr, pd, an = u8(pts["valid"]), f32(pts["world_pos"]), f32(pts["normal"]), u8(pts["desc"]), f32(pts["angle"])
+    mx, mn, pose = f32(pts["max_distance"]), f32(pts["min_distance"]), f32(pts["pose"])
+    kp_to_pt = np.zeros(max(n, 1), np.int32)
+    best = np.zeros(max(m, 1), np.int32)
+    nm = lib().ygzo_search_by_projection_keyframe(
+        _p(kps), _p(desc), _p(cl), n, C.c_float(bounds[0]), C.c_float(bounds[1]), C.c_float(bounds[2]), C.c_float(bounds[3]),
+        C.c_float(inv_w), C.c_float(inv_h), _p(sf), _p(pose), _p(va), _p(wp), _p(nr), _p(pd), _p(an), _p(mx), _p(mn), m,
+        C.c_float(pts["log_scale_factor"]), int(pts["n_scale_levels"]), C.c_float(th), int(orb_dist), int(check_orientation),
+        int(sim3), _p(kp_to_pt), _p(best))
+    return nm, kp_to_pt[:n].copy(), best[:m].copy()
+
+
 def search_by_bow(kf1, second, second_is_frame, nnratio, check_orientation):
     """kf dicts: kps, desc, has_mp, node_ids, node_start, node_feats.  Returns (n_matches, matches)."""
     def pk(kf):

@@ -151,6 +151,53 @@ def lastframe_case(kps, desc, n_pts, seed, motion=(0.02, -0.01, 0.3), jitter=2.0
     return last, u_right, claimed
 
 
+def keyframe_points_case(kps, desc, n_pts, seed, sim3, jitter=2.0, fx=458.654, fy=457.296, cx=367.215, cy=248.375,
+                         scale=1.2, nlevels=8, p_invalid=0.1, rot_outliers=0.15):
+    """MapPoints of a KeyFrame for the relocalisation / Sim3 projection searches: world points that project next to
+    keypoints of the searched frame (kps/desc), with mfMaxDistance chosen so that PredictScale lands near the source
+    keypoint's octave; a few points violate the distance range, the viewing angle (Sim3) or sit behind the camera."""
+    rng = np.random.default_rng(seed)
+    n = len(kps)
+    src = rng.integers(0, n, size=n_pts)
+    u = kps["x"][src] + rng.uniform(-jitter, jitter, n_pts)
+    v = kps["y"][src] + rng.uniform(-jitter, jitter, n_pts)
+    z = rng.uniform(1.0, 12.0, n_pts)
+    z[rng.uniform(size=n_pts) < 0.03] *= -1.0
+    th = rng.uniform(-0.02, 0.02, 3)
+    Rcw = np.array([[1, -th[2], th[1]], [th[2], 1, -th[0]], [-th[1], th[0], 1]], np.float64)
+    tcw = rng.uniform(-0.2, 0.2, 3)
+    pc = np.stack([(u - cx) / fx * z, (v - cy) / fy * z, z], 1)
+    pw = (np.linalg.inv(Rcw) @ (pc - tcw).T).T
+    Ow = -Rcw.T @ tcw
+    PO = pw - Ow
+    dist = np.linalg.norm(PO, axis=1)
+    # PredictScale = ceil(log(maxD / dist) / log(scale)): aim at the source octave (+-1), fractional part uniform
+    lvl = np.clip(kps["octave"][src] + rng.integers(-1, 2, n_pts), 0, nlevels - 1)
+    max_d = dist * scale ** (lvl - rng.uniform(0.05, 0.95, n_pts))
+    min_d = max_d / scale ** (nlevels - 1)
+    bad_range = rng.uniform(size=n_pts) < 0.05
+    max_d = np.where(bad_range, dist * 0.5, max_d)
+    normal = PO / dist[:, None] + rng.normal(0, 0.2, (n_pts, 3))
+    steep = rng.uniform(size=n_pts) < 0.08
+    normal[steep] *= -1.0
+    ang = kps["angle"][src] + rng.normal(0, 3.0, n_pts)
+    out = rng.uniform(size=n_pts) < rot_outliers
+    ang = np.mod(np.where(out, ang + rng.uniform(40, 320, n_pts), ang), 360.0)
+    pose = np.zeros(30, np.float32)
+    pose[:9] = Rcw.reshape(9); pose[9:12] = tcw; pose[24:28] = [fx, fy, cx, cy]
+    if sim3:
+        pose[12:15] = Ow
+    pts = {
+        "valid": (rng.uniform(size=n_pts) >= p_invalid).astype(np.uint8),
+        "world_pos": pw.astype(np.float32), "normal": normal.astype(np.float32),
+        "desc": flip_bits(desc[src], rng.integers(0, 45, size=n_pts), rng),
+        "angle": ang.astype(np.float32), "max_distance": max_d.astype(np.float32), "min_distance": min_d.astype(np.float32),
+        "pose": pose, "log_scale_factor": float(np.float32(np.log(np.float32(scale)))), "n_scale_levels": nlevels, "src": src,
+    }
+    claimed = (rng.uniform(size=n) < 0.05).astype(np.uint8)
+    return pts, claimed
+
+
 def feature_vector(n, n_nodes, seed, base=None, p_keep=0.8):
     """Synthetic DBoW2::FeatureVector as CSR: ascending node ids, features in insertion (index) order.
     With `base` (node of each feature of another keyframe mapped through `src`) matched features

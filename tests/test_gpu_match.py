@@ -92,6 +92,26 @@ def test_search_by_projection_last_vs_oracle(matcher, feats, th, mono, check_lev
         assert np.array_equal(g[1], e[1]) and np.array_equal(g[2], e[2])
 
 
+@pytest.mark.parametrize("th,sim3,orb_dist,check_ori,seed", [
+    (10.0, False, 100, True, 1), (3.0, False, 64, True, 2), (15.0, False, 100, False, 3), (10.0, True, 50, False, 4),
+    (4.0, True, 50, False, 5), (40.0, True, 50, False, 6)])
+def test_search_by_projection_keyframe_vs_oracle(matcher, feats, th, sim3, orb_dist, check_ori, seed):
+    """The relocalisation (src/ORBmatcher.cc:1352-1469) and Sim3 (:265-373) projection searches: in-kernel projection,
+    distance range, viewing angle, PredictScale, level window, claim order, rotation rejection."""
+    img, kps, desc = feats
+    sf, _, _ = synth.scale_tables()
+    bounds = (0.0, 0.0, float(img.shape[1]), float(img.shape[0]))
+    frames, pts, exp = [], [], []
+    for k in range(3):
+        p, claimed = synth.keyframe_points_case(kps, desc, 1200 - 200 * k, seed * 10 + k, sim3)
+        frames.append((kps, desc, claimed)); pts.append(p)
+        exp.append(O.search_by_projection_keyframe(kps, desc, claimed, bounds, sf, p, th, sim3, orb_dist, check_ori))
+    got = matcher.search_by_projection_keyframe(frames, pts, bounds, sf, th, sim3, orb_dist, check_ori)
+    for g, e in zip(got, exp):
+        assert g[0] == e[0] and e[0] > 100
+        assert np.array_equal(g[1], e[1]) and np.array_equal(g[2], e[2])
+
+
 def test_search_by_projection_claim_chain(matcher, feats):
     """Many MapPoints aimed at the same keypoints: long claim chains must resolve like the serial loop."""
     img, kps, desc = feats

@@ -232,6 +232,127 @@ def test_search_by_projection_last_vs_python(th, mono, check_level, check_ori, s
         assert (a[2] >= 0).sum() > a[0]
 
 
+def _py_search_by_projection_keyframe(kps, desc, claimed, bounds, sf, pts, th, sim3, orb_dist, check_ori):
+    """src/ORBmatcher.cc:1352-1469 (sim3=False, Eigen order) and :265-373 (sim3=True) re-derived; the Sim3 variant calls the
+    installed OpenCV (cv2.gemm, cv2.norm) for the cv::Mat expressions, which pins the oracle's restatement of them."""
+    import cv2
+    f = np.float32
+    min_x, min_y, max_x, max_y = [f(b) for b in bounds]
+    inv_w, inv_h = f(64) / (max_x - min_x), f(48) / (max_y - min_y)
+    rnd = lambda v: int(math.floor(abs(v) + 0.5)) * (1 if v >= 0 else -1)
+    grid = {}
+    for i in range(len(kps)):
+        px, py = rnd(float((kps["x"][i] - min_x) * inv_w)), rnd(float((kps["y"][i] - min_y) * inv_h))
+        if 0 <= px < 64 and 0 <= py < 48:
+            grid.setdefault((px, py), []).append(i)
+    P = pts["pose"].astype(np.float32)
+    Rcw, tcw = P[0:9].reshape(3, 3), P[9:12]
+    fx, fy, cx, cy = P[24:28]
+    dot3 = lambda a0, a1, a2: f(a0 + f(a1 + a2))
+    Ow = P[12:15] if sim3 else np.array([f(-dot3(f(Rcw[0, r] * tcw[0]), f(Rcw[1, r] * tcw[1]), f(Rcw[2, r] * tcw[2]))) for r in range(3)], f)
+    D = _hamming_matrix(pts["desc"], desc)
+    blocked = claimed.astype(bool).copy() if claimed is not None else np.zeros(len(kps), bool)
+    kp_to_pt = np.full(len(kps), -1, np.int32)
+    best_of = np.full(len(pts["valid"]), -1, np.int32)
+    hist = [[] for _ in range(30)]
+    n = 0
+    log_sf, nlev = f(pts["log_scale_factor"]), int(pts["n_scale_levels"])
+    for i in range(len(pts["valid"])):
+        if not pts["valid"][i]:
+            continue
+        X = pts["world_pos"][i].astype(np.float32)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            if sim3:
+                c = cv2.gemm(Rcw, X.reshape(3, 1), 1.0, tcw.reshape(3, 1), 1.0)[:, 0]
+                if c[2] < 0.0:
+                    continue
+                invz = f(1) / c[2]
+                u, v = f(f(fx * f(c[0] * invz)) + cx), f(f(fy * f(c[1] * invz)) + cy)
+                if not (u >= min_x and u < max_x and v >= min_y and v < max_y):
+                    continue
+                PO = X - Ow
+                dist = f(cv2.norm(PO.reshape(3, 1)))
+            else:
+                c = [f(dot3(f(Rcw[r, 0] * X[0]), f(Rcw[r, 1] * X[1]), f(Rcw[r, 2] * X[2])) + tcw[r]) for r in range(3)]
+                invz = f(np.float64(1.0) / np.float64(c[2]))
+                u, v = f(f(f(fx * c[0]) * invz) + cx), f(f(f(fy * c[1]) * invz) + cy)
+                if not (np.isfinite(u) and np.isfinite(v)) or u < min_x or u > max_x or v < min_y or v > max_y:
+                    continue
+                PO = X - Ow
+                dist = f(np.sqrt(dot3(f(PO[0] * PO[0]), f(PO[1] * PO[1]), f(PO[2] * PO[2]))))
+        if dist < f(f(0.8) * pts["min_distance"][i]) or dist > f(f(1.2) * pts["max_distance"][i]):
+            continue
+        if sim3:
+            d = np.float64(0)
+            for r in range(3):
+                d = d + np.float64(PO[r]) * np.float64(pts["normal"][i][r])
+            if d < 0.5 * np.float64(dist):
+                continue
+        lvl = int(math.ceil(float(f(f(np.log(f(pts["max_distance"][i] / dist))) / log_sf))))
+        lvl = min(max(lvl, 0), nlev - 1)
+        rad = f(f(th) * sf[lvl])
+        lo, hi = lvl - 1, (lvl if sim3 else lvl + 1)
+        cx0 = max(0, math.floor(float(f(f(u - min_x - rad) * inv_w)))); cx1 = min(63, math.ceil(float(f(f(u - min_x + rad) * inv_w))))
+        cy0 = max(0, math.floor(float(f(f(v - min_y - rad) * inv_h)))); cy1 = min(47, math.ceil(float(f(f(v - min_y + rad) * inv_h))))
+        if cx0 >= 64 or cx1 < 0 or cy0 >= 48 or cy1 < 0:
+            continue
+        b1, bi = 256, -1
+        for ix in range(cx0, cx1 + 1):
+            for iy in range(cy0, cy1 + 1):
+                for idx in grid.get((ix, iy), []):
+                    ko = int(kps["octave"][idx])
+                    if ko < lo or ko > hi:
+                        continue
+                    if not (abs(f(kps["x"][idx] - u)) < rad and abs(f(kps["y"][idx] - v)) < rad):
+                        continue
+                    if blocked[idx]:
+                        continue
+                    if int(D[i, idx]) < b1:
+                        b1, bi = int(D[i, idx]), idx
+        if b1 <= orb_dist:
+            kp_to_pt[bi] = i; blocked[bi] = True; best_of[i] = bi; n += 1
+            if check_ori:
+                rot = f(pts["angle"][i] - kps["angle"][bi])
+                if rot < 0:
+                    rot = f(rot + f(360))
+                b = rnd(float(f(rot * f(f(1.0) / f(30)))))
+                hist[0 if b == 30 else b].append(bi)
+    if check_ori:
+        m1 = m2 = m3 = 0; i1 = i2 = i3 = -1
+        for i in range(30):
+            sz = len(hist[i])
+            if sz > m1:
+                m3, m2, m1, i3, i2, i1 = m2, m1, sz, i2, i1, i
+            elif sz > m2:
+                m3, m2, i3, i2 = m2, sz, i2, i
+            elif sz > m3:
+                m3, i3 = sz, i
+        if f(m2) < f(0.1) * f(m1):
+            i2 = i3 = -1
+        elif f(m3) < f(0.1) * f(m1):
+            i3 = -1
+        for i in range(30):
+            if i not in (i1, i2, i3):
+                for idx in hist[i]:
+                    kp_to_pt[idx] = -1; n -= 1
+    return n, kp_to_pt, best_of
+
+
+@pytest.mark.parametrize("th,sim3,orb_dist,check_ori,seed", [
+    (10.0, False, 100, True, 1), (3.0, False, 64, True, 2), (10.0, True, 50, False, 3), (4.0, True, 50, False, 4)])
+def test_search_by_projection_keyframe_vs_python(th, sim3, orb_dist, check_ori, seed):
+    img, (kps, desc) = _features(seed=seed)
+    sf, _, _ = synth.scale_tables()
+    pts, claimed = synth.keyframe_points_case(kps, desc, 500, seed, sim3, cx=160.0, cy=120.0)
+    bounds = (0.0, 0.0, float(img.shape[1]), float(img.shape[0]))
+    a = O.search_by_projection_keyframe(kps, desc, claimed, bounds, sf, pts, th, sim3, orb_dist, check_ori)
+    b = _py_search_by_projection_keyframe(kps, desc, claimed, bounds, sf, pts, th, sim3, orb_dist, check_ori)
+    assert a[0] == b[0] and a[0] > 30
+    assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+    if check_ori:
+        assert (a[2] >= 0).sum() > a[0]
+
+
 def test_search_by_projection_order_dependence():
     """Two MapPoints with the same descriptor on the same keypoint: the first claims it, the second must skip it."""
     img, (kps, desc) = _features(seed=9)
