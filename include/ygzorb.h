@@ -267,6 +267,27 @@ int ygzorb_search_by_projection_reloc(ygzorb_matcher *m, const ygzorb_frame_feat
 int ygzorb_search_by_projection_sim3(ygzorb_matcher *m, const ygzorb_frame_features *kf, const ygzorb_keyframe_points *pts,
                                      int th, unsigned flags, int32_t *kp_to_pt, int32_t *pt_best_idx, int32_t *n_matches);
 
+/* ORBmatcher::Fuse, the search half of both overloads (the MapPoint graph updates — Replace / AddObservation /
+ * AddMapPoint, :862-877 and :989-998 — stay with the caller, who walks pt_best_idx in order):
+ *   sim3 = 0: Fuse(KeyFrame *pKF, const vector<MapPoint*> &vpMapPoints, th) (src/ORBmatcher.cc:748-886).  Eigen
+ *     arithmetic; pose[12..14] = pKF->GetCameraCenter(), pose[28] = mbf; kf->u_right = mvuRight and inv_level_sigma2 =
+ *     mvInvLevelSigma2 feed the chi-square gate (:835-858).  valid = pMP && !isBad() && !IsInKeyFrame(pKF).
+ *   sim3 = 1: Fuse(KeyFrame *pKF, cv::Mat Scw, vpPoints, th, vpReplacePoint) (:888-1004).  cv::Mat arithmetic, pose as in
+ *     ygzorb_search_by_projection_sim3; valid = !isBad() && not in pKF->GetMapPoints().
+ * pt_best_idx[f*pt_stride + i] = bestIdx when bestDist <= TH_LOW, else -1; n_fused[f] = number of such points (nFused). */
+int ygzorb_fuse(ygzorb_matcher *m, const ygzorb_frame_features *kf, const ygzorb_keyframe_points *pts, float th, int sim3,
+                const float *inv_level_sigma2, unsigned flags, int32_t *pt_best_idx, int32_t *n_fused);
+
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) (src/ORBmatcher.cc:1006-1216).  pts1 = KF1's
+ * MapPoints, entry i1 per keypoint (pt_stride == kf1->kp_stride), valid = pMP && !vbAlreadyMatched1[i1] && !isBad();
+ * its pose = R1w (0..8), t1w (9..11), sR21 (12..20), t21 (21..23), fx, fy, cx, cy (24..27; the reference uses KF1's
+ * intrinsics for both directions), and the image bounds of kf2 gate the projection.  pts2 likewise with R2w, t2w, sR12,
+ * t12.  sR12, sR21, t21 (:1023-1025) are the caller's cv::Mat results.  matches12[f*kp_stride1 + i1] = idx2 when both
+ * directions agree (:1182-1196), else -1; n_found[f] = nFound. */
+int ygzorb_search_by_sim3(ygzorb_matcher *m, const ygzorb_frame_features *kf1, const ygzorb_frame_features *kf2,
+                          const ygzorb_keyframe_points *pts1, const ygzorb_keyframe_points *pts2, float th, unsigned flags,
+                          int32_t *matches12, int32_t *n_found);
+
 /* KeyFrame arrays read by SearchForTriangulation (include/KeyFrame.h:236-271); the DBoW2::FeatureVector
  * (Thirdparty/DBoW2/DBoW2/FeatureVector.h:23-24, std::map<NodeId, vector<unsigned>>) flattened to CSR:
  * node_ids ascending, features of node k = node_feats[node_start[k] .. node_start[k+1]). */

@@ -276,60 +276,73 @@ static int predictScale(float maxDistance, float currentDist, float logScaleFact
     return nScale;
 }
 
-// The two projection searches over a KeyFrame's MapPoints that predict the level from the distance:
-//   sim3 = 0: SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, sAlreadyFound, th, ORBdist), src/ORBmatcher.cc:1352-1469.
+// The projection searches over MapPoints that predict the level from the distance (MapPoint::PredictScale):
+//   variant 0: SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, sAlreadyFound, th, ORBdist), src/ORBmatcher.cc:1352-1469.
 //     Eigen arithmetic, canonical order as in ygzo_search_by_projection_last.  pose = Rcw(9), tcw(3), -, fx, fy, cx, cy at 24..27.
-//   sim3 = 1: SearchByProjection(KeyFrame *pKF, cv::Mat Scw, vpPoints, vpMatched, th), :265-373.  pose = Rcw, tcw, Ow (12..14)
-//     as decomposed by the caller (:275-278).  cv::Mat arithmetic as OpenCV 4.13 evaluates it (tests/test_match_oracle.py
-//     checks this against cv2.gemm / cv2.norm): gemm 3x3 * 3x1 + c = ((a0 + a1) + a2) + c in float; cv::norm and Mat::dot
-//     accumulate in double in index order.
-// blocked = CurrentFrame.mvpMapPoints[i2] / vpMatched[idx] non-null on entry.  Returns nmatches.
-YGZO_API int ygzo_search_by_projection_keyframe(const void *kpsV, const uint8_t *desc, const uint8_t *claimed, int n, float minX,
-                                                float minY, float maxX, float maxY, float invW, float invH,
-                                                const float *scaleFactors, const float *pose, const uint8_t *valid,
-                                                const float *worldPos, const float *normal, const uint8_t *ptDesc,
-                                                const float *angleKF, const float *maxDistance, const float *minDistance, int m,
-                                                float logScaleFactor, int nScaleLevels, float th, int bestDistMax,
-                                                int checkOrientation, int sim3, int32_t *kpToPt, int32_t *ptBestIdx) {
+//   variant 1: SearchByProjection(KeyFrame *pKF, cv::Mat Scw, vpPoints, vpMatched, th), :265-373.  pose = Rcw, tcw, Ow (12..14)
+//     as decomposed by the caller (:275-278).
+//   variant 2: the search of Fuse(KeyFrame *pKF, vpMapPoints, th), :748-886.  Eigen; pose[12..14] = Ow, pose[28] = bf; uRight =
+//     mvuRight, invSigma2 = mvInvLevelSigma2.  No claims: ptBestIdx[i] is the keypoint Fuse would act on, the return value nFused.
+//   variant 3: the search of Fuse(KeyFrame *pKF, cv::Mat Scw, vpPoints, th, vpReplacePoint), :888-1004.  pose as variant 1.
+//   variant 4: one direction of SearchBySim3, :1043-1110 (the other, :1113-1180, is the same code with the roles swapped).
+//     pose = R1w (0..8), t1w (9..11), sR21 (12..20), t21 (21..23), fx, fy, cx, cy.  Accepts bestDist <= TH_HIGH.
+// cv::Mat arithmetic as OpenCV 4.13 evaluates it (tests/test_match_oracle.py checks this against cv2.gemm / cv2.norm):
+// gemm 3x3 * 3x1 + c = ((a0 + a1) + a2) + c in float; cv::norm and Mat::dot accumulate in double in index order.
+// blocked = CurrentFrame.mvpMapPoints[i2] / vpMatched[idx] non-null on entry (variants 0, 1).
+YGZO_API int ygzo_search_by_projection_keyframe(const void *kpsV, const uint8_t *desc, const uint8_t *claimed, const float *uRight,
+                                                int n, float minX, float minY, float maxX, float maxY, float invW, float invH,
+                                                const float *scaleFactors, const float *invSigma2, const float *pose,
+                                                const uint8_t *valid, const float *worldPos, const float *normal,
+                                                const uint8_t *ptDesc, const float *angleKF, const float *maxDistance,
+                                                const float *minDistance, int m, float logScaleFactor, int nScaleLevels, float th,
+                                                int bestDistMax, int checkOrientation, int variant, int32_t *kpToPt,
+                                                int32_t *ptBestIdx) {
     const KeyPoint *kps = (const KeyPoint *)kpsV;
+    const bool eigen = variant == 0 || variant == 2, claims = variant <= 1;
     Grid g;
     assignGrid(g, kps, n, minX, minY, invW, invH);
     std::vector<uint8_t> blocked(n, 0);
-    for (int i = 0; i < n; i++) { kpToPt[i] = -1; blocked[i] = claimed ? claimed[i] : 0; }
+    for (int i = 0; i < n; i++) { kpToPt[i] = -1; blocked[i] = (claims && claimed) ? claimed[i] : 0; }
     int nmatches = 0;
     std::vector<int> rotHist[HISTO_LENGTH];
     const float *Rcw = pose, *tcw = pose + 9;
-    const float fx = pose[24], fy = pose[25], cx = pose[26], cy = pose[27];
+    const float fx = pose[24], fy = pose[25], cx = pose[26], cy = pose[27], bf = pose[28];
     auto dot3 = [](float a0, float a1, float a2) { const float s = a1 + a2; return a0 + s; };
+    auto gemm3 = [](const float *R, const float *x, const float *t, float *out) {
+        for (int r = 0; r < 3; r++) {
+            float t0 = R[3 * r] * x[0]; t0 = t0 + R[3 * r + 1] * x[1]; t0 = t0 + R[3 * r + 2] * x[2];
+            out[r] = t0 + t[r];
+        }
+    };
     float Ow[3];
-    for (int r = 0; r < 3; r++) Ow[r] = sim3 ? pose[12 + r] : -dot3(Rcw[r] * tcw[0], Rcw[3 + r] * tcw[1], Rcw[6 + r] * tcw[2]);   // :1358
+    for (int r = 0; r < 3; r++) Ow[r] = variant == 0 ? -dot3(Rcw[r] * tcw[0], Rcw[3 + r] * tcw[1], Rcw[6 + r] * tcw[2]) : pose[12 + r];   // :1358
     std::vector<int> vIndices;
     for (int i = 0; i < m; i++) {
         if (ptBestIdx) ptBestIdx[i] = -1;
         if (!valid[i]) continue;
         const float *X = worldPos + 3 * (size_t)i;
-        float c[3], u, v;
-        if (!sim3) {
-            for (int r = 0; r < 3; r++) c[r] = dot3(Rcw[3 * r] * X[0], Rcw[3 * r + 1] * X[1], Rcw[3 * r + 2] * X[2]) + tcw[r];
-            const float invzc = (float)(1.0 / (double)c[2]);
-            u = fx * c[0] * invzc + cx; v = fy * c[1] * invzc + cy;
+        float c[3], u, v, invz;
+        if (eigen) for (int r = 0; r < 3; r++) c[r] = dot3(Rcw[3 * r] * X[0], Rcw[3 * r + 1] * X[1], Rcw[3 * r + 2] * X[2]) + tcw[r];
+        else gemm3(Rcw, X, tcw, c);
+        if (variant == 4) { float c2[3]; gemm3(pose + 12, c, pose + 21, c2); c[0] = c2[0]; c[1] = c2[1]; c[2] = c2[2]; }
+        if (variant == 0) {
+            invz = (float)(1.0 / (double)c[2]);
+            u = fx * c[0] * invz + cx; v = fy * c[1] * invz + cy;
             if (!std::isfinite(u) || !std::isfinite(v)) continue;
             if (u < minX || u > maxX) continue;
             if (v < minY || v > maxY) continue;
         } else {
-            for (int r = 0; r < 3; r++) {
-                float t0 = Rcw[3 * r] * X[0]; t0 = t0 + Rcw[3 * r + 1] * X[1]; t0 = t0 + Rcw[3 * r + 2] * X[2];
-                c[r] = t0 + tcw[r];
-            }
-            if (c[2] < 0.0) continue;
-            const float invz = 1 / c[2];
+            if (c[2] < 0.0f) continue;
+            invz = variant == 1 || variant == 2 ? 1 / c[2] : (float)(1.0 / c[2]);
             const float x = c[0] * invz, y = c[1] * invz;
             u = fx * x + cx; v = fy * y + cy;
             if (!(u >= minX && u < maxX && v >= minY && v < maxY)) continue;   // KeyFrame::IsInImage
         }
-        const float PO[3] = {X[0] - Ow[0], X[1] - Ow[1], X[2] - Ow[2]};
+        const float ur = u - bf * invz;
+        float PO[3] = {X[0] - Ow[0], X[1] - Ow[1], X[2] - Ow[2]};
+        if (variant == 4) { PO[0] = c[0]; PO[1] = c[1]; PO[2] = c[2]; }   // dist3D = cv::norm(p3Dc2)
         float dist3D;
-        if (!sim3) dist3D = std::sqrt(dot3(PO[0] * PO[0], PO[1] * PO[1], PO[2] * PO[2]));
+        if (eigen) dist3D = std::sqrt(dot3(PO[0] * PO[0], PO[1] * PO[1], PO[2] * PO[2]));
         else {
             double s = 0;
             for (int r = 0; r < 3; r++) s += (double)PO[r] * (double)PO[r];
@@ -337,24 +350,38 @@ YGZO_API int ygzo_search_by_projection_keyframe(const void *kpsV, const uint8_t 
         }
         const float maxD = 1.2f * maxDistance[i], minD = 0.8f * minDistance[i];
         if (dist3D < minD || dist3D > maxD) continue;
-        if (sim3) {
+        if (variant >= 1 && variant <= 3) {
+            const float *Pn = normal + 3 * (size_t)i;
             double d = 0;
-            for (int r = 0; r < 3; r++) d += (double)PO[r] * (double)normal[3 * (size_t)i + r];
+            if (variant == 2) d = dot3(PO[0] * Pn[0], PO[1] * Pn[1], PO[2] * Pn[2]);
+            else for (int r = 0; r < 3; r++) d += (double)PO[r] * (double)Pn[r];
             if (d < 0.5 * dist3D) continue;
         }
         const int nPredictedLevel = predictScale(maxDistance[i], dist3D, logScaleFactor, nScaleLevels);
         const float radius = th * scaleFactors[nPredictedLevel];
-        featuresInArea(g, kps, u, v, radius, nPredictedLevel - 1, sim3 ? nPredictedLevel : nPredictedLevel + 1, vIndices);
+        featuresInArea(g, kps, u, v, radius, nPredictedLevel - 1, variant == 0 ? nPredictedLevel + 1 : nPredictedLevel, vIndices);
         if (vIndices.empty()) continue;
         int bestDist = 256, bestIdx2 = -1;
         for (int i2 : vIndices) {
             if (blocked[i2]) continue;
+            if (variant == 2) {   // :835-858
+                const int kpLevel = kps[i2].octave;
+                const float ex = u - kps[i2].x, ey = v - kps[i2].y;
+                if (uRight && uRight[i2] >= 0) {
+                    const float er = ur - uRight[i2];
+                    const float e2 = ex * ex + ey * ey + er * er;
+                    if (e2 * invSigma2[kpLevel] > 7.8) continue;
+                } else {
+                    const float e2 = ex * ex + ey * ey;
+                    if (e2 * invSigma2[kpLevel] > 5.99) continue;
+                }
+            }
             const int dist = descriptorDistance(ptDesc + (size_t)i * 32, desc + (size_t)i2 * 32);
             if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
         }
         if (bestDist <= bestDistMax) {
             kpToPt[bestIdx2] = i;
-            blocked[bestIdx2] = 1;
+            if (claims) blocked[bestIdx2] = 1;
             if (ptBestIdx) ptBestIdx[i] = bestIdx2;
             nmatches++;
             if (checkOrientation) rotHist[rotationBin(angleKF[i], kps[bestIdx2].angle)].push_back(bestIdx2);
@@ -369,6 +396,17 @@ YGZO_API int ygzo_search_by_projection_keyframe(const void *kpsV, const uint8_t 
                 for (int idx : rotHist[i]) { kpToPt[idx] = -1; nmatches--; }
     }
     return nmatches;
+}
+
+// SearchBySim3 "check agreement" (src/ORBmatcher.cc:1182-1196) over the two directions' results.
+YGZO_API int ygzo_sim3_agreement(const int32_t *vnMatch1, int n1, const int32_t *vnMatch2, int n2, int32_t *matches12) {
+    int nFound = 0;
+    for (int i1 = 0; i1 < n1; i1++) {
+        matches12[i1] = -1;
+        const int idx2 = vnMatch1[i1];
+        if (idx2 >= 0 && idx2 < n2 && vnMatch2[idx2] == i1) { matches12[i1] = idx2; nFound++; }
+    }
+    return nFound;
 }
 
 // ORBmatcher::SearchByBoW — both overloads over flattened FeatureVectors (CSR, ascending NodeId):

@@ -310,50 +310,65 @@ __device__ __forceinline__ int predictScale(const ProjArgs &A, float maxDistance
     return nScale;
 }
 
-// MODE 2: SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, sAlreadyFound, th, ORBdist) (:1352-1469), Eigen
-// arithmetic (3-term sums as a0 + (a1 + a2)).  MODE 3: SearchByProjection(KeyFrame *pKF, Scw, vpPoints, vpMatched, th)
-// (:265-373), cv::Mat arithmetic: gemm = ((a0 + a1) + a2) + c in float, cv::norm and Mat::dot accumulate in double.
+// The projection variants over MapPoints with a predicted scale level.
+//   MODE 2: SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, sAlreadyFound, th, ORBdist) (:1352-1469), Eigen
+//   MODE 3: SearchByProjection(KeyFrame *pKF, Scw, vpPoints, vpMatched, th) (:265-373), cv::Mat
+//   MODE 4: Fuse(KeyFrame *pKF, vpMapPoints, th) (:748-886), Eigen     MODE 5: Fuse(pKF, Scw, vpPoints, th, ...) (:888-1004), cv::Mat
+//   MODE 6: one direction of SearchBySim3 (:1043-1110 / :1113-1180), cv::Mat, two chained transforms
+// Eigen arithmetic: 3-term sums as a0 + (a1 + a2).  cv::Mat arithmetic (OpenCV 4.13): gemm = ((a0 + a1) + a2) + c in
+// float, cv::norm and Mat::dot accumulate in double.
 template <int MODE> __device__ __forceinline__ bool projQueryKeyFramePoint(const ProjArgs &A, const float *P, size_t mo, float X0,
                                                                             float X1, float X2, ProjQuery &q) {
+    constexpr bool kEigen = MODE == 2 || MODE == 4;
     float c[3], Ow[3];
 #pragma unroll
     for (int r = 0; r < 3; r++) {
         const float a0 = __fmul_rn(P[3 * r], X0), a1 = __fmul_rn(P[3 * r + 1], X1), a2 = __fmul_rn(P[3 * r + 2], X2);
-        c[r] = MODE == 2 ? __fadd_rn(projDot3(a0, a1, a2), P[9 + r]) : __fadd_rn(__fadd_rn(__fadd_rn(a0, a1), a2), P[9 + r]);
+        c[r] = kEigen ? __fadd_rn(projDot3(a0, a1, a2), P[9 + r]) : __fadd_rn(__fadd_rn(__fadd_rn(a0, a1), a2), P[9 + r]);
         Ow[r] = MODE == 2 ? -projDot3(__fmul_rn(P[r], P[9]), __fmul_rn(P[3 + r], P[10]), __fmul_rn(P[6 + r], P[11])) : P[12 + r];
     }
-    float u, v;
+    if (MODE == 6) {   // p3Dc2 = sR21 * p3Dc1 + t21
+        float d[3];
+#pragma unroll
+        for (int r = 0; r < 3; r++)
+            d[r] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(P[12 + 3 * r], c[0]), __fmul_rn(P[13 + 3 * r], c[1])), __fmul_rn(P[14 + 3 * r], c[2])), P[21 + r]);
+        c[0] = d[0]; c[1] = d[1]; c[2] = d[2];
+    }
+    float u, v, invz;
     if (MODE == 2) {
-        const float invzc = __double2float_rn(__ddiv_rn(1.0, (double)c[2]));
-        u = __fadd_rn(__fmul_rn(__fmul_rn(P[24], c[0]), invzc), P[26]);
-        v = __fadd_rn(__fmul_rn(__fmul_rn(P[25], c[1]), invzc), P[27]);
+        invz = __double2float_rn(__ddiv_rn(1.0, (double)c[2]));
+        u = __fadd_rn(__fmul_rn(__fmul_rn(P[24], c[0]), invz), P[26]);
+        v = __fadd_rn(__fmul_rn(__fmul_rn(P[25], c[1]), invz), P[27]);
         if (!isfinite(u) || !isfinite(v)) return false;
         if (u < A.minX || u > A.maxX) return false;
         if (v < A.minY || v > A.maxY) return false;
     } else {
-        if ((double)c[2] < 0.0) return false;
-        const float invz = __fdiv_rn(1.0f, c[2]);
+        if (c[2] < 0.0f) return false;
+        invz = __fdiv_rn(1.0f, c[2]);   // 1 / z and (float)(1.0 / z) round alike
         u = __fadd_rn(__fmul_rn(P[24], __fmul_rn(c[0], invz)), P[26]);
         v = __fadd_rn(__fmul_rn(P[25], __fmul_rn(c[1], invz)), P[27]);
         if (!(u >= A.minX && u < A.maxX && v >= A.minY && v < A.maxY)) return false;   // KeyFrame::IsInImage
     }
-    const float PO0 = __fsub_rn(X0, Ow[0]), PO1 = __fsub_rn(X1, Ow[1]), PO2 = __fsub_rn(X2, Ow[2]);
+    const float PO0 = MODE == 6 ? c[0] : __fsub_rn(X0, Ow[0]), PO1 = MODE == 6 ? c[1] : __fsub_rn(X1, Ow[1]),
+                PO2 = MODE == 6 ? c[2] : __fsub_rn(X2, Ow[2]);
     float dist;
-    if (MODE == 2) dist = __fsqrt_rn(projDot3(__fmul_rn(PO0, PO0), __fmul_rn(PO1, PO1), __fmul_rn(PO2, PO2)));
+    if (kEigen) dist = __fsqrt_rn(projDot3(__fmul_rn(PO0, PO0), __fmul_rn(PO1, PO1), __fmul_rn(PO2, PO2)));
     else {
         const double s = __dadd_rn(__dadd_rn(__dmul_rn(PO0, PO0), __dmul_rn(PO1, PO1)), __dmul_rn(PO2, PO2));
         dist = __double2float_rn(__dsqrt_rn(s));
     }
     const float maxD = A.maxDist[mo];
     if (dist < __fmul_rn(0.8f, A.minDist[mo]) || dist > __fmul_rn(1.2f, maxD)) return false;
-    if (MODE == 3) {   // viewing angle below 60 degrees (:322-325)
+    if (MODE >= 3 && MODE <= 5) {   // viewing angle below 60 degrees (:322-325, :801-804, :951-954)
         const float *Pn = A.normal + 3 * mo;
-        const double d = __dadd_rn(__dadd_rn(__dmul_rn(PO0, Pn[0]), __dmul_rn(PO1, Pn[1])), __dmul_rn(PO2, Pn[2]));
+        const double d = MODE == 4 ? (double)projDot3(__fmul_rn(PO0, Pn[0]), __fmul_rn(PO1, Pn[1]), __fmul_rn(PO2, Pn[2]))
+                                   : __dadd_rn(__dadd_rn(__dmul_rn(PO0, Pn[0]), __dmul_rn(PO1, Pn[1])), __dmul_rn(PO2, Pn[2]));
         if (d < __dmul_rn(0.5, (double)dist)) return false;
     }
     const int lvl = predictScale(A, maxD, dist);
     q.rad = __fmul_rn(A.th, A.scale[lvl]);
-    q.x = u; q.y = v; q.xr = 0.f;
+    q.x = u; q.y = v;
+    q.xr = MODE == 4 ? __fsub_rn(u, __fmul_rn(P[28], invz)) : 0.f;
     q.minLevel = lvl - 1; q.maxLevel = MODE == 2 ? lvl + 1 : lvl;
     return true;
 }
@@ -437,9 +452,17 @@ __device__ int projMatchOne(const ProjArgs &A, int f, int j, int n, const int *c
             if (!(fabsf(__fsub_rn(kp.x, x)) < rad && fabsf(__fsub_rn(kp.y, y)) < rad)) continue;
             const bool skip = claimTime[idx] < j;                      // mvpMapPoints[idx]->Observations() > 0 (:89-91)
             if (!RECORD && skip) continue;
-            if (uRight) {
+            if (MODE <= 1 && uRight) {
                 const float ur = uRight[idx];
                 if (ur > 0 && fabsf(__fsub_rn(projXR, ur)) > rad) continue;   // :93-97
+            }
+            if (MODE == 4) {   // reprojection error gate of Fuse (:835-858)
+                const float ex = __fsub_rn(x, kp.x), ey = __fsub_rn(y, kp.y);
+                float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                const float kpr = uRight ? uRight[idx] : -1.0f;
+                double lim = 5.99;
+                if (kpr >= 0) { const float er = __fsub_rn(projXR, kpr); e2 = __fadd_rn(e2, __fmul_rn(er, er)); lim = 7.8; }
+                if ((double)__fmul_rn(e2, A.invSigma2[oct]) > lim) continue;
             }
             const int dist = hamming256(m0, m1, desc[2 * idx], desc[2 * idx + 1]);
             if (RECORD) {
@@ -519,7 +542,7 @@ template <int MODE> __global__ void __launch_bounds__(kProjThreads) k_search_by_
     }
     __syncthreads();
     // ---- fixed-point iteration over the claim table
-    for (int round = 1; round <= m + 1; round++) {
+    for (int round = 1; MODE < 4 && round <= m + 1; round++) {
         for (int i = tid; i < n; i += kProjThreads) claimTime[i] = (claimed && claimed[i]) ? -1 : INT_MAX;
         __syncthreads();
         for (int j = tid; j < m; j += kProjThreads) {
@@ -588,10 +611,43 @@ int launchSearchByProjection(const ProjArgs &A, int maxKp, cudaStream_t s) {
     return 1;
 }
 
-int launchSearchByProjectionKeyFrame(const ProjArgs &A, int sim3, cudaStream_t s) {
+int launchSearchByProjectionKeyFrame(const ProjArgs &A, int mode, cudaStream_t s) {
     if (A.nFrames <= 0) return 0;
-    if (sim3) k_search_by_projection<3><<<A.nFrames, kProjThreads, 0, s>>>(A);
-    else k_search_by_projection<2><<<A.nFrames, kProjThreads, 0, s>>>(A);
+    switch (mode) {
+        case 2: k_search_by_projection<2><<<A.nFrames, kProjThreads, 0, s>>>(A); break;
+        case 3: k_search_by_projection<3><<<A.nFrames, kProjThreads, 0, s>>>(A); break;
+        case 4: k_search_by_projection<4><<<A.nFrames, kProjThreads, 0, s>>>(A); break;
+        case 5: k_search_by_projection<5><<<A.nFrames, kProjThreads, 0, s>>>(A); break;
+        default: k_search_by_projection<6><<<A.nFrames, kProjThreads, 0, s>>>(A); break;
+    }
+    return 1;
+}
+
+// SearchBySim3 "check agreement" (:1182-1196): vnMatch1[i1] = idx2 stays when vnMatch2[idx2] == i1.
+__global__ void k_sim3_agreement(const int32_t *match1, const int32_t *match2, const int32_t *n1, const int32_t *n2, int stride1,
+                                 int stride2, int32_t *matches12, int32_t *nFound) {
+    const int f = blockIdx.x;
+    const int32_t *m1 = match1 + (size_t)f * stride1, *m2 = match2 + (size_t)f * stride2;
+    int cnt = 0;
+    for (int i1 = threadIdx.x; i1 < min(n1[f], stride1); i1 += blockDim.x) {
+        const int idx2 = m1[i1];
+        const bool ok = idx2 >= 0 && idx2 < min(n2[f], stride2) && m2[idx2] == i1;
+        matches12[(size_t)f * stride1 + i1] = ok ? idx2 : -1;
+        cnt += ok;
+    }
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    __shared__ int total;
+    if (threadIdx.x == 0) total = 0;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(&total, cnt);
+    __syncthreads();
+    if (threadIdx.x == 0) nFound[f] = total;
+}
+
+int launchSim3Agreement(const int32_t *match1, const int32_t *match2, const int32_t *n1, const int32_t *n2, int stride1, int stride2,
+                        int nFrames, int32_t *matches12, int32_t *nFound, cudaStream_t s) {
+    if (nFrames <= 0) return 0;
+    k_sim3_agreement<<<nFrames, 256, 0, s>>>(match1, match2, n1, n2, stride1, stride2, matches12, nFound);
     return 1;
 }
 

@@ -318,16 +318,20 @@ int ygzorb_search_by_projection_last(ygzorb_matcher *h, const ygzorb_frame_featu
     return finish(m, flags);
 }
 
+// Shared driver of the projection searches over MapPoints with a predicted level (kernel modes 2..6).  bestSlot = scratch
+// slot of the per-point result, so that SearchBySim3 can keep the first direction's result while the second one runs.
 static int searchByProjectionKeyFrame(ygzorb_matcher *h, const ygzorb_frame_features *F, const ygzorb_keyframe_points *L, float th,
-                                      int bestDistMax, int checkOrientation, int sim3, unsigned flags, int32_t *kpToPt,
-                                      int32_t *ptBestIdx, int32_t *nMatches) {
+                                      int bestDistMax, int checkOrientation, int mode, const float *invSigma2, unsigned flags,
+                                      int32_t *kpToPt, int32_t *ptBestIdx, int32_t *nMatches, int bestSlot = 15,
+                                      const int32_t **dBest = nullptr, const int32_t **dNPts = nullptr) {
     Matcher *m = (Matcher *)h;
-    if (!m || !F || !L || !kpToPt || !nMatches) return argFailM("null argument");
+    if (!m || !F || !L) return argFailM("null argument");
     if (F->n_frames < 0 || F->kp_stride < 1 || L->pt_stride < 1) return argFailM("bad sizes");
     if (F->nlevels < 1 || F->nlevels > kMaxLevels || !F->scale_factors) return argFailM("nlevels must be 1..16 with scale_factors");
     if (L->n_scale_levels < 1 || L->n_scale_levels > F->nlevels) return argFailM("n_scale_levels must be 1..nlevels");
+    const bool needNormal = mode >= 3 && mode <= 5;
     if (!F->n_kp || !F->kps || !F->desc || !L->n_pts || !L->valid || !L->world_pos || !L->desc || !L->max_distance ||
-        !L->min_distance || !L->pose || (sim3 && !L->normal) || (checkOrientation && !L->angle))
+        !L->min_distance || !L->pose || (needNormal && !L->normal) || (checkOrientation && !L->angle) || (mode == 4 && !invSigma2))
         return argFailM("null array in frame/keyframe-point view");
     if (F->kp_stride > 65535) return argFailM("kp_stride must be <= 65535");
     if (F->n_frames == 0) return 0;
@@ -342,7 +346,8 @@ static int searchByProjectionKeyFrame(ygzorb_matcher *h, const ygzorb_frame_feat
     if ((rc = stageIn(m, 1, L->n_pts, nf, inDev, &A.nMp))) return rc;
     if ((rc = stageIn(m, 2, F->kps, nk, inDev, &A.kps))) return rc;
     if ((rc = stageIn(m, 3, F->desc, nk * 32, inDev, &A.desc))) return rc;
-    if ((rc = stageIn(m, 5, F->claimed, F->claimed ? nk : 0, inDev, &A.claimed))) return rc;
+    if (mode == 4 && (rc = stageIn(m, 4, F->u_right, F->u_right ? nk : 0, inDev, &A.uRight))) return rc;
+    if (mode < 4 && (rc = stageIn(m, 5, F->claimed, F->claimed ? nk : 0, inDev, &A.claimed))) return rc;
     if ((rc = stageIn(m, 6, L->world_pos, nm * 3, inDev, &A.worldPos))) return rc;
     if ((rc = stageIn(m, 7, L->angle, L->angle ? nm : 0, inDev, &A.angleLast))) return rc;
     if ((rc = stageIn(m, 8, L->normal, L->normal ? nm * 3 : 0, inDev, &A.normal))) return rc;
@@ -354,11 +359,11 @@ static int searchByProjectionKeyFrame(ygzorb_matcher *h, const ygzorb_frame_feat
     A.minX = F->min_x; A.minY = F->min_y; A.maxX = F->max_x; A.maxY = F->max_y;
     A.invW = (float)kGridCols / (F->max_x - F->min_x);
     A.invH = (float)kGridRows / (F->max_y - F->min_y);
-    for (int l = 0; l < F->nlevels; l++) A.scale[l] = F->scale_factors[l];
+    for (int l = 0; l < F->nlevels; l++) { A.scale[l] = F->scale_factors[l]; A.invSigma2[l] = invSigma2 ? invSigma2[l] : 1.0f; }
     A.th = th; A.checkLevel = 1; A.checkOrientation = checkOrientation;
     A.logScale = L->log_scale_factor; A.nScaleLevels = L->n_scale_levels; A.bestDistMax = bestDistMax;
     if ((rc = stageOut(m, 14, kpToPt, nk, outDev, &A.kpToMp))) return rc;
-    if ((rc = stageOut(m, 15, ptBestIdx, nm, outDev, &A.mpBestIdx))) return rc;
+    if ((rc = stageOut(m, bestSlot, ptBestIdx, nm, outDev, &A.mpBestIdx))) return rc;
     if ((rc = stageOut(m, 16, nMatches, nf, outDev, &A.nMatches))) return rc;
     void *p;
     if ((rc = scratch(m, 17, nk * 4, &p))) return rc;
@@ -369,22 +374,70 @@ static int searchByProjectionKeyFrame(ygzorb_matcher *h, const ygzorb_frame_feat
     A.candCache = (uint32_t *)p;
     if ((rc = scratch(m, 20, nm, &p))) return rc;
     A.candCnt = (uint8_t *)p;
-    m->launches += launchSearchByProjectionKeyFrame(A, sim3, m->stream);
+    m->launches += launchSearchByProjectionKeyFrame(A, mode, m->stream);
     if ((rc = copyOut(m, kpToPt, A.kpToMp, nk, outDev))) return rc;
     if ((rc = copyOut(m, ptBestIdx, A.mpBestIdx, nm, outDev))) return rc;
     if ((rc = copyOut(m, nMatches, A.nMatches, nf, outDev))) return rc;
-    return finish(m, flags);
+    if (dBest) *dBest = A.mpBestIdx;
+    if (dNPts) *dNPts = A.nMp;
+    return 0;
 }
 
 int ygzorb_search_by_projection_reloc(ygzorb_matcher *h, const ygzorb_frame_features *F, const ygzorb_keyframe_points *L, float th,
                                       int orbDist, int checkOrientation, unsigned flags, int32_t *kpToPt, int32_t *ptBestIdx,
                                       int32_t *nMatches) {
-    return searchByProjectionKeyFrame(h, F, L, th, orbDist, checkOrientation, 0, flags, kpToPt, ptBestIdx, nMatches);
+    if (!kpToPt || !nMatches) return argFailM("null argument");
+    int rc = searchByProjectionKeyFrame(h, F, L, th, orbDist, checkOrientation, 2, nullptr, flags, kpToPt, ptBestIdx, nMatches);
+    return rc ? rc : (F->n_frames ? finish((Matcher *)h, flags) : 0);
 }
 
 int ygzorb_search_by_projection_sim3(ygzorb_matcher *h, const ygzorb_frame_features *F, const ygzorb_keyframe_points *L, int th,
                                      unsigned flags, int32_t *kpToPt, int32_t *ptBestIdx, int32_t *nMatches) {
-    return searchByProjectionKeyFrame(h, F, L, (float)th, kThLow, 0, 1, flags, kpToPt, ptBestIdx, nMatches);
+    if (!kpToPt || !nMatches) return argFailM("null argument");
+    int rc = searchByProjectionKeyFrame(h, F, L, (float)th, kThLow, 0, 3, nullptr, flags, kpToPt, ptBestIdx, nMatches);
+    return rc ? rc : (F->n_frames ? finish((Matcher *)h, flags) : 0);
+}
+
+int ygzorb_fuse(ygzorb_matcher *h, const ygzorb_frame_features *KF, const ygzorb_keyframe_points *L, float th, int sim3,
+                const float *invLevelSigma2, unsigned flags, int32_t *ptBestIdx, int32_t *nFused) {
+    if (!ptBestIdx || !nFused) return argFailM("null argument");
+    int rc = searchByProjectionKeyFrame(h, KF, L, th, kThLow, 0, sim3 ? 5 : 4, invLevelSigma2, flags, nullptr, ptBestIdx, nFused);
+    return rc ? rc : (KF->n_frames ? finish((Matcher *)h, flags) : 0);
+}
+
+int ygzorb_search_by_sim3(ygzorb_matcher *h, const ygzorb_frame_features *KF1, const ygzorb_frame_features *KF2,
+                          const ygzorb_keyframe_points *P1, const ygzorb_keyframe_points *P2, float th, unsigned flags,
+                          int32_t *matches12, int32_t *nFound) {
+    Matcher *m = (Matcher *)h;
+    if (!m || !KF1 || !KF2 || !P1 || !P2 || !matches12 || !nFound) return argFailM("null argument");
+    if (KF1->n_frames != KF2->n_frames) return argFailM("the two keyframe batches differ in length");
+    if (P1->pt_stride != KF1->kp_stride || P2->pt_stride != KF2->kp_stride)
+        return argFailM("MapPoint arrays are indexed by keypoint: pt_stride must equal kp_stride");
+    if (KF1->n_frames == 0) return 0;
+    const bool outDev = flags & YGZORB_OUT_DEVICE;
+    const unsigned inner = (flags & YGZORB_IN_DEVICE) | YGZORB_OUT_DEVICE;
+    const size_t nf = KF1->n_frames;
+    void *b1 = nullptr, *b2 = nullptr, *c1 = nullptr;
+    int rc;
+    if ((rc = scratch(m, 30, nf * P1->pt_stride * 4, &b1))) return rc;
+    if ((rc = scratch(m, 31, nf * P2->pt_stride * 4, &b2))) return rc;
+    if ((rc = scratch(m, 32, nf * 4 * 2, &c1))) return rc;
+    const int32_t *dN1 = nullptr, *dN2 = nullptr;
+    // KF1's MapPoints searched in KF2 (:1043-1110), then KF2's in KF1 (:1113-1180)
+    if ((rc = searchByProjectionKeyFrame(h, KF2, P1, th, kThHigh, 0, 6, nullptr, inner, nullptr, (int32_t *)b1, (int32_t *)c1, 15, nullptr, &dN1))) return rc;
+    // n_pts of the first direction must outlive the second call's staging: keep a copy
+    void *n1copy = nullptr;
+    if ((rc = scratch(m, 33, nf * 4, &n1copy))) return rc;
+    YGZ_CUDA(cudaMemcpyAsync(n1copy, dN1, nf * 4, cudaMemcpyDeviceToDevice, m->stream));
+    if ((rc = searchByProjectionKeyFrame(h, KF1, P2, th, kThHigh, 0, 6, nullptr, inner, nullptr, (int32_t *)b2, (int32_t *)c1 + nf, 15, nullptr, &dN2))) return rc;
+    int32_t *dM12 = nullptr, *dFound = nullptr;
+    if ((rc = stageOut(m, 34, matches12, nf * P1->pt_stride, outDev, &dM12))) return rc;
+    if ((rc = stageOut(m, 35, nFound, nf, outDev, &dFound))) return rc;
+    m->launches += launchSim3Agreement((const int32_t *)b1, (const int32_t *)b2, (const int32_t *)n1copy, dN2, P1->pt_stride,
+                                       P2->pt_stride, KF1->n_frames, dM12, dFound, m->stream);
+    if ((rc = copyOut(m, matches12, dM12, nf * P1->pt_stride, outDev))) return rc;
+    if ((rc = copyOut(m, nFound, dFound, nf, outDev))) return rc;
+    return finish(m, flags);
 }
 
 static int stageKf(Matcher *m, int slot0, const ygzorb_keyframe_features *K, bool inDev, KfView *V) {

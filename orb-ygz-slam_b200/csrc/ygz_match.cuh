@@ -30,7 +30,10 @@ struct ProjArgs {
     int bMono, checkOrientation;
     // KeyFrame-point variants: relocalisation (:1352-1469, MODE 2; pose = Rcw, tcw, -, -, fx, fy, cx, cy) and Sim3
     // (:265-373, MODE 3; pose = Rcw, tcw, Ow, -, fx, fy, cx, cy).  maxDist / minDist = mfMaxDistance / mfMinDistance.
+    // No-claim variants: Fuse (:748-886, MODE 4, Eigen; pose[12..14] = Ow, pose[28] = bf), Fuse with Sim3 (:888-1004, MODE 5,
+    // cv::Mat), one direction of SearchBySim3 (:1006-1216, MODE 6; pose = Rw, tw, sR, t of the target camera).
     const float *maxDist, *minDist, *normal;
+    float invSigma2[kMaxLevels];
     float logScale;
     int nScaleLevels, bestDistMax;
     int32_t *kpToMp, *mpBestIdx, *nMatches;   // outputs (mpBestIdx is also the iteration state)
@@ -88,7 +91,9 @@ int launchKnn2(const uint8_t *query, int nq, const uint8_t *train, int nt, float
                int variant, int32_t *bestIdx, int32_t *d1, int32_t *d2, int32_t *match, cudaStream_t s);
 int launchSearchByProjection(const ProjArgs &A, int maxKp, cudaStream_t s);
 int launchSearchByProjectionLast(const ProjArgs &A, cudaStream_t s);
-int launchSearchByProjectionKeyFrame(const ProjArgs &A, int sim3, cudaStream_t s);
+int launchSearchByProjectionKeyFrame(const ProjArgs &A, int mode, cudaStream_t s);
+int launchSim3Agreement(const int32_t *match1, const int32_t *match2, const int32_t *n1, const int32_t *n2, int stride1, int stride2,
+                        int nFrames, int32_t *matches12, int32_t *nFound, cudaStream_t s);
 
 #ifdef __CUDACC__
 // ORBmatcher::DescriptorDistance / FORB::distance on two 256-bit rows held as 2 x uint4

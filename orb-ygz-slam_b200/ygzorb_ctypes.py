@@ -271,6 +271,9 @@ class Matcher:
                                                         C.c_void_p, C.c_void_p, C.c_void_p]
         L.ygzorb_search_by_projection_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_void_p,
                                                        C.c_void_p, C.c_void_p]
+        L.ygzorb_fuse.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_uint, C.c_void_p, C.c_void_p]
+        L.ygzorb_search_by_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_uint,
+                                            C.c_void_p, C.c_void_p]
         L.ygzorb_search_by_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_float,
                                                   C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ygzorb_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float,
@@ -401,22 +404,23 @@ class Matcher:
                                                      int(check_orientation), 0, _ptr(kp_to_pt), _ptr(best), _ptr(nm)))
         return [(int(nm[i]), kp_to_pt[i, :n_kp[i]].copy(), best[i, :n_pt[i]].copy()) for i in range(nf)]
 
-    def search_by_projection_keyframe(self, frames, pts, bounds, scale_factors, th, sim3, orb_dist=100, check_orientation=False):
-        """The relocalisation (sim3=False) and Sim3 (sim3=True) projection searches.  frames: list of (kps, desc, claimed|None);
-        pts: list of dicts with valid, world_pos, normal, desc, angle, max_distance, min_distance, pose (30,),
-        log_scale_factor, n_scale_levels (tests/synth.keyframe_points_case).  Returns per pair (n, kp_to_pt, pt_best_idx)."""
+    def _keyframe_views(self, frames, pts, bounds, scale_factors, keep):
         nf = len(frames)
         ks = max(max(len(f[0]) for f in frames), 1)
         ps = max(max(len(l["valid"]) for l in pts), 1)
         n_kp = np.array([len(f[0]) for f in frames], np.int32)
         n_pt = np.array([len(l["valid"]) for l in pts], np.int32)
         kps = np.zeros((nf, ks), KP_DTYPE); desc = np.zeros((nf, ks, 32), np.uint8)
-        has_cl = any(f[2] is not None for f in frames)
+        has_cl = any(len(f) > 2 and f[2] is not None for f in frames)
+        has_ur = any(len(f) > 3 and f[3] is not None for f in frames)
         cl = np.zeros((nf, ks), np.uint8) if has_cl else None
+        ur = np.full((nf, ks), -1, np.float32) if has_ur else None
         for i, f in enumerate(frames):
             kps[i, :len(f[0])] = f[0]; desc[i, :len(f[0])] = f[1]
-            if f[2] is not None:
+            if has_cl and f[2] is not None:
                 cl[i, :len(f[0])] = f[2]
+            if has_ur and f[3] is not None:
+                ur[i, :len(f[0])] = f[3]
         va = np.zeros((nf, ps), np.uint8); wp = np.zeros((nf, ps, 3), np.float32); nr = np.zeros((nf, ps, 3), np.float32)
         pd = np.zeros((nf, ps, 32), np.uint8); an = np.zeros((nf, ps), np.float32)
         mx = np.ones((nf, ps), np.float32); mn = np.ones((nf, ps), np.float32)
@@ -426,18 +430,46 @@ class Matcher:
             va[i, :k] = l["valid"]; wp[i, :k] = l["world_pos"]; nr[i, :k] = l["normal"]; pd[i, :k] = l["desc"]
             an[i, :k] = l["angle"]; mx[i, :k] = l["max_distance"]; mn[i, :k] = l["min_distance"]; pose[i] = l["pose"]
         sf = np.ascontiguousarray(scale_factors, np.float32)
-        F = FrameFeatures(nf, ks, _ptr(n_kp), _ptr(kps), _ptr(desc), None, _ptr(cl), bounds[0], bounds[1], bounds[2],
+        keep.extend([n_kp, n_pt, kps, desc, cl, ur, va, wp, nr, pd, an, mx, mn, pose, sf])
+        F = FrameFeatures(nf, ks, _ptr(n_kp), _ptr(kps), _ptr(desc), _ptr(ur), _ptr(cl), bounds[0], bounds[1], bounds[2],
                           bounds[3], len(sf), _ptr(sf))
         L = KeyFramePoints(ps, _ptr(n_pt), _ptr(va), _ptr(wp), _ptr(nr), _ptr(pd), _ptr(an), _ptr(mx), _ptr(mn), _ptr(pose),
                            float(pts[0]["log_scale_factor"]), int(pts[0]["n_scale_levels"]))
+        return F, L, n_kp, n_pt, ks, ps
+
+    def search_by_projection_keyframe(self, frames, pts, bounds, scale_factors, th, variant, orb_dist=100, check_orientation=False,
+                                      inv_sigma2=None):
+        """variant 0: relocalisation SearchByProjection, 1: Sim3 SearchByProjection, 2: Fuse, 3: Fuse with Sim3.
+        frames: list of (kps, desc, claimed|None[, u_right|None]); pts: list of dicts with valid, world_pos, normal, desc,
+        angle, max_distance, min_distance, pose (30,), log_scale_factor, n_scale_levels (tests/synth.keyframe_points_case).
+        Returns per pair (n, kp_to_pt, pt_best_idx) (kp_to_pt is None for Fuse)."""
+        keep = []
+        variant = int(variant)
+        F, L, n_kp, n_pt, ks, ps = self._keyframe_views(frames, pts, bounds, scale_factors, keep)
+        nf = len(frames)
         kp_to_pt = np.zeros((nf, ks), np.int32); best = np.zeros((nf, ps), np.int32); nm = np.zeros(nf, np.int32)
-        if sim3:
+        if variant == 1:
             check(lib().ygzorb_search_by_projection_sim3(self.h, C.byref(F), C.byref(L), int(th), 0, _ptr(kp_to_pt), _ptr(best),
                                                          _ptr(nm)))
-        else:
+        elif variant == 0:
             check(lib().ygzorb_search_by_projection_reloc(self.h, C.byref(F), C.byref(L), th, int(orb_dist),
                                                           int(check_orientation), 0, _ptr(kp_to_pt), _ptr(best), _ptr(nm)))
+        else:
+            is2 = np.ascontiguousarray(inv_sigma2, np.float32) if inv_sigma2 is not None else None
+            check(lib().ygzorb_fuse(self.h, C.byref(F), C.byref(L), th, int(variant == 3), _ptr(is2), 0, _ptr(best), _ptr(nm)))
+            return [(int(nm[i]), None, best[i, :n_pt[i]].copy()) for i in range(nf)]
         return [(int(nm[i]), kp_to_pt[i, :n_kp[i]].copy(), best[i, :n_pt[i]].copy()) for i in range(nf)]
+
+    def search_by_sim3(self, kfs1, kfs2, pts1, pts2, bounds1, bounds2, scale_factors, th):
+        """kfs1 / kfs2: lists of (kps, desc); pts1[i] = MapPoints of kfs1[i] (one per keypoint) with the pose that takes them
+        into kfs2[i], pts2 the other way round.  Returns per pair (n_found, matches12)."""
+        keep = []
+        F2, L1, _, n_pt1, _, ps1 = self._keyframe_views(kfs2, pts1, bounds2, scale_factors, keep)
+        F1, L2, _, _, _, _ = self._keyframe_views(kfs1, pts2, bounds1, scale_factors, keep)
+        nf = len(kfs1)
+        m12 = np.zeros((nf, ps1), np.int32); nfound = np.zeros(nf, np.int32)
+        check(lib().ygzorb_search_by_sim3(self.h, C.byref(F1), C.byref(F2), C.byref(L1), C.byref(L2), th, 0, _ptr(m12), _ptr(nfound)))
+        return [(int(nfound[i]), m12[i, :n_pt1[i]].copy()) for i in range(nf)]
 
     def search_by_projection_raw(self, F, P, th, check_level, nnratio, flags, kp_to_mp_ptr, best_ptr, nm_ptr):
         check(lib().ygzorb_search_by_projection(self.h, C.byref(F), C.byref(P), th, int(check_level), nnratio, flags,

@@ -246,9 +246,11 @@ def search_by_projection_last(kps, desc, u_right, claimed, bounds, scale_factors
     return nm, kp_to_pt[:n].copy(), best[:m].copy()
 
 
-def search_by_projection_keyframe(kps, desc, claimed, bounds, scale_factors, pts, th, sim3, orb_dist=100,
-                                  check_orientation=False):
-    """pts: dict as tests/synth.keyframe_points_case makes it.  Returns (n_matches, kp_to_pt, pt_best_idx)."""
+def search_by_projection_keyframe(kps, desc, claimed, bounds, scale_factors, pts, th, variant, orb_dist=100,
+                                  check_orientation=False, u_right=None, inv_sigma2=None):
+    """variant: 0 relocalisation, 1 Sim3 SearchByProjection, 2 Fuse, 3 Fuse with Sim3, 4 one direction of SearchBySim3
+    (False / True select 0 / 1).  pts: dict as tests/synth.keyframe_points_case makes it.
+    Returns (n_matches, kp_to_pt, pt_best_idx)."""
     n, m = len(kps), len(pts["valid"])
     kps = np.ascontiguousarray(kps)
     desc = np.ascontiguousarray(desc, np.uint8)
@@ -257,16 +259,25 @@ def search_by_projection_keyframe(kps, desc, claimed, bounds, scale_factors, pts
     u8 = lambda a: np.ascontiguousarray(a, np.uint8)
     sf = f32(scale_factors)
     cl = u8(claimed) if claimed is not None else None
+    ur = f32(u_right) if u_right is not None else None
+    is2 = f32(inv_sigma2) if inv_sigma2 is not None else None
     va, wp, nr, pd, an = u8(pts["valid"]), f32(pts["world_pos"]), f32(pts["normal"]), u8(pts["desc"]), f32(pts["angle"])
     mx, mn, pose = f32(pts["max_distance"]), f32(pts["min_distance"]), f32(pts["pose"])
     kp_to_pt = np.zeros(max(n, 1), np.int32)
     best = np.zeros(max(m, 1), np.int32)
     nm = lib().ygzo_search_by_projection_keyframe(
-        _p(kps), _p(desc), _p(cl), n, C.c_float(bounds[0]), C.c_float(bounds[1]), C.c_float(bounds[2]), C.c_float(bounds[3]),
-        C.c_float(inv_w), C.c_float(inv_h), _p(sf), _p(pose), _p(va), _p(wp), _p(nr), _p(pd), _p(an), _p(mx), _p(mn), m,
-        C.c_float(pts["log_scale_factor"]), int(pts["n_scale_levels"]), C.c_float(th), int(orb_dist), int(check_orientation),
-        int(sim3), _p(kp_to_pt), _p(best))
+        _p(kps), _p(desc), _p(cl), _p(ur), n, C.c_float(bounds[0]), C.c_float(bounds[1]), C.c_float(bounds[2]),
+        C.c_float(bounds[3]), C.c_float(inv_w), C.c_float(inv_h), _p(sf), _p(is2), _p(pose), _p(va), _p(wp), _p(nr), _p(pd),
+        _p(an), _p(mx), _p(mn), m, C.c_float(pts["log_scale_factor"]), int(pts["n_scale_levels"]), C.c_float(th),
+        int(orb_dist), int(check_orientation), int(variant), _p(kp_to_pt), _p(best))
     return nm, kp_to_pt[:n].copy(), best[:m].copy()
+
+
+def sim3_agreement(match1, match2):
+    m1, m2 = np.ascontiguousarray(match1, np.int32), np.ascontiguousarray(match2, np.int32)
+    out = np.zeros(max(len(m1), 1), np.int32)
+    n = lib().ygzo_sim3_agreement(_p(m1), len(m1), _p(m2), len(m2), _p(out))
+    return n, out[:len(m1)].copy()
 
 
 def search_by_bow(kf1, second, second_is_frame, nnratio, check_orientation):

@@ -151,10 +151,11 @@ def lastframe_case(kps, desc, n_pts, seed, motion=(0.02, -0.01, 0.3), jitter=2.0
     return last, u_right, claimed
 
 
-def keyframe_points_case(kps, desc, n_pts, seed, sim3, jitter=2.0, fx=458.654, fy=457.296, cx=367.215, cy=248.375,
+def keyframe_points_case(kps, desc, n_pts, seed, variant, jitter=2.0, fx=458.654, fy=457.296, cx=367.215, cy=248.375,
                          scale=1.2, nlevels=8, p_invalid=0.1, rot_outliers=0.15):
-    """MapPoints of a KeyFrame for the relocalisation / Sim3 projection searches: world points that project next to
-    keypoints of the searched frame (kps/desc), with mfMaxDistance chosen so that PredictScale lands near the source
+    """MapPoints for the projection searches with a predicted level (variant: 0 relocalisation, 1 Sim3 SearchByProjection,
+    2 Fuse, 3 Fuse with Sim3, 4 one direction of SearchBySim3): world points that project next to keypoints of the
+    searched frame (kps/desc), with mfMaxDistance chosen so that PredictScale lands near the source
     keypoint's octave; a few points violate the distance range, the viewing angle (Sim3) or sit behind the camera."""
     rng = np.random.default_rng(seed)
     n = len(kps)
@@ -183,16 +184,37 @@ def keyframe_points_case(kps, desc, n_pts, seed, sim3, jitter=2.0, fx=458.654, f
     ang = kps["angle"][src] + rng.normal(0, 3.0, n_pts)
     out = rng.uniform(size=n_pts) < rot_outliers
     ang = np.mod(np.where(out, ang + rng.uniform(40, 320, n_pts), ang), 360.0)
+    variant = int(variant)
     pose = np.zeros(30, np.float32)
     pose[:9] = Rcw.reshape(9); pose[9:12] = tcw; pose[24:28] = [fx, fy, cx, cy]
-    if sim3:
+    bf = 47.9
+    if variant in (1, 2, 3):
         pose[12:15] = Ow
+        pose[28] = bf
+    u_right = np.where(rng.uniform(size=n) < 0.5, kps["x"] - bf / rng.uniform(1.0, 12.0, n), -1.0).astype(np.float32)
+    if variant == 2:   # stereo keypoints consistent with their source points, so that the chi-square gate passes some
+        zs = np.full(n, np.nan); zs[src] = z
+        u_right = np.where(np.isfinite(zs) & (rng.uniform(size=n) < 0.7), kps["x"] - bf / np.abs(zs) + rng.normal(0, 0.7, n),
+                           u_right).astype(np.float32)
+    if variant == 4:
+        # world -> camera 1 (R1w, t1w) -> camera 2 (sR21, t21), composed to the Rcw, tcw used above; distances are measured
+        # in camera 2, so that is where max_d has to refer to
+        a = rng.uniform(-0.3, 0.3, 3)
+        R1w = np.array([[1, -a[2], a[1]], [a[2], 1, -a[0]], [-a[1], a[0], 1]], np.float64)
+        t1w = rng.uniform(-1, 1, 3)
+        sR21 = Rcw @ np.linalg.inv(R1w)
+        t21 = tcw - sR21 @ t1w
+        pose[:9] = R1w.reshape(9); pose[9:12] = t1w; pose[12:21] = sR21.reshape(9); pose[21:24] = t21
+        dist2 = np.linalg.norm(pc, axis=1)
+        max_d = np.where(bad_range, dist2 * 0.5, dist2 * scale ** (lvl - rng.uniform(0.05, 0.95, n_pts)))
+        min_d = max_d / scale ** (nlevels - 1)
     pts = {
         "valid": (rng.uniform(size=n_pts) >= p_invalid).astype(np.uint8),
         "world_pos": pw.astype(np.float32), "normal": normal.astype(np.float32),
         "desc": flip_bits(desc[src], rng.integers(0, 45, size=n_pts), rng),
         "angle": ang.astype(np.float32), "max_distance": max_d.astype(np.float32), "min_distance": min_d.astype(np.float32),
         "pose": pose, "log_scale_factor": float(np.float32(np.log(np.float32(scale)))), "n_scale_levels": nlevels, "src": src,
+        "u_right": u_right,
     }
     claimed = (rng.uniform(size=n) < 0.05).astype(np.uint8)
     return pts, claimed

@@ -92,24 +92,57 @@ def test_search_by_projection_last_vs_oracle(matcher, feats, th, mono, check_lev
         assert np.array_equal(g[1], e[1]) and np.array_equal(g[2], e[2])
 
 
-@pytest.mark.parametrize("th,sim3,orb_dist,check_ori,seed", [
-    (10.0, False, 100, True, 1), (3.0, False, 64, True, 2), (15.0, False, 100, False, 3), (10.0, True, 50, False, 4),
-    (4.0, True, 50, False, 5), (40.0, True, 50, False, 6)])
-def test_search_by_projection_keyframe_vs_oracle(matcher, feats, th, sim3, orb_dist, check_ori, seed):
-    """The relocalisation (src/ORBmatcher.cc:1352-1469) and Sim3 (:265-373) projection searches: in-kernel projection,
-    distance range, viewing angle, PredictScale, level window, claim order, rotation rejection."""
+@pytest.mark.parametrize("th,variant,orb_dist,check_ori,seed", [
+    (10.0, 0, 100, True, 1), (3.0, 0, 64, True, 2), (15.0, 0, 100, False, 3), (10.0, 1, 50, False, 4),
+    (4.0, 1, 50, False, 5), (40.0, 1, 50, False, 6), (3.0, 2, 50, False, 7), (2.5, 2, 50, False, 8), (4.0, 3, 50, False, 9),
+    (20.0, 3, 50, False, 10)])
+def test_search_by_projection_keyframe_vs_oracle(matcher, feats, th, variant, orb_dist, check_ori, seed):
+    """The relocalisation (src/ORBmatcher.cc:1352-1469) and Sim3 (:265-373) projection searches and the search halves of
+    Fuse (:748-886) / Fuse with Sim3 (:888-1004): in-kernel projection, distance range, viewing angle, PredictScale,
+    level window, chi-square gate, claim order, rotation rejection."""
     img, kps, desc = feats
-    sf, _, _ = synth.scale_tables()
+    sf, _, sigma2 = synth.scale_tables()
+    inv_sigma2 = (np.float32(1.0) / sigma2).astype(np.float32)
     bounds = (0.0, 0.0, float(img.shape[1]), float(img.shape[0]))
     frames, pts, exp = [], [], []
     for k in range(3):
-        p, claimed = synth.keyframe_points_case(kps, desc, 1200 - 200 * k, seed * 10 + k, sim3)
-        frames.append((kps, desc, claimed)); pts.append(p)
-        exp.append(O.search_by_projection_keyframe(kps, desc, claimed, bounds, sf, p, th, sim3, orb_dist, check_ori))
-    got = matcher.search_by_projection_keyframe(frames, pts, bounds, sf, th, sim3, orb_dist, check_ori)
+        p, claimed = synth.keyframe_points_case(kps, desc, 1200 - 200 * k, seed * 10 + k, variant)
+        ur = p["u_right"] if variant == 2 else None
+        frames.append((kps, desc, claimed, ur)); pts.append(p)
+        exp.append(O.search_by_projection_keyframe(kps, desc, claimed, bounds, sf, p, th, variant, orb_dist, check_ori, ur, inv_sigma2))
+    got = matcher.search_by_projection_keyframe(frames, pts, bounds, sf, th, variant, orb_dist, check_ori, inv_sigma2)
     for g, e in zip(got, exp):
         assert g[0] == e[0] and e[0] > 100
-        assert np.array_equal(g[1], e[1]) and np.array_equal(g[2], e[2])
+        assert (g[1] is None or np.array_equal(g[1], e[1])) and np.array_equal(g[2], e[2])
+
+
+@pytest.mark.parametrize("th,seed", [(7.5, 1), (3.0, 2)])
+def test_search_by_sim3_vs_oracle(matcher, feats, th, seed):
+    """SearchBySim3 (src/ORBmatcher.cc:1006-1216): both directions + the agreement check.  The two keyframes share the
+    keypoints here (MapPoint i of either side sits near keypoint src[i] of the other), which makes mutual matches common."""
+    img, kps, desc = feats
+    sf, _, _ = synth.scale_tables()
+    bounds = (0.0, 0.0, float(img.shape[1]), float(img.shape[0]))
+    n = len(kps)
+    kfs1, kfs2, P1, P2, exp = [], [], [], [], []
+    for k in range(2):
+        p1, _ = synth.keyframe_points_case(kps, desc, n, seed * 10 + k, 4, jitter=1.0)
+        p2, _ = synth.keyframe_points_case(kps, desc, n, seed * 10 + k + 5, 4, jitter=1.0)
+        # point i of KF1 should land on keypoint i of KF2 and vice versa for agreement: re-aim both at the identity pairing
+        for p in (p1, p2):
+            order = np.argsort(p["src"], kind="stable")
+            first = np.full(n, -1); first[p["src"][order][::-1]] = order[::-1]
+            sel = np.where(first >= 0, first, 0)
+            for key in ("world_pos", "normal", "desc", "angle", "max_distance", "min_distance"):
+                p[key] = p[key][sel]
+            p["valid"] = (p["valid"][sel] & (first >= 0)).astype(np.uint8)
+        m1 = O.search_by_projection_keyframe(kps, desc, None, bounds, sf, p1, th, 4, 100)[2]
+        m2 = O.search_by_projection_keyframe(kps, desc, None, bounds, sf, p2, th, 4, 100)[2]
+        exp.append(O.sim3_agreement(m1, m2))
+        kfs1.append((kps, desc)); kfs2.append((kps, desc)); P1.append(p1); P2.append(p2)
+    got = matcher.search_by_sim3(kfs1, kfs2, P1, P2, bounds, bounds, sf, th)
+    for g, e in zip(got, exp):
+        assert g[0] == e[0] and e[0] > 50 and np.array_equal(g[1], e[1])
 
 
 def test_search_by_projection_claim_chain(matcher, feats):

@@ -232,11 +232,15 @@ def test_search_by_projection_last_vs_python(th, mono, check_level, check_ori, s
         assert (a[2] >= 0).sum() > a[0]
 
 
-def _py_search_by_projection_keyframe(kps, desc, claimed, bounds, sf, pts, th, sim3, orb_dist, check_ori):
-    """src/ORBmatcher.cc:1352-1469 (sim3=False, Eigen order) and :265-373 (sim3=True) re-derived; the Sim3 variant calls the
-    installed OpenCV (cv2.gemm, cv2.norm) for the cv::Mat expressions, which pins the oracle's restatement of them."""
+def _py_search_by_projection_keyframe(kps, desc, claimed, bounds, sf, pts, th, variant, orb_dist, check_ori, u_right=None,
+                                      inv_sigma2=None):
+    """src/ORBmatcher.cc:1352-1469 (variant 0, Eigen order), :265-373 (1), Fuse :748-886 (2, Eigen), Fuse with Sim3 :888-1004
+    (3) and one direction of SearchBySim3 :1043-1110 (4) re-derived; the cv::Mat variants call the installed OpenCV
+    (cv2.gemm, cv2.norm) for those expressions, which pins the oracle's restatement of them."""
     import cv2
     f = np.float32
+    variant = int(variant)
+    eigen, claims = variant in (0, 2), variant <= 1
     min_x, min_y, max_x, max_y = [f(b) for b in bounds]
     inv_w, inv_h = f(64) / (max_x - min_x), f(48) / (max_y - min_y)
     rnd = lambda v: int(math.floor(abs(v) + 0.5)) * (1 if v >= 0 else -1)
@@ -249,9 +253,9 @@ def _py_search_by_projection_keyframe(kps, desc, claimed, bounds, sf, pts, th, s
     Rcw, tcw = P[0:9].reshape(3, 3), P[9:12]
     fx, fy, cx, cy = P[24:28]
     dot3 = lambda a0, a1, a2: f(a0 + f(a1 + a2))
-    Ow = P[12:15] if sim3 else np.array([f(-dot3(f(Rcw[0, r] * tcw[0]), f(Rcw[1, r] * tcw[1]), f(Rcw[2, r] * tcw[2]))) for r in range(3)], f)
+    Ow = P[12:15] if variant != 0 else np.array([f(-dot3(f(Rcw[0, r] * tcw[0]), f(Rcw[1, r] * tcw[1]), f(Rcw[2, r] * tcw[2]))) for r in range(3)], f)
     D = _hamming_matrix(pts["desc"], desc)
-    blocked = claimed.astype(bool).copy() if claimed is not None else np.zeros(len(kps), bool)
+    blocked = claimed.astype(bool).copy() if (claimed is not None and claims) else np.zeros(len(kps), bool)
     kp_to_pt = np.full(len(kps), -1, np.int32)
     best_of = np.full(len(pts["valid"]), -1, np.int32)
     hist = [[] for _ in range(30)]
@@ -262,36 +266,46 @@ def _py_search_by_projection_keyframe(kps, desc, claimed, bounds, sf, pts, th, s
             continue
         X = pts["world_pos"][i].astype(np.float32)
         with np.errstate(divide="ignore", invalid="ignore"):
-            if sim3:
-                c = cv2.gemm(Rcw, X.reshape(3, 1), 1.0, tcw.reshape(3, 1), 1.0)[:, 0]
-                if c[2] < 0.0:
-                    continue
-                invz = f(1) / c[2]
-                u, v = f(f(fx * f(c[0] * invz)) + cx), f(f(fy * f(c[1] * invz)) + cy)
-                if not (u >= min_x and u < max_x and v >= min_y and v < max_y):
-                    continue
-                PO = X - Ow
-                dist = f(cv2.norm(PO.reshape(3, 1)))
-            else:
+            if eigen:
                 c = [f(dot3(f(Rcw[r, 0] * X[0]), f(Rcw[r, 1] * X[1]), f(Rcw[r, 2] * X[2])) + tcw[r]) for r in range(3)]
+            else:
+                c = cv2.gemm(Rcw, X.reshape(3, 1), 1.0, tcw.reshape(3, 1), 1.0)[:, 0]
+            if variant == 4:
+                c = cv2.gemm(P[12:21].reshape(3, 3), c.reshape(3, 1), 1.0, P[21:24].reshape(3, 1), 1.0)[:, 0]
+            if variant == 0:
                 invz = f(np.float64(1.0) / np.float64(c[2]))
                 u, v = f(f(f(fx * c[0]) * invz) + cx), f(f(f(fy * c[1]) * invz) + cy)
                 if not (np.isfinite(u) and np.isfinite(v)) or u < min_x or u > max_x or v < min_y or v > max_y:
                     continue
-                PO = X - Ow
+            else:
+                if c[2] < 0.0:
+                    continue
+                invz = f(1) / f(c[2]) if variant in (1, 2) else f(np.float64(1.0) / np.float64(c[2]))
+                u, v = f(f(fx * f(c[0] * invz)) + cx), f(f(fy * f(c[1] * invz)) + cy)
+                if not (u >= min_x and u < max_x and v >= min_y and v < max_y):
+                    continue
+            ur = f(u - f(P[28] * invz))
+            PO = np.array(c, f) if variant == 4 else X - Ow
+            if eigen:
                 dist = f(np.sqrt(dot3(f(PO[0] * PO[0]), f(PO[1] * PO[1]), f(PO[2] * PO[2]))))
+            else:
+                dist = f(cv2.norm(PO.reshape(3, 1)))
         if dist < f(f(0.8) * pts["min_distance"][i]) or dist > f(f(1.2) * pts["max_distance"][i]):
             continue
-        if sim3:
-            d = np.float64(0)
-            for r in range(3):
-                d = d + np.float64(PO[r]) * np.float64(pts["normal"][i][r])
+        if variant in (1, 2, 3):
+            Pn = pts["normal"][i]
+            if variant == 2:
+                d = np.float64(dot3(f(PO[0] * Pn[0]), f(PO[1] * Pn[1]), f(PO[2] * Pn[2])))
+            else:
+                d = np.float64(0)
+                for r in range(3):
+                    d = d + np.float64(PO[r]) * np.float64(Pn[r])
             if d < 0.5 * np.float64(dist):
                 continue
         lvl = int(math.ceil(float(f(f(np.log(f(pts["max_distance"][i] / dist))) / log_sf))))
         lvl = min(max(lvl, 0), nlev - 1)
         rad = f(f(th) * sf[lvl])
-        lo, hi = lvl - 1, (lvl if sim3 else lvl + 1)
+        lo, hi = lvl - 1, (lvl + 1 if variant == 0 else lvl)
         cx0 = max(0, math.floor(float(f(f(u - min_x - rad) * inv_w)))); cx1 = min(63, math.ceil(float(f(f(u - min_x + rad) * inv_w))))
         cy0 = max(0, math.floor(float(f(f(v - min_y - rad) * inv_h)))); cy1 = min(47, math.ceil(float(f(f(v - min_y + rad) * inv_h))))
         if cx0 >= 64 or cx1 < 0 or cy0 >= 48 or cy1 < 0:
@@ -307,10 +321,19 @@ def _py_search_by_projection_keyframe(kps, desc, claimed, bounds, sf, pts, th, s
                         continue
                     if blocked[idx]:
                         continue
+                    if variant == 2:
+                        ex, ey = f(u - kps["x"][idx]), f(v - kps["y"][idx])
+                        e2 = f(f(ex * ex) + f(ey * ey))
+                        if u_right is not None and u_right[idx] >= 0:
+                            er = f(ur - u_right[idx])
+                            if np.float64(f(f(e2 + f(er * er)) * inv_sigma2[ko])) > 7.8:
+                                continue
+                        elif np.float64(f(e2 * inv_sigma2[ko])) > 5.99:
+                            continue
                     if int(D[i, idx]) < b1:
                         b1, bi = int(D[i, idx]), idx
         if b1 <= orb_dist:
-            kp_to_pt[bi] = i; blocked[bi] = True; best_of[i] = bi; n += 1
+            kp_to_pt[bi] = i; blocked[bi] = claims; best_of[i] = bi; n += 1
             if check_ori:
                 rot = f(pts["angle"][i] - kps["angle"][bi])
                 if rot < 0:
@@ -338,15 +361,19 @@ def _py_search_by_projection_keyframe(kps, desc, claimed, bounds, sf, pts, th, s
     return n, kp_to_pt, best_of
 
 
-@pytest.mark.parametrize("th,sim3,orb_dist,check_ori,seed", [
-    (10.0, False, 100, True, 1), (3.0, False, 64, True, 2), (10.0, True, 50, False, 3), (4.0, True, 50, False, 4)])
-def test_search_by_projection_keyframe_vs_python(th, sim3, orb_dist, check_ori, seed):
+@pytest.mark.parametrize("th,variant,orb_dist,check_ori,seed", [
+    (10.0, 0, 100, True, 1), (3.0, 0, 64, True, 2), (10.0, 1, 50, False, 3), (4.0, 1, 50, False, 4), (3.0, 2, 50, False, 5),
+    (4.0, 3, 50, False, 6), (7.5, 4, 100, False, 7)])
+def test_search_by_projection_keyframe_vs_python(th, variant, orb_dist, check_ori, seed):
     img, (kps, desc) = _features(seed=seed)
-    sf, _, _ = synth.scale_tables()
-    pts, claimed = synth.keyframe_points_case(kps, desc, 500, seed, sim3, cx=160.0, cy=120.0)
+    sf, _, sigma2 = synth.scale_tables()
+    inv_sigma2 = (np.float32(1.0) / sigma2).astype(np.float32)
+    pts, claimed = synth.keyframe_points_case(kps, desc, 500, seed, variant, cx=160.0, cy=120.0)
+    u_right = pts["u_right"] if variant == 2 else None
     bounds = (0.0, 0.0, float(img.shape[1]), float(img.shape[0]))
-    a = O.search_by_projection_keyframe(kps, desc, claimed, bounds, sf, pts, th, sim3, orb_dist, check_ori)
-    b = _py_search_by_projection_keyframe(kps, desc, claimed, bounds, sf, pts, th, sim3, orb_dist, check_ori)
+    a = O.search_by_projection_keyframe(kps, desc, claimed, bounds, sf, pts, th, variant, orb_dist, check_ori, u_right, inv_sigma2)
+    b = _py_search_by_projection_keyframe(kps, desc, claimed, bounds, sf, pts, th, variant, orb_dist, check_ori, u_right,
+                                          inv_sigma2)
     assert a[0] == b[0] and a[0] > 30
     assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
     if check_ori:
