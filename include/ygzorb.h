@@ -288,6 +288,15 @@ int ygzorb_search_by_sim3(ygzorb_matcher *m, const ygzorb_frame_features *kf1, c
                           const ygzorb_keyframe_points *pts1, const ygzorb_keyframe_points *pts2, float th, unsigned flags,
                           int32_t *matches12, int32_t *n_found);
 
+/* ORBmatcher::SearchForInitialization(Frame &F1, Frame &F2, vector<cv::Point2f> &vbPrevMatched, vector<int> &vnMatches12,
+ * int windowSize) (src/ORBmatcher.cc:375-478; Tracking::MonocularInitialization), batched over frame pairs with the serial
+ * take-over order (:412, :426-433) reproduced.  f1 / f2: keypoints and descriptors (claimed, u_right unused; the grid
+ * bounds of f2 are used).  prev_matched: vbPrevMatched as (x, y) floats, [n_frames * f1->kp_stride * 2], read and updated
+ * in place (:472-475; device memory when YGZORB_IN_DEVICE, else host).  matches12[f*kp_stride1 + i1] = vnMatches12. */
+int ygzorb_search_for_initialization(ygzorb_matcher *m, const ygzorb_frame_features *f1, const ygzorb_frame_features *f2,
+                                     float *prev_matched, int window_size, float nnratio, int check_orientation,
+                                     unsigned flags, int32_t *matches12, int32_t *n_matches);
+
 /* KeyFrame arrays read by SearchForTriangulation (include/KeyFrame.h:236-271); the DBoW2::FeatureVector
  * (Thirdparty/DBoW2/DBoW2/FeatureVector.h:23-24, std::map<NodeId, vector<unsigned>>) flattened to CSR:
  * node_ids ascending, features of node k = node_feats[node_start[k] .. node_start[k+1]). */

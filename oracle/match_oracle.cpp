@@ -409,6 +409,57 @@ YGZO_API int ygzo_sim3_agreement(const int32_t *vnMatch1, int n1, const int32_t 
     return nFound;
 }
 
+// ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) — src/ORBmatcher.cc:375-478.
+// prevMatched = vbPrevMatched as (x, y) pairs, updated in place (:472-475).  Returns nmatches.
+YGZO_API int ygzo_search_for_initialization(const void *kps1V, const uint8_t *desc1, int n1, const void *kps2V, const uint8_t *desc2,
+                                            int n2, float minX, float minY, float invW, float invH, float *prevMatched,
+                                            int windowSize, float nnratio, int checkOrientation, int32_t *vnMatches12) {
+    const KeyPoint *kps1 = (const KeyPoint *)kps1V, *kps2 = (const KeyPoint *)kps2V;
+    Grid g;
+    assignGrid(g, kps2, n2, minX, minY, invW, invH);
+    int nmatches = 0;
+    for (int i = 0; i < n1; i++) vnMatches12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    std::vector<int> vMatchedDistance(std::max(n2, 1), INT_MAX), vnMatches21(std::max(n2, 1), -1);
+    std::vector<int> vIndices2;
+    for (int i1 = 0; i1 < n1; i1++) {
+        const int level1 = kps1[i1].octave;
+        if (level1 > 0) continue;
+        featuresInArea(g, kps2, prevMatched[2 * i1], prevMatched[2 * i1 + 1], (float)windowSize, level1, level1, vIndices2);
+        if (vIndices2.empty()) continue;
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (int i2 : vIndices2) {
+            const int dist = descriptorDistance(desc1 + (size_t)i1 * 32, desc2 + (size_t)i2 * 32);
+            if (vMatchedDistance[i2] <= dist) continue;
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist <= TH_LOW) {
+            if (bestDist < (float)bestDist2 * nnratio) {
+                if (vnMatches21[bestIdx2] >= 0) { vnMatches12[vnMatches21[bestIdx2]] = -1; nmatches--; }
+                vnMatches12[i1] = bestIdx2;
+                vnMatches21[bestIdx2] = i1;
+                vMatchedDistance[bestIdx2] = bestDist;
+                nmatches++;
+                if (checkOrientation) rotHist[rotationBin(kps1[i1].angle, kps2[bestIdx2].angle)].push_back(i1);
+            }
+        }
+    }
+    if (checkOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1, sizes[HISTO_LENGTH];
+        for (int i = 0; i < HISTO_LENGTH; i++) sizes[i] = (int)rotHist[i].size();
+        threeMaxima(sizes, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx1 : rotHist[i])
+                if (vnMatches12[idx1] >= 0) { vnMatches12[idx1] = -1; nmatches--; }
+        }
+    }
+    for (int i1 = 0; i1 < n1; i1++)
+        if (vnMatches12[i1] >= 0) { prevMatched[2 * i1] = kps2[vnMatches12[i1]].x; prevMatched[2 * i1 + 1] = kps2[vnMatches12[i1]].y; }
+    return nmatches;
+}
+
 // ORBmatcher::SearchByBoW — both overloads over flattened FeatureVectors (CSR, ascending NodeId):
 //   secondIsFrame = 1: SearchByBoW(KeyFrame *pKF, Frame &F, vector<MapPoint*> &vpMapPointMatches), src/ORBmatcher.cc:155-263.
 //     hasMP1 = the keyframe's MapPoint exists and !isBad(); frame features already matched in this call are skipped;

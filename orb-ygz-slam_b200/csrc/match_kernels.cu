@@ -659,6 +659,160 @@ int launchSearchByProjectionLast(const ProjArgs &A, cudaStream_t s) {
 
 
 // =================================================================================================
+// K8b — ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:375-478).  One CTA per frame pair.
+//
+// The serial loop lets keypoint i1 of F1 skip a candidate i2 whose current match is at least as close
+// (vMatchedDistance[i2] <= dist, :412) and lets a later i1 take i2 away from an earlier one (:426-429).  As in K8 the
+// kernel evaluates every i1 in parallel against the accepted matches of the previous round restricted to i1' < i1 —
+// vMatchedDistance[i2] at the time of i1 is the smallest accepted distance among them, because every new match of i2 is
+// strictly closer than the one before — and iterates to the fixed point, which is the serial result.  Accepted matches of
+// a round are chained per i2 (head / next), so the query walks a list of typically one or two entries.
+__device__ __forceinline__ bool posInGridXY(float minX, float minY, float invW, float invH, float x, float y, int *cell) {
+    const int px = (int)roundf(__fmul_rn(__fsub_rn(x, minX), invW));
+    const int py = (int)roundf(__fmul_rn(__fsub_rn(y, minY), invH));
+    if (px < 0 || px >= kGridCols || py < 0 || py >= kGridRows) return false;
+    *cell = px * kGridRows + py;
+    return true;
+}
+
+__global__ void __launch_bounds__(kProjThreads) k_search_for_initialization(const __grid_constant__ InitArgs A) {
+    __shared__ int cellStart[kGridCols * kGridRows + 1];
+    __shared__ int cellFill[kGridCols * kGridRows];
+    __shared__ int ws[40], hist[kHistoLength], keep[3];
+    const int f = blockIdx.x, tid = threadIdx.x;
+    const int n1 = min(A.n1[f], A.stride1), n2 = min(A.n2[f], A.stride2);
+    const ygzorb_keypoint *kps1 = A.kps1 + (size_t)f * A.stride1, *kps2 = A.kps2 + (size_t)f * A.stride2;
+    const uint4 *desc1 = reinterpret_cast<const uint4 *>(A.desc1 + (size_t)f * A.stride1 * 32);
+    const uint4 *desc2 = reinterpret_cast<const uint4 *>(A.desc2 + (size_t)f * A.stride2 * 32);
+    float *prev = A.prevMatched + (size_t)f * A.stride1 * 2;
+    int32_t *gridList = A.gridList + (size_t)f * A.stride2;
+    int32_t *st = A.state + (size_t)f * (5 * (size_t)A.stride1 + 2 * (size_t)A.stride2);
+    int32_t *best[2] = {st, st + A.stride1}, *bdist[2] = {st + 2 * A.stride1, st + 3 * A.stride1};
+    int32_t *next = st + 4 * A.stride1, *head = st + 5 * A.stride1, *owner = head + A.stride2;
+    int32_t *m12 = A.matches12 + (size_t)f * A.stride1;
+    constexpr int kCells = kGridCols * kGridRows;
+    // ---- F2.AssignFeaturesToGrid (as in K8)
+    for (int c = tid; c < kCells; c += kProjThreads) { cellStart[c] = 0; cellFill[c] = 0; }
+    if (tid < kHistoLength) hist[tid] = 0;
+    __syncthreads();
+    for (int i = tid; i < n2; i += kProjThreads) {
+        int cell;
+        if (posInGridXY(A.minX, A.minY, A.invW, A.invH, kps2[i].x, kps2[i].y, &cell)) atomicAdd(&cellStart[cell], 1);
+    }
+    __syncthreads();
+    const int total = projScan(cellStart, kCells, ws);
+    if (tid == 0) cellStart[kCells] = total;
+    __syncthreads();
+    for (int i = tid; i < n2; i += kProjThreads) {
+        int cell;
+        if (posInGridXY(A.minX, A.minY, A.invW, A.invH, kps2[i].x, kps2[i].y, &cell)) gridList[cellStart[cell] + atomicAdd(&cellFill[cell], 1)] = i;
+    }
+    __syncthreads();
+    for (int c = tid; c < kCells; c += kProjThreads) {
+        const int b = cellStart[c], e = cellStart[c + 1];
+        for (int i = b + 1; i < e; i++) {
+            const int v = gridList[i];
+            int k = i - 1;
+            while (k >= b && gridList[k] > v) { gridList[k + 1] = gridList[k]; k--; }
+            gridList[k + 1] = v;
+        }
+    }
+    for (int i = tid; i < n1; i += kProjThreads) { best[0][i] = -1; bdist[0][i] = INT_MAX; }
+    __syncthreads();
+    // ---- fixed-point iteration; buffer `cur` holds the previous round's matches
+    int cur = 0;
+    for (int round = 0; round <= n1 + 1; round++) {
+        for (int i = tid; i < n2; i += kProjThreads) head[i] = -1;
+        __syncthreads();
+        for (int i = tid; i < n1; i += kProjThreads) {
+            const int b = best[cur][i];
+            if (b >= 0) next[i] = atomicExch(&head[b], i);
+        }
+        __syncthreads();
+        int changed = 0;
+        for (int i1 = tid; i1 < n1; i1 += kProjThreads) {
+            int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+            if (kps1[i1].octave <= 0) {
+                const float x = prev[2 * i1], y = prev[2 * i1 + 1], r = A.window;
+                const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, A.minX), r), A.invW)));
+                const int cx1 = min(kGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, A.minX), r), A.invW)));
+                const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, A.minY), r), A.invH)));
+                const int cy1 = min(kGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, A.minY), r), A.invH)));
+                if (cx0 < kGridCols && cx1 >= 0 && cy0 < kGridRows && cy1 >= 0) {
+                    const uint4 q0 = desc1[2 * i1], q1 = desc1[2 * i1 + 1];
+                    for (int ix = cx0; ix <= cx1; ix++) {
+                        const int cb = ix * kGridRows;
+                        for (int k = cellStart[cb + cy0], ke = cellStart[cb + cy1 + 1]; k < ke; k++) {
+                            const int i2 = gridList[k];
+                            const ygzorb_keypoint &kp = kps2[i2];
+                            if (kp.octave != 0) continue;                     // GetFeaturesInArea(.., level1, level1) with level1 = 0
+                            if (!(fabsf(__fsub_rn(kp.x, x)) < r && fabsf(__fsub_rn(kp.y, y)) < r)) continue;
+                            const int dist = hamming256(q0, q1, desc2[2 * i2], desc2[2 * i2 + 1]);
+                            int matched = INT_MAX;                            // vMatchedDistance[i2] when the serial loop reaches i1
+                            for (int e = head[i2]; e >= 0; e = next[e])
+                                if (e < i1) matched = min(matched, bdist[cur][e]);
+                            if (matched <= dist) continue;
+                            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+                            else if (dist < bestDist2) bestDist2 = dist;
+                        }
+                    }
+                }
+            }
+            const bool ok = bestDist <= kThLow && (float)bestDist < __fmul_rn((float)bestDist2, A.nnratio);
+            const int nb = ok ? bestIdx2 : -1, nd = ok ? bestDist : INT_MAX;
+            if (nb != best[cur][i1] || nd != bdist[cur][i1]) changed = 1;
+            best[cur ^ 1][i1] = nb; bdist[cur ^ 1][i1] = nd;
+        }
+        cur ^= 1;
+        if (!__syncthreads_or(changed)) break;
+    }
+    // ---- vnMatches12: the last taker of i2 keeps it; every accepted match votes in the rotation histogram (:436-445)
+    for (int i = tid; i < n2; i += kProjThreads) owner[i] = -1;
+    if (tid == 0) ws[0] = 0;
+    __syncthreads();
+    for (int i = tid; i < n1; i += kProjThreads) {
+        const int b = best[cur][i];
+        if (b >= 0) {
+            atomicMax(&owner[b], i);
+            if (A.checkOrientation) atomicAdd(&hist[rotationBinDev(kps1[i].angle, kps2[b].angle)], 1);
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < kHistoLength; i++) {
+            const int sz = hist[i];
+            if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
+            else if (sz > max3) { max3 = sz; ind3 = i; }
+        }
+        if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+        else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
+        keep[0] = ind1; keep[1] = ind2; keep[2] = ind3;
+    }
+    __syncthreads();
+    int cnt = 0;
+    for (int i = tid; i < n1; i += kProjThreads) {
+        const int b = best[cur][i];
+        int mt = (b >= 0 && owner[b] == i) ? b : -1;
+        if (mt >= 0 && A.checkOrientation) {
+            const int bin = rotationBinDev(kps1[i].angle, kps2[b].angle);
+            if (bin != keep[0] && bin != keep[1] && bin != keep[2]) mt = -1;
+        }
+        m12[i] = mt;
+        if (mt >= 0) { cnt++; prev[2 * i] = kps2[mt].x; prev[2 * i + 1] = kps2[mt].y; }   // :472-475
+    }
+    if (cnt) atomicAdd(&ws[0], cnt);
+    __syncthreads();
+    if (tid == 0) A.nMatches[f] = ws[0];
+}
+
+int launchSearchForInitialization(const InitArgs &A, cudaStream_t s) {
+    if (A.nFrames <= 0) return 0;
+    k_search_for_initialization<<<A.nFrames, kProjThreads, 0, s>>>(A);
+    return 1;
+}
+
 // K9 — ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:597-746) + CheckDistEpipolarLine
 // (:136-153) + the rotation-histogram vote (:695-731, ComputeThreeMaxima :1471-1502).  One CTA:
 // the call is small (~1-2k keypoints) and latency-bound.  The merge-walk over the two FeatureVectors

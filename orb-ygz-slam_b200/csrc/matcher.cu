@@ -440,6 +440,48 @@ int ygzorb_search_by_sim3(ygzorb_matcher *h, const ygzorb_frame_features *KF1, c
     return finish(m, flags);
 }
 
+int ygzorb_search_for_initialization(ygzorb_matcher *h, const ygzorb_frame_features *F1, const ygzorb_frame_features *F2,
+                                     float *prevMatched, int windowSize, float nnratio, int checkOrientation, unsigned flags,
+                                     int32_t *matches12, int32_t *nMatches) {
+    Matcher *m = (Matcher *)h;
+    if (!m || !F1 || !F2 || !prevMatched || !matches12 || !nMatches) return argFailM("null argument");
+    if (F1->n_frames < 0 || F1->n_frames != F2->n_frames || F1->kp_stride < 1 || F2->kp_stride < 1) return argFailM("bad sizes");
+    if (!F1->n_kp || !F1->kps || !F1->desc || !F2->n_kp || !F2->kps || !F2->desc) return argFailM("null array in frame view");
+    if (F1->n_frames == 0) return 0;
+    YGZ_CUDA(cudaSetDevice(m->device));
+    const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
+    const size_t nf = F1->n_frames, nk1 = nf * F1->kp_stride, nk2 = nf * F2->kp_stride;
+    InitArgs A;
+    memset(&A, 0, sizeof A);
+    A.nFrames = F1->n_frames; A.stride1 = F1->kp_stride; A.stride2 = F2->kp_stride;
+    int rc;
+    if ((rc = stageIn(m, 0, F1->n_kp, nf, inDev, &A.n1))) return rc;
+    if ((rc = stageIn(m, 1, F2->n_kp, nf, inDev, &A.n2))) return rc;
+    if ((rc = stageIn(m, 2, F1->kps, nk1, inDev, &A.kps1))) return rc;
+    if ((rc = stageIn(m, 3, F1->desc, nk1 * 32, inDev, &A.desc1))) return rc;
+    if ((rc = stageIn(m, 4, F2->kps, nk2, inDev, &A.kps2))) return rc;
+    if ((rc = stageIn(m, 5, F2->desc, nk2 * 32, inDev, &A.desc2))) return rc;
+    const float *dPrev = nullptr;
+    if ((rc = stageIn(m, 6, (const float *)prevMatched, nk1 * 2, inDev, &dPrev))) return rc;
+    A.prevMatched = (float *)dPrev;
+    A.minX = F2->min_x; A.minY = F2->min_y;
+    A.invW = (float)kGridCols / (F2->max_x - F2->min_x);
+    A.invH = (float)kGridRows / (F2->max_y - F2->min_y);
+    A.window = (float)windowSize; A.nnratio = nnratio; A.checkOrientation = checkOrientation;
+    if ((rc = stageOut(m, 14, matches12, nk1, outDev, &A.matches12))) return rc;
+    if ((rc = stageOut(m, 16, nMatches, nf, outDev, &A.nMatches))) return rc;
+    void *p;
+    if ((rc = scratch(m, 18, nk2 * 4, &p))) return rc;
+    A.gridList = (int32_t *)p;
+    if ((rc = scratch(m, 19, (5 * nk1 + 2 * nk2) * 4, &p))) return rc;
+    A.state = (int32_t *)p;
+    m->launches += launchSearchForInitialization(A, m->stream);
+    if ((rc = copyOut(m, matches12, A.matches12, nk1, outDev))) return rc;
+    if ((rc = copyOut(m, nMatches, A.nMatches, nf, outDev))) return rc;
+    if (!inDev) YGZ_CUDA(cudaMemcpyAsync(prevMatched, A.prevMatched, nk1 * 2 * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+    return finish(m, flags);
+}
+
 static int stageKf(Matcher *m, int slot0, const ygzorb_keyframe_features *K, bool inDev, KfView *V) {
     int rc;
     V->n = K->n; V->nNodes = K->n_nodes;

@@ -43,6 +43,21 @@ struct ProjArgs {
     uint8_t *candCnt;                         // scratch [nFrames * mpStride]
 };
 
+// ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:375-478), batched over frame pairs
+struct InitArgs {
+    int nFrames, stride1, stride2;
+    const int32_t *n1, *n2;
+    const ygzorb_keypoint *kps1, *kps2;
+    const uint8_t *desc1, *desc2;
+    float minX, minY, invW, invH;      // grid of F2
+    float *prevMatched;                // vbPrevMatched, (x, y) per keypoint of F1, updated in place
+    float window, nnratio;
+    int checkOrientation;
+    int32_t *matches12, *nMatches;
+    int32_t *gridList;                 // scratch [nFrames * stride2]
+    int32_t *state;                    // scratch [nFrames * (5 * stride1 + 2 * stride2)]
+};
+
 struct KfView {          // one KeyFrame's arrays for SearchForTriangulation (device pointers)
     int n, nNodes;
     const ygzorb_keypoint *kps;
@@ -91,6 +106,7 @@ int launchKnn2(const uint8_t *query, int nq, const uint8_t *train, int nt, float
                int variant, int32_t *bestIdx, int32_t *d1, int32_t *d2, int32_t *match, cudaStream_t s);
 int launchSearchByProjection(const ProjArgs &A, int maxKp, cudaStream_t s);
 int launchSearchByProjectionLast(const ProjArgs &A, cudaStream_t s);
+int launchSearchForInitialization(const InitArgs &A, cudaStream_t s);
 int launchSearchByProjectionKeyFrame(const ProjArgs &A, int mode, cudaStream_t s);
 int launchSim3Agreement(const int32_t *match1, const int32_t *match2, const int32_t *n1, const int32_t *n2, int stride1, int stride2,
                         int nFrames, int32_t *matches12, int32_t *nFound, cudaStream_t s);

@@ -271,6 +271,8 @@ class Matcher:
                                                         C.c_void_p, C.c_void_p, C.c_void_p]
         L.ygzorb_search_by_projection_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_void_p,
                                                        C.c_void_p, C.c_void_p]
+        L.ygzorb_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int,
+                                                       C.c_uint, C.c_void_p, C.c_void_p]
         L.ygzorb_fuse.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_uint, C.c_void_p, C.c_void_p]
         L.ygzorb_search_by_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_uint,
                                             C.c_void_p, C.c_void_p]
@@ -459,6 +461,26 @@ class Matcher:
             check(lib().ygzorb_fuse(self.h, C.byref(F), C.byref(L), th, int(variant == 3), _ptr(is2), 0, _ptr(best), _ptr(nm)))
             return [(int(nm[i]), None, best[i, :n_pt[i]].copy()) for i in range(nf)]
         return [(int(nm[i]), kp_to_pt[i, :n_kp[i]].copy(), best[i, :n_pt[i]].copy()) for i in range(nf)]
+
+    def search_for_initialization(self, frames1, frames2, prev_matched, bounds2, window_size, nnratio, check_orientation):
+        """frames1 / frames2: lists of (kps, desc); prev_matched: list of (n1, 2) float32 arrays (vbPrevMatched).
+        Returns per pair (n_matches, matches12, updated prev_matched)."""
+        nf = len(frames1)
+        s1 = max(max(len(f[0]) for f in frames1), 1); s2 = max(max(len(f[0]) for f in frames2), 1)
+        n1 = np.array([len(f[0]) for f in frames1], np.int32); n2 = np.array([len(f[0]) for f in frames2], np.int32)
+        k1 = np.zeros((nf, s1), KP_DTYPE); d1 = np.zeros((nf, s1, 32), np.uint8)
+        k2 = np.zeros((nf, s2), KP_DTYPE); d2 = np.zeros((nf, s2, 32), np.uint8)
+        pm = np.zeros((nf, s1, 2), np.float32)
+        for i in range(nf):
+            k1[i, :n1[i]] = frames1[i][0]; d1[i, :n1[i]] = frames1[i][1]
+            k2[i, :n2[i]] = frames2[i][0]; d2[i, :n2[i]] = frames2[i][1]
+            pm[i, :n1[i]] = prev_matched[i]
+        F1 = FrameFeatures(nf, s1, _ptr(n1), _ptr(k1), _ptr(d1), None, None, bounds2[0], bounds2[1], bounds2[2], bounds2[3], 0, None)
+        F2 = FrameFeatures(nf, s2, _ptr(n2), _ptr(k2), _ptr(d2), None, None, bounds2[0], bounds2[1], bounds2[2], bounds2[3], 0, None)
+        m12 = np.zeros((nf, s1), np.int32); nm = np.zeros(nf, np.int32)
+        check(lib().ygzorb_search_for_initialization(self.h, C.byref(F1), C.byref(F2), _ptr(pm), int(window_size), nnratio,
+                                                     int(check_orientation), 0, _ptr(m12), _ptr(nm)))
+        return [(int(nm[i]), m12[i, :n1[i]].copy(), pm[i, :n1[i]].copy()) for i in range(nf)]
 
     def search_by_sim3(self, kfs1, kfs2, pts1, pts2, bounds1, bounds2, scale_factors, th):
         """kfs1 / kfs2: lists of (kps, desc); pts1[i] = MapPoints of kfs1[i] (one per keypoint) with the pose that takes them

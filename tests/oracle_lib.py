@@ -273,6 +273,19 @@ def search_by_projection_keyframe(kps, desc, claimed, bounds, scale_factors, pts
     return nm, kp_to_pt[:n].copy(), best[:m].copy()
 
 
+def search_for_initialization(kps1, desc1, kps2, desc2, bounds2, prev_matched, window_size, nnratio, check_orientation):
+    """Returns (n_matches, vnMatches12, updated vbPrevMatched)."""
+    k1, k2 = np.ascontiguousarray(kps1), np.ascontiguousarray(kps2)
+    d1, d2 = np.ascontiguousarray(desc1, np.uint8), np.ascontiguousarray(desc2, np.uint8)
+    inv_w, inv_h = grid_inv(*bounds2)
+    pm = np.array(prev_matched, np.float32).reshape(-1, 2).copy()
+    m12 = np.zeros(max(len(k1), 1), np.int32)
+    nm = lib().ygzo_search_for_initialization(_p(k1), _p(d1), len(k1), _p(k2), _p(d2), len(k2), C.c_float(bounds2[0]),
+                                              C.c_float(bounds2[1]), C.c_float(inv_w), C.c_float(inv_h), _p(pm), int(window_size),
+                                              C.c_float(nnratio), int(check_orientation), _p(m12))
+    return nm, m12[:len(k1)].copy(), pm
+
+
 def sim3_agreement(match1, match2):
     m1, m2 = np.ascontiguousarray(match1, np.int32), np.ascontiguousarray(match2, np.int32)
     out = np.zeros(max(len(m1), 1), np.int32)

@@ -220,6 +220,35 @@ def keyframe_points_case(kps, desc, n_pts, seed, variant, jitter=2.0, fx=458.654
     return pts, claimed
 
 
+def initialization_case(kps, desc, seed, shift=(12.0, -7.0), n_dup=200):
+    """Two frames for SearchForInitialization: F1 = the given features (60 % forced to octave 0) plus n_dup near-copies
+    that compete for the same partner; F2 = shifted, jittered, bit-flipped, shuffled counterparts of 80 % of F1 with some
+    rotated angles.  Returns (kps1, desc1, kps2, desc2, prev_matched)."""
+    rng = np.random.default_rng(seed)
+    k1 = kps.copy()
+    k1["octave"] = np.where(rng.uniform(size=len(k1)) < 0.6, 0, k1["octave"])
+    dup = rng.integers(0, len(k1), n_dup)
+    kd = k1[dup].copy()
+    kd["x"] += rng.uniform(-3, 3, n_dup).astype(np.float32); kd["y"] += rng.uniform(-3, 3, n_dup).astype(np.float32)
+    kd["octave"] = 0
+    k1 = np.concatenate([k1, kd]); d1 = np.concatenate([desc, flip_bits(desc[dup], rng.integers(0, 12, n_dup), rng)])
+    order = rng.permutation(len(k1))
+    k1, d1 = k1[order], d1[order]
+    sel = np.flatnonzero(rng.uniform(size=len(kps)) < 0.8)
+    k2 = kps[sel].copy()
+    k2["octave"] = np.where(rng.uniform(size=len(k2)) < 0.75, 0, k2["octave"])
+    k2["x"] = (k2["x"] + shift[0] + rng.uniform(-2, 2, len(k2))).astype(np.float32)
+    k2["y"] = (k2["y"] + shift[1] + rng.uniform(-2, 2, len(k2))).astype(np.float32)
+    ang = k2["angle"] + rng.normal(0, 3.0, len(k2))
+    ang = np.where(rng.uniform(size=len(k2)) < 0.12, ang + rng.uniform(40, 320, len(k2)), ang)
+    k2["angle"] = np.mod(ang, 360.0).astype(np.float32)
+    d2 = flip_bits(desc[sel], rng.integers(0, 40, len(sel)), rng)
+    o2 = rng.permutation(len(k2))
+    k2, d2 = k2[o2], d2[o2]
+    prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+    return k1, d1, k2, d2, prev
+
+
 def feature_vector(n, n_nodes, seed, base=None, p_keep=0.8):
     """Synthetic DBoW2::FeatureVector as CSR: ascending node ids, features in insertion (index) order.
     With `base` (node of each feature of another keyframe mapped through `src`) matched features

@@ -145,6 +145,24 @@ def test_search_by_sim3_vs_oracle(matcher, feats, th, seed):
         assert g[0] == e[0] and e[0] > 50 and np.array_equal(g[1], e[1])
 
 
+@pytest.mark.parametrize("window,ratio,check_ori,seed", [(100, 0.9, True, 1), (30, 0.9, True, 2), (100, 0.7, False, 3),
+                                                         (400, 0.95, True, 4)])
+def test_search_for_initialization_vs_oracle(matcher, feats, window, ratio, check_ori, seed):
+    """SearchForInitialization (src/ORBmatcher.cc:375-478): level-0 window search with the vMatchedDistance take-over rule,
+    rotation rejection and the vbPrevMatched update; competing near-copies in F1 exercise the serial order."""
+    img, kps, desc = feats
+    bounds = (0.0, 0.0, float(img.shape[1]), float(img.shape[0]))
+    f1, f2, prevs, exp = [], [], [], []
+    for k in range(3):
+        k1, d1, k2, d2, prev = synth.initialization_case(kps[:len(kps) - 100 * k], desc[:len(kps) - 100 * k], seed * 10 + k)
+        f1.append((k1, d1)); f2.append((k2, d2)); prevs.append(prev)
+        exp.append(O.search_for_initialization(k1, d1, k2, d2, bounds, prev, window, ratio, check_ori))
+    got = matcher.search_for_initialization(f1, f2, prevs, bounds, window, ratio, check_ori)
+    for g, e in zip(got, exp):
+        assert g[0] == e[0] and e[0] > 100
+        assert np.array_equal(g[1], e[1]) and g[2].tobytes() == e[2].tobytes()
+
+
 def test_search_by_projection_claim_chain(matcher, feats):
     """Many MapPoints aimed at the same keypoints: long claim chains must resolve like the serial loop."""
     img, kps, desc = feats

@@ -380,6 +380,94 @@ def test_search_by_projection_keyframe_vs_python(th, variant, orb_dist, check_or
         assert (a[2] >= 0).sum() > a[0]
 
 
+def _py_search_for_initialization(k1, d1, k2, d2, bounds, prev, window, ratio, check_ori):
+    """src/ORBmatcher.cc:375-478 re-derived."""
+    f = np.float32
+    min_x, min_y, max_x, max_y = [f(b) for b in bounds]
+    inv_w, inv_h = f(64) / (max_x - min_x), f(48) / (max_y - min_y)
+    rnd = lambda v: int(math.floor(abs(v) + 0.5)) * (1 if v >= 0 else -1)
+    grid = {}
+    for i in range(len(k2)):
+        px, py = rnd(float((k2["x"][i] - min_x) * inv_w)), rnd(float((k2["y"][i] - min_y) * inv_h))
+        if 0 <= px < 64 and 0 <= py < 48:
+            grid.setdefault((px, py), []).append(i)
+    D = _hamming_matrix(d1, d2)
+    prev = prev.copy()
+    m12 = np.full(len(k1), -1, np.int32); m21 = np.full(len(k2), -1, np.int32)
+    md = np.full(len(k2), 2**31 - 1, np.int64)
+    hist = [[] for _ in range(30)]
+    n = 0
+    r = f(window)
+    for i1 in range(len(k1)):
+        if k1["octave"][i1] > 0:
+            continue
+        x, y = prev[i1]
+        cx0 = max(0, math.floor(float(f(f(x - min_x - r) * inv_w)))); cx1 = min(63, math.ceil(float(f(f(x - min_x + r) * inv_w))))
+        cy0 = max(0, math.floor(float(f(f(y - min_y - r) * inv_h)))); cy1 = min(47, math.ceil(float(f(f(y - min_y + r) * inv_h))))
+        if cx0 >= 64 or cx1 < 0 or cy0 >= 48 or cy1 < 0:
+            continue
+        b1 = b2 = 2**31 - 1; bi = -1
+        for ix in range(cx0, cx1 + 1):
+            for iy in range(cy0, cy1 + 1):
+                for i2 in grid.get((ix, iy), []):
+                    if k2["octave"][i2] != 0:
+                        continue
+                    if not (abs(f(k2["x"][i2] - x)) < r and abs(f(k2["y"][i2] - y)) < r):
+                        continue
+                    d = int(D[i1, i2])
+                    if md[i2] <= d:
+                        continue
+                    if d < b1:
+                        b2, b1, bi = b1, d, i2
+                    elif d < b2:
+                        b2 = d
+        if b1 <= 50 and f(b1) < f(f(b2) * f(ratio)):
+            if m21[bi] >= 0:
+                m12[m21[bi]] = -1; n -= 1
+            m12[i1] = bi; m21[bi] = i1; md[bi] = b1; n += 1
+            if check_ori:
+                rot = f(k1["angle"][i1] - k2["angle"][bi])
+                if rot < 0:
+                    rot = f(rot + f(360))
+                b = rnd(float(f(rot * f(f(1.0) / f(30)))))
+                hist[0 if b == 30 else b].append(i1)
+    if check_ori:
+        m1 = m2 = m3 = 0; j1 = j2 = j3 = -1
+        for i in range(30):
+            sz = len(hist[i])
+            if sz > m1:
+                m3, m2, m1, j3, j2, j1 = m2, m1, sz, j2, j1, i
+            elif sz > m2:
+                m3, m2, j3, j2 = m2, sz, j2, i
+            elif sz > m3:
+                m3, j3 = sz, i
+        if f(m2) < f(0.1) * f(m1):
+            j2 = j3 = -1
+        elif f(m3) < f(0.1) * f(m1):
+            j3 = -1
+        for i in range(30):
+            if i not in (j1, j2, j3):
+                for idx1 in hist[i]:
+                    if m12[idx1] >= 0:
+                        m12[idx1] = -1; n -= 1
+    for i1 in range(len(k1)):
+        if m12[i1] >= 0:
+            prev[i1] = (k2["x"][m12[i1]], k2["y"][m12[i1]])
+    return n, m12, prev
+
+
+@pytest.mark.parametrize("window,ratio,check_ori,seed", [(100, 0.9, True, 1), (30, 0.9, True, 2), (100, 0.7, False, 3)])
+def test_search_for_initialization_vs_python(window, ratio, check_ori, seed):
+    img, (kps, desc) = _features(seed=seed)
+    k1, d1, k2, d2, prev = synth.initialization_case(kps, desc, seed, n_dup=120)
+    bounds = (0.0, 0.0, float(img.shape[1]), float(img.shape[0]))
+    a = O.search_for_initialization(k1, d1, k2, d2, bounds, prev, window, ratio, check_ori)
+    b = _py_search_for_initialization(k1, d1, k2, d2, bounds, prev, window, ratio, check_ori)
+    assert a[0] == b[0] and a[0] > 40 and a[0] == (a[1] >= 0).sum()
+    assert np.array_equal(a[1], b[1]) and a[2].tobytes() == b[2].tobytes()
+    assert len(set(a[1][a[1] >= 0].tolist())) == a[0]          # a keypoint of F2 has one owner
+
+
 def test_search_by_projection_order_dependence():
     """Two MapPoints with the same descriptor on the same keypoint: the first claims it, the second must skip it."""
     img, (kps, desc) = _features(seed=9)
