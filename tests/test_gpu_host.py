@@ -100,3 +100,108 @@ def test_host_classes_end_to_end():
     assert gn == en and np.array_equal(gm, em) and en > 50
     assert o == len(bowbuf)
     ovoc.close()
+
+
+DEMO2 = os.path.join(PKG, "host", "host_demo2")
+REC = np.dtype([("wpos", "<f4", 3), ("normal", "<f4", 3), ("angle", "<f4"), ("max_d", "<f4"), ("min_d", "<f4"),
+                ("valid", "<i4"), ("n_obs", "<i4"), ("desc", "u1", 32)])
+
+
+def _records(pts, n_obs):
+    r = np.zeros(len(pts["valid"]), REC)
+    r["wpos"] = pts["world_pos"]; r["normal"] = pts["normal"]; r["angle"] = pts["angle"]
+    r["max_d"] = pts["max_distance"]; r["min_d"] = pts["min_distance"]; r["valid"] = pts["valid"]; r["n_obs"] = n_obs
+    r["desc"] = pts["desc"]
+    return r
+
+
+def test_host_matcher_overloads_on_objects():
+    """SearchForInitialization, the relocalisation SearchByProjection and Fuse through ygz::ORBmatcher on Frame / KeyFrame /
+    MapPoint objects (host_demo2.cc), compared with the oracle; Fuse's map updates are replayed here from the oracle's
+    per-point result with the rules of src/ORBmatcher.cc:862-877."""
+    if not os.path.exists(DEMO2):
+        subprocess.run(["make", "-C", os.path.join(PKG, "host")], check=True)
+    w, h, nf = 752, 480, 1000
+    img = synth.textured_frame(w, h, 5)
+    kps, desc = O.extract(O.params(nf), img)
+    n = len(kps)
+    sf, _, sigma2 = synth.scale_tables()
+    inv_sigma2 = (np.float32(1.0) / sigma2).astype(np.float32)
+    bounds = (0.0, 0.0, float(w), float(h))
+    rng = np.random.default_rng(9)
+    _, _, k2, d2, _ = synth.initialization_case(kps, desc, 31)
+    prev = np.stack([kps["x"], kps["y"]], 1).astype(np.float32)
+    reloc, claimed = synth.keyframe_points_case(kps, desc, 900, 32, 0)
+    fuse, _ = synth.keyframe_points_case(kps, desc, 1100, 33, 2)
+    fuse_obs = rng.integers(0, 6, 1100).astype(np.int32)
+    existing = np.where(rng.uniform(size=n) < 0.4, rng.integers(0, 6, n), -1).astype(np.int32)
+    with tempfile.TemporaryDirectory() as td:
+        fin, fout = os.path.join(td, "in.bin"), os.path.join(td, "out.bin")
+        with open(fin, "wb") as f:
+            np.array([n], np.int32).tofile(f); kps.tofile(f); desc.tofile(f)
+            np.array(bounds, np.float32).tofile(f); np.array([len(sf)], np.int32).tofile(f); sf.tofile(f); inv_sigma2.tofile(f)
+            np.array([reloc["log_scale_factor"]], np.float32).tofile(f)
+            np.array([len(k2)], np.int32).tofile(f); k2.tofile(f); d2.tofile(f)
+            np.array([100], np.int32).tofile(f); np.array([0.9], np.float32).tofile(f)
+            np.array([len(reloc["valid"])], np.int32).tofile(f); reloc["pose"].tofile(f); _records(reloc, 1).tofile(f)
+            claimed.tofile(f); np.array([10.0], np.float32).tofile(f); np.array([100], np.int32).tofile(f)
+            np.array([len(fuse["valid"])], np.int32).tofile(f); fuse["pose"].tofile(f); _records(fuse, fuse_obs).tofile(f)
+            fuse["u_right"].tofile(f); existing.tofile(f); np.array([3.0], np.float32).tofile(f)
+        res = subprocess.run([DEMO2, fin, fout], capture_output=True, text=True)
+        assert res.returncode == 0, res.stdout + res.stderr
+        buf = open(fout, "rb").read()
+    off = 0
+
+    def take(dtype, cnt):
+        nonlocal off
+        a = np.frombuffer(buf, dtype, cnt, off)
+        off += a.nbytes
+        return a
+    # SearchForInitialization
+    en, em, ep = O.search_for_initialization(kps, desc, k2, d2, bounds, prev, 100, float(np.float32(0.9)), True)
+    assert int(take("<i4", 1)[0]) == en and en > 50
+    assert np.array_equal(take("<i4", n), em)
+    got_prev = take("<f4", 2 * n).reshape(n, 2)
+    assert got_prev.tobytes() == ep.tobytes()
+    # relocalisation SearchByProjection
+    en, e_kp, _ = O.search_by_projection_keyframe(kps, desc, claimed, bounds, sf, reloc, 10.0, 0, 100, True)
+    assert int(take("<i4", 1)[0]) == en and en > 100
+    want = np.where(e_kp >= 0, e_kp, np.where(claimed > 0, -2, -1))
+    assert np.array_equal(take("<i4", n), want)
+    # Fuse: replay :862-877 over the oracle's per-point keypoints
+    m = len(fuse["valid"])
+    _, _, best = O.search_by_projection_keyframe(kps, desc, None, bounds, sf, fuse, 3.0, 2, 50, False, fuse["u_right"], inv_sigma2)
+    slot = np.where(existing >= 0, m + np.arange(n), -1)
+    obs = np.concatenate([fuse_obs, np.where(existing >= 0, existing, 1)]).astype(np.int64)   # MapPointLite default nObs = 1
+    bad = np.concatenate([fuse["valid"] == 0, np.zeros(n, bool)])
+    in_kf = np.concatenate([np.zeros(m, bool), existing >= 0])
+    kf_idx = np.concatenate([np.full(m, -1), np.arange(n)])
+    replaced = np.full(m + n, -1)
+    n_fused = 0
+
+    def replace(a, b):          # a->Replace(b), MapPointLite::Replace
+        bad[a] = True; replaced[a] = b
+        if in_kf[a]:
+            in_kf[a] = False
+            if not in_kf[b]:
+                slot[kf_idx[a]] = b; in_kf[b] = True; kf_idx[b] = kf_idx[a]; obs[b] += 1
+            else:
+                slot[kf_idx[a]] = -1
+    for i in range(m):
+        if best[i] < 0 or bad[i] or in_kf[i]:
+            continue
+        cur = slot[best[i]]
+        if cur >= 0:
+            if not bad[cur]:
+                if obs[cur] > obs[i]:
+                    replace(i, cur)
+                else:
+                    replace(cur, i)
+        else:
+            slot[best[i]] = i; in_kf[i] = True; kf_idx[i] = best[i]; obs[i] += 1
+        n_fused += 1
+    assert int(take("<i4", 1)[0]) == n_fused and n_fused > 100
+    assert np.array_equal(take("<i4", n), slot)
+    assert np.array_equal(take("<i4", m + n), replaced)
+    assert np.array_equal(take("<i4", m + n), obs)
+    assert off == len(buf)
