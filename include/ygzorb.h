@@ -86,6 +86,26 @@ int ygzorb_extract_batch(ygzorb_extractor *ex, const uint8_t *frames, int n_fram
                          size_t frame_stride, unsigned flags, int cap, int32_t *counts,
                          ygzorb_keypoint *keypoints, uint8_t *desc);
 
+/* ORBextractor::operator()(Frame *frame, vector<KeyPoint> &_keypoints, OutputArray _descriptors, DSO_KEYPOINT, leftEye = true)
+ * (src/ORBextractor.cc:1031-1127 with :1052-1058) as Frame::ExtractORB calls it on frames that come out of direct tracking
+ * (src/Frame.cc:335-337): ComputeKeyPointsDSOSingleLevel (:1275-1386) — cells of mnGridSize pixels on level 0, FAST-10
+ * (Thirdparty/fast; the scalar detector without a margin for cells narrower than 22 px, the SSE2 one with its 3-px margin
+ * otherwise) at threshold 20 then 5, pixels of existing keypoints excluded, Shi-Tomasi score (:1152-1187), the best three per
+ * cell, the grid shrunk by 5 until nfeatures corners are found — then IC_Angle for the new keypoints and the existing ones
+ * (:1383-1385) and descriptors of all of them on the blurred pyramid (:1079-1113).
+ * keypoints is in-out: on entry the first n_exist[f] records of frame f (at keypoints + f*cap) are frame->mvKeys (level-0
+ * coordinates, octave = their level); on return records [0, counts[f]) are the existing keypoints with refreshed angles
+ * followed by the new ones (size 7, octave 0, response 0), desc holds one row per record.  keypoints / desc / counts follow
+ * YGZORB_OUT_DEVICE (the existing keypoints are then read from device memory too).
+ * grid_size (HOST, in-out, one per frame): mnGridSize before / after the frame (< 0: not yet initialised, :1295-1296).  Frames
+ * of one batch are independent extractors; a single camera stream feeds grid_size[0] of one call into the next.
+ * n_exist: HOST.  n_frames <= max_batch.  Canonical where the reference is undefined: equal Shi-Tomasi scores keep raster
+ * order (std::sort is unstable beyond 16 corners), a frame without any corner stops instead of looping forever (:1299-1301),
+ * an existing keypoint closer than 16 px to the border of its level gets a zero descriptor and keeps its angle. */
+int ygzorb_extract_dso_batch(ygzorb_extractor *ex, const uint8_t *frames, int n_frames, int w, int h, int stride,
+                             size_t frame_stride, unsigned flags, int32_t *grid_size, const int32_t *n_exist, int cap,
+                             int32_t *counts, ygzorb_keypoint *keypoints, uint8_t *desc);
+
 /* ORBextractor::ComputePyramid(cv::Mat) alone (src/ORBextractor.cc:1129-1150) — what the Frame
  * constructor runs (src/Frame.cc:773-814).  Host or device input per flags. */
 int ygzorb_compute_pyramid_batch(ygzorb_extractor *ex, const uint8_t *frames, int n_frames, int w, int h,

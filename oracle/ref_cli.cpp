@@ -11,8 +11,12 @@
 //
 // usage: ygz_ref_orb --in frames.u8 --w W --h H --n N [--nfeatures 1000 --scale 1.2 --levels 8
 //                    --ini 20 --min 7] [--out out.bin] [--pyr] [--frame-api] [--repeat R] [--threads T]
+//                    [--dso [--exist exist.bin] [--grid G0]]
 // out.bin, per frame: int32 n | n x 28 B cv::KeyPoint | n x 32 B descriptors |
-//                     (--pyr) per level: int32 w, int32 h, w*h bytes.
+//                     (--pyr) per level: int32 w, int32 h, w*h bytes | (--dso) int32 mnGridSize after the frame.
+// --dso: Frame::ExtractORB's direct-tracking branch (src/Frame.cc:335-337): ONE extractor walks the frames in order (its
+// mnGridSize carries over, src/ORBextractor.cc:1295-1376) and runs operator()(Frame*, mvKeys, desc, DSO_KEYPOINT) on a Frame
+// that already holds the keypoints of exist.bin (per frame: int32 n | n x 28 B cv::KeyPoint); --grid seeds mnGridSize.
 #include <sys/mman.h>
 
 #include <atomic>
@@ -26,7 +30,9 @@
 #include <thread>
 #include <vector>
 
+#define protected public   // mnGridSize (include/ORBextractor.h:191) is read back for the DSO keypoint mode; layout is unaffected
 #include "ORBextractor.h"
+#undef protected
 #include "Frame.h"
 
 // ------------------------------------------------------------------ monotonic bump arena
@@ -77,7 +83,9 @@ struct Opts {
     std::string in, out;
     int w = 0, h = 0, n = 1, nfeatures = 1000, levels = 8, ini = 20, mn = 7, repeat = 1, threads = 1;
     float scale = 1.2f;
-    bool pyr = false, frameApi = false;
+    bool pyr = false, frameApi = false, dso = false;
+    std::string exist;
+    int grid = -1;
 };
 
 struct FrameOut {
@@ -86,7 +94,43 @@ struct FrameOut {
     unsigned char *desc = nullptr;  // malloc'd, n*32
     std::vector<int> lw, lh;
     std::vector<unsigned char *> lv;
+    int gridAfter = 0;
 };
+
+static void storeOut(FrameOut *fo, const std::vector<cv::KeyPoint> &kps, const cv::Mat &desc) {
+    fo->n = (int)kps.size();
+    fo->kps = (unsigned char *)std::malloc((size_t)fo->n * 28 + 1);
+    fo->desc = (unsigned char *)std::malloc((size_t)fo->n * 32 + 1);
+    if (fo->n) std::memcpy(fo->kps, kps.data(), (size_t)fo->n * 28);
+    for (int i = 0; i < fo->n; i++) std::memcpy(fo->desc + (size_t)i * 32, desc.ptr(i), 32);
+}
+
+// --dso: all frames through one extractor, in order
+static void runDso(const Opts &o, const unsigned char *frames, std::vector<FrameOut> &outs) {
+    ygz::ORBextractor ex(o.nfeatures, o.scale, o.levels, o.ini, o.mn);
+    if (o.grid > 0) ex.mnGridSize = o.grid;
+    FILE *fe = o.exist.empty() ? nullptr : std::fopen(o.exist.c_str(), "rb");
+    const size_t fsz = (size_t)o.w * o.h;
+    for (int k = 0; k < o.n; k++) {
+        cv::Mat im(o.h, o.w, cv::CV_8UC1, (void *)(frames + fsz * k), (size_t)o.w);
+        ygz::Frame f;
+        ex.ComputePyramid(im);
+        f.mvImagePyramid.resize(o.levels);
+        for (int l = 0; l < o.levels; l++) f.mvImagePyramid[l] = ex.mvImagePyramid[l].clone();
+        if (fe) {
+            int ne = 0;
+            if (std::fread(&ne, 4, 1, fe) != 1) { std::fputs("short exist file\n", stderr); std::exit(1); }
+            f.mvKeys.resize(ne);
+            if (ne && std::fread(f.mvKeys.data(), 28, (size_t)ne, fe) != (size_t)ne) { std::fputs("short exist file\n", stderr); std::exit(1); }
+        }
+        f.N = (int)f.mvKeys.size();
+        cv::Mat desc;
+        ex(&f, f.mvKeys, desc, ygz::ORBextractor::DSO_KEYPOINT, true);
+        storeOut(&outs[k], f.mvKeys, desc);
+        outs[k].gridAfter = ex.mnGridSize;
+    }
+    if (fe) std::fclose(fe);
+}
 
 static void runOne(const Opts &o, const unsigned char *img, FrameOut *fo) {
     // Everything allocated between mark and release dies inside this scope.
@@ -146,6 +190,9 @@ int main(int argc, char **argv) {
         else if (a == "--threads") o.threads = std::atoi(next());
         else if (a == "--pyr") o.pyr = true;
         else if (a == "--frame-api") o.frameApi = true;
+        else if (a == "--dso") o.dso = true;
+        else if (a == "--exist") o.exist = next();
+        else if (a == "--grid") o.grid = std::atoi(next());
         else { std::fprintf(stderr, "unknown option %s\n", a.c_str()); return 2; }
     }
     if (o.in.empty() || o.w <= 0 || o.h <= 0 || o.n <= 0) { std::fputs("need --in --w --h --n\n", stderr); return 2; }
@@ -161,7 +208,9 @@ int main(int argc, char **argv) {
 
     const auto t0 = std::chrono::steady_clock::now();
     const int total = o.n * o.repeat;
-    if (o.threads <= 1) {
+    if (o.dso) {
+        runDso(o, frames, outs);
+    } else if (o.threads <= 1) {
         for (int k = 0; k < total; k++) {
             const int f = k % o.n;
             runOne(o, frames + fsz * f, k < o.n ? &outs[f] : nullptr);
@@ -196,6 +245,7 @@ int main(int argc, char **argv) {
                 std::fwrite(&r.lh[l], 4, 1, fo);
                 std::fwrite(r.lv[l], 1, (size_t)r.lw[l] * r.lh[l], fo);
             }
+            if (o.dso) std::fwrite(&r.gridAfter, 4, 1, fo);
         }
         std::fclose(fo);
     }

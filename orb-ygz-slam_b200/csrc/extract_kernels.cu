@@ -4,6 +4,7 @@
 // for bit; float arithmetic is written with explicit round-to-nearest intrinsics so nvcc cannot
 // contract it into FMAs the reference's build (-ffp-contract=off) does not execute.
 #include "ygz_common.cuh"
+#include "ygz_dso.cuh"
 #include "orb_pattern.inc"
 
 namespace ygz {
@@ -902,6 +903,54 @@ __device__ __forceinline__ float devFastAtan2(float y, float x) {
 
 __device__ __align__(16) signed char gPattern[1024];  // filled from kOrbPattern by configureKernels()
 
+// IC_Angle (:79-109) by one warp: lane <-> column u = lane-15; the rows of the circular patch that hold column u are
+// |v| <= vmaxOfU[|u|], taken in +-v pairs like the reference (integer sums: order-free).  c0 = patch centre.
+__device__ __forceinline__ float icAngleWarp(const FrameGeom &G, const uint8_t *c0, int pitch, int lane) {
+    int m10 = 0, m01 = 0;
+    const int u = lane - kHalfPatch;
+    if (lane < 31) {
+        const int vmax = G.vmaxOfU[abs(u)];
+        const uint8_t *up = c0 + u, *dn = up;
+        int sum = *up;
+#pragma unroll 4
+        for (int v = 1; v <= vmax; v++) {
+            up -= pitch; dn += pitch;
+            const int a = *dn, b = *up;
+            sum += a + b;
+            m01 += v * (a - b);
+        }
+        m10 = u * sum;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    }
+    return devFastAtan2((float)m01, (float)m10);
+}
+
+// computeOrbDescriptor (:105-149) by one warp: lane <-> byte, 8 tests each.  cb = patch centre on the blurred level.
+__device__ __forceinline__ int orbByteWarp(const uint8_t *cb, int bp, float angle, int lane) {
+    const float factorPI = (float)(3.14159265358979323846 / 180.f);
+    float a, b;
+    devSinCosf(__fmul_rn(angle, factorPI), &b, &a);
+    const char4 *pat = reinterpret_cast<const char4 *>(gPattern) + lane * 8;  // 8 tests (x0,y0,x1,y1) per byte
+    int val = 0;
+#pragma unroll
+    for (int t = 0; t < 8; t++) {
+        const char4 p = pat[t];
+        // GET_VALUE(idx) = center[cvRound(x*b + y*a)*step + cvRound(x*a - y*b)]  (:114-116)
+        const float x0 = p.x, y0 = p.y, x1 = p.z, y1 = p.w;
+        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
+        const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
+        const int q1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+        const int t0 = cb[r0 * bp + q0], t1 = cb[r1 * bp + q1];
+        val |= (t0 < t1) << t;
+    }
+    return val;
+}
+
 constexpr int kDescWarps = 8;
 
 __global__ void __launch_bounds__(kDescWarps * 32) k_describe(const __grid_constant__ FrameGeom G, const DevBuffers B, int cap,
@@ -921,50 +970,9 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(const __grid_const
     const LevelGeom &L = G.lv[level];
     const uint32_t xyr = B.kept[(long long)f * G.keptCap + L.keptOff + k];
     const int x = xyr & 0xfff, y = (xyr >> 12) & 0xfff;
-    // ---- IC_Angle (:79-109): lane <-> column u = lane-15; the rows of the circular patch that hold column u
-    // are |v| <= vmaxOfU[|u|], taken in +-v pairs like the reference (integer sums: order-free)
-    const uint8_t *c0 = levelPtr(G, B, f, level) + (long long)y * L.pitch + x;
-    int m10 = 0, m01 = 0;
-    const int u = lane - kHalfPatch;
-    if (lane < 31) {
-        const int vmax = G.vmaxOfU[abs(u)];
-        const uint8_t *up = c0 + u, *dn = up;
-        int sum = *up;
-#pragma unroll 4
-        for (int v = 1; v <= vmax; v++) {
-            up -= L.pitch; dn += L.pitch;
-            const int a = *dn, b = *up;
-            sum += a + b;
-            m01 += v * (a - b);
-        }
-        m10 = u * sum;
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-    }
-    const float angle = devFastAtan2((float)m01, (float)m10);
-    // ---- descriptor: lane <-> byte, 8 tests each
-    const float factorPI = (float)(3.14159265358979323846 / 180.f);
-    float a, b;
-    devSinCosf(__fmul_rn(angle, factorPI), &b, &a);
-    const uint8_t *cb = B.blur + (long long)f * B.blurSlab + B.blurOff[level] + (long long)y * B.blurPitch[level] + x;
-    const int bp = B.blurPitch[level];
-    const char4 *pat = reinterpret_cast<const char4 *>(gPattern) + lane * 8;  // 8 tests (x0,y0,x1,y1) per byte
-    int val = 0;
-#pragma unroll
-    for (int t = 0; t < 8; t++) {
-        const char4 p = pat[t];
-        // GET_VALUE(idx) = center[cvRound(x*b + y*a)*step + cvRound(x*a - y*b)]  (:114-116)
-        const float x0 = p.x, y0 = p.y, x1 = p.z, y1 = p.w;
-        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
-        const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
-        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
-        const int q1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
-        const int t0 = cb[r0 * bp + q0], t1 = cb[r1 * bp + q1];
-        val |= (t0 < t1) << t;
-    }
+    const float angle = icAngleWarp(G, levelPtr(G, B, f, level) + (long long)y * L.pitch + x, L.pitch, lane);
+    const int val = orbByteWarp(B.blur + (long long)f * B.blurSlab + B.blurOff[level] + (long long)y * B.blurPitch[level] + x,
+                                B.blurPitch[level], angle, lane);
     const long long o = (long long)f * cap + j;
     desc[o * 32 + lane] = (uint8_t)val;
     if (lane == 0) {
@@ -981,6 +989,36 @@ int launchDescribe(const FrameGeom &G, const DevBuffers &B, int nFrames, int cap
                    ygzorb_keypoint *kps, uint8_t *desc, cudaStream_t s) {
     const int blocks = (min(cap, G.keptCap) + kDescWarps - 1) / kDescWarps;
     k_describe<<<dim3(max(blocks, 1), nFrames), kDescWarps * 32, 0, s>>>(G, B, cap, counts, kps, desc);
+    return 1;
+}
+
+
+// Orientation + descriptor for a given list of patch centres (level, x, y): the descriptor pass of
+// operator()(Frame*, ..., DSO_KEYPOINT) (:1079-1113) and the angle refresh of the existing keypoints (:1383-1385).
+// A centre closer than 16 px to the border of its level (the reference would read outside the image) gets a zero descriptor
+// and keeps its angle.
+__global__ void __launch_bounds__(kDescWarps * 32) k_describe_list(const __grid_constant__ FrameGeom G, const DevBuffers B, int cap,
+                                                                   const int4 *centre, const int32_t *counts, ygzorb_keypoint *kps,
+                                                                   uint8_t *desc) {
+    const int f = blockIdx.y, lane = threadIdx.x & 31;
+    const int j = blockIdx.x * kDescWarps + (threadIdx.x >> 5);
+    if (j >= min(counts[f], cap)) return;
+    const long long o = (long long)f * cap + j;
+    const int4 c = centre[o];
+    const int level = c.x, x = c.y, y = c.z;
+    const LevelGeom &L = G.lv[level];
+    if (x < 16 || y < 16 || x >= L.w - 16 || y >= L.h - 16) { desc[o * 32 + lane] = 0; return; }
+    const float angle = icAngleWarp(G, levelPtr(G, B, f, level) + (long long)y * L.pitch + x, L.pitch, lane);
+    const int val = orbByteWarp(B.blur + (long long)f * B.blurSlab + B.blurOff[level] + (long long)y * B.blurPitch[level] + x,
+                                B.blurPitch[level], angle, lane);
+    desc[o * 32 + lane] = (uint8_t)val;
+    if (lane == 0) kps[o].angle = angle;
+}
+
+int launchDescribeList(const FrameGeom &G, const DevBuffers &B, int nFrames, int cap, const int4 *centre, const int32_t *counts,
+                       ygzorb_keypoint *kps, uint8_t *desc, cudaStream_t s) {
+    if (nFrames <= 0 || cap <= 0) return 0;
+    k_describe_list<<<dim3((cap + kDescWarps - 1) / kDescWarps, nFrames), kDescWarps * 32, 0, s>>>(G, B, cap, centre, counts, kps, desc);
     return 1;
 }
 

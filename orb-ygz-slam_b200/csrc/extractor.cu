@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "ygz_common.cuh"
+#include "ygz_dso.cuh"
 
 namespace ygz {
 
@@ -264,6 +265,14 @@ struct Extractor {
     size_t outCap = 0;  // records per frame the dOut* buffers hold
     int lastFrames = 0; bool lastInDevice = false; bool stagesValid = false;
     const uint8_t *lastIn = nullptr; long long lastInFrameStride = 0;
+    // DSO keypoint mode (ygzorb_extract_dso_batch): workspace grown on demand
+    uint32_t *dsoOcc = nullptr; size_t dsoOccBytes = 0;
+    uint32_t *dsoCellKp = nullptr; size_t dsoCellKpBytes = 0;
+    uint8_t *dsoCellCnt = nullptr; size_t dsoCellCntBytes = 0;
+    int32_t *dsoSmall = nullptr; size_t dsoSmallBytes = 0;     // grid, nExist, total, counts [maxBatch] + active bytes
+    int4 *dsoCentre = nullptr; size_t dsoCentreBytes = 0;
+    ygzorb_keypoint *dsoKps = nullptr; size_t dsoKpsBytes = 0;
+    uint8_t *dsoDesc = nullptr; size_t dsoDescBytes = 0;
     long long launches = 0;
     bool profiling = false;
     cudaEvent_t ev[8] = {};
@@ -498,7 +507,8 @@ void ygzorb_extractor_destroy(ygzorb_extractor *h) {
     cudaStream_t streams[] = {ex->h2d, ex->stream, ex->d2h};
     for (cudaStream_t st : streams) if (st) cudaStreamSynchronize(st);
     void *bufs[] = {ex->dIn[0], ex->dIn[1], ex->dPyr, ex->dBlur, ex->dTabs, ex->dCand, ex->dNodeOf, ex->dKept, ex->dCounts,
-                    ex->dOutCounts[0], ex->dOutCounts[1], ex->dOutKps[0], ex->dOutKps[1], ex->dOutDesc[0], ex->dOutDesc[1]};
+                    ex->dOutCounts[0], ex->dOutCounts[1], ex->dOutKps[0], ex->dOutKps[1], ex->dOutDesc[0], ex->dOutDesc[1],
+                    ex->dsoOcc, ex->dsoCellKp, ex->dsoCellCnt, ex->dsoSmall, ex->dsoCentre, ex->dsoKps, ex->dsoDesc};
     for (void *p : bufs) if (p) cudaFree(p);
     for (int i = 0; i < 8; i++) if (ex->ev[i]) cudaEventDestroy(ex->ev[i]);
     for (int sl = 0; sl < 2; sl++) {
@@ -596,6 +606,122 @@ int ygzorb_extract_batch(ygzorb_extractor *h, const uint8_t *frames, int n_frame
         if (rc) return rc;
     }
     if (!(flags & YGZORB_NO_SYNC)) return ygzorb_extractor_sync(h);
+    return 0;
+}
+
+int ygzorb_extract_dso_batch(ygzorb_extractor *h, const uint8_t *frames, int n_frames, int w, int hgt, int stride,
+                             size_t frame_stride, unsigned flags, int32_t *grid_size, const int32_t *n_exist, int cap,
+                             int32_t *counts, ygzorb_keypoint *keypoints, uint8_t *desc) {
+    Extractor *ex = (Extractor *)h;
+    int rc = checkFrames(ex, frames, n_frames, w, hgt, stride);
+    if (rc) return rc;
+    if (!grid_size || !n_exist || !counts || !keypoints || !desc || cap < 1) return argFail("null argument");
+    if (n_frames == 0) return 0;
+    if (w < 64 || hgt < 64) return argFail("image too small for the DSO keypoint grid");
+    if (n_frames > ex->maxBatch) return argFail("n_frames exceeds max_batch");
+    YGZ_CUDA(cudaSetDevice(ex->device));
+    const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
+    if (frame_stride == 0) frame_stride = (size_t)stride * hgt;
+    if ((rc = ensureGeometry(ex, w, hgt, inDev ? stride : w, n_frames, inDev))) return rc;
+    const int nfeat = ex->params.nfeatures;
+    // ---- host-side state of the while (cnt < n) loop (src/ORBextractor.cc:1295-1376), one entry per frame
+    std::vector<int32_t> state(n_frames), used(n_frames), cnt(n_frames, 0), nE(n_frames);
+    std::vector<uint8_t> active(n_frames, 1);
+    int maxExist = 0;
+    for (int f = 0; f < n_frames; f++) {
+        state[f] = grid_size[f] < 0 ? (int)std::sqrt(1.0 * hgt * w / nfeat) : grid_size[f];   // :1295-1296
+        if (state[f] < 7 || state[f] > kDsoMaxGrid) return argFail("grid size outside 7..96 (nfeatures too small for this image?)");
+        if (n_exist[f] < 0 || n_exist[f] > cap) return argFail("n_exist outside 0..cap");
+        nE[f] = n_exist[f]; maxExist = std::max(maxExist, nE[f]);
+    }
+    const int maxCells = (hgt / 7) * (w / 7);
+    const int occPitch = (w + 31) / 32;
+    const size_t nb = (size_t)n_frames;
+    if ((rc = growBuf(ex->dsoOcc, ex->dsoOccBytes, nb * occPitch * hgt * 4))) return rc;
+    if ((rc = growBuf(ex->dsoCellKp, ex->dsoCellKpBytes, nb * maxCells * 3 * 4))) return rc;
+    if ((rc = growBuf(ex->dsoCellCnt, ex->dsoCellCntBytes, nb * maxCells))) return rc;
+    if ((rc = growBuf(ex->dsoSmall, ex->dsoSmallBytes, (size_t)ex->maxBatch * 20))) return rc;
+    if ((rc = growBuf(ex->dsoCentre, ex->dsoCentreBytes, nb * cap * sizeof(int4)))) return rc;
+    if (!outDev) {
+        if ((rc = growBuf(ex->dsoKps, ex->dsoKpsBytes, nb * cap * sizeof(ygzorb_keypoint)))) return rc;
+        if ((rc = growBuf(ex->dsoDesc, ex->dsoDescBytes, nb * cap * 32))) return rc;
+    }
+    int32_t *dGrid = ex->dsoSmall, *dNE = dGrid + ex->maxBatch, *dTotal = dNE + ex->maxBatch, *dCounts = dTotal + ex->maxBatch;
+    uint8_t *dActive = (uint8_t *)(dCounts + ex->maxBatch);
+    ygzorb_keypoint *dKps = outDev ? keypoints : ex->dsoKps;
+    uint8_t *dDesc = outDev ? desc : ex->dsoDesc;
+    int32_t *dCnt = outDev ? counts : dCounts;
+    cudaStream_t st = ex->stream;
+    // ---- level 0, pyramid and blurred pyramid (Frame::ComputeImagePyramid + :1080-1084)
+    int slot = 0;
+    if (!inDev && (rc = uploadInput(ex, frames, n_frames, w, hgt, stride, frame_stride, &slot))) return rc;
+    if ((rc = bindInput(ex, frames, w, hgt, frame_stride, inDev, slot))) return rc;
+    runPyramid(ex, n_frames);
+    ex->launches += launchBlur(ex->G, ex->B, n_frames, st);
+    if (!outDev)
+        for (int f = 0; f < n_frames; f++)
+            if (nE[f]) YGZ_CUDA(cudaMemcpyAsync(dKps + (size_t)f * cap, keypoints + (size_t)f * cap, (size_t)nE[f] * sizeof(ygzorb_keypoint),
+                                                cudaMemcpyHostToDevice, st));
+    YGZ_CUDA(cudaMemcpyAsync(dNE, nE.data(), nb * 4, cudaMemcpyHostToDevice, st));
+    DsoArgs A;
+    memset(&A, 0, sizeof A);
+    A.nFrames = n_frames; A.w = w; A.h = hgt; A.pitch = ex->G.lv[0].pitch; A.nlevels = ex->G.nlevels; A.cap = cap;
+    A.frameStride = ex->B.inFrameStride; A.img = ex->B.in;
+    A.grid = dGrid; A.active = dActive; A.nExist = dNE; A.kps = dKps;
+    A.occ = ex->dsoOcc; A.occPitch = occPitch; A.occWords = (long long)occPitch * hgt;
+    A.maxCells = maxCells; A.cellKp = ex->dsoCellKp; A.cellCnt = ex->dsoCellCnt; A.total = dTotal; A.counts = dCnt;
+    A.centre = ex->dsoCentre;
+    for (int l = 0; l < ex->G.nlevels; l++) A.invScale[l] = ex->tables.invScale[l];
+    YGZ_CUDA(cudaMemsetAsync(ex->dsoOcc, 0, nb * occPitch * hgt * 4, st));
+    ex->launches += launchDsoOccupancy(A, maxExist, st);
+    // ---- shrink the grid until a frame has its nfeatures corners (or the grid bottoms out at 7)
+    std::vector<int32_t> total(n_frames);
+    for (;;) {
+        int maxGrid = 0, maxCellsNow = 0, nActive = 0;
+        for (int f = 0; f < n_frames; f++)
+            if (active[f]) {
+                used[f] = state[f];
+                maxGrid = std::max(maxGrid, state[f]);
+                maxCellsNow = std::max(maxCellsNow, (hgt / state[f]) * (w / state[f]));
+                nActive++;
+            }
+        if (!nActive) break;
+        YGZ_CUDA(cudaMemcpyAsync(dGrid, used.data(), nb * 4, cudaMemcpyHostToDevice, st));
+        YGZ_CUDA(cudaMemcpyAsync(dActive, active.data(), nb, cudaMemcpyHostToDevice, st));
+        YGZ_CUDA(cudaMemsetAsync(dTotal, 0, nb * 4, st));
+        ex->launches += launchDsoCells(A, maxGrid, maxCellsNow, st);
+        YGZ_CUDA(cudaMemcpyAsync(total.data(), dTotal, nb * 4, cudaMemcpyDeviceToHost, st));
+        YGZ_CUDA(cudaStreamSynchronize(st));
+        for (int f = 0; f < n_frames; f++) {
+            if (!active[f]) continue;
+            cnt[f] = total[f];
+            // cnt == 0 would repeat the same grid forever in the reference (:1301 shrinks only when cnt > 0): stop instead
+            if (cnt[f] >= nfeat || cnt[f] == 0) { active[f] = 0; continue; }
+            state[f] -= 5;
+            if (state[f] < 7) { state[f] = 7; active[f] = 0; }      // :1303-1307: keeps the keypoints of the previous grid
+        }
+    }
+    for (int f = 0; f < n_frames; f++) {
+        if (cnt[f] > nfeat) state[f] += 5;                          // :1378-1380
+        grid_size[f] = state[f];
+    }
+    YGZ_CUDA(cudaMemcpyAsync(dGrid, used.data(), nb * 4, cudaMemcpyHostToDevice, st));
+    ex->launches += launchDsoAssemble(A, st);
+    ex->launches += launchDescribeList(ex->G, ex->B, n_frames, cap, ex->dsoCentre, dCnt, dKps, dDesc, st);
+    if (!inDev) YGZ_CUDA(cudaEventRecord(ex->inFree[slot], st));
+    if (!outDev) {
+        YGZ_CUDA(cudaMemcpyAsync(counts, dCnt, nb * 4, cudaMemcpyDeviceToHost, st));
+        YGZ_CUDA(cudaStreamSynchronize(st));
+        for (int f = 0; f < n_frames; f++) {
+            const size_t c = (size_t)std::min(counts[f], cap);
+            if (!c) continue;
+            YGZ_CUDA(cudaMemcpyAsync(keypoints + (size_t)f * cap, dKps + (size_t)f * cap, c * sizeof(ygzorb_keypoint), cudaMemcpyDeviceToHost, st));
+            YGZ_CUDA(cudaMemcpyAsync(desc + (size_t)f * cap * 32, dDesc + (size_t)f * cap * 32, c * 32, cudaMemcpyDeviceToHost, st));
+        }
+    }
+    YGZ_CUDA(cudaGetLastError());
+    ex->lastFrames = n_frames; ex->stagesValid = false;
+    YGZ_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
 

@@ -45,6 +45,8 @@ def lib():
         L.ygzorb_extractor_destroy.argtypes = [C.c_void_p]
         L.ygzorb_extract_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t,
                                            C.c_uint, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ygzorb_extract_dso_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_uint,
+                                               C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ygzorb_compute_pyramid_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                                    C.c_size_t, C.c_uint]
         _lib = L
@@ -123,6 +125,27 @@ class Extractor:
         """Pointer-level call (device or pinned buffers owned by the caller)."""
         check(lib().ygzorb_extract_batch(self.h, C.c_void_p(ptr), n, w, h, stride, frame_stride, flags, cap,
                                          C.c_void_p(counts_ptr), C.c_void_p(kps_ptr), C.c_void_p(desc_ptr)))
+
+    def extract_dso(self, frames, exist=None, grid=None, cap=None):
+        """DSO_KEYPOINT method on independent frames: exist = list of KP_DTYPE arrays (frame->mvKeys on entry) or None,
+        grid = list of mnGridSize values before each frame (-1: uninitialised).
+        Returns (list of (kps, desc) per frame, list of mnGridSize after each frame)."""
+        frames = np.ascontiguousarray(frames, np.uint8)
+        if frames.ndim == 2:
+            frames = frames[None]
+        n, h, w = frames.shape
+        exist = exist if exist is not None else [np.zeros(0, KP_DTYPE)] * n
+        n_exist = np.array([len(e) for e in exist], np.int32)
+        g = np.array(grid if grid is not None else [-1] * n, np.int32)
+        cap = cap or int(n_exist.max()) + 3 * (h // 7) * (w // 7)
+        counts = np.zeros(n, np.int32)
+        kps = np.zeros((n, cap), KP_DTYPE)
+        desc = np.zeros((n, cap, 32), np.uint8)
+        for i, e in enumerate(exist):
+            kps[i, :len(e)] = e
+        check(lib().ygzorb_extract_dso_batch(self.h, _p(frames), n, w, h, w, w * h, 0, _p(g), _p(n_exist), cap, _p(counts),
+                                             _p(kps), _p(desc)))
+        return [(kps[i, :counts[i]].copy(), desc[i, :counts[i]].copy()) for i in range(n)], g.tolist()
 
     def compute_pyramid(self, frames, flags=0):
         frames = np.ascontiguousarray(frames, np.uint8)

@@ -49,3 +49,33 @@ def run_ref(frames, nfeatures=1000, scale=1.2, levels=8, ini=20, mn=7, pyr=False
                 off += int(lw) * int(lh)
         outs.append({"kps": kps, "desc": desc, "pyr": pyrs})
     return outs, stats
+
+
+def run_ref_dso(frames, exist=None, nfeatures=1000, scale=1.2, levels=8, grid=-1):
+    """--dso mode: ONE extractor over the frames in order (mnGridSize carries over), DSO_KEYPOINT method on Frames that
+    already hold exist[i] (KP_DTYPE arrays).  Returns per frame {"kps", "desc", "grid_after"}."""
+    frames = np.ascontiguousarray(frames, np.uint8)
+    if frames.ndim == 2:
+        frames = frames[None]
+    n, h, w = frames.shape
+    with tempfile.TemporaryDirectory() as td:
+        fin, fout, fex = os.path.join(td, "in.u8"), os.path.join(td, "out.bin"), os.path.join(td, "exist.bin")
+        frames.tofile(fin)
+        cmd = [REF_BIN, "--in", fin, "--w", str(w), "--h", str(h), "--n", str(n), "--nfeatures", str(nfeatures),
+               "--scale", repr(float(scale)), "--levels", str(levels), "--out", fout, "--dso", "--grid", str(grid)]
+        if exist is not None:
+            with open(fex, "wb") as f:
+                for e in exist:
+                    np.array([len(e)], np.int32).tofile(f)
+                    np.ascontiguousarray(e, KP_DTYPE).tofile(f)
+            cmd += ["--exist", fex]
+        subprocess.run(cmd, capture_output=True, text=True, check=True)
+        buf = open(fout, "rb").read()
+    outs, off = [], 0
+    for _ in range(n):
+        cnt = int(np.frombuffer(buf, "<i4", 1, off)[0]); off += 4
+        kps = np.frombuffer(buf, KP_DTYPE, cnt, off).copy(); off += 28 * cnt
+        desc = np.frombuffer(buf, np.uint8, 32 * cnt, off).reshape(cnt, 32).copy(); off += 32 * cnt
+        g = int(np.frombuffer(buf, "<i4", 1, off)[0]); off += 4
+        outs.append({"kps": kps, "desc": desc, "grid_after": g})
+    return outs
