@@ -73,10 +73,35 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
 
 void ORBextractor::operator()(Frame *frame, std::vector<cv::KeyPoint> &_keypoints, cv::OutputArray _descriptors,
                               KeyPointMethod method, bool leftEye) {
+    if (method == DSO_KEYPOINT && leftEye) {
+        // :1052-1058 + :1079-1125: grid FAST-10 / Shi-Tomasi keypoints on level 0 next to the keypoints direct tracking left in
+        // frame->mvKeys, orientation and descriptors for both (Frame::ExtractORB, src/Frame.cc:335-337)
+        const cv::Mat &img = frame->mvImagePyramid[0];
+        mvImagePyramid = frame->mvImagePyramid;                       // :1039
+        const int nExist = frame->N;
+        const int cap = nExist + 3 * (img.rows / 7) * (img.cols / 7);
+        mKpBuf.resize(cap); mDescBuf.resize((size_t)cap * 32);
+        if (nExist) std::memcpy((void *)mKpBuf.data(), frame->mvKeys.data(), (size_t)nExist * sizeof(ygzorb_keypoint));
+        int32_t n = 0, ne = nExist;
+        if (ygzorb_extract_dso_batch(mHandle, img.data, 1, img.cols, img.rows, (int)img.step, 0, 0, &mnGridSize, &ne, cap, &n,
+                                     mKpBuf.data(), mDescBuf.data()) != 0)
+            fail("ygzorb_extract_dso_batch");
+        const cv::KeyPoint *rec = (const cv::KeyPoint *)mKpBuf.data();
+        for (int i = 0; i < nExist; i++) frame->mvKeys[i].angle = rec[i].angle;      // :1383-1385
+        const bool same = &_keypoints == &frame->mvKeys;
+        const size_t before = _keypoints.size();
+        _keypoints.insert(_keypoints.end(), rec + nExist, rec + n);                   // :1124
+        const int rows = (int)(same ? _keypoints.size() : before + (size_t)(n - nExist));
+        if (rows == 0) { _descriptors.release(); return; }
+        _descriptors.create(rows, 32, cv::CV_8U);
+        cv::Mat descriptors = _descriptors.getMat();
+        for (int i = 0; i < std::min(rows, (int)n); i++) std::memcpy(descriptors.ptr(i), &mDescBuf[(size_t)i * 32], 32);
+        return;
+    }
     if (method != ORBSLAM_KEYPOINT || frame->N > 0) {
-        // FAST_KEYPOINT / DSO_KEYPOINT (:1040-1056) and descriptors for pre-existing keys (:1088-1099)
-        // are the "next" row f3 of SURVEY.md §8(f): not on the named path, not built yet.
-        std::fprintf(stderr, "ygz::ORBextractor: only ORBSLAM_KEYPOINT on a fresh Frame is implemented on the GPU path\n");
+        // FAST_KEYPOINT (:1045-1051, the fixed 5-px grid variant) and ORBSLAM_KEYPOINT on a Frame that already holds keypoints
+        // are not built.
+        std::fprintf(stderr, "ygz::ORBextractor: FAST_KEYPOINT and ORBSLAM_KEYPOINT on a non-empty Frame are not implemented on the GPU path\n");
         _keypoints.clear();
         _descriptors.release();
         return;

@@ -28,7 +28,8 @@ public:
     // :71-75 — ORB on an image; the mask is ignored, as in the reference.
     void operator()(cv::InputArray image, cv::InputArray mask, std::vector<cv::KeyPoint> &keypoints,
                     cv::OutputArray descriptors);
-    // :79-85 — the Frame overload (ORBSLAM_KEYPOINT branch, src/ORBextractor.cc:1031-1127).
+    // :79-85 — the Frame overload (src/ORBextractor.cc:1031-1127): ORBSLAM_KEYPOINT on a fresh Frame, DSO_KEYPOINT on a
+    // Frame holding the keypoints of direct tracking.
     void operator()(Frame *frame, std::vector<cv::KeyPoint> &keypoints, cv::OutputArray descriptors,
                     KeyPointMethod method, bool leftEye = true);
     // :114 — fills mvImagePyramid (continuous host images, as Frame clones them, src/Frame.cc:810-813).
@@ -55,6 +56,7 @@ protected:
     std::vector<int> mnFeaturesPerLevel;
     std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
     ygzorb_extractor *mHandle;
+    int32_t mnGridSize = -1;                              // :191, dynamic grid size of the DSO keypoint mode
     std::vector<ygzorb_keypoint> mKpBuf;
     std::vector<uint8_t> mDescBuf;
 };

@@ -109,6 +109,20 @@ int main(int argc, char **argv) {
     int32_t nml = nmatchesLast;
     wr(fo, &nml, 1);
     for (int i = 0; i < nL; i++) { int32_t idx = F.mvpMapPoints[i] ? (int32_t)(F.mvpMapPoints[i] - lastMps.data()) : -1; wr(fo, &idx, 1); }
+    {   // Frame::ExtractORB on a frame that comes out of direct tracking (src/Frame.cc:335-337): every 7th keypoint of the
+        // ORB extraction plays the tracked features, two consecutive frames share the extractor's grid size
+        for (int rep = 0; rep < 2; rep++) {
+            Frame D;
+            D.mvImagePyramid = F.mvImagePyramid;
+            for (int i = 0; i < nL; i += 7) D.mvKeys.push_back(F.mvKeys[i]);
+            D.N = (int)D.mvKeys.size();
+            cv::Mat dd;
+            exL(&D, D.mvKeys, dd, ORBextractor::DSO_KEYPOINT, true);
+            int32_t nd = (int32_t)D.mvKeys.size();
+            wr(fo, &nd, 1); wr(fo, D.mvKeys.data(), nd);
+            for (int i = 0; i < nd; i++) wr(fo, dd.ptr(i), 32);
+        }
+    }
     fclose(fo);
     if (argc >= 5) {
         ORBVocabulary voc;

@@ -9,6 +9,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "ygz_ref_orb")
 
+LAST_STATS = None   # the JSON line of the last run_ref_dso call (frames, seconds: processing only)
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
                      ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
 
@@ -69,7 +70,9 @@ def run_ref_dso(frames, exist=None, nfeatures=1000, scale=1.2, levels=8, grid=-1
                     np.array([len(e)], np.int32).tofile(f)
                     np.ascontiguousarray(e, KP_DTYPE).tofile(f)
             cmd += ["--exist", fex]
-        subprocess.run(cmd, capture_output=True, text=True, check=True)
+        res = subprocess.run(cmd, capture_output=True, text=True, check=True)
+        global LAST_STATS
+        LAST_STATS = json.loads(res.stdout.strip().splitlines()[-1])
         buf = open(fout, "rb").read()
     outs, off = [], 0
     for _ in range(n):

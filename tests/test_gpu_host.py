@@ -74,6 +74,14 @@ def test_host_classes_end_to_end():
     gnml = int(take("<i4", 1)[0]); gassign_last = take("<i4", nL)
     nml, kp_to_pt, _ = O.search_by_projection_last(kl, dl, None, None, (0.0, 0.0, float(w), float(h)), sf, last, 15.0, True, True, True)
     assert gnml == nml and np.array_equal(gassign_last, kp_to_pt) and nml > 300
+    # DSO_KEYPOINT through the host class == the reference's own code on the same stream of two frames
+    import refcli
+    if refcli.available():
+        exist = kl[::7].copy()
+        want_dso = refcli.run_ref_dso(np.stack([left, left]), [exist, exist], nfeatures=nf)
+        for k in range(2):
+            nd = int(take("<i4", 1)[0]); gk = take(Y.KP_DTYPE, nd); gd = take(np.uint8, nd * 32).reshape(nd, 32)
+            assert gk.tobytes() == want_dso[k]["kps"].tobytes() and np.array_equal(gd, want_dso[k]["desc"]) and nd > len(exist) + 300
     # ORBVocabulary::transform through the host class == the oracle (pinned to DBoW2) on the same descriptors
     want = ovoc.transform(dl, 4)
     nb = int(np.frombuffer(bowbuf, "<i4", 1, 0)[0])

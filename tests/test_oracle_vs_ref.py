@@ -83,3 +83,20 @@ def test_reference_multithreaded_batch_is_deterministic():
     for f in range(len(frames)):
         assert kps[f, :counts[f]].tobytes() == a[f]["kps"].tobytes()
         assert np.array_equal(desc[f, :counts[f]], a[f]["desc"])
+
+
+@needs_ref
+@pytest.mark.parametrize("name", ["dso_euroc752", "dso_mixed640"])
+def test_reference_dso_mode_reproduces_golden(name):
+    """The DSO_KEYPOINT goldens (tools/make_golden_dso.py) are what the reference binary produces today."""
+    g = np.load(golden_cases.GOLDEN_DIR + "/" + name + ".npz")
+    mk = synth.textured_frame if int(g["textured"]) else synth.mixed_frame
+    frames = np.stack([mk(int(g["w"]), int(g["h"]), int(g["seed"]) + k) for k in range(3)])
+    assert [zlib.crc32(f.tobytes()) for f in frames] == g["frame_crc32"].tolist()
+    exist = [g["exist_%d" % k].view(refcli.KP_DTYPE).reshape(-1) for k in range(3)]
+    outs = refcli.run_ref_dso(frames, exist, nfeatures=int(g["nfeatures"]))
+    for k in range(3):
+        assert outs[k]["kps"].tobytes() == g["kps_%d" % k].tobytes() and np.array_equal(outs[k]["desc"], g["desc_%d" % k])
+        assert outs[k]["grid_after"] == int(g["grid_after"][k])
+        new = outs[k]["kps"][len(exist[k]):]
+        assert (new["octave"] == 0).all() and (new["size"] == 7).all() and len(new) > 500
