@@ -86,6 +86,14 @@ int ygzorb_extract_batch(ygzorb_extractor *ex, const uint8_t *frames, int n_fram
                          size_t frame_stride, unsigned flags, int cap, int32_t *counts,
                          ygzorb_keypoint *keypoints, uint8_t *desc);
 
+/* The undistortion in front of the pyramid, Frame::ComputeImagePyramid (src/Frame.cc:775-805): cv::remap(mImGray, dst, map1,
+ * map2, cv::INTER_LINEAR) with the fixed-point maps cv::initUndistortRectifyMap(..., CV_16SC2, map1, map2) gives (map1: w*h
+ * pairs of int16 (x, y); map2: w*h uint16 interpolation-table indices; HOST pointers, copied).  Once set, every frame given to
+ * ygzorb_extract_batch / ygzorb_compute_pyramid_batch / ygzorb_extract_dso_batch (which must be w x h) is remapped on the
+ * device first — bit-exact with OpenCV's 8-bit remapBilinear, border value 0 — and level 0 of the pyramid is the undistorted
+ * image (ygzorb_get_pyramid_level(.., 0, ..) returns it, what Frame keeps as mImGray).  map1 == NULL removes the maps. */
+int ygzorb_extractor_set_undistort_maps(ygzorb_extractor *ex, const int16_t *map1, const uint16_t *map2, int w, int h);
+
 /* ORBextractor::operator()(Frame *frame, vector<KeyPoint> &_keypoints, OutputArray _descriptors, DSO_KEYPOINT, leftEye = true)
  * (src/ORBextractor.cc:1031-1127 with :1052-1058) as Frame::ExtractORB calls it on frames that come out of direct tracking
  * (src/Frame.cc:335-337): ComputeKeyPointsDSOSingleLevel (:1275-1386) — cells of mnGridSize pixels on level 0, FAST-10

@@ -471,6 +471,27 @@ YGZO_API void ygzo_resize(const unsigned char *src, int sw, int sh, int sstride,
     cv::resize(wrap(src, sw, sh, sstride), d, cv::Size(dw, dh), 0, 0, cv::INTER_LINEAR);
     packTo(d, dst);
 }
+// cv::remap(src, dst, map1 CV_16SC2, map2 CV_16UC1, INTER_LINEAR), BORDER_CONSTANT 0, 8UC1 — the undistortion of
+// Frame::ComputeImagePyramid (src/Frame.cc:775-790) — restated from OpenCV's fixed-point remapBilinear: 5 fractional bits per
+// axis, bilinear weights of 15 bits summing to 1 << 15 ((32-fx)(32-fy)*32, ...), FixedPtCast (sum + (1 << 14)) >> 15; a tap
+// outside the source is the border value.  tests/test_minicv_vs_cv2.py checks it against cv2.remap.
+YGZO_API void ygzo_remap_u8(const unsigned char *src, int w, int h, int stride, const short *map1, const unsigned short *map2,
+                            int dw, int dh, unsigned char *dst) {
+    for (int y = 0; y < dh; y++)
+        for (int x = 0; x < dw; x++) {
+            const size_t o = (size_t)y * dw + x;
+            const int sx = map1[2 * o], sy = map1[2 * o + 1], idx = map2[o] & 1023, fx = idx & 31, fy = idx >> 5;
+            const int wt[4] = {(32 - fx) * (32 - fy) * 32, fx * (32 - fy) * 32, (32 - fx) * fy * 32, fx * fy * 32};
+            int acc = 0;
+            for (int k = 0; k < 4; k++) {
+                const int xx = sx + (k & 1), yy = sy + (k >> 1);
+                const int p = (xx >= 0 && xx < w && yy >= 0 && yy < h) ? src[(size_t)yy * stride + xx] : 0;
+                acc += wt[k] * p;
+            }
+            dst[o] = (unsigned char)((acc + (1 << 14)) >> 15);
+        }
+}
+
 YGZO_API void ygzo_blur7(const unsigned char *src, int w, int h, int stride, unsigned char *dst) {
     cv::Mat d;
     cv::GaussianBlur(wrap(src, w, h, stride), d, cv::Size(7, 7), 2, 2, cv::BORDER_REFLECT_101);

@@ -1022,6 +1022,50 @@ int launchDescribeList(const FrameGeom &G, const DevBuffers &B, int nFrames, int
     return 1;
 }
 
+// K0 — cv::remap(src, dst, map1 (CV_16SC2), map2 (CV_16UC1), INTER_LINEAR), BORDER_CONSTANT 0, 8UC1: the undistortion of
+// Frame::ComputeImagePyramid (src/Frame.cc:775-805) in front of the pyramid.  Fixed point as OpenCV's remapBilinear: 5
+// fractional bits per axis in map2, weights (32-fx)(32-fy)*32 ... summing to 1 << 15, result (sum + (1 << 14)) >> 15; a tap
+// outside the source reads the border value 0.  Thread = 4 consecutive destination pixels.
+__global__ void __launch_bounds__(256) k_remap(const uint8_t *src, long long srcFrameStride, int srcPitch, int w, int h,
+                                               const short2 *map1, const uint16_t *map2, uint8_t *dst) {
+    const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4, y = blockIdx.y, f = blockIdx.z;
+    if (x0 >= w) return;
+    const uint8_t *S = src + (long long)f * srcFrameStride;
+    uint8_t *D = dst + ((long long)f * h + y) * w;
+    const long long mo = (long long)y * w + x0;
+    unsigned packed = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        if (x0 + k >= w) break;
+        const short2 m = map1[mo + k];
+        const int idx = map2[mo + k] & 1023, fx = idx & 31, fy = idx >> 5;
+        const int sx = m.x, sy = m.y;
+        int p00 = 0, p01 = 0, p10 = 0, p11 = 0;
+        if ((unsigned)sx < (unsigned)(w - 1) && (unsigned)sy < (unsigned)(h - 1)) {
+            const uint8_t *r = S + (long long)sy * srcPitch + sx;
+            p00 = r[0]; p01 = r[1]; p10 = r[srcPitch]; p11 = r[srcPitch + 1];
+        } else {
+            const bool xa = (unsigned)sx < (unsigned)w, xb = (unsigned)(sx + 1) < (unsigned)w;
+            const bool ya = (unsigned)sy < (unsigned)h, yb = (unsigned)(sy + 1) < (unsigned)h;
+            if (ya && xa) p00 = S[(long long)sy * srcPitch + sx];
+            if (ya && xb) p01 = S[(long long)sy * srcPitch + sx + 1];
+            if (yb && xa) p10 = S[(long long)(sy + 1) * srcPitch + sx];
+            if (yb && xb) p11 = S[(long long)(sy + 1) * srcPitch + sx + 1];
+        }
+        const int acc = ((32 - fx) * p00 + fx * p01) * (32 - fy) + ((32 - fx) * p10 + fx * p11) * fy;   // weights / 32
+        packed |= (unsigned)((acc * 32 + (1 << 14)) >> 15) << (8 * k);
+    }
+    if (x0 + 3 < w && (w & 3) == 0) *reinterpret_cast<unsigned *>(D + x0) = packed;
+    else for (int k = 0; k < 4 && x0 + k < w; k++) D[x0 + k] = (uint8_t)(packed >> (8 * k));
+}
+
+int launchRemap(const uint8_t *src, long long srcFrameStride, int srcPitch, int w, int h, int nFrames, const short2 *map1,
+                const uint16_t *map2, uint8_t *dst, cudaStream_t s) {
+    if (nFrames <= 0) return 0;
+    k_remap<<<dim3((w + 1023) / 1024, h, nFrames), 256, 0, s>>>(src, srcFrameStride, srcPitch, w, h, map1, map2, dst);
+    return 1;
+}
+
 static bool gConfigured[64];
 
 int configureKernels() {

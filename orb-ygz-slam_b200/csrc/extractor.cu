@@ -265,6 +265,10 @@ struct Extractor {
     size_t outCap = 0;  // records per frame the dOut* buffers hold
     int lastFrames = 0; bool lastInDevice = false; bool stagesValid = false;
     const uint8_t *lastIn = nullptr; long long lastInFrameStride = 0;
+    // undistortion in front of the pyramid (ygzorb_extractor_set_undistort_maps)
+    short2 *dMap1 = nullptr; uint16_t *dMap2 = nullptr; size_t map1Bytes = 0, map2Bytes = 0;
+    int mapW = 0, mapH = 0;
+    uint8_t *dUndist = nullptr; size_t undistBytes = 0;
     // DSO keypoint mode (ygzorb_extract_dso_batch): workspace grown on demand
     uint32_t *dsoOcc = nullptr; size_t dsoOccBytes = 0;
     uint32_t *dsoCellKp = nullptr; size_t dsoCellKpBytes = 0;
@@ -372,6 +376,16 @@ static int bindInput(Extractor *ex, const uint8_t *frames, int w, int h, size_t 
     return 0;
 }
 
+// cv::remap of the bound level 0 into the extractor's own buffer (Frame::ComputeImagePyramid, src/Frame.cc:775-790), when maps are set
+static int applyUndistort(Extractor *ex, int n, int w, int h, int srcPitch) {
+    if (!ex->dMap1) return 0;
+    if (w != ex->mapW || h != ex->mapH) { setError("image size differs from the undistortion maps"); return YGZORB_E_ARG; }
+    if (int rc = growBuf(ex->dUndist, ex->undistBytes, (size_t)ex->maxBatch * w * h + 64)) return rc;
+    ex->launches += launchRemap(ex->B.in, ex->B.inFrameStride, srcPitch, w, h, n, ex->dMap1, ex->dMap2, ex->dUndist, ex->stream);
+    ex->B.in = ex->dUndist; ex->B.inFrameStride = (long long)w * h;
+    return 0;
+}
+
 static int runPyramid(Extractor *ex, int n) {
     for (int l = 1; l < ex->G.nlevels; l++) ex->launches += launchResizeLevel(ex->G, ex->B, l, n, ex->stream);
     return 0;
@@ -380,12 +394,13 @@ static int runPyramid(Extractor *ex, int n) {
 #define YGZ_MARK(i) do { if (ex->profiling) YGZ_CUDA(cudaEventRecord(ex->ev[i], ex->stream)); } while (0)
 
 // Kernels of one chunk (its input already uploaded into `slot` when it comes from the host).
-static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int h, size_t frameStride,
+static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int h, size_t frameStride, int srcPitch,
                         unsigned flags, int cap, int slot, int32_t *counts, ygzorb_keypoint *kps, uint8_t *desc) {
     const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
     int rc;
     YGZ_MARK(0);
     if ((rc = bindInput(ex, frames, w, h, frameStride, inDev, slot))) return rc;
+    if ((rc = applyUndistort(ex, n, w, h, srcPitch))) return rc;
     YGZ_CUDA(cudaMemsetAsync(ex->dCounts, 0, (2 * (size_t)ex->maxBatch * kMaxLevels + 1) * sizeof(int), ex->stream));
     YGZ_MARK(1);
     runPyramid(ex, n);
@@ -508,7 +523,8 @@ void ygzorb_extractor_destroy(ygzorb_extractor *h) {
     for (cudaStream_t st : streams) if (st) cudaStreamSynchronize(st);
     void *bufs[] = {ex->dIn[0], ex->dIn[1], ex->dPyr, ex->dBlur, ex->dTabs, ex->dCand, ex->dNodeOf, ex->dKept, ex->dCounts,
                     ex->dOutCounts[0], ex->dOutCounts[1], ex->dOutKps[0], ex->dOutKps[1], ex->dOutDesc[0], ex->dOutDesc[1],
-                    ex->dsoOcc, ex->dsoCellKp, ex->dsoCellCnt, ex->dsoSmall, ex->dsoCentre, ex->dsoKps, ex->dsoDesc};
+                    ex->dsoOcc, ex->dsoCellKp, ex->dsoCellCnt, ex->dsoSmall, ex->dsoCentre, ex->dsoKps, ex->dsoDesc,
+                    ex->dMap1, ex->dMap2, ex->dUndist};
     for (void *p : bufs) if (p) cudaFree(p);
     for (int i = 0; i < 8; i++) if (ex->ev[i]) cudaEventDestroy(ex->ev[i]);
     for (int sl = 0; sl < 2; sl++) {
@@ -589,7 +605,7 @@ int ygzorb_extract_batch(ygzorb_extractor *h, const uint8_t *frames, int n_frame
     // taps cover every frame of the call.
     int chunk = ex->maxBatch;
     if (!inDev && !(flags & YGZORB_KEEP_STAGES) && !ex->profiling && ex->pipeFrames > 0) chunk = std::min(chunk, ex->pipeFrames);
-    if ((rc = ensureGeometry(ex, w, hgt, inDev ? stride : w, std::min(chunk, n_frames), inDev))) return rc;
+    if ((rc = ensureGeometry(ex, w, hgt, (inDev && !ex->dMap1) ? stride : w, std::min(chunk, n_frames), inDev))) return rc;
     if (cap < ex->G.keptCap) { setError("cap is smaller than ygzorb_extractor_max_keypoints()"); return YGZORB_E_CAPACITY; }
     if (!outDev && (rc = ensureOut(ex, cap))) return rc;
     int slot = 0, nextSlot = 0;
@@ -601,7 +617,7 @@ int ygzorb_extract_batch(ygzorb_extractor *h, const uint8_t *frames, int n_frame
             const int n2 = std::min(chunk, n_frames - f0 - n);
             if ((rc = uploadInput(ex, frames + (size_t)(f0 + n) * frame_stride, n2, w, hgt, stride, frame_stride, &nextSlot))) return rc;
         }
-        rc = extractChunk(ex, frames + (size_t)f0 * frame_stride, n, w, hgt, frame_stride, flags, cap, slot,
+        rc = extractChunk(ex, frames + (size_t)f0 * frame_stride, n, w, hgt, frame_stride, inDev ? stride : w, flags, cap, slot,
                           counts + f0, keypoints + (size_t)f0 * cap, desc + (size_t)f0 * cap * 32);
         if (rc) return rc;
     }
@@ -622,7 +638,7 @@ int ygzorb_extract_dso_batch(ygzorb_extractor *h, const uint8_t *frames, int n_f
     YGZ_CUDA(cudaSetDevice(ex->device));
     const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
     if (frame_stride == 0) frame_stride = (size_t)stride * hgt;
-    if ((rc = ensureGeometry(ex, w, hgt, inDev ? stride : w, n_frames, inDev))) return rc;
+    if ((rc = ensureGeometry(ex, w, hgt, (inDev && !ex->dMap1) ? stride : w, n_frames, inDev))) return rc;
     const int nfeat = ex->params.nfeatures;
     // ---- host-side state of the while (cnt < n) loop (src/ORBextractor.cc:1295-1376), one entry per frame
     std::vector<int32_t> state(n_frames), used(n_frames), cnt(n_frames, 0), nE(n_frames);
@@ -656,6 +672,7 @@ int ygzorb_extract_dso_batch(ygzorb_extractor *h, const uint8_t *frames, int n_f
     int slot = 0;
     if (!inDev && (rc = uploadInput(ex, frames, n_frames, w, hgt, stride, frame_stride, &slot))) return rc;
     if ((rc = bindInput(ex, frames, w, hgt, frame_stride, inDev, slot))) return rc;
+    if ((rc = applyUndistort(ex, n_frames, w, hgt, inDev ? stride : w))) return rc;
     runPyramid(ex, n_frames);
     ex->launches += launchBlur(ex->G, ex->B, n_frames, st);
     if (!outDev)
@@ -735,10 +752,11 @@ int ygzorb_compute_pyramid_batch(ygzorb_extractor *h, const uint8_t *frames, int
     YGZ_CUDA(cudaSetDevice(ex->device));
     if (frame_stride == 0) frame_stride = (size_t)stride * hgt;
     const bool inDev = flags & YGZORB_IN_DEVICE;
-    if ((rc = ensureGeometry(ex, w, hgt, inDev ? stride : w, n_frames, inDev))) return rc;
+    if ((rc = ensureGeometry(ex, w, hgt, (inDev && !ex->dMap1) ? stride : w, n_frames, inDev))) return rc;
     int slot = 0;
     if (!inDev && (rc = uploadInput(ex, frames, n_frames, w, hgt, stride, frame_stride, &slot))) return rc;
     if ((rc = bindInput(ex, frames, w, hgt, frame_stride, inDev, slot))) return rc;
+    if ((rc = applyUndistort(ex, n_frames, w, hgt, inDev ? stride : w))) return rc;
     runPyramid(ex, n_frames);
     if (!inDev) YGZ_CUDA(cudaEventRecord(ex->inFree[slot], ex->stream));
     YGZ_CUDA(cudaGetLastError());
@@ -821,6 +839,30 @@ int ygzorb_get_candidates(ygzorb_extractor *h, int frame, int level, int cap, in
         if (order_key) order_key[i] = tmp[i].y;
     }
     return n;
+}
+
+int ygzorb_extractor_set_undistort_maps(ygzorb_extractor *h, const int16_t *map1, const uint16_t *map2, int w, int hgt) {
+    Extractor *ex = (Extractor *)h;
+    if (!ex) return argFail("null extractor");
+    YGZ_CUDA(cudaSetDevice(ex->device));
+    YGZ_CUDA(cudaStreamSynchronize(ex->stream));
+    const bool had = ex->dMap1 != nullptr;
+    if (!map1 || !map2) {
+        if (ex->dMap1) cudaFree(ex->dMap1);
+        if (ex->dMap2) cudaFree(ex->dMap2);
+        ex->dMap1 = nullptr; ex->dMap2 = nullptr; ex->map1Bytes = ex->map2Bytes = 0; ex->mapW = ex->mapH = 0;
+    } else {
+        if (w < 2 || hgt < 2) return argFail("bad map size");
+        const size_t n = (size_t)w * hgt;
+        int rc;
+        if ((rc = growBuf(ex->dMap1, ex->map1Bytes, n * sizeof(short2)))) return rc;
+        if ((rc = growBuf(ex->dMap2, ex->map2Bytes, n * sizeof(uint16_t)))) return rc;
+        YGZ_CUDA(cudaMemcpy(ex->dMap1, map1, n * sizeof(short2), cudaMemcpyHostToDevice));
+        YGZ_CUDA(cudaMemcpy(ex->dMap2, map2, n * sizeof(uint16_t), cudaMemcpyHostToDevice));
+        ex->mapW = w; ex->mapH = hgt;
+    }
+    if (had != (ex->dMap1 != nullptr)) { ex->gw = -1; ex->stagesValid = false; }   // level-0 pitch changes: rebuild the geometry
+    return 0;
 }
 
 int ygzorb_extractor_sync(ygzorb_extractor *h) {

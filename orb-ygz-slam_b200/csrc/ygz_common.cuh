@@ -93,6 +93,8 @@ int launchQuadtree(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStr
 int launchBlur(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s);
 int launchDescribe(const FrameGeom &G, const DevBuffers &B, int nFrames, int cap, int32_t *counts,
                    ygzorb_keypoint *kps, uint8_t *desc, cudaStream_t s);
+int launchRemap(const uint8_t *src, long long srcFrameStride, int srcPitch, int w, int h, int nFrames, const short2 *map1,
+                const uint16_t *map2, uint8_t *dst, cudaStream_t s);
 size_t quadtreeSmemBytes(int listCap);
 int configureKernels();  // one-time cudaFuncSetAttribute calls
 

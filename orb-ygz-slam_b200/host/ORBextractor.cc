@@ -42,6 +42,13 @@ void ORBextractor::downloadPyramid(int w, int h) {
     }
 }
 
+void ORBextractor::SetUndistortMaps(const cv::Mat &map1, const cv::Mat &map2) {
+    const bool off = map1.empty() || map2.empty();
+    if (ygzorb_extractor_set_undistort_maps(mHandle, off ? nullptr : (const int16_t *)map1.data, off ? nullptr : (const uint16_t *)map2.data,
+                                            map2.cols, map2.rows) != 0)
+        fail("ygzorb_extractor_set_undistort_maps");
+}
+
 void ORBextractor::ComputePyramid(cv::Mat image) {
     if (image.empty()) return;
     if (ygzorb_compute_pyramid_batch(mHandle, image.data, 1, image.cols, image.rows, (int)image.step, 0, 0) != 0)

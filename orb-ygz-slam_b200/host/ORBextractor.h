@@ -32,6 +32,9 @@ public:
     // Frame holding the keypoints of direct tracking.
     void operator()(Frame *frame, std::vector<cv::KeyPoint> &keypoints, cv::OutputArray descriptors,
                     KeyPointMethod method, bool leftEye = true);
+    // New: the maps of Frame::ComputeImagePyramid (src/Frame.cc:776-784, CV_16SC2 + CV_16UC1, continuous).  Once set, every image
+    // handed to this extractor is remapped on the device first (:788) and mvImagePyramid[0] is the undistorted image.
+    void SetUndistortMaps(const cv::Mat &map1, const cv::Mat &map2);
     // :114 — fills mvImagePyramid (continuous host images, as Frame clones them, src/Frame.cc:810-813).
     void ComputePyramid(cv::Mat image);
 

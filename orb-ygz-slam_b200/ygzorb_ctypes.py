@@ -47,6 +47,7 @@ def lib():
                                            C.c_uint, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ygzorb_extract_dso_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_uint,
                                                C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ygzorb_extractor_set_undistort_maps.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
         L.ygzorb_compute_pyramid_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                                    C.c_size_t, C.c_uint]
         _lib = L
@@ -146,6 +147,14 @@ class Extractor:
         check(lib().ygzorb_extract_dso_batch(self.h, _p(frames), n, w, h, w, w * h, 0, _p(g), _p(n_exist), cap, _p(counts),
                                              _p(kps), _p(desc)))
         return [(kps[i, :counts[i]].copy(), desc[i, :counts[i]].copy()) for i in range(n)], g.tolist()
+
+    def set_undistort_maps(self, map1, map2):
+        """cv::initUndistortRectifyMap(..., CV_16SC2) maps ((h, w, 2) int16, (h, w) uint16); None, None removes them."""
+        if map1 is None:
+            check(lib().ygzorb_extractor_set_undistort_maps(self.h, None, None, 0, 0))
+            return
+        m1 = np.ascontiguousarray(map1, np.int16); m2 = np.ascontiguousarray(map2, np.uint16)
+        check(lib().ygzorb_extractor_set_undistort_maps(self.h, _p(m1), _p(m2), m2.shape[1], m2.shape[0]))
 
     def compute_pyramid(self, frames, flags=0):
         frames = np.ascontiguousarray(frames, np.uint8)

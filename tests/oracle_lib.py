@@ -103,6 +103,15 @@ def cossin(a):
     return c, s
 
 
+def remap(img, map1, map2):
+    img, w, h = _img(img)
+    m1 = np.ascontiguousarray(map1, np.int16); m2 = np.ascontiguousarray(map2, np.uint16)
+    dh, dw = m2.shape
+    out = np.zeros((dh, dw), np.uint8)
+    lib().ygzo_remap_u8(_p(img), w, h, w, _p(m1), _p(m2), dw, dh, _p(out))
+    return out
+
+
 def pyramid(p, img):
     img, w, h = _img(img)
     sizes = level_sizes(p, w, h)

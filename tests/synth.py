@@ -319,3 +319,18 @@ def knn_case(nq, nt, seed):
     noise = np.packbits((rng.uniform(size=(half, 256)) < 0.1).astype(np.uint8), axis=1, bitorder="little")
     query[:half] = train[src] ^ noise
     return query, train
+
+
+def undistort_maps(w, h, k1=-0.28, k2=0.07):
+    """Fixed-point remap maps of the CV_16SC2 / CV_16UC1 kind (integer source position + 5-bit fractions packed as
+    fy * 32 + fx) for a radial distortion model; part of the border maps outside the source image."""
+    fx, fy, cx, cy = 0.61 * w, 0.95 * h, 0.49 * w, 0.52 * h
+    xs, ys = np.meshgrid(np.arange(w, dtype=np.float64), np.arange(h, dtype=np.float64))
+    x, y = (xs - cx) / fx, (ys - cy) / fy
+    r2 = x * x + y * y
+    d = 1 + k1 * r2 + k2 * r2 * r2
+    u, v = x * d * fx + cx, y * d * fy + cy
+    iu, iv = np.round(u * 32).astype(np.int64), np.round(v * 32).astype(np.int64)
+    map1 = np.stack([iu >> 5, iv >> 5], -1).astype(np.int16)
+    map2 = ((iv & 31) * 32 + (iu & 31)).astype(np.uint16)
+    return map1, map2

@@ -189,3 +189,32 @@ def test_dot_grid_maxima_density(px, py):
     assert len(okps) > 200
     assert kps.tobytes() == okps.tobytes() and np.array_equal(desc, odesc)
     ex.close()
+
+
+@pytest.mark.parametrize("w,h", [(752, 480), (641, 479)])
+def test_undistort_in_front_of_the_pyramid(w, h):
+    """Frame::ComputeImagePyramid's cv::remap (src/Frame.cc:775-790) on the device: level 0 == the oracle's remap (itself
+    pinned to cv2.remap), and extraction / DSO extraction of the distorted frame == extraction of the undistorted one."""
+    frames = np.stack([synth.textured_frame(w, h, 60 + k) for k in range(3)])
+    m1, m2 = synth.undistort_maps(w, h, 0.25, 0.05)
+    want = [O.remap(f, m1, m2) for f in frames]
+    assert (want[0][0, :] == 0).any() and not np.array_equal(want[0], frames[0])      # the maps do reach outside the image
+    ex = Y.Extractor(1000, max_batch=4)
+    ex.set_undistort_maps(m1, m2)
+    ex.compute_pyramid(frames)
+    for k in range(3):
+        assert np.array_equal(ex.pyramid(k, w, h)[0], want[k])
+    got = ex.extract_batch(frames)
+    plain = Y.Extractor(1000, max_batch=4)
+    exp = plain.extract_batch(np.stack(want))
+    for g, e in zip(got, exp):
+        assert g[0].tobytes() == e[0].tobytes() and np.array_equal(g[1], e[1]) and len(g[0]) > 500
+    gd, _ = ex.extract_dso(frames[:2])
+    ed, _ = plain.extract_dso(np.stack(want[:2]))
+    for g, e in zip(gd, ed):
+        assert g[0].tobytes() == e[0].tobytes() and np.array_equal(g[1], e[1]) and len(g[0]) > 500
+    ex.set_undistort_maps(None, None)                       # and off again
+    back = ex.extract_batch(frames)
+    ref = plain.extract_batch(frames)
+    assert back[0][0].tobytes() == ref[0][0].tobytes()
+    ex.close(); plain.close()

@@ -118,3 +118,22 @@ def test_cosf_sinf_restatement_equals_libm_sampled():
 def test_cosf_sinf_exhaustive():
     # every float in [0, 2*pi]: ~1.08e9 values, ~13 s on one core
     assert O.lib().ygzo_cossin_check_libm(0.0, 6.2832, 1) == 0
+
+
+def undistort_maps(w, h, k1=-0.28, k2=0.07):
+    """cv::initUndistortRectifyMap(K, D, Mat(), K, size, CV_16SC2, map1, map2) as Frame::ComputeImagePyramid calls it
+    (src/Frame.cc:778-783), for a EuRoC-like camera scaled to the image."""
+    K = np.array([[0.61 * w, 0, 0.49 * w], [0, 0.95 * h, 0.52 * h], [0, 0, 1]], np.float64)
+    D = np.array([k1, k2, 0.0002, 0.00002, 0.0])
+    return cv2.initUndistortRectifyMap(K, D, None, K, (w, h), cv2.CV_16SC2)
+
+
+@pytest.mark.parametrize("w,h", [(752, 480), (641, 479), (200, 150)])
+def test_remap_matches_cv2(w, h):
+    img = synth.textured_frame(w, h, 3)
+    m1, m2 = undistort_maps(w, h)
+    assert np.array_equal(O.remap(img, m1, m2), cv2.remap(img, m1, m2, cv2.INTER_LINEAR))
+    rng = np.random.default_rng(1)           # arbitrary maps, taps off every edge
+    r1 = rng.integers(-6, max(w, h) + 6, (h, w, 2)).astype(np.int16)
+    r2 = rng.integers(0, 1024, (h, w)).astype(np.uint16)
+    assert np.array_equal(O.remap(img, r1, r2), cv2.remap(img, r1, r2, cv2.INTER_LINEAR))
