@@ -221,25 +221,29 @@ __device__ __forceinline__ void stsU16(unsigned a, unsigned v) { asm volatile("s
 __device__ __forceinline__ unsigned fastBase(int v) { return (unsigned)(v + 256) * 0xFFFF0001u + (512u << 16); }
 __device__ __forceinline__ unsigned fastE(int p, unsigned base) { return (unsigned)p * 0xFFFFu + base; }
 
+// Compass pretest: an arc of 9 always holds two adjacent compass pixels (ring 0, 4, 8, 12), so m > t needs two
+// adjacent compass pixels both darker or both brighter than the centre by more than t.  `pre2` = t + 256 in both halves.
+__device__ __forceinline__ bool fastPretest(unsigned p, unsigned pre2) {
+    constexpr int P = kTilePitch;
+    const unsigned base = fastBase((int)ldsU8<0>(p));
+    const unsigned e0 = fastE(ldsU8<3 * P>(p), base), e4 = fastE(ldsU8<3>(p), base);
+    const unsigned e8 = fastE(ldsU8<-3 * P>(p), base), e12 = fastE(ldsU8<-3>(p), base);
+    const unsigned pm = __vimax3_u16x2(__vminu2(e0, e4), __vminu2(e4, e8), __vmaxu2(__vminu2(e8, e12), __vminu2(e12, e0)));
+    return __vmaxu2(pm, pre2) != pre2;
+}
+
 // Corner measure m (max over the 16 arcs of 9 contiguous ring pixels of min(v-p) resp. min(p-v)),
-// OpenCV fast_score.cpp cornerScore<16> without the threshold clamp.  `pre2` = minThFAST + 256 in both halves.
-// With PRETEST the function returns -1 early when no two adjacent compass pixels are both darker / both
-// brighter than the threshold (an arc of 9 always holds two adjacent compass pixels), i.e. m <= minThFAST.
+// OpenCV fast_score.cpp cornerScore<16> without the threshold clamp.
 //
 // Arc network (36 packed min/max instead of 16 arcs x 8): arcs k and k+1 share the 8 ring pixels k+1..k+8, so
 //   max(arc_k, arc_k+1) = min(e_k+1 .. e_k+8, max(e_k, e_k+9))        (lattice identity)
 // and the 8-pixel cores are built from pair minima lo2_j (j odd) and their pair minima lo4_j.
-template <bool PRETEST> __device__ __forceinline__ int fastMeasure(unsigned p, unsigned pre2) {
+__device__ __forceinline__ int fastMeasure(unsigned p) {
     constexpr int P = kTilePitch;
     const unsigned base = fastBase((int)ldsU8<0>(p));
     unsigned e[16];
     e[0] = fastE(ldsU8<3 * P>(p), base); e[4] = fastE(ldsU8<3>(p), base);
     e[8] = fastE(ldsU8<-3 * P>(p), base); e[12] = fastE(ldsU8<-3>(p), base);
-    if (PRETEST) {
-        const unsigned pm = __vimax3_u16x2(__vminu2(e[0], e[4]), __vminu2(e[4], e[8]),
-                                           __vmaxu2(__vminu2(e[8], e[12]), __vminu2(e[12], e[0])));
-        if (__vmaxu2(pm, pre2) == pre2) return -1;
-    }
     e[1] = fastE(ldsU8<3 * P + 1>(p), base);   e[2] = fastE(ldsU8<2 * P + 2>(p), base);   e[3] = fastE(ldsU8<P + 3>(p), base);
     e[5] = fastE(ldsU8<-P + 3>(p), base);      e[6] = fastE(ldsU8<-2 * P + 2>(p), base);  e[7] = fastE(ldsU8<-3 * P + 1>(p), base);
     e[9] = fastE(ldsU8<-3 * P - 1>(p), base);  e[10] = fastE(ldsU8<-2 * P - 2>(p), base); e[11] = fastE(ldsU8<-P - 3>(p), base);
@@ -259,8 +263,8 @@ template <bool PRETEST> __device__ __forceinline__ int fastMeasure(unsigned p, u
 // NMS of cv::FAST is threshold-independent on m: a corner at threshold t (m > t) survives iff its
 // stored score m-1 exceeds the stored scores of its 8 neighbours, and a neighbour's stored score is
 // n-1 if n > t and 0 otherwise; since m > t >= 1 this is exactly "every neighbour has n < m".  The
-// score tile holds m for m > minThFAST and 0 elsewhere (and outside the detection area).
-__global__ void __launch_bounds__(kFastThreads, 9) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+// score tile holds m for m > t (t = the threshold in force) and 0 elsewhere (and outside the detection area).
+__global__ void __launch_bounds__(kFastThreads, 12) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
     // dynamic shared memory, sized by the geometry's largest cell (FrameGeom::fastRegionA/fastScoreBytes/fastWarpCap):
     // [image tile, re-used from phase 2 on for the per-warp maxima lists][score tile][per-warp corner lists]
     extern __shared__ __align__(16) uint8_t fastSmem[];
@@ -281,38 +285,41 @@ __global__ void __launch_bounds__(kFastThreads, 9) k_fast(const __grid_constant_
     // ---- tile load: aligned 32-bit words when the level allows it; tile column c <-> image x = xa + c
     const bool aligned = ((L.pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(img) & 3) == 0);
     const int xa = aligned ? (iniX & ~3) : iniX, ox = iniX - xa;
+    const int lane = tid & 31, wid = tid >> 5;
     if (aligned) {
+        // lane = word of a row (two rows per warp step when a row has <= 16 words): no index arithmetic in the loop,
+        // and the unrolled loop keeps every load of the thread in flight at once
         const int nw = (ox + tw + 3) >> 2;           // words per row (<= 19)
-        const float rnw = __fdividef(1.0f, (float)nw);   // (i + 0.5) / nw is never within rounding error of an integer
-        for (int i = tid; i < nw * th; i += kFastThreads) {
-            const int y = (int)(((float)i + 0.5f) * rnw), wq = i - y * nw;
-            *reinterpret_cast<uint32_t *>(&tile[y * kTilePitch + 4 * wq]) =
-                __ldg(reinterpret_cast<const uint32_t *>(img + (long long)y * L.pitch + xa) + wq);
+        const bool two = nw <= 16;
+        const int wq = two ? (lane & 15) : lane, r0 = two ? 2 * wid + (lane >> 4) : wid, rstep = two ? 8 : 4;
+        if (wq < nw) {
+            const uint8_t *src = img + (long long)r0 * L.pitch + xa + 4 * wq;
+            const long long sstep = (long long)rstep * L.pitch;
+            uint8_t *dst = tile + r0 * kTilePitch + 4 * wq;
+#pragma unroll 5
+            for (int y = r0; y < th; y += rstep, src += sstep, dst += rstep * kTilePitch)
+                *reinterpret_cast<uint32_t *>(dst) = __ldg(reinterpret_cast<const uint32_t *>(src));
         }
     } else {
-        const int lane = tid & 31, wid = tid >> 5;
         for (int y = wid; y < th; y += kFastThreads / 32) {
             const uint8_t *row = img + (long long)y * L.pitch + xa;
             for (int x = lane; x < tw; x += 32) tile[y * kTilePitch + x] = row[x];
         }
     }
-    // score tile border (the detection area itself is fully written by phase 1)
-    for (int i = tid; i < 2 * (dw + 2); i += kFastThreads) {
-        const int r = i >= dw + 2;
-        score[(r ? (dh + 1) * kTilePitch : 0) + i - r * (dw + 2)] = 0;
-    }
-    for (int i = tid; i < 2 * dh; i += kFastThreads) {
-        const int r = i >= dh;
-        score[(i - r * dh + 1) * kTilePitch + (r ? dw + 1 : 0)] = 0;
-    }
+    // score tile: all zero; phase 1 writes m only where m exceeds the threshold in force
+    for (int i = tid; i < ((dh + 2) * kTilePitch + 15) / 16; i += kFastThreads) reinterpret_cast<uint4 *>(score)[i] = make_uint4(0, 0, 0, 0);
     __syncthreads();
     const int minTh = G.minTh, iniTh = G.iniTh;
-    // ---- phase 1: measure of every detection pixel -> score tile (same pitch as the image tile, so one
-    // offset `off` = y * pitch + x addresses both); corners at minThFAST go to the warp's own list
-    // (fill count in a register: no shared atomics, no shuffles).  Pixel i = y * dw + x advances by
-    // kFastThreads per iteration; y = i / dw comes from a 24-bit reciprocal (IMAD.HI on i << 8, exact for
-    // i < 4096), so the address update runs on the FMA pipe and leaves the ALU pipe to the min/max network.
-    const int lane = tid & 31, wid = tid >> 5;
+    // ---- phase 1 runs at iniThFAST first and, only if no corner of the cell survives NMS, again at minThFAST
+    // (src/ORBextractor.cc:764-770).  It is split in two so that the 36-op arc network only runs on full warps:
+    //  1a  every detection pixel takes the compass pretest (5 loads, 7 packed min/max); the offsets of the pixels that
+    //      pass go to the warp's own list (fill count in a register: no shared atomics, no shuffles).  On the textured
+    //      frames 37 % pass at threshold 20 while 12 % are corners, so a warp that ran the full measure whenever one
+    //      of its 32 lanes passed would never skip it;
+    //  1b  the warp walks its list 32 entries at a time: full measure m, score tile entry and (in place, the write
+    //      index never passes the read index) the list of the corners m > t.
+    // Pixel i = y * dw + x advances by kFastThreads per iteration; y = i / dw comes from a 24-bit reciprocal (IMAD.HI on
+    // i << 8, exact for i < 4096), so the address update runs on the FMA pipe and leaves the ALU pipe to the min/max ops.
     const unsigned ltMask = (1u << lane) - 1u;
     // 2^24 / dw rounded up by 1..11 (the float reciprocal is good to 2^-22): the quotient is exact while
     // i * (magic * dw - 2^24) < 2^24, i.e. up to an excess of 64 for dw <= 64
@@ -320,46 +327,64 @@ __global__ void __launch_bounds__(kFastThreads, 9) k_fast(const __grid_constant_
     const int wrapOff = kTilePitch - dw;
     const unsigned centre = smemAddr(tile + 3 * kTilePitch + 3 + ox);
     const unsigned sc0a = smemAddr(score + kTilePitch + 1);
-    const unsigned pre2 = ((unsigned)minTh + 256u) * 0x10001u;
     const unsigned cornersAt = smemAddr(corners + wid * kFastWarpCap);
-    int n1 = 0;
-    unsigned lastMask = 0;   // warp-uniform: the compass pretest only pays where whole warps get rejected, so it is
-                             // skipped while the warp keeps finding corners and used again after a corner-free step
-    for (int i = tid; i - lane < npx; i += kFastThreads) {
-        const int off = (int)__umulhi((unsigned)i << 8, magic) * wrapOff + i;
-        int m = -1;
-        if (i < npx) {
-            m = lastMask == 0 ? fastMeasure<true>(centre + off, pre2) : fastMeasure<false>(centre + off, pre2);
-            stsU8(sc0a + off, (unsigned)max(m, 0));
-        }
-        lastMask = __ballot_sync(0xffffffffu, m > minTh);
-        if (m > minTh) stsU16(cornersAt + 2 * (n1 + __popc(lastMask & ltMask)), (unsigned)off);
-        n1 += __popc(lastMask);
-    }
-    __syncthreads();
-    // ---- phase 2: strict local maxima of m among the warp's corners
     const unsigned maximaAt = smemAddr(maxima + wid * kFastWarpCap);
-    int n2 = 0, any = 0;
-    for (int k0 = 0; k0 < n1; k0 += 32) {
-        const int k = k0 + lane;
-        bool ismax = false;
-        unsigned o = 0;
-        if (k < n1) {
-            constexpr int P = kTilePitch;
-            o = ldsU16(cornersAt + 2 * k);
-            const unsigned sc = sc0a + o;
-            const unsigned m = ldsU8<0>(sc);
-            const unsigned nb = max(max(max(ldsU8<-1>(sc), ldsU8<1>(sc)), max(ldsU8<-P - 1>(sc), ldsU8<-P>(sc))),
-                                    max(max(ldsU8<-P + 1>(sc), ldsU8<P - 1>(sc)), max(ldsU8<P>(sc), ldsU8<P + 1>(sc))));
-            ismax = nb < m;
-            any |= ismax && (int)m > iniTh;
+    int t = iniTh, n2 = 0;
+    for (;;) {
+        const unsigned pre2 = ((unsigned)t + 256u) * 0x10001u;
+        int n0 = 0;
+        for (int i = tid; i - lane < npx; i += kFastThreads) {
+            const int ic = min(i, npx - 1);   // clamped, not branched: the tail lanes redo the last pixel and drop the result
+            const int off = (int)__umulhi((unsigned)ic << 8, magic) * wrapOff + ic;
+            const bool pass = fastPretest(centre + off, pre2) && i < npx;
+            const unsigned mask = __ballot_sync(0xffffffffu, pass);
+            if (pass) stsU16(cornersAt + 2 * (n0 + __popc(mask & ltMask)), (unsigned)off);
+            n0 += __popc(mask);
         }
-        const unsigned mask = __ballot_sync(0xffffffffu, ismax);
-        if (ismax) stsU16(maximaAt + 2 * (n2 + __popc(mask & ltMask)), o);
-        n2 += __popc(mask);
+        __syncwarp();
+        int n1 = 0;
+        for (int k0 = 0; k0 < n0; k0 += 32) {
+            const int k = k0 + lane;
+            unsigned off = 0;
+            int m = -1;
+            if (k < n0) {
+                off = ldsU16(cornersAt + 2 * k);
+                m = fastMeasure(centre + off);
+            }
+            const bool corner = m > t;
+            if (corner) stsU8(sc0a + off, (unsigned)m);
+            const unsigned mask = __ballot_sync(0xffffffffu, corner);   // every lane has consumed its list entry by now
+            if (corner) stsU16(cornersAt + 2 * (n1 + __popc(mask & ltMask)), off);
+            n1 += __popc(mask);
+        }
+        __syncthreads();
+        // ---- phase 2: strict local maxima of m among the warp's corners (non-corners hold 0 in the score tile).
+        // The maxima lists alias the image tile: once a maximum exists the tile is not needed any more.
+        int any = 0;
+        n2 = 0;
+        for (int k0 = 0; k0 < n1; k0 += 32) {
+            const int k = k0 + lane;
+            bool ismax = false;
+            unsigned o = 0;
+            if (k < n1) {
+                constexpr int P = kTilePitch;
+                o = ldsU16(cornersAt + 2 * k);
+                const unsigned sc = sc0a + o;
+                const unsigned m = ldsU8<0>(sc);
+                const unsigned nb = max(max(max(ldsU8<-1>(sc), ldsU8<1>(sc)), max(ldsU8<-P - 1>(sc), ldsU8<-P>(sc))),
+                                        max(max(ldsU8<-P + 1>(sc), ldsU8<P - 1>(sc)), max(ldsU8<P>(sc), ldsU8<P + 1>(sc))));
+                ismax = nb < m;
+            }
+            const unsigned mask = __ballot_sync(0xffffffffu, ismax);
+            any |= (int)mask;
+            if (ismax) stsU16(maximaAt + 2 * (n2 + __popc(mask & ltMask)), o);
+            n2 += __popc(mask);
+        }
+        // no maximum anywhere in the cell <=> nothing was written over the tile: the minThFAST pass can re-read it
+        if (__syncthreads_or(any) || t == minTh) break;
+        t = minTh;
     }
-    // ---- threshold fallback: iniThFAST unless nothing survives in the cell (src/ORBextractor.cc:764-770)
-    const int t = __syncthreads_or(any) ? iniTh : minTh;
+    // ---- every maximum of the final pass is a keypoint of the cell
     uint2 *cand = B.cand + (long long)f * G.candPerFrame + L.candOff;
     int *counter = B.candCount + f * kMaxLevels + level;
     for (int k0 = 0; k0 < n2; k0 += 32) {
@@ -370,7 +395,7 @@ __global__ void __launch_bounds__(kFastThreads, 9) k_fast(const __grid_constant_
             const int o = (int)ldsU16(maximaAt + 2 * k);
             y = (o * ((1 << 20) / kTilePitch + 1)) >> 20; x = o - y * kTilePitch;   // exact for o < 2^13
             m = (int)ldsU8<0>(sc0a + o);
-            keep = m > t;
+            keep = true;
         }
         const unsigned mask = __ballot_sync(0xffffffffu, keep);
         if (mask == 0) continue;
