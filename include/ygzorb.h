@@ -409,6 +409,61 @@ int ygzorb_bow_transform(ygzorb_matcher *m, const ygzorb_vocabulary *voc, const 
                          int32_t *bow_count, int32_t *bow_word, double *bow_value, int32_t *fv_count, uint32_t *fv_node,
                          int32_t *fv_start, uint32_t *fv_feat);
 
+/* ---- descriptor post-processing and the pyramid consumers of the direct tracker ---- */
+
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:211-271), batched over n_points MapPoints (the reference calls it
+ * point by point from LocalMapping::ProcessNewKeyFrame / CreateNewMapPoints / SearchInNeighbors and Tracking).  The
+ * observation descriptors of point p are rows obs_start[p] .. obs_start[p+1]-1 of obs_desc (32 B each): mObservations in
+ * map order, bad keyframes skipped (:226-232).  best_idx[p] = the row (relative to obs_start[p]) with the least median
+ * Hamming distance to the others — element (int)(0.5*(N-1)) of the sorted row, first row wins ties (:254-264) — or -1 when
+ * the point has no observation (the reference returns without touching mDescriptor); best_median[p] = that median
+ * (INT_MAX for -1); best_desc + 32*p = the chosen row (mDescriptor; untouched for -1).  obs_start has n_points + 1 entries. */
+int ygzorb_distinctive_descriptors(ygzorb_matcher *m, const uint8_t *obs_desc, const int32_t *obs_start, int n_points,
+                                   unsigned flags, int32_t *best_idx, int32_t *best_median, uint8_t *best_desc);
+
+/* A device-resident copy of one frame's image pyramid (Frame::mvImagePyramid / KeyFrame::mvImagePyramid, src/Frame.cc:810-813,
+ * src/KeyFrame.cc:259-261: continuous 8U images, step == cols) for the direct-tracking entry points below.
+ *   ygzorb_pyramid_create: from n_levels images (host pointers, or device pointers with YGZORB_IN_DEVICE), any pitch.
+ *   ygzorb_pyramid_from_extractor: snapshot of frame `frame` of the extractor's last batch, device to device — the pyramid
+ *     never visits the host (what a keyframe keeps when the tracker promotes the current frame).
+ * n_levels <= 16.  The object is immutable after creation and may be read by several matchers concurrently. */
+typedef struct ygzorb_pyramid ygzorb_pyramid;
+int ygzorb_pyramid_create(int device, const uint8_t *const *levels, const int32_t *w, const int32_t *h, const int32_t *pitch,
+                          int n_levels, unsigned flags, ygzorb_pyramid **out);
+int ygzorb_pyramid_from_extractor(ygzorb_extractor *ex, int frame, ygzorb_pyramid **out);
+void ygzorb_pyramid_destroy(ygzorb_pyramid *p);
+/* *n_levels, and w[l], h[l] for every level (w / h may be NULL) */
+int ygzorb_pyramid_info(const ygzorb_pyramid *p, int32_t *n_levels, int32_t *w, int32_t *h);
+/* continuous host copy of level `level` (w*h bytes) */
+int ygzorb_pyramid_get_level(const ygzorb_pyramid *p, int level, uint8_t *out);
+
+/* What ORBmatcher::FindDirectProjection reads of a reference KeyFrame.  Poses are Sophus::SE3f as stored: the unit
+ * quaternion's coefficients x, y, z, w, then the translation.  t_cur_ref = curr->mTcw * ref->GetPose().inverse()
+ * (src/ORBmatcher.cc:1581-1582), composed by the caller once per keyframe. */
+typedef struct ygzorb_direct_keyframe {
+    const ygzorb_pyramid *pyramid;   /* ref->mvImagePyramid */
+    float pose_ref[7];               /* ref->GetPose() */
+    float t_cur_ref[7];              /* TCR */
+    float fx, fy, cx, cy;            /* ref intrinsics (KeyFrame::Pixel2Camera, include/KeyFrame.h:146-152) */
+} ygzorb_direct_keyframe;
+
+/* ORBmatcher::FindDirectProjection(KeyFrame *ref, Frame *curr, MapPoint *mp, Vector2f &px_curr, int &search_level)
+ * (src/ORBmatcher.cc:1573-1602), batched over n (MapPoint, reference keyframe) pairs as Tracking::SearchLocalPointsDirect
+ * issues them (src/Tracking.cc:2284-2305, 2366-2385): GetWarpAffineMatrix (:1525-1547), GetBestSearchLevel
+ * (include/ORBmatcher.h:226-238), WarpAffine of a 10x10 patch from ref level `octave` (:1549-1571), ygz::Align2D with 10
+ * iterations on level search_level of `cur` (src/Align.cc:8-105).
+ * Pair i: keyframe kfs[kf_index[i]]; px_ref[2i..] = ref->mvKeys[idx].pt, octave[i] = its octave; world_pos[3i..] =
+ * mp->GetWorldPos(); px_curr[2i..] in = (mp->mTrackProjX, mp->mTrackProjY), out = the aligned pixel (level-0 coordinates);
+ * search_level[i]; success[i] = the bool the reference returns.  cur_intrinsics = curr fx, fy, cx, cy; scale_factors /
+ * inv_scale_factors = mvScaleFactors / mvInvScaleFactors (n_levels of `cur`); inv_level_sigma2_1 = ref->mvInvLevelSigma2[1].
+ * Float results follow the reference's evaluation order (Eigen 3.3 fixed-size expressions, uncontracted) and equal the CPU
+ * restatement bit for bit. */
+int ygzorb_find_direct_projection(ygzorb_matcher *m, const ygzorb_direct_keyframe *kfs, int n_kfs, const ygzorb_pyramid *cur,
+                                  const float *cur_intrinsics, const float *scale_factors, const float *inv_scale_factors,
+                                  float inv_level_sigma2_1, int n, const int32_t *kf_index, const float *px_ref,
+                                  const int32_t *octave, const float *world_pos, unsigned flags, float *px_curr,
+                                  int32_t *search_level, uint8_t *success);
+
 #ifdef __cplusplus
 }
 #endif

@@ -614,6 +614,190 @@ int ygzorb_search_by_bow(ygzorb_matcher *h, const ygzorb_keyframe_features *K1, 
 }
 
 // ================================================================================================
+// SURVEY.md 8(f) row f4
+int ygzorb_distinctive_descriptors(ygzorb_matcher *h, const uint8_t *obsDesc, const int32_t *obsStart, int nPoints, unsigned flags,
+                                   int32_t *bestIdx, int32_t *bestMedian, uint8_t *bestDesc) {
+    Matcher *m = (Matcher *)h;
+    if (!m || !obsStart || !bestIdx || !bestMedian || !bestDesc) return argFailM("null argument");
+    if (nPoints < 0) return argFailM("bad sizes");
+    if (nPoints == 0) return 0;
+    YGZ_CUDA(cudaSetDevice(m->device));
+    const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
+    long long nRows = -1;
+    if (!inDev) {
+        for (int p = 0; p < nPoints; p++) if (obsStart[p + 1] < obsStart[p]) return argFailM("obs_start must be non-decreasing");
+        if (obsStart[0] < 0) return argFailM("obs_start must be non-negative");
+        nRows = obsStart[nPoints];
+        if (nRows > 0 && !obsDesc) return argFailM("null argument");
+    }
+    int rc;
+    const uint8_t *dDesc = obsDesc; const int32_t *dStart = nullptr;
+    if (!inDev && (rc = stageIn(m, 0, obsDesc, (size_t)std::max<long long>(nRows, 0) * 32, false, &dDesc))) return rc;
+    if ((rc = stageIn(m, 1, obsStart, (size_t)nPoints + 1, inDev, &dStart))) return rc;
+    int32_t *oi, *om; uint8_t *od;
+    if ((rc = stageOut(m, 2, bestIdx, (size_t)nPoints, outDev, &oi))) return rc;
+    if ((rc = stageOut(m, 3, bestMedian, (size_t)nPoints, outDev, &om))) return rc;
+    if ((rc = stageOut(m, 4, bestDesc, (size_t)nPoints * 32, outDev, &od))) return rc;
+    // rows of points without observations stay as the caller left them: seed the staged copy with the caller's bytes
+    if (!outDev) YGZ_CUDA(cudaMemcpyAsync(od, bestDesc, (size_t)nPoints * 32, cudaMemcpyHostToDevice, m->stream));
+    m->launches += launchDistinctive(dDesc, dStart, nPoints, oi, om, od, m->stream);
+    if ((rc = copyOut(m, bestIdx, oi, (size_t)nPoints, outDev))) return rc;
+    if ((rc = copyOut(m, bestMedian, om, (size_t)nPoints, outDev))) return rc;
+    if ((rc = copyOut(m, bestDesc, od, (size_t)nPoints * 32, outDev))) return rc;
+    return finish(m, flags);
+}
+
+namespace ygz {
+struct Pyramid {
+    int device = 0, nLevels = 0;
+    uint8_t *base = nullptr;
+    int w[kMaxLevels], h[kMaxLevels];
+    size_t off[kMaxLevels];
+};
+static int pyramidAlloc(int device, const int32_t *w, const int32_t *h, int nLevels, Pyramid **out) {
+    if (nLevels < 1 || nLevels > kMaxLevels) return argFailM("n_levels must be 1..16");
+    Pyramid *P = new Pyramid();
+    P->device = device; P->nLevels = nLevels;
+    size_t total = 0;
+    for (int l = 0; l < nLevels; l++) {
+        if (w[l] < 1 || h[l] < 1) { delete P; return argFailM("bad level size"); }
+        P->w[l] = w[l]; P->h[l] = h[l]; P->off[l] = total;
+        total += ((size_t)w[l] * h[l] + 255) & ~(size_t)255;
+    }
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&P->base, total);
+    if (e != cudaSuccess) { delete P; return cudaFail(e, "pyramid_create", __FILE__, __LINE__); }
+    *out = P;
+    return 0;
+}
+}  // namespace ygz
+
+int ygzorb_pyramid_create(int device, const uint8_t *const *levels, const int32_t *w, const int32_t *h, const int32_t *pitch,
+                          int nLevels, unsigned flags, ygzorb_pyramid **out) {
+    if (!levels || !w || !h || !pitch || !out) return argFailM("null argument");
+    for (int l = 0; l < nLevels && l < kMaxLevels; l++)
+        if (!levels[l] || pitch[l] < w[l]) return argFailM("null level or pitch < width");
+    Pyramid *P = nullptr;
+    int rc = pyramidAlloc(device, w, h, nLevels, &P);
+    if (rc) return rc;
+    const cudaMemcpyKind kind = (flags & YGZORB_IN_DEVICE) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    for (int l = 0; l < nLevels; l++) {
+        cudaError_t e = cudaMemcpy2D(P->base + P->off[l], (size_t)w[l], levels[l], (size_t)pitch[l], (size_t)w[l], (size_t)h[l], kind);
+        if (e != cudaSuccess) { ygzorb_pyramid_destroy((ygzorb_pyramid *)P); return cudaFail(e, "pyramid_create copy", __FILE__, __LINE__); }
+    }
+    *out = (ygzorb_pyramid *)P;
+    return 0;
+}
+
+int ygzorb_pyramid_from_extractor(ygzorb_extractor *ex, int frame, ygzorb_pyramid **out) {
+    if (!ex || !out) return argFailM("null argument");
+    int nl = 0; const float *sc, *isc;
+    int rc = extractorTables(ex, &nl, &sc, &isc);
+    if (rc) return rc;
+    int32_t w[kMaxLevels], h[kMaxLevels];
+    LevelView v[kMaxLevels];
+    for (int l = 0; l < nl; l++) {
+        if ((rc = extractorLevelView(ex, frame, l, &v[l]))) return rc;   // drains the extractor's stream
+        w[l] = v[l].w; h[l] = v[l].h;
+    }
+    int device = 0;
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, v[0].ptr) == cudaSuccess) device = attr.device;
+    Pyramid *P = nullptr;
+    if ((rc = pyramidAlloc(device, w, h, nl, &P))) return rc;
+    for (int l = 0; l < nl; l++) {
+        cudaError_t e = cudaMemcpy2D(P->base + P->off[l], (size_t)w[l], v[l].ptr, (size_t)v[l].pitch, (size_t)w[l], (size_t)h[l], cudaMemcpyDeviceToDevice);
+        if (e != cudaSuccess) { ygzorb_pyramid_destroy((ygzorb_pyramid *)P); return cudaFail(e, "pyramid_from_extractor copy", __FILE__, __LINE__); }
+    }
+    *out = (ygzorb_pyramid *)P;
+    return 0;
+}
+
+void ygzorb_pyramid_destroy(ygzorb_pyramid *p) {
+    Pyramid *P = (Pyramid *)p;
+    if (!P) return;
+    cudaSetDevice(P->device);
+    if (P->base) cudaFree(P->base);
+    delete P;
+}
+
+int ygzorb_pyramid_info(const ygzorb_pyramid *p, int32_t *nLevels, int32_t *w, int32_t *h) {
+    const Pyramid *P = (const Pyramid *)p;
+    if (!P || !nLevels) return argFailM("null argument");
+    *nLevels = P->nLevels;
+    for (int l = 0; l < P->nLevels; l++) { if (w) w[l] = P->w[l]; if (h) h[l] = P->h[l]; }
+    return 0;
+}
+
+int ygzorb_pyramid_get_level(const ygzorb_pyramid *p, int level, uint8_t *out) {
+    const Pyramid *P = (const Pyramid *)p;
+    if (!P || !out) return argFailM("null argument");
+    if (level < 0 || level >= P->nLevels) return argFailM("level out of range");
+    YGZ_CUDA(cudaSetDevice(P->device));
+    YGZ_CUDA(cudaMemcpy(out, P->base + P->off[level], (size_t)P->w[level] * P->h[level], cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int ygzorb_find_direct_projection(ygzorb_matcher *h, const ygzorb_direct_keyframe *kfs, int nKfs, const ygzorb_pyramid *cur,
+                                  const float *curIntr, const float *scale, const float *invScale, float invLevelSigma2_1, int n,
+                                  const int32_t *kfIndex, const float *pxRef, const int32_t *octave, const float *worldPos,
+                                  unsigned flags, float *pxCurr, int32_t *searchLevel, uint8_t *success) {
+    Matcher *m = (Matcher *)h;
+    const Pyramid *C = (const Pyramid *)cur;
+    if (!m || !C || !curIntr || !scale || !invScale) return argFailM("null argument");
+    if (n < 0 || nKfs < 0) return argFailM("bad sizes");
+    if (n == 0) return 0;
+    if (!kfs || nKfs == 0 || !kfIndex || !pxRef || !octave || !worldPos || !pxCurr || !searchLevel || !success) return argFailM("null argument");
+    if (C->device != m->device) return argFailM("pyramid lives on another device");
+    const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
+    std::vector<DirectKf> hk((size_t)nKfs);
+    for (int k = 0; k < nKfs; k++) {
+        const Pyramid *P = (const Pyramid *)kfs[k].pyramid;
+        if (!P) return argFailM("keyframe without a pyramid");
+        if (P->device != m->device) return argFailM("pyramid lives on another device");
+        DirectKf &D = hk[k];
+        memset(&D, 0, sizeof D);
+        for (int l = 0; l < P->nLevels; l++) { D.lv[l] = P->base + P->off[l]; D.w[l] = P->w[l]; D.h[l] = P->h[l]; D.pitch[l] = P->w[l]; }
+        memcpy(D.poseRef, kfs[k].pose_ref, sizeof D.poseRef); memcpy(D.tCurRef, kfs[k].t_cur_ref, sizeof D.tCurRef);
+        D.fx = kfs[k].fx; D.fy = kfs[k].fy; D.cx = kfs[k].cx; D.cy = kfs[k].cy;
+    }
+    if (!inDev)
+        for (int i = 0; i < n; i++) {
+            if (kfIndex[i] < 0 || kfIndex[i] >= nKfs) return argFailM("kf_index out of range");
+            const Pyramid *P = (const Pyramid *)kfs[kfIndex[i]].pyramid;
+            if (octave[i] < 0 || octave[i] >= P->nLevels || octave[i] >= C->nLevels) return argFailM("octave out of range");
+        }
+    YGZ_CUDA(cudaSetDevice(m->device));
+    DirectArgs A;
+    memset(&A, 0, sizeof A);
+    int rc;
+    const DirectKf *dk = nullptr;
+    if ((rc = stageIn(m, 0, hk.data(), (size_t)nKfs, false, &dk))) return rc;
+    YGZ_CUDA(cudaStreamSynchronize(m->stream));   // hk is a local: the staged copy must be complete before it goes away
+    A.kfs = dk;
+    for (int l = 0; l < C->nLevels; l++) {
+        A.curLv[l] = C->base + C->off[l]; A.curW[l] = C->w[l]; A.curH[l] = C->h[l]; A.curPitch[l] = C->w[l];
+        A.scale[l] = scale[l]; A.invScale[l] = invScale[l];
+    }
+    A.nLevels = C->nLevels; A.n = n;
+    A.fx = curIntr[0]; A.fy = curIntr[1]; A.cx = curIntr[2]; A.cy = curIntr[3];
+    A.invLevelSigma2_1 = invLevelSigma2_1;
+    if ((rc = stageIn(m, 1, kfIndex, (size_t)n, inDev, &A.kfIndex))) return rc;
+    if ((rc = stageIn(m, 2, pxRef, (size_t)2 * n, inDev, &A.pxRef))) return rc;
+    if ((rc = stageIn(m, 3, octave, (size_t)n, inDev, &A.octave))) return rc;
+    if ((rc = stageIn(m, 4, worldPos, (size_t)3 * n, inDev, &A.worldPos))) return rc;
+    if ((rc = stageOut(m, 5, pxCurr, (size_t)2 * n, outDev, &A.pxCurr))) return rc;
+    if (!outDev) YGZ_CUDA(cudaMemcpyAsync(A.pxCurr, pxCurr, (size_t)2 * n * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+    if ((rc = stageOut(m, 6, searchLevel, (size_t)n, outDev, &A.searchLevel))) return rc;
+    if ((rc = stageOut(m, 7, success, (size_t)n, outDev, &A.success))) return rc;
+    m->launches += launchFindDirectProjection(A, m->stream);
+    if ((rc = copyOut(m, pxCurr, (const float *)A.pxCurr, (size_t)2 * n, outDev))) return rc;
+    if ((rc = copyOut(m, searchLevel, (const int32_t *)A.searchLevel, (size_t)n, outDev))) return rc;
+    if ((rc = copyOut(m, success, (const uint8_t *)A.success, (size_t)n, outDev))) return rc;
+    return finish(m, flags);
+}
+
+// ================================================================================================
 // Bag of words
 }  // extern "C"
 

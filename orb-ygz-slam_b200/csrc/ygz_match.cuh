@@ -137,6 +137,30 @@ int launchBowTransform(const BowArgs &A, cudaStream_t s);
 int launchTriangulation(const TriArgs &A, cudaStream_t s);
 int launchSearchByBoW(const TriArgs &A, cudaStream_t s);
 int launchStereo(const StereoArgs &A, cudaStream_t s);
+// ORBmatcher::FindDirectProjection (direct_kernels.cu); all pointers are device pointers
+struct DirectKf {
+    const uint8_t *lv[kMaxLevels];
+    int w[kMaxLevels], h[kMaxLevels], pitch[kMaxLevels];
+    float poseRef[7], tCurRef[7];
+    float fx, fy, cx, cy;
+};
+struct DirectArgs {
+    const DirectKf *kfs;
+    const uint8_t *curLv[kMaxLevels];
+    int curW[kMaxLevels], curH[kMaxLevels], curPitch[kMaxLevels];
+    int nLevels, n;
+    float fx, fy, cx, cy;
+    float scale[kMaxLevels], invScale[kMaxLevels];
+    float invLevelSigma2_1;
+    const int32_t *kfIndex, *octave;
+    const float *pxRef, *worldPos;
+    float *pxCurr;
+    int32_t *searchLevel;
+    uint8_t *success;
+};
+int launchFindDirectProjection(const DirectArgs &A, cudaStream_t s);
+int launchDistinctive(const uint8_t *obsDesc, const int32_t *obsStart, int nPoints, int32_t *bestIdx, int32_t *bestMedian,
+                      uint8_t *bestDesc, cudaStream_t s);
 int configureMatchKernels();
 
 }  // namespace ygz

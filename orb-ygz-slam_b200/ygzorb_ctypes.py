@@ -271,6 +271,51 @@ def _ptr(a):
     return a.ctypes.data if a is not None else None
 
 
+class DirectKeyFrame(C.Structure):
+    _fields_ = [("pyramid", C.c_void_p), ("pose_ref", C.c_float * 7), ("t_cur_ref", C.c_float * 7),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float)]
+
+
+class Pyramid:
+    """Device-resident image pyramid (ygzorb_pyramid): from host images or as a snapshot of an extractor's frame."""
+
+    def __init__(self, levels=None, device=0, extractor=None, frame=0):
+        L = lib()
+        L.ygzorb_pyramid_create.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_void_p]
+        L.ygzorb_pyramid_from_extractor.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.ygzorb_pyramid_destroy.argtypes = [C.c_void_p]
+        L.ygzorb_pyramid_destroy.restype = None
+        L.ygzorb_pyramid_info.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ygzorb_pyramid_get_level.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        h = C.c_void_p()
+        if extractor is not None:
+            check(L.ygzorb_pyramid_from_extractor(extractor.h, frame, C.byref(h)))
+        else:
+            imgs = [np.ascontiguousarray(a, np.uint8) for a in levels]
+            ptrs = (C.c_void_p * len(imgs))(*[a.ctypes.data for a in imgs])
+            w = np.array([a.shape[1] for a in imgs], np.int32)
+            hh = np.array([a.shape[0] for a in imgs], np.int32)
+            check(L.ygzorb_pyramid_create(device, ptrs, _ptr(w), _ptr(hh), _ptr(w), len(imgs), 0, C.byref(h)))
+        self.h = h
+
+    def sizes(self):
+        n = C.c_int32()
+        w, h = np.zeros(16, np.int32), np.zeros(16, np.int32)
+        check(lib().ygzorb_pyramid_info(self.h, C.byref(n), _ptr(w), _ptr(h)))
+        return [(int(w[l]), int(h[l])) for l in range(n.value)]
+
+    def level(self, l):
+        w, h = self.sizes()[l]
+        out = np.zeros((h, w), np.uint8)
+        check(lib().ygzorb_pyramid_get_level(self.h, l, _ptr(out)))
+        return out
+
+    def close(self):
+        if self.h:
+            lib().ygzorb_pyramid_destroy(self.h)
+            self.h = None
+
+
 class Matcher:
     """Handle behind ygz::ORBmatcher's Hamming searches and Frame::ComputeStereoMatches."""
 
@@ -286,6 +331,8 @@ class Matcher:
         L.ygzorb_hamming_knn2.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_int,
                                           C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ygzorb_descriptor_distance.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_void_p]
+        L.ygzorb_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_void_p, C.c_void_p,
+                                                     C.c_void_p]
         L.ygzorb_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_uint, C.c_void_p,
                                            C.c_void_p]
         L.ygzorb_bow_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_uint] + \
@@ -354,6 +401,43 @@ class Matcher:
         out = np.zeros(len(a), np.int32)
         check(lib().ygzorb_descriptor_distance(self.h, _ptr(a), _ptr(b), len(a), 0, _ptr(out)))
         return out
+
+    def distinctive_descriptors(self, obs_desc, obs_start, best_desc=None):
+        """MapPoint::ComputeDistinctiveDescriptors over a CSR of observation descriptors -> (best_idx, best_median, best_desc)."""
+        obs_desc = np.ascontiguousarray(obs_desc, np.uint8).reshape(-1, 32)
+        obs_start = np.ascontiguousarray(obs_start, np.int32)
+        n = len(obs_start) - 1
+        idx, med = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.int32)
+        out = np.zeros((max(n, 1), 32), np.uint8) if best_desc is None else np.ascontiguousarray(best_desc, np.uint8)
+        check(lib().ygzorb_distinctive_descriptors(self.h, _ptr(obs_desc) if len(obs_desc) else None, _ptr(obs_start), n, 0,
+                                                   _ptr(idx), _ptr(med), _ptr(out)))
+        return idx[:n], med[:n], out[:n]
+
+    def find_direct_projection(self, kfs, cur, cur_intr, scale, inv_scale, inv_sigma2_1, kf_index, px_ref, octave, world_pos,
+                               px_curr):
+        """ORBmatcher::FindDirectProjection, batched.  kfs: list of dicts {pyramid: Pyramid, pose_ref[7], t_cur_ref[7], fx, fy,
+        cx, cy}; cur: Pyramid of the current frame.  Returns (px_curr_out (n, 2), search_level, success)."""
+        L = lib()
+        L.ygzorb_find_direct_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                    C.c_float, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint,
+                                                    C.c_void_p, C.c_void_p, C.c_void_p]
+        arr = (DirectKeyFrame * max(len(kfs), 1))()
+        for a, k in zip(arr, kfs):
+            a.pyramid = k["pyramid"].h
+            a.pose_ref[:] = [float(x) for x in k["pose_ref"]]
+            a.t_cur_ref[:] = [float(x) for x in k["t_cur_ref"]]
+            a.fx, a.fy, a.cx, a.cy = (float(k[n]) for n in ("fx", "fy", "cx", "cy"))
+        kf_index = np.ascontiguousarray(kf_index, np.int32); octave = np.ascontiguousarray(octave, np.int32)
+        px_ref = np.ascontiguousarray(px_ref, np.float32); world_pos = np.ascontiguousarray(world_pos, np.float32)
+        out = np.array(px_curr, np.float32).reshape(-1, 2).copy()
+        n = len(kf_index)
+        intr = np.ascontiguousarray(cur_intr, np.float32)
+        scale = np.ascontiguousarray(scale, np.float32); inv_scale = np.ascontiguousarray(inv_scale, np.float32)
+        level, ok = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.uint8)
+        check(L.ygzorb_find_direct_projection(self.h, arr, len(kfs), cur.h, _ptr(intr), _ptr(scale), _ptr(inv_scale),
+                                              C.c_float(inv_sigma2_1), n, _ptr(kf_index), _ptr(px_ref), _ptr(octave),
+                                              _ptr(world_pos), 0, _ptr(out), _ptr(level), _ptr(ok)))
+        return out, level[:n], ok[:n]
 
     def hamming_knn2(self, query, train, ratio, th):
         query = np.ascontiguousarray(query, np.uint8).reshape(-1, 32)

@@ -192,6 +192,50 @@ def descriptor_distance(a, b):
     return lib().ygzo_descriptor_distance(_p(a), _p(b))
 
 
+def distinctive_descriptors(obs_desc, obs_start, best_desc=None):
+    obs_desc = np.ascontiguousarray(obs_desc, np.uint8).reshape(-1, 32)
+    obs_start = np.ascontiguousarray(obs_start, np.int32)
+    n = len(obs_start) - 1
+    idx, med = np.zeros(n, np.int32), np.zeros(n, np.int32)
+    out = np.zeros((n, 32), np.uint8) if best_desc is None else np.ascontiguousarray(best_desc, np.uint8)
+    lib().ygzo_distinctive_descriptors(_p(obs_desc), _p(obs_start), n, _p(idx), _p(med), _p(out))
+    return idx, med, out
+
+
+class DirectKeyFrame(C.Structure):
+    _fields_ = [("levels", C.c_void_p * 8), ("w", C.c_int32 * 8), ("h", C.c_int32 * 8), ("pitch", C.c_int32 * 8),
+                ("pose_ref", C.c_float * 7), ("t_cur_ref", C.c_float * 7),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float)]
+
+
+def find_direct_projection(kfs, cur_levels, cur_intr, scale, inv_scale, inv_sigma2_1, kf_index, px_ref, octave, world_pos, px_curr):
+    """kfs: list of dicts {levels: [images], pose_ref, t_cur_ref, fx, fy, cx, cy}; cur_levels: list of images."""
+    keep = []
+    arr = (DirectKeyFrame * max(len(kfs), 1))()
+    for a, k in zip(arr, kfs):
+        imgs = [np.ascontiguousarray(x, np.uint8) for x in k["levels"]]
+        keep.append(imgs)
+        for l, im in enumerate(imgs):
+            a.levels[l] = im.ctypes.data; a.w[l] = im.shape[1]; a.h[l] = im.shape[0]; a.pitch[l] = im.shape[1]
+        a.pose_ref[:] = [float(x) for x in k["pose_ref"]]
+        a.t_cur_ref[:] = [float(x) for x in k["t_cur_ref"]]
+        a.fx, a.fy, a.cx, a.cy = (float(k[n]) for n in ("fx", "fy", "cx", "cy"))
+    cur = [np.ascontiguousarray(x, np.uint8) for x in cur_levels]
+    ptrs = (C.c_void_p * len(cur))(*[x.ctypes.data for x in cur])
+    cw = np.array([x.shape[1] for x in cur], np.int32); ch = np.array([x.shape[0] for x in cur], np.int32)
+    kf_index = np.ascontiguousarray(kf_index, np.int32); octave = np.ascontiguousarray(octave, np.int32)
+    px_ref = np.ascontiguousarray(px_ref, np.float32); world_pos = np.ascontiguousarray(world_pos, np.float32)
+    out = np.array(px_curr, np.float32).reshape(-1, 2).copy()
+    n = len(kf_index)
+    intr = np.ascontiguousarray(cur_intr, np.float32)
+    scale = np.ascontiguousarray(scale, np.float32); inv_scale = np.ascontiguousarray(inv_scale, np.float32)
+    level, ok = np.zeros(n, np.int32), np.zeros(n, np.uint8)
+    lib().ygzo_find_direct_projection(arr, len(kfs), ptrs, _p(cw), _p(ch), _p(cw), len(cur), _p(intr), _p(scale), _p(inv_scale),
+                                      C.c_float(inv_sigma2_1), n, _p(kf_index), _p(px_ref), _p(octave), _p(world_pos), _p(out),
+                                      _p(level), _p(ok))
+    return out, level, ok
+
+
 def hamming_knn2(query, train, ratio, th, threads=1):
     query = np.ascontiguousarray(query, np.uint8)
     train = np.ascontiguousarray(train, np.uint8)

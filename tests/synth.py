@@ -334,3 +334,72 @@ def undistort_maps(w, h, k1=-0.28, k2=0.07):
     map1 = np.stack([iu >> 5, iv >> 5], -1).astype(np.int16)
     map2 = ((iv & 31) * 32 + (iu & 31)).astype(np.uint16)
     return map1, map2
+
+
+def quat_from_rotvec(r):
+    """Unit quaternion (x, y, z, w) of a rotation vector, float32."""
+    r = np.asarray(r, np.float64)
+    th = np.linalg.norm(r)
+    if th < 1e-12:
+        return np.array([0, 0, 0, 1], np.float32)
+    ax = r / th
+    return np.concatenate([ax * np.sin(th / 2), [np.cos(th / 2)]]).astype(np.float32)
+
+
+def quat_rotate(q, v):
+    """R(q) v in float64 (plain rotation-matrix form; an independent route from Eigen's _transformVector)."""
+    x, y, z, w = (float(a) for a in q)
+    R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                  [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                  [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+    return R @ np.asarray(v, np.float64)
+
+
+def pyramid_of(img, scale=1.2, levels=8):
+    """mvImagePyramid as ORBextractor::ComputePyramid builds it (sizes from level 0, each level resized from the previous)."""
+    import cv2
+    out = [np.ascontiguousarray(img)]
+    sc, inv, _ = scale_tables(scale, levels)
+    for l in range(1, levels):
+        w = int(np.rint(np.float32(img.shape[1]) * inv[l])); h = int(np.rint(np.float32(img.shape[0]) * inv[l]))
+        out.append(cv2.resize(out[-1], (w, h), interpolation=cv2.INTER_LINEAR))
+    return out
+
+
+def direct_projection_case(seed, n=300, w=752, h=480, fx=458.654, fy=457.296, cx=367.215, cy=248.375):
+    """Two reference keyframes and a current frame for FindDirectProjection: the current image is keyframe 0's image shifted by
+    the parallax of a sideways camera motion at the common depth of most points, so Align2D converges for them; other points sit
+    at wrong depths, near the border, or belong to keyframe 1 (different intrinsics: the affine warp picks search level > 0)."""
+    import cv2
+    rng = np.random.default_rng(seed)
+    ref = textured_frame(w, h, 40 + seed)
+    Z, t_cr = 5.0, np.array([0.06, -0.035, 0.0])
+    shift = np.array([fx * t_cr[0] / Z, fy * t_cr[1] / Z])
+    M = np.array([[1, 0, shift[0]], [0, 1, shift[1]]], np.float64)
+    cur = cv2.warpAffine(ref, M, (w, h), flags=cv2.INTER_LINEAR, borderMode=cv2.BORDER_REFLECT_101)
+    ref2 = textured_frame(w, h, 90 + seed)
+    sc, inv, _ = scale_tables()
+    q_ref = quat_from_rotvec([0.05, -0.08, 0.02]); t_ref = np.array([0.3, -0.2, 0.1], np.float32)
+    q_cr = quat_from_rotvec([0.0, 0.0, 0.004]); t_cr32 = t_cr.astype(np.float32)
+    kfs = [dict(levels=pyramid_of(ref), pose_ref=np.concatenate([q_ref, t_ref]), t_cur_ref=np.concatenate([q_cr, t_cr32]),
+                fx=fx, fy=fy, cx=cx, cy=cy),
+           dict(levels=pyramid_of(ref2), pose_ref=np.concatenate([q_ref, t_ref]), t_cur_ref=np.concatenate([q_cr, t_cr32]),
+                fx=fx / 2.2, fy=fy / 2.2, cx=cx, cy=cy)]
+    q_inv = q_ref * np.array([-1, -1, -1, 1], np.float32)
+    kf_index = (rng.random(n) < 0.15).astype(np.int32)
+    octave = rng.choice(8, size=n, p=[.3, .2, .15, .1, .1, .05, .05, .05]).astype(np.int32)
+    px_ref = np.stack([rng.uniform(30, w - 30, n), rng.uniform(30, h - 30, n)], axis=1).astype(np.float32)
+    px_ref[: n // 20] = np.stack([rng.uniform(0, 12, n // 20), rng.uniform(0, h, n // 20)], axis=1)   # warp leaves the image
+    depth = np.where(rng.random(n) < 0.8, Z, rng.uniform(1.0, 20.0, n))
+    world = np.zeros((n, 3), np.float32); px_curr = np.zeros((n, 2), np.float32)
+    for i in range(n):
+        k = kfs[kf_index[i]]
+        p_ref = np.array([(px_ref[i, 0] - k["cx"]) * depth[i] / k["fx"], (px_ref[i, 1] - k["cy"]) * depth[i] / k["fy"], depth[i]])
+        world[i] = quat_rotate(q_inv, p_ref - t_ref.astype(np.float64))
+        p_cur = quat_rotate(q_cr, p_ref) + t_cr
+        px_curr[i] = [fx * p_cur[0] / p_cur[2] + cx, fy * p_cur[1] / p_cur[2] + cy]
+    px_curr += rng.uniform(-1.5, 1.5, size=(n, 2)).astype(np.float32)
+    px_curr[n // 20: n // 10] = np.stack([rng.uniform(w - 6, w + 5, n // 10 - n // 20), rng.uniform(0, h, n // 10 - n // 20)], axis=1)
+    return dict(kfs=kfs, cur_levels=pyramid_of(cur), cur_intr=np.array([fx, fy, cx, cy], np.float32), scale=sc, inv_scale=inv,
+                inv_sigma2_1=float(np.float32(1.0) / (sc[1] * sc[1])), kf_index=kf_index, px_ref=px_ref, octave=octave,
+                world_pos=world, px_curr=px_curr)
