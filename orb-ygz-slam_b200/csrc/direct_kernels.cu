@@ -57,8 +57,10 @@ int launchDistinctive(const uint8_t *obsDesc, const int32_t *obsStart, int nPoin
 // ---- K14: ORBmatcher::FindDirectProjection, one thread per (MapPoint, reference keyframe) pair.  Everything a point does
 // is sequential float arithmetic whose order fixes the result (the Hessian and Jres sums of Align2D run over the 64 patch
 // pixels in raster order), so a point is not split over lanes; the per-thread patch and gradient arrays live in shared
-// memory, lane-interleaved (element k of lane l at k * 32 + l: conflict-free).  Eigen / Sophus evaluation order as in
-// oracle/direct_oracle.cpp; --fmad=false keeps every product and sum separate.
+// memory, lane-interleaved (element k of lane l at k * 32 + l: conflict-free).  Eigen / Sophus expressions are evaluated the
+// way Eigen 3.3 evaluates them for these fixed sizes: three-term sums as a0 + (a1 + a2), Matrix2f / Matrix3f inverse by the
+// cofactor formulas of Eigen/src/LU/InverseImpl.h, SE3f * point = q._transformVector(p) + t with Eigen's
+// "uv = q.vec x v; uv += uv; v + w * uv + q.vec x uv"; --fmad=false keeps every product and sum separate.
 constexpr int kDirectThreads = 32;
 
 struct DV3 { float x, y, z; };
