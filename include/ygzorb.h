@@ -464,6 +464,37 @@ int ygzorb_find_direct_projection(ygzorb_matcher *m, const ygzorb_direct_keyfram
                                   const int32_t *octave, const float *world_pos, unsigned flags, float *px_curr,
                                   int32_t *search_level, uint8_t *success);
 
+/* SparseImgAlign (include/SparseImageAlign.h, src/SparseImageAlign.cc): sparse direct alignment of the current frame against
+ * the reference frame's features, 4x4 patches, inverse compositional, as Tracking::TrackWithSparseAlignment runs it
+ * (src/Tracking.cc:284, :2171: max_level = nLevels - 1, min_level = 1, Gauss-Newton, 10 iterations per level, unit weights).
+ * A handle owns the class's caches on the device (ref_patch_cache_, jacobian_cache_, visible_fts_) and runs on the matcher's
+ * stream.  Poses are Sophus::SE3f storage (quaternion x, y, z, w, translation).
+ *   ygzorb_sparse_align_begin: what run() sets up (:20-37) — the reference frame's N features: kp_xy[2i..] = mvKeys[i].pt,
+ *     valid[i] = mvpMapPoints[i] && !isBad() && !mvbOutlier[i] (:68-70), world_pos[3i..] = GetWorldPos(), ref_pose =
+ *     ref_frame->mTcw, focal = ref fx, inv_scale_factors = mvInvScaleFactors; clears visible_fts_.
+ *   ygzorb_sparse_align_run: the whole coarse-to-fine optimisation in ONE kernel launch: t_cur_ref in = cur->mTcw *
+ *     ref->mTcw.inverse(), out = TCR; returns through *n_tracked the value run() returns (n_meas_ / patch_area_);
+ *     stats (may be NULL): [0] Gauss-Newton iterations done, [1] final chi2_.
+ *   ygzorb_sparse_align_precompute / _residuals: the two hot loops alone, for a caller that keeps the reference's own
+ *     NLLSSolver<6, SE3f> driver: precomputeReferencePatches() at `level` (:57-128; also zeroes jacobian_cache_ like :42) and
+ *     computeResiduals(model, true) at that level (:130-225): H (6x6 row-major), Jres (6), chi2 SUM (the caller divides by
+ *     n_meas like :224), n_meas.
+ * Per feature the arithmetic is the reference's in its order; across features the sums are reduced by a fixed tree in
+ * double, so H / Jres / chi2 equal the reference's sequential float sums to rounding (rel. ~1e-6), not bit for bit. */
+typedef struct ygzorb_sparse_align ygzorb_sparse_align;
+int ygzorb_sparse_align_create(ygzorb_matcher *m, ygzorb_sparse_align **out);
+void ygzorb_sparse_align_destroy(ygzorb_sparse_align *sa);
+int ygzorb_sparse_align_begin(ygzorb_sparse_align *sa, const ygzorb_pyramid *ref, const ygzorb_pyramid *cur, int n,
+                              const float *kp_xy, const uint8_t *valid, const float *world_pos, const float *ref_pose,
+                              float focal, const float *cur_intrinsics, const float *inv_scale_factors);
+int ygzorb_sparse_align_run(ygzorb_sparse_align *sa, int max_level, int min_level, float *t_cur_ref, int64_t *n_tracked,
+                            float *stats);
+int ygzorb_sparse_align_precompute(ygzorb_sparse_align *sa, int level);
+int ygzorb_sparse_align_residuals(ygzorb_sparse_align *sa, int level, const float *t_cur_ref, float *h36, float *jres6,
+                                  float *chi2_sum, int64_t *n_meas);
+/* host copies of the caches after precompute (any may be NULL): visible[n], ref_patch[n*16], jacobian[n*16*6] */
+int ygzorb_sparse_align_caches(ygzorb_sparse_align *sa, uint8_t *visible, float *ref_patch, float *jacobian);
+
 #ifdef __cplusplus
 }
 #endif

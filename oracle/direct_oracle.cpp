@@ -219,3 +219,237 @@ YGZO_API void ygzo_find_direct_projection(const YgzoDirectKeyFrame *kfs, int nKf
         success[i] = ok ? 1 : 0;
     }
 }
+
+// =====================================================================================================================
+// SparseImgAlign (src/SparseImageAlign.cc:20-256, include/SparseImageAlign.h:95-116) driven by NLLSSolver<6, SE3f>::
+// optimizeGaussNewton (include/NLSSolver_impl.hpp:17-92), as Tracking::TrackWithSparseAlignment runs it
+// (src/Tracking.cc:284, :2171: max_level = nLevels - 1, min_level = 1, 10 iterations per level, Gauss-Newton, no robust
+// weights, no prior).  Sums over features are sequential in float like the reference's H_ / Jres_ / chi2 (accumulate = 0) or,
+// for the comparison with the device's tree reduction, in double over per-feature float partials (accumulate = 1).
+// Sophus pieces (Thirdparty/sophus/sophus/se3.hpp:239-271, 407-428, so3.hpp:268-276, 426-456) restated on (q, t) storage;
+// H_.ldlt().solve(Jres_) as a diagonally pivoted LDL^T (Eigen/src/Cholesky/LDLT.h).
+namespace {
+struct Se3 { float q[4]; float t[3]; };   // q = x y z w
+inline Se3 se3Load(const float *p) { Se3 T; std::memcpy(T.q, p, 16); std::memcpy(T.t, p + 4, 12); return T; }
+inline void se3Store(const Se3 &T, float *p) { std::memcpy(p, T.q, 16); std::memcpy(p + 4, T.t, 12); }
+inline V3 se3Apply(const Se3 &T, const V3 &v) { float b[7]; se3Store(T, b); return se3Mul(b, v); }
+Se3 se3Compose(const Se3 &A, const Se3 &B) {   // A *= B: fastMultiply (translation first, then quaternion product) + normalize
+    Se3 R;
+    const V3 rt = [&] { float b[7]; Se3 Rot = A; Rot.t[0] = Rot.t[1] = Rot.t[2] = 0; se3Store(Rot, b); return se3Mul(b, V3{B.t[0], B.t[1], B.t[2]}); }();
+    R.t[0] = A.t[0] + rt.x; R.t[1] = A.t[1] + rt.y; R.t[2] = A.t[2] + rt.z;
+    const float ax = A.q[0], ay = A.q[1], az = A.q[2], aw = A.q[3], bx = B.q[0], by = B.q[1], bz = B.q[2], bw = B.q[3];
+    float q[4] = {aw * bx + ax * bw + ay * bz - az * by, aw * by + ay * bw + az * bx - ax * bz, aw * bz + az * bw + ax * by - ay * bx,
+                  aw * bw - ax * bx - ay * by - az * bz};
+    const float len = std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+    for (int i = 0; i < 4; i++) R.q[i] = q[i] / len;
+    return R;
+}
+Se3 se3Exp(const float *a) {   // a = (upsilon, omega)
+    const float wx = a[3], wy = a[4], wz = a[5];
+    const float thetaSq = wx * wx + wy * wy + wz * wz, theta = std::sqrt(thetaSq), half = 0.5f * theta;
+    const float eps = 1e-5f;   // SophusConstants<float>::epsilon()
+    float imag, real;
+    if (theta < eps) {
+        const float po4 = thetaSq * thetaSq;
+        imag = 0.5f - (float)(1.0 / 48.0) * thetaSq + (float)(1.0 / 3840.0) * po4;
+        real = 1.0f - 0.5f * thetaSq + (float)(1.0 / 384.0) * po4;
+    } else {
+        imag = std::sin(half) / theta; real = std::cos(half);
+    }
+    Se3 T;
+    T.q[0] = imag * wx; T.q[1] = imag * wy; T.q[2] = imag * wz; T.q[3] = real;
+    const float O[3][3] = {{0, -wz, wy}, {wz, 0, -wx}, {-wy, wx, 0}};
+    float O2[3][3], V[3][3];
+    for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) O2[r][c] = sum3(O[r][0] * O[0][c], O[r][1] * O[1][c], O[r][2] * O[2][c]);
+    if (theta < eps) {   // V = so3.matrix()
+        const float x = T.q[0], y = T.q[1], z = T.q[2], w = T.q[3];
+        const float M[3][3] = {{1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)},
+                               {2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)},
+                               {2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)}};
+        std::memcpy(V, M, sizeof V);
+    } else {
+        const float A = (1.0f - std::cos(theta)) / thetaSq, B = (theta - std::sin(theta)) / (thetaSq * theta);
+        for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) V[r][c] = ((r == c ? 1.0f : 0.0f) + A * O[r][c]) + B * O2[r][c];
+    }
+    for (int r = 0; r < 3; r++) T.t[r] = sum3(V[r][0] * a[0], V[r][1] * a[1], V[r][2] * a[2]);
+    return T;
+}
+// x = H.ldlt().solve(b), 6 x 6: LDL^T with the largest remaining diagonal entry as pivot
+void ldltSolve6(const float *Hin, const float *b, float *x) {
+    const int n = 6;
+    float A[6][6]; int perm[6];
+    for (int r = 0; r < n; r++) { perm[r] = r; for (int c = 0; c < n; c++) A[r][c] = Hin[r * 6 + c]; }
+    for (int k = 0; k < n; k++) {
+        int p = k;
+        for (int i = k + 1; i < n; i++) if (std::fabs(A[i][i]) > std::fabs(A[p][p])) p = i;
+        if (p != k) {
+            for (int c = 0; c < n; c++) std::swap(A[k][c], A[p][c]);
+            for (int r = 0; r < n; r++) std::swap(A[r][k], A[r][p]);
+            std::swap(perm[k], perm[p]);
+        }
+        float d = A[k][k];
+        for (int j = 0; j < k; j++) d -= A[k][j] * A[k][j] * A[j][j];
+        A[k][k] = d;
+        for (int i = k + 1; i < n; i++) {
+            float v = A[i][k];
+            for (int j = 0; j < k; j++) v -= A[i][j] * A[k][j] * A[j][j];
+            A[i][k] = d != 0 ? v / d : v;
+        }
+    }
+    float y[6];
+    for (int i = 0; i < n; i++) { float v = b[perm[i]]; for (int j = 0; j < i; j++) v -= A[i][j] * y[j]; y[i] = v; }
+    for (int i = 0; i < n; i++) y[i] = std::fabs(A[i][i]) > 1.17549435e-38f ? y[i] / A[i][i] : 0.0f;
+    for (int i = n - 1; i >= 0; i--) { float v = y[i]; for (int j = i + 1; j < n; j++) v -= A[j][i] * y[j]; y[i] = v; }
+    for (int i = 0; i < n; i++) x[perm[i]] = y[i];
+}
+
+struct SparseAlignState {
+    int n = 0;
+    std::vector<float> refPatch;   // ref_patch_cache_, n x 16 (persists over the levels of a run)
+    std::vector<float> jac;        // jacobian_cache_, n x 16 x 6 (zeroed per level)
+    std::vector<uint8_t> visible;  // visible_fts_ (set per level, never cleared inside a run)
+};
+
+// SparseImgAlign::precomputeReferencePatches (src/SparseImageAlign.cc:57-128) at one level
+void precomputeRef(SparseAlignState &S, const uint8_t *img, int cols, int rows, int stride, float scale, float focal, const float *refPose,
+                   const float *kpXY, const uint8_t *valid, const float *worldPos) {
+    const int border = 3, half = 2, size = 4;
+    for (int i = 0; i < S.n; i++) {
+        if (!valid[i]) continue;
+        const float u = kpXY[2 * i] * scale, v = kpXY[2 * i + 1] * scale;
+        const int ui = (int)floorf(u), vi = (int)floorf(v);
+        if (ui - border < 0 || vi - border < 0 || ui + border >= cols || vi + border >= rows) continue;
+        S.visible[i] = 1;
+        const V3 p = se3Mul(refPose, V3{worldPos[3 * i], worldPos[3 * i + 1], worldPos[3 * i + 2]});
+        // JacobXYZ2Cam (include/SparseImageAlign.h:95-116)
+        float J[2][6];
+        const float x = p.x, y = p.y, zInv = (float)(1. / p.z), zInv2 = zInv * zInv;
+        J[0][0] = -zInv; J[0][1] = 0.0f; J[0][2] = x * zInv2; J[0][3] = y * J[0][2]; J[0][4] = (float)(-(1.0 + x * J[0][2])); J[0][5] = y * zInv;
+        J[1][0] = 0.0f; J[1][1] = -zInv; J[1][2] = y * zInv2; J[1][3] = (float)(1.0 + y * J[1][2]); J[1][4] = -J[0][3]; J[1][5] = -x * zInv;
+        const float su = u - ui, sv = v - vi;
+        const float wTL = (1.0 - su) * (1.0 - sv), wTR = su * (1.0 - sv), wBL = (1.0 - su) * sv, wBR = su * sv;
+        const float fs = focal * scale;
+        int k = 0;
+        for (int yy = 0; yy < size; ++yy) {
+            const uint8_t *r = img + (long)(vi + yy - half) * stride + (ui - half);
+            for (int xx = 0; xx < size; ++xx, ++r, ++k) {
+                S.refPatch[i * 16 + k] = wTL * r[0] + wTR * r[1] + wBL * r[stride] + wBR * r[stride + 1];
+                const float dx = 0.5f * ((wTL * r[1] + wTR * r[2] + wBL * r[stride + 1] + wBR * r[stride + 2]) -
+                                         (wTL * r[-1] + wTR * r[0] + wBL * r[stride - 1] + wBR * r[stride]));
+                const float dy = 0.5f * ((wTL * r[stride] + wTR * r[1 + stride] + wBL * r[stride * 2] + wBR * r[stride * 2 + 1]) -
+                                         (wTL * r[-stride] + wTR * r[1 - stride] + wBL * r[0] + wBR * r[1]));
+                for (int c = 0; c < 6; c++) S.jac[(i * 16 + k) * 6 + c] = (dx * J[0][c] + dy * J[1][c]) * fs;
+            }
+        }
+    }
+}
+
+// SparseImgAlign::computeResiduals (:130-225) with linearize_system, unit weights.  Returns the chi2 SUM; *nMeas counts.
+template <class Acc> float computeRes(const SparseAlignState &S, const uint8_t *cur, int cols, int rows, int stride, float scale,
+                                      const float *curIntr, const float *refPose, const float *tCurRef, const float *worldPos,
+                                      float *H36, float *Jres6, long *nMeas) {
+    const int border = 3, half = 2, size = 4;
+    Acc H[6][6], Jr[6], chi2 = 0;
+    for (int r = 0; r < 6; r++) { Jr[r] = 0; for (int c = 0; c < 6; c++) H[r][c] = 0; }
+    long meas = 0;
+    const bool perFeature = sizeof(Acc) == sizeof(double);
+    for (int i = 0; i < S.n; i++) {
+        if (!S.visible[i]) continue;
+        const V3 pr = se3Mul(refPose, V3{worldPos[3 * i], worldPos[3 * i + 1], worldPos[3 * i + 2]});
+        const V3 pc = se3Mul(tCurRef, pr);
+        const float uc = (curIntr[0] * pc.x / pc.z + curIntr[2]) * scale, vc = (curIntr[1] * pc.y / pc.z + curIntr[3]) * scale;
+        const int ui = (int)floorf(uc), vi = (int)floorf(vc);
+        if (ui < 0 || vi < 0 || ui - border < 0 || vi - border < 0 || ui + border >= cols || vi + border >= rows) continue;
+        const float su = uc - ui, sv = vc - vi;
+        const float wTL = (1.0 - su) * (1.0 - sv), wTR = su * (1.0 - sv), wBL = (1.0 - su) * sv, wBR = su * sv;
+        float fH[6][6], fJ[6], fChi = 0;   // per-feature float partials (accumulate = 1)
+        for (int r = 0; r < 6; r++) { fJ[r] = 0; for (int c = 0; c < 6; c++) fH[r][c] = 0; }
+        int k = 0;
+        for (int yy = 0; yy < size; ++yy) {
+            const uint8_t *p = cur + (long)(vi + yy - half) * stride + (ui - half);
+            for (int xx = 0; xx < size; ++xx, ++k, ++p) {
+                const float inten = wTL * p[0] + wTR * p[1] + wBL * p[stride] + wBR * p[stride + 1];
+                const float res = inten - S.refPatch[i * 16 + k];
+                const float *J = &S.jac[(i * 16 + k) * 6];
+                meas++;
+                if (perFeature) {
+                    fChi += res * res * 1.0f;
+                    for (int r = 0; r < 6; r++) { fJ[r] -= J[r] * res * 1.0f; for (int c = 0; c < 6; c++) fH[r][c] += J[r] * J[c] * 1.0f; }
+                } else {
+                    chi2 += res * res * 1.0f;
+                    for (int r = 0; r < 6; r++) { Jr[r] -= J[r] * res * 1.0f; for (int c = 0; c < 6; c++) H[r][c] += J[r] * J[c] * 1.0f; }
+                }
+            }
+        }
+        if (perFeature) {
+            chi2 += fChi;
+            for (int r = 0; r < 6; r++) { Jr[r] += fJ[r]; for (int c = 0; c < 6; c++) H[r][c] += fH[r][c]; }
+        }
+    }
+    for (int r = 0; r < 6; r++) { Jres6[r] = (float)Jr[r]; for (int c = 0; c < 6; c++) H36[r * 6 + c] = (float)H[r][c]; }
+    *nMeas = meas;
+    return (float)chi2;
+}
+}  // namespace
+
+struct YgzoPyramid { const uint8_t *levels[8]; int32_t w[8], h[8], pitch[8]; };
+
+// One computeResiduals call at `level` after precomputeReferencePatches at that level on a fresh state (unit test of the two
+// hot loops).  Outputs H (36), Jres (6), chi2 sum, n_meas, visible[n], refPatch[n*16], jac[n*96].
+YGZO_API void ygzo_sparse_align_residuals(const YgzoPyramid *ref, const YgzoPyramid *cur, int level, float scale, float focal,
+                                          const float *curIntr, const float *refPose, const float *tCurRef, int n, const float *kpXY,
+                                          const uint8_t *valid, const float *worldPos, int accumulate, float *H36, float *Jres6,
+                                          float *chi2, int64_t *nMeas, uint8_t *visible, float *refPatch, float *jac) {
+    SparseAlignState S;
+    S.n = n; S.refPatch.assign((size_t)n * 16, 0.f); S.jac.assign((size_t)n * 96, 0.f); S.visible.assign(n, 0);
+    precomputeRef(S, ref->levels[level], ref->w[level], ref->h[level], ref->pitch[level], scale, focal, refPose, kpXY, valid, worldPos);
+    long m = 0;
+    *chi2 = accumulate ? computeRes<double>(S, cur->levels[level], cur->w[level], cur->h[level], cur->pitch[level], scale, curIntr, refPose, tCurRef, worldPos, H36, Jres6, &m)
+                       : computeRes<float>(S, cur->levels[level], cur->w[level], cur->h[level], cur->pitch[level], scale, curIntr, refPose, tCurRef, worldPos, H36, Jres6, &m);
+    *nMeas = m;
+    if (visible) std::memcpy(visible, S.visible.data(), n);
+    if (refPatch) std::memcpy(refPatch, S.refPatch.data(), (size_t)n * 64);
+    if (jac) std::memcpy(jac, S.jac.data(), (size_t)n * 384);
+}
+
+// SparseImgAlign::run (:20-55): tCurRef in = cur->mTcw * ref->mTcw.inverse(), out = TCR.  Returns n_meas_ / patch_area_.
+// stats (may be NULL): [0] total iterations, [1] final chi2_ (mean).
+YGZO_API int64_t ygzo_sparse_align_run(const YgzoPyramid *ref, const YgzoPyramid *cur, int maxLevel, int minLevel, const float *invScale,
+                                       float focal, const float *curIntr, const float *refPose, int n, const float *kpXY,
+                                       const uint8_t *valid, const float *worldPos, int accumulate, float *tCurRef, float *stats) {
+    SparseAlignState S;
+    S.n = n; S.refPatch.assign((size_t)n * 16, 0.f); S.jac.assign((size_t)n * 96, 0.f); S.visible.assign(n, 0);
+    if (n == 0) return 0;   // "no features to track" (:24-27)
+    Se3 model = se3Load(tCurRef);
+    float chi2_ = 1e10f;      // reset() (include/NLSSolver_impl.hpp:289-298)
+    bool stop = false;
+    long nMeas = 0, iters = 0;
+    const float eps = 0.000001f;
+    for (int level = maxLevel; level >= minLevel; level -= 1) {
+        std::fill(S.jac.begin(), S.jac.end(), 0.f);
+        precomputeRef(S, ref->levels[level], ref->w[level], ref->h[level], ref->pitch[level], invScale[level], focal, refPose, kpXY, valid, worldPos);
+        Se3 oldModel = model;
+        for (int iter = 0; iter < 10; ++iter) {
+            float H[36], Jres[6], T[7], x[6];
+            se3Store(model, T);
+            const float sum = accumulate ? computeRes<double>(S, cur->levels[level], cur->w[level], cur->h[level], cur->pitch[level], invScale[level], curIntr, refPose, T, worldPos, H, Jres, &nMeas)
+                                         : computeRes<float>(S, cur->levels[level], cur->w[level], cur->h[level], cur->pitch[level], invScale[level], curIntr, refPose, T, worldPos, H, Jres, &nMeas);
+            const float newChi2 = sum / nMeas;
+            iters++;
+            ldltSolve6(H, Jres, x);
+            if (std::isnan(x[0])) stop = true;
+            if ((iter > 0 && newChi2 > 1.2 * chi2_) || stop) { model = oldModel; break; }
+            float mx[6];
+            for (int i = 0; i < 6; i++) mx[i] = -x[i];
+            const Se3 newModel = se3Compose(model, se3Exp(mx));
+            oldModel = model; model = newModel;
+            chi2_ = newChi2;
+            float nm = -1;
+            for (int i = 0; i < 6; i++) nm = std::max(nm, std::fabs(x[i]));
+            if (nm <= eps) break;
+        }
+    }
+    se3Store(model, tCurRef);
+    if (stats) { stats[0] = (float)iters; stats[1] = chi2_; }
+    return nMeas / 16;
+}

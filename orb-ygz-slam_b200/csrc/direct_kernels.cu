@@ -206,4 +206,267 @@ int launchFindDirectProjection(const DirectArgs &A, cudaStream_t s) {
     return 1;
 }
 
+// ---- K15: SparseImgAlign (src/SparseImageAlign.cc) — the two hot loops as device functions, used by the step kernels
+// (precomputeReferencePatches / computeResiduals behind the reference's own NLLSSolver driver) and by the fused kernel that
+// runs the whole coarse-to-fine Gauss-Newton of SparseImgAlign::run in one launch.  One CTA: a frame has at most a few
+// thousand features x 16 pixels, far too little to split across SMs once every iteration ends in a 6 x 6 solve.
+// Per feature the arithmetic is the reference's, in its order, in float; ACROSS features the 21 + 6 + 1 sums are reduced by a
+// fixed tree in double (deterministic; the reference adds them up one after the other in float), so H, Jres and chi2 agree
+// with the sequential float sums to rounding, not bit for bit.
+constexpr int kAlignThreads = 512, kAlignSums = 29;   // 21 upper-triangle H + 6 Jres + chi2 + n_meas
+
+__device__ void alignPrecompute(const SparseAlignArgs &A, int level, const uint8_t *img, int cols, int rows, int stride, float scale) {
+    for (int i = threadIdx.x; i < A.n; i += blockDim.x) {
+        float *jac = A.jac + (size_t)i * 96;
+        for (int k = 0; k < 96; k++) jac[k] = 0.0f;                    // jacobian_cache_.setZero() (:42)
+        if (!A.valid[i]) continue;
+        const float u = A.kpXY[2 * i] * scale, v = A.kpXY[2 * i + 1] * scale;
+        const int ui = (int)floorf(u), vi = (int)floorf(v);
+        if (ui - 3 < 0 || vi - 3 < 0 || ui + 3 >= cols || vi + 3 >= rows) continue;
+        A.visible[i] = 1;
+        const DV3 p = dSe3Mul(A.refPose, DV3{A.worldPos[3 * i], A.worldPos[3 * i + 1], A.worldPos[3 * i + 2]});
+        float J[2][6];
+        const float x = p.x, y = p.y, zInv = (float)(1. / (double)p.z), zInv2 = zInv * zInv;
+        J[0][0] = -zInv; J[0][1] = 0.0f; J[0][2] = x * zInv2; J[0][3] = y * J[0][2]; J[0][4] = (float)(-(1.0 + (double)(x * J[0][2]))); J[0][5] = y * zInv;
+        J[1][0] = 0.0f; J[1][1] = -zInv; J[1][2] = y * zInv2; J[1][3] = (float)(1.0 + (double)(y * J[1][2])); J[1][4] = -J[0][3]; J[1][5] = -x * zInv;
+        const float su = u - (float)ui, sv = v - (float)vi;
+        const float wTL = (float)((1.0 - su) * (1.0 - sv)), wTR = (float)(su * (1.0 - sv)), wBL = (float)((1.0 - su) * sv), wBR = su * sv;
+        const float fs = A.focal * scale;
+        int k = 0;
+        for (int yy = 0; yy < 4; ++yy) {
+            const uint8_t *r = img + (long long)(vi + yy - 2) * stride + (ui - 2);
+            for (int xx = 0; xx < 4; ++xx, ++r, ++k) {
+                A.refPatch[(size_t)i * 16 + k] = ((wTL * r[0] + wTR * r[1]) + wBL * r[stride]) + wBR * r[stride + 1];
+                const float dx = 0.5f * ((((wTL * r[1] + wTR * r[2]) + wBL * r[stride + 1]) + wBR * r[stride + 2]) -
+                                         (((wTL * r[-1] + wTR * r[0]) + wBL * r[stride - 1]) + wBR * r[stride]));
+                const float dy = 0.5f * ((((wTL * r[stride] + wTR * r[1 + stride]) + wBL * r[stride * 2]) + wBR * r[stride * 2 + 1]) -
+                                         (((wTL * r[-stride] + wTR * r[1 - stride]) + wBL * r[0]) + wBR * r[1]));
+#pragma unroll
+                for (int c = 0; c < 6; c++) jac[k * 6 + c] = (dx * J[0][c] + dy * J[1][c]) * fs;
+            }
+        }
+    }
+}
+
+// computeResiduals (:130-225): this thread's features -> acc[29] (float partials per feature, added up in double)
+__device__ void alignResiduals(const SparseAlignArgs &A, const float *T, const uint8_t *cur, int cols, int rows, int stride, float scale,
+                               double *acc) {
+#pragma unroll
+    for (int k = 0; k < kAlignSums; k++) acc[k] = 0.0;
+    for (int i = threadIdx.x; i < A.n; i += blockDim.x) {
+        if (!A.visible[i]) continue;
+        const DV3 pr = dSe3Mul(A.refPose, DV3{A.worldPos[3 * i], A.worldPos[3 * i + 1], A.worldPos[3 * i + 2]});
+        const DV3 pc = dSe3Mul(T, pr);
+        const float uc = (A.fx * pc.x / pc.z + A.cx) * scale, vc = (A.fy * pc.y / pc.z + A.cy) * scale;
+        const int ui = (int)floorf(uc), vi = (int)floorf(vc);
+        if (ui < 0 || vi < 0 || ui - 3 < 0 || vi - 3 < 0 || ui + 3 >= cols || vi + 3 >= rows) continue;
+        const float su = uc - (float)ui, sv = vc - (float)vi;
+        const float wTL = (float)((1.0 - su) * (1.0 - sv)), wTR = (float)(su * (1.0 - sv)), wBL = (float)((1.0 - su) * sv), wBR = su * sv;
+        float f[kAlignSums - 1];
+#pragma unroll
+        for (int k = 0; k < kAlignSums - 1; k++) f[k] = 0.0f;
+        int k = 0;
+        for (int yy = 0; yy < 4; ++yy) {
+            const uint8_t *p = cur + (long long)(vi + yy - 2) * stride + (ui - 2);
+            for (int xx = 0; xx < 4; ++xx, ++k, ++p) {
+                const float inten = ((wTL * p[0] + wTR * p[1]) + wBL * p[stride]) + wBR * p[stride + 1];
+                const float res = inten - A.refPatch[(size_t)i * 16 + k];
+                const float *Jp = A.jac + ((size_t)i * 16 + k) * 6;
+                float J[6];
+#pragma unroll
+                for (int c = 0; c < 6; c++) J[c] = Jp[c];
+                f[27] += res * res;
+                int q = 0;
+#pragma unroll
+                for (int r = 0; r < 6; r++) {
+                    f[21 + r] -= J[r] * res;
+#pragma unroll
+                    for (int c = r; c < 6; c++) f[q++] += J[r] * J[c];
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < kAlignSums - 1; q++) acc[q] += (double)f[q];
+        acc[28] += 16.0;
+    }
+}
+
+// block-wide fixed-order tree sum of acc[29] -> sums[29] in shared memory (valid after the trailing barrier)
+__device__ void alignReduce(double *acc, double *warpBuf, double *sums) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+#pragma unroll
+    for (int k = 0; k < kAlignSums; k++) {
+        double v = acc[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if (lane == 0) warpBuf[wid * kAlignSums + k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < kAlignSums) {
+        double v = 0.0;
+        for (int w = 0; w < nw; w++) v += warpBuf[w * kAlignSums + threadIdx.x];
+        sums[threadIdx.x] = v;
+    }
+    __syncthreads();
+}
+
+__device__ void alignUnpack(const double *sums, float *H36, float *Jres6) {
+    int q = 0;
+    for (int r = 0; r < 6; r++)
+        for (int c = r; c < 6; c++) { H36[r * 6 + c] = H36[c * 6 + r] = (float)sums[q++]; }
+    for (int r = 0; r < 6; r++) Jres6[r] = (float)sums[21 + r];
+}
+
+__global__ void __launch_bounds__(kAlignThreads) k_sparse_align_precompute(const __grid_constant__ SparseAlignArgs A, int level) {
+    alignPrecompute(A, level, A.refLv[level], A.w[level], A.h[level], A.refPitch[level], A.invScale[level]);
+}
+
+// out: H (36), Jres (6), chi2 sum, n_meas
+__global__ void __launch_bounds__(kAlignThreads) k_sparse_align_residuals(const __grid_constant__ SparseAlignArgs A, int level, float *out) {
+    __shared__ double warpBuf[(kAlignThreads / 32) * kAlignSums], sums[kAlignSums];
+    __shared__ float T[7];
+    if (threadIdx.x < 7) T[threadIdx.x] = A.tCurRef[threadIdx.x];
+    __syncthreads();
+    double acc[kAlignSums];
+    alignResiduals(A, T, A.curLv[level], A.w[level], A.h[level], A.curPitch[level], A.invScale[level], acc);
+    alignReduce(acc, warpBuf, sums);
+    if (threadIdx.x == 0) { alignUnpack(sums, out, out + 36); out[42] = (float)sums[27]; out[43] = (float)sums[28]; }
+}
+
+// ---- host-free Gauss-Newton driver pieces (thread 0): Sophus SE3f on (q, t) storage and H.ldlt().solve(b)
+__device__ void dSe3Compose(const float *A, const float *B, float *R) {   // SE3Group::operator*= : fastMultiply + normalize
+    float rot[7] = {A[0], A[1], A[2], A[3], 0.f, 0.f, 0.f};
+    const DV3 rt = dSe3Mul(rot, DV3{B[4], B[5], B[6]});
+    const float ax = A[0], ay = A[1], az = A[2], aw = A[3], bx = B[0], by = B[1], bz = B[2], bw = B[3];
+    const float q0 = aw * bx + ax * bw + ay * bz - az * by, q1 = aw * by + ay * bw + az * bx - ax * bz;
+    const float q2 = aw * bz + az * bw + ax * by - ay * bx, q3 = aw * bw - ax * bx - ay * by - az * bz;
+    const float len = sqrtf(q0 * q0 + q1 * q1 + q2 * q2 + q3 * q3);
+    R[4] = A[4] + rt.x; R[5] = A[5] + rt.y; R[6] = A[6] + rt.z;
+    R[0] = q0 / len; R[1] = q1 / len; R[2] = q2 / len; R[3] = q3 / len;
+}
+__device__ void dSe3Exp(const float *a, float *T) {   // SE3Group::exp (se3.hpp:407-428), SO3Group::expAndTheta (so3.hpp:426-456)
+    const float wx = a[3], wy = a[4], wz = a[5];
+    const float thetaSq = wx * wx + wy * wy + wz * wz, theta = sqrtf(thetaSq), half = 0.5f * theta;
+    const float eps = 1e-5f;
+    float imag, real;
+    if (theta < eps) {
+        const float po4 = thetaSq * thetaSq;
+        imag = 0.5f - (float)(1.0 / 48.0) * thetaSq + (float)(1.0 / 3840.0) * po4;
+        real = 1.0f - 0.5f * thetaSq + (float)(1.0 / 384.0) * po4;
+    } else {
+        imag = (float)sin((double)half) / theta; real = (float)cos((double)half);
+    }
+    T[0] = imag * wx; T[1] = imag * wy; T[2] = imag * wz; T[3] = real;
+    const float O[3][3] = {{0, -wz, wy}, {wz, 0, -wx}, {-wy, wx, 0}};
+    float V[3][3];
+    if (theta < eps) {
+        const float x = T[0], y = T[1], z = T[2], w = T[3];
+        V[0][0] = 1 - 2 * (y * y + z * z); V[0][1] = 2 * (x * y - z * w); V[0][2] = 2 * (x * z + y * w);
+        V[1][0] = 2 * (x * y + z * w); V[1][1] = 1 - 2 * (x * x + z * z); V[1][2] = 2 * (y * z - x * w);
+        V[2][0] = 2 * (x * z - y * w); V[2][1] = 2 * (y * z + x * w); V[2][2] = 1 - 2 * (x * x + y * y);
+    } else {
+        const float Ac = (1.0f - (float)cos((double)theta)) / thetaSq, Bc = (theta - (float)sin((double)theta)) / (thetaSq * theta);
+        for (int r = 0; r < 3; r++)
+            for (int c = 0; c < 3; c++) {
+                const float o2 = dSum3(O[r][0] * O[0][c], O[r][1] * O[1][c], O[r][2] * O[2][c]);
+                V[r][c] = ((r == c ? 1.0f : 0.0f) + Ac * O[r][c]) + Bc * o2;
+            }
+    }
+    for (int r = 0; r < 3; r++) T[4 + r] = dSum3(V[r][0] * a[0], V[r][1] * a[1], V[r][2] * a[2]);
+}
+__device__ void dLdltSolve6(const float *Hin, const float *b, float *x) {   // LDL^T, largest remaining diagonal entry as pivot
+    float A[6][6]; int perm[6];
+    for (int r = 0; r < 6; r++) { perm[r] = r; for (int c = 0; c < 6; c++) A[r][c] = Hin[r * 6 + c]; }
+    for (int k = 0; k < 6; k++) {
+        int p = k;
+        for (int i = k + 1; i < 6; i++) if (fabsf(A[i][i]) > fabsf(A[p][p])) p = i;
+        if (p != k) {
+            for (int c = 0; c < 6; c++) { const float t = A[k][c]; A[k][c] = A[p][c]; A[p][c] = t; }
+            for (int r = 0; r < 6; r++) { const float t = A[r][k]; A[r][k] = A[r][p]; A[r][p] = t; }
+            const int t = perm[k]; perm[k] = perm[p]; perm[p] = t;
+        }
+        float d = A[k][k];
+        for (int j = 0; j < k; j++) d -= A[k][j] * A[k][j] * A[j][j];
+        A[k][k] = d;
+        for (int i = k + 1; i < 6; i++) {
+            float v = A[i][k];
+            for (int j = 0; j < k; j++) v -= A[i][j] * A[k][j] * A[j][j];
+            A[i][k] = d != 0 ? v / d : v;
+        }
+    }
+    float y[6];
+    for (int i = 0; i < 6; i++) { float v = b[perm[i]]; for (int j = 0; j < i; j++) v -= A[i][j] * y[j]; y[i] = v; }
+    for (int i = 0; i < 6; i++) y[i] = fabsf(A[i][i]) > 1.17549435e-38f ? y[i] / A[i][i] : 0.0f;
+    for (int i = 5; i >= 0; i--) { float v = y[i]; for (int j = i + 1; j < 6; j++) v -= A[j][i] * y[j]; y[i] = v; }
+    for (int i = 0; i < 6; i++) x[perm[i]] = y[i];
+}
+
+// SparseImgAlign::run (:20-55) + NLLSSolver::optimizeGaussNewton (include/NLSSolver_impl.hpp:17-92) in one launch.
+// out: TCR (7), n_meas (as float), iterations, final chi2_
+__global__ void __launch_bounds__(kAlignThreads) k_sparse_align_run(const __grid_constant__ SparseAlignArgs A, int maxLevel, int minLevel,
+                                                                    float *out) {
+    __shared__ double warpBuf[(kAlignThreads / 32) * kAlignSums], sums[kAlignSums];
+    __shared__ float model[7], oldModel[7];
+    __shared__ int brk;
+    __shared__ float chi2S, nMeasS, itersS;
+    __shared__ int stopS;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < A.n; i += blockDim.x) A.visible[i] = 0;          // visible_fts_ = vector<bool>(N, false) (:34)
+    if (tid < 7) model[tid] = A.tCurRef[tid];
+    if (tid == 0) { chi2S = 1e10f; nMeasS = 0.f; itersS = 0.f; stopS = 0; }
+    __syncthreads();
+    for (int level = maxLevel; level >= minLevel; --level) {
+        alignPrecompute(A, level, A.refLv[level], A.w[level], A.h[level], A.refPitch[level], A.invScale[level]);
+        if (tid < 7) oldModel[tid] = model[tid];
+        __syncthreads();
+        for (int iter = 0; iter < 10; ++iter) {
+            double acc[kAlignSums];
+            alignResiduals(A, model, A.curLv[level], A.w[level], A.h[level], A.curPitch[level], A.invScale[level], acc);
+            alignReduce(acc, warpBuf, sums);
+            if (tid == 0) {
+                float H[36], Jres[6], x[6];
+                alignUnpack(sums, H, Jres);
+                const float nMeas = (float)sums[28];
+                const float newChi2 = (float)sums[27] / nMeas;
+                nMeasS = nMeas; itersS += 1.0f;
+                dLdltSolve6(H, Jres, x);
+                if (isnan(x[0])) stopS = 1;
+                brk = 0;
+                if ((iter > 0 && (double)newChi2 > 1.2 * (double)chi2S) || stopS) {
+                    for (int k = 0; k < 7; k++) model[k] = oldModel[k];       // rollback
+                    brk = 1;
+                } else {
+                    float mx[6], E[7], N[7];
+                    for (int k = 0; k < 6; k++) mx[k] = -x[k];
+                    dSe3Exp(mx, E);
+                    dSe3Compose(model, E, N);
+                    for (int k = 0; k < 7; k++) { oldModel[k] = model[k]; model[k] = N[k]; }
+                    chi2S = newChi2;
+                    float nm = -1.0f;
+                    for (int k = 0; k < 6; k++) nm = fmaxf(nm, fabsf(x[k]));
+                    if (nm <= 0.000001f) brk = 1;
+                }
+            }
+            __syncthreads();
+            if (brk) break;
+        }
+        __syncthreads();
+    }
+    if (tid < 7) out[tid] = model[tid];
+    if (tid == 0) { out[7] = nMeasS; out[8] = itersS; out[9] = chi2S; }
+}
+
+int launchSparseAlignPrecompute(const SparseAlignArgs &A, int level, cudaStream_t s) {
+    k_sparse_align_precompute<<<1, kAlignThreads, 0, s>>>(A, level);
+    return 1;
+}
+int launchSparseAlignResiduals(const SparseAlignArgs &A, int level, float *out, cudaStream_t s) {
+    k_sparse_align_residuals<<<1, kAlignThreads, 0, s>>>(A, level, out);
+    return 1;
+}
+int launchSparseAlignRun(const SparseAlignArgs &A, int maxLevel, int minLevel, float *out, cudaStream_t s) {
+    k_sparse_align_run<<<1, kAlignThreads, 0, s>>>(A, maxLevel, minLevel, out);
+    return 1;
+}
+
 }  // namespace ygz

@@ -797,6 +797,169 @@ int ygzorb_find_direct_projection(ygzorb_matcher *h, const ygzorb_direct_keyfram
     return finish(m, flags);
 }
 
+namespace ygz {
+struct SparseAlign {
+    Matcher *m = nullptr;
+    SparseAlignArgs A;
+    int cap = 0, nLevels = 0;
+    float *dKp = nullptr, *dWorld = nullptr, *dPose = nullptr, *dOut = nullptr, *dPatch = nullptr, *dJac = nullptr;
+    uint8_t *dValid = nullptr, *dVisible = nullptr;
+    float *hOut = nullptr;   // pinned
+    bool begun = false;
+};
+static void sparseAlignFree(SparseAlign *S) {
+    for (void *p : {(void *)S->dKp, (void *)S->dWorld, (void *)S->dPatch, (void *)S->dJac, (void *)S->dValid, (void *)S->dVisible})
+        if (p) cudaFree(p);
+    S->dKp = S->dWorld = S->dPatch = S->dJac = nullptr; S->dValid = S->dVisible = nullptr; S->cap = 0;
+}
+}  // namespace ygz
+
+int ygzorb_sparse_align_create(ygzorb_matcher *h, ygzorb_sparse_align **out) {
+    Matcher *m = (Matcher *)h;
+    if (!m || !out) return argFailM("null argument");
+    YGZ_CUDA(cudaSetDevice(m->device));
+    SparseAlign *S = new SparseAlign();
+    S->m = m;
+    memset(&S->A, 0, sizeof S->A);
+    cudaError_t e = cudaMalloc((void **)&S->dPose, 14 * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc((void **)&S->dOut, 64 * sizeof(float));
+    if (e == cudaSuccess) e = cudaMallocHost((void **)&S->hOut, 64 * sizeof(float));
+    if (e != cudaSuccess) { ygzorb_sparse_align_destroy((ygzorb_sparse_align *)S); return cudaFail(e, "sparse_align_create", __FILE__, __LINE__); }
+    *out = (ygzorb_sparse_align *)S;
+    return 0;
+}
+
+void ygzorb_sparse_align_destroy(ygzorb_sparse_align *sa) {
+    SparseAlign *S = (SparseAlign *)sa;
+    if (!S) return;
+    cudaSetDevice(S->m->device);
+    cudaStreamSynchronize(S->m->stream);
+    sparseAlignFree(S);
+    if (S->dPose) cudaFree(S->dPose);
+    if (S->dOut) cudaFree(S->dOut);
+    if (S->hOut) cudaFreeHost(S->hOut);
+    delete S;
+}
+
+int ygzorb_sparse_align_begin(ygzorb_sparse_align *sa, const ygzorb_pyramid *ref, const ygzorb_pyramid *cur, int n, const float *kpXY,
+                              const uint8_t *valid, const float *worldPos, const float *refPose, float focal, const float *curIntr,
+                              const float *invScale) {
+    SparseAlign *S = (SparseAlign *)sa;
+    const Pyramid *R = (const Pyramid *)ref, *C = (const Pyramid *)cur;
+    if (!S || !R || !C || !refPose || !curIntr || !invScale) return argFailM("null argument");
+    if (n < 0 || (n > 0 && (!kpXY || !valid || !worldPos))) return argFailM("bad feature arrays");
+    if (R->nLevels != C->nLevels) return argFailM("reference and current pyramids differ in depth");
+    for (int l = 0; l < R->nLevels; l++)
+        if (R->w[l] != C->w[l] || R->h[l] != C->h[l]) return argFailM("reference and current pyramids differ in size");
+    Matcher *m = S->m;
+    if (R->device != m->device || C->device != m->device) return argFailM("pyramid lives on another device");
+    YGZ_CUDA(cudaSetDevice(m->device));
+    if (n > S->cap) {
+        YGZ_CUDA(cudaStreamSynchronize(m->stream));
+        sparseAlignFree(S);
+        const size_t cap = (size_t)n + n / 4 + 64;
+        YGZ_CUDA(cudaMalloc((void **)&S->dKp, cap * 2 * sizeof(float)));
+        YGZ_CUDA(cudaMalloc((void **)&S->dWorld, cap * 3 * sizeof(float)));
+        YGZ_CUDA(cudaMalloc((void **)&S->dPatch, cap * 16 * sizeof(float)));
+        YGZ_CUDA(cudaMalloc((void **)&S->dJac, cap * 96 * sizeof(float)));
+        YGZ_CUDA(cudaMalloc((void **)&S->dValid, cap));
+        YGZ_CUDA(cudaMalloc((void **)&S->dVisible, cap));
+        S->cap = (int)cap;
+    }
+    SparseAlignArgs &A = S->A;
+    memset(&A, 0, sizeof A);
+    for (int l = 0; l < R->nLevels; l++) {
+        A.refLv[l] = R->base + R->off[l]; A.curLv[l] = C->base + C->off[l];
+        A.w[l] = R->w[l]; A.h[l] = R->h[l]; A.refPitch[l] = R->w[l]; A.curPitch[l] = C->w[l];
+        A.invScale[l] = invScale[l];
+    }
+    S->nLevels = R->nLevels;
+    A.focal = focal; A.fx = curIntr[0]; A.fy = curIntr[1]; A.cx = curIntr[2]; A.cy = curIntr[3];
+    A.n = n;
+    A.kpXY = S->dKp; A.worldPos = S->dWorld; A.valid = S->dValid; A.refPose = S->dPose; A.tCurRef = S->dPose + 7;
+    A.refPatch = S->dPatch; A.jac = S->dJac; A.visible = S->dVisible;
+    if (n > 0) {
+        YGZ_CUDA(cudaMemcpyAsync(S->dKp, kpXY, (size_t)n * 2 * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+        YGZ_CUDA(cudaMemcpyAsync(S->dWorld, worldPos, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+        YGZ_CUDA(cudaMemcpyAsync(S->dValid, valid, (size_t)n, cudaMemcpyHostToDevice, m->stream));
+        YGZ_CUDA(cudaMemsetAsync(S->dVisible, 0, (size_t)n, m->stream));
+        YGZ_CUDA(cudaMemsetAsync(S->dPatch, 0, (size_t)n * 16 * sizeof(float), m->stream));
+    }
+    YGZ_CUDA(cudaMemcpyAsync(S->dPose, refPose, 7 * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+    YGZ_CUDA(cudaStreamSynchronize(m->stream));   // the caller's arrays may go away after the call
+    S->begun = true;
+    return 0;
+}
+
+static int sparseAlignLevelOk(SparseAlign *S, int level) {
+    if (!S) return argFailM("null argument");
+    if (!S->begun) { setError("ygzorb_sparse_align_begin has not been called"); return YGZORB_E_STATE; }
+    if (level < 0 || level >= S->nLevels) return argFailM("level out of range");
+    return 0;
+}
+
+int ygzorb_sparse_align_run(ygzorb_sparse_align *sa, int maxLevel, int minLevel, float *tCurRef, int64_t *nTracked, float *stats) {
+    SparseAlign *S = (SparseAlign *)sa;
+    int rc;
+    if ((rc = sparseAlignLevelOk(S, maxLevel)) || (rc = sparseAlignLevelOk(S, minLevel))) return rc;
+    if (!tCurRef || !nTracked) return argFailM("null argument");
+    Matcher *m = S->m;
+    YGZ_CUDA(cudaSetDevice(m->device));
+    if (S->A.n == 0) { *nTracked = 0; if (stats) stats[0] = stats[1] = 0; return 0; }   // "no features to track" (:24-27)
+    YGZ_CUDA(cudaMemcpyAsync(S->dPose + 7, tCurRef, 7 * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+    m->launches += launchSparseAlignRun(S->A, maxLevel, minLevel, S->dOut, m->stream);
+    YGZ_CUDA(cudaMemcpyAsync(S->hOut, S->dOut, 10 * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+    YGZ_CUDA(cudaStreamSynchronize(m->stream));
+    YGZ_CUDA(cudaGetLastError());
+    memcpy(tCurRef, S->hOut, 7 * sizeof(float));
+    *nTracked = (int64_t)S->hOut[7] / 16;
+    if (stats) { stats[0] = S->hOut[8]; stats[1] = S->hOut[9]; }
+    return 0;
+}
+
+int ygzorb_sparse_align_precompute(ygzorb_sparse_align *sa, int level) {
+    SparseAlign *S = (SparseAlign *)sa;
+    int rc;
+    if ((rc = sparseAlignLevelOk(S, level))) return rc;
+    YGZ_CUDA(cudaSetDevice(S->m->device));
+    if (S->A.n > 0) S->m->launches += launchSparseAlignPrecompute(S->A, level, S->m->stream);
+    YGZ_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int ygzorb_sparse_align_residuals(ygzorb_sparse_align *sa, int level, const float *tCurRef, float *h36, float *jres6, float *chi2Sum,
+                                  int64_t *nMeas) {
+    SparseAlign *S = (SparseAlign *)sa;
+    int rc;
+    if ((rc = sparseAlignLevelOk(S, level))) return rc;
+    if (!tCurRef || !h36 || !jres6 || !chi2Sum || !nMeas) return argFailM("null argument");
+    Matcher *m = S->m;
+    YGZ_CUDA(cudaSetDevice(m->device));
+    if (S->A.n == 0) { memset(h36, 0, 36 * sizeof(float)); memset(jres6, 0, 6 * sizeof(float)); *chi2Sum = 0; *nMeas = 0; return 0; }
+    YGZ_CUDA(cudaMemcpyAsync(S->dPose + 7, tCurRef, 7 * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+    m->launches += launchSparseAlignResiduals(S->A, level, S->dOut, m->stream);
+    YGZ_CUDA(cudaMemcpyAsync(S->hOut, S->dOut, 44 * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+    YGZ_CUDA(cudaStreamSynchronize(m->stream));
+    YGZ_CUDA(cudaGetLastError());
+    memcpy(h36, S->hOut, 36 * sizeof(float)); memcpy(jres6, S->hOut + 36, 6 * sizeof(float));
+    *chi2Sum = S->hOut[42]; *nMeas = (int64_t)S->hOut[43];
+    return 0;
+}
+
+int ygzorb_sparse_align_caches(ygzorb_sparse_align *sa, uint8_t *visible, float *refPatch, float *jac) {
+    SparseAlign *S = (SparseAlign *)sa;
+    if (!S) return argFailM("null argument");
+    if (!S->begun) { setError("ygzorb_sparse_align_begin has not been called"); return YGZORB_E_STATE; }
+    YGZ_CUDA(cudaSetDevice(S->m->device));
+    YGZ_CUDA(cudaStreamSynchronize(S->m->stream));
+    const size_t n = (size_t)S->A.n;
+    if (n == 0) return 0;
+    if (visible) YGZ_CUDA(cudaMemcpy(visible, S->dVisible, n, cudaMemcpyDeviceToHost));
+    if (refPatch) YGZ_CUDA(cudaMemcpy(refPatch, S->dPatch, n * 16 * sizeof(float), cudaMemcpyDeviceToHost));
+    if (jac) YGZ_CUDA(cudaMemcpy(jac, S->dJac, n * 96 * sizeof(float), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 // ================================================================================================
 // Bag of words
 }  // extern "C"

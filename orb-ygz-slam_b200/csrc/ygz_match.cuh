@@ -159,6 +159,23 @@ struct DirectArgs {
     uint8_t *success;
 };
 int launchFindDirectProjection(const DirectArgs &A, cudaStream_t s);
+// SparseImgAlign (direct_kernels.cu); device pointers.  refPatch / jac / visible are the handle's caches
+// (ref_patch_cache_, jacobian_cache_, visible_fts_ of include/SparseImageAlign.h:82-86).
+struct SparseAlignArgs {
+    const uint8_t *refLv[kMaxLevels], *curLv[kMaxLevels];
+    int w[kMaxLevels], h[kMaxLevels], refPitch[kMaxLevels], curPitch[kMaxLevels];
+    float invScale[kMaxLevels];
+    float focal, fx, fy, cx, cy;
+    int n;
+    const float *kpXY, *worldPos;
+    const uint8_t *valid;
+    const float *refPose, *tCurRef;     // 7 floats each, device
+    float *refPatch, *jac;
+    uint8_t *visible;
+};
+int launchSparseAlignPrecompute(const SparseAlignArgs &A, int level, cudaStream_t s);
+int launchSparseAlignResiduals(const SparseAlignArgs &A, int level, float *out, cudaStream_t s);
+int launchSparseAlignRun(const SparseAlignArgs &A, int maxLevel, int minLevel, float *out, cudaStream_t s);
 int launchDistinctive(const uint8_t *obsDesc, const int32_t *obsStart, int nPoints, int32_t *bestIdx, int32_t *bestMedian,
                       uint8_t *bestDesc, cudaStream_t s);
 int configureMatchKernels();

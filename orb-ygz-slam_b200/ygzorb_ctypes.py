@@ -316,6 +316,59 @@ class Pyramid:
             self.h = None
 
 
+class SparseAlign:
+    """ygzorb_sparse_align: SparseImgAlign on the device (caches + the fused Gauss-Newton kernel)."""
+
+    def __init__(self, matcher):
+        L = lib()
+        L.ygzorb_sparse_align_create.argtypes = [C.c_void_p, C.c_void_p]
+        L.ygzorb_sparse_align_destroy.argtypes = [C.c_void_p]
+        L.ygzorb_sparse_align_destroy.restype = None
+        L.ygzorb_sparse_align_begin.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                C.c_void_p, C.c_float, C.c_void_p, C.c_void_p]
+        L.ygzorb_sparse_align_run.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ygzorb_sparse_align_precompute.argtypes = [C.c_void_p, C.c_int]
+        L.ygzorb_sparse_align_residuals.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ygzorb_sparse_align_caches.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        h = C.c_void_p()
+        check(L.ygzorb_sparse_align_create(matcher.h, C.byref(h)))
+        self.h, self.n = h, 0
+
+    def begin(self, ref, cur, kp_xy, valid, world_pos, ref_pose, focal, cur_intr, inv_scale):
+        kp_xy = np.ascontiguousarray(kp_xy, np.float32); valid = np.ascontiguousarray(valid, np.uint8)
+        world_pos = np.ascontiguousarray(world_pos, np.float32); ref_pose = np.ascontiguousarray(ref_pose, np.float32)
+        cur_intr = np.ascontiguousarray(cur_intr, np.float32); inv_scale = np.ascontiguousarray(inv_scale, np.float32)
+        self.n = len(valid)
+        check(lib().ygzorb_sparse_align_begin(self.h, ref.h, cur.h, self.n, _ptr(kp_xy), _ptr(valid), _ptr(world_pos), _ptr(ref_pose),
+                                              C.c_float(focal), _ptr(cur_intr), _ptr(inv_scale)))
+
+    def run(self, max_level, min_level, t_cur_ref):
+        T = np.array(t_cur_ref, np.float32).copy()
+        n = C.c_int64()
+        stats = np.zeros(2, np.float32)
+        check(lib().ygzorb_sparse_align_run(self.h, max_level, min_level, _ptr(T), C.byref(n), _ptr(stats)))
+        return T, n.value, stats
+
+    def precompute(self, level):
+        check(lib().ygzorb_sparse_align_precompute(self.h, level))
+
+    def residuals(self, level, t_cur_ref):
+        T = np.ascontiguousarray(t_cur_ref, np.float32)
+        H, J, chi2, n = np.zeros((6, 6), np.float32), np.zeros(6, np.float32), C.c_float(), C.c_int64()
+        check(lib().ygzorb_sparse_align_residuals(self.h, level, _ptr(T), _ptr(H), _ptr(J), C.byref(chi2), C.byref(n)))
+        return H, J, chi2.value, n.value
+
+    def caches(self):
+        vis, patch, jac = np.zeros(self.n, np.uint8), np.zeros((self.n, 16), np.float32), np.zeros((self.n, 16, 6), np.float32)
+        check(lib().ygzorb_sparse_align_caches(self.h, _ptr(vis), _ptr(patch), _ptr(jac)))
+        return vis, patch, jac
+
+    def close(self):
+        if self.h:
+            lib().ygzorb_sparse_align_destroy(self.h)
+            self.h = None
+
+
 class Matcher:
     """Handle behind ygz::ORBmatcher's Hamming searches and Frame::ComputeStereoMatches."""
 

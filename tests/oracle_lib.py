@@ -236,6 +236,48 @@ def find_direct_projection(kfs, cur_levels, cur_intr, scale, inv_scale, inv_sigm
     return out, level, ok
 
 
+class OPyramid(C.Structure):
+    _fields_ = [("levels", C.c_void_p * 8), ("w", C.c_int32 * 8), ("h", C.c_int32 * 8), ("pitch", C.c_int32 * 8)]
+
+
+def _opyr(levels):
+    imgs = [np.ascontiguousarray(x, np.uint8) for x in levels]
+    P = OPyramid()
+    for l, im in enumerate(imgs):
+        P.levels[l] = im.ctypes.data; P.w[l] = im.shape[1]; P.h[l] = im.shape[0]; P.pitch[l] = im.shape[1]
+    return P, imgs
+
+
+def sparse_align_residuals(ref_levels, cur_levels, level, scale, focal, cur_intr, ref_pose, t_cur_ref, kp_xy, valid, world_pos,
+                           accumulate=0):
+    R, k1 = _opyr(ref_levels); Cu, k2 = _opyr(cur_levels)
+    kp_xy = np.ascontiguousarray(kp_xy, np.float32); valid = np.ascontiguousarray(valid, np.uint8)
+    world_pos = np.ascontiguousarray(world_pos, np.float32)
+    n = len(valid)
+    H, J, chi2, nm = np.zeros((6, 6), np.float32), np.zeros(6, np.float32), C.c_float(), C.c_int64()
+    vis, patch, jac = np.zeros(n, np.uint8), np.zeros((n, 16), np.float32), np.zeros((n, 16, 6), np.float32)
+    lib().ygzo_sparse_align_residuals(C.byref(R), C.byref(Cu), level, C.c_float(scale), C.c_float(focal),
+                                      _p(np.ascontiguousarray(cur_intr, np.float32)), _p(np.ascontiguousarray(ref_pose, np.float32)),
+                                      _p(np.ascontiguousarray(t_cur_ref, np.float32)), n, _p(kp_xy), _p(valid), _p(world_pos),
+                                      accumulate, _p(H), _p(J), C.byref(chi2), C.byref(nm), _p(vis), _p(patch), _p(jac))
+    return H, J, chi2.value, nm.value, vis, patch, jac
+
+
+def sparse_align_run(ref_levels, cur_levels, max_level, min_level, inv_scale, focal, cur_intr, ref_pose, kp_xy, valid, world_pos,
+                     t_cur_ref, accumulate=0):
+    R, k1 = _opyr(ref_levels); Cu, k2 = _opyr(cur_levels)
+    kp_xy = np.ascontiguousarray(kp_xy, np.float32); valid = np.ascontiguousarray(valid, np.uint8)
+    world_pos = np.ascontiguousarray(world_pos, np.float32)
+    T = np.array(t_cur_ref, np.float32).copy()
+    stats = np.zeros(2, np.float32)
+    lib().ygzo_sparse_align_run.restype = C.c_int64
+    n = lib().ygzo_sparse_align_run(C.byref(R), C.byref(Cu), max_level, min_level, _p(np.ascontiguousarray(inv_scale, np.float32)),
+                                    C.c_float(focal), _p(np.ascontiguousarray(cur_intr, np.float32)),
+                                    _p(np.ascontiguousarray(ref_pose, np.float32)), len(valid), _p(kp_xy), _p(valid), _p(world_pos),
+                                    accumulate, _p(T), _p(stats))
+    return T, n, stats
+
+
 def hamming_knn2(query, train, ratio, th, threads=1):
     query = np.ascontiguousarray(query, np.uint8)
     train = np.ascontiguousarray(train, np.uint8)

@@ -403,3 +403,29 @@ def direct_projection_case(seed, n=300, w=752, h=480, fx=458.654, fy=457.296, cx
     return dict(kfs=kfs, cur_levels=pyramid_of(cur), cur_intr=np.array([fx, fy, cx, cy], np.float32), scale=sc, inv_scale=inv,
                 inv_sigma2_1=float(np.float32(1.0) / (sc[1] * sc[1])), kf_index=kf_index, px_ref=px_ref, octave=octave,
                 world_pos=world, px_curr=px_curr)
+
+
+def sparse_align_case(seed, n=800, w=752, h=480, fx=458.654, fy=457.296, cx=367.215, cy=248.375, perturb=(0.02, -0.012, 0.0)):
+    """Reference + current frame for SparseImgAlign: the current image is the reference shifted by the parallax of a sideways
+    motion t_true at the common depth Z of the features (a fronto-parallel plane), so the optimum of the alignment is known; the
+    initial guess is off by `perturb`.  Some features are invalid (no MapPoint / outlier), some too close to the border."""
+    import cv2
+    rng = np.random.default_rng(seed)
+    ref = textured_frame(w, h, 60 + seed)
+    Z, t_true = 4.0, np.array([0.05, -0.03, 0.0])
+    shift = np.array([fx * t_true[0] / Z, fy * t_true[1] / Z])
+    M = np.array([[1, 0, shift[0]], [0, 1, shift[1]]], np.float64)
+    cur = cv2.warpAffine(ref, M, (w, h), flags=cv2.INTER_LINEAR, borderMode=cv2.BORDER_REFLECT_101)
+    sc, inv, _ = scale_tables()
+    q_ref = quat_from_rotvec([0.03, 0.05, -0.02]); t_ref = np.array([-0.2, 0.1, 0.3], np.float32)
+    q_inv = q_ref * np.array([-1, -1, -1, 1], np.float32)
+    kp = np.stack([rng.uniform(2, w - 2, n), rng.uniform(2, h - 2, n)], axis=1).astype(np.float32)
+    valid = (rng.random(n) < 0.9).astype(np.uint8)
+    world = np.zeros((n, 3), np.float32)
+    for i in range(n):
+        p_ref = np.array([(kp[i, 0] - cx) * Z / fx, (kp[i, 1] - cy) * Z / fy, Z])
+        world[i] = quat_rotate(q_inv, p_ref - t_ref.astype(np.float64))
+    t0 = np.concatenate([quat_from_rotvec([0.001, -0.0015, 0.002]), (t_true + np.array(perturb)).astype(np.float32)])
+    return dict(ref_levels=pyramid_of(ref), cur_levels=pyramid_of(cur), inv_scale=inv, focal=fx,
+                cur_intr=np.array([fx, fy, cx, cy], np.float32), ref_pose=np.concatenate([q_ref, t_ref]), kp_xy=kp, valid=valid,
+                world_pos=world, t_cur_ref=t0.astype(np.float32), t_true=t_true)

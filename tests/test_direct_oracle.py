@@ -133,3 +133,69 @@ def test_find_direct_projection_vs_float64(seed):
     assert np.array_equal(o_ok[clear], p_ok[clear]) and clear.mean() > 0.9
     both = (o_ok == 1) & (p_ok == 1)
     assert np.abs(o_px[both] - p_px[both]).max() < 2e-2            # float32 op order vs float64: well below the 0.03 px update threshold
+
+
+# ---- SparseImgAlign: float64 re-derivation (src/SparseImageAlign.cc:57-225) of the two hot loops, and the known optimum of the
+# synthetic case for the whole run
+def py_sparse_align_residuals(c, level, T):
+    ref, cur = c["ref_levels"][level].astype(np.float64), c["cur_levels"][level].astype(np.float64)
+    scale = float(c["inv_scale"][level]); f = float(c["focal"])
+    fx, fy, cx, cy = (float(v) for v in c["cur_intr"])
+    H, Jr, chi2, nm = np.zeros((6, 6)), np.zeros(6), 0.0, 0
+    rows, cols = ref.shape
+
+    def interp(img, x, y):      # bilinear at float position
+        x0, y0 = int(np.floor(x)), int(np.floor(y))
+        a, b = x - x0, y - y0
+        return (1 - a) * (1 - b) * img[y0, x0] + a * (1 - b) * img[y0, x0 + 1] + (1 - a) * b * img[y0 + 1, x0] + a * b * img[y0 + 1, x0 + 1]
+
+    for i in range(len(c["valid"])):
+        if not c["valid"][i]:
+            continue
+        u, v = (c["kp_xy"][i].astype(np.float64) * np.float64(np.float32(scale)))
+        u, v = float(np.float32(u)), float(np.float32(v))
+        ui, vi = int(np.floor(u)), int(np.floor(v))
+        if ui - 3 < 0 or vi - 3 < 0 or ui + 3 >= cols or vi + 3 >= rows:
+            continue
+        p = synth.quat_rotate(c["ref_pose"][:4], c["world_pos"][i]) + c["ref_pose"][4:].astype(np.float64)
+        x, y, z = p
+        Jp = np.array([[-1 / z, 0, x / z ** 2, x * y / z ** 2, -(1 + x * x / z ** 2), y / z],
+                       [0, -1 / z, y / z ** 2, 1 + y * y / z ** 2, -x * y / z ** 2, -x / z]])
+        q = synth.quat_rotate(T[:4], p) + T[4:].astype(np.float64)
+        uc, vc = (fx * q[0] / q[2] + cx) * scale, (fy * q[1] / q[2] + cy) * scale
+        uci, vci = int(np.floor(uc)), int(np.floor(vc))
+        if uci - 3 < 0 or vci - 3 < 0 or uci + 3 >= cols or vci + 3 >= rows:
+            continue
+        for yy in range(4):
+            for xx in range(4):
+                rx, ry = u + xx - 2, v + yy - 2
+                dx = 0.5 * (interp(ref, rx + 1, ry) - interp(ref, rx - 1, ry)); dy = 0.5 * (interp(ref, rx, ry + 1) - interp(ref, rx, ry - 1))
+                J = (dx * Jp[0] + dy * Jp[1]) * (f * scale)
+                res = interp(cur, uc + xx - 2, vc + yy - 2) - interp(ref, rx, ry)
+                H += np.outer(J, J); Jr -= J * res; chi2 += res * res; nm += 1
+    return H, Jr, chi2, nm
+
+
+@pytest.mark.parametrize("level", [1, 4])
+def test_sparse_align_residuals_vs_float64(level):
+    c = synth.sparse_align_case(0, n=300)
+    args = dict(ref_levels=c["ref_levels"], cur_levels=c["cur_levels"], level=level, scale=float(c["inv_scale"][level]), focal=c["focal"],
+                cur_intr=c["cur_intr"], ref_pose=c["ref_pose"], t_cur_ref=c["t_cur_ref"], kp_xy=c["kp_xy"], valid=c["valid"],
+                world_pos=c["world_pos"])
+    H, J, chi2, nm, vis, _, _ = O.sparse_align_residuals(**args)
+    H2, J2, chi22, nm2, _, _, _ = O.sparse_align_residuals(accumulate=1, **args)
+    eH, eJ, echi2, enm = py_sparse_align_residuals(c, level, c["t_cur_ref"])
+    assert nm == nm2 == enm and 0 < vis.sum() < len(vis)
+    for a, b in ((H, eH), (H2, eH), (J, eJ), (J2, eJ)):
+        assert np.abs(a - b).max() <= 2e-4 * np.abs(b).max()
+    assert abs(chi2 - echi2) <= 2e-4 * echi2 and abs(chi22 - echi2) <= 2e-4 * echi2
+
+
+def test_sparse_align_run_recovers_the_motion():
+    c = synth.sparse_align_case(1, n=600)
+    args = {k: v for k, v in c.items() if k != "t_true"}
+    T, n, stats = O.sparse_align_run(max_level=7, min_level=1, **args)
+    T2, n2, _ = O.sparse_align_run(max_level=7, min_level=1, accumulate=1, **args)
+    assert n > 300 and n == n2 and stats[0] >= 7
+    assert np.abs(T[4:] - c["t_true"]).max() < 2e-3 and np.abs(T[:3]).max() < 1e-3     # start was off by 2 cm / 2 mrad
+    assert np.abs(T - T2).max() < 1e-4                                                     # float vs double accumulation

@@ -73,3 +73,62 @@ def test_pyramid_snapshot_of_extractor():
     for l, a in enumerate(ref):
         assert np.array_equal(snap.level(l), a)
     snap.close(); ex.close()
+
+
+def _align_handles(matcher, c):
+    ref, cur = Y.Pyramid(c["ref_levels"]), Y.Pyramid(c["cur_levels"])
+    sa = Y.SparseAlign(matcher)
+    sa.begin(ref, cur, c["kp_xy"], c["valid"], c["world_pos"], c["ref_pose"], c["focal"], c["cur_intr"], c["inv_scale"])
+    return sa, ref, cur
+
+
+@pytest.mark.parametrize("level,n", [(1, 700), (3, 2500), (7, 64)])
+def test_sparse_align_hot_loops_vs_oracle(matcher, level, n):
+    """precomputeReferencePatches + computeResiduals (src/SparseImageAlign.cc:57-225): the caches are bit-exact (per-feature
+    float arithmetic in the reference's order); H / Jres / chi2 are sums over features, reduced on the device by a fixed tree in
+    double: tolerance 1e-6 relative against the oracle's double accumulation of the same float partials, 2e-4 against the
+    reference's sequential float sums.  n_meas exact."""
+    c = synth.sparse_align_case(2, n=n)
+    args = dict(ref_levels=c["ref_levels"], cur_levels=c["cur_levels"], level=level, scale=float(c["inv_scale"][level]), focal=c["focal"],
+                cur_intr=c["cur_intr"], ref_pose=c["ref_pose"], t_cur_ref=c["t_cur_ref"], kp_xy=c["kp_xy"], valid=c["valid"],
+                world_pos=c["world_pos"])
+    eH, eJ, echi2, enm, evis, epatch, ejac = O.sparse_align_residuals(accumulate=1, **args)
+    fH, fJ, fchi2, _, _, _, _ = O.sparse_align_residuals(accumulate=0, **args)
+    sa, ref, cur = _align_handles(matcher, c)
+    sa.precompute(level)
+    vis, patch, jac = sa.caches()
+    H, J, chi2, nm = sa.residuals(level, c["t_cur_ref"])
+    sa.close(); ref.close(); cur.close()
+    assert np.array_equal(vis, evis) and patch.tobytes() == epatch.tobytes() and jac.tobytes() == ejac.tobytes()
+    assert nm == enm and nm > 0
+    assert np.abs(H - eH).max() <= 1e-6 * np.abs(eH).max() and np.abs(J - eJ).max() <= 1e-6 * np.abs(eJ).max()
+    assert abs(chi2 - echi2) <= 1e-6 * echi2
+    assert np.abs(H - fH).max() <= 2e-4 * np.abs(fH).max() and np.abs(J - fJ).max() <= 2e-4 * np.abs(fJ).max()
+    assert np.allclose(H, H.T)
+
+
+@pytest.mark.parametrize("seed,n", [(1, 600), (3, 2000)])
+def test_sparse_align_run_vs_oracle(matcher, seed, n):
+    """SparseImgAlign::run (one kernel launch): TCR within 1e-4 of the oracle's (float Gauss-Newton whose sums differ in the last
+    bits), the same number of tracked features, and the known motion of the synthetic case recovered."""
+    c = synth.sparse_align_case(seed, n=n)
+    args = {k: v for k, v in c.items() if k != "t_true"}
+    eT, en, estats = O.sparse_align_run(max_level=7, min_level=1, accumulate=1, **args)
+    sa, ref, cur = _align_handles(matcher, c)
+    T, nt, stats = sa.run(7, 1, c["t_cur_ref"])
+    sa.close(); ref.close(); cur.close()
+    assert nt == en and nt > n // 2
+    assert np.abs(T - eT).max() < 1e-4
+    assert np.abs(T[4:] - c["t_true"]).max() < 2e-3
+    assert abs(stats[0] - estats[0]) <= 3
+
+
+def test_sparse_align_no_features(matcher):
+    c = synth.sparse_align_case(0, n=8)
+    ref, cur = Y.Pyramid(c["ref_levels"]), Y.Pyramid(c["cur_levels"])
+    sa = Y.SparseAlign(matcher)
+    sa.begin(ref, cur, np.zeros((0, 2), np.float32), np.zeros(0, np.uint8), np.zeros((0, 3), np.float32), c["ref_pose"], c["focal"],
+             c["cur_intr"], c["inv_scale"])
+    T, nt, _ = sa.run(7, 1, c["t_cur_ref"])
+    assert nt == 0 and np.array_equal(T, c["t_cur_ref"])
+    sa.close(); ref.close(); cur.close()
