@@ -468,7 +468,7 @@ int ygzorb_find_direct_projection(ygzorb_matcher *m, const ygzorb_direct_keyfram
  * the reference frame's features, 4x4 patches, inverse compositional, as Tracking::TrackWithSparseAlignment runs it
  * (src/Tracking.cc:284, :2171: max_level = nLevels - 1, min_level = 1, Gauss-Newton, 10 iterations per level, unit weights).
  * A handle owns the class's caches on the device (ref_patch_cache_, jacobian_cache_, visible_fts_) and runs on the matcher's
- * stream.  Poses are Sophus::SE3f storage (quaternion x, y, z, w, translation).
+ * stream; destroy it before the matcher it was created on.  Poses are Sophus::SE3f storage (quaternion x, y, z, w, translation).
  *   ygzorb_sparse_align_begin: what run() sets up (:20-37) — the reference frame's N features: kp_xy[2i..] = mvKeys[i].pt,
  *     valid[i] = mvpMapPoints[i] && !isBad() && !mvbOutlier[i] (:68-70), world_pos[3i..] = GetWorldPos(), ref_pose =
  *     ref_frame->mTcw, focal = ref fx, inv_scale_factors = mvInvScaleFactors; clears visible_fts_.

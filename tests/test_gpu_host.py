@@ -213,3 +213,83 @@ def test_host_matcher_overloads_on_objects():
     assert np.array_equal(take("<i4", m + n), replaced)
     assert np.array_equal(take("<i4", m + n), obs)
     assert off == len(buf)
+
+
+DEMO3 = os.path.join(PKG, "host", "host_demo3")
+
+
+def test_host_direct_tracking_on_objects():
+    """SparseImgAlign::run, ORBmatcher::FindDirectProjection (batched) and MapPoint::ComputeDistinctiveDescriptors through the
+    host drop-ins of host/DirectTracking.h on Frame / KeyFrame / MapPoint objects (host_demo3.cc) against the oracle.  The host
+    composes T_cur_from_ref with its pose type's own product, so floats agree to rounding of that product, not bit for bit."""
+    from test_direct_oracle import synth_observations
+    if not os.path.exists(DEMO3):
+        subprocess.run(["make", "-C", os.path.join(PKG, "host")], check=True)
+    c = synth.sparse_align_case(4, n=700)
+    n = len(c["valid"])
+    rng = np.random.default_rng(3)
+    valid = c["valid"].copy()
+    bad = np.where(valid == 1)[0]
+    valid[bad[:20]] = 2; valid[bad[20:40]] = 3                      # outliers / bad MapPoints: not used (src/SparseImageAlign.cc:68-70)
+    used = (valid == 1).astype(np.uint8)
+    kps = np.zeros(n, O.KP_DTYPE)
+    kps["x"] = c["kp_xy"][:, 0]; kps["y"] = c["kp_xy"][:, 1]; kps["octave"] = rng.integers(0, 4, n); kps["size"] = 31; kps["angle"] = -1
+    sc, inv, sigma2 = synth.scale_tables()
+    inv_sigma2 = (np.float32(1.0) / sigma2).astype(np.float32)
+    # cur->mTcw such that cur->mTcw * ref->mTcw.inverse() is the case's initial guess: cur = guess * ref
+    q_g, t_g, q_r, t_r = c["t_cur_ref"][:4], c["t_cur_ref"][4:], c["ref_pose"][:4], c["ref_pose"][4:]
+
+    def qmul(a, b):
+        ax, ay, az, aw = (float(v) for v in a); bx, by, bz, bw = (float(v) for v in b)
+        return np.array([aw * bx + ax * bw + ay * bz - az * by, aw * by + ay * bw + az * bx - ax * bz, aw * bz + az * bw + ax * by - ay * bx,
+                         aw * bw - ax * bx - ay * by - az * bz])
+    q_c = qmul(q_g, q_r); q_c /= np.linalg.norm(q_c)
+    t_c = synth.quat_rotate(q_g, t_r) + t_g.astype(np.float64)
+    cur_pose = np.concatenate([q_c, t_c]).astype(np.float32)
+    # direct-projection requests on valid interior features
+    sel = np.where((used == 1) & (c["kp_xy"][:, 0] > 40) & (c["kp_xy"][:, 0] < 700) & (c["kp_xy"][:, 1] > 40) & (c["kp_xy"][:, 1] < 440))[0][:200]
+    fx, fy, cx, cy = (float(v) for v in c["cur_intr"])
+    px0 = np.zeros((len(sel), 2), np.float32)
+    t_true_pose = np.concatenate([[0, 0, 0, 1], c["t_true"]]).astype(np.float32)
+    for j, i in enumerate(sel):
+        p_ref = synth.quat_rotate(q_r, c["world_pos"][i]) + t_r.astype(np.float64)
+        p_cur = p_ref + c["t_true"]
+        px0[j] = [fx * p_cur[0] / p_cur[2] + cx, fy * p_cur[1] / p_cur[2] + cy]
+    px0 += rng.uniform(-1.2, 1.2, px0.shape).astype(np.float32)
+    desc, start = synth_observations(50, 7)
+    with tempfile.TemporaryDirectory() as td:
+        fin, fout = os.path.join(td, "in.bin"), os.path.join(td, "out.bin")
+        with open(fin, "wb") as f:
+            np.array([8], np.int32).tofile(f)
+            for pyr in (c["ref_levels"], c["cur_levels"]):
+                for im in pyr:
+                    np.array([im.shape[1], im.shape[0]], np.int32).tofile(f); np.ascontiguousarray(im).tofile(f)
+            sc.tofile(f); inv.tofile(f); inv_sigma2.tofile(f); c["cur_intr"].tofile(f)
+            c["ref_pose"].astype(np.float32).tofile(f); cur_pose.tofile(f)
+            np.array([n], np.int32).tofile(f); kps.tofile(f); valid.tofile(f); c["world_pos"].tofile(f)
+            np.array([len(sel)], np.int32).tofile(f)
+            for j, i in enumerate(sel):
+                np.array([i], np.int32).tofile(f); px0[j].tofile(f)
+            np.array([len(start) - 1], np.int32).tofile(f); start.tofile(f); desc.tofile(f)
+        res = subprocess.run([DEMO3, fin, fout], capture_output=True, text=True)
+        assert res.returncode == 0, res.stdout + res.stderr
+        with open(fout, "rb") as f:
+            T = np.fromfile(f, np.float32, 7); tracked = int(np.fromfile(f, np.int64, 1)[0])
+            dp = np.fromfile(f, np.dtype([("px", "<f4", 2), ("level", "<i4"), ("ok", "<i4")]), len(sel))
+            best = np.fromfile(f, np.uint8, (len(start) - 1) * 32).reshape(-1, 32)
+    # SparseImgAlign::run
+    args = {k: v for k, v in c.items() if k not in ("t_true", "valid")}
+    eT, en, _ = O.sparse_align_run(max_level=7, min_level=1, accumulate=1, valid=used, **args)
+    assert tracked == en and np.abs(T - eT).max() < 2e-4 and np.abs(T[4:] - c["t_true"]).max() < 2e-3
+    # FindDirectProjection: the keyframe is the reference frame; TCR = the host's product of the two poses ~ the initial guess
+    kf = dict(levels=c["ref_levels"], pose_ref=c["ref_pose"], t_cur_ref=c["t_cur_ref"], fx=fx, fy=fy, cx=cx, cy=cy)
+    e_px, e_lv, e_ok = O.find_direct_projection([kf], c["cur_levels"], c["cur_intr"], sc, inv, float(inv_sigma2[1]),
+                                                np.zeros(len(sel), np.int32), c["kp_xy"][sel], kps["octave"][sel], c["world_pos"][sel], px0)
+    assert np.array_equal(dp["level"], e_lv)
+    assert (dp["ok"] == e_ok).mean() > 0.97 and e_ok.mean() > 0.5
+    both = (dp["ok"] == 1) & (e_ok == 1)
+    assert np.abs(dp["px"][both] - e_px[both]).max() < 5e-3
+    # ComputeDistinctiveDescriptors
+    marker = np.full((len(start) - 1, 32), 0xA5, np.uint8)
+    _, _, e_best = O.distinctive_descriptors(desc, start, marker)
+    assert np.array_equal(best, e_best)
