@@ -1,6 +1,8 @@
 // direct_kernels.cu — SURVEY.md §8(f) row f4: the descriptor post-processing of MapPoint and the pyramid consumers of the
 // direct tracker (MapPoint::ComputeDistinctiveDescriptors src/MapPoint.cc:211-271; ORBmatcher::FindDirectProjection
 // src/ORBmatcher.cc:1525-1602 with ygz::Align2D src/Align.cc:8-105; SparseImgAlign src/SparseImageAlign.cc:60-256).
+#include <cooperative_groups.h>
+
 #include "ygz_match.cuh"
 
 namespace ygz {
@@ -208,22 +210,33 @@ int launchFindDirectProjection(const DirectArgs &A, cudaStream_t s) {
 
 // ---- K15: SparseImgAlign (src/SparseImageAlign.cc) — the two hot loops as device functions, used by the step kernels
 // (precomputeReferencePatches / computeResiduals behind the reference's own NLLSSolver driver) and by the fused kernel that
-// runs the whole coarse-to-fine Gauss-Newton of SparseImgAlign::run in one launch.  One CTA: a frame has at most a few
-// thousand features x 16 pixels, far too little to split across SMs once every iteration ends in a 6 x 6 solve.
-// Per feature the arithmetic is the reference's, in its order, in float; ACROSS features the 21 + 6 + 1 sums are reduced by a
-// fixed tree in double (deterministic; the reference adds them up one after the other in float), so H, Jres and chi2 agree
-// with the sequential float sums to rounding, not bit for bit.
-constexpr int kAlignThreads = 512, kAlignSums = 29;   // 21 upper-triangle H + 6 Jres + chi2 + n_meas
+// runs the whole coarse-to-fine Gauss-Newton of SparseImgAlign::run in one launch on a cluster of 8 CTAs (a frame has a few
+// thousand features x 16 pixels: one thread per feature, and what bounds an iteration is the scattered 5 x 5 byte gathers, so
+// they are spread over 8 SMs' load/store units; the 6 x 6 solve runs in one thread of CTA 0 between two cluster barriers).
+// The caches are feature-minor (element e of feature i at e * stride + i), so a warp's loads and stores of the same element
+// coalesce.  Per feature the arithmetic is the reference's, in its order, in float; ACROSS features the 21 + 6 + 1 sums are
+// reduced by a fixed tree in double (warp shuffles, warps in order, CTAs in rank order: deterministic; the reference adds them up
+// one after the other in float), so H, Jres and chi2 agree with the sequential float sums to rounding, not bit for bit.
+constexpr int kAlignThreads = 256, kAlignCluster = 8, kAlignSums = 29;   // 21 upper-triangle H + 6 Jres + chi2 + n_meas
 
-__device__ void alignPrecompute(const SparseAlignArgs &A, int level, const uint8_t *img, int cols, int rows, int stride, float scale) {
-    for (int i = threadIdx.x; i < A.n; i += blockDim.x) {
-        float *jac = A.jac + (size_t)i * 96;
-        for (int k = 0; k < 96; k++) jac[k] = 0.0f;                    // jacobian_cache_.setZero() (:42)
+__device__ void alignPrecompute(const SparseAlignArgs &A, const uint8_t *__restrict__ img, int cols, int rows, int stride, float scale,
+                                int first, int step) {
+    const size_t S = (size_t)A.stride;
+    for (int i = first; i < A.n; i += step) {
+        float *__restrict__ jac = A.jac + i;
+        float *__restrict__ patch = A.refPatch + i;
+#pragma unroll 8
+        for (int k = 0; k < 96; k++) jac[k * S] = 0.0f;                // jacobian_cache_.setZero() (:42)
         if (!A.valid[i]) continue;
         const float u = A.kpXY[2 * i] * scale, v = A.kpXY[2 * i + 1] * scale;
         const int ui = (int)floorf(u), vi = (int)floorf(v);
         if (ui - 3 < 0 || vi - 3 < 0 || ui + 3 >= cols || vi + 3 >= rows) continue;
         A.visible[i] = 1;
+        float px[7][7];                                                // rows vi-3 .. vi+3, columns ui-3 .. ui+3: every load in flight at once
+#pragma unroll
+        for (int yy = 0; yy < 7; yy++)
+#pragma unroll
+            for (int xx = 0; xx < 7; xx++) px[yy][xx] = (float)__ldg(img + (long long)(vi + yy - 3) * stride + (ui + xx - 3));
         const DV3 p = dSe3Mul(A.refPose, DV3{A.worldPos[3 * i], A.worldPos[3 * i + 1], A.worldPos[3 * i + 2]});
         float J[2][6];
         const float x = p.x, y = p.y, zInv = (float)(1. / (double)p.z), zInv2 = zInv * zInv;
@@ -232,49 +245,57 @@ __device__ void alignPrecompute(const SparseAlignArgs &A, int level, const uint8
         const float su = u - (float)ui, sv = v - (float)vi;
         const float wTL = (float)((1.0 - su) * (1.0 - sv)), wTR = (float)(su * (1.0 - sv)), wBL = (float)((1.0 - su) * sv), wBR = su * sv;
         const float fs = A.focal * scale;
-        int k = 0;
-        for (int yy = 0; yy < 4; ++yy) {
-            const uint8_t *r = img + (long long)(vi + yy - 2) * stride + (ui - 2);
-            for (int xx = 0; xx < 4; ++xx, ++r, ++k) {
-                A.refPatch[(size_t)i * 16 + k] = ((wTL * r[0] + wTR * r[1]) + wBL * r[stride]) + wBR * r[stride + 1];
-                const float dx = 0.5f * ((((wTL * r[1] + wTR * r[2]) + wBL * r[stride + 1]) + wBR * r[stride + 2]) -
-                                         (((wTL * r[-1] + wTR * r[0]) + wBL * r[stride - 1]) + wBR * r[stride]));
-                const float dy = 0.5f * ((((wTL * r[stride] + wTR * r[1 + stride]) + wBL * r[stride * 2]) + wBR * r[stride * 2 + 1]) -
-                                         (((wTL * r[-stride] + wTR * r[1 - stride]) + wBL * r[0]) + wBR * r[1]));
 #pragma unroll
-                for (int c = 0; c < 6; c++) jac[k * 6 + c] = (dx * J[0][c] + dy * J[1][c]) * fs;
+        for (int yy = 0; yy < 4; ++yy)
+#pragma unroll
+            for (int xx = 0; xx < 4; ++xx) {
+                const int k = yy * 4 + xx, r = yy + 1, c0 = xx + 1;   // r[0] of the reference = px[r][c0]
+#define YGZ_BL(dy, dx) (((wTL * px[r + (dy)][c0 + (dx)] + wTR * px[r + (dy)][c0 + (dx) + 1]) + wBL * px[r + (dy) + 1][c0 + (dx)]) + wBR * px[r + (dy) + 1][c0 + (dx) + 1])
+                patch[k * S] = YGZ_BL(0, 0);
+                const float dx = 0.5f * (YGZ_BL(0, 1) - YGZ_BL(0, -1));
+                const float dy = 0.5f * (YGZ_BL(1, 0) - YGZ_BL(-1, 0));
+#undef YGZ_BL
+#pragma unroll
+                for (int c = 0; c < 6; c++) jac[(k * 6 + c) * S] = (dx * J[0][c] + dy * J[1][c]) * fs;
             }
-        }
     }
 }
 
 // computeResiduals (:130-225): this thread's features -> acc[29] (float partials per feature, added up in double)
-__device__ void alignResiduals(const SparseAlignArgs &A, const float *T, const uint8_t *cur, int cols, int rows, int stride, float scale,
-                               double *acc) {
+__device__ void alignResiduals(const SparseAlignArgs &A, const float *T, const uint8_t *__restrict__ cur, int cols, int rows, int stride,
+                               float scale, int first, int step, double *acc) {
+    const size_t S = (size_t)A.stride;
 #pragma unroll
     for (int k = 0; k < kAlignSums; k++) acc[k] = 0.0;
-    for (int i = threadIdx.x; i < A.n; i += blockDim.x) {
+    for (int i = first; i < A.n; i += step) {
         if (!A.visible[i]) continue;
         const DV3 pr = dSe3Mul(A.refPose, DV3{A.worldPos[3 * i], A.worldPos[3 * i + 1], A.worldPos[3 * i + 2]});
         const DV3 pc = dSe3Mul(T, pr);
         const float uc = (A.fx * pc.x / pc.z + A.cx) * scale, vc = (A.fy * pc.y / pc.z + A.cy) * scale;
         const int ui = (int)floorf(uc), vi = (int)floorf(vc);
         if (ui < 0 || vi < 0 || ui - 3 < 0 || vi - 3 < 0 || ui + 3 >= cols || vi + 3 >= rows) continue;
+        float px[5][5];
+#pragma unroll
+        for (int yy = 0; yy < 5; yy++)
+#pragma unroll
+            for (int xx = 0; xx < 5; xx++) px[yy][xx] = (float)__ldg(cur + (long long)(vi + yy - 2) * stride + (ui + xx - 2));
+        const float *__restrict__ jac = A.jac + i;
+        const float *__restrict__ patch = A.refPatch + i;
         const float su = uc - (float)ui, sv = vc - (float)vi;
         const float wTL = (float)((1.0 - su) * (1.0 - sv)), wTR = (float)(su * (1.0 - sv)), wBL = (float)((1.0 - su) * sv), wBR = su * sv;
         float f[kAlignSums - 1];
 #pragma unroll
         for (int k = 0; k < kAlignSums - 1; k++) f[k] = 0.0f;
-        int k = 0;
-        for (int yy = 0; yy < 4; ++yy) {
-            const uint8_t *p = cur + (long long)(vi + yy - 2) * stride + (ui - 2);
-            for (int xx = 0; xx < 4; ++xx, ++k, ++p) {
-                const float inten = ((wTL * p[0] + wTR * p[1]) + wBL * p[stride]) + wBR * p[stride + 1];
-                const float res = inten - A.refPatch[(size_t)i * 16 + k];
-                const float *Jp = A.jac + ((size_t)i * 16 + k) * 6;
+#pragma unroll
+        for (int yy = 0; yy < 4; ++yy)
+#pragma unroll
+            for (int xx = 0; xx < 4; ++xx) {
+                const int k = yy * 4 + xx;
+                const float inten = ((wTL * px[yy][xx] + wTR * px[yy][xx + 1]) + wBL * px[yy + 1][xx]) + wBR * px[yy + 1][xx + 1];
+                const float res = inten - patch[k * S];
                 float J[6];
 #pragma unroll
-                for (int c = 0; c < 6; c++) J[c] = Jp[c];
+                for (int c = 0; c < 6; c++) J[c] = jac[(k * 6 + c) * S];
                 f[27] += res * res;
                 int q = 0;
 #pragma unroll
@@ -284,7 +305,6 @@ __device__ void alignResiduals(const SparseAlignArgs &A, const float *T, const u
                     for (int c = r; c < 6; c++) f[q++] += J[r] * J[c];
                 }
             }
-        }
 #pragma unroll
         for (int q = 0; q < kAlignSums - 1; q++) acc[q] += (double)f[q];
         acc[28] += 16.0;
@@ -318,7 +338,8 @@ __device__ void alignUnpack(const double *sums, float *H36, float *Jres6) {
 }
 
 __global__ void __launch_bounds__(kAlignThreads) k_sparse_align_precompute(const __grid_constant__ SparseAlignArgs A, int level) {
-    alignPrecompute(A, level, A.refLv[level], A.w[level], A.h[level], A.refPitch[level], A.invScale[level]);
+    alignPrecompute(A, A.refLv[level], A.w[level], A.h[level], A.refPitch[level], A.invScale[level],
+                    blockIdx.x * kAlignThreads + threadIdx.x, gridDim.x * kAlignThreads);
 }
 
 // out: H (36), Jres (6), chi2 sum, n_meas
@@ -328,7 +349,7 @@ __global__ void __launch_bounds__(kAlignThreads) k_sparse_align_residuals(const 
     if (threadIdx.x < 7) T[threadIdx.x] = A.tCurRef[threadIdx.x];
     __syncthreads();
     double acc[kAlignSums];
-    alignResiduals(A, T, A.curLv[level], A.w[level], A.h[level], A.curPitch[level], A.invScale[level], acc);
+    alignResiduals(A, T, A.curLv[level], A.w[level], A.h[level], A.curPitch[level], A.invScale[level], threadIdx.x, kAlignThreads, acc);
     alignReduce(acc, warpBuf, sums);
     if (threadIdx.x == 0) { alignUnpack(sums, out, out + 36); out[42] = (float)sums[27]; out[43] = (float)sums[28]; }
 }
@@ -401,63 +422,85 @@ __device__ void dLdltSolve6(const float *Hin, const float *b, float *x) {   // L
     for (int i = 0; i < 6; i++) x[perm[i]] = y[i];
 }
 
-// SparseImgAlign::run (:20-55) + NLLSSolver::optimizeGaussNewton (include/NLSSolver_impl.hpp:17-92) in one launch.
-// out: TCR (7), n_meas (as float), iterations, final chi2_
-__global__ void __launch_bounds__(kAlignThreads) k_sparse_align_run(const __grid_constant__ SparseAlignArgs A, int maxLevel, int minLevel,
-                                                                    float *out) {
+// SparseImgAlign::run (:20-55) + NLLSSolver::optimizeGaussNewton (include/NLSSolver_impl.hpp:17-92) in one launch on one
+// cluster.  out: TCR (7), n_meas (as float), iterations, final chi2_
+__global__ void __cluster_dims__(kAlignCluster, 1, 1) __launch_bounds__(kAlignThreads)
+k_sparse_align_run(const __grid_constant__ SparseAlignArgs A, int maxLevel, int minLevel, float *out) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
     __shared__ double warpBuf[(kAlignThreads / 32) * kAlignSums], sums[kAlignSums];
-    __shared__ float model[7], oldModel[7];
-    __shared__ int brk;
+    __shared__ float ctl[16];          // CTA 0's copy is the master: [0..6] model, [7] break flag; every CTA mirrors it after the barrier
+    __shared__ float oldModel[7];
     __shared__ float chi2S, nMeasS, itersS;
     __shared__ int stopS;
-    const int tid = threadIdx.x;
-    for (int i = tid; i < A.n; i += blockDim.x) A.visible[i] = 0;          // visible_fts_ = vector<bool>(N, false) (:34)
-    if (tid < 7) model[tid] = A.tCurRef[tid];
-    if (tid == 0) { chi2S = 1e10f; nMeasS = 0.f; itersS = 0.f; stopS = 0; }
+    const int tid = threadIdx.x, rank = (int)cluster.block_rank();
+    const int first = rank * kAlignThreads + tid, step = kAlignCluster * kAlignThreads;
+    for (int i = first; i < A.n; i += step) A.visible[i] = 0;               // visible_fts_ = vector<bool>(N, false) (:34)
+    if (tid < 7) ctl[tid] = A.tCurRef[tid];
+    if (tid == 0) { chi2S = 1e10f; nMeasS = 0.f; itersS = 0.f; stopS = 0; ctl[7] = 0.f; }
     __syncthreads();
+    const double *remoteSums[kAlignCluster];
+    for (int r = 0; r < kAlignCluster; r++) remoteSums[r] = cluster.map_shared_rank(sums, r);
+    const float *masterCtl = cluster.map_shared_rank(ctl, 0);
     for (int level = maxLevel; level >= minLevel; --level) {
-        alignPrecompute(A, level, A.refLv[level], A.w[level], A.h[level], A.refPitch[level], A.invScale[level]);
-        if (tid < 7) oldModel[tid] = model[tid];
-        __syncthreads();
+        alignPrecompute(A, A.refLv[level], A.w[level], A.h[level], A.refPitch[level], A.invScale[level], first, step);
+        if (rank == 0 && tid < 7) oldModel[tid] = ctl[tid];
+        __syncthreads();                                                    // a thread only reads back its own features' caches
         for (int iter = 0; iter < 10; ++iter) {
             double acc[kAlignSums];
-            alignResiduals(A, model, A.curLv[level], A.w[level], A.h[level], A.curPitch[level], A.invScale[level], acc);
+            alignResiduals(A, ctl, A.curLv[level], A.w[level], A.h[level], A.curPitch[level], A.invScale[level], first, step, acc);
             alignReduce(acc, warpBuf, sums);
-            if (tid == 0) {
+            cluster.sync();
+            if (rank == 0 && tid == 0) {
+                double tot[kAlignSums];
+                for (int k = 0; k < kAlignSums; k++) {
+                    double v = 0.0;
+                    for (int r = 0; r < kAlignCluster; r++) v += remoteSums[r][k];
+                    tot[k] = v;
+                }
                 float H[36], Jres[6], x[6];
-                alignUnpack(sums, H, Jres);
-                const float nMeas = (float)sums[28];
-                const float newChi2 = (float)sums[27] / nMeas;
+                alignUnpack(tot, H, Jres);
+                const float nMeas = (float)tot[28];
+                const float newChi2 = (float)tot[27] / nMeas;
                 nMeasS = nMeas; itersS += 1.0f;
                 dLdltSolve6(H, Jres, x);
                 if (isnan(x[0])) stopS = 1;
-                brk = 0;
+                float brk = 0.f;
                 if ((iter > 0 && (double)newChi2 > 1.2 * (double)chi2S) || stopS) {
-                    for (int k = 0; k < 7; k++) model[k] = oldModel[k];       // rollback
-                    brk = 1;
+                    for (int k = 0; k < 7; k++) ctl[k] = oldModel[k];       // rollback
+                    brk = 1.f;
                 } else {
                     float mx[6], E[7], N[7];
                     for (int k = 0; k < 6; k++) mx[k] = -x[k];
                     dSe3Exp(mx, E);
-                    dSe3Compose(model, E, N);
-                    for (int k = 0; k < 7; k++) { oldModel[k] = model[k]; model[k] = N[k]; }
+                    dSe3Compose(ctl, E, N);
+                    for (int k = 0; k < 7; k++) { oldModel[k] = ctl[k]; ctl[k] = N[k]; }
                     chi2S = newChi2;
                     float nm = -1.0f;
                     for (int k = 0; k < 6; k++) nm = fmaxf(nm, fabsf(x[k]));
-                    if (nm <= 0.000001f) brk = 1;
+                    if (nm <= 0.000001f) brk = 1.f;
                 }
+                ctl[7] = brk;
             }
+            cluster.sync();
+            float mine = 0.f;
+            if (tid < 8) mine = masterCtl[tid];
             __syncthreads();
+            if (rank != 0 && tid < 8) ctl[tid] = mine;
+            __syncthreads();
+            const bool brk = ctl[7] != 0.f;
+            cluster.sync();                                                 // CTA 0 may overwrite ctl / sums only after everyone has read them
             if (brk) break;
         }
-        __syncthreads();
     }
-    if (tid < 7) out[tid] = model[tid];
-    if (tid == 0) { out[7] = nMeasS; out[8] = itersS; out[9] = chi2S; }
+    if (rank == 0) {
+        if (tid < 7) out[tid] = ctl[tid];
+        if (tid == 0) { out[7] = nMeasS; out[8] = itersS; out[9] = chi2S; }
+    }
 }
 
 int launchSparseAlignPrecompute(const SparseAlignArgs &A, int level, cudaStream_t s) {
-    k_sparse_align_precompute<<<1, kAlignThreads, 0, s>>>(A, level);
+    k_sparse_align_precompute<<<(A.n + kAlignThreads - 1) / kAlignThreads, kAlignThreads, 0, s>>>(A, level);
     return 1;
 }
 int launchSparseAlignResiduals(const SparseAlignArgs &A, int level, float *out, cudaStream_t s) {
@@ -465,7 +508,7 @@ int launchSparseAlignResiduals(const SparseAlignArgs &A, int level, float *out, 
     return 1;
 }
 int launchSparseAlignRun(const SparseAlignArgs &A, int maxLevel, int minLevel, float *out, cudaStream_t s) {
-    k_sparse_align_run<<<1, kAlignThreads, 0, s>>>(A, maxLevel, minLevel, out);
+    k_sparse_align_run<<<kAlignCluster, kAlignThreads, 0, s>>>(A, maxLevel, minLevel, out);
     return 1;
 }
 

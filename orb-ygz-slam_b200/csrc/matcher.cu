@@ -857,7 +857,7 @@ int ygzorb_sparse_align_begin(ygzorb_sparse_align *sa, const ygzorb_pyramid *ref
     if (n > S->cap) {
         YGZ_CUDA(cudaStreamSynchronize(m->stream));
         sparseAlignFree(S);
-        const size_t cap = (size_t)n + n / 4 + 64;
+        const size_t cap = (((size_t)n + n / 4 + 64) + 31) & ~(size_t)31;
         YGZ_CUDA(cudaMalloc((void **)&S->dKp, cap * 2 * sizeof(float)));
         YGZ_CUDA(cudaMalloc((void **)&S->dWorld, cap * 3 * sizeof(float)));
         YGZ_CUDA(cudaMalloc((void **)&S->dPatch, cap * 16 * sizeof(float)));
@@ -875,7 +875,7 @@ int ygzorb_sparse_align_begin(ygzorb_sparse_align *sa, const ygzorb_pyramid *ref
     }
     S->nLevels = R->nLevels;
     A.focal = focal; A.fx = curIntr[0]; A.fy = curIntr[1]; A.cx = curIntr[2]; A.cy = curIntr[3];
-    A.n = n;
+    A.n = n; A.stride = S->cap;
     A.kpXY = S->dKp; A.worldPos = S->dWorld; A.valid = S->dValid; A.refPose = S->dPose; A.tCurRef = S->dPose + 7;
     A.refPatch = S->dPatch; A.jac = S->dJac; A.visible = S->dVisible;
     if (n > 0) {
@@ -883,7 +883,7 @@ int ygzorb_sparse_align_begin(ygzorb_sparse_align *sa, const ygzorb_pyramid *ref
         YGZ_CUDA(cudaMemcpyAsync(S->dWorld, worldPos, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice, m->stream));
         YGZ_CUDA(cudaMemcpyAsync(S->dValid, valid, (size_t)n, cudaMemcpyHostToDevice, m->stream));
         YGZ_CUDA(cudaMemsetAsync(S->dVisible, 0, (size_t)n, m->stream));
-        YGZ_CUDA(cudaMemsetAsync(S->dPatch, 0, (size_t)n * 16 * sizeof(float), m->stream));
+        YGZ_CUDA(cudaMemsetAsync(S->dPatch, 0, (size_t)S->cap * 16 * sizeof(float), m->stream));
     }
     YGZ_CUDA(cudaMemcpyAsync(S->dPose, refPose, 7 * sizeof(float), cudaMemcpyHostToDevice, m->stream));
     YGZ_CUDA(cudaStreamSynchronize(m->stream));   // the caller's arrays may go away after the call
@@ -955,8 +955,19 @@ int ygzorb_sparse_align_caches(ygzorb_sparse_align *sa, uint8_t *visible, float 
     const size_t n = (size_t)S->A.n;
     if (n == 0) return 0;
     if (visible) YGZ_CUDA(cudaMemcpy(visible, S->dVisible, n, cudaMemcpyDeviceToHost));
-    if (refPatch) YGZ_CUDA(cudaMemcpy(refPatch, S->dPatch, n * 16 * sizeof(float), cudaMemcpyDeviceToHost));
-    if (jac) YGZ_CUDA(cudaMemcpy(jac, S->dJac, n * 96 * sizeof(float), cudaMemcpyDeviceToHost));
+    // device layout is feature-minor (element e of feature i at e * cap + i); the caller gets the reference's [feature][element]
+    const size_t cap = (size_t)S->cap;
+    std::vector<float> tmp;
+    if (refPatch) {
+        tmp.resize(cap * 16);
+        YGZ_CUDA(cudaMemcpy(tmp.data(), S->dPatch, cap * 16 * sizeof(float), cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < n; i++) for (size_t e = 0; e < 16; e++) refPatch[i * 16 + e] = tmp[e * cap + i];
+    }
+    if (jac) {
+        tmp.resize(cap * 96);
+        YGZ_CUDA(cudaMemcpy(tmp.data(), S->dJac, cap * 96 * sizeof(float), cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < n; i++) for (size_t e = 0; e < 96; e++) jac[i * 96 + e] = tmp[e * cap + i];
+    }
     return 0;
 }
 

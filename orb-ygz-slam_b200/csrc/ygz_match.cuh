@@ -166,7 +166,7 @@ struct SparseAlignArgs {
     int w[kMaxLevels], h[kMaxLevels], refPitch[kMaxLevels], curPitch[kMaxLevels];
     float invScale[kMaxLevels];
     float focal, fx, fy, cx, cy;
-    int n;
+    int n, stride;                      // caches are feature-minor: element e of feature i at e * stride + i
     const float *kpXY, *worldPos;
     const uint8_t *valid;
     const float *refPose, *tCurRef;     // 7 floats each, device
