@@ -41,6 +41,25 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def bind_to_gpu_cpus(index):
+    """Pins this rank to the CPUs NVML names as local to its GPU, BEFORE the pinned staging buffers are allocated: on a
+    multi-socket box first-touch then places them on the GPU's own NUMA node, so N ranks do not all stream their frames out
+    of one socket's memory.  Best effort (a container may hide the topology); returns what was done for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = [64 * i + b for i, wd in enumerate(words) for b in range(64) if (wd >> b) & 1]
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            return {"cpus": len(allowed), "first": allowed[0]}
+    except Exception as e:   # noqa: BLE001
+        return {"error": str(e)[:80]}
+    return None
+
+
 class ClockSampler:
     """Samples SM clock and throttle reasons through NVML while the timed region runs."""
 
@@ -220,6 +239,7 @@ def run_ours(args, rank, local_rank, world):
         raise RuntimeError("bench.py needs a CUDA device: the product has no CPU path")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa = bind_to_gpu_cpus(local_rank) if world > 1 else None
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -381,6 +401,8 @@ def run_ours(args, rank, local_rank, world):
         shutdown()
         return
     line = build_line(args, world, B, cap, ms, ms_e2e, launches, clocks, stage_ms, n_kp, n_match, h_mp, mp_keys)
+    if numa is not None:
+        line["config"]["rank_cpu_binding"] = numa
     if world == 1 and not args.no_cpu:
         line["hamming"].update(knn_probe(Y, mt, torch))
         line["cpu_baseline"] = cpu_baseline_leg(frames_np, counts0, kps0, desc0, mp)
