@@ -411,9 +411,14 @@ template <int MODE> __device__ __forceinline__ bool projQuery(const ProjArgs &A,
     return true;
 }
 
+// Frame-side data of the window walk staged in shared memory when it fits (ProjStage::xy != nullptr): keypoint position and
+// (index | octave << 16) in GRID-LIST order, so a thread walking a cell range reads consecutive entries instead of chasing
+// gridList[k] -> kps[idx] through L2, plus the frame's descriptors and the claim table.
+struct ProjStage { const float2 *xy; const uint32_t *meta; const uint4 *desc; };
+
 template <bool RECORD, int MODE>
 __device__ int projMatchOne(const ProjArgs &A, int f, int j, int n, const int *cellStart, const int32_t *gridList,
-                            const int32_t *claimTime, int *recorded, int dir) {
+                            const int32_t *claimTime, int *recorded, int dir, const ProjStage &S) {
     const size_t mo = (size_t)f * A.mpStride + j;
     if (RECORD) *recorded = 0;
     ProjQuery q;
@@ -432,7 +437,8 @@ __device__ int projMatchOne(const ProjArgs &A, int f, int j, int n, const int *c
     const uint4 *md = reinterpret_cast<const uint4 *>(A.mpDesc + mo * 32);
     const uint4 m0 = md[0], m1 = md[1];
     const ygzorb_keypoint *kps = A.kps + (size_t)f * A.kpStride;
-    const uint4 *desc = reinterpret_cast<const uint4 *>(A.desc + (size_t)f * A.kpStride * 32);
+    const bool staged = S.xy != nullptr;
+    const uint4 *desc = staged ? S.desc : reinterpret_cast<const uint4 *>(A.desc + (size_t)f * A.kpStride * 32);
     const float *uRight = A.uRight ? A.uRight + (size_t)f * A.kpStride : nullptr;
     const float projXR = q.xr;
     int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
@@ -442,14 +448,22 @@ __device__ int projMatchOne(const ProjArgs &A, int f, int j, int n, const int *c
     for (int ix = cx0; ix <= cx1; ix++) {
         const int cb = ix * kGridRows;
         for (int k = cellStart[cb + cy0], ke = cellStart[cb + cy1 + 1]; k < ke; k++) {   // cells (ix, cy0..cy1) are contiguous
-            const int idx = gridList[k];
-            const ygzorb_keypoint &kp = kps[idx];
-            const int oct = kp.octave;
+            int idx, oct;
+            float kx, ky;
+            if (staged) {
+                const float2 p = S.xy[k];
+                const uint32_t me = S.meta[k];
+                idx = (int)(me & 0xffffu); oct = (int)(me >> 16); kx = p.x; ky = p.y;
+            } else {
+                idx = gridList[k];
+                const ygzorb_keypoint &kp0 = kps[idx];
+                oct = kp0.octave; kx = kp0.x; ky = kp0.y;
+            }
             if (checkLevels) {
                 if (oct < minLevel) continue;
                 if (maxLevel >= 0 && oct > maxLevel) continue;
             }
-            if (!(fabsf(__fsub_rn(kp.x, x)) < rad && fabsf(__fsub_rn(kp.y, y)) < rad)) continue;
+            if (!(fabsf(__fsub_rn(kx, x)) < rad && fabsf(__fsub_rn(ky, y)) < rad)) continue;
             const bool skip = claimTime[idx] < j;                      // mvpMapPoints[idx]->Observations() > 0 (:89-91)
             if (!RECORD && skip) continue;
             if (MODE <= 1 && uRight) {
@@ -457,7 +471,7 @@ __device__ int projMatchOne(const ProjArgs &A, int f, int j, int n, const int *c
                 if (ur > 0 && fabsf(__fsub_rn(projXR, ur)) > rad) continue;   // :93-97
             }
             if (MODE == 4) {   // reprojection error gate of Fuse (:835-858)
-                const float ex = __fsub_rn(x, kp.x), ey = __fsub_rn(y, kp.y);
+                const float ex = __fsub_rn(x, kx), ey = __fsub_rn(y, ky);
                 float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
                 const float kpr = uRight ? uRight[idx] : -1.0f;
                 double lim = 5.99;
@@ -485,11 +499,16 @@ template <int MODE> __global__ void __launch_bounds__(kProjThreads) k_search_by_
     __shared__ int dirS, hist[kHistoLength], keep[3];
     __shared__ int cellFill[kGridCols * kGridRows];
     __shared__ int ws[40];
+    extern __shared__ __align__(16) uint8_t projSmem[];   // A.stageSmem: [desc 32 B][xy 8 B][meta 4 B][claim 4 B] x kpStride
     const int f = blockIdx.x, tid = threadIdx.x;
     const int n = min(A.nKp[f], A.kpStride), m = min(A.nMp[f], A.mpStride);
     const ygzorb_keypoint *kps = A.kps + (size_t)f * A.kpStride;
     int32_t *gridList = A.gridList + (size_t)f * A.kpStride;
-    int32_t *claimTime = A.claimTime + (size_t)f * A.kpStride;
+    uint4 *sDesc = reinterpret_cast<uint4 *>(projSmem);
+    float2 *sXY = reinterpret_cast<float2 *>(projSmem + (size_t)A.kpStride * 32);
+    uint32_t *sMeta = reinterpret_cast<uint32_t *>(projSmem + (size_t)A.kpStride * 40);
+    int32_t *claimTime = A.stageSmem ? reinterpret_cast<int32_t *>(projSmem + (size_t)A.kpStride * 44) : A.claimTime + (size_t)f * A.kpStride;
+    ProjStage S{nullptr, nullptr, nullptr};
     int32_t *best = A.mpBestIdx + (size_t)f * A.mpStride;
     int32_t *kpToMp = A.kpToMp + (size_t)f * A.kpStride;
     const uint8_t *claimed = A.claimed ? A.claimed + (size_t)f * A.kpStride : nullptr;
@@ -519,6 +538,18 @@ template <int MODE> __global__ void __launch_bounds__(kProjThreads) k_search_by_
             gridList[k + 1] = v;
         }
     }
+    if (A.stageSmem) {
+        __syncthreads();
+        const uint4 *gdesc = reinterpret_cast<const uint4 *>(A.desc + (size_t)f * A.kpStride * 32);
+        for (int i = tid; i < 2 * n; i += kProjThreads) sDesc[i] = gdesc[i];
+        for (int k = tid; k < total; k += kProjThreads) {
+            const int idx = gridList[k];
+            const ygzorb_keypoint &kp = kps[idx];
+            sXY[k] = make_float2(kp.x, kp.y);
+            sMeta[k] = (uint32_t)idx | ((uint32_t)kp.octave << 16);
+        }
+        S.xy = sXY; S.meta = sMeta; S.desc = sDesc;
+    }
     uint8_t *candCnt = A.candCnt + (size_t)f * A.mpStride;
     if (MODE == 1 && tid == 0) {   // tlc = Rlw * (-Rcw^T tcw) + tlw; forward / backward motion along the optical axis (:1227-1239)
         const float *P = A.pose + (size_t)f * 30;
@@ -537,7 +568,7 @@ template <int MODE> __global__ void __launch_bounds__(kProjThreads) k_search_by_
     __syncthreads();
     for (int j = tid; j < m; j += kProjThreads) {
         int nrec;
-        best[j] = projMatchOne<true, MODE>(A, f, j, n, cellStart, gridList, claimTime, &nrec, dir);
+        best[j] = projMatchOne<true, MODE>(A, f, j, n, cellStart, gridList, claimTime, &nrec, dir, S);
         candCnt[j] = (uint8_t)(nrec > kProjCache ? kProjOverflow : nrec);
     }
     __syncthreads();
@@ -553,7 +584,7 @@ template <int MODE> __global__ void __launch_bounds__(kProjThreads) k_search_by_
         int changed = 0;
         for (int j = tid; j < m; j += kProjThreads) {
             const int cnt = candCnt[j];
-            const int b = cnt == kProjOverflow ? projMatchOne<false, MODE>(A, f, j, n, cellStart, gridList, claimTime, nullptr, dir)
+            const int b = cnt == kProjOverflow ? projMatchOne<false, MODE>(A, f, j, n, cellStart, gridList, claimTime, nullptr, dir, S)
                                                : projMatchCached<MODE>(A, f, j, cnt, claimTime);
             if (b != best[j]) { best[j] = b; changed = 1; }
         }
@@ -604,21 +635,41 @@ template <int MODE> __global__ void __launch_bounds__(kProjThreads) k_search_by_
     if (tid == 0) A.nMatches[f] = ws[0];
 }
 
+// Shared-memory staging of the frame side (48 B per keypoint slot) when it leaves room for two CTAs per SM; octaves must fit
+// 16 bits next to a 16-bit keypoint index (kpStride <= 65536 is assumed by the candidate cache already).
+constexpr int kProjStageMax = 96 * 1024;
+static int projStageBytes(ProjArgs &A) {
+    const size_t b = (size_t)A.kpStride * 48;
+    A.stageSmem = (A.kpStride <= 65536 && b <= (size_t)kProjStageMax) ? 1 : 0;
+    return A.stageSmem ? (int)b : 0;
+}
+template <int MODE> static void launchProj(ProjArgs A, cudaStream_t s) {
+    static bool configured[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !configured[dev]) {
+        cudaFuncSetAttribute(k_search_by_projection<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kProjStageMax);
+        configured[dev] = true;
+    }
+    const int smem = projStageBytes(A);
+    k_search_by_projection<MODE><<<A.nFrames, kProjThreads, smem, s>>>(A);
+}
+
 int launchSearchByProjection(const ProjArgs &A, int maxKp, cudaStream_t s) {
     (void)maxKp;
     if (A.nFrames <= 0) return 0;
-    k_search_by_projection<0><<<A.nFrames, kProjThreads, 0, s>>>(A);
+    launchProj<0>(A, s);
     return 1;
 }
 
 int launchSearchByProjectionKeyFrame(const ProjArgs &A, int mode, cudaStream_t s) {
     if (A.nFrames <= 0) return 0;
     switch (mode) {
-        case 2: k_search_by_projection<2><<<A.nFrames, kProjThreads, 0, s>>>(A); break;
-        case 3: k_search_by_projection<3><<<A.nFrames, kProjThreads, 0, s>>>(A); break;
-        case 4: k_search_by_projection<4><<<A.nFrames, kProjThreads, 0, s>>>(A); break;
-        case 5: k_search_by_projection<5><<<A.nFrames, kProjThreads, 0, s>>>(A); break;
-        default: k_search_by_projection<6><<<A.nFrames, kProjThreads, 0, s>>>(A); break;
+        case 2: launchProj<2>(A, s); break;
+        case 3: launchProj<3>(A, s); break;
+        case 4: launchProj<4>(A, s); break;
+        case 5: launchProj<5>(A, s); break;
+        default: launchProj<6>(A, s); break;
     }
     return 1;
 }
@@ -653,7 +704,7 @@ int launchSim3Agreement(const int32_t *match1, const int32_t *match2, const int3
 
 int launchSearchByProjectionLast(const ProjArgs &A, cudaStream_t s) {
     if (A.nFrames <= 0) return 0;
-    k_search_by_projection<1><<<A.nFrames, kProjThreads, 0, s>>>(A);
+    launchProj<1>(A, s);
     return 1;
 }
 

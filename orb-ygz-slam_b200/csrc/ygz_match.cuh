@@ -41,6 +41,7 @@ struct ProjArgs {
     int32_t *gridList;                        // scratch [nFrames * kpStride]
     uint32_t *candCache;                      // scratch [nFrames * 12 * mpStride]
     uint8_t *candCnt;                         // scratch [nFrames * mpStride]
+    int stageSmem;                            // set by the launcher: frame-side arrays staged in dynamic shared memory
 };
 
 // ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:375-478), batched over frame pairs
