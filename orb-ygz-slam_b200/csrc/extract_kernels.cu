@@ -266,12 +266,11 @@ __device__ __forceinline__ int fastMeasure(unsigned p) {
 // score tile holds m for m > t (t = the threshold in force) and 0 elsewhere (and outside the detection area).
 __global__ void __launch_bounds__(kFastThreads, 12) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
     // dynamic shared memory, sized by the geometry's largest cell (FrameGeom::fastRegionA/fastScoreBytes/fastWarpCap):
-    // [image tile, re-used from phase 2 on for the per-warp maxima lists][score tile][per-warp corner lists]
+    // [image tile][score tile][per-warp corner lists]
     extern __shared__ __align__(16) uint8_t fastSmem[];
     uint8_t *tile = fastSmem;
     uint8_t *score = fastSmem + G.fastRegionA;
-    uint16_t *corners = reinterpret_cast<uint16_t *>(score + G.fastScoreBytes);   // per warp: tile offsets of pixels with m > minThFAST
-    uint16_t *maxima = reinterpret_cast<uint16_t *>(fastSmem);                    // per warp: the strict local maxima among them
+    uint16_t *corners = reinterpret_cast<uint16_t *>(score + G.fastScoreBytes);   // per warp: tile offsets of pretest passers, then of the corners
     const int kFastWarpCap = G.fastWarpCap;
     const int f = blockIdx.y, tid = threadIdx.x;
     // cell window (src/ORBextractor.cc:749-762) from the host-built cell table; detection area = window minus 3 px
@@ -328,8 +327,10 @@ __global__ void __launch_bounds__(kFastThreads, 12) k_fast(const __grid_constant
     const unsigned centre = smemAddr(tile + 3 * kTilePitch + 3 + ox);
     const unsigned sc0a = smemAddr(score + kTilePitch + 1);
     const unsigned cornersAt = smemAddr(corners + wid * kFastWarpCap);
-    const unsigned maximaAt = smemAddr(maxima + wid * kFastWarpCap);
-    int t = iniTh, n2 = 0;
+    uint2 *cand = B.cand + (long long)f * G.candPerFrame + L.candOff;
+    int *counter = B.candCount + f * kMaxLevels + level;
+    const int candCap = L.candCap;
+    int t = iniTh;
     for (;;) {
         const unsigned pre2 = ((unsigned)t + 256u) * 0x10001u;
         int n0 = 0;
@@ -358,60 +359,43 @@ __global__ void __launch_bounds__(kFastThreads, 12) k_fast(const __grid_constant
             n1 += __popc(mask);
         }
         __syncthreads();
-        // ---- phase 2: strict local maxima of m among the warp's corners (non-corners hold 0 in the score tile).
-        // The maxima lists alias the image tile: once a maximum exists the tile is not needed any more.
+        // ---- phase 2: strict local maxima of m among the warp's corners (non-corners hold 0 in the score tile) are the
+        // keypoints of the cell.  A warp that finds one knows the pass is final (the cell has a survivor), so it appends its
+        // maxima to the level's candidate array right away, one atomicAdd per batch; a cell where no warp finds any repeats
+        // the pass at minThFAST.
         int any = 0;
-        n2 = 0;
         for (int k0 = 0; k0 < n1; k0 += 32) {
             const int k = k0 + lane;
             bool ismax = false;
-            unsigned o = 0;
+            unsigned o = 0, m = 0;
             if (k < n1) {
                 constexpr int P = kTilePitch;
                 o = ldsU16(cornersAt + 2 * k);
                 const unsigned sc = sc0a + o;
-                const unsigned m = ldsU8<0>(sc);
+                m = ldsU8<0>(sc);
                 const unsigned nb = max(max(max(ldsU8<-1>(sc), ldsU8<1>(sc)), max(ldsU8<-P - 1>(sc), ldsU8<-P>(sc))),
                                         max(max(ldsU8<-P + 1>(sc), ldsU8<P - 1>(sc)), max(ldsU8<P>(sc), ldsU8<P + 1>(sc))));
                 ismax = nb < m;
             }
             const unsigned mask = __ballot_sync(0xffffffffu, ismax);
-            any |= (int)mask;
-            if (ismax) stsU16(maximaAt + 2 * (n2 + __popc(mask & ltMask)), o);
-            n2 += __popc(mask);
-        }
-        // no maximum anywhere in the cell <=> nothing was written over the tile: the minThFAST pass can re-read it
-        if (__syncthreads_or(any) || t == minTh) break;
-        t = minTh;
-    }
-    // ---- every maximum of the final pass is a keypoint of the cell
-    uint2 *cand = B.cand + (long long)f * G.candPerFrame + L.candOff;
-    int *counter = B.candCount + f * kMaxLevels + level;
-    for (int k0 = 0; k0 < n2; k0 += 32) {
-        const int k = k0 + lane;
-        bool keep = false;
-        int y = 0, x = 0, m = 0;
-        if (k < n2) {
-            const int o = (int)ldsU16(maximaAt + 2 * k);
-            y = (o * ((1 << 20) / kTilePitch + 1)) >> 20; x = o - y * kTilePitch;   // exact for o < 2^13
-            m = (int)ldsU8<0>(sc0a + o);
-            keep = true;
-        }
-        const unsigned mask = __ballot_sync(0xffffffffu, keep);
-        if (mask == 0) continue;
-        int base = 0;
-        if (lane == __ffs(mask) - 1) base = atomicAdd(counter, __popc(mask));
-        base = __shfl_sync(0xffffffffu, base, __ffs(mask) - 1);
-        if (keep) {
-            const int slot = base + __popc(mask & ltMask);
-            if (slot < L.candCap) {
-                const uint32_t ax = iniX + 3 + x, ay = iniY + 3 + y;  // absolute level coordinates
-                cand[slot] = make_uint2(ax | (ay << 12) | ((uint32_t)(m - 1) << 24),
-                                        ((uint32_t)cell << 12) | ((uint32_t)y << 6) | (uint32_t)x);
-            } else {
-                atomicOr(B.status, 1);
+            if (mask == 0) continue;
+            any = 1;
+            int base = 0;
+            if (lane == 0) base = atomicAdd(counter, __popc(mask));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (ismax) {
+                const int slot = base + __popc(mask & ltMask);
+                if (slot < candCap) {
+                    const unsigned y = (o * ((1u << 20) / kTilePitch + 1)) >> 20, x = o - y * kTilePitch;   // exact for o < 2^13
+                    const uint32_t ax = iniX + 3 + x, ay = iniY + 3 + y;  // absolute level coordinates
+                    cand[slot] = make_uint2(ax | (ay << 12) | ((uint32_t)(m - 1) << 24), ((uint32_t)cell << 12) | (y << 6) | x);
+                } else {
+                    atomicOr(B.status, 1);
+                }
             }
         }
+        if (__syncthreads_or(any) || t == minTh) break;
+        t = minTh;
     }
 }
 

@@ -218,10 +218,9 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
             }
     }
     G.totalCells = cells; G.totalTiles = tiles;
-    // k_fast shared memory: [image tile | per-warp maxima lists (alias, phase 2 on)] [score tile] [per-warp corner lists];
-    // a list holds every pixel its warp visits (strict maxima can reach 17 of 32 consecutive pixels on dot patterns)
+    // k_fast shared memory: [image tile] [score tile] [per-warp lists]; a list holds every pixel its warp visits
     G.fastWarpCap = (maxNpx + 127) / 128 * 32;
-    G.fastRegionA = alignUp(std::max((maxDh + 6) * kFastTilePitch, 8 * G.fastWarpCap), 16);
+    G.fastRegionA = alignUp((maxDh + 6) * kFastTilePitch, 16);
     G.fastScoreBytes = alignUp((maxDh + 2) * kFastTilePitch, 16);
     G.cellTab = (int)tabs.size(); tabs.insert(tabs.end(), cellTab.begin(), cellTab.end());
     G.tileTab = (int)tabs.size(); tabs.insert(tabs.end(), tileTab.begin(), tileTab.end());
