@@ -264,7 +264,7 @@ __device__ __forceinline__ int fastMeasure(unsigned p) {
 // stored score m-1 exceeds the stored scores of its 8 neighbours, and a neighbour's stored score is
 // n-1 if n > t and 0 otherwise; since m > t >= 1 this is exactly "every neighbour has n < m".  The
 // score tile holds m for m > t (t = the threshold in force) and 0 elsewhere (and outside the detection area).
-__global__ void __launch_bounds__(kFastThreads, 12) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+__global__ void __launch_bounds__(kFastThreads, 16) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
     // dynamic shared memory, sized by the geometry's largest cell (FrameGeom::fastRegionA/fastScoreBytes/fastWarpCap):
     // [image tile][score tile][per-warp corner lists]
     extern __shared__ __align__(16) uint8_t fastSmem[];
