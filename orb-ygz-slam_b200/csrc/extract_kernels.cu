@@ -9,6 +9,19 @@
 
 namespace ygz {
 
+// <<<>>> or, with B.pdl, cudaLaunchKernelEx with programmatic stream serialization (the kernel may start while its predecessor
+// in the stream still runs; pdlEnter() in the kernel orders the data)
+template <class... KArgs, class... Args>
+static void launchChain(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+
 // =================================================================================================
 // K1 — pyramid level by cv::resize(INTER_LINEAR), 8UC1 (src/ORBextractor.cc:1139).
 // OpenCV's HResizeLinear/VResizeLinear fixed point: 11-bit coefficients, horizontal pass in int32,
@@ -18,7 +31,8 @@ namespace ygz {
 // Table entry X[dx] = {x0 | x1<<16, a0 | a1<<16}; Y[dy] = {y0 | y1<<16, b0 | b1<<16}.
 constexpr int kResizeRows = 4;   // destination rows per thread
 
-__global__ void __launch_bounds__(256) k_resize_generic(const __grid_constant__ FrameGeom G, const DevBuffers B, int level) {
+template <bool PDL> __global__ void __launch_bounds__(256) k_resize_generic(const __grid_constant__ FrameGeom G, const DevBuffers B, int level) {
+    if (PDL) pdlEnter(B);
     const LevelGeom &D = G.lv[level];
     const LevelGeom &S = G.lv[level - 1];
     const int f = blockIdx.z;
@@ -100,7 +114,8 @@ __global__ void __launch_bounds__(256) k_resize_generic(const __grid_constant__ 
 // 16-bit weights (a0 | a1 << 16) exactly as the table stores them.  The vertical pass uses the high half of
 // the 32-bit products ((b * (h >> 4)) >> 16); the saturate_cast of the reference is the identity here
 // (weights sum to 2048, so the result is <= 255).
-__global__ void __launch_bounds__(256) k_resize(const __grid_constant__ FrameGeom G, const DevBuffers B, int level) {
+template <bool PDL> __global__ void __launch_bounds__(256) k_resize(const __grid_constant__ FrameGeom G, const DevBuffers B, int level) {
+    if (PDL) pdlEnter(B);
     const LevelGeom &D = G.lv[level];
     const LevelGeom &S = G.lv[level - 1];
     const int f = blockIdx.z;
@@ -174,8 +189,10 @@ int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nF
     // level 0 is caller memory: the word path needs 4-byte aligned rows there (levels >= 1 always are)
     const bool rowsAligned = (S.pitch & 3) == 0 &&
                              (level > 1 || ((reinterpret_cast<uintptr_t>(B.in) & 3) == 0 && (B.inFrameStride & 3) == 0));
-    if (D.fastResize && !D.area2x && rowsAligned) k_resize<<<grid, block, 0, s>>>(G, B, level);
-    else k_resize_generic<<<grid, block, 0, s>>>(G, B, level);
+    const bool word = D.fastResize && !D.area2x && rowsAligned;
+    if (B.pdl) { if (word) launchChain(true, k_resize<true>, grid, block, 0, s, G, B, level); else launchChain(true, k_resize_generic<true>, grid, block, 0, s, G, B, level); }
+    else if (word) k_resize<false><<<grid, block, 0, s>>>(G, B, level);
+    else k_resize_generic<false><<<grid, block, 0, s>>>(G, B, level);
     return 1;
 }
 
@@ -264,7 +281,8 @@ __device__ __forceinline__ int fastMeasure(unsigned p) {
 // stored score m-1 exceeds the stored scores of its 8 neighbours, and a neighbour's stored score is
 // n-1 if n > t and 0 otherwise; since m > t >= 1 this is exactly "every neighbour has n < m".  The
 // score tile holds m for m > t (t = the threshold in force) and 0 elsewhere (and outside the detection area).
-__global__ void __launch_bounds__(kFastThreads, 16) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+template <bool PDL> __global__ void __launch_bounds__(kFastThreads, 16) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+    if (PDL) pdlEnter(B);
     // dynamic shared memory, sized by the geometry's largest cell (FrameGeom::fastRegionA/fastScoreBytes/fastWarpCap):
     // [image tile][score tile][per-warp corner lists]
     extern __shared__ __align__(16) uint8_t fastSmem[];
@@ -403,7 +421,8 @@ int launchFast(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_
     if (G.totalCells == 0) return 0;
     size_t smem = (size_t)G.fastRegionA + G.fastScoreBytes + (size_t)(kFastThreads / 32) * G.fastWarpCap * sizeof(uint16_t);
     if (const char *pad = getenv("YGZ_FAST_SMEM_PAD")) smem += (size_t)atoi(pad);   // occupancy experiments
-    k_fast<<<dim3(G.totalCells, nFrames), kFastThreads, smem, s>>>(G, B);
+    if (B.pdl) launchChain(true, k_fast<true>, dim3(G.totalCells, nFrames), dim3(kFastThreads), smem, s, G, B);
+    else k_fast<false><<<dim3(G.totalCells, nFrames), kFastThreads, smem, s>>>(G, B);
     return 1;
 }
 
@@ -544,7 +563,8 @@ __device__ int qtCommit(const QtSmem &S, const short4 *b1, const int *c1, short4
     return totalChildren + untouched;
 }
 
-__global__ void __launch_bounds__(kQtThreads) k_quadtree(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+template <bool PDL> __global__ void __launch_bounds__(kQtThreads) k_quadtree(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+    if (PDL) pdlEnter(B);
     extern __shared__ __align__(16) unsigned char qtRaw[];
     const int level = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
     const LevelGeom &L = G.lv[level];
@@ -701,7 +721,8 @@ size_t quadtreeSmemBytes(int listCap) {
 }
 
 int launchQuadtree(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s) {
-    k_quadtree<<<dim3(G.nlevels, nFrames), kQtThreads, quadtreeSmemBytes(G.maxListCap), s>>>(G, B);
+    if (B.pdl) launchChain(true, k_quadtree<true>, dim3(G.nlevels, nFrames), dim3(kQtThreads), quadtreeSmemBytes(G.maxListCap), s, G, B);
+    else k_quadtree<false><<<dim3(G.nlevels, nFrames), kQtThreads, quadtreeSmemBytes(G.maxListCap), s>>>(G, B);
     return 1;
 }
 
@@ -726,7 +747,8 @@ __device__ __forceinline__ void cpAsync16(void *smemDst, const void *gmemSrc) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smemDst)), "l"(gmemSrc));
 }
 
-__global__ void __launch_bounds__(kBlurThreads) k_blur(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+template <bool PDL> __global__ void __launch_bounds__(kBlurThreads) k_blur(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+    if (PDL) pdlEnter(B);
     __shared__ __align__(16) uint8_t raw[kBlurRawRows * kBlurRawPitch];
     __shared__ __align__(16) uint2 hs[kBlurRawRows * (kBlurTW / 4)];   // 4 x u16 horizontal sums
     const int f = blockIdx.y, tid = threadIdx.x;
@@ -837,7 +859,8 @@ __global__ void __launch_bounds__(kBlurThreads) k_blur(const __grid_constant__ F
 
 int launchBlur(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s) {
     if (G.totalTiles == 0) return 0;
-    k_blur<<<dim3(G.totalTiles, nFrames), kBlurThreads, 0, s>>>(G, B);
+    if (B.pdl) launchChain(true, k_blur<true>, dim3(G.totalTiles, nFrames), dim3(kBlurThreads), 0, s, G, B);
+    else k_blur<false><<<dim3(G.totalTiles, nFrames), kBlurThreads, 0, s>>>(G, B);
     return 1;
 }
 
@@ -962,8 +985,9 @@ __device__ __forceinline__ int orbByteWarp(const uint8_t *cb, int bp, float angl
 
 constexpr int kDescWarps = 8;
 
-__global__ void __launch_bounds__(kDescWarps * 32) k_describe(const __grid_constant__ FrameGeom G, const DevBuffers B, int cap,
+template <bool PDL> __global__ void __launch_bounds__(kDescWarps * 32) k_describe(const __grid_constant__ FrameGeom G, const DevBuffers B, int cap,
                                                               int32_t *counts, ygzorb_keypoint *kps, uint8_t *desc) {
+    if (PDL) pdlEnter(B);
     const int f = blockIdx.y, lane = threadIdx.x & 31;
     const int j = blockIdx.x * kDescWarps + (threadIdx.x >> 5);
     // level-major offsets from the per-level kept counts
@@ -997,7 +1021,8 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(const __grid_const
 int launchDescribe(const FrameGeom &G, const DevBuffers &B, int nFrames, int cap, int32_t *counts,
                    ygzorb_keypoint *kps, uint8_t *desc, cudaStream_t s) {
     const int blocks = (min(cap, G.keptCap) + kDescWarps - 1) / kDescWarps;
-    k_describe<<<dim3(max(blocks, 1), nFrames), kDescWarps * 32, 0, s>>>(G, B, cap, counts, kps, desc);
+    if (B.pdl) launchChain(true, k_describe<true>, dim3(max(blocks, 1), nFrames), dim3(kDescWarps * 32), 0, s, G, B, cap, counts, kps, desc);
+    else k_describe<false><<<dim3(max(blocks, 1), nFrames), kDescWarps * 32, 0, s>>>(G, B, cap, counts, kps, desc);
     return 1;
 }
 
@@ -1082,7 +1107,8 @@ int configureKernels() {
     YGZ_CUDA(cudaGetDevice(&dev));
     if (dev >= 0 && dev < 64 && gConfigured[dev]) return 0;
     YGZ_CUDA(cudaMemcpyToSymbol(gPattern, kOrbPattern, sizeof(kOrbPattern)));
-    YGZ_CUDA(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    YGZ_CUDA(cudaFuncSetAttribute(k_quadtree<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    YGZ_CUDA(cudaFuncSetAttribute(k_quadtree<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     if (dev >= 0 && dev < 64) gConfigured[dev] = true;
     return 0;
 }

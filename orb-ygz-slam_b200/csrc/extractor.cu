@@ -385,6 +385,8 @@ static int applyUndistort(Extractor *ex, int n, int w, int h, int srcPitch) {
     return 0;
 }
 
+constexpr int kPdlMaxFrames = 8;
+
 static int runPyramid(Extractor *ex, int n) {
     for (int l = 1; l < ex->G.nlevels; l++) ex->launches += launchResizeLevel(ex->G, ex->B, l, n, ex->stream);
     return 0;
@@ -402,6 +404,7 @@ static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int 
     if ((rc = applyUndistort(ex, n, w, h, srcPitch))) return rc;
     YGZ_CUDA(cudaMemsetAsync(ex->dCounts, 0, (2 * (size_t)ex->maxBatch * kMaxLevels + 1) * sizeof(int), ex->stream));
     YGZ_MARK(1);
+    ex->B.pdl = (n <= kPdlMaxFrames && !ex->profiling) ? 1 : 0;   // live tracking: the chain is launch-latency bound
     runPyramid(ex, n);
     YGZ_MARK(2);
     ex->launches += launchFast(ex->G, ex->B, n, ex->stream);
@@ -416,6 +419,7 @@ static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int 
     uint8_t *od = outDev ? desc : ex->dOutDesc[os];
     if (!outDev) YGZ_CUDA(cudaStreamWaitEvent(ex->stream, ex->outFree[os], 0));
     ex->launches += launchDescribe(ex->G, ex->B, n, cap, oc, ok, od, ex->stream);
+    ex->B.pdl = 0;
     YGZ_MARK(6);
     if (!inDev) YGZ_CUDA(cudaEventRecord(ex->inFree[slot], ex->stream));   // IC_Angle was the last reader of level 0
     if (!outDev) {   // drain on the download stream so that the next chunk's kernels overlap it

@@ -71,7 +71,19 @@ struct DevBuffers {
     uint32_t *kept;            // kept keypoints x | y<<12 | resp<<24: kept + f*keptCap + lv[l].keptOff
     int *keptCount;            // [frame][kMaxLevels]
     int *status;               // device-side error flags
+    int pdl;                   // launched with programmatic dependent launch (small batches): kernels release their dependents early
 };
+
+#ifdef __CUDACC__
+// Programmatic dependent launch (sm_90+).  Every kernel of the extraction chain waits for its predecessor before it touches
+// anything a previous kernel wrote; with B.pdl it first lets the NEXT kernel of the stream start launching, so that kernel's
+// launch latency and prologue overlap this kernel's execution.  Used for small batches (live tracking), where the chain of 11
+// short kernels is launch-latency bound; a no-op for kernels launched the ordinary way.
+__device__ __forceinline__ void pdlEnter(const DevBuffers &B) {
+    if (B.pdl) asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+#endif
 
 __device__ __forceinline__ const uint8_t *levelPtr(const FrameGeom &G, const DevBuffers &B, int f, int l) {
     return l == 0 ? B.in + (long long)f * B.inFrameStride : B.pyr + (long long)f * G.slabBytes + G.lv[l].off;
