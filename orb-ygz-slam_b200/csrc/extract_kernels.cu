@@ -442,7 +442,8 @@ int launchFast(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_
 //    inside a node is the original vToDistributeKeys order, carried here by the candidates' order key.
 // So points never move: each point carries the index of its node, and a pass is two sweeps over the
 // points (count children, relabel) plus block-wide scans over the node list.
-constexpr int kQtThreads = 512;
+constexpr int kQtThreads = 512;        // CTA size for small batches (one frame: latency); batches run kQtThreadsBatch
+constexpr int kQtThreadsBatch = 256;   // more CTAs per SM hide the barrier stalls of the passes (0.47 -> 0.43 ms / 512 frames)
 
 struct QtSmem {
     short4 *bA, *bB;      // node bounds x0,x1,y0,y1 (x = UL.x, y = UR.x, z = UL.y, w = BL.y)
@@ -465,8 +466,8 @@ __device__ __forceinline__ int qtQuadrant(uint32_t xyr, const short4 b) {
 }
 
 // In-place exclusive scan of a[0..n) by the whole CTA; returns the total.  `ws` = 33 ints scratch.
-__device__ int qtScan(int *a, int n, int *ws) {
-    const int T = kQtThreads, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+template <int QT> __device__ int qtScan(int *a, int n, int *ws) {
+    const int T = QT, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int chunk = (n + T - 1) / T;
     const int b = min(tid * chunk, n), e = min(b + chunk, n);
     int sum = 0;
@@ -499,10 +500,10 @@ __device__ int qtScan(int *a, int n, int *ws) {
 }
 
 // Sweep 1 of a pass: per processed parent (rank r), count the points falling in each quadrant.
-__device__ void qtCountChildren(const QtSmem &S, const short4 *bnd, int P, const uint2 *cand, const uint16_t *nodeOf, int np) {
-    for (int i = threadIdx.x; i < 4 * P; i += kQtThreads) S.childCnt[i] = 0;
+template <int QT> __device__ void qtCountChildren(const QtSmem &S, const short4 *bnd, int P, const uint2 *cand, const uint16_t *nodeOf, int np) {
+    for (int i = threadIdx.x; i < 4 * P; i += QT) S.childCnt[i] = 0;
     __syncthreads();
-    for (int p = threadIdx.x; p < np; p += kQtThreads) {
+    for (int p = threadIdx.x; p < np; p += QT) {
         const int nd = nodeOf[p];
         const int r = S.procOrder[nd];
         if (r >= 0) atomicAdd(&S.childCnt[4 * r + qtQuadrant(cand[p].x, bnd[nd])], 1);
@@ -513,19 +514,19 @@ __device__ void qtCountChildren(const QtSmem &S, const short4 *bnd, int P, const
 // Rest of a pass: builds the new list (into b2/c2/g2) from the old one (b1/c1) given procOrder /
 // byOrder / childCnt for P processed parents, relabels the points.  Returns the new list size and
 // the number of multi-point children through *nToExpand.
-__device__ int qtCommit(const QtSmem &S, const short4 *b1, const int *c1, short4 *b2, int *c2, int *g2, int n, int P,
+template <int QT> __device__ int qtCommit(const QtSmem &S, const short4 *b1, const int *c1, short4 *b2, int *c2, int *g2, int n, int P,
                         const uint2 *cand, uint16_t *nodeOf, int np, int *nToExpand) {
     const int tid = threadIdx.x;
-    for (int r = tid; r < P; r += kQtThreads) {
+    for (int r = tid; r < P; r += QT) {
         const int *c = &S.childCnt[4 * r];
         S.scanR[r] = (c[0] > 0) + (c[1] > 0) + (c[2] > 0) + (c[3] > 0);
     }
-    for (int i = tid; i < n; i += kQtThreads) S.scanU[i] = S.procOrder[i] < 0;
+    for (int i = tid; i < n; i += QT) S.scanU[i] = S.procOrder[i] < 0;
     if (tid == 0) S.misc[33] = 0;
     __syncthreads();
-    const int totalChildren = qtScan(S.scanR, P, S.misc);
-    const int untouched = qtScan(S.scanU, n, S.misc);
-    for (int r = tid; r < P; r += kQtThreads) {
+    const int totalChildren = qtScan<QT>(S.scanR, P, S.misc);
+    const int untouched = qtScan<QT>(S.scanU, n, S.misc);
+    for (int r = tid; r < P; r += QT) {
         const short4 pb = b1[S.byOrder[r]];
         const int mx = pb.x + ((pb.y - pb.x + 1) >> 1), my = pb.z + ((pb.w - pb.z + 1) >> 1);
         int seq = S.scanR[r], multi = 0;
@@ -545,7 +546,7 @@ __device__ int qtCommit(const QtSmem &S, const short4 *b1, const int *c1, short4
         }
         if (multi) atomicAdd(&S.misc[33], multi);
     }
-    for (int i = tid; i < n; i += kQtThreads) {
+    for (int i = tid; i < n; i += QT) {
         if (S.procOrder[i] < 0) {
             const int pos = totalChildren + S.scanU[i];
             b2[pos] = b1[i]; c2[pos] = c1[i]; g2[pos] = -1;
@@ -553,7 +554,7 @@ __device__ int qtCommit(const QtSmem &S, const short4 *b1, const int *c1, short4
         }
     }
     __syncthreads();
-    for (int p = tid; p < np; p += kQtThreads) {
+    for (int p = tid; p < np; p += QT) {
         const int nd = nodeOf[p];
         const int r = S.procOrder[nd];
         nodeOf[p] = (uint16_t)(r >= 0 ? S.childIdx[4 * r + qtQuadrant(cand[p].x, b1[nd])] : S.oldToNew[nd]);
@@ -563,7 +564,7 @@ __device__ int qtCommit(const QtSmem &S, const short4 *b1, const int *c1, short4
     return totalChildren + untouched;
 }
 
-template <bool PDL> __global__ void __launch_bounds__(kQtThreads) k_quadtree(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+template <bool PDL, int QT> __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ FrameGeom G, const DevBuffers B) {
     if (PDL) pdlEnter(B);
     extern __shared__ __align__(16) unsigned char qtRaw[];
     const int level = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
@@ -594,19 +595,19 @@ template <bool PDL> __global__ void __launch_bounds__(kQtThreads) k_quadtree(con
     // ---- roots (:537-574): nIni roots of width hX over [0, maxX-minX) x [0, maxY-minY]; empty ones dropped
     const int nIni = L.nIni;
     const float hX = L.hX;
-    for (int i = tid; i < nIni; i += kQtThreads) S.childCnt[i] = 0;
+    for (int i = tid; i < nIni; i += QT) S.childCnt[i] = 0;
     __syncthreads();
-    for (int p = tid; p < np; p += kQtThreads) {
+    for (int p = tid; p < np; p += QT) {
         const int x = (int)(cand[p].x & 0xfff) - kMinBorder;
         const int root = (int)__fdiv_rn((float)x, hX);
         nodeOf[p] = (uint16_t)root;
         atomicAdd(&S.childCnt[root], 1);
     }
     __syncthreads();
-    for (int i = tid; i < nIni; i += kQtThreads) S.scanU[i] = S.childCnt[i] > 0;
+    for (int i = tid; i < nIni; i += QT) S.scanU[i] = S.childCnt[i] > 0;
     __syncthreads();
-    int n = qtScan(S.scanU, nIni, S.misc);
-    for (int i = tid; i < nIni; i += kQtThreads) {
+    int n = qtScan<QT>(S.scanU, nIni, S.misc);
+    for (int i = tid; i < nIni; i += QT) {
         const int cnt = S.childCnt[i];
         if (cnt > 0) {
             const int pos = S.scanU[i];
@@ -616,7 +617,7 @@ template <bool PDL> __global__ void __launch_bounds__(kQtThreads) k_quadtree(con
         }
     }
     __syncthreads();
-    for (int p = tid; p < np; p += kQtThreads) nodeOf[p] = (uint16_t)S.scanU[nodeOf[p]];
+    for (int p = tid; p < np; p += QT) nodeOf[p] = (uint16_t)S.scanU[nodeOf[p]];
     __syncthreads();
 
     // ---- main loop (:576-700)
@@ -624,10 +625,10 @@ template <bool PDL> __global__ void __launch_bounds__(kQtThreads) k_quadtree(con
     while (!finish) {
         const int prevSize = n;
         // phase-1 pass: every multi-point node, in list order
-        for (int i = tid; i < n; i += kQtThreads) S.scanR[i] = c1[i] > 1;
+        for (int i = tid; i < n; i += QT) S.scanR[i] = c1[i] > 1;
         __syncthreads();
-        int P = qtScan(S.scanR, n, S.misc);
-        for (int i = tid; i < n; i += kQtThreads) {
+        int P = qtScan<QT>(S.scanR, n, S.misc);
+        for (int i = tid; i < n; i += QT) {
             const bool e = c1[i] > 1;
             S.procOrder[i] = e ? S.scanR[i] : -1;
             if (e) S.byOrder[S.scanR[i]] = i;
@@ -635,8 +636,8 @@ template <bool PDL> __global__ void __launch_bounds__(kQtThreads) k_quadtree(con
         __syncthreads();
         int nToExpand = 0;
         if (P > 0) {
-            qtCountChildren(S, b1, P, cand, nodeOf, np);
-            n = qtCommit(S, b1, c1, b2, c2, g2, n, P, cand, nodeOf, np, &nToExpand);
+            qtCountChildren<QT>(S, b1, P, cand, nodeOf, np);
+            n = qtCommit<QT>(S, b1, c1, b2, c2, g2, n, P, cand, nodeOf, np, &nToExpand);
             { short4 *t = b1; b1 = b2; b2 = t; } { int *t = c1; c1 = c2; c2 = t; } { int *t = g1; g1 = g2; g2 = t; }
         }
         if (n >= N || n == prevSize) {
@@ -646,15 +647,15 @@ template <bool PDL> __global__ void __launch_bounds__(kQtThreads) k_quadtree(con
             while (!finish) {
                 const int prevSize2 = n;
                 // compact the generation: gen entry e -> list node, keyed by (size, seq)
-                for (int i = tid; i < n; i += kQtThreads) S.scanR[i] = g1[i] >= 0;
+                for (int i = tid; i < n; i += QT) S.scanR[i] = g1[i] >= 0;
                 __syncthreads();
-                const int F = qtScan(S.scanR, n, S.misc);
-                for (int i = tid; i < n; i += kQtThreads) if (g1[i] >= 0) S.oldToNew[S.scanR[i]] = i;
+                const int F = qtScan<QT>(S.scanR, n, S.misc);
+                for (int i = tid; i < n; i += QT) if (g1[i] >= 0) S.oldToNew[S.scanR[i]] = i;
                 __syncthreads();
                 // rank r = number of generation nodes that sort after this one (processed earlier)
-                for (int i = tid; i < n; i += kQtThreads) S.procOrder[i] = -1;
+                for (int i = tid; i < n; i += QT) S.procOrder[i] = -1;
                 __syncthreads();
-                for (int e = tid; e < F; e += kQtThreads) {
+                for (int e = tid; e < F; e += QT) {
                     const int i = S.oldToNew[e];
                     const int sz = c1[i], sq = g1[i];
                     int r = 0;
@@ -667,25 +668,25 @@ template <bool PDL> __global__ void __launch_bounds__(kQtThreads) k_quadtree(con
                     S.byOrder[r] = i;
                 }
                 __syncthreads();
-                qtCountChildren(S, b1, F, cand, nodeOf, np);
+                qtCountChildren<QT>(S, b1, F, cand, nodeOf, np);
                 // the split loop breaks once the list holds N nodes: rank r is processed iff the list
                 // size after ranks < r is still below N
-                for (int r = tid; r < F; r += kQtThreads) {
+                for (int r = tid; r < F; r += QT) {
                     const int *c = &S.childCnt[4 * r];
                     S.scanU[r] = (c[0] > 0) + (c[1] > 0) + (c[2] > 0) + (c[3] > 0) - 1;
                 }
                 __syncthreads();
-                qtScan(S.scanU, F, S.misc);   // exclusive: gain of ranks < r
+                qtScan<QT>(S.scanU, F, S.misc);   // exclusive: gain of ranks < r
                 if (tid == 0) S.misc[34] = 0;
                 __syncthreads();
                 int cntProc = 0;
-                for (int r = tid; r < F; r += kQtThreads) cntProc += (n + S.scanU[r] < N);
+                for (int r = tid; r < F; r += QT) cntProc += (n + S.scanU[r] < N);
                 if (cntProc) atomicAdd(&S.misc[34], cntProc);
                 __syncthreads();
                 P = S.misc[34];   // processed ranks are a prefix 0..P-1 (gains are >= 0)
-                for (int r = tid; r < F; r += kQtThreads) if (r >= P) S.procOrder[S.byOrder[r]] = -1;
+                for (int r = tid; r < F; r += QT) if (r >= P) S.procOrder[S.byOrder[r]] = -1;
                 __syncthreads();
-                n = qtCommit(S, b1, c1, b2, c2, g2, n, P, cand, nodeOf, np, &nToExpand);
+                n = qtCommit<QT>(S, b1, c1, b2, c2, g2, n, P, cand, nodeOf, np, &nToExpand);
                 { short4 *t = b1; b1 = b2; b2 = t; } { int *t = c1; c1 = c2; c2 = t; } { int *t = g1; g1 = g2; g2 = t; }
                 if (n >= N || n == prevSize2) finish = true;
             }
@@ -694,16 +695,16 @@ template <bool PDL> __global__ void __launch_bounds__(kQtThreads) k_quadtree(con
 
     // ---- best response per node, first in key order on ties (:703-720); output in list order
     unsigned long long *best = (unsigned long long *)S.childCnt;
-    for (int i = tid; i < n; i += kQtThreads) best[i] = 0ull;
+    for (int i = tid; i < n; i += QT) best[i] = 0ull;
     __syncthreads();
-    for (int p = tid; p < np; p += kQtThreads) {
+    for (int p = tid; p < np; p += QT) {
         const uint2 c = cand[p];
         const unsigned long long key = ((unsigned long long)(c.x >> 24) << 32) | (unsigned long long)(0xffffffffu - c.y);
         atomicMax(&best[nodeOf[p]], key);
     }
     __syncthreads();
     uint32_t *kept = B.kept + (long long)f * G.keptCap + L.keptOff;
-    for (int p = tid; p < np; p += kQtThreads) {
+    for (int p = tid; p < np; p += QT) {
         const uint2 c = cand[p];
         const unsigned long long key = ((unsigned long long)(c.x >> 24) << 32) | (unsigned long long)(0xffffffffu - c.y);
         const int nd = nodeOf[p];
@@ -721,8 +722,10 @@ size_t quadtreeSmemBytes(int listCap) {
 }
 
 int launchQuadtree(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s) {
-    if (B.pdl) launchChain(true, k_quadtree<true>, dim3(G.nlevels, nFrames), dim3(kQtThreads), quadtreeSmemBytes(G.maxListCap), s, G, B);
-    else k_quadtree<false><<<dim3(G.nlevels, nFrames), kQtThreads, quadtreeSmemBytes(G.maxListCap), s>>>(G, B);
+    const size_t smem = quadtreeSmemBytes(G.maxListCap);
+    if (B.pdl) launchChain(true, k_quadtree<true, kQtThreads>, dim3(G.nlevels, nFrames), dim3(kQtThreads), smem, s, G, B);
+    else if (nFrames <= 8) k_quadtree<false, kQtThreads><<<dim3(G.nlevels, nFrames), kQtThreads, smem, s>>>(G, B);
+    else k_quadtree<false, kQtThreadsBatch><<<dim3(G.nlevels, nFrames), kQtThreadsBatch, smem, s>>>(G, B);
     return 1;
 }
 
@@ -1107,8 +1110,9 @@ int configureKernels() {
     YGZ_CUDA(cudaGetDevice(&dev));
     if (dev >= 0 && dev < 64 && gConfigured[dev]) return 0;
     YGZ_CUDA(cudaMemcpyToSymbol(gPattern, kOrbPattern, sizeof(kOrbPattern)));
-    YGZ_CUDA(cudaFuncSetAttribute(k_quadtree<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    YGZ_CUDA(cudaFuncSetAttribute(k_quadtree<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    YGZ_CUDA(cudaFuncSetAttribute(k_quadtree<false, kQtThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    YGZ_CUDA(cudaFuncSetAttribute(k_quadtree<true, kQtThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    YGZ_CUDA(cudaFuncSetAttribute(k_quadtree<false, kQtThreadsBatch>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     if (dev >= 0 && dev < 64) gConfigured[dev] = true;
     return 0;
 }
