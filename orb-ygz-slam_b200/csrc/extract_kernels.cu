@@ -750,7 +750,7 @@ __device__ __forceinline__ void cpAsync16(void *smemDst, const void *gmemSrc) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smemDst)), "l"(gmemSrc));
 }
 
-template <bool PDL> __global__ void __launch_bounds__(kBlurThreads) k_blur(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+template <bool PDL> __global__ void __launch_bounds__(kBlurThreads, 5) k_blur(const __grid_constant__ FrameGeom G, const DevBuffers B) {
     if (PDL) pdlEnter(B);
     __shared__ __align__(16) uint8_t raw[kBlurRawRows * kBlurRawPitch];
     __shared__ __align__(16) uint2 hs[kBlurRawRows * (kBlurTW / 4)];   // 4 x u16 horizontal sums
