@@ -404,8 +404,10 @@ static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int 
     if ((rc = applyUndistort(ex, n, w, h, srcPitch))) return rc;
     YGZ_CUDA(cudaMemsetAsync(ex->dCounts, 0, (2 * (size_t)ex->maxBatch * kMaxLevels + 1) * sizeof(int), ex->stream));
     YGZ_MARK(1);
-    ex->B.pdl = (n <= kPdlMaxFrames && !ex->profiling) ? 1 : 0;   // live tracking: the chain is launch-latency bound
+    const int pdl = (n <= kPdlMaxFrames && !ex->profiling) ? 1 : 0;   // live tracking: the chain is launch-latency bound
+    ex->B.pdl = ex->profiling ? 0 : 1;   // the 7 dependent pyramid launches are short at any batch size
     runPyramid(ex, n);
+    ex->B.pdl = pdl;
     YGZ_MARK(2);
     ex->launches += launchFast(ex->G, ex->B, n, ex->stream);
     YGZ_MARK(3);
