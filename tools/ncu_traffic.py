@@ -5,6 +5,7 @@ than once per step (the capture window wrapped around), its launches are average
 import collections
 import csv
 import json
+import re
 import subprocess
 import sys
 
@@ -20,7 +21,7 @@ agg = collections.OrderedDict()
 for r in rows[2:]:
     if len(r) < len(H):
         continue
-    k = r[ik].split("(")[0]
+    k = re.sub(r"^void |ygz::|<.*$", "", r[ik].split("(")[0])   # template instantiations of one kernel count together
     a = agg.setdefault(k, [0, 0.0, 0.0, 0.0])
     a[0] += 1
     a[1] += float(r[ir]) * scale[U[ir]]
