@@ -41,7 +41,32 @@ def test_no_cpu_fallback_without_gpu():
     assert "CUDA" in str(e.value)
     with pytest.raises(Y.YgzError):
         Y.Matcher()
+    import numpy as np
+    with pytest.raises(Y.YgzError):          # the pyramid object of the direct-tracking entry points lives on the device too
+        Y.Pyramid([np.zeros((48, 64), np.uint8)])
     assert Y.lib().ygzorb_version().startswith(b"ygzorb-b200")
+
+
+def test_direct_tracking_entry_points_reject_null_handles():
+    """Row f4 entry points: argument errors come back as codes with a message, never as a crash or a silent success."""
+    L = Y.lib()
+    i64, f7 = ctypes.c_int64(), (ctypes.c_float * 7)()
+    L.ygzorb_sparse_align_run.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    assert L.ygzorb_sparse_align_run(None, 7, 1, f7, ctypes.byref(i64), None) < 0
+    L.ygzorb_sparse_align_create.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    assert L.ygzorb_sparse_align_create(None, None) < 0
+    L.ygzorb_pyramid_info.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    assert L.ygzorb_pyramid_info(None, None, None, None) < 0
+    L.ygzorb_distinctive_descriptors.argtypes = [ctypes.c_void_p] * 3 + [ctypes.c_int, ctypes.c_uint] + [ctypes.c_void_p] * 3
+    assert L.ygzorb_distinctive_descriptors(None, None, None, 1, 0, None, None, None) < 0
+    assert b"null" in L.ygzorb_last_error()
+
+
+def test_direct_tracking_demo_builds():
+    subprocess.run(["make", "-C", os.path.join(PKG, "host")], check=True, stdout=subprocess.DEVNULL)
+    demo = os.path.join(PKG, "host", "host_demo3")
+    res = subprocess.run([demo], capture_output=True, text=True)
+    assert res.returncode == 2 and "usage" in res.stderr
 
 
 def test_product_does_not_reference_the_oracle():
