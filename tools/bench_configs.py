@@ -1,5 +1,6 @@
 """Secondary benchmarks for the other BASELINE.json configs (bench.py covers configs[1]):
   --config 0 : one 640x480 frame, 1000 features — single-frame latency through the C ABI (host in/out)
+  --config 1 : 752x480 stream with the reference's own EuRoC.yaml extractor parameters (scale 2.0, 4 levels), device-resident batch
   --config 2 : KITTI-shape 1241x376 stereo pair, 2000 features/image + ComputeStereoMatches (host in/out)
   --config 3 : batched extraction of N_FRAMES 1280x720 frames, 2000 features, frame-sharded over the ranks
   --config 4 : brute-force kNN-2 + ratio, NQ x NT 256-bit rows, query-sharded over the ranks
@@ -162,6 +163,35 @@ def batched(args, rank, local, world, dev):
             "staged_GBps": staged * n_total / (ms * 1e-3) / 1e9, "scaling": "strong"}
 
 
+def euroc_yaml(args, rank, local, world, dev):
+    """Secondary line of configs[1]: the extractor parameters of the reference's own
+    Examples/Monocular/EuRoC.yaml:35-38 (scaleFactor 2.0, 4 levels; level 3 has no FAST cell row and yields nothing), 752x480,
+    1000 features, a device-resident batch of 512 frames."""
+    w, h, nf, n = 752, 480, 1000, 512
+    base = synth.frame_batch(w, h, n, seed0=300 + rank, distinct=8)
+    d_in = torch.from_numpy(base).to(dev)
+    ex = Y.Extractor(nf, 2.0, 4, 20, 7, max_batch=n, device=local)
+    cap = ex.max_keypoints(w, h)
+    counts = torch.zeros(n, dtype=torch.int32, device=dev)
+    kps = torch.zeros((n, cap, 7), device=dev); desc = torch.zeros((n, cap, 32), dtype=torch.uint8, device=dev)
+    stream = torch.cuda.ExternalStream(ex.stream(), device=dev)
+    flags = Y.IN_DEVICE | Y.OUT_DEVICE | Y.NO_SYNC
+    _KEEP.extend([ex, stream])
+    def run():
+        ex.extract_raw(d_in.data_ptr(), n, w, h, w, w * h, flags, cap, counts.data_ptr(), kps.data_ptr(), desc.data_ptr())
+    for _ in range(3):
+        run()
+    ex.sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(10):
+        run()
+    e1.record(stream); ex.sync()
+    ms = e0.elapsed_time(e1) / 10
+    return {"config": "752x480, 1000 features, scaleFactor 2.0 / 4 levels (Examples/Monocular/EuRoC.yaml), 512 device-resident frames per step",
+            "ms_per_step": ms, "frames_per_s": n / (ms * 1e-3), "keypoints_per_frame": float(counts.float().mean().item())}
+
+
 def knn(args, rank, local, world, dev):
     nq, nt = args.nq, args.nt
     b, e = sharding.shard_range(nq, rank, world)
@@ -218,7 +248,7 @@ def main():
     ap.add_argument("--ratio", type=float, default=0.6)
     args = ap.parse_args()
     rank, local, world, dev = setup()
-    fn = {0: single_frame, 2: stereo, 3: batched, 4: knn}[args.config]
+    fn = {0: single_frame, 1: euroc_yaml, 2: stereo, 3: batched, 4: knn}[args.config]
     res = fn(args, rank, local, world, dev)
     res["n_gpus"] = world
     if rank == 0:
