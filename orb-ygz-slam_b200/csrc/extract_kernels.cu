@@ -207,7 +207,8 @@ int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nF
 // Survivors are appended (unordered) to the level's candidate array with an order key
 // (cell, y-in-cell, x-in-cell) that encodes the reference's vToDistributeKeys order, which is all
 // the quadtree needs from the order (its only order dependence is "first wins" on response ties).
-constexpr int kFastThreads = 128;
+constexpr int kFastThreads = kFastCtaThreads;
+constexpr int kFastWarps = kFastThreads / 32;
 constexpr int kTilePitch = kFastTilePitch;   // image / score tile pitch
 
 // The 16 ring differences are kept as packed 16-bit pairs E = (d + 256) | (256 - d) << 16 with
@@ -281,7 +282,7 @@ __device__ __forceinline__ int fastMeasure(unsigned p) {
 // stored score m-1 exceeds the stored scores of its 8 neighbours, and a neighbour's stored score is
 // n-1 if n > t and 0 otherwise; since m > t >= 1 this is exactly "every neighbour has n < m".  The
 // score tile holds m for m > t (t = the threshold in force) and 0 elsewhere (and outside the detection area).
-template <bool PDL> __global__ void __launch_bounds__(kFastThreads, 16) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+template <bool PDL> __global__ void __launch_bounds__(kFastThreads, 28) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
     if (PDL) pdlEnter(B);
     // dynamic shared memory, sized by the geometry's largest cell (FrameGeom::fastRegionA/fastScoreBytes/fastWarpCap):
     // [image tile][score tile][per-warp corner lists]
@@ -308,12 +309,12 @@ template <bool PDL> __global__ void __launch_bounds__(kFastThreads, 16) k_fast(c
         // and the unrolled loop keeps every load of the thread in flight at once
         const int nw = (ox + tw + 3) >> 2;           // words per row (<= 19)
         const bool two = nw <= 16;
-        const int wq = two ? (lane & 15) : lane, r0 = two ? 2 * wid + (lane >> 4) : wid, rstep = two ? 8 : 4;
+        const int wq = two ? (lane & 15) : lane, r0 = two ? 2 * wid + (lane >> 4) : wid, rstep = two ? 2 * kFastWarps : kFastWarps;
         if (wq < nw) {
             const uint8_t *src = img + (long long)r0 * L.pitch + xa + 4 * wq;
             const long long sstep = (long long)rstep * L.pitch;
             uint8_t *dst = tile + r0 * kTilePitch + 4 * wq;
-#pragma unroll 5
+#pragma unroll 10
             for (int y = r0; y < th; y += rstep, src += sstep, dst += rstep * kTilePitch)
                 *reinterpret_cast<uint32_t *>(dst) = __ldg(reinterpret_cast<const uint32_t *>(src));
         }

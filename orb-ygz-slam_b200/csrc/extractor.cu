@@ -219,7 +219,7 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
     }
     G.totalCells = cells; G.totalTiles = tiles;
     // k_fast shared memory: [image tile] [score tile] [per-warp lists]; a list holds every pixel its warp visits
-    G.fastWarpCap = (maxNpx + 127) / 128 * 32;
+    G.fastWarpCap = (maxNpx + kFastCtaThreads - 1) / kFastCtaThreads * 32;
     G.fastRegionA = alignUp((maxDh + 6) * kFastTilePitch, 16);
     G.fastScoreBytes = alignUp((maxDh + 2) * kFastTilePitch, 16);
     G.cellTab = (int)tabs.size(); tabs.insert(tabs.end(), cellTab.begin(), cellTab.end());

@@ -14,6 +14,7 @@ constexpr int kMaxLevels = 16;
 constexpr int kEdge = 19;        // EDGE_THRESHOLD, src/ORBextractor.cc:72
 constexpr int kMinBorder = 16;   // EDGE_THRESHOLD - 3, :733
 constexpr int kHalfPatch = 15;   // HALF_PATCH_SIZE, :71
+constexpr int kFastCtaThreads = 64;  // k_fast CTA size (extract_kernels.cu: kFastThreads); sizes the per-warp lists
 constexpr int kFastTilePitch = 76;   // k_fast image / score tile pitch: cell + 6 + up to 3 alignment bytes, multiple of 4
 constexpr int kBlurTW = 256, kBlurTH = 32;  // blur tile (k_blur)
 
