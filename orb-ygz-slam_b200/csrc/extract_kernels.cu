@@ -29,7 +29,7 @@ static void launchChain(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 bloc
 // the host (extractor.cu, makeResizeTables) with the double/float recipe of resize.cpp, so the
 // kernel is integer-only.  One thread produces 4 horizontally adjacent pixels (one 32-bit store).
 // Table entry X[dx] = {x0 | x1<<16, a0 | a1<<16}; Y[dy] = {y0 | y1<<16, b0 | b1<<16}.
-constexpr int kResizeRows = 4;   // destination rows per thread
+constexpr int kResizeRows = 8;   // destination rows per thread
 
 template <bool PDL> __global__ void __launch_bounds__(256) k_resize_generic(const __grid_constant__ FrameGeom G, const DevBuffers B, int level) {
     if (PDL) pdlEnter(B);
