@@ -209,7 +209,7 @@ int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nF
 // the quadtree needs from the order (its only order dependence is "first wins" on response ties).
 constexpr int kFastThreads = kFastCtaThreads;
 constexpr int kFastWarps = kFastThreads / 32;
-constexpr int kTilePitch = kFastTilePitch;   // image / score tile pitch
+// image / score tile pitch = template parameter TP (kFastTilePitchNarrow or kFastTilePitch)
 
 // The 16 ring differences are kept as packed 16-bit pairs E = (d + 256) | (256 - d) << 16 with
 // d = v - p, both halves positive, so ONE VIMNMX3.U16x2 handles the "darker" arcs (low half) and
@@ -241,8 +241,8 @@ __device__ __forceinline__ unsigned fastE(int p, unsigned base) { return (unsign
 
 // Compass pretest: an arc of 9 always holds two adjacent compass pixels (ring 0, 4, 8, 12), so m > t needs two
 // adjacent compass pixels both darker or both brighter than the centre by more than t.  `pre2` = t + 256 in both halves.
-__device__ __forceinline__ bool fastPretest(unsigned p, unsigned pre2) {
-    constexpr int P = kTilePitch;
+template <int TP> __device__ __forceinline__ bool fastPretest(unsigned p, unsigned pre2) {
+    constexpr int P = TP;
     const unsigned base = fastBase((int)ldsU8<0>(p));
     const unsigned e0 = fastE(ldsU8<3 * P>(p), base), e4 = fastE(ldsU8<3>(p), base);
     const unsigned e8 = fastE(ldsU8<-3 * P>(p), base), e12 = fastE(ldsU8<-3>(p), base);
@@ -256,8 +256,8 @@ __device__ __forceinline__ bool fastPretest(unsigned p, unsigned pre2) {
 // Arc network (36 packed min/max instead of 16 arcs x 8): arcs k and k+1 share the 8 ring pixels k+1..k+8, so
 //   max(arc_k, arc_k+1) = min(e_k+1 .. e_k+8, max(e_k, e_k+9))        (lattice identity)
 // and the 8-pixel cores are built from pair minima lo2_j (j odd) and their pair minima lo4_j.
-__device__ __forceinline__ int fastMeasure(unsigned p) {
-    constexpr int P = kTilePitch;
+template <int TP> __device__ __forceinline__ int fastMeasure(unsigned p) {
+    constexpr int P = TP;
     const unsigned base = fastBase((int)ldsU8<0>(p));
     unsigned e[16];
     e[0] = fastE(ldsU8<3 * P>(p), base); e[4] = fastE(ldsU8<3>(p), base);
@@ -282,7 +282,7 @@ __device__ __forceinline__ int fastMeasure(unsigned p) {
 // stored score m-1 exceeds the stored scores of its 8 neighbours, and a neighbour's stored score is
 // n-1 if n > t and 0 otherwise; since m > t >= 1 this is exactly "every neighbour has n < m".  The
 // score tile holds m for m > t (t = the threshold in force) and 0 elsewhere (and outside the detection area).
-template <bool PDL> __global__ void __launch_bounds__(kFastThreads, 28) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+template <bool PDL, int TP> __global__ void __launch_bounds__(kFastThreads, 32) k_fast(const __grid_constant__ FrameGeom G, const DevBuffers B) {
     if (PDL) pdlEnter(B);
     // dynamic shared memory, sized by the geometry's largest cell (FrameGeom::fastRegionA/fastScoreBytes/fastWarpCap):
     // [image tile][score tile][per-warp corner lists]
@@ -313,19 +313,19 @@ template <bool PDL> __global__ void __launch_bounds__(kFastThreads, 28) k_fast(c
         if (wq < nw) {
             const uint8_t *src = img + (long long)r0 * L.pitch + xa + 4 * wq;
             const long long sstep = (long long)rstep * L.pitch;
-            uint8_t *dst = tile + r0 * kTilePitch + 4 * wq;
+            uint8_t *dst = tile + r0 * TP + 4 * wq;
 #pragma unroll 10
-            for (int y = r0; y < th; y += rstep, src += sstep, dst += rstep * kTilePitch)
+            for (int y = r0; y < th; y += rstep, src += sstep, dst += rstep * TP)
                 *reinterpret_cast<uint32_t *>(dst) = __ldg(reinterpret_cast<const uint32_t *>(src));
         }
     } else {
         for (int y = wid; y < th; y += kFastThreads / 32) {
             const uint8_t *row = img + (long long)y * L.pitch + xa;
-            for (int x = lane; x < tw; x += 32) tile[y * kTilePitch + x] = row[x];
+            for (int x = lane; x < tw; x += 32) tile[y * TP + x] = row[x];
         }
     }
     // score tile: all zero; phase 1 writes m only where m exceeds the threshold in force
-    for (int i = tid; i < ((dh + 2) * kTilePitch + 15) / 16; i += kFastThreads) reinterpret_cast<uint4 *>(score)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < ((dh + 2) * TP + 15) / 16; i += kFastThreads) reinterpret_cast<uint4 *>(score)[i] = make_uint4(0, 0, 0, 0);
     __syncthreads();
     const int minTh = G.minTh, iniTh = G.iniTh;
     // ---- phase 1 runs at iniThFAST first and, only if no corner of the cell survives NMS, again at minThFAST
@@ -342,9 +342,9 @@ template <bool PDL> __global__ void __launch_bounds__(kFastThreads, 28) k_fast(c
     // 2^24 / dw rounded up by 1..11 (the float reciprocal is good to 2^-22): the quotient is exact while
     // i * (magic * dw - 2^24) < 2^24, i.e. up to an excess of 64 for dw <= 64
     const unsigned magic = (unsigned)(16777216.0f * __fdividef(1.0f, (float)dw)) + 6u;
-    const int wrapOff = kTilePitch - dw;
-    const unsigned centre = smemAddr(tile + 3 * kTilePitch + 3 + ox);
-    const unsigned sc0a = smemAddr(score + kTilePitch + 1);
+    const int wrapOff = TP - dw;
+    const unsigned centre = smemAddr(tile + 3 * TP + 3 + ox);
+    const unsigned sc0a = smemAddr(score + TP + 1);
     const unsigned cornersAt = smemAddr(corners + wid * kFastWarpCap);
     uint2 *cand = B.cand + (long long)f * G.candPerFrame + L.candOff;
     int *counter = B.candCount + f * kMaxLevels + level;
@@ -356,7 +356,7 @@ template <bool PDL> __global__ void __launch_bounds__(kFastThreads, 28) k_fast(c
         for (int i = tid; i - lane < npx; i += kFastThreads) {
             const int ic = min(i, npx - 1);   // clamped, not branched: the tail lanes redo the last pixel and drop the result
             const int off = (int)__umulhi((unsigned)ic << 8, magic) * wrapOff + ic;
-            const bool pass = fastPretest(centre + off, pre2) && i < npx;
+            const bool pass = fastPretest<TP>(centre + off, pre2) && i < npx;
             const unsigned mask = __ballot_sync(0xffffffffu, pass);
             if (pass) stsU16(cornersAt + 2 * (n0 + __popc(mask & ltMask)), (unsigned)off);
             n0 += __popc(mask);
@@ -369,7 +369,7 @@ template <bool PDL> __global__ void __launch_bounds__(kFastThreads, 28) k_fast(c
             int m = -1;
             if (k < n0) {
                 off = ldsU16(cornersAt + 2 * k);
-                m = fastMeasure(centre + off);
+                m = fastMeasure<TP>(centre + off);
             }
             const bool corner = m > t;
             if (corner) stsU8(sc0a + off, (unsigned)m);
@@ -388,7 +388,7 @@ template <bool PDL> __global__ void __launch_bounds__(kFastThreads, 28) k_fast(c
             bool ismax = false;
             unsigned o = 0, m = 0;
             if (k < n1) {
-                constexpr int P = kTilePitch;
+                constexpr int P = TP;
                 o = ldsU16(cornersAt + 2 * k);
                 const unsigned sc = sc0a + o;
                 m = ldsU8<0>(sc);
@@ -405,7 +405,7 @@ template <bool PDL> __global__ void __launch_bounds__(kFastThreads, 28) k_fast(c
             if (ismax) {
                 const int slot = base + __popc(mask & ltMask);
                 if (slot < candCap) {
-                    const unsigned y = (o * ((1u << 20) / kTilePitch + 1)) >> 20, x = o - y * kTilePitch;   // exact for o < 2^13
+                    const unsigned y = (o * ((1u << 20) / TP + 1)) >> 20, x = o - y * TP;   // exact for o < 2^13
                     const uint32_t ax = iniX + 3 + x, ay = iniY + 3 + y;  // absolute level coordinates
                     cand[slot] = make_uint2(ax | (ay << 12) | ((uint32_t)(m - 1) << 24), ((uint32_t)cell << 12) | (y << 6) | x);
                 } else {
@@ -422,8 +422,14 @@ int launchFast(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_
     if (G.totalCells == 0) return 0;
     size_t smem = (size_t)G.fastRegionA + G.fastScoreBytes + (size_t)(kFastThreads / 32) * G.fastWarpCap * sizeof(uint16_t);
     if (const char *pad = getenv("YGZ_FAST_SMEM_PAD")) smem += (size_t)atoi(pad);   // occupancy experiments
-    if (B.pdl) launchChain(true, k_fast<true>, dim3(G.totalCells, nFrames), dim3(kFastThreads), smem, s, G, B);
-    else k_fast<false><<<dim3(G.totalCells, nFrames), kFastThreads, smem, s>>>(G, B);
+    const dim3 grid(G.totalCells, nFrames);
+    if (G.fastPitch == kFastTilePitchNarrow) {
+        if (B.pdl) launchChain(true, k_fast<true, kFastTilePitchNarrow>, grid, dim3(kFastThreads), smem, s, G, B);
+        else k_fast<false, kFastTilePitchNarrow><<<grid, kFastThreads, smem, s>>>(G, B);
+    } else {
+        if (B.pdl) launchChain(true, k_fast<true, kFastTilePitch>, grid, dim3(kFastThreads), smem, s, G, B);
+        else k_fast<false, kFastTilePitch><<<grid, kFastThreads, smem, s>>>(G, B);
+    }
     return 1;
 }
 

@@ -124,7 +124,7 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
     long long off = 0, candOff = 0, bOff = 0;
     int cells = 0, tiles = 0, keptOff = 0;
     std::vector<int2> cellTab, tileTab;
-    int maxDh = 1, maxNpx = 1;
+    int maxDh = 1, maxDw = 1, maxNpx = 1;
     for (int l = 0; l < P.nlevels; l++) {
         LevelGeom &L = G.lv[l];
         L.w = cvRoundF((float)w * T.invScale[l]);   // :1131-1133, from LEVEL-0 dims
@@ -190,7 +190,7 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
                     ce.x = iniX | (iniY << 12) | (l << 24);
                     ce.y = dw | (dh << 7) | ((i * nCols + j) << 14);
                     cellTab.push_back(ce);
-                    maxDh = std::max(maxDh, dh); maxNpx = std::max(maxNpx, dw * dh);
+                    maxDh = std::max(maxDh, dh); maxDw = std::max(maxDw, dw); maxNpx = std::max(maxNpx, dw * dh);
                     cells++;
                 }
             }
@@ -220,8 +220,11 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
     G.totalCells = cells; G.totalTiles = tiles;
     // k_fast shared memory: [image tile] [score tile] [per-warp lists]; a list holds every pixel its warp visits
     G.fastWarpCap = (maxNpx + kFastCtaThreads - 1) / kFastCtaThreads * 32;
-    G.fastRegionA = alignUp((maxDh + 6) * kFastTilePitch, 16);
-    G.fastScoreBytes = alignUp((maxDh + 2) * kFastTilePitch, 16);
+    // tile pitch: the narrow instantiation when every cell (dw + 6 window + up to 3 alignment bytes) fits 48 bytes — the usual
+    // 30..39-px cells — which brings the CTA's shared memory under the 32-CTAs-per-SM line; else the general 76
+    G.fastPitch = (maxDw + 9 <= kFastTilePitchNarrow) ? kFastTilePitchNarrow : kFastTilePitch;
+    G.fastRegionA = alignUp((maxDh + 6) * G.fastPitch, 16);
+    G.fastScoreBytes = alignUp((maxDh + 2) * G.fastPitch, 16);
     G.cellTab = (int)tabs.size(); tabs.insert(tabs.end(), cellTab.begin(), cellTab.end());
     G.tileTab = (int)tabs.size(); tabs.insert(tabs.end(), tileTab.begin(), tileTab.end());
     G.slabBytes = std::max(off, 256LL);

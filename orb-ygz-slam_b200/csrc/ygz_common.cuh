@@ -15,6 +15,7 @@ constexpr int kEdge = 19;        // EDGE_THRESHOLD, src/ORBextractor.cc:72
 constexpr int kMinBorder = 16;   // EDGE_THRESHOLD - 3, :733
 constexpr int kHalfPatch = 15;   // HALF_PATCH_SIZE, :71
 constexpr int kFastCtaThreads = 64;  // k_fast CTA size (extract_kernels.cu: kFastThreads); sizes the per-warp lists
+constexpr int kFastTilePitchNarrow = 48;   // k_fast tile pitch for cells up to 39 px wide
 constexpr int kFastTilePitch = 76;   // k_fast image / score tile pitch: cell + 6 + up to 3 alignment bytes, multiple of 4
 constexpr int kBlurTW = 256, kBlurTH = 32;  // blur tile (k_blur)
 
@@ -46,6 +47,7 @@ struct FrameGeom {
     int iniTh, minTh;
     int totalCells, totalTiles;   // totalCells: entries of the FAST cell table (cells with a non-empty detection area)
     int tileTab;                  // offset of the blur tile table in DevBuffers::tabs (x = x0 | y0<<12 | level<<24)
+    int fastPitch;                // k_fast tile pitch of this geometry (kFastTilePitchNarrow or kFastTilePitch)
     int fastRegionA, fastScoreBytes, fastWarpCap;   // k_fast dynamic shared memory layout (bytes, bytes, list entries per warp)
     int cellTab;                  // offset of the cell table in DevBuffers::tabs (8-byte entries)
     int maxListCap;
