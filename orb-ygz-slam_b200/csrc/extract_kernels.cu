@@ -993,7 +993,7 @@ __device__ __forceinline__ int orbByteWarp(const uint8_t *cb, int bp, float angl
     return val;
 }
 
-constexpr int kDescWarps = 8;
+constexpr int kDescWarps = 4;
 
 template <bool PDL> __global__ void __launch_bounds__(kDescWarps * 32) k_describe(const __grid_constant__ FrameGeom G, const DevBuffers B, int cap,
                                                               int32_t *counts, ygzorb_keypoint *kps, uint8_t *desc) {
