@@ -29,6 +29,7 @@ static void launchChain(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 bloc
 // the host (extractor.cu, makeResizeTables) with the double/float recipe of resize.cpp, so the
 // kernel is integer-only.  One thread produces 4 horizontally adjacent pixels (one 32-bit store).
 // Table entry X[dx] = {x0 | x1<<16, a0 | a1<<16}; Y[dy] = {y0 | y1<<16, b0 | b1<<16}.
+constexpr int kResizeBlockY = 4;   // block = 32 x kResizeBlockY threads
 constexpr int kResizeRows = 8;   // destination rows per thread
 
 template <bool PDL> __global__ void __launch_bounds__(256) k_resize_generic(const __grid_constant__ FrameGeom G, const DevBuffers B, int level) {
@@ -37,7 +38,7 @@ template <bool PDL> __global__ void __launch_bounds__(256) k_resize_generic(cons
     const LevelGeom &S = G.lv[level - 1];
     const int f = blockIdx.z;
     const int dx0 = (blockIdx.x * 32 + threadIdx.x) * 4;
-    const int dyBase = (blockIdx.y * 8 + threadIdx.y) * kResizeRows;
+    const int dyBase = (blockIdx.y * kResizeBlockY + threadIdx.y) * kResizeRows;
     if (dx0 >= D.pitch || dyBase >= D.h) return;
     const uint8_t *src = levelPtr(G, B, f, level - 1);
     uint8_t *dst = B.pyr + (long long)f * G.slabBytes + D.off + dx0;
@@ -120,7 +121,7 @@ template <bool PDL> __global__ void __launch_bounds__(256) k_resize(const __grid
     const LevelGeom &S = G.lv[level - 1];
     const int f = blockIdx.z;
     const int dx0 = (blockIdx.x * 32 + threadIdx.x) * 4;
-    const int dyBase = (blockIdx.y * 8 + threadIdx.y) * kResizeRows;
+    const int dyBase = (blockIdx.y * kResizeBlockY + threadIdx.y) * kResizeRows;
     if (dx0 >= D.pitch || dyBase >= D.h) return;
     const uint8_t *src = levelPtr(G, B, f, level - 1);
     uint8_t *dst = B.pyr + (long long)f * G.slabBytes + D.off + dx0;
@@ -185,7 +186,7 @@ template <bool PDL> __global__ void __launch_bounds__(256) k_resize(const __grid
 int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nFrames, cudaStream_t s) {
     const LevelGeom &D = G.lv[level];
     const LevelGeom &S = G.lv[level - 1];
-    dim3 block(32, 8), grid((D.pitch / 4 + 31) / 32, (D.h + 8 * kResizeRows - 1) / (8 * kResizeRows), nFrames);
+    dim3 block(32, kResizeBlockY), grid((D.pitch / 4 + 31) / 32, (D.h + kResizeBlockY * kResizeRows - 1) / (kResizeBlockY * kResizeRows), nFrames);
     // level 0 is caller memory: the word path needs 4-byte aligned rows there (levels >= 1 always are)
     const bool rowsAligned = (S.pitch & 3) == 0 &&
                              (level > 1 || ((reinterpret_cast<uintptr_t>(B.in) & 3) == 0 && (B.inFrameStride & 3) == 0));
