@@ -213,7 +213,7 @@ size_t knnPartialBytes(int nq, int splits) { return (size_t)nq * splits * sizeof
 // indices < j, so after t rounds the first t MapPoints are final and the fixed point IS the serial
 // result.  Candidates are visited in the reference's order (cell column, cell row, insertion order)
 // by one thread per MapPoint, which keeps the first-wins / strict-< top-2 rule literal.
-constexpr int kProjThreads = 512;
+constexpr int kProjThreads = 1024;
 
 __device__ int projScan(int *a, int n, int *ws) {   // in-place exclusive scan by the CTA, returns the total
     const int T = kProjThreads, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
