@@ -435,7 +435,7 @@ def build_line(args, world, B, cap, ms, ms_e2e, launches, clocks, stage_ms, n_kp
         pass
     roofline = {"bound": "hbm", "kernel": "k_" + dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-                "note": "the kernel is ALU-pipe / issue bound (ncu: 87 % issue-slot utilisation, DRAM 3 %), see DESIGN.md 5",
+                "note": "the kernel is ALU-pipe / issue bound (ncu: 85 % issue-slot utilisation, DRAM 4 %), see DESIGN.md 5",
                 "launches_in_stage": launches_per_stage, "algorithmic_bytes_per_launch": dom_bytes / launches_per_stage,
                 "pipeline_staged_GBps": staged, "pipeline_frac": staged / hbm_peak}
     mp_bytes = sum(int(h_mp[k].numel() * h_mp[k].element_size()) for k in mp_keys)
