@@ -451,7 +451,7 @@ int launchFast(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_
 // So points never move: each point carries the index of its node, and a pass is two sweeps over the
 // points (count children, relabel) plus block-wide scans over the node list.
 constexpr int kQtThreads = 512;        // CTA size for small batches (one frame: latency); batches run kQtThreadsBatch
-constexpr int kQtThreadsBatch = 256;   // more CTAs per SM hide the barrier stalls of the passes (0.47 -> 0.43 ms / 512 frames)
+constexpr int kQtThreadsBatch = 384;   // more CTAs per SM hide the barrier stalls of the passes (0.47 -> 0.42 ms / 512 frames at 384 threads; 256: 0.43, 192: 0.47, 448: 0.59)
 
 struct QtSmem {
     short4 *bA, *bB;      // node bounds x0,x1,y0,y1 (x = UL.x, y = UR.x, z = UL.y, w = BL.y)
