@@ -238,6 +238,9 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
 
 
 // -------------------------------------------------------------------------------------------------
+constexpr int kInSlots = 3;   // host-input staging slots
+static_assert(kInSlots == 3, "ygzorb_extractor_destroy lists dIn[0..2]");
+
 struct Extractor {
     ygzorb_params params;
     Tables tables;
@@ -249,10 +252,11 @@ struct Extractor {
     DevBuffers B;
     long long blurOff[kMaxLevels]; int blurPitch[kMaxLevels]; long long blurSlab = 0;
     // device workspace (grown on demand)
-    // host-input staging: two slots filled by the upload stream while the compute stream works on the other
-    uint8_t *dIn[2] = {}; size_t inBytes[2] = {};
+    // host-input staging: kInSlots slots filled by the upload stream while the compute stream works on an earlier one (three, so
+    // that the upload of chunk k+2 need not wait for the kernels of chunk k: the PCIe link stays busy)
+    uint8_t *dIn[kInSlots] = {}; size_t inBytes[kInSlots] = {};
     cudaStream_t h2d = nullptr, d2h = nullptr;
-    cudaEvent_t inReady[2] = {}, inFree[2] = {}, outReady[2] = {}, outFree[2] = {};
+    cudaEvent_t inReady[kInSlots] = {}, inFree[kInSlots] = {}, outReady[2] = {}, outFree[2] = {};
     unsigned inSeq = 0, outSeq = 0;
     int pipeFrames = 256;      // frames per pipelined chunk of a host-input call (0: one chunk per max_batch)
     uint8_t *dPyr = nullptr; size_t pyrBytes = 0;
@@ -313,7 +317,7 @@ static int ensureGeometry(Extractor *ex, int w, int h, int stride, int nFrames, 
     (void)nFrames;
     int rc;
     if (!inDevice)
-        for (int sl = 0; sl < 2; sl++)
+        for (int sl = 0; sl < kInSlots; sl++)
             if ((rc = growBuf(ex->dIn[sl], ex->inBytes[sl], nb * (size_t)w * h + 64))) return rc;
     if ((rc = growBuf(ex->dPyr, ex->pyrBytes, nb * (size_t)ex->G.slabBytes))) return rc;
     if ((rc = growBuf(ex->dBlur, ex->blurBytes, nb * (size_t)ex->blurSlab))) return rc;
@@ -349,7 +353,7 @@ static int ensureOut(Extractor *ex, int cap) {
 // Host input: enqueue the upload of a chunk of frames into the next staging slot on the upload stream
 // (which first waits until the kernels that last read that slot are done).  Returns the slot.
 static int uploadInput(Extractor *ex, const uint8_t *frames, int n, int w, int h, int stride, size_t frameStride, int *slotOut) {
-    const int sl = (int)(ex->inSeq++ & 1u);
+    const int sl = (int)(ex->inSeq++ % (unsigned)kInSlots);
     uint8_t *dst = ex->dIn[sl];
     YGZ_CUDA(cudaStreamWaitEvent(ex->h2d, ex->inFree[sl], 0));
     // staging buffer is continuous: pitch == w (the geometry was built with stride == w for host input)
@@ -514,7 +518,11 @@ int ygzorb_extractor_create(const ygzorb_params *params, int max_w, int max_h, i
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ex->d2h, cudaStreamNonBlocking);
     for (int sl = 0; sl < 2 && e == cudaSuccess; sl++) {
         e = cudaMalloc((void **)&ex->dOutCounts[sl], (size_t)max_batch * sizeof(int32_t));
-        cudaEvent_t *evs[] = {&ex->inReady[sl], &ex->inFree[sl], &ex->outReady[sl], &ex->outFree[sl]};
+        cudaEvent_t *evs[] = {&ex->outReady[sl], &ex->outFree[sl]};
+        for (cudaEvent_t *pe : evs) if (e == cudaSuccess) e = cudaEventCreateWithFlags(pe, cudaEventDisableTiming);
+    }
+    for (int sl = 0; sl < kInSlots && e == cudaSuccess; sl++) {
+        cudaEvent_t *evs[] = {&ex->inReady[sl], &ex->inFree[sl]};
         for (cudaEvent_t *pe : evs) if (e == cudaSuccess) e = cudaEventCreateWithFlags(pe, cudaEventDisableTiming);
     }
     for (int i = 0; i < 8 && e == cudaSuccess; i++) e = cudaEventCreate(&ex->ev[i]);
@@ -529,14 +537,18 @@ void ygzorb_extractor_destroy(ygzorb_extractor *h) {
     cudaSetDevice(ex->device);
     cudaStream_t streams[] = {ex->h2d, ex->stream, ex->d2h};
     for (cudaStream_t st : streams) if (st) cudaStreamSynchronize(st);
-    void *bufs[] = {ex->dIn[0], ex->dIn[1], ex->dPyr, ex->dBlur, ex->dTabs, ex->dCand, ex->dNodeOf, ex->dKept, ex->dCounts,
+    void *bufs[] = {ex->dIn[0], ex->dIn[1], ex->dIn[2], ex->dPyr, ex->dBlur, ex->dTabs, ex->dCand, ex->dNodeOf, ex->dKept, ex->dCounts,
                     ex->dOutCounts[0], ex->dOutCounts[1], ex->dOutKps[0], ex->dOutKps[1], ex->dOutDesc[0], ex->dOutDesc[1],
                     ex->dsoOcc, ex->dsoCellKp, ex->dsoCellCnt, ex->dsoSmall, ex->dsoCentre, ex->dsoKps, ex->dsoDesc,
                     ex->dMap1, ex->dMap2, ex->dUndist};
     for (void *p : bufs) if (p) cudaFree(p);
     for (int i = 0; i < 8; i++) if (ex->ev[i]) cudaEventDestroy(ex->ev[i]);
     for (int sl = 0; sl < 2; sl++) {
-        cudaEvent_t evs[] = {ex->inReady[sl], ex->inFree[sl], ex->outReady[sl], ex->outFree[sl]};
+        cudaEvent_t evs[] = {ex->outReady[sl], ex->outFree[sl]};
+        for (cudaEvent_t e : evs) if (e) cudaEventDestroy(e);
+    }
+    for (int sl = 0; sl < kInSlots; sl++) {
+        cudaEvent_t evs[] = {ex->inReady[sl], ex->inFree[sl]};
         for (cudaEvent_t e : evs) if (e) cudaEventDestroy(e);
     }
     for (cudaStream_t st : streams) if (st) cudaStreamDestroy(st);
