@@ -269,14 +269,20 @@ def run_ours(args, rank, local_rank, world):
     kps0 = d_kps.cpu().numpy().view(KP_DTYPE).reshape(B, cap)
     desc0 = d_desc.cpu().numpy()
     mp = make_mappoints(counts0, kps0, desc0, 1 + rank)
-    mp_keys = ["n_mp", "proj_x", "proj_y", "proj_xr", "view_cos", "level", "in_view", "has_obs", "desc"]
+    # the frames are monocular (mvuRight = -1, u_right = NULL below), so mTrackProjXR is never read (src/ORBmatcher.cc:93-97) and is
+    # neither marshalled nor uploaded: proj_xr = NULL in ygzorb_mappoint_proj
+    mp_fields = ["n_mp", "proj_x", "proj_y", "proj_xr", "view_cos", "level", "in_view", "has_obs", "desc"]
+    mp_keys = [k for k in mp_fields if k != "proj_xr"]
     h_mp = {k: torch.from_numpy(mp[k]).pin_memory() for k in mp_keys}
     d_mp = {k: h_mp[k].to(dev) for k in mp_keys}
+
+    def mp_struct(m):
+        return Y.MapPointProj(M, *[m[k].data_ptr() if k in m else None for k in mp_fields])
     sf, _, _ = synth.scale_tables(SCALE, LEVELS)
     assert sf.tobytes() == ex.tables()["scale"].tobytes()
     F = Y.FrameFeatures(B, cap, d_counts.data_ptr(), d_kps.data_ptr(), d_desc.data_ptr(), None, None,
                         0.0, 0.0, float(W), float(H), LEVELS, sf.ctypes.data)
-    P = Y.MapPointProj(M, *[d_mp[k].data_ptr() for k in mp_keys])
+    P = mp_struct(d_mp)
     dflags = Y.IN_DEVICE | Y.OUT_DEVICE | Y.NO_SYNC
     d_out = {"counts": d_counts, "kps": d_kps, "desc": d_desc, "kp2mp": d_kp2mp, "nm": d_nm}
 
@@ -301,7 +307,7 @@ def run_ours(args, rank, local_rank, world):
             "out": o, "mp": m, "best": d_best if sl == 0 else torch.zeros_like(d_best),
             "F": Y.FrameFeatures(B, cap, o["counts"].data_ptr(), o["kps"].data_ptr(), o["desc"].data_ptr(), None, None,
                                  0.0, 0.0, float(W), float(H), LEVELS, sf.ctypes.data),
-            "P": Y.MapPointProj(M, *[m[k].data_ptr() for k in mp_keys]),
+            "P": mp_struct(m),
             "h_out": {k: torch.zeros(v.shape, dtype=v.dtype).pin_memory() for k, v in d_out.items()},
             "mp_ready": torch.cuda.Event(), "search_done": torch.cuda.Event(), "out_done": torch.cuda.Event()})
     h_out = slots[0]["h_out"]
