@@ -27,6 +27,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 METRIC = "ORB frames/sec (752x480, 1000 kp, 8 lvl) and Hamming matches/sec vs CPU"
 W, H, NFEAT, SCALE, LEVELS, INI_TH, MIN_TH = 752, 480, 1000, 1.2, 8, 20, 7
 N_MAPPOINTS = 3000
+N_SLOTS = 2   # device buffer sets of the e2e leg (MapPoints in, results out); 3 and 4 measured slower (uploads run too far ahead of the frames)
 # algorithmic bytes per 752x480 frame, stage by stage (inputs read once + outputs written once)
 STAGE_BYTES = {"pyramid": 1845634, "fast": 1117367, "blur": 2234734, "quadtree_orient_desc": 60000}
 STAGED_TOTAL = 5257735
@@ -300,7 +301,7 @@ def run_ours(args, rank, local_rank, world):
     # MapPoint upload and the result download run on two side streams here, ordered by events.
     copy_in, copy_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
     slots = []
-    for sl in range(2):
+    for sl in range(N_SLOTS):
         o = d_out if sl == 0 else {k: torch.zeros_like(v) for k, v in d_out.items()}
         m = d_mp if sl == 0 else {k: torch.zeros_like(v) for k, v in d_mp.items()}
         slots.append({
@@ -314,9 +315,12 @@ def run_ours(args, rank, local_rank, world):
     host_step = [0]
 
     def step_host():
-        S = slots[host_step[0] & 1]
+        S = slots[host_step[0] % N_SLOTS]
         host_step[0] += 1
         copy_in.wait_event(S["search_done"])            # the previous search on this slot has read its MapPoints
+        # ... and the previous STEP's search is done: the MapPoints of a step go up while its extraction runs, not earlier, so the
+        # frames (needed first) do not share the link with records needed last (running further ahead measured slower)
+        copy_in.wait_event(slots[(host_step[0] - 2) % N_SLOTS]["search_done"])
         with torch.cuda.stream(copy_in):
             for k in mp_keys:
                 S["mp"][k].copy_(h_mp[k], non_blocking=True)
