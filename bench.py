@@ -180,7 +180,7 @@ def cpu_search_by_projection(counts, kps, desc, mp, threads, repeat):
                                              SBP_TH, False, SBP_RATIO, threads=threads)
     sec = time.perf_counter() - t0
     return {"frames": len(counts) * repeat, "seconds": sec, "frames_per_s": len(counts) * repeat / sec,
-            "matches_per_frame": float(nm.mean())}
+            "matches_per_frame": float(nm.mean()), "kind": "oracle-port"}
 
 
 def cpu_extract(frames, threads, repeat):
@@ -189,48 +189,63 @@ def cpu_extract(frames, threads, repeat):
     return "port", run_port_cpu(frames, threads, repeat)
 
 
+def workload_config(B):
+    """The `config` object of the JSON line: identical for both arms (the reference arm runs a bounded sample of it per step)."""
+    M = N_MAPPOINTS
+    return {"workload": "EuRoC-shape 752x480 mono frame stream, 1000 features + SearchByProjection against %d projected "
+                        "MapPoints per frame (configs[1]); %d frames per step per GPU" % (M, B),
+            "nfeatures": NFEAT, "scale": SCALE, "levels": LEVELS, "fast": [INI_TH, MIN_TH], "mappoints": M, "batch": B,
+            "sbp": {"th": SBP_TH, "nnratio": SBP_RATIO},
+            "l2": "inputs larger than L2 (%.0f MB of frames + %.0f MB of pyramid/blur workspace per step)"
+                  % (B * W * H / 1e6, B * 2.0)}
+
+
+def reference_sample_frames(threads):
+    """Frames per CPU step: >= 8 per thread so that thread start-up and the tail of the dynamic schedule are amortised."""
+    return max(8 * threads, 64)
+
+
 def run_reference_arm(args, rank, world):
     """--impl reference: the reference's CPU implementation of the step on the box's host cores, rank 0 only:
-    ORBextractor.cc itself (oracle/_ref, compiled from the reference's own source) + the oracle port of
-    SearchByProjection (ORBmatcher.cc cannot be compiled in this image)."""
+    extraction = ORBextractor.cc itself (oracle/_ref/ygz_ref_orb, the reference's own source compiled unmodified), ONE process
+    for all timed steps (--repeat steps); SearchByProjection = the reference's own ORBmatcher.cc (oracle/_ref/ygz_ref_match)
+    when that binary exists, else the oracle port."""
     if rank != 0:
         return
     import oracle_lib as O
     threads = os.cpu_count() or 1
-    sample = max(2 * threads, 16)
+    sample = reference_sample_frames(threads)
     frames = make_frames(sample, 0)
     p = O.params(NFEAT, SCALE, LEVELS, INI_TH, MIN_TH)
     cap = NFEAT + 64
     counts, kps, desc = O.extract_batch(p, frames, threads=threads, cap=cap)    # untimed set-up: inputs of the search
     mp = make_mappoints(counts, kps, desc, 1)
-    kind, _ = cpu_extract(frames[: max(threads, 4)], threads, 1)   # warm-up of page cache / binary
-    for _ in range(max(args.warmup - 1, 0)):
-        cpu_extract(frames, threads, 1)
     t0 = time.perf_counter()
-    t_ext = t_sbp = 0.0
-    for _ in range(args.steps):
-        _, st = cpu_extract(frames, threads, 1)
-        t_ext += st["seconds"]
-        sb = cpu_search_by_projection(counts, kps, desc, mp, threads, 1)
-        t_sbp += sb["seconds"]
+    if args.warmup > 0:
+        cpu_extract(frames, threads, args.warmup)
+        cpu_search_by_projection(counts, kps, desc, mp, threads, 1)
+    kind, st = cpu_extract(frames, threads, args.steps)                          # one process, `steps` passes over the sample
+    sb = cpu_search_by_projection(counts, kps, desc, mp, threads, args.steps)
     wall = time.perf_counter() - t0
+    t_ext, t_sbp = st["seconds"], sb["seconds"]
     fps = sample * args.steps / (t_ext + t_sbp)
     line = {
         "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * (t_ext + t_sbp) / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "EuRoC-shape 752x480 mono frame stream, 1000 features + SearchByProjection against %d "
-                               "projected MapPoints (configs[1]); bounded sample of %d frames per step" % (N_MAPPOINTS, sample),
-                   "nfeatures": NFEAT, "scale": SCALE, "levels": LEVELS, "fast": [INI_TH, MIN_TH], "mappoints": N_MAPPOINTS},
+        "config": workload_config(args.batch),
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind,
-                         "sample": "%d frames x %d steps, %d threads over frames; extraction = reference ORBextractor.cc "
-                                   "(timed inside the binary), SearchByProjection = oracle port; wall %.1f s"
-                                   % (sample, args.steps, threads, wall)},
+                         "kind_per_leg": {"extraction": kind, "search_by_projection": sb["kind"]},
+                         "sample": "each step = a bounded sample of %d frames of the workload (%d per thread), %d steps in one "
+                                   "process, %d threads over frames; extraction = reference ORBextractor.cc (timed inside the "
+                                   "binary), SearchByProjection = %s; wall %.1f s"
+                                   % (sample, sample // threads, args.steps, threads, sb["kind"], wall)},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "hamming": {"mappoints_per_s": sample * args.steps * N_MAPPOINTS / t_sbp, "extract_frames_per_s": sample * args.steps / t_ext},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
 
 def run_ours(args, rank, local_rank, world):
     import torch
@@ -398,14 +413,18 @@ def run_ours(args, rank, local_rank, world):
     ms_sbp, _ = timed(search, args.steps)
     stage_ms["search_by_projection"] = ms_sbp / args.steps
     def shutdown():
-        # torch's pinned-memory allocator records events on the extractor's stream when its buffers are freed at
-        # interpreter exit, i.e. after the handles (and their streams) are gone: leave without running destructors.
+        """Orderly teardown, normal interpreter exit afterwards (exit hooks run, the mapped libraries stay visible):
+        everything queued on the handles' streams is drained, torch's work is drained, then the handles go — BEFORE any
+        pinned buffer is released, which is the order an embedder gets when the handle is a member destroyed first."""
+        ex.sync()
+        mt.sync()
         torch.cuda.synchronize()
         if dist is not None:
+            dist.barrier()
             dist.destroy_process_group()
-        sys.stdout.flush()
-        sys.stderr.flush()
-        os._exit(0)
+        mt.close()
+        ex.close()
+        torch.cuda.synchronize()
 
     if rank != 0:
         shutdown()
@@ -416,6 +435,7 @@ def run_ours(args, rank, local_rank, world):
     if world == 1 and not args.no_cpu:
         line["hamming"].update(knn_probe(Y, mt, torch))
         line["cpu_baseline"] = cpu_baseline_leg(frames_np, counts0, kps0, desc0, mp)
+    line["native_library"] = Y.LIB_PATH if os.path.exists(Y.LIB_PATH) else None
     print(json.dumps(line), flush=True)
     shutdown()
 
@@ -453,12 +473,7 @@ def build_line(args, world, B, cap, ms, ms_e2e, launches, clocks, stage_ms, n_kp
         "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "EuRoC-shape 752x480 mono frame stream, 1000 features + SearchByProjection against %d projected "
-                               "MapPoints per frame (configs[1]); %d frames per step per GPU" % (M, B),
-                   "nfeatures": NFEAT, "scale": SCALE, "levels": LEVELS, "fast": [INI_TH, MIN_TH], "mappoints": M, "batch": B,
-                   "sbp": {"th": SBP_TH, "nnratio": SBP_RATIO},
-                   "l2": "inputs larger than L2 (%.0f MB of frames + %.0f MB of pyramid/blur workspace per step)"
-                         % (B * W * H / 1e6, B * 2.0)},
+        "config": workload_config(B),
         "clocks": clocks,
         "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": B * W * H + mp_bytes,
                 "d2h_bytes_per_step": B * (4 + cap * 60 + cap * 4 + 4), "ms_per_step": ms_e2e / args.steps},
@@ -503,7 +518,7 @@ def knn_probe(Y, mt, torch):
 def cpu_baseline_leg(frames_np, counts, kps, desc, mp):
     """The reference's CPU path on the box's host cores, bounded sample of the same workload."""
     threads = os.cpu_count() or 1
-    n = max(2 * threads, 16)
+    n = min(reference_sample_frames(threads), len(frames_np))
     sample = frames_np[:n]
     kind, st1 = cpu_extract(sample, threads, 1)
     repeat = int(max(1, min(200, 12.0 / max(st1["seconds"], 1e-3))))
@@ -515,9 +530,10 @@ def cpu_baseline_leg(frames_np, counts, kps, desc, mp):
     fps = 1.0 / (1.0 / st["frames_per_s"] + 1.0 / sb["frames_per_s"])
     _, s1 = cpu_extract(sample[:8], 1, 1)
     return {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind,
+            "kind_per_leg": {"extraction": kind, "search_by_projection": sb["kind"]},
             "sample": "%d frames: extraction x %d repeats = reference ORBextractor.cc (%.1f s, %.1f frames/s), SearchByProjection "
-                      "x %d repeats = oracle port (%.1f s, %.0f frames/s); threads over frames"
-                      % (n, repeat, st["seconds"], st["frames_per_s"], rep2, sb["seconds"], sb["frames_per_s"]),
+                      "x %d repeats = %s (%.1f s, %.0f frames/s); threads over frames"
+                      % (n, repeat, st["seconds"], st["frames_per_s"], rep2, sb["kind"], sb["seconds"], sb["frames_per_s"]),
             "extract_frames_per_s": st["frames_per_s"], "sbp_mappoints_per_s": sb["frames_per_s"] * N_MAPPOINTS,
             "single_thread_extract_frames_per_s": s1["frames_per_s"]}
 
@@ -539,14 +555,7 @@ def main():
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
         return
-    try:
-        run_ours(args, rank, local_rank, world)
-    except BaseException:
-        # leave without running destructors: a failed run must report its traceback, not a teardown crash
-        import traceback
-        traceback.print_exc()
-        sys.stdout.flush(); sys.stderr.flush()
-        os._exit(1)
+    run_ours(args, rank, local_rank, world)
 
 
 if __name__ == "__main__":

@@ -114,6 +114,14 @@ int ygzorb_extract_dso_batch(ygzorb_extractor *ex, const uint8_t *frames, int n_
                              size_t frame_stride, unsigned flags, int32_t *grid_size, const int32_t *n_exist, int cap,
                              int32_t *counts, ygzorb_keypoint *keypoints, uint8_t *desc);
 
+/* The "existing keys" rows of ORBextractor::operator()(Frame *frame, ..., ORBSLAM_KEYPOINT, leftEye = true) on a Frame that
+ * already holds keypoints (src/ORBextractor.cc:1086-1099): rBRIEF descriptors of n keypoints (HOST records in level-0
+ * coordinates, octave = their level, angle as they carry it — not recomputed, :1091) sampled on the blurred level `octave` of
+ * frame `frame` of the LAST ygzorb_extract_batch call, at cvRound(pt * mvInvScaleFactor[octave]) (:1095-1096, :111).  desc: HOST,
+ * n x 32 B.  Canonical where the reference is undefined: a centre closer than 16 px to the border of its level (the reference
+ * would sample outside the image) gets a zero descriptor.  The host class puts these rows in front of the new OctTree keys. */
+int ygzorb_describe_existing(ygzorb_extractor *ex, int frame, int n, const ygzorb_keypoint *keypoints, uint8_t *desc);
+
 /* ORBextractor::ComputePyramid(cv::Mat) alone (src/ORBextractor.cc:1129-1150) — what the Frame
  * constructor runs (src/Frame.cc:773-814).  Host or device input per flags. */
 int ygzorb_compute_pyramid_batch(ygzorb_extractor *ex, const uint8_t *frames, int n_frames, int w, int h,

@@ -105,7 +105,8 @@ static void storeOut(FrameOut *fo, const std::vector<cv::KeyPoint> &kps, const c
     for (int i = 0; i < fo->n; i++) std::memcpy(fo->desc + (size_t)i * 32, desc.ptr(i), 32);
 }
 
-// --dso: all frames through one extractor, in order
+// --dso (DSO_KEYPOINT) or --frame-api --exist (ORBSLAM_KEYPOINT on Frames that already hold keypoints,
+// src/ORBextractor.cc:1086-1099): all frames through one extractor, in order
 static void runDso(const Opts &o, const unsigned char *frames, std::vector<FrameOut> &outs) {
     ygz::ORBextractor ex(o.nfeatures, o.scale, o.levels, o.ini, o.mn);
     if (o.grid > 0) ex.mnGridSize = o.grid;
@@ -125,7 +126,7 @@ static void runDso(const Opts &o, const unsigned char *frames, std::vector<Frame
         }
         f.N = (int)f.mvKeys.size();
         cv::Mat desc;
-        ex(&f, f.mvKeys, desc, ygz::ORBextractor::DSO_KEYPOINT, true);
+        ex(&f, f.mvKeys, desc, o.dso ? ygz::ORBextractor::DSO_KEYPOINT : ygz::ORBextractor::ORBSLAM_KEYPOINT, true);
         storeOut(&outs[k], f.mvKeys, desc);
         outs[k].gridAfter = ex.mnGridSize;
     }
@@ -208,7 +209,7 @@ int main(int argc, char **argv) {
 
     const auto t0 = std::chrono::steady_clock::now();
     const int total = o.n * o.repeat;
-    if (o.dso) {
+    if (o.dso || (o.frameApi && !o.exist.empty())) {
         runDso(o, frames, outs);
     } else if (o.threads <= 1) {
         for (int k = 0; k < total; k++) {

@@ -421,8 +421,7 @@ template <bool PDL, int TP> __global__ void __launch_bounds__(kFastThreads, 32) 
 
 int launchFast(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s) {
     if (G.totalCells == 0) return 0;
-    size_t smem = (size_t)G.fastRegionA + G.fastScoreBytes + (size_t)(kFastThreads / 32) * G.fastWarpCap * sizeof(uint16_t);
-    if (const char *pad = getenv("YGZ_FAST_SMEM_PAD")) smem += (size_t)atoi(pad);   // occupancy experiments
+    const size_t smem = (size_t)G.fastRegionA + G.fastScoreBytes + (size_t)(kFastThreads / 32) * G.fastWarpCap * sizeof(uint16_t);
     const dim3 grid(G.totalCells, nFrames);
     if (G.fastPitch == kFastTilePitchNarrow) {
         if (B.pdl) launchChain(true, k_fast<true, kFastTilePitchNarrow>, grid, dim3(kFastThreads), smem, s, G, B);
@@ -1042,6 +1041,7 @@ int launchDescribe(const FrameGeom &G, const DevBuffers &B, int nFrames, int cap
 // operator()(Frame*, ..., DSO_KEYPOINT) (:1079-1113) and the angle refresh of the existing keypoints (:1383-1385).
 // A centre closer than 16 px to the border of its level (the reference would read outside the image) gets a zero descriptor
 // and keeps its angle.
+template <bool kGivenAngle>
 __global__ void __launch_bounds__(kDescWarps * 32) k_describe_list(const __grid_constant__ FrameGeom G, const DevBuffers B, int cap,
                                                                    const int4 *centre, const int32_t *counts, ygzorb_keypoint *kps,
                                                                    uint8_t *desc) {
@@ -1053,17 +1053,21 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe_list(const __grid_
     const int level = c.x, x = c.y, y = c.z;
     const LevelGeom &L = G.lv[level];
     if (x < 16 || y < 16 || x >= L.w - 16 || y >= L.h - 16) { desc[o * 32 + lane] = 0; return; }
-    const float angle = icAngleWarp(G, levelPtr(G, B, f, level) + (long long)y * L.pitch + x, L.pitch, lane);
+    // kGivenAngle: the descriptors of pre-existing keys in front of new OctTree keys (:1088-1099) use the angle the key carries
+    const float angle = kGivenAngle ? kps[o].angle
+                                    : icAngleWarp(G, levelPtr(G, B, f, level) + (long long)y * L.pitch + x, L.pitch, lane);
     const int val = orbByteWarp(B.blur + (long long)f * B.blurSlab + B.blurOff[level] + (long long)y * B.blurPitch[level] + x,
                                 B.blurPitch[level], angle, lane);
     desc[o * 32 + lane] = (uint8_t)val;
-    if (lane == 0) kps[o].angle = angle;
+    if (!kGivenAngle && lane == 0) kps[o].angle = angle;
 }
 
 int launchDescribeList(const FrameGeom &G, const DevBuffers &B, int nFrames, int cap, const int4 *centre, const int32_t *counts,
-                       ygzorb_keypoint *kps, uint8_t *desc, cudaStream_t s) {
+                       ygzorb_keypoint *kps, uint8_t *desc, cudaStream_t s, bool givenAngle) {
     if (nFrames <= 0 || cap <= 0) return 0;
-    k_describe_list<<<dim3((cap + kDescWarps - 1) / kDescWarps, nFrames), kDescWarps * 32, 0, s>>>(G, B, cap, centre, counts, kps, desc);
+    const dim3 grid((cap + kDescWarps - 1) / kDescWarps, nFrames);
+    if (givenAngle) k_describe_list<true><<<grid, kDescWarps * 32, 0, s>>>(G, B, cap, centre, counts, kps, desc);
+    else k_describe_list<false><<<grid, kDescWarps * 32, 0, s>>>(G, B, cap, centre, counts, kps, desc);
     return 1;
 }
 

@@ -409,7 +409,8 @@ static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int 
     YGZ_MARK(0);
     if ((rc = bindInput(ex, frames, w, h, frameStride, inDev, slot))) return rc;
     if ((rc = applyUndistort(ex, n, w, h, srcPitch))) return rc;
-    YGZ_CUDA(cudaMemsetAsync(ex->dCounts, 0, (2 * (size_t)ex->maxBatch * kMaxLevels + 1) * sizeof(int), ex->stream));
+    // the counters only: the status word behind them is sticky across the chunks of a call and cleared when it is read
+    YGZ_CUDA(cudaMemsetAsync(ex->dCounts, 0, 2 * (size_t)ex->maxBatch * kMaxLevels * sizeof(int), ex->stream));
     YGZ_MARK(1);
     const int pdl = (n <= kPdlMaxFrames && !ex->profiling) ? 1 : 0;   // live tracking: the chain is launch-latency bound
     ex->B.pdl = ex->profiling ? 0 : 1;   // the 7 dependent pyramid launches are short at any batch size
@@ -454,7 +455,11 @@ static int finishProfile(Extractor *ex) {
 static int checkStatus(Extractor *ex) {
     int st = 0;
     YGZ_CUDA(cudaMemcpy(&st, ex->B.status, sizeof st, cudaMemcpyDeviceToHost));
-    if (st) { setError("internal capacity overflow in the FAST/quadtree stage (status " + std::to_string(st) + ")"); return YGZORB_E_CAPACITY; }
+    if (st) {
+        YGZ_CUDA(cudaMemset(ex->B.status, 0, sizeof st));
+        setError("internal capacity overflow in the FAST/quadtree stage (status " + std::to_string(st) + ")");
+        return YGZORB_E_CAPACITY;
+    }
     return 0;
 }
 
@@ -514,6 +519,7 @@ int ygzorb_extractor_create(const ygzorb_params *params, int max_w, int max_h, i
     if (rc) { delete ex; return rc; }
     cudaError_t e = cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaMalloc((void **)&ex->dCounts, (2 * (size_t)max_batch * kMaxLevels + 1) * sizeof(int));
+    if (e == cudaSuccess) e = cudaMemset(ex->dCounts, 0, (2 * (size_t)max_batch * kMaxLevels + 1) * sizeof(int));
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ex->h2d, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ex->d2h, cudaStreamNonBlocking);
     for (int sl = 0; sl < 2 && e == cudaSuccess; sl++) {
@@ -758,6 +764,44 @@ int ygzorb_extract_dso_batch(ygzorb_extractor *h, const uint8_t *frames, int n_f
     }
     YGZ_CUDA(cudaGetLastError());
     ex->lastFrames = n_frames; ex->stagesValid = false;
+    YGZ_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int ygzorb_describe_existing(ygzorb_extractor *h, int frame, int n, const ygzorb_keypoint *keypoints, uint8_t *desc) {
+    Extractor *ex = (Extractor *)h;
+    if (!ex || (n > 0 && (!keypoints || !desc))) return argFail("null argument");
+    if (n < 0) return argFail("n < 0");
+    if (n == 0) return 0;
+    if (!ex->stagesValid || ex->lastFrames <= 0) { setError("no blurred pyramid: call ygzorb_extract_batch first"); return YGZORB_E_STATE; }
+    if (frame < 0 || frame >= ex->lastFrames) return argFail("frame out of range");
+    YGZ_CUDA(cudaSetDevice(ex->device));
+    // :1091-1096 — tmp.pt *= mvInvScaleFactor[tmp.octave] (float), then computeOrbDescriptor reads at cvRound(pt) (:111)
+    std::vector<int4> centre((size_t)n);
+    for (int i = 0; i < n; i++) {
+        const int oct = keypoints[i].octave;
+        if (oct < 0 || oct >= ex->G.nlevels) return argFail("keypoint octave outside the pyramid");
+        const float inv = ex->tables.invScale[oct];
+        centre[i] = make_int4(oct, cvRoundF(keypoints[i].x * inv), cvRoundF(keypoints[i].y * inv), 0);
+    }
+    int rc;
+    const size_t nb = (size_t)n;
+    if ((rc = growBuf(ex->dsoCentre, ex->dsoCentreBytes, nb * sizeof(int4)))) return rc;
+    if ((rc = growBuf(ex->dsoKps, ex->dsoKpsBytes, nb * sizeof(ygzorb_keypoint)))) return rc;
+    if ((rc = growBuf(ex->dsoDesc, ex->dsoDescBytes, nb * 32))) return rc;
+    if ((rc = growBuf(ex->dsoSmall, ex->dsoSmallBytes, (size_t)ex->maxBatch * 20))) return rc;
+    cudaStream_t st = ex->stream;
+    YGZ_CUDA(cudaMemcpyAsync(ex->dsoCentre, centre.data(), nb * sizeof(int4), cudaMemcpyHostToDevice, st));
+    YGZ_CUDA(cudaMemcpyAsync(ex->dsoKps, keypoints, nb * sizeof(ygzorb_keypoint), cudaMemcpyHostToDevice, st));
+    YGZ_CUDA(cudaMemcpyAsync(ex->dsoSmall, &n, sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    // one "frame" of n records whose level buffers are those of `frame`: shift the frame bases instead of the kernel's index
+    DevBuffers B = ex->B;
+    B.in = ex->B.in + (long long)frame * ex->B.inFrameStride;
+    B.pyr = ex->B.pyr + (long long)frame * ex->G.slabBytes;
+    B.blur = ex->B.blur + (long long)frame * ex->B.blurSlab;
+    ex->launches += launchDescribeList(ex->G, B, 1, n, ex->dsoCentre, ex->dsoSmall, ex->dsoKps, ex->dsoDesc, st, true);
+    YGZ_CUDA(cudaMemcpyAsync(desc, ex->dsoDesc, nb * 32, cudaMemcpyDeviceToHost, st));
+    YGZ_CUDA(cudaGetLastError());
     YGZ_CUDA(cudaStreamSynchronize(st));
     return 0;
 }

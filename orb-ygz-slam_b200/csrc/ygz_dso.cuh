@@ -30,6 +30,6 @@ int launchDsoOccupancy(const DsoArgs &A, int maxExist, cudaStream_t s);
 int launchDsoCells(const DsoArgs &A, int maxGrid, int maxCellsNow, cudaStream_t s);
 int launchDsoAssemble(const DsoArgs &A, cudaStream_t s);
 int launchDescribeList(const FrameGeom &G, const DevBuffers &B, int nFrames, int cap, const int4 *centre, const int32_t *counts,
-                       ygzorb_keypoint *kps, uint8_t *desc, cudaStream_t s);
+                       ygzorb_keypoint *kps, uint8_t *desc, cudaStream_t s, bool givenAngle = false);
 
 }  // namespace ygz

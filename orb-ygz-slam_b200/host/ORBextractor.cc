@@ -105,17 +105,52 @@ void ORBextractor::operator()(Frame *frame, std::vector<cv::KeyPoint> &_keypoint
         for (int i = 0; i < std::min(rows, (int)n); i++) std::memcpy(descriptors.ptr(i), &mDescBuf[(size_t)i * 32], 32);
         return;
     }
-    if (method != ORBSLAM_KEYPOINT || frame->N > 0) {
-        // FAST_KEYPOINT (:1045-1051, the fixed 5-px grid variant) and ORBSLAM_KEYPOINT on a Frame that already holds keypoints
-        // are not built.
-        std::fprintf(stderr, "ygz::ORBextractor: FAST_KEYPOINT and ORBSLAM_KEYPOINT on a non-empty Frame are not implemented on the GPU path\n");
+    if (method != ORBSLAM_KEYPOINT) {
+        // FAST_KEYPOINT (:1045-1051, ComputeKeyPointsFast): the reference's own header says not to call it; not built.
+        std::fprintf(stderr, "ygz::ORBextractor: FAST_KEYPOINT is not implemented on the GPU path\n");
         _keypoints.clear();
         _descriptors.release();
         return;
     }
-    // :1037-1040 — right eye: pyramid of mImRight; left eye: the Frame's own pyramid (level 0 = the image)
-    const cv::Mat &src = leftEye ? frame->mvImagePyramid[0] : frame->mImRight;
-    (*this)(src, cv::_InputArray(), _keypoints, _descriptors);
+    if (!leftEye) {
+        // :1037-1038 + :1059-1060 — right eye: ComputePyramid(frame->mImRight) + the plain OctTree, whatever the Frame already
+        // holds (frame->N belongs to the left image; the existing-key rows :1086-1099 are left-eye only).  This is what
+        // Frame::ExtractORB(1, ...) runs on every stereo frame, also those that come out of direct tracking (src/Frame.cc:345).
+        // Rows: the reference sizes the Mat for _keypoints.size() + new keys and fills the new keys' rows from 0 (offset = 0).
+        const size_t before = _keypoints.size();
+        std::vector<cv::KeyPoint> fresh;
+        cv::Mat d;
+        (*this)(frame->mImRight, cv::_InputArray(), fresh, d);
+        const int rows = (int)(before + fresh.size());
+        _keypoints.insert(_keypoints.end(), fresh.begin(), fresh.end());
+        if (rows == 0) { _descriptors.release(); return; }
+        _descriptors.create(rows, 32, cv::CV_8U);
+        cv::Mat descriptors = _descriptors.getMat();
+        for (size_t i = 0; i < fresh.size(); i++) std::memcpy(descriptors.ptr((int)i), d.ptr((int)i), 32);
+        for (int i = (int)fresh.size(); i < rows; i++) std::memset(descriptors.ptr(i), 0, 32);   // uninitialised in the reference
+        return;
+    }
+    // left eye: the Frame's own pyramid (:1039-1040; level 0 = the image, the levels above are what ComputePyramid gives)
+    if (frame->N <= 0) {
+        (*this)(frame->mvImagePyramid[0], cv::_InputArray(), _keypoints, _descriptors);
+        return;
+    }
+    // :1086-1099 — a Frame that already holds keypoints: rows [0, N) = descriptors of frame->mvKeys at
+    // pt * mvInvScaleFactor[octave] with the angle each key carries, then the new OctTree keys
+    const int nExist = frame->N;
+    std::vector<cv::KeyPoint> fresh;
+    cv::Mat d;
+    (*this)(frame->mvImagePyramid[0], cv::_InputArray(), fresh, d);
+    std::vector<uint8_t> ed((size_t)nExist * 32);
+    if (ygzorb_describe_existing(mHandle, 0, nExist, (const ygzorb_keypoint *)frame->mvKeys.data(), ed.data()) != 0)
+        fail("ygzorb_describe_existing");
+    const int rows = (int)(_keypoints.size() + fresh.size());                       // :1069 nkeypoints += _keypoints.size()
+    _keypoints.insert(_keypoints.end(), fresh.begin(), fresh.end());
+    _descriptors.create(rows, 32, cv::CV_8U);
+    cv::Mat descriptors = _descriptors.getMat();
+    for (int i = 0; i < rows; i++) std::memset(descriptors.ptr(i), 0, 32);
+    for (int i = 0; i < std::min(nExist, rows); i++) std::memcpy(descriptors.ptr(i), &ed[(size_t)i * 32], 32);
+    for (size_t i = 0; i < fresh.size() && nExist + (int)i < rows; i++) std::memcpy(descriptors.ptr(nExist + (int)i), d.ptr((int)i), 32);
 }
 
 }  // namespace ygz

@@ -121,7 +121,32 @@ int main(int argc, char **argv) {
             int32_t nd = (int32_t)D.mvKeys.size();
             wr(fo, &nd, 1); wr(fo, D.mvKeys.data(), nd);
             for (int i = 0; i < nd; i++) wr(fo, dd.ptr(i), 32);
+            if (rep == 1) {
+                // ... and the right image of that stereo frame: Frame::ExtractORB(1, ...) calls the Right extractor with
+                // ORBSLAM_KEYPOINT, leftEye = false on a Frame whose N is already > 0 (src/Frame.cc:345, :728-731)
+                D.N = nd;
+                D.mImRight = right;
+                exR(&D, D.mvKeysRight, D.mDescriptorsRight, ORBextractor::ORBSLAM_KEYPOINT, false);
+                int32_t nr = (int32_t)D.mvKeysRight.size();
+                wr(fo, &nr, 1); wr(fo, D.mvKeysRight.data(), nr);
+                for (int i = 0; i < nr; i++) wr(fo, D.mDescriptorsRight.ptr(i), 32);
+                for (int l = 0; l < exR.GetLevels(); l++) {        // the Right extractor's pyramid was refreshed (:1037-1038)
+                    int32_t wh[2] = {exR.mvImagePyramid[l].cols, exR.mvImagePyramid[l].rows};
+                    wr(fo, wh, 2);
+                    for (int r = 0; r < wh[1]; r++) wr(fo, exR.mvImagePyramid[l].ptr(r), (size_t)wh[0]);
+                }
+            }
         }
+        // ORBSLAM_KEYPOINT, leftEye = true on a Frame that already holds keypoints (src/ORBextractor.cc:1086-1099)
+        Frame E;
+        E.mvImagePyramid = F.mvImagePyramid;
+        for (int i = 0; i < nL; i += 7) E.mvKeys.push_back(F.mvKeys[i]);
+        E.N = (int)E.mvKeys.size();
+        cv::Mat de;
+        exL(&E, E.mvKeys, de, ORBextractor::ORBSLAM_KEYPOINT, true);
+        int32_t ne = (int32_t)E.mvKeys.size();
+        wr(fo, &ne, 1); wr(fo, E.mvKeys.data(), ne);
+        for (int i = 0; i < ne; i++) wr(fo, de.ptr(i), 32);
     }
     fclose(fo);
     if (argc >= 5) {

@@ -52,9 +52,11 @@ def run_ref(frames, nfeatures=1000, scale=1.2, levels=8, ini=20, mn=7, pyr=False
     return outs, stats
 
 
-def run_ref_dso(frames, exist=None, nfeatures=1000, scale=1.2, levels=8, grid=-1):
+def run_ref_dso(frames, exist=None, nfeatures=1000, scale=1.2, levels=8, grid=-1, orbslam=False):
     """--dso mode: ONE extractor over the frames in order (mnGridSize carries over), DSO_KEYPOINT method on Frames that
-    already hold exist[i] (KP_DTYPE arrays).  Returns per frame {"kps", "desc", "grid_after"}."""
+    already hold exist[i] (KP_DTYPE arrays).  Returns per frame {"kps", "desc", "grid_after"}.
+    orbslam=True: the same Frames through ORBSLAM_KEYPOINT, leftEye = true (src/ORBextractor.cc:1086-1099: descriptors of the
+    existing keys in front of the new OctTree keys); grid_after is then absent."""
     frames = np.ascontiguousarray(frames, np.uint8)
     if frames.ndim == 2:
         frames = frames[None]
@@ -63,7 +65,7 @@ def run_ref_dso(frames, exist=None, nfeatures=1000, scale=1.2, levels=8, grid=-1
         fin, fout, fex = os.path.join(td, "in.u8"), os.path.join(td, "out.bin"), os.path.join(td, "exist.bin")
         frames.tofile(fin)
         cmd = [REF_BIN, "--in", fin, "--w", str(w), "--h", str(h), "--n", str(n), "--nfeatures", str(nfeatures),
-               "--scale", repr(float(scale)), "--levels", str(levels), "--out", fout, "--dso", "--grid", str(grid)]
+               "--scale", repr(float(scale)), "--levels", str(levels), "--out", fout] + (["--frame-api"] if orbslam else ["--dso", "--grid", str(grid)])
         if exist is not None:
             with open(fex, "wb") as f:
                 for e in exist:
@@ -79,6 +81,8 @@ def run_ref_dso(frames, exist=None, nfeatures=1000, scale=1.2, levels=8, grid=-1
         cnt = int(np.frombuffer(buf, "<i4", 1, off)[0]); off += 4
         kps = np.frombuffer(buf, KP_DTYPE, cnt, off).copy(); off += 28 * cnt
         desc = np.frombuffer(buf, np.uint8, 32 * cnt, off).reshape(cnt, 32).copy(); off += 32 * cnt
-        g = int(np.frombuffer(buf, "<i4", 1, off)[0]); off += 4
+        g = None
+        if not orbslam:
+            g = int(np.frombuffer(buf, "<i4", 1, off)[0]); off += 4
         outs.append({"kps": kps, "desc": desc, "grid_after": g})
     return outs

@@ -82,6 +82,17 @@ def test_host_classes_end_to_end():
         for k in range(2):
             nd = int(take("<i4", 1)[0]); gk = take(Y.KP_DTYPE, nd); gd = take(np.uint8, nd * 32).reshape(nd, 32)
             assert gk.tobytes() == want_dso[k]["kps"].tobytes() and np.array_equal(gd, want_dso[k]["desc"]) and nd > len(exist) + 300
+        # the right eye of a stereo frame that came out of direct tracking (Frame N > 0): plain OctTree on mImRight
+        # (src/ORBextractor.cc:1037-1038, 1059-1060), and the Right extractor's pyramid is the right image's
+        nr = int(take("<i4", 1)[0]); gk = take(Y.KP_DTYPE, nr); gd = take(np.uint8, nr * 32).reshape(nr, 32)
+        assert gk.tobytes() == kr.tobytes() and np.array_equal(gd, dr) and nr > 900
+        for lv in O.pyramid(p, right):
+            lw, lh = take("<i4", 2)
+            assert (lh, lw) == lv.shape and np.array_equal(take(np.uint8, int(lw) * int(lh)).reshape(lv.shape), lv)
+        # ORBSLAM_KEYPOINT on a left Frame that already holds keypoints == the reference's own code (:1086-1099)
+        want_e = refcli.run_ref_dso(left[None], [exist], nfeatures=nf, orbslam=True)[0]
+        ne = int(take("<i4", 1)[0]); gk = take(Y.KP_DTYPE, ne); gd = take(np.uint8, ne * 32).reshape(ne, 32)
+        assert ne == len(exist) + len(kl) and gk.tobytes() == want_e["kps"].tobytes() and np.array_equal(gd, want_e["desc"])
     # ORBVocabulary::transform through the host class == the oracle (pinned to DBoW2) on the same descriptors
     want = ovoc.transform(dl, 4)
     nb = int(np.frombuffer(bowbuf, "<i4", 1, 0)[0])
