@@ -201,6 +201,23 @@ int ygzorb_matcher_set_knn_variant(ygzorb_matcher *m, int variant);
  * microkernel) — the denominator of the Hamming roofline. */
 int ygzorb_measure_popc_peak(ygzorb_matcher *m, double *popc_per_s);
 
+/* ygzorb_hamming_knn2 for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.  Same computation
+ * and results as ygzorb_hamming_knn2 (the same kernels), but: no matcher handle, every pointer is DEVICE memory on `device`
+ * (query nq x 32 B, train nt x 32 B; outputs nq x int32, any may be NULL), the work is enqueued on `stream` (a cudaStream_t
+ * as void*, NULL = the default stream) and NOT synchronised, and the kernels' scratch (12 B per query and train split) is a
+ * file-scope static __device__ array of YGZORB_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit.
+ * The call makes no cudaMalloc / cudaFree / allocating library call; the first call on a device resolves the array's device
+ * address (cudaGetSymbolAddress, once per device).  Limit: nq x splits x 12 B <= YGZORB_NOALLOC_SCRATCH_BYTES, which every
+ * nq <= YGZORB_NOALLOC_MAX_QUERIES satisfies; beyond it the call fails with YGZORB_E_CAPACITY and a message (use
+ * ygzorb_hamming_knn2).  All calls on a device share the array: it keeps the last call's contents (nothing in it has to
+ * start at zero: every partial result the merge kernel reads is written by the scan kernel of the same call), and two calls
+ * that overlap on the GPU (different streams, or concurrent host threads) RACE on it — serialise them. */
+#define YGZORB_NOALLOC_SCRATCH_BYTES (8 * 1024 * 1024)
+#define YGZORB_NOALLOC_MAX_QUERIES 600000
+int ygzorb_hamming_knn2_noalloc(int device, void *stream, const uint8_t *query, int nq, const uint8_t *train, int nt,
+                                float ratio, int th, int32_t *best_idx, int32_t *d1, int32_t *d2, int32_t *match);
+
 /* The Frame arrays the searches read (include/Frame.h:248-332) for n_frames frames at fixed strides
  * (frame f: n_kp[f] records starting at f*kp_stride). */
 typedef struct ygzorb_frame_features {

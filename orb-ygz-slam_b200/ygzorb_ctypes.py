@@ -50,6 +50,8 @@ def lib():
         L.ygzorb_extractor_set_undistort_maps.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
         L.ygzorb_compute_pyramid_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                                    C.c_size_t, C.c_uint]
+        L.ygzorb_hamming_knn2_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_int,
+                                                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -777,6 +779,15 @@ def bow_transform(matcher, voc, frames, levelsup, stride=None):
                     "bow_word": bw[i, :nb].copy(), "bow_value": bv[i, :nb].copy(), "fv_node": fn[i, :nn].astype(np.int32),
                     "fv_start": fs[i, :nn + 1].copy(), "fv_feat": ff[i, :int(fs[i, nn])].astype(np.int32)})
     return out
+
+
+NOALLOC_SCRATCH_BYTES = 8 * 1024 * 1024   # YGZORB_NOALLOC_SCRATCH_BYTES
+NOALLOC_MAX_QUERIES = 600000              # YGZORB_NOALLOC_MAX_QUERIES
+
+
+def hamming_knn2_noalloc(device, stream, q_ptr, nq, t_ptr, nt, ratio, th, idx_ptr, d1_ptr, d2_ptr, match_ptr):
+    """ygzorb_hamming_knn2_noalloc: device pointers only, enqueued on `stream` (int cudaStream_t or None), not synchronised."""
+    check(lib().ygzorb_hamming_knn2_noalloc(device, stream, q_ptr, nq, t_ptr, nt, ratio, th, idx_ptr, d1_ptr, d2_ptr, match_ptr))
 
 
 def hamming_knn2(query, train, ratio, th, device=0):
