@@ -170,17 +170,26 @@ def make_mappoints(counts, kps, desc, seed):
 
 
 def cpu_search_by_projection(counts, kps, desc, mp, threads, repeat):
-    """Times the oracle port of ORBmatcher::SearchByProjection (threads over frames) on host cores."""
+    """Times ORBmatcher::SearchByProjection (threads over frames) on host cores: the reference's own src/ORBmatcher.cc +
+    Frame::AssignFeaturesToGrid / GetFeaturesInArea (oracle/_ref/libygz_ref_match.so, compiled from the reference's source) when
+    that library travelled with the snapshot, else the oracle port."""
     import oracle_lib as O
+    import ref_match_lib as R
     import synth
     sf, _, _ = synth.scale_tables(SCALE, LEVELS)
-    t0 = time.perf_counter()
-    for _ in range(repeat):
-        _, nm = O.search_by_projection_batch(counts, mp["n_mp"], kps, desc, (0.0, 0.0, float(W), float(H)), sf, mp,
-                                             SBP_TH, False, SBP_RATIO, threads=threads)
-    sec = time.perf_counter() - t0
+    bounds = (0.0, 0.0, float(W), float(H))
+    if R.available():
+        _, nm, sec = R.search_by_projection_batch(counts, mp["n_mp"], kps, desc, bounds, sf, mp, SBP_TH, False, SBP_RATIO,
+                                                  threads=threads, repeat=repeat)
+        kind = "reference"
+    else:
+        t0 = time.perf_counter()
+        for _ in range(repeat):
+            _, nm = O.search_by_projection_batch(counts, mp["n_mp"], kps, desc, bounds, sf, mp, SBP_TH, False, SBP_RATIO, threads=threads)
+        sec = time.perf_counter() - t0
+        kind = "oracle-port"
     return {"frames": len(counts) * repeat, "seconds": sec, "frames_per_s": len(counts) * repeat / sec,
-            "matches_per_frame": float(nm.mean()), "kind": "oracle-port"}
+            "matches_per_frame": float(nm.mean()), "kind": kind}
 
 
 def cpu_extract(frames, threads, repeat):

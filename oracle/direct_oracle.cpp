@@ -2,9 +2,11 @@
 // direct tracker and the descriptor post-processing of MapPoint (part 4 of the oracle).  Linked into
 // oracle/libygz_oracle.so; used by tests/ only — never by the product.
 //
-// PARITY UNPINNED: src/MapPoint.cc, src/ORBmatcher.cc, src/Align.cc and src/SparseImageAlign.cc need Eigen, sophus, OpenCV C++
-// and glog, none of which exist in this image, and the reference ships no test vectors for them.  These are line-by-line
-// restatements over flat arrays, checked against independent numpy re-derivations in tests/test_direct_oracle.py.
+// ComputeDistinctiveDescriptors, FindDirectProjection and Align2D are PINNED to the reference's own code (src/MapPoint.cc:211-271,
+// src/ORBmatcher.cc:1525-1602 and src/Align.cc compiled unmodified into oracle/_ref/libygz_ref_match.so; tests/test_ref_match.py,
+// tests/golden/match_golden.npz).  The SparseImgAlign part is PARITY UNPINNED: src/SparseImageAlign.cc needs dynamic-size Eigen,
+// SE3f::exp and the NLLSSolver / robust-cost templates, beyond the fixed-size stand-in of oracle/ref_shim/eigen_lite.h; it is a
+// line-by-line restatement checked against independent numpy re-derivations in tests/test_direct_oracle.py.
 // Citations are file:line in /root/reference.
 #include <algorithm>
 #include <climits>

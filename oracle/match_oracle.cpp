@@ -2,10 +2,13 @@
 // paths on flat arrays (part 2 of the oracle; part 1 is orb_oracle.cpp).  Linked into
 // oracle/libygz_oracle.so; used by tests/, smoke() and bench.py's CPU legs — never by the product.
 //
-// PARITY UNPINNED: src/ORBmatcher.cc and src/Frame.cc cannot be compiled in this image (they need
-// Eigen, sophus, DBoW2::Vocabulary, OpenCV C++, glog) and the reference ships no test vectors for
-// them, so these functions are line-by-line restatements checked only against brute-force
-// re-derivations in tests/test_match_oracle.py.  Citations are file:line in /root/reference.
+// PINNED to the reference's own code: src/ORBmatcher.cc (whole, unmodified) and the hot-path member functions of Frame /
+// KeyFrame / MapPoint are compiled into oracle/_ref/libygz_ref_match.so (oracle/Makefile target refmatch,
+// oracle/ref_match_api.cpp); tests/test_ref_match.py asserts every function here equal to that library live and to the golden
+// vectors it produced (tests/golden/match_golden.npz).  What stays a restatement is the order of float operations inside an
+// Eigen / cv::Mat expression (a fixed-size stand-in replaces Eigen there, oracle/ref_shim/eigen_lite.h), written out the same
+// way on both sides.  Independent brute-force re-derivations: tests/test_match_oracle.py.  Citations are file:line in
+// /root/reference.
 #include <algorithm>
 #include <atomic>
 #include <climits>

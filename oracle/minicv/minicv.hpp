@@ -96,6 +96,7 @@ struct MatStep {
 };
 
 struct MatZerosExpr { int rows, cols, type; };
+struct MatTransposed;
 
 class Mat {
 public:
@@ -156,7 +157,16 @@ public:
     Mat rowRange(int a, int b) const { Mat m(*this); m.data = data + (size_t)a * step.p[0]; m.rows = b - a; return m; }
     Mat colRange(int a, int b) const { Mat m(*this); m.data = data + (size_t)a * elemSize(); m.cols = b - a; return m; }
     Mat row(int r) const { return rowRange(r, r + 1); }
+    Mat col(int c) const { return colRange(c, c + 1); }
     Mat operator()(const Rect &r) const { return Mat(*this, r); }
+    // single-index access of a vector (n x 1 or 1 x n), as cv::Mat::at<T>(int i0)
+    template <typename T> T &at(int i) { return cols == 1 ? at<T>(i, 0) : at<T>(i / cols, i % cols); }
+    template <typename T> const T &at(int i) const { return cols == 1 ? at<T>(i, 0) : at<T>(i / cols, i % cols); }
+    // float-matrix surface of src/ORBmatcher.cc / src/Frame.cc, defined in minicv_matops.hpp
+    struct MatTransposed t() const;   // lazy, like cv::MatExpr: -A.t() * B becomes a gemm with the GEMM_1_T flag
+    double dot(const Mat &o) const;
+    void convertTo(Mat &dst, int type) const;
+    static Mat ones(int r, int c, int type);
 
     Mat clone() const {
         Mat m(rows, cols, type_);

@@ -220,6 +220,52 @@ def keyframe_points_case(kps, desc, n_pts, seed, variant, jitter=2.0, fx=458.654
     return pts, claimed
 
 
+def sim3_pair_case(kps, desc, seed, s12=1.3, jitter=1.0, fx=458.654, fy=457.296, cx=367.215, cy=248.375, scale=1.2, nlevels=8,
+                   p_invalid=0.1):
+    """A consistent input of ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) (src/ORBmatcher.cc:1006-1216):
+    two keyframes that share the given keypoints, one MapPoint per keypoint on either side, MapPoint i of KF1 projecting
+    (through R1w, t1w and then sR21, t21) next to keypoint i of KF2 and vice versa, so that mutual matches are common.
+    Returns dict: pose1 / pose2 (Rkw 9 + tkw 3), s12, R12, t12, pts1, pts2 (valid, world_pos, desc, max_distance, min_distance,
+    normal, angle), intr, already12."""
+    rng = np.random.default_rng(seed)
+    n = len(kps)
+
+    def small_rot(a):
+        return np.array([[1, -a[2], a[1]], [a[2], 1, -a[0]], [-a[1], a[0], 1]], np.float64)
+    R1w, t1w = small_rot(rng.uniform(-0.3, 0.3, 3)), rng.uniform(-1, 1, 3)
+    R2w, t2w = small_rot(rng.uniform(-0.3, 0.3, 3)), rng.uniform(-1, 1, 3)
+    R12 = small_rot(rng.uniform(-0.05, 0.05, 3))
+    t12 = rng.uniform(-0.3, 0.3, 3)
+    sR12 = s12 * R12
+    sR21 = (1.0 / s12) * R12.T
+    t21 = -sR21 @ t12
+
+    def side(Rw, tw, A, b):
+        # target camera coordinates next to keypoint i of the OTHER keyframe: pc_other = A (Rw pw + tw) + b
+        u = kps["x"] + rng.uniform(-jitter, jitter, n)
+        v = kps["y"] + rng.uniform(-jitter, jitter, n)
+        z = rng.uniform(1.0, 12.0, n)
+        z[rng.uniform(size=n) < 0.03] *= -1.0
+        pc = np.stack([(u - cx) / fx * z, (v - cy) / fy * z, z], 1)
+        pw = (np.linalg.inv(Rw) @ ((np.linalg.inv(A) @ (pc - b).T).T - tw).T).T
+        dist = np.linalg.norm(pc, axis=1)
+        lvl = np.clip(kps["octave"] + rng.integers(-1, 2, n), 0, nlevels - 1)
+        max_d = dist * scale ** (lvl - rng.uniform(0.05, 0.95, n))
+        max_d = np.where(rng.uniform(size=n) < 0.05, dist * 0.5, max_d)
+        return {"valid": (rng.uniform(size=n) >= p_invalid).astype(np.uint8), "world_pos": pw.astype(np.float32),
+                "desc": flip_bits(desc, rng.integers(0, 45, size=n), rng), "max_distance": max_d.astype(np.float32),
+                "min_distance": (max_d / scale ** (nlevels - 1)).astype(np.float32), "normal": np.zeros((n, 3), np.float32),
+                "angle": kps["angle"].astype(np.float32), "log_scale_factor": float(np.float32(np.log(np.float32(scale)))),
+                "n_scale_levels": nlevels}
+    pts1 = side(R1w, t1w, sR21, t21)        # KF1's points are searched in KF2
+    pts2 = side(R2w, t2w, sR12, t12)
+    already = np.where(rng.uniform(size=n) < 0.05, rng.integers(0, n, n), -1).astype(np.int32)
+    f = lambda a: np.asarray(a, np.float32).reshape(-1)
+    return {"pose1": np.concatenate([f(R1w), f(t1w)]), "pose2": np.concatenate([f(R2w), f(t2w)]), "s12": float(np.float32(s12)),
+            "R12": f(R12), "t12": f(t12), "pts1": pts1, "pts2": pts2, "intr": np.array([fx, fy, cx, cy], np.float32),
+            "already12": already}
+
+
 def initialization_case(kps, desc, seed, shift=(12.0, -7.0), n_dup=200):
     """Two frames for SearchForInitialization: F1 = the given features (60 % forced to octave 0) plus n_dup near-copies
     that compete for the same partner; F2 = shifted, jittered, bit-flipped, shuffled counterparts of 80 % of F1 with some

@@ -137,3 +137,27 @@ def test_remap_matches_cv2(w, h):
     r1 = rng.integers(-6, max(w, h) + 6, (h, w, 2)).astype(np.int16)
     r2 = rng.integers(0, 1024, (h, w)).astype(np.uint16)
     assert np.array_equal(O.remap(img, r1, r2), cv2.remap(img, r1, r2, cv2.INTER_LINEAR))
+
+
+def test_mat_float_expressions_vs_cv2():
+    """oracle/minicv/minicv_matops.hpp (the cv::Mat expressions of the Sim3 overloads of src/ORBmatcher.cc, used when the
+    reference's own file is compiled into oracle/_ref/libygz_ref_match.so) against the installed OpenCV: gemm with and without the
+    transposition flag and alpha, norm, dot; scaling = element * (float)alpha as cv::Mat::convertTo does."""
+    import ref_match_lib as R
+    if not R.available():
+        pytest.skip("oracle/_ref/libygz_ref_match.so needs the reference tree at build time")
+    import ctypes as C
+    rng = np.random.default_rng(3)
+    for k in range(300):
+        Rm = rng.normal(0, 1 + 10 * (k % 3), (3, 3)).astype(np.float32)
+        x = rng.normal(0, 5, (3, 1)).astype(np.float32); t = rng.normal(0, 2, (3, 1)).astype(np.float32)
+        s = np.float32(rng.uniform(0.3, 3.0))
+        out = np.zeros(38, np.float32)
+        R.lib().ygzr_matops_probe(R._p(Rm), R._p(x), R._p(t), C.c_float(s), R._p(out))
+        assert out[0:3].tobytes() == cv2.gemm(Rm, x, 1.0, t, 1.0).astype(np.float32).tobytes()
+        assert out[3:6].tobytes() == cv2.gemm(Rm, t, -1.0, None, 0.0, flags=cv2.GEMM_1_T).astype(np.float32).tobytes()
+        assert out[26:29].tobytes() == cv2.gemm(Rm, t, -1.0, None, 0.0).astype(np.float32).tobytes()
+        assert out[6] == np.float32(cv2.norm(x)) and out[7] == np.float32(float(np.dot(x[:, 0].astype(np.float64), t[:, 0].astype(np.float64))))
+        assert out[8:17].tobytes() == (Rm.T * np.float32(1.0 / float(s))).astype(np.float32).tobytes()
+        assert out[17:26].tobytes() == (Rm * s).astype(np.float32).tobytes()
+        assert out[29:38].tobytes() == (Rm * np.float32(1.0 / float(s))).astype(np.float32).tobytes()
