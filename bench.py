@@ -256,6 +256,134 @@ def run_reference_arm(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def sharded_block(args, Y, torch, dist, rank, local_rank, world, dev):
+    """BASELINE.json configs[3] and [4], the two workloads north_star shards: through the library's multi-GPU layer
+    (ygzorb_extract_batch_sharded / ygzorb_hamming_knn2_sharded: contiguous shards, the gather of the results on rank 0 over NCCL
+    INSIDE the timed region).  Strong scaling: the totals are fixed, every N (including 1) runs the same job."""
+    import synth
+    comm = Y.Comm.from_torch_distributed(local_rank) if world > 1 else Y.Comm(0, 1, local_rank)
+
+    def max_ms(ms):
+        if dist is None:
+            return ms
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+    out = {}
+    # ---- configs[3]: 4096 distinct 1280x720 frames, 2000 features, streamed from pinned host memory, frame-sharded
+    w, h, nf, n_total, chunk = 1280, 720, 2000, args.shard_frames, 256
+    b, e = Y.shard_range(n_total, rank, world)
+    n = e - b
+    host = torch.empty((max(n, 1), h, w), dtype=torch.uint8).pin_memory()
+    host.numpy()[:n] = synth.frame_batch(w, h, n, seed0=1000 + 16 * rank, distinct=16) if n else 0   # every frame differs (rolled textures)
+    ex = Y.Extractor(nf, SCALE, LEVELS, INI_TH, MIN_TH, max_batch=chunk, device=local_rank)
+    cap = ex.max_keypoints(w, h)
+    stream = torch.cuda.ExternalStream(ex.stream(), device=dev)
+    root = rank == 0
+    g_counts = torch.zeros(n_total if root else 1, dtype=torch.int32, device=dev)
+    g_off = torch.zeros(n_total if root else 1, dtype=torch.int64, device=dev)
+    g_kps = torch.zeros(((n_total * cap) if root else 1, 7), dtype=torch.float32, device=dev)
+    g_desc = torch.zeros(((n_total * cap) if root else 1, 32), dtype=torch.uint8, device=dev)
+    l_counts = torch.zeros(max(n, 1), dtype=torch.int32, device=dev)
+    l_kps = torch.zeros((max(n, 1) * cap, 7), dtype=torch.float32, device=dev)
+    l_desc = torch.zeros((max(n, 1) * cap, 32), dtype=torch.uint8, device=dev)
+
+    def run_sharded():
+        comm.extract_batch_sharded(ex, host.data_ptr(), n_total, w, h, w, w * h, Y.NO_SYNC, cap, chunk, g_counts.data_ptr(),
+                                   g_off.data_ptr(), g_kps.data_ptr(), g_desc.data_ptr())
+
+    def run_local():
+        if n:
+            ex.extract_raw(host.data_ptr(), n, w, h, w, w * h, Y.OUT_DEVICE | Y.NO_SYNC, cap, l_counts.data_ptr(), l_kps.data_ptr(), l_desc.data_ptr())
+
+    d_frames = host.to(dev)                                     # the same shard resident in HBM (3.8 GB / N): kernels + gather without the host link
+
+    def run_sharded_dev():
+        comm.extract_batch_sharded(ex, d_frames.data_ptr(), n_total, w, h, w, w * h, Y.IN_DEVICE | Y.NO_SYNC, cap, chunk, g_counts.data_ptr(),
+                                   g_off.data_ptr(), g_kps.data_ptr(), g_desc.data_ptr())
+
+    def timed(fn):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream); fn(); e1.record(stream)
+        ex.sync(); torch.cuda.synchronize()
+        return max_ms(e0.elapsed_time(e1))
+    run_sharded(); ex.sync()                                   # warm-up (NCCL connections, workspace growth)
+    ms_local = timed(run_local)
+    ms = min(timed(run_sharded), timed(run_sharded))
+    run_sharded_dev(); ex.sync()
+    ms_dev = min(timed(run_sharded_dev), timed(run_sharded_dev))
+    n_kp_local = torch.tensor([int(l_counts[:n].sum().item())], dtype=torch.int64, device=dev)
+    if dist is not None:
+        dist.all_reduce(n_kp_local)
+    if root:
+        total_kp = int(g_counts.sum().item())
+        assert total_kp == int(n_kp_local.item()) and total_kp > 1000 * n_total, "gathered counts differ from the shards' own"
+        last = n_total - 1
+        assert int(g_off[last].item()) >= 0
+        out["config3"] = {
+            "workload": "batched offline extraction of %d distinct 1280x720 frames, 2000 features each, from pinned host memory, "
+                        "frame-sharded over %d GPU(s); gather of counts + packed records on rank 0 inside the timed region" % (n_total, world),
+            "ms": ms, "frames_per_s": n_total / (ms * 1e-3), "ms_extract_only": ms_local, "gather_ms_exposed": max(ms - ms_local, 0.0),
+            "h2d_GBps_all_ranks": n_total * w * h / (ms * 1e-3) / 1e9,
+            "ms_device_resident": ms_dev, "frames_per_s_device_resident": n_total / (ms_dev * 1e-3),
+            "gathered_bytes": total_kp * 60 + 4 * n_total, "keypoints_per_frame": total_kp / n_total, "chunk_frames": chunk, "scaling": "strong"}
+    del host, d_frames, g_kps, g_desc, l_kps, l_desc
+    ex.close()
+    # ---- configs[4]: brute-force Hamming kNN-2 + ratio 0.6, nq x nt 256-bit rows, query-sharded; train rows broadcast from rank 0
+    nq, nt = args.shard_queries, args.shard_queries
+    b, e = Y.shard_range(nq, rank, world)
+    n = e - b
+    rng = np.random.default_rng(5)
+    train = torch.from_numpy(rng.integers(0, 256, size=(nt, 32), dtype=np.uint8)).to(dev) if root else torch.zeros((nt, 32), dtype=torch.uint8, device=dev)
+    ref_train = train
+    if dist is not None:
+        ref_train = train.clone()
+        dist.broadcast(ref_train, src=0)                        # set-up only: the queries are derived from train rows
+    g = torch.Generator(device=dev); g.manual_seed(100 + rank)
+    query = torch.randint(0, 256, (max(n, 1), 32), dtype=torch.uint8, device=dev, generator=g)
+    half = n // 2
+    if half:
+        src = torch.randint(0, nt, (half,), device=dev, generator=g)
+        noise = (torch.rand((half, 32, 8), device=dev, generator=g) < 0.1).to(torch.uint8)
+        bits = (noise << torch.arange(8, device=dev, dtype=torch.uint8)).sum(dim=2).to(torch.uint8)
+        query[:half] = ref_train[src] ^ bits
+    del ref_train
+    mt = Y.Matcher(local_rank)
+    mstream = torch.cuda.ExternalStream(mt.stream(), device=dev)
+    res = [torch.full((nq,), -7, dtype=torch.int32, device=dev) for _ in range(4)]
+
+    def run_knn():
+        comm.hamming_knn2_sharded(mt, query.data_ptr(), nq, train.data_ptr(), nt, 0.6, 50, Y.BROADCAST_TRAIN | Y.NO_SYNC,
+                                  *[r.data_ptr() for r in res])
+    comm.hamming_knn2_sharded(mt, query.data_ptr(), nq, train.data_ptr(), nt if n else nt, 0.6, 50, Y.BROADCAST_TRAIN | Y.NO_SYNC,
+                              *[r.data_ptr() for r in res])
+    mt.sync()
+    peak = mt.popc_peak()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(mstream); run_knn(); e1.record(mstream)
+    mt.sync(); torch.cuda.synchronize()
+    ms = max_ms(e0.elapsed_time(e1))
+    if root:
+        matches = int((res[3] >= 0).sum().item())
+        assert int((res[1] == -7).sum().item()) == 0 and matches > nq // 4, "kNN gather incomplete"
+        pairs = nq * nt / (ms * 1e-3)
+        out["config4"] = {
+            "workload": "brute-force Hamming kNN k=2 + ratio 0.6, %d x %d 256-bit rows, query-sharded over %d GPU(s); train rows "
+                        "broadcast from rank 0 and (idx, d1, d2, match) gathered on rank 0 inside the timed region" % (nq, nt, world),
+            "ms": ms, "pairs_per_s": pairs, "queries_per_s": nq / (ms * 1e-3), "matches": matches, "popc_peak_per_s_per_gpu": peak,
+            "frac_of_popc_peak": pairs * 8 / (peak * world), "scaling": "strong"}
+    mt.close()
+    comm.close()
+    return out
+
+
 def run_ours(args, rank, local_rank, world):
     import torch
     import synth
@@ -435,6 +563,13 @@ def run_ours(args, rank, local_rank, world):
         ex.close()
         torch.cuda.synchronize()
 
+    sharded = None
+    if not args.no_sharded:
+        # free the headline workload's device buffers first: configs[3] holds ~1.5 GB of results on rank 0
+        for S in slots:
+            S.clear()
+        del slots[:]
+        sharded = sharded_block(args, Y, torch, dist, rank, local_rank, world, dev)
     if rank != 0:
         shutdown()
         return
@@ -444,6 +579,8 @@ def run_ours(args, rank, local_rank, world):
     if world == 1 and not args.no_cpu:
         line["hamming"].update(knn_probe(Y, mt, torch))
         line["cpu_baseline"] = cpu_baseline_leg(frames_np, counts0, kps0, desc0, mp)
+    if sharded is not None:
+        line["sharded"] = sharded
     line["native_library"] = Y.LIB_PATH if os.path.exists(Y.LIB_PATH) else None
     print(json.dumps(line), flush=True)
     shutdown()
@@ -555,6 +692,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=512)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline and kNN legs")
+    ap.add_argument("--no-sharded", action="store_true", help="skip the sharded block (configs[3] and [4] through the multi-GPU layer)")
+    ap.add_argument("--shard-frames", type=int, default=4096, help="frames of configs[3]")
+    ap.add_argument("--shard-queries", type=int, default=1 << 20, help="query = train rows of configs[4]")
     ap.add_argument("--pipe", type=int, default=-1, help="frames per pipelined upload chunk of the e2e leg (-1: library default)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

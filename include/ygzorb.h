@@ -520,6 +520,50 @@ int ygzorb_sparse_align_residuals(ygzorb_sparse_align *sa, int level, const floa
 /* host copies of the caches after precompute (any may be NULL): visible[n], ref_patch[n*16], jacobian[n*16*6] */
 int ygzorb_sparse_align_caches(ygzorb_sparse_align *sa, uint8_t *visible, float *ref_patch, float *jacobian);
 
+/* ---- multi-GPU: the two workloads that shard (BASELINE.json configs[3], [4]) ------------------------------- */
+
+/* Frames of a batched extraction and query rows of a brute-force kNN are independent: each rank takes the contiguous range
+ * ygzorb_shard_range gives it (sizes differ by at most one) and runs the single-GPU path; the only communication is the gather
+ * of the results on rank 0 over NCCL.  No reference counterpart (the reference is a single-process CPU system); the interface is
+ * SURVEY.md 8(b)'s.  NCCL is bound at run time (dlopen): these entry points fail with YGZORB_E_STATE where libnccl is absent,
+ * everything else works without it. */
+typedef struct ygzorb_comm ygzorb_comm;
+int ygzorb_shard_range(long long n, int rank, int world, long long *begin, long long *end);
+/* One process per GPU: rank 0 calls ygzorb_comm_unique_id (ncclGetUniqueId, 128 bytes), the host code hands the bytes to the
+ * other ranks by any means (bench.py: torch.distributed broadcast), every rank calls ygzorb_comm_create_rank (ncclCommInitRank).
+ * world == 1 gives a handle without NCCL (the sharded calls then reduce to the single-GPU path + the packing). */
+int ygzorb_comm_unique_id(uint8_t *id128);
+int ygzorb_comm_create_rank(const uint8_t *id128, int rank, int world, int device, ygzorb_comm **out);
+/* One process driving n_gpus devices (ncclCommInitAll over devices 0..n_gpus-1): fills out[0..n_gpus); use one host thread per
+ * handle for the sharded calls (they synchronise with the device between chunks). */
+int ygzorb_comm_create(int n_gpus, ygzorb_comm **out);
+void ygzorb_comm_destroy(ygzorb_comm *comm);
+int ygzorb_comm_info(const ygzorb_comm *comm, int *rank, int *world, int *device);
+long long ygzorb_comm_launch_count(const ygzorb_comm *comm);
+
+#define YGZORB_BROADCAST_TRAIN 16u   /* ygzorb_hamming_knn2_sharded: replicate the train rows from rank 0 first (ncclBroadcast) */
+
+/* ygzorb_hamming_knn2 (the best / second-best + ratio rule of src/ORBmatcher.cc:193-217 over all pairs), query-sharded.
+ * query_shard: this rank's rows [begin, end) of the nq_total queries; train: nt rows on every rank (with
+ * YGZORB_BROADCAST_TRAIN only rank 0's content matters).  best_idx / d1 / d2 / match: full-size arrays (nq_total) on every rank;
+ * a rank fills its own slice, rank 0 ends up with all of them (one grouped ncclSend / ncclRecv on the matcher's stream).
+ * All pointers are device memory.  YGZORB_NO_SYNC: return after enqueueing (events on the matcher's stream then include
+ * the gather). */
+int ygzorb_hamming_knn2_sharded(ygzorb_comm *comm, ygzorb_matcher *m, const uint8_t *query_shard, long long nq_total, uint8_t *train,
+                                int nt, float ratio, int th, unsigned flags, int32_t *best_idx, int32_t *d1, int32_t *d2,
+                                int32_t *match);
+
+/* ygzorb_extract_batch, frame-sharded.  frames_shard: this rank's frames [begin, end) of the n_total (host or device per
+ * YGZORB_IN_DEVICE).  The shard is extracted in chunks of chunk_frames (<= the extractor's max_batch); each chunk's records are
+ * packed back to back on the device and gathered on rank 0 — counts first, then the packed keypoint records and descriptor rows
+ * of exactly the keypoints found — on the communicator's own stream while the next chunk extracts.  Outputs on rank 0 (device
+ * memory; ignored elsewhere): counts[n_total]; keypoints / desc with room for n_total * cap records: the records of rank r's
+ * frames lie back to back from record r_begin * cap on; frame_offset[f] = record index of frame f's first keypoint.
+ * The extractor's stream waits for the gather, so events recorded on it after the call include it. */
+int ygzorb_extract_batch_sharded(ygzorb_comm *comm, ygzorb_extractor *ex, const uint8_t *frames_shard, long long n_total, int w, int h,
+                                 int stride, size_t frame_stride, unsigned flags, int cap, int chunk_frames, int32_t *counts,
+                                 int64_t *frame_offset, ygzorb_keypoint *keypoints, uint8_t *desc);
+
 #ifdef __cplusplus
 }
 #endif

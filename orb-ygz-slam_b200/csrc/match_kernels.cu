@@ -173,12 +173,32 @@ __global__ void k_knn2_merge(const KnnPartial *partial, int nq, int splits, floa
     if (match) match[qi] = (d1 <= th && __fmul_rn(ratio, (float)d2) > (float)d1) ? idx : -1;
 }
 
-int knnSplits(int nq, int nt, int smCount) {
+// Train splits of a kNN call.  Few query blocks leave SMs idle, so the train set is split (gridDim.y) until the grid holds at
+// least 4 CTAs per SM; beyond that the split count is chosen so that the CTA count is (close to) a multiple of the SM count:
+// every CTA does the same work, so an SM that is handed one CTA more than the others sets the kernel's time (768 CTAs on 148
+// SMs = 5 or 6 per SM ran at 0.86 of the balanced rate).  Bounded by one stage of train rows per split, 64 splits, and
+// maxPartialBytes of scratch for the per-split partial results.
+int knnSplits(int nq, int nt, int smCount, size_t maxPartialBytes) {
     const int qBlocks = (nq + kKnnThreads * kKnnQ - 1) / (kKnnThreads * kKnnQ);
-    int splits = 1;
+    const int maxByRows = max(1, (nt + kKnnStage - 1) / kKnnStage);
+    long long maxByBytes = (long long)(maxPartialBytes / (sizeof(KnnPartial) * (size_t)max(nq, 1)));
+    if (maxByBytes < 1) maxByBytes = 1;
+    long long hiLL = min(maxByRows, 64);
+    if (maxByBytes < hiLL) hiLL = maxByBytes;
+    const int hi = (int)hiLL;
     const int want = 4 * smCount;
-    if (qBlocks < want) splits = min((want + qBlocks - 1) / qBlocks, max(1, (nt + kKnnStage - 1) / kKnnStage));
-    return max(1, min(splits, 1024));
+    int lo = 1;
+    if (qBlocks < want) lo = min((want + qBlocks - 1) / qBlocks, hi);
+    if (smCount <= 0 || qBlocks >= 32 * smCount) return lo;   // many waves: the tail is negligible
+    int best = lo;
+    double bestEff = 0.0;
+    for (int sp = lo; sp <= hi; sp++) {
+        const long long c = (long long)qBlocks * sp;
+        const double eff = (double)c / (double)(((c + smCount - 1) / smCount) * smCount);
+        if (eff > bestEff + 1e-9) { bestEff = eff; best = sp; }
+        if (eff >= 0.995) break;
+    }
+    return best;
 }
 
 int launchKnn2(const uint8_t *query, int nq, const uint8_t *train, int nt, float ratio, int th, int splits, void *partial,

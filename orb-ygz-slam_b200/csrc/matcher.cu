@@ -189,7 +189,7 @@ int ygzorb_hamming_knn2(ygzorb_matcher *h, const uint8_t *query, int nq, const u
     if ((rc = stageIn(m, 0, query, (size_t)nq * 32, inDev, &dq))) return rc;
     if (nt > 0) { if ((rc = stageIn(m, 1, train, (size_t)nt * 32, inDev, &dt))) return rc; }
     else { void *p; if ((rc = scratch(m, 1, 256, &p))) return rc; dt = (const uint8_t *)p; }
-    const int splits = knnSplits(nq, nt, m->smCount);
+    const int splits = knnSplits(nq, nt, m->smCount, (size_t)256 << 20);
     void *partial = nullptr;
     if ((rc = scratch(m, 2, knnPartialBytes(nq, splits), &partial))) return rc;
     int32_t *oi = nullptr, *o1 = nullptr, *o2 = nullptr, *om = nullptr;

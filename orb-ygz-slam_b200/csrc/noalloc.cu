@@ -57,7 +57,7 @@ extern "C" int ygzorb_hamming_knn2_noalloc(int device, void *stream, const uint8
     YGZ_CUDA(cudaSetDevice(device));
     PerDevice *D = nullptr;
     if (int rc = setupDevice(device, &D)) return rc;
-    const int splits = ygz::knnSplits(nq, nt, D->smCount);
+    const int splits = ygz::knnSplits(nq, nt, D->smCount, kScratchBytes);   // never plans more scratch than the array holds
     const size_t need = ygz::knnPartialBytes(nq, splits);
     if (need > kScratchBytes) {
         ygz::setError("ygzorb_hamming_knn2_noalloc: " + std::to_string(nq) + " queries x " + std::to_string(splits) +

@@ -101,7 +101,7 @@ struct StereoArgs {
 
 int launchPopcPeak(unsigned *out, int blocks, int threads, int iters, cudaStream_t s);
 int launchDescriptorDistance(const uint8_t *a, const uint8_t *b, int n, int32_t *dist, cudaStream_t s);
-int knnSplits(int nq, int nt, int smCount);
+int knnSplits(int nq, int nt, int smCount, size_t maxPartialBytes);
 size_t knnPartialBytes(int nq, int splits);
 int launchKnn2(const uint8_t *query, int nq, const uint8_t *train, int nt, float ratio, int th, int splits, void *partial,
                int variant, int32_t *bestIdx, int32_t *d1, int32_t *d2, int32_t *match, cudaStream_t s);

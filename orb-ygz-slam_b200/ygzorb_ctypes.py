@@ -781,6 +781,78 @@ def bow_transform(matcher, voc, frames, levelsup, stride=None):
     return out
 
 
+BROADCAST_TRAIN = 16   # YGZORB_BROADCAST_TRAIN
+
+
+def shard_range(n, rank, world):
+    """ygzorb_shard_range: contiguous [begin, end) of rank `rank` (host logic, no device needed)."""
+    b, e = C.c_longlong(), C.c_longlong()
+    check(lib().ygzorb_shard_range(C.c_longlong(n), int(rank), int(world), C.byref(b), C.byref(e)))
+    return b.value, e.value
+
+
+class Comm:
+    """ygzorb_comm: the gather layer of the two sharded workloads (frames of a batched extraction, queries of a brute-force kNN)."""
+
+    def __init__(self, rank=0, world=1, device=0, unique_id=None):
+        L = lib()
+        L.ygzorb_comm_destroy.restype = None
+        L.ygzorb_comm_destroy.argtypes = [C.c_void_p]
+        L.ygzorb_comm_launch_count.restype = C.c_longlong
+        L.ygzorb_comm_launch_count.argtypes = [C.c_void_p]
+        L.ygzorb_comm_create_rank.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.ygzorb_hamming_knn2_sharded.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_int, C.c_float,
+                                                  C.c_int, C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ygzorb_extract_batch_sharded.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_int,
+                                                   C.c_size_t, C.c_uint, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        self.rank, self.world, self.device = rank, world, device
+        h = C.c_void_p()
+        idp = None
+        if world > 1:
+            self._id = (C.c_uint8 * 128).from_buffer_copy(bytes(unique_id))
+            idp = C.cast(self._id, C.c_void_p)
+        check(L.ygzorb_comm_create_rank(idp, rank, world, device, C.byref(h)))
+        self.h = h
+
+    @staticmethod
+    def unique_id():
+        buf = (C.c_uint8 * 128)()
+        check(lib().ygzorb_comm_unique_id(buf))
+        return bytes(buf)
+
+    @classmethod
+    def from_torch_distributed(cls, device):
+        """One process per GPU under torchrun: rank 0 makes the NCCL id, torch.distributed carries the 128 bytes."""
+        import torch
+        import torch.distributed as dist
+        rank, world = dist.get_rank(), dist.get_world_size()
+        t = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            t = torch.frombuffer(bytearray(cls.unique_id()), dtype=torch.uint8).clone()
+        t = t.to("cuda:%d" % device)
+        dist.broadcast(t, src=0)
+        return cls(rank, world, device, bytes(t.cpu().numpy().tobytes()))
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().ygzorb_comm_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def launch_count(self):
+        return int(lib().ygzorb_comm_launch_count(self.h))
+
+    def hamming_knn2_sharded(self, matcher, q_ptr, nq_total, t_ptr, nt, ratio, th, flags, idx_ptr, d1_ptr, d2_ptr, match_ptr):
+        check(lib().ygzorb_hamming_knn2_sharded(self.h, matcher.h, q_ptr, nq_total, t_ptr, nt, ratio, th, flags, idx_ptr, d1_ptr,
+                                                d2_ptr, match_ptr))
+
+    def extract_batch_sharded(self, ex, frames_ptr, n_total, w, h, stride, frame_stride, flags, cap, chunk, counts_ptr, off_ptr,
+                              kps_ptr, desc_ptr):
+        check(lib().ygzorb_extract_batch_sharded(self.h, ex.h, frames_ptr, n_total, w, h, stride, frame_stride, flags, cap, chunk,
+                                                 counts_ptr, off_ptr, kps_ptr, desc_ptr))
+
+
 NOALLOC_SCRATCH_BYTES = 8 * 1024 * 1024   # YGZORB_NOALLOC_SCRATCH_BYTES
 NOALLOC_MAX_QUERIES = 600000              # YGZORB_NOALLOC_MAX_QUERIES
 

@@ -52,3 +52,40 @@ def _worker(rank, world, port, n):
 @pytest.mark.parametrize("world,n", [(2, 1001), (3, 10)])
 def test_gather_rows_gloo(world, n):
     mp.spawn(_worker, args=(world, _free_port(), n), nprocs=world, join=True)
+
+
+def _ragged_worker(rank, world, port, n, cap):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from ygz import Y
+        b, e = sharding.shard_range(n, rank, world)
+        assert (b, e) == Y.shard_range(n, rank, world)            # the library's rule (ygzorb_shard_range) == the host mirror
+        rng = np.random.default_rng(1234)                          # same stream on every rank: the global truth
+        counts_all = rng.integers(0, cap + 1, size=n).astype(np.int32)
+        counts_all[::5] = 0
+        rows_all = [np.stack([np.full(c, f, np.int32), np.arange(c, dtype=np.int32)], 1) for f, c in enumerate(counts_all)]
+        local_rows = [rows_all[f] for f in range(b, e)]
+        payload = torch.from_numpy(np.concatenate(local_rows) if local_rows else np.zeros((0, 2), np.int32))
+        res = sharding.gather_ragged(torch.from_numpy(counts_all[b:e].copy()), payload, n, cap)
+        if rank == 0:
+            counts, off, rows = res
+            assert np.array_equal(counts.numpy(), counts_all)
+            for r in range(world):
+                rb, re = sharding.shard_range(n, r, world)
+                if re > rb:
+                    assert int(off[rb]) == rb * cap                 # a rank's region starts at its first frame's fixed-stride slot
+            for f in range(n):
+                o, c = int(off[f]), int(counts_all[f])
+                assert np.array_equal(rows[o:o + c].numpy(), rows_all[f])
+        else:
+            assert res is None
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n,cap", [(2, 37, 6), (3, 4, 3)])
+def test_counts_then_payload_gather_layout_gloo(world, n, cap):
+    """The gather layout of ygzorb_extract_batch_sharded (counts first, then the packed ragged payload; per-rank regions),
+    world size 2 and 3 on CPU."""
+    mp.spawn(_ragged_worker, args=(world, _free_port(), n, cap), nprocs=world, join=True)
