@@ -133,6 +133,20 @@ int ygzorb_get_pyramid_level(ygzorb_extractor *ex, int frame, int level, uint8_t
 /* All levels of one frame, packed back to back (continuous each), into dst (sum of lw*lh bytes). */
 int ygzorb_get_pyramid(ygzorb_extractor *ex, int frame, uint8_t *dst);
 
+/* Live tracking (one frame per call): the host buffer that receives mvImagePyramid.  Once set (NULL removes it), every
+ * ygzorb_extract_batch / ygzorb_compute_pyramid_batch call with n_frames == 1 copies all levels of the frame, continuous and back
+ * to back like ygzorb_get_pyramid, to host_dst on the download stream right after the pyramid kernels, i.e. while FAST, the
+ * quadtree, the blur and the descriptors run; the data is complete when the call returns (or after ygzorb_extractor_sync with
+ * YGZORB_NO_SYNC).  host_dst must hold the sum of lw*lh bytes and should be page-locked (ygzorb_host_alloc).  Replaces the
+ * separate ygzorb_get_pyramid round trip in Frame::ComputeImagePyramid's clone (src/Frame.cc:807-813). */
+int ygzorb_extractor_set_pyramid_sink(ygzorb_extractor *ex, uint8_t *host_dst);
+
+/* Page-locked host memory (cudaHostAlloc / cudaFreeHost) for the buffers a caller hands to the host-pointer entry points:
+ * copies from and to it run at the full rate of the link and asynchronously.  No reference counterpart; the host classes keep
+ * their staging (the pyramid slab behind mvImagePyramid, src/Frame.cc:810-813 copies out of it) in such memory. */
+int ygzorb_host_alloc(size_t bytes, void **out);
+void ygzorb_host_free(void *p);
+
 /* Parity-test taps, valid after a call with YGZORB_KEEP_STAGES: the 7x7 sigma-2 blurred level
  * (src/ORBextractor.cc:1009-1010) and the per-cell FAST candidates of a level before the quadtree
  * (vToDistributeKeys, :747-781; x,y relative to (16,16) like the reference; UNORDERED — sort by

@@ -283,6 +283,9 @@ struct Extractor {
     int4 *dsoCentre = nullptr; size_t dsoCentreBytes = 0;
     ygzorb_keypoint *dsoKps = nullptr; size_t dsoKpsBytes = 0;
     uint8_t *dsoDesc = nullptr; size_t dsoDescBytes = 0;
+    // ygzorb_extractor_set_pyramid_sink: host slab that receives the pyramid of single-frame calls on the download stream
+    uint8_t *pyrSink = nullptr;
+    cudaEvent_t pyrReady = nullptr, pyrCopied = nullptr;
     long long launches = 0;
     bool profiling = false;
     cudaEvent_t ev[8] = {};
@@ -399,6 +402,24 @@ static int runPyramid(Extractor *ex, int n) {
     return 0;
 }
 
+// Single-frame calls with a pyramid sink: the levels go to the host on the download stream while FAST / quadtree / blur /
+// descriptors run (the reference's callers read mvImagePyramid right after operator(), src/Frame.cc:810-813).
+static int sinkPyramid(Extractor *ex, int n) {
+    if (!ex->pyrSink || n != 1) return 0;
+    YGZ_CUDA(cudaEventRecord(ex->pyrReady, ex->stream));
+    YGZ_CUDA(cudaStreamWaitEvent(ex->d2h, ex->pyrReady, 0));
+    size_t off = 0;
+    for (int l = 0; l < ex->G.nlevels; l++) {
+        const LevelGeom &L = ex->G.lv[l];
+        const uint8_t *src = l == 0 ? ex->B.in : ex->B.pyr + L.off;
+        YGZ_CUDA(cudaMemcpy2DAsync(ex->pyrSink + off, L.w, src, L.pitch, L.w, L.h, cudaMemcpyDeviceToHost, ex->d2h));
+        off += (size_t)L.w * L.h;
+    }
+    YGZ_CUDA(cudaEventRecord(ex->pyrCopied, ex->d2h));
+    YGZ_CUDA(cudaStreamWaitEvent(ex->stream, ex->pyrCopied, 0));   // level 0's staging slot and the slab are reused by later work of this stream
+    return 0;
+}
+
 #define YGZ_MARK(i) do { if (ex->profiling) YGZ_CUDA(cudaEventRecord(ex->ev[i], ex->stream)); } while (0)
 
 // Kernels of one chunk (its input already uploaded into `slot` when it comes from the host).
@@ -417,6 +438,19 @@ static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int 
     runPyramid(ex, n);
     ex->B.pdl = pdl;
     YGZ_MARK(2);
+    const bool sink = ex->pyrSink && n == 1;
+    if (sink) {   // the copies start now; the stream takes their completion in only at the end of the chunk
+        YGZ_CUDA(cudaEventRecord(ex->pyrReady, ex->stream));
+        YGZ_CUDA(cudaStreamWaitEvent(ex->d2h, ex->pyrReady, 0));
+        size_t off = 0;
+        for (int l = 0; l < ex->G.nlevels; l++) {
+            const LevelGeom &L = ex->G.lv[l];
+            const uint8_t *src = l == 0 ? ex->B.in : ex->B.pyr + L.off;
+            YGZ_CUDA(cudaMemcpy2DAsync(ex->pyrSink + off, L.w, src, L.pitch, L.w, L.h, cudaMemcpyDeviceToHost, ex->d2h));
+            off += (size_t)L.w * L.h;
+        }
+        YGZ_CUDA(cudaEventRecord(ex->pyrCopied, ex->d2h));
+    }
     ex->launches += launchFast(ex->G, ex->B, n, ex->stream);
     YGZ_MARK(3);
     ex->launches += launchQuadtree(ex->G, ex->B, n, ex->stream);
@@ -431,6 +465,7 @@ static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int 
     ex->launches += launchDescribe(ex->G, ex->B, n, cap, oc, ok, od, ex->stream);
     ex->B.pdl = 0;
     YGZ_MARK(6);
+    if (sink) YGZ_CUDA(cudaStreamWaitEvent(ex->stream, ex->pyrCopied, 0));   // slot and slab are reused only after the copies
     if (!inDev) YGZ_CUDA(cudaEventRecord(ex->inFree[slot], ex->stream));   // IC_Angle was the last reader of level 0
     if (!outDev) {   // drain on the download stream so that the next chunk's kernels overlap it
         YGZ_CUDA(cudaEventRecord(ex->outReady[os], ex->stream));
@@ -532,6 +567,8 @@ int ygzorb_extractor_create(const ygzorb_params *params, int max_w, int max_h, i
         for (cudaEvent_t *pe : evs) if (e == cudaSuccess) e = cudaEventCreateWithFlags(pe, cudaEventDisableTiming);
     }
     for (int i = 0; i < 8 && e == cudaSuccess; i++) e = cudaEventCreate(&ex->ev[i]);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ex->pyrReady, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ex->pyrCopied, cudaEventDisableTiming);
     if (e != cudaSuccess) { ygzorb_extractor_destroy((ygzorb_extractor *)ex); return cudaFail(e, "extractor_create", __FILE__, __LINE__); }
     *out = (ygzorb_extractor *)ex;
     return 0;
@@ -549,6 +586,8 @@ void ygzorb_extractor_destroy(ygzorb_extractor *h) {
                     ex->dMap1, ex->dMap2, ex->dUndist};
     for (void *p : bufs) if (p) cudaFree(p);
     for (int i = 0; i < 8; i++) if (ex->ev[i]) cudaEventDestroy(ex->ev[i]);
+    if (ex->pyrReady) cudaEventDestroy(ex->pyrReady);
+    if (ex->pyrCopied) cudaEventDestroy(ex->pyrCopied);
     for (int sl = 0; sl < 2; sl++) {
         cudaEvent_t evs[] = {ex->outReady[sl], ex->outFree[sl]};
         for (cudaEvent_t e : evs) if (e) cudaEventDestroy(e);
@@ -822,6 +861,7 @@ int ygzorb_compute_pyramid_batch(ygzorb_extractor *h, const uint8_t *frames, int
     if ((rc = bindInput(ex, frames, w, hgt, frame_stride, inDev, slot))) return rc;
     if ((rc = applyUndistort(ex, n_frames, w, hgt, inDev ? stride : w))) return rc;
     runPyramid(ex, n_frames);
+    if ((rc = sinkPyramid(ex, n_frames))) return rc;
     if (!inDev) YGZ_CUDA(cudaEventRecord(ex->inFree[slot], ex->stream));
     YGZ_CUDA(cudaGetLastError());
     ex->lastFrames = n_frames; ex->stagesValid = false;
@@ -866,6 +906,25 @@ int ygzorb_get_pyramid(ygzorb_extractor *h, int frame, uint8_t *dst) {
     }
     YGZ_CUDA(cudaStreamSynchronize(ex->stream));
     return 0;
+}
+
+int ygzorb_extractor_set_pyramid_sink(ygzorb_extractor *h, uint8_t *host_dst) {
+    Extractor *ex = (Extractor *)h;
+    if (!ex) return argFail("null extractor");
+    YGZ_CUDA(cudaSetDevice(ex->device));
+    YGZ_CUDA(cudaStreamSynchronize(ex->d2h));
+    ex->pyrSink = host_dst;
+    return 0;
+}
+
+int ygzorb_host_alloc(size_t bytes, void **out) {
+    if (!out || bytes == 0) return argFail("bad argument");
+    YGZ_CUDA(cudaHostAlloc(out, bytes, cudaHostAllocDefault));
+    return 0;
+}
+
+void ygzorb_host_free(void *p) {
+    if (p) cudaFreeHost(p);
 }
 
 int ygzorb_get_blurred_level(ygzorb_extractor *h, int frame, int level, uint8_t *dst) {

@@ -31,14 +31,54 @@ ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int
         fail("ygzorb_extractor_tables");
 }
 
-ORBextractor::~ORBextractor() { ygzorb_extractor_destroy(mHandle); }
+ORBextractor::~ORBextractor() {
+    ygzorb_extractor_destroy(mHandle);
+    ygzorb_host_free(mPyrSlab);
+    ygzorb_host_free(mStage);
+}
 
-void ORBextractor::downloadPyramid(int w, int h) {
-    std::vector<int> lw(nlevels), lh(nlevels);
-    if (ygzorb_extractor_level_sizes(mHandle, w, h, lw.data(), lh.data()) != 0) fail("ygzorb_extractor_level_sizes");
+// Page-locked staging of one call: [image w*h][keypoints cap*28][descriptors cap*32].  The caller's cv::Mat / std::vector are
+// pageable; one memcpy into / out of this block costs less than a pageable cudaMemcpy's own staging, and lets every transfer
+// of the call run asynchronously beside the kernels.
+void ORBextractor::ensureStage(size_t imageBytes, int cap) {
+    const size_t need = ((imageBytes + 255) & ~(size_t)255) + (size_t)cap * (sizeof(ygzorb_keypoint) + 32) + 256;
+    if (need > mStageBytes) {
+        ygzorb_host_free(mStage);
+        mStage = nullptr; mStageBytes = 0;
+        void *p = nullptr;
+        if (ygzorb_host_alloc(need, &p) != 0) fail("ygzorb_host_alloc");
+        mStage = (uint8_t *)p; mStageBytes = need;
+    }
+    mStageKps = (ygzorb_keypoint *)(mStage + ((imageBytes + 255) & ~(size_t)255));
+    mStageDesc = (uint8_t *)(mStageKps + cap);
+    mStageCount = (int32_t *)(mStageDesc + (size_t)cap * 32 + ((4 - ((size_t)cap * 32) % 4) % 4));
+}
+
+// ComputePyramid's visible effect (:1129-1150): mvImagePyramid holds the levels.  They arrive in a page-locked slab through the
+// extractor's pyramid sink (copied on the download stream while the rest of the extraction runs); the Mats are headers over it
+// (continuous, step == cols), valid until the next call on this extractor like the reference's own mvImagePyramid.  Frame
+// deep-copies them (src/Frame.cc:810-813).
+void ORBextractor::preparePyramidSink(int w, int h) {
+    mLw.resize(nlevels); mLh.resize(nlevels);
+    if (ygzorb_extractor_level_sizes(mHandle, w, h, mLw.data(), mLh.data()) != 0) fail("ygzorb_extractor_level_sizes");
+    size_t total = 0;
+    for (int l = 0; l < nlevels; l++) total += (size_t)mLw[l] * mLh[l];
+    if (total > mPyrSlabBytes) {
+        ygzorb_extractor_set_pyramid_sink(mHandle, nullptr);
+        ygzorb_host_free(mPyrSlab);
+        mPyrSlab = nullptr; mPyrSlabBytes = 0;
+        void *p = nullptr;
+        if (ygzorb_host_alloc(total, &p) != 0) fail("ygzorb_host_alloc");
+        mPyrSlab = (uint8_t *)p; mPyrSlabBytes = total;
+    }
+    if (ygzorb_extractor_set_pyramid_sink(mHandle, mPyrSlab) != 0) fail("ygzorb_extractor_set_pyramid_sink");
+}
+
+void ORBextractor::downloadPyramid(int /*w*/, int /*h*/) {   // the sink has been filled by the call that just returned
+    size_t off = 0;
     for (int l = 0; l < nlevels; l++) {
-        mvImagePyramid[l].create(lh[l], lw[l], cv::CV_8UC1);
-        if (ygzorb_get_pyramid_level(mHandle, 0, l, mvImagePyramid[l].data) != 0) fail("ygzorb_get_pyramid_level");
+        mvImagePyramid[l] = cv::Mat(mLh[l], mLw[l], cv::CV_8UC1, mPyrSlab + off, (size_t)mLw[l]);
+        off += (size_t)mLw[l] * mLh[l];
     }
 }
 
@@ -51,7 +91,10 @@ void ORBextractor::SetUndistortMaps(const cv::Mat &map1, const cv::Mat &map2) {
 
 void ORBextractor::ComputePyramid(cv::Mat image) {
     if (image.empty()) return;
-    if (ygzorb_compute_pyramid_batch(mHandle, image.data, 1, image.cols, image.rows, (int)image.step, 0, 0) != 0)
+    preparePyramidSink(image.cols, image.rows);
+    ensureStage((size_t)image.cols * image.rows, 1);
+    for (int r = 0; r < image.rows; r++) std::memcpy(mStage + (size_t)r * image.cols, image.ptr(r), (size_t)image.cols);
+    if (ygzorb_compute_pyramid_batch(mHandle, mStage, 1, image.cols, image.rows, image.cols, 0, 0) != 0)
         fail("ygzorb_compute_pyramid_batch");
     downloadPyramid(image.cols, image.rows);
 }
@@ -62,11 +105,12 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
     cv::Mat image = _image.getMat();
     const int cap = ygzorb_extractor_max_keypoints(mHandle, image.cols, image.rows);
     if (cap < 0) fail("ygzorb_extractor_max_keypoints");
-    mKpBuf.resize(cap); mDescBuf.resize((size_t)cap * 32);
-    int32_t n = 0;
-    if (ygzorb_extract_batch(mHandle, image.data, 1, image.cols, image.rows, (int)image.step, 0, 0, cap, &n, mKpBuf.data(),
-                             mDescBuf.data()) != 0)
+    preparePyramidSink(image.cols, image.rows);
+    ensureStage((size_t)image.cols * image.rows, cap);
+    for (int r = 0; r < image.rows; r++) std::memcpy(mStage + (size_t)r * image.cols, image.ptr(r), (size_t)image.cols);
+    if (ygzorb_extract_batch(mHandle, mStage, 1, image.cols, image.rows, image.cols, 0, 0, cap, mStageCount, mStageKps, mStageDesc) != 0)
         fail("ygzorb_extract_batch");
+    const int32_t n = *mStageCount;
     downloadPyramid(image.cols, image.rows);                          // ComputePyramid(image) side effect (:979)
     _keypoints.clear();
     if (n == 0) { _descriptors.release(); return; }                   // :990-991
@@ -74,8 +118,8 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
     cv::Mat descriptors = _descriptors.getMat();
     _keypoints.resize(n);
     static_assert(sizeof(cv::KeyPoint) == sizeof(ygzorb_keypoint), "layout");
-    std::memcpy((void *)_keypoints.data(), mKpBuf.data(), (size_t)n * sizeof(ygzorb_keypoint));
-    for (int i = 0; i < n; i++) std::memcpy(descriptors.ptr(i), &mDescBuf[(size_t)i * 32], 32);
+    std::memcpy((void *)_keypoints.data(), mStageKps, (size_t)n * sizeof(ygzorb_keypoint));
+    for (int i = 0; i < n; i++) std::memcpy(descriptors.ptr(i), mStageDesc + (size_t)i * 32, 32);
 }
 
 void ORBextractor::operator()(Frame *frame, std::vector<cv::KeyPoint> &_keypoints, cv::OutputArray _descriptors,

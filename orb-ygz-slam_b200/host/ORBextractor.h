@@ -51,6 +51,8 @@ public:
 
 protected:
     void downloadPyramid(int w, int h);
+    void preparePyramidSink(int w, int h);
+    void ensureStage(size_t imageBytes, int cap);
     int nfeatures;
     double scaleFactor;
     int nlevels;
@@ -62,6 +64,11 @@ protected:
     int32_t mnGridSize = -1;                              // :191, dynamic grid size of the DSO keypoint mode
     std::vector<ygzorb_keypoint> mKpBuf;
     std::vector<uint8_t> mDescBuf;
+    uint8_t *mPyrSlab = nullptr;                          // page-locked slab behind mvImagePyramid
+    size_t mPyrSlabBytes = 0;
+    std::vector<int> mLw, mLh;                            // level sizes of the current image size
+    uint8_t *mStage = nullptr; size_t mStageBytes = 0;    // page-locked staging of one call (image in, keypoints + descriptors out)
+    ygzorb_keypoint *mStageKps = nullptr; uint8_t *mStageDesc = nullptr; int32_t *mStageCount = nullptr;
 };
 
 }  // namespace ygz

@@ -27,6 +27,7 @@ class YgzError(RuntimeError):
 
 
 _lib = None
+_live = []   # weak references to every open handle object (Extractor, Matcher, Comm, ...): close_all() for an orderly shutdown
 
 
 def lib():
@@ -56,6 +57,22 @@ def lib():
     return _lib
 
 
+def _track(obj):
+    import weakref
+    _live.append(weakref.ref(obj))
+
+
+def close_all():
+    """Closes every handle still open, in reverse creation order.  Scripts call it before they return so that handles (and their
+    CUDA streams) go before the interpreter tears down whatever else holds device or pinned memory — the order an embedder gets
+    when the handles are members destroyed first."""
+    for r in reversed(_live):
+        o = r()
+        if o is not None and getattr(o, "h", None):
+            o.close()
+    del _live[:]
+
+
 def check(rc):
     if rc < 0:
         raise YgzError("ygzorb error %d: %s" % (rc, lib().ygzorb_last_error().decode()))
@@ -79,6 +96,7 @@ class Extractor:
         h = C.c_void_p()
         check(lib().ygzorb_extractor_create(C.byref(self.params), 0, 0, max_batch, device, C.byref(h)))
         self.h = h
+        _track(self)
 
     def close(self):
         if getattr(self, "h", None):
@@ -299,6 +317,7 @@ class Pyramid:
             hh = np.array([a.shape[0] for a in imgs], np.int32)
             check(L.ygzorb_pyramid_create(device, ptrs, _ptr(w), _ptr(hh), _ptr(w), len(imgs), 0, C.byref(h)))
         self.h = h
+        _track(self)
 
     def sizes(self):
         n = C.c_int32()
@@ -420,6 +439,7 @@ class Matcher:
         L.ygzorb_measure_popc_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         check(L.ygzorb_matcher_create(device, C.byref(h)))
         self.h = h
+        _track(self)
 
     def close(self):
         if getattr(self, "h", None):
@@ -813,6 +833,7 @@ class Comm:
             idp = C.cast(self._id, C.c_void_p)
         check(L.ygzorb_comm_create_rank(idp, rank, world, device, C.byref(h)))
         self.h = h
+        _track(self)
 
     @staticmethod
     def unique_id():

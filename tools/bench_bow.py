@@ -99,7 +99,8 @@ def main():
             "cpu_baseline": cpu, "parity_vs_reference_sample": "bit-exact" if cpu else "not checked (no oracle/_ref)",
             "hamming_pairs_per_s": F * N * 60 / (ms * 1e-3)}
     print(json.dumps(line))
-    os._exit(0)
+    torch.cuda.synchronize()
+    Y.close_all()   # orderly shutdown: handles first, then a normal interpreter exit (exit hooks run)
 
 
 if __name__ == "__main__":

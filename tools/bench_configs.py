@@ -33,7 +33,7 @@ def setup():
     return rank, local, world, dev
 
 
-_KEEP = []   # handles and pinned buffers stay alive until os._exit (pinned frees record events on the handles' streams)
+_KEEP = []   # handles and pinned buffers stay alive until the orderly shutdown at the end of main()
 
 
 def timed_gather(fn, dev):
@@ -256,10 +256,9 @@ def main():
     torch.cuda.synchronize()
     if world > 1:
         dist.destroy_process_group()
-    # torch's pinned-memory allocator records events on the handles' streams when its buffers are freed at interpreter exit,
-    # i.e. after the handles are gone: leave without running destructors (as bench.py does)
     sys.stdout.flush(); sys.stderr.flush()
-    os._exit(0)
+    torch.cuda.synchronize()
+    Y.close_all()   # orderly shutdown: handles first, then a normal interpreter exit (exit hooks run)
 
 
 if __name__ == "__main__":

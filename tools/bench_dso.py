@@ -56,7 +56,7 @@ def main():
     print(json.dumps({"bench": "DSO_KEYPOINT extraction, host buffers (wrapper call incl. packing)", "frames_per_call": B,
                       "gpu_frames_per_s": gpu, "cpu_reference_frames_per_s_1thread": cpu, "matches_reference": ok,
                       "keypoints_per_frame": float(np.mean([len(g[0]) for g in got]))}))
-    os._exit(0)
+    Y.close_all()   # orderly shutdown: handles first, then a normal interpreter exit (exit hooks run)
 
 
 if __name__ == "__main__":

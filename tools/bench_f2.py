@@ -105,7 +105,7 @@ def main():
                                       "note": "GPU time includes the Python packing of the batch (wrapper call)"}
     print(json.dumps({"bench": "f2 matcher searches, host buffers through the C ABI", "pairs": B, "keypoints": n, "cpu_threads": cores,
                       "results": out}))
-    os._exit(0)
+    Y.close_all()   # orderly shutdown: handles first, then a normal interpreter exit (exit hooks run)
 
 
 if __name__ == "__main__":

@@ -32,4 +32,5 @@ for pipe in (256, 512):
         ms = e0.elapsed_time(e1) / 10
         print("pipe %d %-6s: %.3f ms per step, %.1fk frames/s (host enqueue %.2f ms per step)" % (pipe, mode, ms, B / ms, t_enq * 100))
     ex.sync(); torch.cuda.synchronize()
-os._exit(0)
+torch.cuda.synchronize()
+Y.close_all()   # orderly shutdown: handles first, then a normal interpreter exit (exit hooks run)
