@@ -110,6 +110,57 @@ def make_frames(n, seed0):
     return synth.frame_batch(W, H, n, seed0=seed0, distinct=8)
 
 
+def make_mixed_frames(n, seed0):
+    import synth
+    def one(seed):   # left half full contrast, right half at 0.18 of it (iniThFAST 20 finds nothing there, minThFAST 7 does), a flat band
+        a = synth.textured_frame(W, H, seed).astype(np.float64)
+        a[:, W // 2:] = 128 + (a[:, W // 2:] - 128) * 0.18
+        a[H // 3: H // 3 + 45, :] = 97
+        return np.clip(np.rint(a), 0, 255).astype(np.uint8)
+    base = [one(seed0 + i) for i in range(min(8, n))]
+    out = np.empty((n, H, W), np.uint8)
+    for i in range(n):
+        out[i] = np.roll(base[i % len(base)], shift=3 * (i // len(base)), axis=0)     # vertical roll: the halves stay halves
+    return out
+
+
+def retry_cell_fraction(img):
+    """Share of the FAST cells of one frame whose iniThFAST pass comes back empty, i.e. which the reference detects a second
+    time at minThFAST (src/ORBextractor.cc:764-770); counted with the oracle's pyramid and OpenCV's own detector on the
+    reference's cell grid (:728-762).  Set-up only."""
+    import cv2
+    import oracle_lib as O
+    import math
+    p = O.params(NFEAT, SCALE, LEVELS, INI_TH, MIN_TH)
+    ini, mn = cv2.FastFeatureDetector_create(INI_TH, True), cv2.FastFeatureDetector_create(MIN_TH, True)
+    cells = retry = empty = 0
+    for lv in O.pyramid(p, img):
+        h, w = lv.shape
+        max_bx, max_by = w - 16, h - 16
+        width, height = float(max_bx - 16), float(max_by - 16)
+        ncols, nrows = int(width / 30), int(height / 30)
+        if ncols <= 0 or nrows <= 0:
+            continue
+        wc, hc = math.ceil(width / ncols), math.ceil(height / nrows)
+        for i in range(nrows):
+            iy = 16 + i * hc
+            if iy >= max_by - 3:
+                continue
+            my = min(iy + hc + 6, max_by)
+            for j in range(ncols):
+                ix = 16 + j * wc
+                if ix >= max_bx - 6:
+                    continue
+                mx = min(ix + wc + 6, max_bx)
+                sub = np.ascontiguousarray(lv[iy:my, ix:mx])
+                cells += 1
+                if not ini.detect(sub):
+                    retry += 1
+                    if not mn.detect(sub):
+                        empty += 1
+    return {"fast_cells_per_frame": cells, "retry_cell_fraction": retry / max(cells, 1), "empty_cell_fraction": empty / max(cells, 1)}
+
+
 def ref_binary():
     return os.path.join(ROOT, "oracle", "_ref", "ygz_ref_orb")
 
@@ -587,6 +638,45 @@ def run_ours(args, rank, local_rank, world):
     stage_ms = {STAGE_NAMES[i]: float(acc[i] / reps) for i in range(7)}
     ms_sbp, _ = timed(search, args.steps)
     stage_ms["search_by_projection"] = ms_sbp / args.steps
+    # ---- second workload, same shapes: frames with low-contrast halves and a flat band (tests/synth.mixed_frame), so that a
+    # large share of the FAST cells takes the minThFAST retry of src/ORBextractor.cc:764-770 (the dense texture above never does);
+    # the buffers of the first workload are refilled in place and the same two timed loops run again
+    mixed = None
+    if not args.no_mixed:
+        mixed_np = make_mixed_frames(B, 500 + 100 * rank)
+        host_in.numpy()[:] = mixed_np
+        dev_in.copy_(host_in)
+        torch.cuda.synchronize()
+        ex.extract_raw(dev_in.data_ptr(), B, W, H, W, W * H, Y.IN_DEVICE | Y.OUT_DEVICE, cap,
+                       d_counts.data_ptr(), d_kps.data_ptr(), d_desc.data_ptr())
+        counts_m = d_counts.cpu().numpy()
+        kps_m = d_kps.cpu().numpy().view(KP_DTYPE).reshape(B, cap)
+        desc_m = d_desc.cpu().numpy()
+        mp_m = make_mappoints(counts_m, kps_m, desc_m, 7 + rank)
+        for k in mp_keys:
+            h_mp[k].numpy()[...] = mp_m[k]
+            d_mp[k].copy_(h_mp[k])
+        torch.cuda.synchronize()
+        for _ in range(3):
+            step_device()
+        ex.sync()
+        ms_mixed, _ = timed(step_device, args.steps)
+        n_kp_m, n_match_m = int(d_counts.sum().item()), int(d_nm.sum().item())
+        for _ in range(2):
+            step_host()
+        ex.sync(); torch.cuda.synchronize()
+        ms_e2e_mixed, _ = timed(step_host, args.steps, drain_host)
+        for S in slots:
+            assert int(S["h_out"]["counts"].sum().item()) == n_kp_m and int(S["h_out"]["nm"].sum().item()) == n_match_m, \
+                "host and device paths disagree on the mixed workload"
+        mixed = {"workload": "same shapes on frames whose right half has 0.18 of the contrast and which carry a flat band",
+                 "value": world * B * args.steps / (ms_mixed * 1e-3), "unit": "frames/s", "ms_per_step": ms_mixed / args.steps,
+                 "e2e": world * B * args.steps / (ms_e2e_mixed * 1e-3), "e2e_ms_per_step": ms_e2e_mixed / args.steps,
+                 "keypoints_per_frame": n_kp_m / B, "mappoint_matches_per_frame": n_match_m / B}
+        if rank == 0:
+            mixed.update(retry_cell_fraction(mixed_np[0]))
+            if world == 1 and not args.no_cpu:
+                mixed["cpu_baseline"] = cpu_baseline_leg(mixed_np, counts_m, kps_m, desc_m, mp_m, budget_s=5.0)
     def shutdown():
         """Orderly teardown, normal interpreter exit afterwards (exit hooks run, the mapped libraries stay visible):
         everything queued on the handles' streams is drained, torch's work is drained, then the handles go — BEFORE any
@@ -618,6 +708,8 @@ def run_ours(args, rank, local_rank, world):
     if world == 1 and not args.no_cpu:
         line["hamming"].update(knn_probe(Y, mt, torch))
         line["cpu_baseline"] = cpu_baseline_leg(frames_np, counts0, kps0, desc0, mp)
+    if mixed is not None:
+        line["mixed"] = mixed
     if sharded is not None:
         line["sharded"] = sharded
     line["native_library"] = Y.LIB_PATH if os.path.exists(Y.LIB_PATH) else None
@@ -700,13 +792,13 @@ def knn_probe(Y, mt, torch):
                      "frac_of_popc_peak": pairs * 8 / peak, "matches": int((out[3] >= 0).sum().item())}}
 
 
-def cpu_baseline_leg(frames_np, counts, kps, desc, mp):
+def cpu_baseline_leg(frames_np, counts, kps, desc, mp, budget_s=12.0):
     """The reference's CPU path on the box's host cores, bounded sample of the same workload."""
     threads = os.cpu_count() or 1
     n = min(reference_sample_frames(threads), len(frames_np))
     sample = frames_np[:n]
     kind, st1 = cpu_extract(sample, threads, 1)
-    repeat = int(max(1, min(200, 12.0 / max(st1["seconds"], 1e-3))))
+    repeat = int(max(1, min(200, budget_s / max(st1["seconds"], 1e-3))))
     kind, st = cpu_extract(sample, threads, repeat)
     sub = {k: np.ascontiguousarray(v[:n]) for k, v in mp.items()}
     sb1 = cpu_search_by_projection(counts[:n].copy(), np.ascontiguousarray(kps[:n]), np.ascontiguousarray(desc[:n]), sub, threads, 1)
@@ -731,6 +823,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=512)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline and kNN legs")
+    ap.add_argument("--no-mixed", action="store_true", help="skip the second (mixed-contrast) workload")
     ap.add_argument("--no-sharded", action="store_true", help="skip the sharded block (configs[3] and [4] through the multi-GPU layer)")
     ap.add_argument("--shard-frames", type=int, default=4096, help="frames of configs[3]")
     ap.add_argument("--shard-queries", type=int, default=1 << 20, help="query = train rows of configs[4]")
