@@ -731,13 +731,13 @@ def build_line(args, world, B, cap, ms, ms_e2e, launches, clocks, stage_ms, n_kp
     achieved = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9
     staged = STAGED_TOTAL * B * args.steps / (ms * 1e-3) / 1e9
     # DRAM traffic of that kernel per launch: dram__bytes_read + dram__bytes_write of one `ncu --set full` capture
-    # (tools/ncu_traffic.py -> profiles/r1_traffic.json, per frame), scaled to this launch's frames
+    # (tools/ncu_traffic.py -> profiles/r2_traffic.json, per frame), scaled to this launch's frames
     traffic, traffic_src = None, None
     try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))
         tk = tj["kernels"]["k_" + dom]
         traffic = (tk["dram_read_bytes_per_frame"] + tk["dram_write_bytes_per_frame"]) * B / launches_per_stage
-        traffic_src = "profiles/r1_traffic.json (%s, %d frames, scaled per frame)" % (tj["report"], tj["frames"])
+        traffic_src = "profiles/r2_traffic.json (%s, %d frames, scaled per frame)" % (tj["report"], tj["frames"])
     except (OSError, KeyError, ValueError):
         pass
     roofline = {"bound": "hbm", "kernel": "k_" + dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",

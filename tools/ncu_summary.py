@@ -15,6 +15,10 @@ want = [("gpu__time_duration.sum", "time"), ("dram__bytes_read.sum", "dram_rd"),
         ("launch__registers_per_thread", "regs"), ("smsp__inst_executed.sum", "warp_inst"),
         ("l1tex__throughput.avg.pct_of_peak_sustained_active", "l1%"),
         ("lts__throughput.avg.pct_of_peak_sustained_elapsed", "l2%"),
+        ("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "alu%"),
+        ("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "fma%"),
+        ("sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "lsu%"),
+        ("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed", "smem%"),
         ("launch__grid_size", "grid"), ("launch__block_size", "block")]
 idx = {h: i for i, h in enumerate(H)}
 lines = []
@@ -29,7 +33,13 @@ for r in rows[2:]:
     for m, _ in want:
         if m in idx:
             u = rows[1][idx[m]]
-            vals.append(r[idx[m]] + (" " + u if u and u not in ("%",) else ""))
+            v = r[idx[m]]
+            try:
+                v = "%.1f" % float(v) if "." in v else v
+            except ValueError:
+                pass
+            u = {"register/thread": "", "inst": ""}.get(u, u)
+            vals.append(v + (" " + u if u and u not in ("%",) else ""))
         else:
             vals.append("-")
     lines.append("| " + name + " | " + " | ".join(vals) + " |")
