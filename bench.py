@@ -165,13 +165,14 @@ def ref_binary():
     return os.path.join(ROOT, "oracle", "_ref", "ygz_ref_orb")
 
 
-def run_reference_cpu(frames, threads, repeat):
+def run_reference_cpu(frames, threads, repeat, nfeatures=NFEAT):
     """Times the reference's own ORBextractor.cc (oracle/_ref/ygz_ref_orb) on host cores."""
     import tempfile
     with tempfile.TemporaryDirectory() as td:
         fin = os.path.join(td, "in.u8")
         frames.tofile(fin)
-        cmd = [ref_binary(), "--in", fin, "--w", str(W), "--h", str(H), "--n", str(len(frames)), "--nfeatures", str(NFEAT),
+        cmd = [ref_binary(), "--in", fin, "--w", str(frames.shape[2]), "--h", str(frames.shape[1]), "--n", str(len(frames)),
+               "--nfeatures", str(nfeatures),
                "--scale", repr(SCALE), "--levels", str(LEVELS), "--ini", str(INI_TH), "--min", str(MIN_TH),
                "--repeat", str(repeat), "--threads", str(threads)]
         out = subprocess.run(cmd, capture_output=True, text=True, check=True).stdout
@@ -384,6 +385,13 @@ def sharded_block(args, Y, torch, dist, rank, local_rank, world, dev):
             "h2d_GBps_all_ranks": n_total * w * h / (ms * 1e-3) / 1e9,
             "ms_device_resident": ms_dev, "frames_per_s_device_resident": n_total / (ms_dev * 1e-3),
             "gathered_bytes": total_kp * 60 + 4 * n_total, "keypoints_per_frame": total_kp / n_total, "chunk_frames": chunk, "scaling": "strong"}
+        if world == 1 and not args.no_cpu and os.path.exists(ref_binary()):
+            # the reference's own ORBextractor.cc on a bounded sample of the same frames, all host threads (a few seconds)
+            threads = os.cpu_count() or 1
+            ns = min(n, max(4 * threads, 32))
+            r = run_reference_cpu(host.numpy()[:ns], threads, 1, nfeatures=nf)
+            out["config3"]["cpu_baseline"] = {"value": r["frames_per_s"], "unit": "frames/s", "cores": threads, "kind": "reference",
+                                              "sample": "%d of the 1280x720 frames x 1 pass = reference ORBextractor.cc (%.1f s)" % (ns, r["seconds"])}
     del host, d_frames, g_kps, g_desc, l_kps, l_desc
     ex.close()
     # ---- configs[4]: brute-force Hamming kNN-2 + ratio 0.6, nq x nt 256-bit rows, query-sharded; train rows broadcast from rank 0
@@ -430,6 +438,18 @@ def sharded_block(args, Y, torch, dist, rank, local_rank, world, dev):
                         "broadcast from rank 0 and (idx, d1, d2, match) gathered on rank 0 inside the timed region" % (nq, nt, world),
             "ms": ms, "pairs_per_s": pairs, "queries_per_s": nq / (ms * 1e-3), "matches": matches, "popc_peak_per_s_per_gpu": peak,
             "frac_of_popc_peak": pairs * 8 / (peak * world), "scaling": "strong"}
+        if world == 1 and not args.no_cpu:
+            # CPU figure beside it: the oracle port of the same rule (DescriptorDistance's bit trick per pair, top-2 + ratio),
+            # threads over queries, on a bounded sample (sq x st rows) of the same arrays
+            import oracle_lib as O
+            threads = os.cpu_count() or 1
+            sq, st = min(nq, 4096 * threads), min(nt, 65536)
+            qh, th_ = query[:sq].cpu().numpy(), train[:st].cpu().numpy()
+            t0 = time.perf_counter()
+            O.hamming_knn2(qh, th_, 0.6, 50, threads=threads)
+            sec = time.perf_counter() - t0
+            out["config4"]["cpu_baseline"] = {"value": sq * st / sec, "unit": "pairs/s", "cores": threads, "kind": "port",
+                                              "sample": "%d x %d rows of the same arrays, oracle port (%.1f s)" % (sq, st, sec)}
     mt.close()
     comm.close()
     return out
