@@ -757,10 +757,20 @@ __device__ __forceinline__ void cpAsync16(void *smemDst, const void *gmemSrc) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smemDst)), "l"(gmemSrc));
 }
 
-template <bool PDL> __global__ void __launch_bounds__(kBlurThreads, 5) k_blur(const __grid_constant__ FrameGeom G, const DevBuffers B) {
+constexpr int kBlurPairs = kBlurRawRows / 2;    // 19 raw-row pairs (rows 2m, 2m+1)
+static_assert(kBlurRawRows % 2 == 0 && kBlurTH % 8 == 0 && kBlurTW == 256, "k_blur thread mapping");
+
+// byte 2 of four 24-bit accumulators -> one word of four output bytes
+__device__ __forceinline__ uint32_t packByte2(uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3) {
+    return __byte_perm(__byte_perm(a0, a1, 0x0062), __byte_perm(a2, a3, 0x0062), 0x5410);
+}
+
+template <bool PDL> __global__ void __launch_bounds__(kBlurThreads, 6) k_blur(const __grid_constant__ FrameGeom G, const DevBuffers B) {
     if (PDL) pdlEnter(B);
     __shared__ __align__(16) uint8_t raw[kBlurRawRows * kBlurRawPitch];
-    __shared__ __align__(16) uint2 hs[kBlurRawRows * (kBlurTW / 4)];   // 4 x u16 horizontal sums
+    // horizontal sums, stored as ROW PAIRS: hs[m][g] = four columns (4g .. 4g+3) of h[row 2m] | h[row 2m+1] << 16 — the
+    // operand form of DP2A in the vertical pass, so that pass needs no re-packing
+    __shared__ __align__(16) uint4 hs[kBlurPairs * (kBlurTW / 4)];
     const int f = blockIdx.y, tid = threadIdx.x;
     const int2 te = __ldg(B.tabs + G.tileTab + blockIdx.x);            // host-built tile table
     const int level = te.x >> 24, x0 = te.x & 0xfff, y0 = (te.x >> 12) & 0xfff;
@@ -774,13 +784,21 @@ template <bool PDL> __global__ void __launch_bounds__(kBlurThreads, 5) k_blur(co
     const bool aligned = ((L.pitch & 15) == 0) && ((reinterpret_cast<uintptr_t>(img) & 15) == 0);
     if (aligned && L.w >= 8 && L.h >= 8) {
         const int hm = 2 * (L.h - 1), wm = 2 * (L.w - 1);
-        for (int i = tid; i < kBlurRawRows * kChunks; i += kBlurThreads) {
-            const int r = i / kChunks, c = i - r * kChunks;
-            const int gx = x0 - 16 + 16 * c;
-            if (gx >= 0 && gx + 16 <= L.w) {
-                int sy = abs(y0 + r - 3);
-                sy = max(min(sy, hm - sy), 0);                       // one reflection: the halo (3) is shorter than the image
-                cpAsync16(&raw[r * kBlurRawPitch + 16 * c], img + (long long)sy * L.pitch + gx);
+        // thread = (chunk column c, row r0 + 14 i): 252 threads cover 14 rows per step, no division in the loop
+        constexpr int kRowsPerStep = kBlurThreads / kChunks;   // 14
+        const int r0 = tid / kChunks, c = tid - r0 * kChunks;
+        const int gx = x0 - 16 + 16 * c;
+        if (r0 < kRowsPerStep && gx >= 0 && gx + 16 <= L.w) {
+            const uint8_t *src = img + gx;
+            uint8_t *dst = &raw[r0 * kBlurRawPitch + 16 * c];
+#pragma unroll
+            for (int i = 0; i < (kBlurRawRows + kRowsPerStep - 1) / kRowsPerStep; i++) {
+                const int r = r0 + kRowsPerStep * i;
+                if (r < kBlurRawRows) {
+                    int sy = abs(y0 + r - 3);
+                    sy = max(min(sy, hm - sy), 0);                   // one reflection: the halo (3) is shorter than the image
+                    cpAsync16(dst + i * kRowsPerStep * kBlurRawPitch, src + (long long)sy * L.pitch);
+                }
             }
         }
         // columns the chunks did not bring: [-3, 0) of the image, and [w & ~15, w + 3) clipped to this tile
@@ -811,60 +829,60 @@ template <bool PDL> __global__ void __launch_bounds__(kBlurThreads, 5) k_blur(co
         }
     }
     __syncthreads();
-    // ---- horizontal pass: 4 outputs per thread (columns x .. x+3) from the words w0 = [x-4, x), w1 = [x, x+4),
-    // w2 = [x+4, x+8).  Output k is the dot product of bytes (1+k .. 7+k) of that window with
-    // {18,34,48,56,48,34,18}: two byte-aligned windows (funnel shifts) and two DP4A.
+    // ---- horizontal pass: thread = 4 columns (x .. x+3) of one raw-row PAIR.  Per row the words w0 = [x-4, x),
+    // w1 = [x, x+4), w2 = [x+4, x+8); output k is the dot product of bytes (1+k .. 7+k) of that window with
+    // {18,34,48,56,48,34,18}: two byte-aligned windows (funnel shifts) and two DP4A.  The two rows of the pair are packed
+    // per column (low half = even raw row).  Warps whose 128 columns lie right of the image skip both passes.
     const int tx = tid & 63, tg = tid >> 6;
     const int x = x0 + 4 * tx;
+    const bool live = x0 + 4 * (tx & ~31) < L.w;        // warp-uniform
     constexpr uint32_t kW0 = 18u | (34u << 8) | (48u << 16) | (56u << 24), kW1 = 48u | (34u << 8) | (18u << 16);
-    for (int r = tg; r < kBlurRawRows; r += 4) {
-        const uint32_t *w = reinterpret_cast<const uint32_t *>(&raw[r * kBlurRawPitch + 12 + 4 * tx]);
-        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
-        uint32_t o[4];
+    if (live) {
+        const uint32_t *w = reinterpret_cast<const uint32_t *>(&raw[2 * tg * kBlurRawPitch + 12 + 4 * tx]);
+        uint4 *hd = hs + tg * (kBlurTW / 4) + tx;
 #pragma unroll
-        for (int k = 0; k < 3; k++) {
-            const uint32_t a = __funnelshift_r(w0, w1, 8 * (k + 1)), b = __funnelshift_r(w1, w2, 8 * (k + 1));
-            o[k] = __dp4a(b, kW1, __dp4a(a, kW0, 0u));
+        for (int i = 0; i < (kBlurPairs + 3) / 4; i++) {
+            if (tg + 4 * i < kBlurPairs) {
+                const uint32_t *wa = w + i * (8 * kBlurRawPitch / 4), *wb = wa + kBlurRawPitch / 4;
+                const uint32_t a0 = wa[0], a1 = wa[1], a2 = wa[2], b0 = wb[0], b1 = wb[1], b2 = wb[2];
+                uint32_t o[4];
+#pragma unroll
+                for (int k = 0; k < 3; k++) {
+                    const uint32_t ha = __dp4a(__funnelshift_r(a1, a2, 8 * (k + 1)), kW1, __dp4a(__funnelshift_r(a0, a1, 8 * (k + 1)), kW0, 0u));
+                    const uint32_t hb = __dp4a(__funnelshift_r(b1, b2, 8 * (k + 1)), kW1, __dp4a(__funnelshift_r(b0, b1, 8 * (k + 1)), kW0, 0u));
+                    o[k] = __byte_perm(ha, hb, 0x5410);
+                }
+                o[3] = __byte_perm(__dp4a(a2, kW1, __dp4a(a1, kW0, 0u)), __dp4a(b2, kW1, __dp4a(b1, kW0, 0u)), 0x5410);
+                hd[i * 4 * (kBlurTW / 4)] = make_uint4(o[0], o[1], o[2], o[3]);
+            }
         }
-        o[3] = __dp4a(w2, kW1, __dp4a(w1, kW0, 0u));
-        hs[r * (kBlurTW / 4) + tx] = make_uint2(o[0] | (o[1] << 16), o[2] | (o[3] << 16));
     }
     __syncthreads();
-    // ---- vertical pass: each thread 4 columns x 8 rows over a 14-row register window.  Rows are paired per column
-    // (PRMT) so that one DP2A applies two taps: acc = (18,34).P[k] + (48,56).P[k+2] + (48,34).P[k+4] + (0,18).P[k+5].
-    if (x >= L.w) return;
-    uint8_t *dst = B.blur + (long long)f * B.blurSlab + B.blurOff[level];
+    // ---- vertical pass: thread = 4 columns x 8 output rows (k = 8 tg .. 8 tg + 7), from the 7 row pairs Q[4 tg .. 4 tg + 6].
+    // Output row k covers raw rows k .. k+6.  Even k = 2m: pairs m, m+1, m+2 whole and the low half of m+3; odd k = 2m+1:
+    // the high half of pair m, then m+1, m+2, m+3 whole with the taps shifted by one.  Four DP2A per output either way, the
+    // rounding constant rides in the accumulator, the result is byte 2 of the 24-bit sum.
+    if (!live || x >= L.w) return;
+    uint8_t *dst = B.blur + (long long)f * B.blurSlab + B.blurOff[level] + (long long)(y0 + 8 * tg) * B.blurPitch[level] + x;
     const int dp = B.blurPitch[level];
-    constexpr int kRowsPer = kBlurTH / 4;
-    const int rBase = tg * kRowsPer;
-    uint32_t pr[4][kRowsPer + 5];   // pr[c][j] = h[row j][col c] | h[row j+1][col c] << 16
-    {
-        uint2 prev = hs[rBase * (kBlurTW / 4) + tx];
+    const int nrows = L.h - (y0 + 8 * tg);            // rows of this thread that exist (may be <= 0)
+    uint4 Q[7];
 #pragma unroll
-        for (int j = 0; j < kRowsPer + 5; j++) {
-            const uint2 cur = hs[(rBase + j + 1) * (kBlurTW / 4) + tx];
-            pr[0][j] = __byte_perm(prev.x, cur.x, 0x5410); pr[1][j] = __byte_perm(prev.x, cur.x, 0x7632);
-            pr[2][j] = __byte_perm(prev.y, cur.y, 0x5410); pr[3][j] = __byte_perm(prev.y, cur.y, 0x7632);
-            prev = cur;
-        }
+    for (int j = 0; j < 7; j++) Q[j] = hs[(4 * tg + j) * (kBlurTW / 4) + tx];
+    constexpr uint32_t kE0 = 18u | (34u << 8), kE1 = 48u | (56u << 8), kE2 = 48u | (34u << 8), kE3 = 18u;
+    constexpr uint32_t kO0 = 18u << 8, kO1 = 34u | (48u << 8), kO2 = 56u | (48u << 8), kO3 = 34u | (18u << 8);
+#define YGZ_BLUR_COL(F, W0, W1, W2, W3) \
+    __dp2a_lo(Q[mm + 3].F, W3, __dp2a_lo(Q[mm + 2].F, W2, __dp2a_lo(Q[mm + 1].F, W1, __dp2a_lo(Q[mm].F, W0, 32768u))))
+#pragma unroll
+    for (int mm = 0; mm < 4; mm++) {
+        const uint32_t ev = packByte2(YGZ_BLUR_COL(x, kE0, kE1, kE2, kE3), YGZ_BLUR_COL(y, kE0, kE1, kE2, kE3),
+                                      YGZ_BLUR_COL(z, kE0, kE1, kE2, kE3), YGZ_BLUR_COL(w, kE0, kE1, kE2, kE3));
+        const uint32_t od = packByte2(YGZ_BLUR_COL(x, kO0, kO1, kO2, kO3), YGZ_BLUR_COL(y, kO0, kO1, kO2, kO3),
+                                      YGZ_BLUR_COL(z, kO0, kO1, kO2, kO3), YGZ_BLUR_COL(w, kO0, kO1, kO2, kO3));
+        if (2 * mm < nrows) *reinterpret_cast<uint32_t *>(dst + (2 * mm) * dp) = ev;
+        if (2 * mm + 1 < nrows) *reinterpret_cast<uint32_t *>(dst + (2 * mm + 1) * dp) = od;
     }
-    constexpr uint32_t kV01 = 18u | (34u << 8), kV23 = 48u | (56u << 8), kV45 = 48u | (34u << 8), kV6 = 18u << 8;
-#pragma unroll
-    for (int k = 0; k < kRowsPer; k++) {
-        const int y = y0 + rBase + k;
-        if (y < L.h) {
-            uint32_t out = 0;
-#pragma unroll
-            for (int c = 0; c < 4; c++) {
-                uint32_t acc = __dp2a_lo(pr[c][k], kV01, 32768u);
-                acc = __dp2a_lo(pr[c][k + 2], kV23, acc);
-                acc = __dp2a_lo(pr[c][k + 4], kV45, acc);
-                acc = __dp2a_lo(pr[c][k + 5], kV6, acc);
-                out |= (acc >> 16) << (8 * c);
-            }
-            *reinterpret_cast<uint32_t *>(dst + (long long)y * dp + x) = out;
-        }
-    }
+#undef YGZ_BLUR_COL
 }
 
 int launchBlur(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s) {
