@@ -183,6 +183,73 @@ template <bool PDL> __global__ void __launch_bounds__(256) k_resize(const __grid
     }
 }
 
+// Band variant (the one batches run): CTA = 64 destination columns x nSub sub-tiles of kRzTH destination rows; 256 threads.
+// Per sub-tile the horizontal pass of EVERY source row it touches (rows y0(first dy) .. y1(last dy), about 1.2 x kRzTH + 2 of
+// them) goes to shared memory once, as four 32-bit sums per column group (thread = column group x row slot); the vertical pass
+// then picks its two rows by index (thread = two column groups x row slot).  Against k_resize (register-resident row reuse)
+// this has no data-dependent branches, no table decode in the horizontal pass (the host pre-digests the X table per column
+// group: weights, byte selectors, window offset, shift) and one address update per source row.
+// A column group whose 8-byte window would cross the end of the source row has it slid back on the host (offset - delta,
+// selectors + delta), so the three word loads stay inside the row (the third one is folded onto the second when the slid window
+// ends exactly at the row's last word).
+constexpr int kRzTH = 64, kRzThreads = 256, kRzSlots = 16, kRzMaxBand = 160;
+
+template <bool PDL> __global__ void __launch_bounds__(kRzThreads, 6) k_resize_band(const __grid_constant__ FrameGeom G, const DevBuffers B, int level, int nSub) {
+    if (PDL) pdlEnter(B);
+    extern __shared__ __align__(16) uint2 rzH[];   // [band row][16 column groups]: four 16-bit sums (h >> 4 <= 32640) per group
+    const LevelGeom &D = G.lv[level];
+    const LevelGeom &S = G.lv[level - 1];
+    const int f = blockIdx.z, tid = threadIdx.x;
+    const int cg = tid & 15, slot = tid >> 4;              // horizontal pass mapping
+    const int cp = tid & 7, vslot = tid >> 3;              // vertical pass mapping: column groups cp and cp + 8
+    const int sp = S.pitch;
+    const int2 *tY = B.tabs + D.tabY;
+    // pre-digested X table: per column group {coef[4]}, {sel[4]}, {window word offset, shift, third-word offset, -}
+    const int4 *tg = reinterpret_cast<const int4 *>(B.tabs + D.tabXG) + 3 * (blockIdx.x * 16 + cg);
+    const int4 coef = __ldg(tg), sel = __ldg(tg + 1), misc = __ldg(tg + 2);
+    const uint8_t *srcCol = levelPtr(G, B, f, level - 1) + misc.x;
+    const long long step = (long long)kRzSlots * sp;
+    uint8_t *dst = B.pyr + (long long)f * G.slabBytes + D.off + (blockIdx.x * 16 + cp) * 4;
+    const uint2 *hc = rzH + cp;
+    for (int sub = 0; sub < nSub; sub++) {
+        const int dyBase = (blockIdx.y * nSub + sub) * kRzTH;
+        if (dyBase >= D.h) break;
+        const int dyLast = min(dyBase + kRzTH - 1, D.h - 1);
+        const int yFirst = __ldg(tY + dyBase).x & 0xffff, yLast = (int)((uint32_t)__ldg(tY + dyLast).x >> 16);
+        if (sub > 0) __syncthreads();                      // the previous sub-tile's vertical pass is done with rzH
+        {
+            const uint8_t *p = srcCol + (long long)(yFirst + slot) * sp;
+            uint2 *hd = rzH + slot * 16 + cg;
+#pragma unroll 2
+            for (int y = yFirst + slot; y <= yLast; y += kRzSlots, p += step, hd += kRzSlots * 16) {
+                const uint32_t w0 = __ldg(reinterpret_cast<const uint32_t *>(p)), w1 = __ldg(reinterpret_cast<const uint32_t *>(p + 4));
+                const uint32_t w2 = __ldg(reinterpret_cast<const uint32_t *>(p + misc.z));
+                const uint32_t v0 = __funnelshift_r(w0, w1, misc.y), v1 = __funnelshift_r(w1, w2, misc.y);
+                const uint32_t h0 = __dp2a_lo((uint32_t)coef.x, __byte_perm(v0, v1, sel.x), 0u) >> 4;
+                const uint32_t h1 = __dp2a_lo((uint32_t)coef.y, __byte_perm(v0, v1, sel.y), 0u) >> 4;
+                const uint32_t h2 = __dp2a_lo((uint32_t)coef.z, __byte_perm(v0, v1, sel.z), 0u) >> 4;
+                const uint32_t h3 = __dp2a_lo((uint32_t)coef.w, __byte_perm(v0, v1, sel.w), 0u) >> 4;
+                *hd = make_uint2(h1 * 65536u + h0, h3 * 65536u + h2);
+            }
+        }
+        __syncthreads();
+#pragma unroll 2
+        for (int dy = dyBase + vslot; dy <= dyLast; dy += kRzThreads / 8) {
+            const int2 ty = __ldg(tY + dy);
+            const int y0 = (ty.x & 0xffff) - yFirst, y1 = (int)((uint32_t)ty.x >> 16) - yFirst;
+            const uint32_t b0 = (uint32_t)ty.y << 16, b1 = (uint32_t)ty.y & 0xffff0000u;
+            uint8_t *d = dst + (long long)dy * D.pitch;
+#pragma unroll
+            for (int half = 0; half < 2; half++) {
+                const uint2 a = hc[y0 * 16 + 8 * half], b = hc[y1 * 16 + 8 * half];
+                const uint32_t r0 = (__umulhi(b0, a.x & 0xffffu) + __umulhi(b1, b.x & 0xffffu) + 2u) >> 2, r1 = (__umulhi(b0, a.x >> 16) + __umulhi(b1, b.x >> 16) + 2u) >> 2;
+                const uint32_t r2 = (__umulhi(b0, a.y & 0xffffu) + __umulhi(b1, b.y & 0xffffu) + 2u) >> 2, r3 = (__umulhi(b0, a.y >> 16) + __umulhi(b1, b.y >> 16) + 2u) >> 2;
+                *reinterpret_cast<uint32_t *>(d + 32 * half) = (r3 * 256u + r2) * 65536u + (r1 * 256u + r0);  // padding columns are scratch
+            }
+        }
+    }
+}
+
 int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nFrames, cudaStream_t s) {
     const LevelGeom &D = G.lv[level];
     const LevelGeom &S = G.lv[level - 1];
@@ -191,6 +258,17 @@ int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nF
     const bool rowsAligned = (S.pitch & 3) == 0 &&
                              (level > 1 || ((reinterpret_cast<uintptr_t>(B.in) & 3) == 0 && (B.inFrameStride & 3) == 0));
     const bool word = D.fastResize && !D.area2x && rowsAligned;
+    if (word && D.bandRows > 0 && D.bandRows <= kRzMaxBand) {
+        // sub-tiles per CTA: a whole column strip for batches (the per-thread set-up is paid once per strip), one for small
+        // batches (more CTAs)
+        const int tilesY = (D.h + kRzTH - 1) / kRzTH;
+        const int nSub = (long long)(D.pitch / 64) * nFrames >= 2048 ? tilesY : ((long long)(D.pitch / 64) * nFrames * ((tilesY + 1) / 2) >= 1024 ? 2 : 1);
+        const dim3 bgrid(D.pitch / 64, (tilesY + nSub - 1) / nSub, nFrames);
+        const size_t smem = (size_t)D.bandRows * 16 * sizeof(uint2);
+        if (B.pdl) launchChain(true, k_resize_band<true>, bgrid, dim3(kRzThreads), smem, s, G, B, level, nSub);
+        else k_resize_band<false><<<bgrid, kRzThreads, smem, s>>>(G, B, level, nSub);
+        return 1;
+    }
     if (B.pdl) { if (word) launchChain(true, k_resize<true>, grid, block, 0, s, G, B, level); else launchChain(true, k_resize_generic<true>, grid, block, 0, s, G, B, level); }
     else if (word) k_resize<false><<<grid, block, 0, s>>>(G, B, level);
     else k_resize_generic<false><<<grid, block, 0, s>>>(G, B, level);

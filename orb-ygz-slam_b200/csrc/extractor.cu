@@ -154,9 +154,47 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
                 fast = b0 >= 0 && b1 >= 0 && b0 + b1 == 2048;
             }
             L.fastResize = fast ? 1 : 0;
+            // k_resize_band: source rows touched by a 64-row destination tile (the Y table must be monotone: it is for every
+            // down-scale; checked so that an exotic table falls back to k_resize)
+            L.bandRows = 0;
+            if (fast && G.lv[l - 1].pitch >= 8) {
+                bool mono = true;
+                int band = 0;
+                for (int dy0 = 0; dy0 < L.h && mono; dy0 += 64) {
+                    const int dy1 = std::min(dy0 + 63, L.h - 1);
+                    const int yFirst = Y[dy0].x & 0xffff, yLast = (int)((uint32_t)Y[dy1].x >> 16);
+                    for (int dy = dy0; dy <= dy1 && mono; dy++) {
+                        const int y0 = Y[dy].x & 0xffff, y1 = (int)((uint32_t)Y[dy].x >> 16);
+                        mono = y0 >= yFirst && y1 <= yLast && y0 <= y1;
+                    }
+                    band = std::max(band, yLast - yFirst + 1);
+                }
+                if (mono) L.bandRows = band;
+            }
+            std::vector<int2> XG;
+            if (L.bandRows > 0) {
+                // per column group of 4 destination pixels: {coef[4]}, {sel[4]}, {byte offset of the window's first word,
+                // funnel shift, offset of the third word, 0}
+                const int sp = G.lv[l - 1].pitch;
+                for (int g = 0; g < L.pitch / 4; g++) {
+                    const int2 *e = &X[4 * g];
+                    const int base = e[0].x & 0xffff;
+                    const int bs = std::min(base, sp - 8), delta = base - bs;
+                    int sel[4];
+                    for (int i = 0; i < 4; i++) {
+                        const int d = (e[i].x & 0xffff) - base;
+                        sel[i] = (d | ((d + 1) << 4)) + 0x11 * delta;
+                    }
+                    XG.push_back(make_int2(e[0].y, e[1].y)); XG.push_back(make_int2(e[2].y, e[3].y));
+                    XG.push_back(make_int2(sel[0], sel[1])); XG.push_back(make_int2(sel[2], sel[3]));
+                    XG.push_back(make_int2(bs & ~3, 8 * (bs & 3))); XG.push_back(make_int2((bs & ~3) + 12 <= sp ? 8 : 4, 0));
+                }
+            }
             if (tabs.size() % 2) tabs.push_back(make_int2(0, 0));
             L.tabX = (int)tabs.size(); tabs.insert(tabs.end(), X.begin(), X.end());
             L.tabY = (int)tabs.size(); tabs.insert(tabs.end(), Y.begin(), Y.end());
+            if (tabs.size() % 2) tabs.push_back(make_int2(0, 0));
+            L.tabXG = (int)tabs.size(); tabs.insert(tabs.end(), XG.begin(), XG.end());
         }
         blurPitch[l] = alignUp(L.w, 64);
         blurOff[l] = bOff;

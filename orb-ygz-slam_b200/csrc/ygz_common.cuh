@@ -38,6 +38,8 @@ struct LevelGeom {
     int tabX, tabY;           // offsets of the resize tables (in 8-byte entries)
     int area2x;               // cv::resize switches exact 2x decimation to INTER_AREA
     int fastResize;           // the level's tables satisfy the assumptions of the word-based k_resize
+    int tabXG;                // k_resize_band: pre-digested X table, 3 x int4 per column group (offset in 8-byte entries, 16-byte aligned)
+    int bandRows;             // k_resize_band: most source rows (y0(first) .. y1(last)) any 64-row destination tile touches; 0 = not usable
     int tileStart, tilesX, tilesY;  // blur tiles
 };
 

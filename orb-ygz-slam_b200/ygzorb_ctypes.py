@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libygzorb_cuda.so")
+LIB_PATH = os.environ.get("YGZORB_LIB") or os.path.join(HERE, "libygzorb_cuda.so")   # YGZORB_LIB: kernel experiments only
 
 IN_DEVICE, OUT_DEVICE, KEEP_STAGES, NO_SYNC = 1, 2, 4, 8
 
