@@ -2,11 +2,11 @@
 // direct tracker and the descriptor post-processing of MapPoint (part 4 of the oracle).  Linked into
 // oracle/libygz_oracle.so; used by tests/ only — never by the product.
 //
-// ComputeDistinctiveDescriptors, FindDirectProjection and Align2D are PINNED to the reference's own code (src/MapPoint.cc:211-271,
-// src/ORBmatcher.cc:1525-1602 and src/Align.cc compiled unmodified into oracle/_ref/libygz_ref_match.so; tests/test_ref_match.py,
-// tests/golden/match_golden.npz).  The SparseImgAlign part is PARITY UNPINNED: src/SparseImageAlign.cc needs dynamic-size Eigen,
-// SE3f::exp and the NLLSSolver / robust-cost templates, beyond the fixed-size stand-in of oracle/ref_shim/eigen_lite.h; it is a
-// line-by-line restatement checked against independent numpy re-derivations in tests/test_direct_oracle.py.
+// PINNED to the reference's own code: src/MapPoint.cc:211-271, src/ORBmatcher.cc:1525-1602, src/Align.cc and
+// src/SparseImageAlign.cc (+ include/NLSSolver.h, NLSSolver_impl.hpp) compiled unmodified into oracle/_ref/libygz_ref_match.so
+// (oracle/Makefile target refmatch, oracle/ref_match_api.cpp); tests/test_ref_match.py asserts this file == that library, live and
+// through tests/golden/match_golden.npz, bit for bit (SparseImgAlign: caches, H_, Jres_, chi2, n_meas_ and whole run() calls over
+// levels 5..1 — run() indexes a 6-entry iterations[] with the level, so levels 6 and 7 are undefined behaviour in the reference).
 // Citations are file:line in /root/reference.
 #include <algorithm>
 #include <climits>
@@ -242,13 +242,13 @@ Se3 se3Compose(const Se3 &A, const Se3 &B) {   // A *= B: fastMultiply (translat
     const float ax = A.q[0], ay = A.q[1], az = A.q[2], aw = A.q[3], bx = B.q[0], by = B.q[1], bz = B.q[2], bw = B.q[3];
     float q[4] = {aw * bx + ax * bw + ay * bz - az * by, aw * by + ay * bw + az * bx - ax * bz, aw * bz + az * bw + ax * by - ay * bx,
                   aw * bw - ax * bx - ay * by - az * bz};
-    const float len = std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+    const float len = std::sqrt((q[0] * q[0] + q[1] * q[1]) + (q[2] * q[2] + q[3] * q[3]));   // coeffs().norm(): one packet of four, pairwise
     for (int i = 0; i < 4; i++) R.q[i] = q[i] / len;
     return R;
 }
-Se3 se3Exp(const float *a) {   // a = (upsilon, omega)
+Se3 se3Exp(const float *a) {   // a = (upsilon, omega); Thirdparty/sophus/sophus/se3.hpp:407-428 over so3.hpp:426-456
     const float wx = a[3], wy = a[4], wz = a[5];
-    const float thetaSq = wx * wx + wy * wy + wz * wz, theta = std::sqrt(thetaSq), half = 0.5f * theta;
+    const float thetaSq = sum3(wx * wx, wy * wy, wz * wz), theta = std::sqrt(thetaSq), half = 0.5f * theta;   // omega.squaredNorm()
     const float eps = 1e-5f;   // SophusConstants<float>::epsilon()
     float imag, real;
     if (theta < eps) {
@@ -260,17 +260,23 @@ Se3 se3Exp(const float *a) {   // a = (upsilon, omega)
     }
     Se3 T;
     T.q[0] = imag * wx; T.q[1] = imag * wy; T.q[2] = imag * wz; T.q[3] = real;
+    {   // the SO3Group(Quaternion) constructor normalises (so3.hpp:739-743 -> :268-276)
+        const float len = std::sqrt((T.q[0] * T.q[0] + T.q[1] * T.q[1]) + (T.q[2] * T.q[2] + T.q[3] * T.q[3]));
+        for (int i = 0; i < 4; i++) T.q[i] = T.q[i] / len;
+    }
     const float O[3][3] = {{0, -wz, wy}, {wz, 0, -wx}, {-wy, wx, 0}};
     float O2[3][3], V[3][3];
     for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) O2[r][c] = sum3(O[r][0] * O[0][c], O[r][1] * O[1][c], O[r][2] * O[2][c]);
-    if (theta < eps) {   // V = so3.matrix()
+    if (theta < eps) {   // V = so3.matrix() = Quaternion::toRotationMatrix()
         const float x = T.q[0], y = T.q[1], z = T.q[2], w = T.q[3];
-        const float M[3][3] = {{1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)},
-                               {2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)},
-                               {2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)}};
+        const float tx = 2.0f * x, ty = 2.0f * y, tz = 2.0f * z;
+        const float twx = tx * w, twy = ty * w, twz = tz * w, txx = tx * x, txy = ty * x, txz = tz * x, tyy = ty * y, tyz = tz * y, tzz = tz * z;
+        const float M[3][3] = {{1.0f - (tyy + tzz), txy - twz, txz + twy}, {txy + twz, 1.0f - (txx + tzz), tyz - twx},
+                               {txz - twy, tyz + twx, 1.0f - (txx + tyy)}};
         std::memcpy(V, M, sizeof V);
     } else {
-        const float A = (1.0f - std::cos(theta)) / thetaSq, B = (theta - std::sin(theta)) / (thetaSq * theta);
+        const float thetaSq2 = theta * theta;   // se3.hpp:422 squares the root again
+        const float A = (1.0f - std::cos(theta)) / thetaSq2, B = (theta - std::sin(theta)) / (thetaSq2 * theta);
         for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) V[r][c] = ((r == c ? 1.0f : 0.0f) + A * O[r][c]) + B * O2[r][c];
     }
     for (int r = 0; r < 3; r++) T.t[r] = sum3(V[r][0] * a[0], V[r][1] * a[1], V[r][2] * a[2]);

@@ -68,6 +68,10 @@ struct Size {
     Size() : width(0), height(0) {}
     Size(int w, int h) : width(w), height(h) {}
 };
+struct Scalar {   // only the single-value form (src/SparseImageAlign.cc:140)
+    double v0;
+    Scalar(double v = 0) : v0(v) {}
+};
 struct Rect {
     int x, y, width, height;
     Rect() : x(0), y(0), width(0), height(0) {}
@@ -107,6 +111,10 @@ public:
     Mat() : rows(0), cols(0), data(nullptr), type_(CV_8UC1) {}
     Mat(int r, int c, int type) : rows(0), cols(0), data(nullptr), type_(type) { create(r, c, type); }
     Mat(Size sz, int type) : rows(0), cols(0), data(nullptr), type_(type) { create(sz.height, sz.width, type); }
+    Mat(Size sz, int type, const Scalar &s) : rows(0), cols(0), data(nullptr), type_(type) {
+        create(sz.height, sz.width, type);
+        for (int r = 0; r < rows; r++) for (int c = 0; c < cols; c++) { if (type == CV_32F) at<float>(r, c) = (float)s.v0; else at<uchar>(r, c) = (uchar)s.v0; }
+    }
     // External (non-owned) data, like cv::Mat(rows, cols, type, void* data, step).
     Mat(int r, int c, int type, void *ext, size_t stepBytes = 0)
         : rows(r), cols(c), data((uchar *)ext), type_(type) {

@@ -12,8 +12,10 @@
 // ygzr_* on every case; tools/make_golden_match.py commits the ygzr_* outputs as tests/golden/match_*.npz.
 #include "ORBmatcher.h"
 #include "Align.h"
+#include "SparseImageAlign.h"
 
 #include <cstring>
+#include <deque>
 #include <memory>
 
 namespace ygz {
@@ -494,6 +496,96 @@ YGZR_API void ygzr_find_direct_projection(YgzrDirectKeyFrame *kfs, int nKfs, con
         pxCurr[2 * i] = px[0]; pxCurr[2 * i + 1] = px[1];
         searchLevel[i] = level;
     }
+}
+
+// ---- SparseImgAlign (src/SparseImageAlign.cc, whole file) driven by NLLSSolver<6, SE3f>::optimizeGaussNewton
+// (include/NLSSolver_impl.hpp:17-92), constructed as Tracking does (src/Tracking.cc:284: SparseImgAlign(nLevels - 1, 1, 30,
+// GaussNewton, false, false)).  Layout of the pyramids = YgzoPyramid (oracle/direct_oracle.cpp); levels must be continuous
+// (the reference takes stride = img.cols, src/SparseImageAlign.cc:60, 147).
+struct YgzrPyramid { const uint8_t *levels[8]; int32_t w[8], h[8], pitch[8]; };
+namespace {
+struct SparseProbe : public SparseImgAlign {   // a derived class may read the protected state and call the protected steps
+    SparseProbe(int maxLevel, int minLevel) : SparseImgAlign(maxLevel, minLevel, 30, GaussNewton, false, false) {}
+    void prepare(Frame *ref, Frame *cur, int level) {   // what run() does before optimize() (:22-45), for ONE level
+        reset();
+        ref_frame_ = ref; cur_frame_ = cur;
+        ref_patch_cache_ = cv::Mat(ref->N, 16, cv::CV_32F);
+        std::memset(ref_patch_cache_.data, 0, (size_t)ref->N * 64);   // the probe reports the cache: start it defined
+        jacobian_cache_.resize(Eigen::NoChange, ref_patch_cache_.rows * 16);
+        visible_fts_ = vector<bool>(ref_patch_cache_.rows, false);
+        level_ = level;
+        jacobian_cache_.setZero();
+        have_ref_patch_cache_ = false;
+    }
+    float residuals(const SE3f &T) { H_.setZero(); Jres_.setZero(); n_meas_ = 0; return computeResiduals(T, true, false); }
+    const Matrix<float, 6, 6> &H() const { return H_; }
+    const Matrix<float, 6, 1> &Jres() const { return Jres_; }
+    size_t nMeas() const { return n_meas_; }
+    bool visible(int i) const { return visible_fts_[i]; }
+    const float *patch() const { return reinterpret_cast<const float *>(ref_patch_cache_.data); }
+    const float *jac() { return &jacobian_cache_.d[0]; }
+    float chi2() const { return chi2_; }
+};
+void fillDirectFrames(Frame &Ref, Frame &Cur, std::deque<MapPoint> &mps, const YgzrPyramid *ref, const YgzrPyramid *cur, int nLevels,
+                      const float *invScale, float focal, const float *curIntr, const float *refPose, const float *curPose, int n,
+                      const float *kpXY, const uint8_t *valid, const float *worldPos) {
+    for (int l = 0; l < nLevels; l++) {
+        Ref.mvImagePyramid.push_back(cv::Mat(ref->h[l], ref->w[l], cv::CV_8U, (void *)ref->levels[l], (size_t)ref->pitch[l]));
+        Cur.mvImagePyramid.push_back(cv::Mat(cur->h[l], cur->w[l], cv::CV_8U, (void *)cur->levels[l], (size_t)cur->pitch[l]));
+    }
+    Ref.mvInvScaleFactors = levels(invScale, nLevels); Cur.mvInvScaleFactors = Ref.mvInvScaleFactors;
+    Ref.fx = focal; Ref.fy = focal;
+    Cur.fx = curIntr[0]; Cur.fy = curIntr[1]; Cur.cx = curIntr[2]; Cur.cy = curIntr[3];
+    Ref.mTcw = poseFromQt(refPose);
+    if (curPose) Cur.mTcw = poseFromQt(curPose);
+    Ref.N = n;
+    Ref.mvKeys.assign((size_t)n, cv::KeyPoint());
+    Ref.mvpMapPoints.assign((size_t)n, nullptr);
+    Ref.mvbOutlier.assign((size_t)n, false);
+    mps.resize((size_t)n);
+    for (int i = 0; i < n; i++) {
+        Ref.mvKeys[i].pt = cv::Point2f(kpXY[2 * i], kpXY[2 * i + 1]);
+        mps[i].mWorldPos = Vector3f(worldPos[3 * i], worldPos[3 * i + 1], worldPos[3 * i + 2]);
+        if (valid[i]) Ref.mvpMapPoints[i] = &mps[i];      // valid = MapPoint present, not bad, not an outlier (:72-74)
+    }
+}
+void storeQt(const SE3f &T, float *o) { o[0] = T.q.qx; o[1] = T.q.qy; o[2] = T.q.qz; o[3] = T.q.qw; for (int r = 0; r < 3; r++) o[4 + r] = T.t[r]; }
+}  // namespace
+
+// One precomputeReferencePatches + computeResiduals(linearize) at `level` with the given T_cur_from_ref.
+YGZR_API void ygzr_sparse_align_residuals(const YgzrPyramid *ref, const YgzrPyramid *cur, int nLevels, int level, const float *invScale,
+                                          float focal, const float *curIntr, const float *refPose, const float *tCurRef, int n,
+                                          const float *kpXY, const uint8_t *valid, const float *worldPos, float *H36, float *Jres6,
+                                          float *chi2mean, int64_t *nMeas, uint8_t *visible, float *refPatch, float *jac) {
+    std::unique_ptr<Frame> Ref(new Frame()), Cur(new Frame());
+    std::deque<MapPoint> mps;   // MapPoint holds mutexes: not movable
+    fillDirectFrames(*Ref, *Cur, mps, ref, cur, nLevels, invScale, focal, curIntr, refPose, nullptr, n, kpXY, valid, worldPos);
+    SparseProbe P(nLevels - 1, 1);
+    P.prepare(Ref.get(), Cur.get(), level);
+    *chi2mean = P.residuals(poseFromQt(tCurRef));
+    for (int r = 0; r < 6; r++) { Jres6[r] = P.Jres()(r); for (int c = 0; c < 6; c++) H36[6 * r + c] = P.H()(r, c); }
+    *nMeas = (int64_t)P.nMeas();
+    for (int i = 0; i < n; i++) visible[i] = P.visible(i) ? 1 : 0;
+    std::memcpy(refPatch, P.patch(), (size_t)n * 64);
+    std::memcpy(jac, P.jac(), (size_t)n * 384);
+}
+
+// SparseImgAlign::run(ref, cur, TCR).  tCurRef0 (out) = cur->mTcw * ref->mTcw.inverse() as the reference composed it (:35), the
+// starting point the restatement is given; tCurRef (out) = TCR; stats (out): [0] final chi2_, [1] n_meas_.
+YGZR_API int64_t ygzr_sparse_align_run(const YgzrPyramid *ref, const YgzrPyramid *cur, int nLevels, int maxLevel, int minLevel,
+                                       const float *invScale, float focal, const float *curIntr, const float *refPose,
+                                       const float *curPose, int n, const float *kpXY, const uint8_t *valid, const float *worldPos,
+                                       float *tCurRef0, float *tCurRef, float *stats) {
+    std::unique_ptr<Frame> Ref(new Frame()), Cur(new Frame());
+    std::deque<MapPoint> mps;   // MapPoint holds mutexes: not movable
+    fillDirectFrames(*Ref, *Cur, mps, ref, cur, nLevels, invScale, focal, curIntr, refPose, curPose, n, kpXY, valid, worldPos);
+    storeQt(Cur->mTcw * Ref->mTcw.inverse(), tCurRef0);
+    SparseProbe P(maxLevel, minLevel);
+    SE3f TCR;
+    const size_t ret = P.run(Ref.get(), Cur.get(), TCR);
+    storeQt(TCR, tCurRef);
+    if (stats) { stats[0] = P.chi2(); stats[1] = (float)P.nMeas(); }
+    return (int64_t)ret;
 }
 
 // ---- bench.py's CPU leg: ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th, checkLevel) of the reference on a batch

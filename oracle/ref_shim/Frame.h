@@ -1,7 +1,7 @@
 // Frame.h — TEST INFRASTRUCTURE ONLY: the four members of ygz::Frame (reference include/Frame.h:248-332)
 // that src/ORBextractor.cc touches (:1038-1040, 1047, 1056, 1089-1098).  Shadows the real header,
 // which needs Eigen/sophus/DBoW2.
-#ifndef YGZ_REF_SHIM_FRAME_H_
+#if !defined(YGZ_REF_SHIM_FRAME_H_) && !defined(YGZ_FRAME_H_)   // YGZ_FRAME_H_: match_prelude.h brings its own, larger shim
 #define YGZ_REF_SHIM_FRAME_H_
 namespace ygz {
 class Frame {

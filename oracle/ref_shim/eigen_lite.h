@@ -14,12 +14,16 @@
 //     Sophus' normalize() (Thirdparty/sophus/sophus/so3.hpp:268-276: coeffs() /= norm()).  Pose PRODUCTS are not on the
 //     device path (they stay in the caller's Sophus code); the wrappers hand the product they computed to
 //     the restatement as an input, so nothing downstream depends on how the four squares of norm() are summed.
+//   * round 2 (SparseImageAlign / NLSSolver): Matrix<float,6,1>, <6,6>, <2,6>, <6,Dynamic>; (J * J^T) * w and (J * r) * w element
+//     by element in that order; LDLT as written in MatF::LDLT::solve; SE3f::exp from the vendored sophus text.
 // All of it uncontracted (-ffp-contract=off).  The same conventions are written out in oracle/match_oracle.cpp and
 // oracle/direct_oracle.cpp (restatement) and in the kernels; DESIGN.md §2 names them as the canonical float order.
 #ifndef YGZ_REF_SHIM_EIGEN_LITE_H_
 #define YGZ_REF_SHIM_EIGEN_LITE_H_
 #include <cmath>
 #include <cstring>
+#include <ostream>
+#include <vector>
 
 namespace Eigen {
 
@@ -68,6 +72,9 @@ template <int N> struct VecF {
     VecF &operator*=(float s) { for (int i = 0; i < N; i++) d[i] = d[i] * s; return *this; }
     VecF operator-() const { VecF r; for (int i = 0; i < N; i++) r.d[i] = -d[i]; return r; }
     template <int K> VecF<K> head() const { VecF<K> r; for (int i = 0; i < K; i++) r.d[i] = d[i]; return r; }
+    VecF &noalias() { return *this; }                            // v.noalias() -= expr: the expression is evaluated first either way
+    struct Diag { const float *d; };                             // v.asDiagonal(), only as the right operand of M += ...
+    Diag asDiagonal() const { return Diag{d}; }
 };
 template <int N> inline VecF<N> operator+(const VecF<N> &a, const VecF<N> &b) { VecF<N> r; for (int i = 0; i < N; i++) r.d[i] = a.d[i] + b.d[i]; return r; }
 template <int N> inline VecF<N> operator-(const VecF<N> &a, const VecF<N> &b) { VecF<N> r; for (int i = 0; i < N; i++) r.d[i] = a.d[i] - b.d[i]; return r; }
@@ -95,7 +102,51 @@ template <int N> struct MatF {
     MatF &operator+=(const MatF &o) { for (int r = 0; r < N; r++) for (int c = 0; c < N; c++) m[r][c] = m[r][c] + o.m[r][c]; return *this; }
     float determinant() const;
     MatF inverse() const;
+    // --- what include/NLSSolver_impl.hpp and src/SparseImageAlign.cc add (N = 6)
+    MatF &noalias() { return *this; }
+    VecF<N> diagonal() const { VecF<N> r; for (int i = 0; i < N; i++) r.d[i] = m[i][i]; return r; }
+    MatF &operator+=(const typename VecF<N>::Diag &dg) { for (int i = 0; i < N; i++) m[i][i] = m[i][i] + dg.d[i]; return *this; }
+    struct LDLT { const MatF *A; VecF<N> solve(const VecF<N> &b) const; };
+    LDLT ldlt() const { return LDLT{this}; }
 };
+template <int N> inline MatF<N> operator/(const MatF<N> &A, float s) { MatF<N> r; for (int i = 0; i < N; i++) for (int j = 0; j < N; j++) r.m[i][j] = A.m[i][j] / s; return r; }
+template <int N> inline std::ostream &operator<<(std::ostream &o, const MatF<N> &A) {
+    for (int i = 0; i < N; i++) { for (int j = 0; j < N; j++) o << A.m[i][j] << (j + 1 < N ? " " : ""); o << "\n"; }
+    return o;
+}
+template <int N> inline std::ostream &operator<<(std::ostream &o, const VecF<N> &v) { for (int i = 0; i < N; i++) o << v.d[i] << "\n"; return o; }
+// x = A.ldlt().solve(b): LDL^T with the largest remaining |diagonal| as pivot (Eigen/src/Cholesky/LDLT.h: unblocked in-place
+// factorisation with transpositions, then P, L, D (entries below the smallest normal float count as zero), L^T, P^T).  The
+// order of the float operations inside the column updates is a choice of this stand-in (sequential, as written below); it is
+// the one oracle/direct_oracle.cpp (ldltSolve6) and the kernel use.
+template <int N> inline VecF<N> MatF<N>::LDLT::solve(const VecF<N> &b) const {
+    float Aw[N][N]; int perm[N];
+    for (int r = 0; r < N; r++) { perm[r] = r; for (int c = 0; c < N; c++) Aw[r][c] = A->m[r][c]; }
+    for (int k = 0; k < N; k++) {
+        int p = k;
+        for (int i = k + 1; i < N; i++) if (std::fabs(Aw[i][i]) > std::fabs(Aw[p][p])) p = i;
+        if (p != k) {
+            for (int c = 0; c < N; c++) { const float t = Aw[k][c]; Aw[k][c] = Aw[p][c]; Aw[p][c] = t; }
+            for (int r = 0; r < N; r++) { const float t = Aw[r][k]; Aw[r][k] = Aw[r][p]; Aw[r][p] = t; }
+            const int t = perm[k]; perm[k] = perm[p]; perm[p] = t;
+        }
+        float d = Aw[k][k];
+        for (int j = 0; j < k; j++) d -= Aw[k][j] * Aw[k][j] * Aw[j][j];
+        Aw[k][k] = d;
+        for (int i = k + 1; i < N; i++) {
+            float v = Aw[i][k];
+            for (int j = 0; j < k; j++) v -= Aw[i][j] * Aw[k][j] * Aw[j][j];
+            Aw[i][k] = d != 0 ? v / d : v;
+        }
+    }
+    float y[N];
+    for (int i = 0; i < N; i++) { float v = b.d[perm[i]]; for (int j = 0; j < i; j++) v -= Aw[i][j] * y[j]; y[i] = v; }
+    for (int i = 0; i < N; i++) y[i] = std::fabs(Aw[i][i]) > 1.17549435e-38f ? y[i] / Aw[i][i] : 0.0f;
+    for (int i = N - 1; i >= 0; i--) { float v = y[i]; for (int j = i + 1; j < N; j++) v -= Aw[j][i] * y[j]; y[i] = v; }
+    VecF<N> x;
+    for (int i = 0; i < N; i++) x.d[perm[i]] = y[i];
+    return x;
+}
 // outer product J * J.transpose()
 template <int N> inline MatF<N> operator*(const VecF<N> &a, const RowVecF<N> &b) {
     MatF<N> r; for (int i = 0; i < N; i++) for (int j = 0; j < N; j++) r.m[i][j] = a.d[i] * b.d[j]; return r;
@@ -147,6 +198,41 @@ typedef VecF<3> Vector3f;
 typedef MatF<2> Matrix2f;
 typedef MatF<3> Matrix3f;
 
+// ---- Matrix<float, R, C> spellings used by include/NLSSolver.h and include/SparseImageAlign.h
+enum { Dynamic = -1, ColMajor = 0, RowMajor = 1 };
+enum NoChange_t { NoChange };
+struct Mat26 {                      // Matrix<float, 2, 6>: JacobXYZ2Cam
+    float m[2][6];
+    float &operator()(int r, int c) { return m[r][c]; }
+    const float &operator()(int r, int c) const { return m[r][c]; }
+    VecF<6> row(int r) const { VecF<6> v; for (int i = 0; i < 6; i++) v.d[i] = m[r][i]; return v; }   // only inside (a * row + b * row) * s
+};
+struct Col6Ref {                    // jacobian_cache_.col(j): six contiguous floats (column-major 6 x n)
+    float *p;
+    Col6Ref &operator=(const VecF<6> &v) { for (int i = 0; i < 6; i++) p[i] = v.d[i]; return *this; }
+    operator VecF<6>() const { VecF<6> r; for (int i = 0; i < 6; i++) r.d[i] = p[i]; return r; }
+};
+struct Mat6X {                      // Matrix<float, 6, Dynamic, ColMajor>
+    std::vector<float> d;
+    void resize(NoChange_t, long cols) { d.resize((size_t)6 * cols); }
+    void setZero() { for (float &v : d) v = 0.0f; }
+    long cols() const { return (long)(d.size() / 6); }
+    Col6Ref col(long j) { return Col6Ref{&d[(size_t)6 * j]}; }
+};
+struct VectorXf {                   // only as the parameter type of norm_max (include/NLSSolver.h)
+    std::vector<float> d;
+    template <int N> VectorXf(const VecF<N> &v) : d(v.d, v.d + N) {}
+    int size() const { return (int)d.size(); }
+    float operator[](int i) const { return d[i]; }
+};
+template <typename T, int R, int C> struct MatrixSel;
+template <int N> struct MatrixSel<float, N, 1> { typedef VecF<N> type; };
+template <int N> struct MatrixSel<float, N, N> { typedef MatF<N> type; };
+template <> struct MatrixSel<float, 2, 6> { typedef Mat26 type; };
+template <> struct MatrixSel<float, 6, Dynamic> { typedef Mat6X type; };
+template <typename T, int R, int C, int Options = 0> using Matrix = typename MatrixSel<T, R, C>::type;
+#define EIGEN_MAKE_ALIGNED_OPERATOR_NEW
+
 inline Vector3f cross(const Vector3f &a, const Vector3f &b) {
     return Vector3f(a[1] * b[2] - a[2] * b[1], a[2] * b[0] - a[0] * b[2], a[0] * b[1] - a[1] * b[0]);
 }
@@ -190,6 +276,7 @@ inline Quaternionf operator*(const Quaternionf &a, const Quaternionf &b) {
 }  // namespace Eigen
 
 namespace Sophus {
+typedef Eigen::VecF<6> Vector6f;   // Thirdparty/sophus/sophus/se3.hpp:40
 // Sophus::SE3Group<float> on (unit quaternion, translation) storage — Thirdparty/sophus/sophus/se3.hpp, so3.hpp.
 class SE3f {
 public:
@@ -220,6 +307,43 @@ public:
         p.qx /= length; p.qy /= length; p.qz /= length; p.qw /= length;
         r.q = p;
         return r;
+    }
+    // SE3Group::exp (Thirdparty/sophus/sophus/se3.hpp:407-428) over SO3Group::expAndTheta (so3.hpp:426-456); a = (upsilon, omega).
+    // The SO3Group(Quaternion) constructor normalises (so3.hpp:739-743 -> :268-276); V uses theta * theta, not the squared
+    // norm it took the root of (se3.hpp:422).
+    static SE3f exp(const Eigen::VecF<6> &a) {
+        const Eigen::Vector3f omega(a[3], a[4], a[5]), upsilon(a[0], a[1], a[2]);
+        const float theta_sq = omega.squaredNorm();
+        const float theta = std::sqrt(theta_sq);
+        const float half_theta = 0.5f * theta;
+        const float eps = 1e-5f;   // SophusConstants<float>::epsilon() (sophus.hpp)
+        float imag_factor, real_factor;
+        if (theta < eps) {
+            const float theta_po4 = theta_sq * theta_sq;
+            imag_factor = 0.5f - (float)(1.0 / 48.0) * theta_sq + (float)(1.0 / 3840.0) * theta_po4;
+            real_factor = 1.0f - 0.5f * theta_sq + (float)(1.0 / 384.0) * theta_po4;
+        } else {
+            const float sin_half_theta = std::sin(half_theta);
+            imag_factor = sin_half_theta / theta;
+            real_factor = std::cos(half_theta);
+        }
+        Eigen::Quaternionf q(real_factor, imag_factor * omega.x(), imag_factor * omega.y(), imag_factor * omega.z());
+        const float length = std::sqrt(q.squaredNorm());
+        q.qx /= length; q.qy /= length; q.qz /= length; q.qw /= length;
+        Eigen::Matrix3f Omega;   // SO3Group::hat
+        Omega(0, 0) = 0.0f; Omega(0, 1) = -omega[2]; Omega(0, 2) = omega[1];
+        Omega(1, 0) = omega[2]; Omega(1, 1) = 0.0f; Omega(1, 2) = -omega[0];
+        Omega(2, 0) = -omega[1]; Omega(2, 1) = omega[0]; Omega(2, 2) = 0.0f;
+        const Eigen::Matrix3f Omega_sq = Omega * Omega;
+        Eigen::Matrix3f V;
+        if (theta < eps) {
+            V = q.toRotationMatrix();
+        } else {
+            const float theta_sq2 = theta * theta;
+            const float c1 = (1.0f - std::cos(theta)) / theta_sq2, c2 = (theta - std::sin(theta)) / (theta_sq2 * theta);
+            for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) V(r, c) = ((r == c ? 1.0f : 0.0f) + c1 * Omega(r, c)) + c2 * Omega_sq(r, c);
+        }
+        return SE3f(q, V * upsilon);
     }
 };
 }  // namespace Sophus

@@ -1,5 +1,5 @@
-// match_prelude.h — TEST INFRASTRUCTURE ONLY.  Force-included (-include) when the reference's own src/ORBmatcher.cc and
-// src/Align.cc are compiled, unmodified and in place, into oracle/_ref/libygz_ref_match.so (oracle/Makefile, refmatch).
+// match_prelude.h — TEST INFRASTRUCTURE ONLY.  Force-included (-include) when the reference's own src/ORBmatcher.cc,
+// src/Align.cc and src/SparseImageAlign.cc (with include/NLSSolver.h, NLSSolver_impl.hpp, RobustCost.h) are compiled, unmodified and in place, into oracle/_ref/libygz_ref_match.so (oracle/Makefile, refmatch).
 //
 // include/ORBmatcher.h pulls in Common.h (Eigen, sophus, g2o, pangolin, glog, OpenCV C++) and the full Frame / KeyFrame /
 // MapPoint headers (DBoW2 vocabulary, IMU, Map, g2o types); none of that exists in this image and none of it is used by the
@@ -59,10 +59,22 @@ struct YgzNullLog {   // glog stand-in (include/Common.h:70): messages are dropp
 };
 #define LOG(severity) YgzNullLog()
 
+// display-only statements of src/SparseImageAlign.cc (:139-140 resimg_, :201-203, :247-253 imshow): compiled, never executed
+// (display_ is false in Tracking.cc:284 and here)
+namespace cv {
+struct DisplayExpr {};
+inline DisplayExpr operator*(const Mat &, int) { return DisplayExpr(); }
+inline void namedWindow(const char *, int) {}
+inline void imshow(const char *, const DisplayExpr &) {}
+inline int waitKey(int) { return 0; }
+}  // namespace cv
+#define CV_WINDOW_AUTOSIZE 1
+
 #define FRAME_GRID_ROWS 48   // include/Frame.h:27-28
 #define FRAME_GRID_COLS 64
 
 namespace ygz {
+using namespace Sophus;   // src/IMU/IMUPreintegrator.h:10 (reaches SparseImageAlign.cc through Frame.h): Vector6f
 
 class Frame;
 class KeyFrame;

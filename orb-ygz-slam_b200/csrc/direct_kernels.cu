@@ -361,13 +361,13 @@ __device__ void dSe3Compose(const float *A, const float *B, float *R) {   // SE3
     const float ax = A[0], ay = A[1], az = A[2], aw = A[3], bx = B[0], by = B[1], bz = B[2], bw = B[3];
     const float q0 = aw * bx + ax * bw + ay * bz - az * by, q1 = aw * by + ay * bw + az * bx - ax * bz;
     const float q2 = aw * bz + az * bw + ax * by - ay * bx, q3 = aw * bw - ax * bx - ay * by - az * bz;
-    const float len = sqrtf(q0 * q0 + q1 * q1 + q2 * q2 + q3 * q3);
+    const float len = sqrtf((q0 * q0 + q1 * q1) + (q2 * q2 + q3 * q3));   // coeffs().norm(): one packet of four, pairwise
     R[4] = A[4] + rt.x; R[5] = A[5] + rt.y; R[6] = A[6] + rt.z;
     R[0] = q0 / len; R[1] = q1 / len; R[2] = q2 / len; R[3] = q3 / len;
 }
 __device__ void dSe3Exp(const float *a, float *T) {   // SE3Group::exp (se3.hpp:407-428), SO3Group::expAndTheta (so3.hpp:426-456)
     const float wx = a[3], wy = a[4], wz = a[5];
-    const float thetaSq = wx * wx + wy * wy + wz * wz, theta = sqrtf(thetaSq), half = 0.5f * theta;
+    const float thetaSq = dSum3(wx * wx, wy * wy, wz * wz), theta = sqrtf(thetaSq), half = 0.5f * theta;   // omega.squaredNorm()
     const float eps = 1e-5f;
     float imag, real;
     if (theta < eps) {
@@ -378,15 +378,22 @@ __device__ void dSe3Exp(const float *a, float *T) {   // SE3Group::exp (se3.hpp:
         imag = (float)sin((double)half) / theta; real = (float)cos((double)half);
     }
     T[0] = imag * wx; T[1] = imag * wy; T[2] = imag * wz; T[3] = real;
+    {   // the SO3Group(Quaternion) constructor normalises (so3.hpp:739-743 -> :268-276)
+        const float len = sqrtf((T[0] * T[0] + T[1] * T[1]) + (T[2] * T[2] + T[3] * T[3]));
+        T[0] = T[0] / len; T[1] = T[1] / len; T[2] = T[2] / len; T[3] = T[3] / len;
+    }
     const float O[3][3] = {{0, -wz, wy}, {wz, 0, -wx}, {-wy, wx, 0}};
     float V[3][3];
-    if (theta < eps) {
+    if (theta < eps) {   // V = so3.matrix() = Quaternion::toRotationMatrix()
         const float x = T[0], y = T[1], z = T[2], w = T[3];
-        V[0][0] = 1 - 2 * (y * y + z * z); V[0][1] = 2 * (x * y - z * w); V[0][2] = 2 * (x * z + y * w);
-        V[1][0] = 2 * (x * y + z * w); V[1][1] = 1 - 2 * (x * x + z * z); V[1][2] = 2 * (y * z - x * w);
-        V[2][0] = 2 * (x * z - y * w); V[2][1] = 2 * (y * z + x * w); V[2][2] = 1 - 2 * (x * x + y * y);
+        const float tx = 2.0f * x, ty = 2.0f * y, tz = 2.0f * z;
+        const float twx = tx * w, twy = ty * w, twz = tz * w, txx = tx * x, txy = ty * x, txz = tz * x, tyy = ty * y, tyz = tz * y, tzz = tz * z;
+        V[0][0] = 1.0f - (tyy + tzz); V[0][1] = txy - twz; V[0][2] = txz + twy;
+        V[1][0] = txy + twz; V[1][1] = 1.0f - (txx + tzz); V[1][2] = tyz - twx;
+        V[2][0] = txz - twy; V[2][1] = tyz + twx; V[2][2] = 1.0f - (txx + tyy);
     } else {
-        const float Ac = (1.0f - (float)cos((double)theta)) / thetaSq, Bc = (theta - (float)sin((double)theta)) / (thetaSq * theta);
+        const float thetaSq2 = theta * theta;   // se3.hpp:422 squares the root again
+        const float Ac = (1.0f - (float)cos((double)theta)) / thetaSq2, Bc = (theta - (float)sin((double)theta)) / (thetaSq2 * theta);
         for (int r = 0; r < 3; r++)
             for (int c = 0; c < 3; c++) {
                 const float o2 = dSum3(O[r][0] * O[0][c], O[r][1] * O[1][c], O[r][2] * O[2][c]);

@@ -66,6 +66,15 @@ for n_points, seed, big in [(1, 0, None), (7, 1, None), (500, 2, None), (40, 3, 
     CASES.append(("distinct", "distinct/n%d_s%d" % (n_points, seed), (n_points, seed, big)))
 for seed, n in [(0, 1), (1, 33), (2, 400), (3, 3000)]:
     CASES.append(("fdp", "fdp/s%d_n%d" % (seed, n), (seed, n)))
+# SparseImgAlign (src/SparseImageAlign.cc + include/NLSSolver_impl.hpp): one precompute + computeResiduals at a level ("sares"),
+# and the whole coarse-to-fine run ("sarun").  Levels <= 5 only: run() reads `int iterations[] = {10, 10, 10, 10, 10, 10}` at
+# index level_ (:37, :42), so with 8 pyramid levels the reference reads past the array at levels 6 and 7 (undefined behaviour;
+# the compiled reference here happens to find 0 there and skips both levels).  DESIGN.md 2 records it.
+for seed, n, level in [(0, 300, 1), (1, 300, 3), (2, 800, 5), (3, 50, 2)]:
+    CASES.append(("sares", "sares/s%d_n%d_l%d" % (seed, n, level), (seed, n, level)))
+for seed, n, hi, lo, all_invalid in [(0, 300, 5, 1, False), (1, 800, 5, 1, False), (2, 300, 4, 2, False), (3, 40, 5, 1, False), (4, 8, 5, 1, True)]:
+    CASES.append(("sarun", "sarun/s%d_n%d_l%d_%d_inv%d" % (seed, n, hi, lo, all_invalid), (seed, n, hi, lo, all_invalid)))
+GPU_TOLERANCE_KINDS = ("sares", "sarun")   # sums over features: sequential float in the reference, a tree on the device
 
 BY_KEY = {c[1]: c for c in CASES}
 
@@ -146,6 +155,19 @@ def build_inputs(case):
         q /= np.linalg.norm(q)
         t = synth.quat_rotate(k0["t_cur_ref"][:4].astype(np.float64), k0["pose_ref"][4:].astype(np.float64)) + k0["t_cur_ref"][4:]
         d.update(c=c, cur_pose=np.concatenate([q, t]).astype(np.float32), inv_sigma2=inv_s2)
+    elif kind in ("sares", "sarun"):
+        seed, n = p[0], p[1]
+        c = synth.sparse_align_case(seed, n=n)
+        if kind == "sarun" and p[4]:
+            c["valid"][:] = 0
+        q = _qmul(c["t_cur_ref"][:4], c["ref_pose"][:4])
+        q /= np.linalg.norm(q)
+        t = synth.quat_rotate(c["t_cur_ref"][:4].astype(np.float64), c["ref_pose"][4:].astype(np.float64)) + c["t_cur_ref"][4:]
+        d.update(c=c, cur_pose=np.concatenate([q, t]).astype(np.float32))
+        if kind == "sares":
+            d.update(level=p[2])
+        else:
+            d.update(max_level=p[2], min_level=p[3])
     else:
         raise KeyError(kind)
     return d
@@ -198,6 +220,16 @@ def run_ref(d):
         px, lv, ok, tcr = R.find_direct_projection(c["kfs"], c["cur_levels"], c["cur_intr"], d["cur_pose"], c["scale"], c["inv_scale"],
                                                    d["inv_sigma2"], c["kf_index"], c["px_ref"], c["octave"], c["world_pos"], c["px_curr"])
         return [px, lv, ok], {"tcr": np.stack(tcr)}
+    if k == "sares":
+        c = d["c"]
+        H, J, chi2, nm, vis, patch, jac = R.sparse_align_residuals(c["ref_levels"], c["cur_levels"], d["level"], c["inv_scale"], c["focal"],
+                                                                   c["cur_intr"], c["ref_pose"], c["t_cur_ref"], c["kp_xy"], c["valid"], c["world_pos"])
+        return [H, J, np.float32(chi2), np.int64(nm), vis, patch, jac], {}
+    if k == "sarun":
+        c = d["c"]
+        t0, T, ret, st = R.sparse_align_run(c["ref_levels"], c["cur_levels"], d["max_level"], d["min_level"], c["inv_scale"], c["focal"],
+                                            c["cur_intr"], c["ref_pose"], d["cur_pose"], c["kp_xy"], c["valid"], c["world_pos"])
+        return [T, np.int64(ret), np.float32(st[0])], {"t0": t0}
     raise KeyError(k)
 
 
@@ -211,6 +243,8 @@ def apply_derived(d, der):
     if k == "fdp":
         for kf, t in zip(d["c"]["kfs"], der["tcr"]):
             kf["t_cur_ref"] = np.asarray(t, np.float32)
+    if k == "sarun":
+        d["c"]["t_cur_ref"] = np.asarray(der["t0"], np.float32)   # cur->mTcw * ref->mTcw.inverse() as the reference composed it
     return d
 
 
@@ -270,6 +304,18 @@ def run_oracle(d):
     if k == "fdp":
         px, lv, ok = O.find_direct_projection(**d["c"])
         return [px, lv, ok]
+    if k == "sares":
+        c = d["c"]
+        H, J, chi2, nm, vis, patch, jac = O.sparse_align_residuals(c["ref_levels"], c["cur_levels"], d["level"], c["inv_scale"][d["level"]], c["focal"],
+                                                                   c["cur_intr"], c["ref_pose"], c["t_cur_ref"], c["kp_xy"], c["valid"], c["world_pos"],
+                                                                   accumulate=0)
+        mean = np.float32(chi2) / np.float32(nm) if nm else np.float32(np.nan)   # the reference returns chi2 / n_meas_ (:218)
+        return [H, J, np.float32(mean), np.int64(nm), vis, patch, jac]
+    if k == "sarun":
+        c = d["c"]
+        T, ret, st = O.sparse_align_run(c["ref_levels"], c["cur_levels"], d["max_level"], d["min_level"], c["inv_scale"], c["focal"], c["cur_intr"],
+                                        c["ref_pose"], c["kp_xy"], c["valid"], c["world_pos"], c["t_cur_ref"], accumulate=0)
+        return [T, np.int64(ret), np.float32(st[1])]
     raise KeyError(k)
 
 

@@ -259,3 +259,43 @@ def search_by_projection_batch(n_kp, n_mp, kps, desc, bounds, scale_factors, mp,
              _p(f32(mp["view_cos"])), _p(i32(mp["level"])), _p(u8(mp["in_view"])), _p(u8(mp["has_obs"])), _p(u8(mp["desc"])),
              cf(th), int(check_level), cf(nnratio), int(threads), int(repeat), _p(kp_to_mp), _p(nm))
     return kp_to_mp, nm, float(sec)
+
+
+class RPyramid(C.Structure):   # = YgzrPyramid (oracle/ref_match_api.cpp)
+    _fields_ = [("levels", C.c_void_p * 8), ("w", C.c_int32 * 8), ("h", C.c_int32 * 8), ("pitch", C.c_int32 * 8)]
+
+
+def _rpyr(levels):
+    imgs = [np.ascontiguousarray(x, np.uint8) for x in levels]
+    P = RPyramid()
+    for l, im in enumerate(imgs):
+        P.levels[l] = im.ctypes.data; P.w[l] = im.shape[1]; P.h[l] = im.shape[0]; P.pitch[l] = im.shape[1]
+    return P, imgs
+
+
+def sparse_align_residuals(ref_levels, cur_levels, level, inv_scale, focal, cur_intr, ref_pose, t_cur_ref, kp_xy, valid, world_pos):
+    """precomputeReferencePatches + computeResiduals(linearize) of the reference's SparseImgAlign at one level.
+    Returns H, Jres, chi2 (mean, as the reference returns it), n_meas, visible, ref_patch_cache, jacobian_cache."""
+    R, k1 = _rpyr(ref_levels); Cu, k2 = _rpyr(cur_levels)
+    kp_xy, valid, world_pos = f32(kp_xy), u8(valid), f32(world_pos)
+    n = len(valid)
+    H, J, chi2, nm = np.zeros((6, 6), np.float32), np.zeros(6, np.float32), C.c_float(), C.c_int64()
+    vis, patch, jac = np.zeros(n, np.uint8), np.zeros((n, 16), np.float32), np.zeros((n, 16, 6), np.float32)
+    lib().ygzr_sparse_align_residuals(C.byref(R), C.byref(Cu), len(ref_levels), level, _p(f32(inv_scale)), cf(focal), _p(f32(cur_intr)),
+                                      _p(f32(ref_pose)), _p(f32(t_cur_ref)), n, _p(kp_xy), _p(valid), _p(world_pos), _p(H), _p(J),
+                                      C.byref(chi2), C.byref(nm), _p(vis), _p(patch), _p(jac))
+    return H, J, chi2.value, nm.value, vis, patch, jac
+
+
+def sparse_align_run(ref_levels, cur_levels, max_level, min_level, inv_scale, focal, cur_intr, ref_pose, cur_pose, kp_xy, valid,
+                     world_pos):
+    """SparseImgAlign::run(ref, cur, TCR).  Returns (t_cur_ref0 = cur->mTcw * ref->mTcw.inverse() as composed by the reference,
+    TCR, return value, [chi2_, n_meas_])."""
+    R, k1 = _rpyr(ref_levels); Cu, k2 = _rpyr(cur_levels)
+    kp_xy, valid, world_pos = f32(kp_xy), u8(valid), f32(world_pos)
+    T0, T, stats = np.zeros(7, np.float32), np.zeros(7, np.float32), np.zeros(2, np.float32)
+    lib().ygzr_sparse_align_run.restype = C.c_int64
+    ret = lib().ygzr_sparse_align_run(C.byref(R), C.byref(Cu), len(ref_levels), max_level, min_level, _p(f32(inv_scale)), cf(focal),
+                                      _p(f32(cur_intr)), _p(f32(ref_pose)), _p(f32(cur_pose)), len(valid), _p(kp_xy), _p(valid),
+                                      _p(world_pos), _p(T0), _p(T), _p(stats))
+    return T0, T, ret, stats

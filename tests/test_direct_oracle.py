@@ -1,5 +1,6 @@
 """CPU checks of oracle/direct_oracle.cpp against independent numpy re-derivations written from the
-reference text, not from the oracle code.  The reference's own files need Eigen/sophus/OpenCV C++ (absent): parity unpinned."""
+reference text, not from the oracle code.  These are the independent re-derivations of round 1; since round 2 the restatement is also pinned to the reference's own compiled code
+(tests/test_ref_match.py)."""
 import numpy as np
 import pytest
 
