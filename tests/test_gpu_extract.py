@@ -132,6 +132,23 @@ def test_strided_input_and_repeatability():
     ex.close()
 
 
+@pytest.mark.parametrize("w,h,n", [(752, 480, 24), (750, 300, 40), (640, 480, 20)])
+def test_large_batch_takes_the_persistent_fast_kernel(w, h, n):
+    """Batches large enough for k_fast_tma (persistent CTAs, cell windows fetched by TMA two deep) give per-frame results equal
+    to the oracle's; 750 px wide frames have a stride TMA cannot describe and must fall back to k_fast with the same results.
+    Textured, mixed-contrast (minThFAST retry cells) and flat frames in one batch."""
+    frames = np.stack([synth.textured_frame(w, h, 300 + i) if i % 4 else synth.mixed_frame(w, h, 300 + i) for i in range(n)])
+    frames[3] = 90   # a flat frame: every cell retries at minThFAST and finds nothing
+    p = O.params(1000, 1.2, 8, 20, 7)
+    ex = Y.Extractor(1000, 1.2, 8, 20, 7, max_batch=n)
+    outs = ex.extract_batch(frames)
+    for f in range(n):
+        okps, odesc = O.extract(p, frames[f])
+        assert outs[f][0].tobytes() == okps.tobytes(), "frame %d" % f
+        assert np.array_equal(outs[f][1], odesc)
+    ex.close()
+
+
 @pytest.mark.parametrize("pipe,max_batch", [(2, 16), (3, 4), (0, 16), (128, 16)])
 def test_pipelined_host_chunks(pipe, max_batch):
     """Host-input calls split into pipelined chunks (upload / kernels / download on three streams, two staging
