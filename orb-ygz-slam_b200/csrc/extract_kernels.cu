@@ -286,6 +286,9 @@ int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nF
 // Survivors are appended (unordered) to the level's candidate array with an order key
 // (cell, y-in-cell, x-in-cell) that encodes the reference's vToDistributeKeys order, which is all
 // the quadtree needs from the order (its only order dependence is "first wins" on response ties).
+// Tried in round 2 and dropped (profiles/r2_k_fast_experiments.md): a persistent variant fed by TMA (cp.async.bulk.tensor.3d, two tile
+// buffers, mbarrier completion) — bit-exact, 2.27-2.50 ms against 1.91 ms: the 16-byte alignment TMA wants of the x coordinate costs
+// a 64-byte tile pitch, i.e. shared memory for 16-21 CTAs per SM instead of 31, and a CTA then serialises its cells' barrier chains.
 constexpr int kFastThreads = kFastCtaThreads;
 constexpr int kFastWarps = kFastThreads / 32;
 // image / score tile pitch = template parameter TP (kFastTilePitchNarrow or kFastTilePitch)
@@ -310,11 +313,6 @@ template <int IMM> __device__ __forceinline__ unsigned ldsU8(unsigned a) {
 __device__ __forceinline__ unsigned ldsU16(unsigned a) {
     unsigned v;
     asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a));
-    return v;
-}
-__device__ __forceinline__ unsigned ldsU32(unsigned a) {
-    unsigned v;
-    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
     return v;
 }
 __device__ __forceinline__ void stsU8(unsigned a, unsigned v) { asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v)); }
@@ -502,187 +500,8 @@ template <bool PDL, int TP> __global__ void __launch_bounds__(kFastThreads, 32) 
     }
 }
 
-// ---- TMA-fed persistent variant (batches).  A CTA walks cells w = blockIdx.x, + gridDim.x, ... (frame-major); the 48 x fastRows
-// byte window of cell i+1 (64 bytes wide from iniX & ~15: TMA wants the x coordinate 16-byte aligned) is fetched by ONE cp.async.bulk.tensor instruction (thread 0) into the other of two tile buffers
-// while the CTA works on cell i, completion on an mbarrier.  Against k_fast this removes the tile-load loop and its address
-// arithmetic, pays the kernel prologue once per CTA instead of once per cell, and takes the load latency off the cell's
-// critical path.  Tile column c <-> image x = iniX + c (TMA needs no alignment of the coordinates); rows / columns of the box
-// beyond the image are zero-filled and never read.  Phases 1a / 1b / 2 are k_fast's.
-__device__ __forceinline__ void mbarInit(unsigned bar, unsigned count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory"); }
-__device__ __forceinline__ void mbarExpectTx(unsigned bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbarWait(unsigned bar, unsigned parity) {
-    asm volatile(
-        "{\n\t.reg .pred P1;\n\tLAB_WAIT:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
-        "@P1 bra DONE;\n\tbra LAB_WAIT;\n\tDONE:\n\t}" ::"r"(bar), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void tmaLoad3D(unsigned dst, const CUtensorMap *map, int x, int y, int z, unsigned bar) {
-    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
-                 ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(z), "r"(bar) : "memory");
-}
-
-#ifndef YGZ_FAST_MINB
-#define YGZ_FAST_MINB 24
-#endif
-constexpr int kFastTmaMinBlocks = YGZ_FAST_MINB;
-#ifndef YGZ_FAST_TP
-#define YGZ_FAST_TP 64
-#endif
-constexpr int kFastTmaPitch = YGZ_FAST_TP;   // box = 64 bytes from iniX & ~15: up to 15 bytes of lead-in + the window (<= 45 wide on the narrow geometry)
-__global__ void __launch_bounds__(kFastThreads, kFastTmaMinBlocks) k_fast_tma(const __grid_constant__ FrameGeom G, const DevBuffers B,
-                                                                            const __grid_constant__ TmaMaps M, int nItems, int tileBytes) {
-    constexpr int TP = kFastTmaPitch;
-    extern __shared__ __align__(128) uint8_t fastSmem[];
-    uint8_t *score = fastSmem + 2 * tileBytes;
-    uint16_t *corners = reinterpret_cast<uint16_t *>(score + (G.fastRows - 4) * TP);   // score tile: (maxDh + 2) rows of TP bytes
-    const int kFastWarpCap = G.fastWarpCap;
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const unsigned tile0 = smemAddr(fastSmem);
-    // behind the lists (16-byte aligned): two work items {cell.x, cell.y, frame, valid} and two 8-byte mbarriers.  The items live
-    // in shared memory, written by thread 0 one cell ahead, so that no thread carries the look-ahead in registers.
-    int4 *items = reinterpret_cast<int4 *>(corners + kFastWarps * kFastWarpCap);   // generic pointer: thread 0's writes only
-    const unsigned itemsAt = smemAddr(items), bar0 = itemsAt + 32;
-    const unsigned boxBytes = (unsigned)(TP * G.fastRows);
-    if (tid == 0) {
-        mbarInit(bar0, 1); mbarInit(bar0 + 8, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        const int w = blockIdx.x;
-        int4 item = make_int4(0, 0, 0, 0);
-        if (w < nItems) {
-            const int f = w / G.totalCells;
-            const int2 ce = __ldg(B.tabs + G.cellTab + (w - f * G.totalCells));
-            item = make_int4(ce.x, ce.y, f, 1);
-            mbarExpectTx(bar0, boxBytes);
-            tmaLoad3D(tile0, &M.lv[ce.x >> 24], ce.x & 0xff0, (ce.x >> 12) & 0xfff, f, bar0);
-        }
-        items[0] = item;
-    }
-    __syncthreads();
-    if (!ldsU32(itemsAt + 12)) return;
-    const unsigned ltMask = (1u << lane) - 1u;
-    const unsigned scoreAt = tile0 + 2 * tileBytes, sc0a = scoreAt + TP + 1;
-    const unsigned cornersAt = smemAddr(corners + wid * kFastWarpCap);
-    for (int it = 0;; it++) {
-        const int buf = it & 1;
-        if (tid == 0) {      // look one cell ahead; the other tile buffer was last read in iteration it - 1, which ended with a barrier
-            const long long wn = (long long)blockIdx.x + (long long)(it + 1) * gridDim.x;
-            int4 item = make_int4(0, 0, 0, 0);
-            if (wn < nItems) {
-                const int fN = (int)(wn / G.totalCells);
-                const int2 ceN = __ldg(B.tabs + G.cellTab + (int)(wn - (long long)fN * G.totalCells));
-                item = make_int4(ceN.x, ceN.y, fN, 1);
-                mbarExpectTx(bar0 + 8 * (buf ^ 1), boxBytes);
-                tmaLoad3D(tile0 + (buf ^ 1) * tileBytes, &M.lv[ceN.x >> 24], ceN.x & 0xff0, (ceN.x >> 12) & 0xfff, fN, bar0 + 8 * (buf ^ 1));
-            }
-            items[buf ^ 1] = item;
-        }
-        int4 cur;
-        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(cur.x), "=r"(cur.y), "=r"(cur.z), "=r"(cur.w) : "r"(itemsAt + 16 * buf));
-        const int f = cur.z;
-        const int level = cur.x >> 24, iniX = cur.x & 0xfff, iniY = (cur.x >> 12) & 0xfff;
-        const int dw = cur.y & 127, dh = (cur.y >> 7) & 127, cell = (int)((unsigned)cur.y >> 14);
-        const LevelGeom &L = G.lv[level];
-        const int npx = dw * dh;
-        // score tile: all zero; phase 1 writes m only where m exceeds the threshold in force
-        for (int i = tid; i < ((dh + 2) * TP + 15) / 16; i += kFastThreads) asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(scoreAt + 16 * i), "r"(0));
-        mbarWait(bar0 + 8 * buf, (unsigned)(it >> 1) & 1u);
-        __syncthreads();
-        const int minTh = G.minTh;
-        const unsigned magic = (unsigned)(16777216.0f * __fdividef(1.0f, (float)dw)) + 6u;
-        const int wrapOff = TP - dw;
-        const unsigned centre = tile0 + buf * tileBytes + 3 * TP + 3 + (iniX & 15);   // the box starts at iniX & ~15 (TMA: 16-byte aligned x)
-        int t = G.iniTh;
-        for (;;) {
-            const unsigned pre2 = ((unsigned)t + 256u) * 0x10001u;
-            int n0 = 0;
-            for (int i = tid; i - lane < npx; i += kFastThreads) {
-                const int ic = min(i, npx - 1);
-                const int off = (int)__umulhi((unsigned)ic << 8, magic) * wrapOff + ic;
-                const bool pass = fastPretest<TP>(centre + off, pre2) && i < npx;
-                const unsigned mask = __ballot_sync(0xffffffffu, pass);
-                if (pass) stsU16(cornersAt + 2 * (n0 + __popc(mask & ltMask)), (unsigned)off);
-                n0 += __popc(mask);
-            }
-            __syncwarp();
-            int n1 = 0;
-            for (int k0 = 0; k0 < n0; k0 += 32) {
-                const int k = k0 + lane;
-                unsigned off = 0;
-                int m = -1;
-                if (k < n0) {
-                    off = ldsU16(cornersAt + 2 * k);
-                    m = fastMeasure<TP>(centre + off);
-                }
-                const bool corner = m > t;
-                if (corner) stsU8(sc0a + off, (unsigned)m);
-                const unsigned mask = __ballot_sync(0xffffffffu, corner);
-                if (corner) stsU16(cornersAt + 2 * (n1 + __popc(mask & ltMask)), off);
-                n1 += __popc(mask);
-            }
-            __syncthreads();
-            int any = 0;
-            for (int k0 = 0; k0 < n1; k0 += 32) {
-                const int k = k0 + lane;
-                bool ismax = false;
-                unsigned o = 0, m = 0;
-                if (k < n1) {
-                    constexpr int P = TP;
-                    o = ldsU16(cornersAt + 2 * k);
-                    const unsigned sc = sc0a + o;
-                    m = ldsU8<0>(sc);
-                    const unsigned nb = max(max(max(ldsU8<-1>(sc), ldsU8<1>(sc)), max(ldsU8<-P - 1>(sc), ldsU8<-P>(sc))),
-                                            max(max(ldsU8<-P + 1>(sc), ldsU8<P - 1>(sc)), max(ldsU8<P>(sc), ldsU8<P + 1>(sc))));
-                    ismax = nb < m;
-                }
-                const unsigned mask = __ballot_sync(0xffffffffu, ismax);
-                if (mask == 0) continue;
-                any = 1;
-                int base = 0;
-                if (lane == 0) base = atomicAdd(B.candCount + f * kMaxLevels + level, __popc(mask));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (ismax) {
-                    const int slot = base + __popc(mask & ltMask);
-                    if (slot < L.candCap) {
-                        const unsigned y = (o * ((1u << 20) / TP + 1)) >> 20, x = o - y * TP;
-                        const uint32_t ax = iniX + 3 + x, ay = iniY + 3 + y;
-                        (B.cand + (long long)f * G.candPerFrame + L.candOff)[slot] = make_uint2(ax | (ay << 12) | ((uint32_t)(m - 1) << 24), ((uint32_t)cell << 12) | (y << 6) | x);
-                    } else {
-                        atomicOr(B.status, 1);
-                    }
-                }
-            }
-            // the barrier also ends the cell: every thread is done with this tile buffer, the score tile and the lists
-            if (__syncthreads_or(any) || t == minTh) break;
-            t = minTh;
-        }
-        if (!ldsU32(itemsAt + 16 * (buf ^ 1) + 12)) break;      // written by thread 0 before this cell's barriers
-    }
-}
-
-int launchFast(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s, const TmaMaps *maps) {
+int launchFast(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s) {
     if (G.totalCells == 0) return 0;
-    // batches on a geometry TMA can describe: the persistent kernel; small batches keep the one-CTA-per-cell kernel (more CTAs
-    // than a persistent grid could use, and the programmatic-dependent-launch chain)
-    if (maps && maps->ok && !B.pdl && G.fastPitch == kFastTilePitchNarrow) {
-        static int ctasPerSm = 0, smCount = 0;
-        const int tileBytes = (kFastTmaPitch * G.fastRows + 127) & ~127;
-        const size_t smemT = (size_t)2 * tileBytes + (size_t)G.fastScoreBytes / kFastTilePitchNarrow * kFastTmaPitch + 64 + (size_t)kFastWarps * G.fastWarpCap * sizeof(uint16_t) + 2 * sizeof(int4) + 16;
-        if (!smCount) {
-            int dev = 0;
-            cudaGetDevice(&dev);
-            cudaDeviceGetAttribute(&smCount, cudaDevAttrMultiProcessorCount, dev);
-        }
-        int occ = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_fast_tma, kFastThreads, smemT) == cudaSuccess && occ > 0) ctasPerSm = occ;
-        const long long nItems = (long long)G.totalCells * nFrames;
-        if (ctasPerSm > 0 && nItems >= (long long)2 * smCount * ctasPerSm && nItems < (1ll << 31)) {
-            const int grid = smCount * ctasPerSm;
-            k_fast_tma<<<grid, kFastThreads, smemT, s>>>(G, B, *maps, (int)nItems, tileBytes);
-            return 1;
-        }
-    }
     const size_t smem = (size_t)G.fastRegionA + G.fastScoreBytes + (size_t)(kFastThreads / 32) * G.fastWarpCap * sizeof(uint16_t);
     const dim3 grid(G.totalCells, nFrames);
     if (G.fastPitch == kFastTilePitchNarrow) {

@@ -261,7 +261,6 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
     // tile pitch: the narrow instantiation when every cell (dw + 6 window + up to 3 alignment bytes) fits 48 bytes — the usual
     // 30..39-px cells — which brings the CTA's shared memory under the 32-CTAs-per-SM line; else the general 76
     G.fastPitch = (maxDw + 9 <= kFastTilePitchNarrow) ? kFastTilePitchNarrow : kFastTilePitch;
-    G.fastRows = maxDh + 6;
     G.fastRegionA = alignUp((maxDh + 6) * G.fastPitch, 16);
     G.fastScoreBytes = alignUp((maxDh + 2) * G.fastPitch, 16);
     G.cellTab = (int)tabs.size(); tabs.insert(tabs.end(), cellTab.begin(), cellTab.end());
@@ -284,9 +283,6 @@ constexpr int kInSlots = YGZ_IN_SLOTS;   // host-input staging slots
 
 struct Extractor {
     ygzorb_params params;
-    // k_fast_tma tensor maps and what they were encoded for (re-encoded only when one of these changes)
-    TmaMaps tma = {};
-    const void *tmaIn = nullptr, *tmaPyr = nullptr; long long tmaInStride = -1; int tmaFrames = -1, tmaGeomSeq = -1, geomSeq = 0;
     Tables tables;
     int device = 0, maxBatch = 1;
     cudaStream_t stream = nullptr;
@@ -354,7 +350,7 @@ static int ensureGeometry(Extractor *ex, int w, int h, int stride, int nFrames, 
         const int rc = makeGeometry(ex->params, ex->tables, w, h, stride, G, tabs, bo, bp, &bs);
         if (rc) return rc;
         ex->G = G; memcpy(ex->blurOff, bo, sizeof bo); memcpy(ex->blurPitch, bp, sizeof bp); ex->blurSlab = bs;
-        ex->gw = w; ex->gh = h; ex->gstride = stride; ex->geomSeq++;
+        ex->gw = w; ex->gh = h; ex->gstride = stride;
         ex->stagesValid = false;
         YGZ_CUDA(cudaStreamSynchronize(ex->stream));
         if (int rc2 = growBuf(ex->dTabs, ex->tabBytes, std::max<size_t>(tabs.size(), 1) * sizeof(int2))) return rc2;
@@ -467,55 +463,6 @@ static int sinkPyramid(Extractor *ex, int n) {
 #define YGZ_MARK(i) do { if (ex->profiling) YGZ_CUDA(cudaEventRecord(ex->ev[i], ex->stream)); } while (0)
 
 // Kernels of one chunk (its input already uploaded into `slot` when it comes from the host).
-// ---- TMA descriptors for k_fast_tma.  cuTensorMapEncodeTiled lives in the driver; it is fetched through the runtime
-// (cudaGetDriverEntryPoint), so the library keeps linking against cudart only.
-#ifndef YGZ_FAST_TP
-#define YGZ_FAST_TP 64
-#endif
-typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
-                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static EncodeTiledFn encodeTiledFn() {
-    static EncodeTiledFn fn = [] {
-        void *p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
-        return (EncodeTiledFn)p;
-    }();
-    return fn;
-}
-// One level as a 3-D byte tensor (x = pitch bytes, y = rows, z = frames); box = one cell window.  false = TMA's rules not met.
-static bool encodeLevelMap(CUtensorMap *m, const void *base, int pitch, int rows, long long frameStride, int frames, int boxW, int boxH) {
-    EncodeTiledFn fn = encodeTiledFn();
-    if (!fn || !base || (reinterpret_cast<uintptr_t>(base) & 15) || (pitch & 15) || (frameStride & 15) || pitch < boxW) return false;
-    const cuuint64_t dims[3] = {(cuuint64_t)pitch, (cuuint64_t)rows, (cuuint64_t)std::max(frames, 1)};
-    const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)frameStride};
-    const cuuint32_t box[3] = {(cuuint32_t)boxW, (cuuint32_t)boxH, 1}, estr[3] = {1, 1, 1};
-    return fn(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
-}
-static const TmaMaps *fastTensorMaps(Extractor *ex, int nFrames) {
-    const FrameGeom &G = ex->G;
-    if (G.fastPitch != kFastTilePitchNarrow || G.fastRows > 256 || G.totalCells == 0) return nullptr;
-    const bool geomSame = ex->tmaGeomSeq == ex->geomSeq && ex->tmaFrames >= nFrames;
-    if (!(geomSame && ex->tmaPyr == ex->B.pyr)) {
-        ex->tma.ok = 1;
-        for (int l = 1; l < G.nlevels && ex->tma.ok; l++)
-            ex->tma.ok = encodeLevelMap(&ex->tma.lv[l], ex->B.pyr + G.lv[l].off, G.lv[l].pitch, G.lv[l].h, G.slabBytes, ex->maxBatch,
-                                        YGZ_FAST_TP, G.fastRows) ? 1 : 0;
-        ex->tmaPyr = ex->B.pyr; ex->tmaGeomSeq = ex->geomSeq; ex->tmaFrames = ex->maxBatch; ex->tmaIn = nullptr;
-    }
-    if (ex->tma.ok && !(ex->tmaIn == ex->B.in && ex->tmaInStride == ex->B.inFrameStride)) {
-        // level 0 is caller memory or a staging slot: its base changes from call to call
-        if (!encodeLevelMap(&ex->tma.lv[0], ex->B.in, G.lv[0].pitch, G.lv[0].h, ex->B.inFrameStride, ex->maxBatch, YGZ_FAST_TP, G.fastRows)) {
-            ex->tmaIn = nullptr;
-            return nullptr;      // this input cannot be described (unaligned base or stride): the non-TMA kernel runs
-        }
-        ex->tmaIn = ex->B.in; ex->tmaInStride = ex->B.inFrameStride;
-    }
-    return ex->tma.ok ? &ex->tma : nullptr;
-}
-
 static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int h, size_t frameStride, int srcPitch,
                         unsigned flags, int cap, int slot, int32_t *counts, ygzorb_keypoint *kps, uint8_t *desc) {
     const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
@@ -544,7 +491,7 @@ static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int 
         }
         YGZ_CUDA(cudaEventRecord(ex->pyrCopied, ex->d2h));
     }
-    ex->launches += launchFast(ex->G, ex->B, n, ex->stream, fastTensorMaps(ex, n));
+    ex->launches += launchFast(ex->G, ex->B, n, ex->stream);
     YGZ_MARK(3);
     ex->launches += launchQuadtree(ex->G, ex->B, n, ex->stream);
     YGZ_MARK(4);

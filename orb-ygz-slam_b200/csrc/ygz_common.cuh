@@ -1,6 +1,5 @@
 // ygz_common.cuh — shared declarations of libygzorb_cuda.so (sm_100a only).
 #pragma once
-#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -51,7 +50,6 @@ struct FrameGeom {
     int totalCells, totalTiles;   // totalCells: entries of the FAST cell table (cells with a non-empty detection area)
     int tileTab;                  // offset of the blur tile table in DevBuffers::tabs (x = x0 | y0<<12 | level<<24)
     int fastPitch;                // k_fast tile pitch of this geometry (kFastTilePitchNarrow or kFastTilePitch)
-    int fastRows;                 // rows of the largest cell window (maxDh + 6): the TMA box height of k_fast_tma
     int fastRegionA, fastScoreBytes, fastWarpCap;   // k_fast dynamic shared memory layout (bytes, bytes, list entries per warp)
     int cellTab;                  // offset of the cell table in DevBuffers::tabs (8-byte entries)
     int maxListCap;
@@ -61,15 +59,6 @@ struct FrameGeom {
     int umax[16];
     int vmaxOfU[16];   // rows |v| <= vmaxOfU[|u|] of the circular patch hold column u (umax is non-increasing)
     LevelGeom lv[kMaxLevels];
-};
-
-// Tensor maps (TMA descriptors) of the pyramid levels: 3-D byte tensors (x, y, frame) with box = one FAST cell window
-// (kFastTilePitchNarrow bytes x FrameGeom::fastRows rows).  Built on the host (extractor.cu, cuTensorMapEncodeTiled through
-// cudaGetDriverEntryPoint) whenever a base pointer or the geometry changes; `ok` = every level met TMA's alignment rules
-// (16-byte aligned base and strides), else the non-TMA k_fast runs.
-struct TmaMaps {
-    CUtensorMap lv[kMaxLevels];
-    int ok;
 };
 
 struct DevBuffers {
@@ -116,7 +105,7 @@ int cudaFail(cudaError_t e, const char *what, const char *file, int line);
 
 // Kernel launchers (extract_kernels.cu).  Each returns the number of kernel launches it enqueued.
 int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nFrames, cudaStream_t s);
-int launchFast(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s, const TmaMaps *maps = nullptr);
+int launchFast(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s);
 int launchQuadtree(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s);
 int launchBlur(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_t s);
 int launchDescribe(const FrameGeom &G, const DevBuffers &B, int nFrames, int cap, int32_t *counts,

@@ -133,9 +133,9 @@ def test_strided_input_and_repeatability():
 
 
 @pytest.mark.parametrize("w,h,n", [(752, 480, 24), (750, 300, 40), (640, 480, 20)])
-def test_large_batch_takes_the_persistent_fast_kernel(w, h, n):
-    """Batches large enough for k_fast_tma (persistent CTAs, cell windows fetched by TMA two deep) give per-frame results equal
-    to the oracle's; 750 px wide frames have a stride TMA cannot describe and must fall back to k_fast with the same results.
+def test_large_batch_per_frame_results(w, h, n):
+    """Larger batches (the kernels' batch-size dependent choices: strip resize with several sub-tiles per CTA, 384-thread quadtree)
+    give per-frame results equal to the oracle's; 750 px wide frames have 2-byte aligned rows (generic resize and blur paths).
     Textured, mixed-contrast (minThFAST retry cells) and flat frames in one batch."""
     frames = np.stack([synth.textured_frame(w, h, 300 + i) if i % 4 else synth.mixed_frame(w, h, 300 + i) for i in range(n)])
     frames[3] = 90   # a flat frame: every cell retries at minThFAST and finds nothing
