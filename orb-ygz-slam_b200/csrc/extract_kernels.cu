@@ -194,9 +194,28 @@ template <bool PDL> __global__ void __launch_bounds__(256) k_resize(const __grid
 // ends exactly at the row's last word).
 constexpr int kRzTH = 64, kRzThreads = 256, kRzSlots = 16, kRzMaxBand = 160;
 
-template <bool PDL> __global__ void __launch_bounds__(kRzThreads, 6) k_resize_band(const __grid_constant__ FrameGeom G, const DevBuffers B, int level, int nSub) {
+// STAGED = the source band goes global -> shared as 16-byte cp.async chunks (7 per row: the strip's source columns from
+// xs = first window & ~15, kRzRawPitch = 112 bytes; levels that need more — scale factors above ~1.3 — take the LDG form) — no registers, the whole band in flight at once — and the horizontal pass reads it with
+// LDS; the band of sub-tile s + 1 is requested right after the horizontal pass of sub-tile s, so it travels while the vertical
+// pass of s runs.  Needs 16-byte aligned source rows (base and pitch); otherwise the horizontal pass loads its words with LDG.
+constexpr int kRzRawPitch = 112;   // staged bytes per source row of a strip: enough for the 1.2x pyramid (LevelGeom::rawPitch says what a level needs)
+__device__ __forceinline__ void cpAsync16(void *smemDst, const void *gmemSrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smemDst)), "l"(gmemSrc));
+}
+__device__ __forceinline__ void rzStageBand(uint8_t *raw, int rawPitch, const uint8_t *srcStrip, int sp, int xs, int yFirst, int yLast, int tid) {
+    // thread = (chunk column tid & 15, row tid >> 4 + 16 i)
+    const int c = tid & 15;
+    if (16 * c < rawPitch && xs + 16 * c + 16 <= sp) {
+        const uint8_t *g = srcStrip + (long long)(yFirst + (tid >> 4)) * sp + 16 * c;
+        uint8_t *d = raw + (tid >> 4) * rawPitch + 16 * c;
+        for (int y = yFirst + (tid >> 4); y <= yLast; y += kRzThreads / 16, g += (long long)(kRzThreads / 16) * sp, d += (kRzThreads / 16) * rawPitch)
+            cpAsync16(d, g);
+    }
+}
+
+template <bool PDL, bool STAGED> __global__ void __launch_bounds__(kRzThreads, 6) k_resize_band(const __grid_constant__ FrameGeom G, const DevBuffers B, int level, int nSub) {
     if (PDL) pdlEnter(B);
-    extern __shared__ __align__(16) uint2 rzH[];   // [band row][16 column groups]: four 16-bit sums (h >> 4 <= 32640) per group
+    extern __shared__ __align__(16) uint2 rzH[];   // [band row][16 column groups]: four 16-bit sums (h >> 4 <= 32640) per group; STAGED: the raw band behind it
     const LevelGeom &D = G.lv[level];
     const LevelGeom &S = G.lv[level - 1];
     const int f = blockIdx.z, tid = threadIdx.x;
@@ -204,20 +223,41 @@ template <bool PDL> __global__ void __launch_bounds__(kRzThreads, 6) k_resize_ba
     const int cp = tid & 7, vslot = tid >> 3;              // vertical pass mapping: column groups cp and cp + 8
     const int sp = S.pitch;
     const int2 *tY = B.tabs + D.tabY;
-    // pre-digested X table: per column group {coef[4]}, {sel[4]}, {window word offset, shift, third-word offset, -}
+    // pre-digested X table: per column group {coef[4]}, {sel[4]}, {window word offset, shift, third-word offset, strip start xs}
     const int4 *tg = reinterpret_cast<const int4 *>(B.tabs + D.tabXG) + 3 * (blockIdx.x * 16 + cg);
     const int4 coef = __ldg(tg), sel = __ldg(tg + 1), misc = __ldg(tg + 2);
-    const uint8_t *srcCol = levelPtr(G, B, f, level - 1) + misc.x;
+    const uint8_t *srcLevel = levelPtr(G, B, f, level - 1);
+    const uint8_t *srcCol = srcLevel + misc.x;
     const long long step = (long long)kRzSlots * sp;
     uint8_t *dst = B.pyr + (long long)f * G.slabBytes + D.off + (blockIdx.x * 16 + cp) * 4;
     const uint2 *hc = rzH + cp;
+    uint8_t *raw = reinterpret_cast<uint8_t *>(rzH + D.bandRows * 16);
+    const int dy0 = blockIdx.y * nSub * kRzTH;
+    if (dy0 >= D.h) return;
+    int yFirst = __ldg(tY + dy0).x & 0xffff, yLast = (int)((uint32_t)__ldg(tY + min(dy0 + kRzTH - 1, D.h - 1)).x >> 16);
+    constexpr int rawPitch = kRzRawPitch;
+    if (STAGED) rzStageBand(raw, rawPitch, srcLevel + misc.w, sp, misc.w, yFirst, yLast, tid);
     for (int sub = 0; sub < nSub; sub++) {
-        const int dyBase = (blockIdx.y * nSub + sub) * kRzTH;
+        const int dyBase = dy0 + sub * kRzTH;
         if (dyBase >= D.h) break;
         const int dyLast = min(dyBase + kRzTH - 1, D.h - 1);
-        const int yFirst = __ldg(tY + dyBase).x & 0xffff, yLast = (int)((uint32_t)__ldg(tY + dyLast).x >> 16);
-        if (sub > 0) __syncthreads();                      // the previous sub-tile's vertical pass is done with rzH
-        {
+        if (STAGED) asm volatile("cp.async.wait_all;" ::: "memory");
+        if (STAGED || sub > 0) __syncthreads();            // the band has landed; the previous sub-tile's vertical pass is done with rzH
+        if (STAGED) {
+            const uint8_t *p = raw + slot * rawPitch + (misc.x - misc.w);
+            uint2 *hd = rzH + slot * 16 + cg;
+#pragma unroll 2
+            for (int y = yFirst + slot; y <= yLast; y += kRzSlots, p += kRzSlots * rawPitch, hd += kRzSlots * 16) {
+                const uint32_t w0 = *reinterpret_cast<const uint32_t *>(p), w1 = *reinterpret_cast<const uint32_t *>(p + 4);
+                const uint32_t w2 = *reinterpret_cast<const uint32_t *>(p + misc.z);
+                const uint32_t v0 = __funnelshift_r(w0, w1, misc.y), v1 = __funnelshift_r(w1, w2, misc.y);
+                const uint32_t h0 = __dp2a_lo((uint32_t)coef.x, __byte_perm(v0, v1, sel.x), 0u) >> 4;
+                const uint32_t h1 = __dp2a_lo((uint32_t)coef.y, __byte_perm(v0, v1, sel.y), 0u) >> 4;
+                const uint32_t h2 = __dp2a_lo((uint32_t)coef.z, __byte_perm(v0, v1, sel.z), 0u) >> 4;
+                const uint32_t h3 = __dp2a_lo((uint32_t)coef.w, __byte_perm(v0, v1, sel.w), 0u) >> 4;
+                *hd = make_uint2(h1 * 65536u + h0, h3 * 65536u + h2);
+            }
+        } else {
             const uint8_t *p = srcCol + (long long)(yFirst + slot) * sp;
             uint2 *hd = rzH + slot * 16 + cg;
 #pragma unroll 2
@@ -233,10 +273,16 @@ template <bool PDL> __global__ void __launch_bounds__(kRzThreads, 6) k_resize_ba
             }
         }
         __syncthreads();
+        const int yF = yFirst;
+        if (sub + 1 < nSub && dyBase + kRzTH < D.h) {       // next sub-tile's band: known now, requested now (STAGED), used after the vertical pass
+            yFirst = __ldg(tY + dyBase + kRzTH).x & 0xffff;
+            yLast = (int)((uint32_t)__ldg(tY + min(dyBase + 2 * kRzTH - 1, D.h - 1)).x >> 16);
+            if (STAGED) rzStageBand(raw, rawPitch, srcLevel + misc.w, sp, misc.w, yFirst, yLast, tid);
+        }
 #pragma unroll 2
         for (int dy = dyBase + vslot; dy <= dyLast; dy += kRzThreads / 8) {
             const int2 ty = __ldg(tY + dy);
-            const int y0 = (ty.x & 0xffff) - yFirst, y1 = (int)((uint32_t)ty.x >> 16) - yFirst;
+            const int y0 = (ty.x & 0xffff) - yF, y1 = (int)((uint32_t)ty.x >> 16) - yF;
             const uint32_t b0 = (uint32_t)ty.y << 16, b1 = (uint32_t)ty.y & 0xffff0000u;
             uint8_t *d = dst + (long long)dy * D.pitch;
 #pragma unroll
@@ -264,9 +310,18 @@ int launchResizeLevel(const FrameGeom &G, const DevBuffers &B, int level, int nF
         const int tilesY = (D.h + kRzTH - 1) / kRzTH;
         const int nSub = (long long)(D.pitch / 64) * nFrames >= 2048 ? tilesY : ((long long)(D.pitch / 64) * nFrames * ((tilesY + 1) / 2) >= 1024 ? 2 : 1);
         const dim3 bgrid(D.pitch / 64, (tilesY + nSub - 1) / nSub, nFrames);
-        const size_t smem = (size_t)D.bandRows * 16 * sizeof(uint2);
-        if (B.pdl) launchChain(true, k_resize_band<true>, bgrid, dim3(kRzThreads), smem, s, G, B, level, nSub);
-        else k_resize_band<false><<<bgrid, kRzThreads, smem, s>>>(G, B, level, nSub);
+        // cp.async staging of the source band needs 16-byte aligned source rows
+        const uint8_t *srcBase = level == 1 ? B.in : B.pyr + S.off;
+        const long long srcFrame = level == 1 ? B.inFrameStride : G.slabBytes;
+        const bool staged = D.rawPitch > 0 && D.rawPitch <= kRzRawPitch && (S.pitch & 15) == 0 && (reinterpret_cast<uintptr_t>(srcBase) & 15) == 0 && (srcFrame & 15) == 0;
+        const size_t smem = (size_t)D.bandRows * 16 * sizeof(uint2) + (staged ? (size_t)D.bandRows * kRzRawPitch : 0);
+        if (staged) {
+            if (B.pdl) launchChain(true, k_resize_band<true, true>, bgrid, dim3(kRzThreads), smem, s, G, B, level, nSub);
+            else k_resize_band<false, true><<<bgrid, kRzThreads, smem, s>>>(G, B, level, nSub);
+        } else {
+            if (B.pdl) launchChain(true, k_resize_band<true, false>, bgrid, dim3(kRzThreads), smem, s, G, B, level, nSub);
+            else k_resize_band<false, false><<<bgrid, kRzThreads, smem, s>>>(G, B, level, nSub);
+        }
         return 1;
     }
     if (B.pdl) { if (word) launchChain(true, k_resize<true>, grid, block, 0, s, G, B, level); else launchChain(true, k_resize_generic<true>, grid, block, 0, s, G, B, level); }
@@ -834,9 +889,6 @@ __device__ __forceinline__ int reflect101(int p, int len) {
 
 constexpr int kBlurRawPitch = kBlurTW + 32;     // bytes; raw column c <-> image x = x0 - 16 + c (16-byte aligned chunks)
 
-__device__ __forceinline__ void cpAsync16(void *smemDst, const void *gmemSrc) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smemDst)), "l"(gmemSrc));
-}
 
 constexpr int kBlurPairs = kBlurRawRows / 2;    // 19 raw-row pairs (rows 2m, 2m+1)
 static_assert(kBlurRawRows % 2 == 0 && kBlurTH % 8 == 0 && kBlurTW == 256, "k_blur thread mapping");

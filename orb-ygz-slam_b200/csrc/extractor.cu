@@ -172,10 +172,12 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
                 if (mono) L.bandRows = band;
             }
             std::vector<int2> XG;
+            L.rawPitch = 0;
             if (L.bandRows > 0) {
                 // per column group of 4 destination pixels: {coef[4]}, {sel[4]}, {byte offset of the window's first word,
                 // funnel shift, offset of the third word, 0}
                 const int sp = G.lv[l - 1].pitch;
+                int stripXs = 0, rawNeed = 0;
                 for (int g = 0; g < L.pitch / 4; g++) {
                     const int2 *e = &X[4 * g];
                     const int base = e[0].x & 0xffff;
@@ -187,8 +189,11 @@ static int makeGeometry(const ygzorb_params &P, const Tables &T, int w, int h, i
                     }
                     XG.push_back(make_int2(e[0].y, e[1].y)); XG.push_back(make_int2(e[2].y, e[3].y));
                     XG.push_back(make_int2(sel[0], sel[1])); XG.push_back(make_int2(sel[2], sel[3]));
-                    XG.push_back(make_int2(bs & ~3, 8 * (bs & 3))); XG.push_back(make_int2((bs & ~3) + 12 <= sp ? 8 : 4, 0));
+                    if (g % 16 == 0) stripXs = bs & ~15;       // k_resize_band<STAGED>: the strip's staged columns start here
+                    rawNeed = std::max(rawNeed, (bs & ~3) + 12 - stripXs);   // the three words of this group's window
+                    XG.push_back(make_int2(bs & ~3, 8 * (bs & 3))); XG.push_back(make_int2((bs & ~3) + 12 <= sp ? 8 : 4, stripXs));
                 }
+                L.rawPitch = alignUp(rawNeed, 16) <= 256 ? alignUp(rawNeed, 16) : 0;
             }
             if (tabs.size() % 2) tabs.push_back(make_int2(0, 0));
             L.tabX = (int)tabs.size(); tabs.insert(tabs.end(), X.begin(), X.end());

@@ -39,6 +39,7 @@ struct LevelGeom {
     int area2x;               // cv::resize switches exact 2x decimation to INTER_AREA
     int fastResize;           // the level's tables satisfy the assumptions of the word-based k_resize
     int tabXG;                // k_resize_band: pre-digested X table, 3 x int4 per column group (offset in 8-byte entries, 16-byte aligned)
+    int rawPitch;             // k_resize_band<STAGED>: bytes of a source row one strip stages (multiple of 16, <= 256); 0 = not stageable
     int bandRows;             // k_resize_band: most source rows (y0(first) .. y1(last)) any 64-row destination tile touches; 0 = not usable
     int tileStart, tilesX, tilesY;  // blur tiles
 };
