@@ -764,7 +764,11 @@ def build_line(args, world, B, cap, ms, ms_e2e, launches, clocks, stage_ms, n_kp
                 "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "note": "the kernel is ALU-pipe / issue bound (ncu: 85 % issue-slot utilisation, DRAM 4 %), see DESIGN.md 5",
                 "launches_in_stage": launches_per_stage, "algorithmic_bytes_per_launch": dom_bytes / launches_per_stage,
-                "pipeline_staged_GBps": staged, "pipeline_frac": staged / hbm_peak}
+                "pipeline_staged_GBps": staged, "pipeline_frac": staged / hbm_peak,
+                # the streaming stages beside the dominant one: algorithmic bytes of the stage / its event time
+                "per_stage": {k: {"achieved": STAGE_BYTES[kern_stages[k]] * B / (stage_ms[k] * 1e-3) / 1e9,
+                                  "frac": STAGE_BYTES[kern_stages[k]] * B / (stage_ms[k] * 1e-3) / 1e9 / hbm_peak}
+                              for k in ("pyramid", "fast", "blur")}}
     mp_bytes = sum(int(h_mp[k].numel() * h_mp[k].element_size()) for k in mp_keys)
     return {
         "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
