@@ -288,6 +288,7 @@ constexpr int kInSlots = YGZ_IN_SLOTS;   // host-input staging slots
 
 struct Extractor {
     ygzorb_params params;
+    cudaStream_t side = nullptr; cudaEvent_t sideGo = nullptr, sideDone = nullptr;   // blur beside the quadtree (batches)
     Tables tables;
     int device = 0, maxBatch = 1;
     cudaStream_t stream = nullptr;
@@ -496,12 +497,36 @@ static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int 
         }
         YGZ_CUDA(cudaEventRecord(ex->pyrCopied, ex->d2h));
     }
-    ex->launches += launchFast(ex->G, ex->B, n, ex->stream);
-    YGZ_MARK(3);
-    ex->launches += launchQuadtree(ex->G, ex->B, n, ex->stream);
-    YGZ_MARK(4);
-    ex->launches += launchBlur(ex->G, ex->B, n, ex->stream);
-    YGZ_MARK(5);
+#ifndef YGZ_BLUR_SIDE
+#define YGZ_BLUR_SIDE 1
+#endif
+    if (YGZ_BLUR_SIDE && !pdl && !ex->profiling) {
+        // batches: the blur (which only needs the pyramid) runs on a side stream beside the quadtree, whose CTAs leave half of
+        // the issue slots idle (barrier-separated passes)
+        if (!ex->side) {
+            YGZ_CUDA(cudaStreamCreateWithFlags(&ex->side, cudaStreamNonBlocking));
+            YGZ_CUDA(cudaEventCreateWithFlags(&ex->sideGo, cudaEventDisableTiming));
+            YGZ_CUDA(cudaEventCreateWithFlags(&ex->sideDone, cudaEventDisableTiming));
+        }
+        if (YGZ_BLUR_SIDE == 2) YGZ_CUDA(cudaEventRecord(ex->sideGo, ex->stream));
+        ex->launches += launchFast(ex->G, ex->B, n, ex->stream);
+        YGZ_MARK(3);
+        if (YGZ_BLUR_SIDE == 1) YGZ_CUDA(cudaEventRecord(ex->sideGo, ex->stream));
+        YGZ_CUDA(cudaStreamWaitEvent(ex->side, ex->sideGo, 0));
+        ex->launches += launchBlur(ex->G, ex->B, n, ex->side);
+        YGZ_CUDA(cudaEventRecord(ex->sideDone, ex->side));
+        ex->launches += launchQuadtree(ex->G, ex->B, n, ex->stream);
+        YGZ_MARK(4);
+        YGZ_CUDA(cudaStreamWaitEvent(ex->stream, ex->sideDone, 0));
+        YGZ_MARK(5);
+    } else {
+        ex->launches += launchFast(ex->G, ex->B, n, ex->stream);
+        YGZ_MARK(3);
+        ex->launches += launchQuadtree(ex->G, ex->B, n, ex->stream);
+        YGZ_MARK(4);
+        ex->launches += launchBlur(ex->G, ex->B, n, ex->stream);
+        YGZ_MARK(5);
+    }
     const int os = outDev ? 0 : (int)(ex->outSeq++ & 1u);
     int32_t *oc = outDev ? counts : ex->dOutCounts[os];
     ygzorb_keypoint *ok = outDev ? kps : ex->dOutKps[os];
@@ -623,8 +648,10 @@ void ygzorb_extractor_destroy(ygzorb_extractor *h) {
     Extractor *ex = (Extractor *)h;
     if (!ex) return;
     cudaSetDevice(ex->device);
-    cudaStream_t streams[] = {ex->h2d, ex->stream, ex->d2h};
+    cudaStream_t streams[] = {ex->h2d, ex->stream, ex->d2h, ex->side};
     for (cudaStream_t st : streams) if (st) cudaStreamSynchronize(st);
+    if (ex->sideGo) cudaEventDestroy(ex->sideGo);
+    if (ex->sideDone) cudaEventDestroy(ex->sideDone);
     for (int sl = 0; sl < kInSlots; sl++) if (ex->dIn[sl]) cudaFree(ex->dIn[sl]);
     void *bufs[] = {ex->dPyr, ex->dBlur, ex->dTabs, ex->dCand, ex->dNodeOf, ex->dKept, ex->dCounts,
                     ex->dOutCounts[0], ex->dOutCounts[1], ex->dOutKps[0], ex->dOutKps[1], ex->dOutDesc[0], ex->dOutDesc[1],
