@@ -27,7 +27,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 METRIC = "ORB frames/sec (752x480, 1000 kp, 8 lvl) and Hamming matches/sec vs CPU"
 W, H, NFEAT, SCALE, LEVELS, INI_TH, MIN_TH = 752, 480, 1000, 1.2, 8, 20, 7
 N_MAPPOINTS = 3000
-N_SLOTS = 2   # device buffer sets of the e2e leg (MapPoints in, results out); 3 and 4 measured slower (uploads run too far ahead of the frames)
+N_SLOTS = 2   # device buffer sets of the e2e leg (MapPoints in, results out); 3 measured 2 % slower
 # algorithmic bytes per 752x480 frame, stage by stage (inputs read once + outputs written once)
 STAGE_BYTES = {"pyramid": 1845634, "fast": 1117367, "blur": 2234734, "quadtree_orient_desc": 60000}
 STAGED_TOTAL = 5257735
@@ -474,8 +474,9 @@ def run_ours(args, rank, local_rank, world):
     host_in.numpy()[:] = frames_np
     dev_in = host_in.to(dev)
     ex = Y.Extractor(NFEAT, SCALE, LEVELS, INI_TH, MIN_TH, max_batch=B, device=local_rank)
-    if args.pipe >= 0:
-        ex.set_pipeline(args.pipe)
+    # host-input calls of the e2e leg: three upload chunks per step (171 frames of 512) measured best (256: -3 %, 128: -3 %, 64: -8 %):
+    # a MapPoint upload waits behind at most one 1.1 ms frame chunk, and the kernels still run on batches large enough
+    ex.set_pipeline(args.pipe if args.pipe >= 0 else (args.batch + 2) // 3)
     mt = Y.Matcher(local_rank)
     mt.set_stream(ex.stream())          # the search consumes the extraction's device-resident outputs in stream order
     cap = ex.max_keypoints(W, H)
@@ -524,6 +525,7 @@ def run_ours(args, rank, local_rank, world):
     # MapPoint upload and the result download run on two side streams here, ordered by events.
     copy_in, copy_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
     slots = []
+    N_SLOTS = args.slots
     for sl in range(N_SLOTS):
         o = d_out if sl == 0 else {k: torch.zeros_like(v) for k, v in d_out.items()}
         m = d_mp if sl == 0 else {k: torch.zeros_like(v) for k, v in d_mp.items()}
@@ -536,6 +538,7 @@ def run_ours(args, rank, local_rank, world):
             "mp_ready": torch.cuda.Event(), "search_done": torch.cuda.Event(), "out_done": torch.cuda.Event()})
     h_out = slots[0]["h_out"]
     host_step = [0]
+    timeline = [] if args.timeline else None   # --timeline: per-step event times of the e2e leg (diagnostic, on stderr)
 
     up_keys = [list(mp_keys)]                           # the MapPoint fields uploaded every step (all of them: the headline e2e)
 
@@ -543,25 +546,32 @@ def run_ours(args, rank, local_rank, world):
         S = slots[host_step[0] % N_SLOTS]
         host_step[0] += 1
         copy_in.wait_event(S["search_done"])            # the previous search on this slot has read its MapPoints
-        # ... and the previous STEP's search is done: the MapPoints of a step go up while its extraction runs, not earlier, so the
-        # frames (needed first) do not share the link with records needed last (running further ahead measured slower)
-        copy_in.wait_event(slots[(host_step[0] - 2) % N_SLOTS]["search_done"])
+        # The upload is NOT held back until the previous step's search is done (round 1 did that): the copy engine serves copies in
+        # the order they become ready, and a MapPoint upload that becomes ready late queues behind up to three frame chunks (5 ms),
+        # stalling its search and, behind it in the stream, the next extraction (bench.py --timeline shows the bubbles).
+        tl = [torch.cuda.Event(enable_timing=True) for _ in range(5)] if timeline is not None else None
         with torch.cuda.stream(copy_in):
+            if tl: tl[0].record(copy_in)
             for k in up_keys[0]:
                 S["mp"][k].copy_(h_mp[k], non_blocking=True)
             S["mp_ready"].record(copy_in)
+            if tl: tl[1].record(copy_in)
         stream.wait_event(S["out_done"])                # the previous results of this slot are on the host
         o = S["out"]
         ex.extract_raw(host_in.data_ptr(), B, W, H, W, W * H, Y.OUT_DEVICE | Y.NO_SYNC, cap,
                        o["counts"].data_ptr(), o["kps"].data_ptr(), o["desc"].data_ptr())
+        if tl: tl[2].record(stream)
         stream.wait_event(S["mp_ready"])
         search(S["F"], S["P"], o, S["best"])
         S["search_done"].record(stream)
+        if tl: tl[3].record(stream)
         copy_out.wait_event(S["search_done"])
         with torch.cuda.stream(copy_out):
             for k in o:
                 S["h_out"][k].copy_(o[k], non_blocking=True)
             S["out_done"].record(copy_out)
+            if tl: tl[4].record(copy_out)
+        if tl: timeline.append(tl)
 
     def drain_host():                                    # the timed region ends when the last download has landed
         for S in slots:
@@ -606,7 +616,15 @@ def run_ours(args, rank, local_rank, world):
         step_host()
     ex.sync()
     torch.cuda.synchronize()
+    if timeline is not None:
+        timeline.clear()
     ms_e2e, _ = timed(step_host, args.steps, drain_host)
+    if timeline:
+        t0 = timeline[0][0]
+        sys.stderr.write("e2e timeline, ms since the first MapPoint upload began: [mp_up start, mp_up end, extraction end, search end, download end]\n")
+        for tl in timeline:
+            sys.stderr.write("  " + " ".join("%7.3f" % t0.elapsed_time(e) for e in tl) + "\n")
+        timeline = None
     for S in slots:
         assert int(S["h_out"]["counts"].sum().item()) == n_kp and int(S["h_out"]["nm"].sum().item()) == n_match, \
             "host and device paths disagree"
@@ -846,12 +864,14 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=512)
+    ap.add_argument("--slots", type=int, default=N_SLOTS, help="device buffer sets of the e2e leg")
+    ap.add_argument("--timeline", action="store_true", help="print per-step event times of the e2e leg to stderr")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline and kNN legs")
     ap.add_argument("--no-mixed", action="store_true", help="skip the second (mixed-contrast) workload")
     ap.add_argument("--no-sharded", action="store_true", help="skip the sharded block (configs[3] and [4] through the multi-GPU layer)")
     ap.add_argument("--shard-frames", type=int, default=4096, help="frames of configs[3]")
     ap.add_argument("--shard-queries", type=int, default=1 << 20, help="query = train rows of configs[4]")
-    ap.add_argument("--pipe", type=int, default=-1, help="frames per pipelined upload chunk of the e2e leg (-1: library default)")
+    ap.add_argument("--pipe", type=int, default=-1, help="frames per pipelined upload chunk of the e2e leg (-1: a third of the batch; 0: one chunk)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
