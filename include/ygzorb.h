@@ -30,6 +30,11 @@ extern "C" {
 #define YGZORB_OUT_DEVICE 2u   /* counts / keypoints / descriptors pointers are device memory */
 #define YGZORB_KEEP_STAGES 4u  /* one chunk per max_batch frames (no upload pipelining), so that the stage taps
                                   (pyramid, blurred levels, FAST candidates) cover every frame of the call */
+#define YGZORB_OUT_PINNED 32u   /* counts / keypoints / descriptors are PAGE-LOCKED host memory (ygzorb_host_alloc, cudaHostAlloc,
+                                 * cudaHostRegister): calls of up to 8 frames let the last kernel write them directly (no device slot,
+                                 * no three device-to-host copies: ~30 us less per live-tracking frame).  Ignored for larger calls and
+                                 * together with YGZORB_OUT_DEVICE.  Passing pageable memory with this flag is an error the library
+                                 * cannot detect cheaply: the kernel would fault. */
 #define YGZORB_NO_SYNC 8u      /* return after enqueueing; caller calls ygzorb_extractor_sync() */
 
 const char *ygzorb_last_error(void);

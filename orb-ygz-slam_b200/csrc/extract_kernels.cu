@@ -585,7 +585,10 @@ int launchFast(const FrameGeom &G, const DevBuffers &B, int nFrames, cudaStream_
 //    inside a node is the original vToDistributeKeys order, carried here by the candidates' order key.
 // So points never move: each point carries the index of its node, and a pass is two sweeps over the
 // points (count children, relabel) plus block-wide scans over the node list.
-constexpr int kQtThreads = 512;        // CTA size for small batches (one frame: latency); batches run kQtThreadsBatch
+#ifndef YGZ_QT_SINGLE
+#define YGZ_QT_SINGLE 1024
+#endif
+constexpr int kQtThreads = YGZ_QT_SINGLE;        // CTA size for small batches (one frame: latency; 1024: 41 us, 512: 44, 256: 56 on 640x480); batches run kQtThreadsBatch
 constexpr int kQtThreadsBatch = 384;   // more CTAs per SM hide the barrier stalls of the passes (0.47 -> 0.42 ms / 512 frames at 384 threads; 256: 0.43, 192: 0.47, 448: 0.59)
 
 struct QtSmem {

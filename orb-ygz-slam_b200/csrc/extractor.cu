@@ -471,7 +471,9 @@ static int sinkPyramid(Extractor *ex, int n) {
 // Kernels of one chunk (its input already uploaded into `slot` when it comes from the host).
 static int extractChunk(Extractor *ex, const uint8_t *frames, int n, int w, int h, size_t frameStride, int srcPitch,
                         unsigned flags, int cap, int slot, int32_t *counts, ygzorb_keypoint *kps, uint8_t *desc) {
-    const bool inDev = flags & YGZORB_IN_DEVICE, outDev = flags & YGZORB_OUT_DEVICE;
+    const bool inDev = flags & YGZORB_IN_DEVICE;
+    // page-locked host outputs of a small call are written by k_describe itself (UVA: the host pointer is a device pointer)
+    const bool outDev = (flags & YGZORB_OUT_DEVICE) || ((flags & YGZORB_OUT_PINNED) && n <= kPdlMaxFrames);
     int rc;
     YGZ_MARK(0);
     if ((rc = bindInput(ex, frames, w, h, frameStride, inDev, slot))) return rc;

@@ -108,7 +108,8 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
     preparePyramidSink(image.cols, image.rows);
     ensureStage((size_t)image.cols * image.rows, cap);
     for (int r = 0; r < image.rows; r++) std::memcpy(mStage + (size_t)r * image.cols, image.ptr(r), (size_t)image.cols);
-    if (ygzorb_extract_batch(mHandle, mStage, 1, image.cols, image.rows, image.cols, 0, 0, cap, mStageCount, mStageKps, mStageDesc) != 0)
+    // the staging slab is page-locked (ygzorb_host_alloc): the last kernel writes the results into it directly
+    if (ygzorb_extract_batch(mHandle, mStage, 1, image.cols, image.rows, image.cols, 0, YGZORB_OUT_PINNED, cap, mStageCount, mStageKps, mStageDesc) != 0)
         fail("ygzorb_extract_batch");
     const int32_t n = *mStageCount;
     downloadPyramid(image.cols, image.rows);                          // ComputePyramid(image) side effect (:979)
