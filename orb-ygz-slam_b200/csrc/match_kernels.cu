@@ -233,7 +233,12 @@ size_t knnPartialBytes(int nq, int splits) { return (size_t)nq * splits * sizeof
 // indices < j, so after t rounds the first t MapPoints are final and the fixed point IS the serial
 // result.  Candidates are visited in the reference's order (cell column, cell row, insertion order)
 // by one thread per MapPoint, which keeps the first-wins / strict-< top-2 rule literal.
-constexpr int kProjThreads = 1024;
+// CTA size: 1024 threads (one CTA per SM at 64 registers) measured best on 512 frames x 3000 MapPoints: 0.434 ms; 768: 0.473,
+// 512 (two CTAs per SM): 0.445, 384: 0.526
+#ifndef YGZ_PROJ_THREADS
+#define YGZ_PROJ_THREADS 1024
+#endif
+constexpr int kProjThreads = YGZ_PROJ_THREADS;
 
 __device__ int projScan(int *a, int n, int *ws) {   // in-place exclusive scan by the CTA, returns the total
     const int T = kProjThreads, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
